@@ -1,0 +1,534 @@
+// bre_api.cu -- the extern "C" boundary of libbre.so (see include/bre.h).
+#include "bre_internal.cuh"
+#include <cmath>
+#include <cstring>
+#include <vector>
+
+namespace bre {
+
+int set_err(bre_ctx *c, int code, const std::string &msg) {
+    if (c) c->err = msg;
+    return code;
+}
+int check_cuda(bre_ctx *c, cudaError_t e, const char *what) {
+    if (e == cudaSuccess) return BRE_OK;
+    return set_err(c, BRE_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+int ensure(bre_ctx *c, Buf &b, size_t bytes) {
+    if (bytes == 0) bytes = 16;
+    if (b.cap >= bytes) return BRE_OK;
+    if (b.p) { cudaFree(b.p); b.p = nullptr; b.cap = 0; }
+    size_t cap = bytes + bytes / 8;
+    cudaError_t e = cudaMalloc(&b.p, cap);
+    if (e != cudaSuccess) {
+        b.p = nullptr;
+        return set_err(c, BRE_ERR_NOMEM, std::string("cudaMalloc(") + std::to_string(cap) + "): " + cudaGetErrorString(e));
+    }
+    b.cap = cap;
+    return BRE_OK;
+}
+int grow_photon_store(bre_ctx *ctx, uint64_t newCount);
+
+// pack AoS float triples into float4 (w from a scalar or a per-element array)
+__global__ void __launch_bounds__(256) k_pack3(const float *__restrict__ in3, uint64_t n,
+                                               const float *__restrict__ w, float wconst,
+                                               float4 *__restrict__ out) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = make_float4(in3[3 * i], in3[3 * i + 1], in3[3 * i + 2], w ? w[i] : wconst);
+}
+__global__ void __launch_bounds__(256) k_unpack3(const float4 *__restrict__ in, uint64_t n,
+                                                 float *__restrict__ out3, float *__restrict__ w) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 v = in[i];
+    if (out3) { out3[3 * i] = v.x; out3[3 * i + 1] = v.y; out3[3 * i + 2] = v.z; }
+    if (w) w[i] = v.w;
+}
+__global__ void __launch_bounds__(256) k_set_w(float4 *__restrict__ a, uint64_t n, float w) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) a[i].w = w;
+}
+
+static void host_coordinate_system(const float v1[3], float v2[3], float v3[3]) {
+    // same arithmetic as oracle coordinate_system / reference geometry.h:1020-1027
+    if (std::fabs(v1[0]) > std::fabs(v1[1])) {
+        float inv = 1.f / std::sqrt(v1[0] * v1[0] + v1[2] * v1[2]);
+        v2[0] = -v1[2] * inv; v2[1] = 0.f; v2[2] = v1[0] * inv;
+    } else {
+        float inv = 1.f / std::sqrt(v1[1] * v1[1] + v1[2] * v1[2]);
+        v2[0] = 0.f; v2[1] = v1[2] * inv; v2[2] = -v1[1] * inv;
+    }
+    double ax = v1[0], ay = v1[1], az = v1[2], bx = v2[0], by = v2[1], bz = v2[2];
+    v3[0] = (float)((ay * bz) - (az * by));
+    v3[1] = (float)((az * bx) - (ax * bz));
+    v3[2] = (float)((ax * by) - (ay * bx));
+}
+
+// upload n*3 host floats and pack to float4 at dst[dstOff...]
+static int upload_pack(bre_ctx *ctx, const float *h3, uint64_t n, const float *hw, float wconst,
+                       float4 *dst) {
+    int s;
+    size_t bytes3 = (size_t)n * 12, bytesw = hw ? (size_t)n * 4 : 0;
+    size_t offw = (bytes3 + 15) & ~(size_t)15;
+    if ((s = ensure(ctx, ctx->scratch, offw + bytesw + 64)) != BRE_OK) return s;
+    float *d3 = (float *)ctx->scratch.p;
+    float *dw = hw ? (float *)((char *)ctx->scratch.p + offw) : nullptr;
+    BRE_CUDA(cudaMemcpyAsync(d3, h3, bytes3, cudaMemcpyHostToDevice, ctx->stream));
+    if (hw) BRE_CUDA(cudaMemcpyAsync(dw, hw, bytesw, cudaMemcpyHostToDevice, ctx->stream));
+    k_pack3<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(d3, n, dw, wconst, dst);
+    BRE_CUDA(cudaGetLastError());
+    // scratch is reused by the next call: finish before returning
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return BRE_OK;
+}
+
+}  // namespace bre
+
+using namespace bre;
+
+#define CTX_CHECK()                          \
+    if (!ctx) return BRE_ERR_INVALID;        \
+    cudaSetDevice(ctx->device)
+
+extern "C" {
+
+int bre_abi_version(void) { return BRE_ABI_VERSION; }
+
+int bre_create(bre_ctx **out, const bre_config *cfg) {
+    if (!out) return BRE_ERR_INVALID;
+    *out = nullptr;
+    int nDev = 0;
+    cudaError_t e = cudaGetDeviceCount(&nDev);
+    if (e != cudaSuccess || nDev == 0) return BRE_ERR_NO_DEVICE;  // no CPU fallback
+    bre_ctx *ctx = new bre_ctx();
+    if (cfg) {
+        ctx->device = cfg->device;
+        ctx->n_ranks = cfg->n_ranks > 0 ? cfg->n_ranks : 1;
+        ctx->rank = cfg->rank;
+        if (cfg->max_leaf_photons > 0) ctx->max_leaf = cfg->max_leaf_photons;
+        if (cfg->tau_steps > 0) ctx->tau_steps = cfg->tau_steps;
+    }
+    if (ctx->device < 0 || ctx->device >= nDev || ctx->max_leaf > 16 || ctx->rank < 0 ||
+        ctx->rank >= ctx->n_ranks) {
+        delete ctx;
+        return BRE_ERR_INVALID;
+    }
+    if (cudaSetDevice(ctx->device) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete ctx;
+        return BRE_ERR_CUDA;
+    }
+    if (ctx->n_ranks > 1) {
+        if (!cfg->nccl_unique_id) { cudaStreamDestroy(ctx->stream); delete ctx; return BRE_ERR_INVALID; }
+        int s = nccl_init(ctx, cfg->nccl_unique_id);
+        if (s != BRE_OK) { cudaStreamDestroy(ctx->stream); delete ctx; return s; }
+    }
+    *out = ctx;
+    return BRE_OK;
+}
+
+int bre_destroy(bre_ctx *ctx) {
+    if (!ctx) return BRE_ERR_INVALID;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    nccl_destroy(ctx);
+    Buf *bufs[] = {&ctx->density, &ctx->pos_r, &ctx->pow, &ctx->dir, &ctx->s_pos_r, &ctx->s_pow,
+                   &ctx->s_dir, &ctx->order, &ctx->codes, &ctx->keys_alt, &ctx->vals_alt, &ctx->hist,
+                   &ctx->node_lo, &ctx->node_hi, &ctx->node_range, &ctx->parent, &ctx->leaf_lo,
+                   &ctx->leaf_hi, &ctx->flags, &ctx->fast, &ctx->scratch, &ctx->rays_o, &ctx->rays_d,
+                   &ctx->out_rgb, &ctx->tau, &ctx->hit_counts, &ctx->hit_offsets, &ctx->hit_idx,
+                   &ctx->counters_d, &ctx->pix_idx, &ctx->film, &ctx->path_counts, &ctx->path_offsets};
+    for (Buf *b : bufs) if (b->p) cudaFree(b->p);
+    if (ctx->lights_d) cudaFree(ctx->lights_d);
+    for (int i = 0; i < 8; ++i)
+        for (int j = 0; j < 2; ++j) if (ctx->ev[i][j]) cudaEventDestroy(ctx->ev[i][j]);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return BRE_OK;
+}
+
+const char *bre_last_error(const bre_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+void *bre_get_stream(bre_ctx *ctx) { return ctx ? (void *)ctx->stream : nullptr; }
+int bre_synchronize(bre_ctx *ctx) {
+    CTX_CHECK();
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return BRE_OK;
+}
+int bre_nccl_unique_id(void *out128) { return nccl_unique_id(out128); }
+
+// ---------------------------------------------------------------- scene
+int bre_set_medium_homogeneous(bre_ctx *ctx, const float sa[3], const float ss[3], float g) {
+    CTX_CHECK();
+    if (!sa || !ss) return set_err(ctx, BRE_ERR_INVALID, "null sigma");
+    MediumDev &m = ctx->medium;
+    memset(&m, 0, sizeof(m));
+    m.kind = 0;
+    for (int k = 0; k < 3; ++k) { m.sigma_a[k] = sa[k]; m.sigma_s[k] = ss[k]; m.sigma_t[k] = sa[k] + ss[k]; }
+    m.g = g;
+    ctx->have_medium = true;
+    return BRE_OK;
+}
+
+int bre_set_medium_grid(bre_ctx *ctx, const float sa[3], const float ss[3], float g, int nx, int ny,
+                        int nz, const float *density, const float w2m[16]) {
+    CTX_CHECK();
+    if (!sa || !ss || !density || !w2m || nx < 1 || ny < 1 || nz < 1)
+        return set_err(ctx, BRE_ERR_INVALID, "bad grid medium arguments");
+    // GridDensityMedium requires a spectrally uniform sigma_t (media/grid.h:63-67)
+    float st0 = sa[0] + ss[0];
+    if (sa[1] + ss[1] != st0 || sa[2] + ss[2] != st0)
+        return set_err(ctx, BRE_ERR_INVALID, "GridDensityMedium requires a spectrally uniform attenuation coefficient");
+    int s = bre_set_medium_homogeneous(ctx, sa, ss, g);
+    if (s != BRE_OK) return s;
+    MediumDev &m = ctx->medium;
+    size_t cnt = (size_t)nx * ny * nz;
+    if ((s = ensure(ctx, ctx->density, cnt * 4)) != BRE_OK) { ctx->have_medium = false; return s; }
+    BRE_CUDA(cudaMemcpyAsync(ctx->density.p, density, cnt * 4, cudaMemcpyHostToDevice, ctx->stream));
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    float maxDensity = 0;  // grid.h:69-73
+    for (size_t i = 0; i < cnt; ++i) maxDensity = std::max(maxDensity, density[i]);
+    m.kind = 1;
+    m.nx = nx; m.ny = ny; m.nz = nz;
+    m.density = (const float *)ctx->density.p;
+    m.invMaxDensity = 1 / maxDensity;
+    memcpy(m.w2m, w2m, 12 * sizeof(float));
+    return BRE_OK;
+}
+
+int bre_set_lights(bre_ctx *ctx, int n, const bre_light *lights) {
+    CTX_CHECK();
+    if (n < 1 || n > BRE_MAX_LIGHTS || !lights) return set_err(ctx, BRE_ERR_INVALID, "1..64 lights required");
+    std::vector<LightsDev> hv(1);
+    LightsDev &h = hv[0];
+    memset(&h, 0, sizeof(h));
+    h.n = n;
+    const float Pi = BRE_PI;
+    for (int i = 0; i < n; ++i) {
+        LightDev &L = h.l[i];
+        L.kind = lights[i].kind;
+        if (L.kind != 0 && L.kind != 1) return set_err(ctx, BRE_ERR_UNSUPPORTED, "only point and spot lights");
+        memcpy(L.pos, lights[i].pos, 12); memcpy(L.I, lights[i].I, 12); memcpy(L.axis, lights[i].axis, 12);
+        L.cosTotalWidth = lights[i].cos_total_width;
+        L.cosFalloffStart = lights[i].cos_falloff_start;
+        if (L.kind == 1) host_coordinate_system(L.axis, L.ax, L.ay);
+        float p[3];
+        for (int c = 0; c < 3; ++c) {
+            if (L.kind == 0) p[c] = 4 * Pi * L.I[c];                                                // point.cpp:55
+            else p[c] = L.I[c] * 2 * Pi * (1 - .5f * (L.cosFalloffStart + L.cosTotalWidth));        // spot.cpp:75-77
+        }
+        h.func[i] = 0.212671f * p[0] + 0.715160f * p[1] + 0.072169f * p[2];
+    }
+    // Distribution1D, sampling.h:55-75
+    h.cdf[0] = 0;
+    for (int i = 0; i < n; ++i) h.cdf[i + 1] = h.cdf[i] + h.func[i] / n;
+    h.funcInt = h.cdf[n];
+    if (h.funcInt == 0) for (int i = 1; i <= n; ++i) h.cdf[i] = (float)i / (float)n;
+    else for (int i = 1; i <= n; ++i) h.cdf[i] /= h.funcInt;
+    if (!ctx->lights_d) BRE_CUDA(cudaMalloc(&ctx->lights_d, sizeof(LightsDev)));
+    BRE_CUDA(cudaMemcpyAsync(ctx->lights_d, &h, sizeof(LightsDev), cudaMemcpyHostToDevice, ctx->stream));
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->n_lights = n;
+    return BRE_OK;
+}
+
+int bre_set_bounds(bre_ctx *ctx, const float lo[3], const float hi[3]) {
+    CTX_CHECK();
+    if (!lo || !hi) return set_err(ctx, BRE_ERR_INVALID, "null bounds");
+    for (int k = 0; k < 3; ++k) {
+        if (!(lo[k] < hi[k])) return set_err(ctx, BRE_ERR_INVALID, "empty bounds");
+        ctx->blo[k] = lo[k]; ctx->bhi[k] = hi[k];
+    }
+    ctx->have_bounds = true;
+    return BRE_OK;
+}
+
+int bre_set_triangles(bre_ctx *ctx, uint32_t, const float *, const uint32_t *, const float *) {
+    if (!ctx) return BRE_ERR_INVALID;
+    return set_err(ctx, BRE_ERR_UNSUPPORTED,
+                   "surface photon tracing is not built yet (SURVEY.md 8f-1); use bre_set_bounds or bre_upload_photons");
+}
+
+// ---------------------------------------------------------------- photons
+int bre_trace_photons(bre_ctx *ctx, uint64_t first, uint64_t nPaths, int maxDepth, float radius,
+                      uint64_t *nStored) {
+    CTX_CHECK();
+    if (!(radius > 0.f)) return set_err(ctx, BRE_ERR_INVALID, "radius must be > 0");
+    int s = trace_photons(ctx, first, nPaths, maxDepth, radius);
+    if (s != BRE_OK) return s;
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (nStored) *nStored = ctx->n_photons;
+    return BRE_OK;
+}
+
+int bre_upload_photons(bre_ctx *ctx, uint64_t n, const float *p, const float *alpha, const float *wi,
+                       float radius, const float *radii, int append) {
+    CTX_CHECK();
+    if (n > 0 && (!p || !alpha || !wi)) return set_err(ctx, BRE_ERR_INVALID, "null photon arrays");
+    if (!radii && n > 0 && !(radius > 0.f)) return set_err(ctx, BRE_ERR_INVALID, "radius must be > 0");
+    if (!append) ctx->n_photons = 0;
+    ctx->built = false;
+    if (n == 0) return BRE_OK;
+    int s = grow_photon_store(ctx, ctx->n_photons + n);
+    if (s != BRE_OK) return s;
+    uint64_t off = ctx->n_photons;
+    if ((s = upload_pack(ctx, p, n, radii, radius, (float4 *)ctx->pos_r.p + off)) != BRE_OK) return s;
+    if ((s = upload_pack(ctx, alpha, n, nullptr, 0.f, (float4 *)ctx->pow.p + off)) != BRE_OK) return s;
+    if ((s = upload_pack(ctx, wi, n, nullptr, 0.f, (float4 *)ctx->dir.p + off)) != BRE_OK) return s;
+    ctx->n_photons += n;
+    return BRE_OK;
+}
+
+int bre_clear_photons(bre_ctx *ctx) {
+    CTX_CHECK();
+    ctx->n_photons = 0;
+    ctx->built = false;
+    return BRE_OK;
+}
+
+int bre_photon_count(bre_ctx *ctx, uint64_t *n) {
+    if (!ctx || !n) return BRE_ERR_INVALID;
+    *n = ctx->n_photons;
+    return BRE_OK;
+}
+
+int bre_download_photons(bre_ctx *ctx, uint64_t cap, float *p, float *alpha, float *wi, float *radii) {
+    CTX_CHECK();
+    uint64_t n = ctx->n_photons < cap ? ctx->n_photons : cap;
+    if (n == 0) return BRE_OK;
+    int s;
+    if ((s = ensure(ctx, ctx->scratch, (size_t)n * 16 + 64)) != BRE_OK) return s;
+    float *d3 = (float *)ctx->scratch.p, *dw = d3 + 3 * n;
+    const float4 *src[3] = {(const float4 *)ctx->pos_r.p, (const float4 *)ctx->pow.p, (const float4 *)ctx->dir.p};
+    float *dst[3] = {p, alpha, wi};
+    for (int a = 0; a < 3; ++a) {
+        if (!dst[a] && !(a == 0 && radii)) continue;
+        k_unpack3<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(src[a], n, d3, a == 0 ? dw : nullptr);
+        BRE_CUDA(cudaGetLastError());
+        if (dst[a]) BRE_CUDA(cudaMemcpyAsync(dst[a], d3, (size_t)n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+        if (a == 0 && radii) BRE_CUDA(cudaMemcpyAsync(radii, dw, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    return BRE_OK;
+}
+
+int bre_set_radius(bre_ctx *ctx, float radius) {
+    CTX_CHECK();
+    if (!(radius > 0.f)) return set_err(ctx, BRE_ERR_INVALID, "radius must be > 0");
+    ctx->built = false;
+    if (ctx->n_photons)
+        k_set_w<<<(unsigned)((ctx->n_photons + 255) / 256), 256, 0, ctx->stream>>>((float4 *)ctx->pos_r.p, ctx->n_photons, radius);
+    BRE_CUDA(cudaGetLastError());
+    return BRE_OK;
+}
+
+int bre_allgather_photons(bre_ctx *ctx) {
+    CTX_CHECK();
+    if (ctx->n_ranks == 1) return BRE_OK;
+    ctx->built = false;
+    return nccl_allgather_photons(ctx);
+}
+
+// ---------------------------------------------------------------- build
+int bre_build(bre_ctx *ctx) {
+    CTX_CHECK();
+    return build_tree(ctx);
+}
+
+int bre_download_tree(bre_ctx *ctx, uint32_t *order, uint32_t *codes, float *node_lo, float *node_hi,
+                      int32_t *node_children) {
+    CTX_CHECK();
+    if (!ctx->built) return set_err(ctx, BRE_ERR_INVALID, "bre_build has not been called");
+    uint32_t n = ctx->n_built;
+    if (n == 0) return BRE_OK;
+    if (order) BRE_CUDA(cudaMemcpyAsync(order, ctx->order.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (codes) BRE_CUDA(cudaMemcpyAsync(codes, ctx->codes.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (n > 1 && (node_lo || node_hi || node_children)) {
+        std::vector<float4> lo(n - 1), hi(n - 1);
+        BRE_CUDA(cudaMemcpyAsync(lo.data(), ctx->node_lo.p, (size_t)(n - 1) * 16, cudaMemcpyDeviceToHost, ctx->stream));
+        BRE_CUDA(cudaMemcpyAsync(hi.data(), ctx->node_hi.p, (size_t)(n - 1) * 16, cudaMemcpyDeviceToHost, ctx->stream));
+        BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+        for (uint32_t i = 0; i + 1 < n; ++i) {
+            if (node_lo) { node_lo[3 * i] = lo[i].x; node_lo[3 * i + 1] = lo[i].y; node_lo[3 * i + 2] = lo[i].z; }
+            if (node_hi) { node_hi[3 * i] = hi[i].x; node_hi[3 * i + 1] = hi[i].y; node_hi[3 * i + 2] = hi[i].z; }
+            if (node_children) {
+                memcpy(&node_children[2 * i], &lo[i].w, 4);
+                memcpy(&node_children[2 * i + 1], &hi[i].w, 4);
+            }
+        }
+    }
+    return BRE_OK;
+}
+
+// ---------------------------------------------------------------- query
+static int upload_rays(bre_ctx *ctx, uint32_t n, const float *o4, const float *d3) {
+    int s;
+    if ((s = ensure(ctx, ctx->rays_o, (size_t)n * 16)) != BRE_OK) return s;
+    if ((s = ensure(ctx, ctx->rays_d, (size_t)n * 16)) != BRE_OK) return s;
+    BRE_CUDA(cudaMemcpyAsync(ctx->rays_o.p, o4, (size_t)n * 16, cudaMemcpyHostToDevice, ctx->stream));
+    return upload_pack(ctx, d3, n, nullptr, 0.f, (float4 *)ctx->rays_d.p);
+}
+
+static int query_ready(bre_ctx *ctx) {
+    if (!ctx->built) return set_err(ctx, BRE_ERR_INVALID, "bre_build has not been called since the photons changed");
+    if (!ctx->have_medium) return set_err(ctx, BRE_ERR_INVALID, "no medium set");
+    return BRE_OK;
+}
+
+int bre_query(bre_ctx *ctx, uint32_t n, const float *o4, const float *d3, float nPathsNorm,
+              float *out_rgb, bre_hitdump *hits) {
+    CTX_CHECK();
+    int s = query_ready(ctx);
+    if (s != BRE_OK) return s;
+    if (n == 0) { if (hits) { hits->total = 0; if (hits->offsets) hits->offsets[0] = 0; } return BRE_OK; }
+    if (!o4 || !d3) return set_err(ctx, BRE_ERR_INVALID, "null ray arrays");
+    if ((s = upload_rays(ctx, n, o4, d3)) != BRE_OK) return s;
+    if (out_rgb) {
+        if ((s = ensure(ctx, ctx->out_rgb, (size_t)n * 16 + (size_t)n * 12)) != BRE_OK) return s;
+        float4 *o4d = (float4 *)ctx->out_rgb.p;
+        float *o3d = (float *)(o4d + n);
+        if ((s = run_query(ctx, n, (const float4 *)ctx->rays_o.p, (const float4 *)ctx->rays_d.p, nPathsNorm, o4d)) != BRE_OK) return s;
+        k_unpack3<<<(n + 255) / 256, 256, 0, ctx->stream>>>(o4d, n, o3d, nullptr);
+        BRE_CUDA(cudaGetLastError());
+        BRE_CUDA(cudaMemcpyAsync(out_rgb, o3d, (size_t)n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+        BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    if (hits) return run_hitdump(ctx, n, (const float4 *)ctx->rays_o.p, (const float4 *)ctx->rays_d.p, hits);
+    return BRE_OK;
+}
+
+int bre_query_d(bre_ctx *ctx, uint32_t n, const void *ro, const void *rd, float nPathsNorm, void *out) {
+    CTX_CHECK();
+    int s = query_ready(ctx);
+    if (s != BRE_OK) return s;
+    if (n > 0 && (!ro || !rd || !out)) return set_err(ctx, BRE_ERR_INVALID, "null device pointer");
+    return run_query(ctx, n, (const float4 *)ro, (const float4 *)rd, nPathsNorm, (float4 *)out);
+}
+
+int bre_query_to_film(bre_ctx *ctx, uint32_t n, const float *o4, const float *d3, const uint32_t *pix,
+                      float nPathsNorm) {
+    CTX_CHECK();
+    int s = query_ready(ctx);
+    if (s != BRE_OK) return s;
+    if (!ctx->film.p) return set_err(ctx, BRE_ERR_INVALID, "bre_film_create has not been called");
+    if (n == 0) return BRE_OK;
+    if (!o4 || !d3) return set_err(ctx, BRE_ERR_INVALID, "null ray arrays");
+    if ((s = upload_rays(ctx, n, o4, d3)) != BRE_OK) return s;
+    if ((s = ensure(ctx, ctx->out_rgb, (size_t)n * 16)) != BRE_OK) return s;
+    const uint32_t *pd = nullptr;
+    if (pix) {
+        if ((s = ensure(ctx, ctx->pix_idx, (size_t)n * 4)) != BRE_OK) return s;
+        BRE_CUDA(cudaMemcpyAsync(ctx->pix_idx.p, pix, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+        pd = (const uint32_t *)ctx->pix_idx.p;
+    }
+    if ((s = run_query(ctx, n, (const float4 *)ctx->rays_o.p, (const float4 *)ctx->rays_d.p, nPathsNorm,
+                       (float4 *)ctx->out_rgb.p)) != BRE_OK) return s;
+    return film_accumulate(ctx, n, pd, (const float4 *)ctx->out_rgb.p);
+}
+
+int bre_count(bre_ctx *ctx, uint32_t n, const float *o4, const float *d3) {
+    CTX_CHECK();
+    int s = query_ready(ctx);
+    if (s != BRE_OK) return s;
+    if (n > 0) {
+        if (!o4 || !d3) return set_err(ctx, BRE_ERR_INVALID, "null ray arrays");
+        if ((s = upload_rays(ctx, n, o4, d3)) != BRE_OK) return s;
+    }
+    return run_count(ctx, n, (const float4 *)ctx->rays_o.p, (const float4 *)ctx->rays_d.p);
+}
+
+int bre_count_d(bre_ctx *ctx, uint32_t n, const void *ro, const void *rd) {
+    CTX_CHECK();
+    int s = query_ready(ctx);
+    if (s != BRE_OK) return s;
+    return run_count(ctx, n, (const float4 *)ro, (const float4 *)rd);
+}
+
+int bre_get_counters(bre_ctx *ctx, bre_counters *out) {
+    if (!ctx || !out) return BRE_ERR_INVALID;
+    *out = ctx->counters;
+    return BRE_OK;
+}
+
+// ---------------------------------------------------------------- film
+int bre_film_create(bre_ctx *ctx, uint32_t nPixels) {
+    CTX_CHECK();
+    if (nPixels == 0) return set_err(ctx, BRE_ERR_INVALID, "empty film");
+    int s = ensure(ctx, ctx->film, (size_t)nPixels * 16);
+    if (s != BRE_OK) return s;
+    ctx->n_pixels = nPixels;
+    return bre_film_clear(ctx);
+}
+int bre_film_clear(bre_ctx *ctx) {
+    CTX_CHECK();
+    if (!ctx->film.p) return set_err(ctx, BRE_ERR_INVALID, "bre_film_create has not been called");
+    BRE_CUDA(cudaMemsetAsync(ctx->film.p, 0, (size_t)ctx->n_pixels * 16, ctx->stream));
+    return BRE_OK;
+}
+int bre_film_accumulate(bre_ctx *ctx, uint32_t n, const uint32_t *pix, const float *rgb) {
+    CTX_CHECK();
+    if (n == 0) return BRE_OK;
+    if (!rgb) return set_err(ctx, BRE_ERR_INVALID, "null rgb");
+    int s;
+    if ((s = ensure(ctx, ctx->out_rgb, (size_t)n * 16)) != BRE_OK) return s;
+    if ((s = upload_pack(ctx, rgb, n, nullptr, 0.f, (float4 *)ctx->out_rgb.p)) != BRE_OK) return s;
+    const uint32_t *pd = nullptr;
+    if (pix) {
+        if ((s = ensure(ctx, ctx->pix_idx, (size_t)n * 4)) != BRE_OK) return s;
+        for (uint32_t q = 0; q < n; ++q)
+            if (pix[q] >= ctx->n_pixels) return set_err(ctx, BRE_ERR_INVALID, "pixel index out of range");
+        BRE_CUDA(cudaMemcpyAsync(ctx->pix_idx.p, pix, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+        pd = (const uint32_t *)ctx->pix_idx.p;
+    }
+    s = film_accumulate(ctx, n, pd, (const float4 *)ctx->out_rgb.p);
+    if (s != BRE_OK) return s;
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return BRE_OK;
+}
+int bre_film_accumulate_d(bre_ctx *ctx, uint32_t n, const uint32_t *pix_d, const void *rgb_d) {
+    CTX_CHECK();
+    return film_accumulate(ctx, n, pix_d, (const float4 *)rgb_d);
+}
+int bre_film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out) {
+    CTX_CHECK();
+    if (!rgb_out || iter < 0) return set_err(ctx, BRE_ERR_INVALID, "bad resolve arguments");
+    return film_resolve(ctx, iter, scale, rgb_out);
+}
+
+// ---------------------------------------------------------------- timing
+int bre_set_timing(bre_ctx *ctx, int enabled) {
+    CTX_CHECK();
+    if (enabled && !ctx->ev[0][0])
+        for (int i = 0; i < 8; ++i)
+            for (int j = 0; j < 2; ++j) BRE_CUDA(cudaEventCreate(&ctx->ev[i][j]));
+    ctx->timing = enabled != 0;
+    return BRE_OK;
+}
+int bre_get_timings(bre_ctx *ctx, float ms[8]) {
+    CTX_CHECK();
+    if (!ms) return set_err(ctx, BRE_ERR_INVALID, "null output");
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (int i = 0; i < 8; ++i) {
+        ms[i] = 0.f;
+        if (ctx->ev_valid[i]) BRE_CUDA(cudaEventElapsedTime(&ms[i], ctx->ev[i][0], ctx->ev[i][1]));
+    }
+    return BRE_OK;
+}
+
+// ---------------------------------------------------------------- sharding helpers
+void bre_shard_range(uint64_t n, int nRanks, int rank, uint64_t *first, uint64_t *count) {
+    if (nRanks < 1) nRanks = 1;
+    uint64_t base = n / (uint64_t)nRanks, rem = n % (uint64_t)nRanks;
+    uint64_t r = (uint64_t)rank;
+    uint64_t f = r * base + (r < rem ? r : rem);
+    uint64_t c = base + (r < rem ? 1 : 0);
+    if (first) *first = f;
+    if (count) *count = c;
+}
+int bre_tile_owner(uint32_t tx, uint32_t ty, uint32_t tilesX, int nRanks) {
+    if (nRanks < 1) nRanks = 1;
+    return (int)(((uint64_t)ty * tilesX + tx) % (uint64_t)nRanks);
+}
+
+}  // extern "C"

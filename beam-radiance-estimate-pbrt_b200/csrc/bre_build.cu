@@ -1,0 +1,445 @@
+// bre_build.cu -- K2..K4: Morton-code LBVH over photon bounding spheres.
+//
+// Replaces (reference src/): PhotonBeamBVH ctor + recursiveBuild / HLBVH2Build
+// (core/photonbeambvh.cpp:204-248,259-425,427-495), EncodeMorton3/LeftShift3 (:109-139),
+// RadixSort (:141-182), emitLBVH2 (:497-559), flattenBVH2Tree (:663-681) and
+// KdTree<Photon> build (core/kdtree.h:101-149).
+//
+// Pipeline (all on the context stream, no host round trip except one 4-byte read of abs_max):
+//   k_bounds      min/max of photon positions                  (centroid bounds, :431-436)
+//   k_morton      30-bit Morton code per photon                 (:438-445)
+//   radix sort    4 x 8-bit stable LSD passes of (code, index)  (integer; hist / scan / scatter)
+//   k_gather      photon SoA -> Morton order, leaf boxes, max |coord|
+//   k_karras      binary radix tree over keys (code<<32 | index): one thread per internal node
+//   k_refit       bottom-up AABB union with per-node arrival counters
+//   k_emit_fast   64-byte two-child nodes of the production tree, leaves of <= max_leaf photons
+#include "bre_internal.cuh"
+#include <cfloat>
+
+namespace bre {
+
+// ---------------------------------------------------------------- bounds
+__device__ __forceinline__ uint32_t f2ord(float f) {
+    uint32_t b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(uint32_t u) {
+    return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+
+__global__ void k_bounds_init(uint32_t *b) {
+    if (threadIdx.x < 3) b[threadIdx.x] = 0xffffffffu;       // min
+    else if (threadIdx.x < 6) b[threadIdx.x] = 0u;            // max
+    else if (threadIdx.x == 6) b[6] = 0u;                     // abs_max bits
+}
+
+__global__ void __launch_bounds__(256) k_bounds(const float4 *__restrict__ pos_r, uint32_t n,
+                                                uint32_t *__restrict__ b) {
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        float4 p = __ldg(pos_r + i);
+        lo[0] = fminf(lo[0], p.x); hi[0] = fmaxf(hi[0], p.x);
+        lo[1] = fminf(lo[1], p.y); hi[1] = fmaxf(hi[1], p.y);
+        lo[2] = fminf(lo[2], p.z); hi[2] = fmaxf(hi[2], p.z);
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], o));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], o));
+        }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            atomicMin(b + k, f2ord(lo[k]));
+            atomicMax(b + 3 + k, f2ord(hi[k]));
+        }
+    }
+}
+
+// ---------------------------------------------------------------- Morton codes
+__device__ __forceinline__ uint32_t left_shift3(uint32_t x) {  // photonbeambvh.cpp:109-132
+    if (x == (1u << 10)) --x;
+    x = (x | (x << 16)) & 0x30000ffu;
+    x = (x | (x << 8)) & 0x300f00fu;
+    x = (x | (x << 4)) & 0x30c30c3u;
+    x = (x | (x << 2)) & 0x9249249u;
+    return x;
+}
+__device__ __forceinline__ uint32_t morton_axis(float p, float lo, float hi) {
+    // Bounds3::Offset then * mortonScale (photonbeambvh.cpp:440-444), float32, no contraction
+    float o = fsub(p, lo);
+    if (hi > lo) o = fdiv(o, fsub(hi, lo));
+    float s = fmul(o, 1024.f);
+    uint32_t v = (uint32_t)s;  // truncation toward zero, saturating like the oracle's clamp
+    if (v > 1024u) v = 1024u;
+    return left_shift3(v);
+}
+
+__global__ void __launch_bounds__(256) k_morton(const float4 *__restrict__ pos_r, uint32_t n,
+                                                const uint32_t *__restrict__ b,
+                                                uint32_t *__restrict__ codes) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float lo0 = ord2f(b[0]), lo1 = ord2f(b[1]), lo2 = ord2f(b[2]);
+    float hi0 = ord2f(b[3]), hi1 = ord2f(b[4]), hi2 = ord2f(b[5]);
+    float4 p = __ldg(pos_r + i);
+    codes[i] = (morton_axis(p.z, lo2, hi2) << 2) | (morton_axis(p.y, lo1, hi1) << 1) |
+               morton_axis(p.x, lo0, hi0);
+}
+
+// ---------------------------------------------------------------- radix sort
+// Stable LSD sort of (key u32, value u32), 8 bits per pass.  Tile = 256 threads x 16 keys;
+// warp w owns the contiguous chunk [w*512, (w+1)*512) of its tile, processed 32 keys at a time
+// in index order, so (warp, item, lane) order == index order and the sort is stable.
+constexpr int RS_THREADS = 256;
+constexpr int RS_ITEMS = 16;
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS;
+
+__global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const uint32_t *__restrict__ keys,
+                                                         uint32_t n, int shift,
+                                                         uint32_t *__restrict__ hist,
+                                                         uint32_t numBlocks) {
+    __shared__ uint32_t sh[256];
+    sh[threadIdx.x] = 0;
+    __syncthreads();
+    uint32_t base = blockIdx.x * RS_TILE;
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) {
+        uint32_t idx = base + k * RS_THREADS + threadIdx.x;
+        if (idx < n) atomicAdd(&sh[(__ldg(keys + idx) >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    hist[threadIdx.x * numBlocks + blockIdx.x] = sh[threadIdx.x];
+}
+
+// exclusive scan of `len` counters in place, single block
+__global__ void __launch_bounds__(1024) k_rs_scan(uint32_t *__restrict__ hist, uint32_t len) {
+    __shared__ uint32_t warpSums[32];
+    __shared__ uint32_t carry;
+    uint32_t per = (len + blockDim.x - 1) / blockDim.x;
+    uint32_t b = threadIdx.x * per, e = min(b + per, len);
+    uint32_t sum = 0;
+    for (uint32_t i = b; i < e; ++i) sum += hist[i];
+    // block exclusive scan of `sum`
+    uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint32_t incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) warpSums[w] = incl;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    if (w == 0) {
+        uint32_t v = warpSums[lane], iv = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, iv, o);
+            if (lane >= o) iv += t;
+        }
+        warpSums[lane] = iv - v;
+    }
+    __syncthreads();
+    uint32_t run = warpSums[w] + incl - sum;
+    for (uint32_t i = b; i < e; ++i) {
+        uint32_t v = hist[i];
+        hist[i] = run;
+        run += v;
+    }
+}
+
+__global__ void __launch_bounds__(RS_THREADS) k_rs_scatter(
+    const uint32_t *__restrict__ keysIn, const uint32_t *__restrict__ valsIn,
+    uint32_t *__restrict__ keysOut, uint32_t *__restrict__ valsOut, uint32_t n, int shift,
+    const uint32_t *__restrict__ hist, uint32_t numBlocks, int iotaVals) {
+    __shared__ uint32_t whist[RS_THREADS / 32][256];
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < (RS_THREADS / 32) * 256; i += RS_THREADS) (&whist[0][0])[i] = 0;
+    __syncthreads();
+    const uint32_t base = blockIdx.x * RS_TILE + w * (RS_ITEMS * 32);
+    uint32_t key[RS_ITEMS], rank[RS_ITEMS];
+    const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) {
+        uint32_t idx = base + k * 32 + lane;
+        bool valid = idx < n;
+        key[k] = valid ? __ldg(keysIn + idx) : 0xffffffffu;
+        uint32_t d = (key[k] >> shift) & 255u;
+        uint32_t vmask = __ballot_sync(0xffffffffu, valid);
+        rank[k] = 0;
+        if (valid) {
+            uint32_t peers = __match_any_sync(vmask, d);
+            int leader = __ffs(peers) - 1;
+            uint32_t old = 0;
+            if ((int)lane == leader) {
+                old = whist[w][d];
+                whist[w][d] = old + __popc(peers);
+            }
+            old = __shfl_sync(peers, old, leader);
+            rank[k] = old + __popc(peers & lt);
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    {   // digit threadIdx.x: exclusive prefix over warps + global base
+        uint32_t d = threadIdx.x;
+        uint32_t run = __ldg(hist + d * numBlocks + blockIdx.x);
+#pragma unroll
+        for (int ww = 0; ww < RS_THREADS / 32; ++ww) {
+            uint32_t c = whist[ww][d];
+            whist[ww][d] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) {
+        uint32_t idx = base + k * 32 + lane;
+        if (idx < n) {
+            uint32_t d = (key[k] >> shift) & 255u;
+            uint32_t dst = whist[w][d] + rank[k];
+            keysOut[dst] = key[k];
+            valsOut[dst] = iotaVals ? idx : __ldg(valsIn + idx);
+        }
+    }
+}
+
+// ---------------------------------------------------------------- gather to Morton order
+__global__ void __launch_bounds__(256) k_gather(
+    const float4 *__restrict__ pos_r, const float4 *__restrict__ pw, const float4 *__restrict__ dr,
+    const uint32_t *__restrict__ order, uint32_t n, float4 *__restrict__ s_pos_r,
+    float4 *__restrict__ s_pow, float4 *__restrict__ s_dir, float4 *__restrict__ leaf_lo,
+    float4 *__restrict__ leaf_hi, uint32_t *__restrict__ bnd) {
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    float amax = 0.f;
+    if (s < n) {
+        uint32_t i = __ldg(order + s);
+        float4 p = __ldg(pos_r + i);
+        s_pos_r[s] = p;
+        s_pow[s] = __ldg(pw + i);
+        s_dir[s] = __ldg(dr + i);
+        // leaf box: sphere bound p +- r*(1+2e-6), then one ulp outward (DESIGN.md "conservative cull")
+        float rp = fmul(p.w, 1.000002f);
+        float4 lo, hi;
+        lo.x = next_down(fsub(p.x, rp)); hi.x = next_up(fadd(p.x, rp));
+        lo.y = next_down(fsub(p.y, rp)); hi.y = next_up(fadd(p.y, rp));
+        lo.z = next_down(fsub(p.z, rp)); hi.z = next_up(fadd(p.z, rp));
+        lo.w = 0.f; hi.w = 0.f;
+        leaf_lo[s] = lo;
+        leaf_hi[s] = hi;
+        amax = fmaxf(fmaxf(fmaxf(fabsf(lo.x), fabsf(hi.x)), fmaxf(fabsf(lo.y), fabsf(hi.y))),
+                     fmaxf(fabsf(lo.z), fabsf(hi.z)));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    if ((threadIdx.x & 31) == 0 && amax > 0.f) atomicMax(bnd + 6, __float_as_uint(amax));
+}
+
+// ---------------------------------------------------------------- Karras radix tree
+__device__ __forceinline__ int delta64(const uint32_t *__restrict__ codes,
+                                       const uint32_t *__restrict__ order, uint64_t ki, int j,
+                                       int n) {
+    if (j < 0 || j >= n) return -1;
+    uint64_t kj = ((uint64_t)__ldg(codes + j) << 32) | __ldg(order + j);
+    return __clzll((long long)(ki ^ kj));
+}
+
+// node_lo[i].w / node_hi[i].w hold the left / right child refs (>=0 internal, <0 = ~leaf).
+// parent[0..n-2] internal parents, parent[n-1+s] leaf parents.  node_range[i] = {first,last}.
+__global__ void __launch_bounds__(256) k_karras(const uint32_t *__restrict__ codes,
+                                                const uint32_t *__restrict__ order, int n,
+                                                float4 *__restrict__ node_lo,
+                                                float4 *__restrict__ node_hi,
+                                                int2 *__restrict__ node_range,
+                                                int *__restrict__ parent) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    uint64_t ki = ((uint64_t)__ldg(codes + i) << 32) | __ldg(order + i);
+    int d = delta64(codes, order, ki, i + 1, n) - delta64(codes, order, ki, i - 1, n) > 0 ? 1 : -1;
+    int dmin = delta64(codes, order, ki, i - d, n);
+    int lmax = 2;
+    while (delta64(codes, order, ki, i + lmax * d, n) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta64(codes, order, ki, i + (l + t) * d, n) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = delta64(codes, order, ki, j, n);
+    int s = 0, t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (delta64(codes, order, ki, i + (s + t) * d, n) > dnode) s += t;
+    } while (t > 1);
+    int gamma = i + s * d + min(d, 0);
+    int first = min(i, j), last = max(i, j);
+    int left = (first == gamma) ? ~gamma : gamma;
+    int right = (last == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+    node_lo[i].w = __int_as_float(left);
+    node_hi[i].w = __int_as_float(right);
+    node_range[i] = make_int2(first, last);
+    if (left >= 0) parent[left] = i; else parent[n - 1 + gamma] = i;
+    if (right >= 0) parent[right] = i; else parent[n - 1 + gamma + 1] = i;
+    if (i == 0) parent[0] = -1;
+}
+
+__global__ void __launch_bounds__(256) k_refit(int n, float4 *node_lo, float4 *node_hi,
+                                               const float4 *__restrict__ leaf_lo,
+                                               const float4 *__restrict__ leaf_hi,
+                                               const int *__restrict__ parent,
+                                               uint32_t *__restrict__ flags) {
+    int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    int cur = __ldg(parent + n - 1 + s);
+    while (cur >= 0) {
+        __threadfence();
+        if (atomicAdd(flags + cur, 1u) == 0u) return;  // first arrival: sibling not done yet
+        __threadfence();
+        float4 nlo = __ldcg(node_lo + cur), nhi = __ldcg(node_hi + cur);
+        int left = __float_as_int(nlo.w), right = __float_as_int(nhi.w);
+        float4 llo, lhi, rlo, rhi;
+        if (left >= 0) { llo = __ldcg(node_lo + left); lhi = __ldcg(node_hi + left); }
+        else { llo = __ldg(leaf_lo + ~left); lhi = __ldg(leaf_hi + ~left); }
+        if (right >= 0) { rlo = __ldcg(node_lo + right); rhi = __ldcg(node_hi + right); }
+        else { rlo = __ldg(leaf_lo + ~right); rhi = __ldg(leaf_hi + ~right); }
+        nlo.x = fminf(llo.x, rlo.x); nlo.y = fminf(llo.y, rlo.y); nlo.z = fminf(llo.z, rlo.z);
+        nhi.x = fmaxf(lhi.x, rhi.x); nhi.y = fmaxf(lhi.y, rhi.y); nhi.z = fmaxf(lhi.z, rhi.z);
+        __stcg(node_lo + cur, nlo);
+        __stcg(node_hi + cur, nhi);
+        cur = __ldg(parent + cur);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_emit_fast(int n, int maxLeaf,
+                                                   const float4 *__restrict__ node_lo,
+                                                   const float4 *__restrict__ node_hi,
+                                                   const int2 *__restrict__ node_range,
+                                                   const float4 *__restrict__ leaf_lo,
+                                                   const float4 *__restrict__ leaf_hi,
+                                                   FastNode *__restrict__ fast) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int2 rg = __ldg(node_range + i);
+    if (rg.y - rg.x + 1 <= maxLeaf && i != 0) return;  // inside a fat leaf: never visited
+    float4 nlo = __ldg(node_lo + i), nhi = __ldg(node_hi + i);
+    int ch[2] = {__float_as_int(nlo.w), __float_as_int(nhi.w)};
+    float4 lo[2], hi[2];
+    int ref[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        if (ch[k] >= 0) {
+            lo[k] = __ldg(node_lo + ch[k]);
+            hi[k] = __ldg(node_hi + ch[k]);
+            int2 cr = __ldg(node_range + ch[k]);
+            int cnt = cr.y - cr.x + 1;
+            ref[k] = cnt <= maxLeaf ? leaf_ref((uint32_t)cr.x, (uint32_t)cnt) : ch[k];
+        } else {
+            lo[k] = __ldg(leaf_lo + ~ch[k]);
+            hi[k] = __ldg(leaf_hi + ~ch[k]);
+            ref[k] = leaf_ref((uint32_t)~ch[k], 1u);
+        }
+    }
+    FastNode f;
+    f.a = make_float4(lo[0].x, lo[0].y, lo[0].z, hi[0].x);
+    f.b = make_float4(hi[0].y, hi[0].z, lo[1].x, lo[1].y);
+    f.c = make_float4(lo[1].z, hi[1].x, hi[1].y, hi[1].z);
+    f.d = make_int4(ref[0], ref[1], 0, 0);
+    fast[i] = f;
+}
+
+// ---------------------------------------------------------------- host driver
+int build_tree(bre_ctx *ctx) {
+    ctx->built = false;
+    if (ctx->n_photons >= BRE_MAX_PHOTONS)
+        return set_err(ctx, BRE_ERR_UNSUPPORTED, "photon count exceeds 2^27 (leaf reference encoding)");
+    const uint32_t n = (uint32_t)ctx->n_photons;
+    ctx->n_built = n;
+    ctx->abs_max = 0.f;
+    ctx->root_ref = 0;
+    if (n == 0) { ctx->built = true; return BRE_OK; }
+    cudaStream_t st = ctx->stream;
+    const size_t n4 = (size_t)n * sizeof(float4);
+    int s;
+#define ENS(buf, bytes) if ((s = ensure(ctx, ctx->buf, (bytes))) != BRE_OK) return s
+    ENS(s_pos_r, n4); ENS(s_pow, n4); ENS(s_dir, n4);
+    ENS(order, (size_t)n * 4); ENS(codes, (size_t)n * 4);
+    ENS(keys_alt, (size_t)n * 4); ENS(vals_alt, (size_t)n * 4);
+    ENS(leaf_lo, n4); ENS(leaf_hi, n4);
+    ENS(node_lo, n4); ENS(node_hi, n4);
+    ENS(node_range, (size_t)n * 8); ENS(parent, (size_t)2 * n * 4);
+    ENS(flags, (size_t)n * 4); ENS(fast, (size_t)n * sizeof(FastNode));
+    ENS(scratch, 64);
+    const uint32_t numBlocks = (n + RS_TILE - 1) / RS_TILE;
+    ENS(hist, (size_t)256 * numBlocks * 4);
+#undef ENS
+    uint32_t *bnd = (uint32_t *)ctx->scratch.p;
+    const float4 *pos_r = (const float4 *)ctx->pos_r.p;
+    uint32_t *codes = (uint32_t *)ctx->codes.p, *order = (uint32_t *)ctx->order.p;
+    uint32_t *kalt = (uint32_t *)ctx->keys_alt.p, *valt = (uint32_t *)ctx->vals_alt.p;
+    uint32_t *hist = (uint32_t *)ctx->hist.p;
+    const int g256 = (int)((n + 255) / 256);
+
+    PhaseTimer *pt = new PhaseTimer(ctx, PH_BUILD);
+    k_bounds_init<<<1, 32, 0, st>>>(bnd);
+    k_bounds<<<min(g256, 148 * 8), 256, 0, st>>>(pos_r, n, bnd);
+    k_morton<<<g256, 256, 0, st>>>(pos_r, n, bnd, codes);
+    // 4 passes: codes/order ping-pong with kalt/valt; result ends in codes/order
+    uint32_t *kin = codes, *vin = order, *kout = kalt, *vout = valt;
+    for (int pass = 0; pass < 4; ++pass) {
+        int shift = 8 * pass;
+        k_rs_hist<<<numBlocks, RS_THREADS, 0, st>>>(kin, n, shift, hist, numBlocks);
+        k_rs_scan<<<1, 1024, 0, st>>>(hist, 256u * numBlocks);
+        k_rs_scatter<<<numBlocks, RS_THREADS, 0, st>>>(kin, vin, kout, vout, n, shift, hist,
+                                                       numBlocks, pass == 0);
+        uint32_t *t = kin; kin = kout; kout = t;
+        t = vin; vin = vout; vout = t;
+    }
+    // after 4 passes kin == codes, vin == order
+    k_gather<<<g256, 256, 0, st>>>(pos_r, (const float4 *)ctx->pow.p, (const float4 *)ctx->dir.p,
+                                   order, n, (float4 *)ctx->s_pos_r.p, (float4 *)ctx->s_pow.p,
+                                   (float4 *)ctx->s_dir.p, (float4 *)ctx->leaf_lo.p,
+                                   (float4 *)ctx->leaf_hi.p, bnd);
+    if (n > 1) {
+        BRE_CUDA(cudaMemsetAsync(ctx->flags.p, 0, (size_t)n * 4, st));
+        k_karras<<<g256, 256, 0, st>>>(codes, order, (int)n, (float4 *)ctx->node_lo.p,
+                                       (float4 *)ctx->node_hi.p, (int2 *)ctx->node_range.p,
+                                       (int *)ctx->parent.p);
+        k_refit<<<g256, 256, 0, st>>>((int)n, (float4 *)ctx->node_lo.p, (float4 *)ctx->node_hi.p,
+                                      (const float4 *)ctx->leaf_lo.p, (const float4 *)ctx->leaf_hi.p,
+                                      (const int *)ctx->parent.p, (uint32_t *)ctx->flags.p);
+        k_emit_fast<<<g256, 256, 0, st>>>((int)n, ctx->max_leaf, (const float4 *)ctx->node_lo.p,
+                                          (const float4 *)ctx->node_hi.p,
+                                          (const int2 *)ctx->node_range.p,
+                                          (const float4 *)ctx->leaf_lo.p,
+                                          (const float4 *)ctx->leaf_hi.p, (FastNode *)ctx->fast.p);
+    }
+    delete pt;
+    BRE_CUDA(cudaGetLastError());
+    uint32_t amaxBits = 0;
+    BRE_CUDA(cudaMemcpyAsync(&amaxBits, bnd + 6, 4, cudaMemcpyDeviceToHost, st));
+    BRE_CUDA(cudaStreamSynchronize(st));
+    memcpy(&ctx->abs_max, &amaxBits, 4);
+    ctx->root_ref = (n <= (uint32_t)ctx->max_leaf) ? leaf_ref(0u, n) : 0;
+    ctx->built = true;
+    return BRE_OK;
+}
+
+TreeDev tree_view(const bre_ctx *ctx) {
+    TreeDev t;
+    t.n = ctx->n_built;
+    t.s_pos_r = (const float4 *)ctx->s_pos_r.p;
+    t.s_pow = (const float4 *)ctx->s_pow.p;
+    t.s_dir = (const float4 *)ctx->s_dir.p;
+    t.order = (const uint32_t *)ctx->order.p;
+    t.node_lo = (const float4 *)ctx->node_lo.p;
+    t.node_hi = (const float4 *)ctx->node_hi.p;
+    t.leaf_lo = (const float4 *)ctx->leaf_lo.p;
+    t.leaf_hi = (const float4 *)ctx->leaf_hi.p;
+    t.fast = (const FastNode *)ctx->fast.p;
+    t.root_ref = ctx->root_ref;
+    t.abs_max = ctx->abs_max;
+    return t;
+}
+
+}  // namespace bre

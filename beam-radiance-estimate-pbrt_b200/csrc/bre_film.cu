@@ -1,0 +1,76 @@
+// bre_film.cu -- K7: per-pixel film accumulation and resolve.
+//
+// Replaces (reference src/): PhotonBeamPixel::Ld += ... (integrators/photonbeam.cpp:504),
+// L = Ld / (iter+1) (:578), Film::SetImage (core/film.cpp:132-140: RGB->XYZ, weight 1) and the
+// arithmetic of Film::WriteImage (core/film.cpp:168-204: XYZ->RGB, /weight, max(0,.), *scale)
+// with RGBToXYZ / XYZToRGB of core/spectrum.h:56-66.
+#include "bre_internal.cuh"
+
+namespace bre {
+
+__global__ void __launch_bounds__(256) k_film_add(float4 *__restrict__ film, uint32_t n,
+                                                  const uint32_t *__restrict__ pix,
+                                                  const float4 *__restrict__ rgb) {
+    uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    float4 v = __ldg(rgb + q);
+    if (pix == nullptr) {
+        float4 f = film[q];
+        f.x = fadd(f.x, v.x); f.y = fadd(f.y, v.y); f.z = fadd(f.z, v.z);
+        film[q] = f;
+    } else {
+        float *f = reinterpret_cast<float *>(film + __ldg(pix + q));
+        atomicAdd(f + 0, v.x); atomicAdd(f + 1, v.y); atomicAdd(f + 2, v.z);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_film_resolve(const float4 *__restrict__ film, uint32_t n,
+                                                      float inv, float scale,
+                                                      float *__restrict__ out) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 f = __ldg(film + i);
+    float r = fmul(f.x, inv), g = fmul(f.y, inv), b = fmul(f.z, inv);
+    // RGBToXYZ spectrum.h:62-66
+    float X = fadd(fadd(fmul(0.412453f, r), fmul(0.357580f, g)), fmul(0.180423f, b));
+    float Y = fadd(fadd(fmul(0.212671f, r), fmul(0.715160f, g)), fmul(0.072169f, b));
+    float Z = fadd(fadd(fmul(0.019334f, r), fmul(0.119193f, g)), fmul(0.950227f, b));
+    // XYZToRGB spectrum.h:56-60
+    float R = fsub(fsub(fmul(3.240479f, X), fmul(1.537150f, Y)), fmul(0.498535f, Z));
+    float G = fadd(fadd(fmul(-0.969256f, X), fmul(1.875991f, Y)), fmul(0.041556f, Z));
+    float B = fadd(fsub(fmul(0.055648f, X), fmul(0.204043f, Y)), fmul(1.057311f, Z));
+    // weight = 1, no splats: max(0, rgb * 1) * scale   film.cpp:178-201
+    out[3 * (size_t)i + 0] = fmul(fmaxf(0.f, R), scale);
+    out[3 * (size_t)i + 1] = fmul(fmaxf(0.f, G), scale);
+    out[3 * (size_t)i + 2] = fmul(fmaxf(0.f, B), scale);
+}
+
+int film_accumulate(bre_ctx *ctx, uint32_t n, const uint32_t *pix_d, const float4 *rgb_d) {
+    if (!ctx->film.p) return set_err(ctx, BRE_ERR_INVALID, "bre_film_create has not been called");
+    if (pix_d == nullptr && n > ctx->n_pixels)
+        return set_err(ctx, BRE_ERR_INVALID, "more rays than pixels and no pixel index");
+    if (n == 0) return BRE_OK;
+    {
+        PhaseTimer pt(ctx, PH_FILM);
+        k_film_add<<<(n + 255) / 256, 256, 0, ctx->stream>>>((float4 *)ctx->film.p, n, pix_d, rgb_d);
+    }
+    BRE_CUDA(cudaGetLastError());
+    return BRE_OK;
+}
+
+int film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out_host) {
+    if (!ctx->film.p) return set_err(ctx, BRE_ERR_INVALID, "bre_film_create has not been called");
+    uint32_t n = ctx->n_pixels;
+    int s;
+    if ((s = ensure(ctx, ctx->out_rgb, (size_t)n * 12)) != BRE_OK) return s;
+    float inv = 1.f / (float)(iter + 1);
+    k_film_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, n, inv,
+                                                             scale, (float *)ctx->out_rgb.p);
+    BRE_CUDA(cudaGetLastError());
+    BRE_CUDA(cudaMemcpyAsync(rgb_out_host, ctx->out_rgb.p, (size_t)n * 12, cudaMemcpyDeviceToHost,
+                             ctx->stream));
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return BRE_OK;
+}
+
+}  // namespace bre

@@ -1,0 +1,186 @@
+// bre_internal.cuh -- shared declarations of libbre.so (sm_100a only).
+//
+// Data layout in HBM (all float4 / 16-byte aligned, SoA):
+//   photons (store order)   pos_r[n] {x,y,z,radius}  pow[n] {r,g,b,0}  dir[n] {wx,wy,wz,0}
+//   photons (Morton order)  s_pos_r, s_pow, s_dir + order[n] (sorted position -> store index)
+//   canonical LBVH          node_lo[n-1] {lo.xyz, left}  node_hi[n-1] {hi.xyz, right}
+//                           leaf_lo[n], leaf_hi[n] float4, node_range[n-1] {first,last}
+//   production tree         fast[n-1] 64-byte two-child nodes (boxes of both children + refs)
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include "../../include/bre.h"
+
+namespace bre {
+
+// ------------------------------------------------------------------ float helpers
+// Everything that decides a photon hit or a Morton code uses these explicitly
+// rounded, never-contracted operations so that the results are bit-identical to
+// the CPU oracle (compiled -ffp-contract=off).
+__device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float fsub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float fdiv(float a, float b) { return __fdiv_rn(a, b); }
+
+__device__ __forceinline__ float next_up(float x) {   // nextafterf(x, +inf), finite x
+    if (x == 0.f) return __int_as_float(1);
+    int b = __float_as_int(x);
+    return __int_as_float(x > 0.f ? b + 1 : b - 1);
+}
+__device__ __forceinline__ float next_down(float x) { // nextafterf(x, -inf), finite x
+    if (x == 0.f) return __int_as_float(0x80000001);
+    int b = __float_as_int(x);
+    return __int_as_float(x > 0.f ? b - 1 : b + 1);
+}
+
+#define BRE_PI 3.14159265358979323846f
+#define BRE_INV_PI 0.31830988618379067154f
+#define BRE_INV4PI 0.07957747154594766788f
+#define BRE_ONE_MINUS_EPS 0.99999994f
+// 1 + 2*gamma(3), core/pbrt.h:263-265 with MachineEpsilon = 2^-24
+#define BRE_SLAB_WIDEN 1.00000035762793f
+
+// ------------------------------------------------------------------ device structs
+struct MediumDev {
+    int kind;                 // 0 homogeneous, 1 grid
+    float sigma_a[3], sigma_s[3], sigma_t[3];
+    float g;
+    int nx, ny, nz;
+    const float *density;     // device
+    float invMaxDensity;
+    float w2m[12];            // affine rows
+};
+
+struct LightDev {
+    int kind;
+    float pos[3], I[3], axis[3], ax[3], ay[3];
+    float cosTotalWidth, cosFalloffStart;
+};
+#define BRE_MAX_LIGHTS 64
+struct LightsDev {
+    int n;
+    float cdf[BRE_MAX_LIGHTS + 1];
+    float func[BRE_MAX_LIGHTS];
+    float funcInt;
+    LightDev l[BRE_MAX_LIGHTS];
+};
+
+// 64-byte node of the production tree: boxes of both children + child references.
+// ref >= 0: internal node index;  ref < 0: leaf, see leaf_ref().
+struct __align__(16) FastNode {
+    float4 a;  // c0.lo.x c0.lo.y c0.lo.z c0.hi.x
+    float4 b;  // c0.hi.y c0.hi.z c1.lo.x c1.lo.y
+    float4 c;  // c1.lo.z c1.hi.x c1.hi.y c1.hi.z
+    int4 d;    // ref0 ref1 - -
+};
+// leaf reference: bit31 set, (count-1) in bits 27..30, first sorted photon in bits 0..26
+__host__ __device__ __forceinline__ int leaf_ref(uint32_t first, uint32_t count) {
+    return (int)(0x80000000u | ((count - 1u) << 27) | first);
+}
+#define BRE_MAX_PHOTONS (1u << 27)
+
+struct TreeDev {
+    uint32_t n;               // photons
+    const float4 *s_pos_r, *s_pow, *s_dir;
+    const uint32_t *order;
+    const float4 *node_lo, *node_hi;   // .w = child refs as int bits
+    const float4 *leaf_lo, *leaf_hi;
+    const FastNode *fast;
+    int root_ref;             // fast-path root: internal 0, or a leaf ref when n <= max leaf
+    float abs_max;            // max |coordinate| of any leaf box
+};
+
+// ------------------------------------------------------------------ context
+struct Buf {
+    void *p = nullptr;
+    size_t cap = 0;
+};
+
+}  // namespace bre
+
+struct bre_ctx {
+    int device = 0, n_ranks = 1, rank = 0;
+    int max_leaf = 8, tau_steps = 64;
+    cudaStream_t stream = nullptr;
+    std::string err;
+
+    // scene
+    bre::MediumDev medium{};
+    bool have_medium = false;
+    bre::Buf density;
+    bre::LightsDev *lights_d = nullptr;
+    int n_lights = 0;
+    float blo[3] = {0, 0, 0}, bhi[3] = {0, 0, 0};
+    bool have_bounds = false;
+
+    // photon store (store order)
+    uint64_t n_photons = 0;
+    bre::Buf pos_r, pow, dir;
+    // build products
+    bool built = false;
+    uint32_t n_built = 0;
+    bre::Buf s_pos_r, s_pow, s_dir, order, codes, keys_alt, vals_alt, hist, node_lo, node_hi,
+        node_range, parent, leaf_lo, leaf_hi, flags, fast, scratch;
+    float abs_max = 0;
+    int root_ref = 0;
+    // query scratch
+    bre::Buf rays_o, rays_d, out_rgb, tau, hit_counts, hit_offsets, hit_idx, counters_d, pix_idx;
+    bre_counters counters{};
+    // film
+    bre::Buf film;
+    uint32_t n_pixels = 0;
+    // trace scratch
+    bre::Buf path_counts, path_offsets;
+    // nccl
+    void *nccl_comm = nullptr;
+    // per-phase device timing (bre_set_timing)
+    bool timing = false;
+    cudaEvent_t ev[8][2] = {};
+    bool ev_valid[8] = {};
+};
+
+namespace bre {
+
+int set_err(bre_ctx *c, int code, const std::string &msg);
+int ensure(bre_ctx *c, Buf &b, size_t bytes);   // grow-only device allocation
+int check_cuda(bre_ctx *c, cudaError_t e, const char *what);
+#define BRE_CUDA(call)                                                    \
+    do {                                                                  \
+        int _s = bre::check_cuda(ctx, (call), #call);                     \
+        if (_s != BRE_OK) return _s;                                      \
+    } while (0)
+
+// build.cu
+int build_tree(bre_ctx *ctx);
+// query.cu
+int run_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, float nPathsNorm,
+              float4 *out);
+int run_count(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd);
+int run_hitdump(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, bre_hitdump *hd);
+// film.cu
+int film_accumulate(bre_ctx *ctx, uint32_t n, const uint32_t *pix_d, const float4 *rgb_d);
+int film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out_host);
+// trace.cu
+int trace_photons(bre_ctx *ctx, uint64_t first, uint64_t nPaths, int maxDepth, float radius);
+// nccl.cpp
+int nccl_init(bre_ctx *ctx, const void *uid);
+int nccl_allgather_photons(bre_ctx *ctx);
+void nccl_destroy(bre_ctx *ctx);
+int nccl_unique_id(void *out128);
+
+TreeDev tree_view(const bre_ctx *ctx);
+
+enum Phase { PH_TRACE = 0, PH_BUILD = 1, PH_TAU = 2, PH_QUERY = 3, PH_FILM = 4 };
+// RAII event bracket around a phase on the context stream (no-op unless timing is enabled)
+struct PhaseTimer {
+    bre_ctx *c; int ph;
+    PhaseTimer(bre_ctx *ctx, int phase) : c(ctx), ph(phase) {
+        if (c->timing) cudaEventRecord(c->ev[ph][0], c->stream);
+    }
+    ~PhaseTimer() {
+        if (c->timing) { cudaEventRecord(c->ev[ph][1], c->stream); c->ev_valid[ph] = true; }
+    }
+};
+
+}  // namespace bre

@@ -1,0 +1,430 @@
+// bre_query.cu -- K5 beam query (+ K6 optical-depth table for grid media).
+//
+// Replaces (reference src/): PhotonBeamBVH::Intersect (core/photonbeambvh.cpp:685-723) with
+// Bounds3::IntersectP (core/geometry.h:1410-1438), the per-candidate loop of the camera pass
+// (integrators/photonbeam.cpp:494-508), kernel() (integrators/photonmap.cpp:170-174, normalised as
+// :198), PhaseHG (core/medium.h:66-69) and Medium::Tr (media/homogeneous.cpp:44-48; for grid media a
+// deterministic optical-depth table instead of the stochastic media/grid.cpp:89-121).
+#include "bre_internal.cuh"
+
+namespace bre {
+
+// ---------------------------------------------------------------- per-ray state
+struct RayS {
+    float ox, oy, oz, tMax, dx, dy, dz;
+    float ix, iy, iz;        // 1/d
+    float nx, ny, nz;        // padded origin used for the near planes
+    float fx, fy, fz;        // padded origin used for the far planes
+    bool sx, sy, sz;         // direction negative
+};
+
+__device__ __forceinline__ RayS ray_setup(float4 o, float4 d, float absMax) {
+    RayS r;
+    r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tMax = o.w;
+    r.dx = d.x; r.dy = d.y; r.dz = d.z;
+    r.ix = fdiv(1.f, d.x); r.iy = fdiv(1.f, d.y); r.iz = fdiv(1.f, d.z);
+    r.sx = r.ix < 0.f; r.sy = r.iy < 0.f; r.sz = r.iz < 0.f;
+    // conservative cull: pad every box by 2^-18 * (|o|_inf + max|coord|)  
+    float M = fadd(fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z)), absMax);
+    float pad = fmul(M, 0x1p-18f);
+    float px = r.sx ? -pad : pad, py = r.sy ? -pad : pad, pz = r.sz ? -pad : pad;
+    r.nx = fadd(o.x, px); r.fx = fsub(o.x, px);
+    r.ny = fadd(o.y, py); r.fy = fsub(o.y, py);
+    r.nz = fadd(o.z, pz); r.fz = fsub(o.z, pz);
+    return r;
+}
+
+// Bounds3::IntersectP(ray, invDir, dirIsNeg), geometry.h:1410-1438, same operation order.
+__device__ __forceinline__ bool slab_hit(const RayS &r, float lox, float loy, float loz, float hix,
+                                         float hiy, float hiz) {
+    float tMin = fmul(fsub(r.sx ? hix : lox, r.nx), r.ix);
+    float tMax = fmul(fsub(r.sx ? lox : hix, r.fx), r.ix);
+    float tyMin = fmul(fsub(r.sy ? hiy : loy, r.ny), r.iy);
+    float tyMax = fmul(fsub(r.sy ? loy : hiy, r.fy), r.iy);
+    tMax = fmul(tMax, BRE_SLAB_WIDEN);
+    tyMax = fmul(tyMax, BRE_SLAB_WIDEN);
+    if (tMin > tyMax || tyMin > tMax) return false;
+    if (tyMin > tMin) tMin = tyMin;
+    if (tyMax < tMax) tMax = tyMax;
+    float tzMin = fmul(fsub(r.sz ? hiz : loz, r.nz), r.iz);
+    float tzMax = fmul(fsub(r.sz ? loz : hiz, r.fz), r.iz);
+    tzMax = fmul(tzMax, BRE_SLAB_WIDEN);
+    if (tMin > tzMax || tzMin > tMax) return false;
+    if (tzMin > tMin) tMin = tzMin;
+    if (tzMax < tMax) tMax = tzMax;
+    return (tMin < r.tMax) && (tMax > 0.f);
+}
+
+// Disk predicate (DESIGN.md "disk predicate"): bit-identical to oracle/bre_oracle.c orc_disk_test.
+__device__ __forceinline__ bool disk_test(const RayS &r, float4 p, float &t, float &d2) {
+    float vx = fsub(p.x, r.ox), vy = fsub(p.y, r.oy), vz = fsub(p.z, r.oz);
+    t = fadd(fadd(fmul(vx, r.dx), fmul(vy, r.dy)), fmul(vz, r.dz));
+    if (!(t > 0.f && t < r.tMax)) return false;
+    float wx = fsub(vx, fmul(t, r.dx)), wy = fsub(vy, fmul(t, r.dy)), wz = fsub(vz, fmul(t, r.dz));
+    d2 = fadd(fadd(fmul(wx, wx), fmul(wy, wy)), fmul(wz, wz));
+    float r2 = fmul(p.w, p.w);
+    return d2 < r2;
+}
+
+__device__ __forceinline__ float phase_hg(float cosTheta, float g) {  // medium.h:66-69
+    float denom = fadd(fadd(1.f, fmul(g, g)), fmul(fmul(2.f, g), cosTheta));
+    return fdiv(fmul(BRE_INV4PI, fsub(1.f, fmul(g, g))), fmul(denom, sqrtf(denom)));
+}
+
+struct TrState {
+    const float *tau;   // this ray's table (grid) or nullptr
+    float t0, t1;
+    int steps;
+};
+
+__device__ __forceinline__ void eval_tr(const MediumDev &m, const TrState &ts, float t, float tr[3]) {
+    if (m.kind == 0) {  // homogeneous.cpp:44-48
+#pragma unroll
+        for (int c = 0; c < 3; ++c) tr[c] = expf(-m.sigma_t[c] * t);
+    } else {
+        float od = 0.f;
+        if (ts.t1 > ts.t0) {
+            float dt = fdiv(fsub(ts.t1, ts.t0), (float)ts.steps);
+            float s = fdiv(fsub(t, ts.t0), dt);
+            if (s > 0.f) {
+                if (s >= (float)ts.steps) od = ts.tau[ts.steps];
+                else {
+                    int k = (int)s;
+                    float f = fsub(s, (float)k);
+                    float a = ts.tau[k], b = ts.tau[k + 1];
+                    od = fadd(a, fmul(f, fsub(b, a)));
+                }
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < 3; ++c) tr[c] = expf(-m.sigma_t[c] * od);
+    }
+}
+
+// ---------------------------------------------------------------- K6: optical depth table
+__device__ __forceinline__ float grid_D(const MediumDev &m, int x, int y, int z) {  // grid.h:78-82
+    if (x < 0 || y < 0 || z < 0 || x >= m.nx || y >= m.ny || z >= m.nz) return 0.f;
+    return __ldg(m.density + ((size_t)z * m.ny + y) * m.nx + x);
+}
+__device__ __forceinline__ float lerp1(float t, float a, float b) {
+    return fadd(fmul(fsub(1.f, t), a), fmul(t, b));
+}
+__device__ float grid_density(const MediumDev &m, float px, float py, float pz) {  // grid.cpp:45-60
+    float sx = fsub(fmul(px, (float)m.nx), .5f), sy = fsub(fmul(py, (float)m.ny), .5f),
+          sz = fsub(fmul(pz, (float)m.nz), .5f);
+    float fx = floorf(sx), fy = floorf(sy), fz = floorf(sz);
+    int ix = (int)fx, iy = (int)fy, iz = (int)fz;
+    float dx = fsub(sx, fx), dy = fsub(sy, fy), dz = fsub(sz, fz);
+    float d00 = lerp1(dx, grid_D(m, ix, iy, iz), grid_D(m, ix + 1, iy, iz));
+    float d10 = lerp1(dx, grid_D(m, ix, iy + 1, iz), grid_D(m, ix + 1, iy + 1, iz));
+    float d01 = lerp1(dx, grid_D(m, ix, iy, iz + 1), grid_D(m, ix + 1, iy, iz + 1));
+    float d11 = lerp1(dx, grid_D(m, ix, iy + 1, iz + 1), grid_D(m, ix + 1, iy + 1, iz + 1));
+    return lerp1(dz, lerp1(dy, d00, d10), lerp1(dy, d01, d11));
+}
+// Bounds3::IntersectP(ray,&t0,&t1) against the unit cube, geometry.h:1386-1408
+__device__ __forceinline__ bool unit_box(const float o[3], const float d[3], float tMaxRay,
+                                         float &t0, float &t1) {
+    t0 = 0.f; t1 = tMaxRay;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        float inv = fdiv(1.f, d[i]);
+        float tNear = fmul(fsub(0.f, o[i]), inv);
+        float tFar = fmul(fsub(1.f, o[i]), inv);
+        if (tNear > tFar) { float s = tNear; tNear = tFar; tFar = s; }
+        tFar = fmul(tFar, BRE_SLAB_WIDEN);
+        t0 = tNear > t0 ? tNear : t0;
+        t1 = tFar < t1 ? tFar : t1;
+        if (t0 > t1) return false;
+    }
+    return true;
+}
+__device__ __forceinline__ void to_medium(const MediumDev &m, const float o[3], const float d[3],
+                                          float om[3], float dm[3]) {
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        const float *w = m.w2m + 4 * r;
+        om[r] = fadd(fadd(fadd(fmul(w[0], o[0]), fmul(w[1], o[1])), fmul(w[2], o[2])), w[3]);
+        dm[r] = fadd(fadd(fmul(w[0], d[0]), fmul(w[1], d[1])), fmul(w[2], d[2]));
+    }
+}
+
+__global__ void __launch_bounds__(128) k_tau_table(MediumDev m, uint32_t n,
+                                                   const float4 *__restrict__ ro,
+                                                   const float4 *__restrict__ rd, int steps,
+                                                   float *__restrict__ tau,
+                                                   float2 *__restrict__ span) {
+    uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n) return;
+    float4 o4 = __ldg(ro + q), d4 = __ldg(rd + q);
+    float o[3] = {o4.x, o4.y, o4.z}, d[3] = {d4.x, d4.y, d4.z}, om[3], dm[3];
+    to_medium(m, o, d, om, dm);
+    float *row = tau + (size_t)q * (steps + 1);
+    float t0, t1;
+    if (!unit_box(om, dm, o4.w, t0, t1)) {
+        for (int k = 0; k <= steps; ++k) row[k] = 0.f;
+        span[q] = make_float2(0.f, 0.f);
+        return;
+    }
+    float dt = fdiv(fsub(t1, t0), (float)steps);
+    float acc = 0.f;
+    row[0] = 0.f;
+    for (int k = 0; k < steps; ++k) {
+        float t = fadd(t0, fmul(fadd((float)k, 0.5f), dt));
+        float dens = grid_density(m, fadd(om[0], fmul(dm[0], t)), fadd(om[1], fmul(dm[1], t)),
+                                  fadd(om[2], fmul(dm[2], t)));
+        acc = fadd(acc, fmul(dens, dt));
+        row[k + 1] = acc;
+    }
+    span[q] = make_float2(t0, t1);
+}
+
+// ---------------------------------------------------------------- K5: production traversal
+// MODE 0: radiance.  MODE 1: count hits per ray.  MODE 2: write hit indices (store order).
+// COUNT: also accumulate fast_nodes / fast_disk_tests.
+constexpr int QT = 128;
+constexpr int STACK = 64;
+
+template <int MODE, bool COUNT>
+__global__ void __launch_bounds__(QT) k_query(TreeDev t, MediumDev m, uint32_t n,
+                                              const float4 *__restrict__ ro,
+                                              const float4 *__restrict__ rd, float nPathsNorm,
+                                              float4 *__restrict__ out,
+                                              const float *__restrict__ tau,
+                                              const float2 *__restrict__ span, int tauSteps,
+                                              uint32_t *__restrict__ hitCounts,
+                                              const uint64_t *__restrict__ hitOffsets,
+                                              uint32_t *__restrict__ hitIdx,
+                                              unsigned long long *__restrict__ counters) {
+    uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long cNodes = 0, cTests = 0;
+    if (q < n) {
+        RayS r = ray_setup(__ldg(ro + q), __ldg(rd + q), t.abs_max);
+        TrState ts;
+        ts.tau = nullptr; ts.t0 = ts.t1 = 0.f; ts.steps = tauSteps;
+        if (MODE == 0 && m.kind == 1) {
+            ts.tau = tau + (size_t)q * (tauSteps + 1);
+            float2 sp = __ldg(span + q);
+            ts.t0 = sp.x; ts.t1 = sp.y;
+        }
+        float L0 = 0.f, L1 = 0.f, L2 = 0.f;
+        uint32_t nh = 0;
+        uint32_t *dst = nullptr;
+        if (MODE == 2) dst = hitIdx + hitOffsets[q];
+        int stack[STACK];
+        int sp = 0;
+        int cur = t.root_ref;
+        bool alive = t.n > 0 && r.tMax > 0.f;
+        while (alive) {
+            if (cur >= 0) {
+                const FastNode *fn = t.fast + cur;
+                float4 a = __ldg(&fn->a), b = __ldg(&fn->b), c = __ldg(&fn->c);
+                int4 d = __ldg(&fn->d);
+                if (COUNT) ++cNodes;
+                bool h0 = slab_hit(r, a.x, a.y, a.z, a.w, b.x, b.y);
+                bool h1 = slab_hit(r, b.z, b.w, c.x, c.y, c.z, c.w);
+                if (h0 && h1) { stack[sp++] = d.y; cur = d.x; }
+                else if (h0) cur = d.x;
+                else if (h1) cur = d.y;
+                else { if (sp == 0) break; cur = stack[--sp]; }
+            } else {
+                uint32_t first = (uint32_t)cur & 0x07ffffffu;
+                uint32_t cnt = (((uint32_t)cur >> 27) & 15u) + 1u;
+                for (uint32_t k = 0; k < cnt; ++k) {
+                    uint32_t s = first + k;
+                    float4 p = __ldg(t.s_pos_r + s);
+                    if (COUNT) ++cTests;
+                    float th, d2;
+                    if (disk_test(r, p, th, d2)) {
+                        if (MODE == 0) {
+                            float r2 = fmul(p.w, p.w);
+                            float sK = fsub(1.f, fdiv(d2, r2));
+                            float kk = fmul(fmul(3.f * BRE_INV_PI, sK), sK);
+                            float wgt = fdiv(kk, fmul(nPathsNorm, r2));
+                            float4 w = __ldg(t.s_dir + s);
+                            float cosT = fadd(fadd(fmul(-r.dx, w.x), fmul(-r.dy, w.y)), fmul(-r.dz, w.z));
+                            float wp = fmul(wgt, phase_hg(cosT, m.g));
+                            float tr[3];
+                            eval_tr(m, ts, th, tr);
+                            float4 pw = __ldg(t.s_pow + s);
+                            L0 = fadd(L0, fmul(fmul(wp, tr[0]), pw.x));
+                            L1 = fadd(L1, fmul(fmul(wp, tr[1]), pw.y));
+                            L2 = fadd(L2, fmul(fmul(wp, tr[2]), pw.z));
+                        } else if (MODE == 2) {
+                            dst[nh] = __ldg(t.order + s);
+                        }
+                        ++nh;
+                    }
+                }
+                if (sp == 0) break;
+                cur = stack[--sp];
+            }
+        }
+        if (MODE == 0) out[q] = make_float4(L0, L1, L2, 0.f);
+        if (MODE == 1) hitCounts[q] = nh;
+    }
+    if (COUNT) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            cNodes += __shfl_xor_sync(0xffffffffu, cNodes, o);
+            cTests += __shfl_xor_sync(0xffffffffu, cTests, o);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(counters + 3, cNodes);
+            atomicAdd(counters + 4, cTests);
+        }
+    }
+}
+
+// ---------------------------------------------------------------- canonical counting traversal
+// Walks the 1-photon-per-leaf canonical LBVH exactly like oracle/bre_oracle.c orc_query_ray and
+// counts V (slab tests), T (disk tests), H (hits).  counters[0..2].
+__global__ void __launch_bounds__(QT) k_count_canonical(TreeDev t, uint32_t n,
+                                                        const float4 *__restrict__ ro,
+                                                        const float4 *__restrict__ rd,
+                                                        unsigned long long *__restrict__ counters) {
+    uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long V = 0, T = 0, H = 0;
+    if (q < n && t.n > 0) {
+        RayS r = ray_setup(__ldg(ro + q), __ldg(rd + q), t.abs_max);
+        int stack[128];
+        int sp = 0;
+        int cur = t.n > 1 ? 0 : ~0;
+        for (;;) {
+            ++V;
+            if (cur < 0) {
+                int s = ~cur;
+                float4 lo = __ldg(t.leaf_lo + s), hi = __ldg(t.leaf_hi + s);
+                if (slab_hit(r, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z)) {
+                    ++T;
+                    float th, d2;
+                    if (disk_test(r, __ldg(t.s_pos_r + s), th, d2)) ++H;
+                }
+                if (sp == 0) break;
+                cur = stack[--sp];
+            } else {
+                float4 lo = __ldg(t.node_lo + cur), hi = __ldg(t.node_hi + cur);
+                if (slab_hit(r, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z)) {
+                    stack[sp++] = __float_as_int(hi.w);
+                    cur = __float_as_int(lo.w);
+                } else {
+                    if (sp == 0) break;
+                    cur = stack[--sp];
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        V += __shfl_xor_sync(0xffffffffu, V, o);
+        T += __shfl_xor_sync(0xffffffffu, T, o);
+        H += __shfl_xor_sync(0xffffffffu, H, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(counters + 0, V);
+        atomicAdd(counters + 1, T);
+        atomicAdd(counters + 2, H);
+    }
+}
+
+// ---------------------------------------------------------------- host drivers
+static int prepare_tau(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd,
+                       const float **tau, const float2 **span) {
+    *tau = nullptr; *span = nullptr;
+    if (ctx->medium.kind != 1) return BRE_OK;
+    int s;
+    size_t rowBytes = (size_t)(ctx->tau_steps + 1) * 4;
+    size_t offSpan = ((size_t)n * rowBytes + 15) & ~(size_t)15;
+    if ((s = ensure(ctx, ctx->tau, offSpan + (size_t)n * 8)) != BRE_OK) return s;
+    float *tp = (float *)ctx->tau.p;
+    float2 *sp = (float2 *)((char *)ctx->tau.p + offSpan);
+    {
+        PhaseTimer pt(ctx, PH_TAU);
+        k_tau_table<<<(n + 127) / 128, 128, 0, ctx->stream>>>(ctx->medium, n, ro, rd, ctx->tau_steps, tp, sp);
+    }
+    *tau = tp; *span = sp;
+    return BRE_OK;
+}
+
+int run_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, float nPathsNorm,
+              float4 *out) {
+    if (n == 0) return BRE_OK;
+    const float *tau; const float2 *span;
+    int s = prepare_tau(ctx, n, ro, rd, &tau, &span);
+    if (s != BRE_OK) return s;
+    {
+        PhaseTimer pt(ctx, PH_QUERY);
+        k_query<0, false><<<(n + QT - 1) / QT, QT, 0, ctx->stream>>>(
+            tree_view(ctx), ctx->medium, n, ro, rd, nPathsNorm, out, tau, span, ctx->tau_steps, nullptr,
+            nullptr, nullptr, nullptr);
+    }
+    BRE_CUDA(cudaGetLastError());
+    return BRE_OK;
+}
+
+int run_count(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd) {
+    int s;
+    if ((s = ensure(ctx, ctx->counters_d, 8 * 8)) != BRE_OK) return s;
+    unsigned long long *cd = (unsigned long long *)ctx->counters_d.p;
+    BRE_CUDA(cudaMemsetAsync(cd, 0, 64, ctx->stream));
+    if (n > 0) {
+        if ((s = ensure(ctx, ctx->hit_counts, (size_t)n * 4)) != BRE_OK) return s;
+        k_count_canonical<<<(n + QT - 1) / QT, QT, 0, ctx->stream>>>(tree_view(ctx), n, ro, rd, cd);
+        k_query<1, true><<<(n + QT - 1) / QT, QT, 0, ctx->stream>>>(
+            tree_view(ctx), ctx->medium, n, ro, rd, 1.f, nullptr, nullptr, nullptr, ctx->tau_steps,
+            (uint32_t *)ctx->hit_counts.p, nullptr, nullptr, cd);
+    }
+    unsigned long long h[8];
+    BRE_CUDA(cudaMemcpyAsync(h, cd, 64, cudaMemcpyDeviceToHost, ctx->stream));
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->counters.nodes_visited = h[0];
+    ctx->counters.disk_tests = h[1];
+    ctx->counters.hits = h[2];
+    ctx->counters.bytes_algorithmic = 48ull * n + 32ull * h[0] + 16ull * h[1] + 32ull * h[2];
+    ctx->counters.fast_nodes = h[3];
+    ctx->counters.fast_disk_tests = h[4];
+    return BRE_OK;
+}
+
+}  // namespace bre
+
+#include <algorithm>
+#include <vector>
+
+namespace bre {
+
+int run_hitdump(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, bre_hitdump *hd) {
+    hd->total = 0;
+    if (hd->offsets) hd->offsets[0] = 0;
+    if (n == 0) return BRE_OK;
+    int s;
+    if ((s = ensure(ctx, ctx->hit_counts, (size_t)n * 4)) != BRE_OK) return s;
+    if ((s = ensure(ctx, ctx->hit_offsets, ((size_t)n + 1) * 8)) != BRE_OK) return s;
+    k_query<1, false><<<(n + QT - 1) / QT, QT, 0, ctx->stream>>>(
+        tree_view(ctx), ctx->medium, n, ro, rd, 1.f, nullptr, nullptr, nullptr, ctx->tau_steps,
+        (uint32_t *)ctx->hit_counts.p, nullptr, nullptr, nullptr);
+    BRE_CUDA(cudaGetLastError());
+    std::vector<uint32_t> counts(n);
+    BRE_CUDA(cudaMemcpyAsync(counts.data(), ctx->hit_counts.p, (size_t)n * 4, cudaMemcpyDeviceToHost,
+                             ctx->stream));
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    std::vector<uint64_t> offs((size_t)n + 1);
+    offs[0] = 0;
+    for (uint32_t q = 0; q < n; ++q) offs[q + 1] = offs[q] + counts[q];
+    hd->total = offs[n];
+    if (hd->offsets) memcpy(hd->offsets, offs.data(), ((size_t)n + 1) * 8);
+    if (!hd->indices || hd->total > hd->capacity || hd->total == 0) return BRE_OK;
+    if ((s = ensure(ctx, ctx->hit_idx, (size_t)hd->total * 4)) != BRE_OK) return s;
+    BRE_CUDA(cudaMemcpyAsync(ctx->hit_offsets.p, offs.data(), ((size_t)n + 1) * 8,
+                             cudaMemcpyHostToDevice, ctx->stream));
+    k_query<2, false><<<(n + QT - 1) / QT, QT, 0, ctx->stream>>>(
+        tree_view(ctx), ctx->medium, n, ro, rd, 1.f, nullptr, nullptr, nullptr, ctx->tau_steps,
+        nullptr, (const uint64_t *)ctx->hit_offsets.p, (uint32_t *)ctx->hit_idx.p, nullptr);
+    BRE_CUDA(cudaGetLastError());
+    BRE_CUDA(cudaMemcpyAsync(hd->indices, ctx->hit_idx.p, (size_t)hd->total * 4,
+                             cudaMemcpyDeviceToHost, ctx->stream));
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (uint32_t q = 0; q < n; ++q) std::sort(hd->indices + offs[q], hd->indices + offs[q + 1]);
+    return BRE_OK;
+}
+
+}  // namespace bre

@@ -1,0 +1,193 @@
+/* include/bre.h -- C ABI of libbre.so, the B200-native (sm_100a) beam radiance estimate.
+ *
+ * This is the drop-in boundary for the volumetric photon-mapping Integrator of the
+ * pbrt-v3 fork bwiberg/beam-radiance-estimate-pbrt.  A pbrt-side adapter
+ * (beam-radiance-estimate-pbrt_b200/host/bre_integrator.{h,cpp})
+ * implements `class Integrator { virtual void Render(const Scene&) }`
+ * (reference src/core/integrator.h:53-58) and calls these entry points instead of
+ * the CPU code cited beside each of them.  `file:line` citations are relative to
+ * the reference's src/ directory.
+ *
+ * Conventions: plain C, opaque handle, every call returns BRE_OK (0) or a negative
+ * bre_status; bre_last_error(ctx) gives a message.  All pointers are HOST pointers
+ * unless the parameter name ends in `_d` (device pointer on the context's GPU).
+ * The caller owns every host buffer; the library owns device memory until
+ * bre_destroy.  One context per host thread, or serialise calls externally.
+ * Work is issued on one CUDA stream per context; calls that return host data
+ * synchronise before returning, `_d` calls are asynchronous on bre_get_stream().
+ * There is NO CPU fallback: without a CUDA device bre_create fails with
+ * BRE_ERR_NO_DEVICE.
+ */
+#ifndef BRE_H
+#define BRE_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BRE_ABI_VERSION 1
+
+typedef enum {
+    BRE_OK = 0,
+    BRE_ERR_INVALID = -1,     /* bad argument / call order */
+    BRE_ERR_NO_DEVICE = -2,   /* no usable CUDA device (no CPU fallback exists) */
+    BRE_ERR_CUDA = -3,        /* CUDA runtime error, see bre_last_error */
+    BRE_ERR_NOMEM = -4,
+    BRE_ERR_UNSUPPORTED = -5,
+    BRE_ERR_NCCL = -6
+} bre_status;
+
+typedef struct bre_ctx bre_ctx;
+
+typedef struct {
+    int device;                /* CUDA device ordinal for this rank */
+    int n_ranks;               /* 1 = single GPU */
+    int rank;
+    const void *nccl_unique_id; /* 128-byte ncclUniqueId shared by all ranks, or NULL when n_ranks==1 */
+    int max_leaf_photons;      /* photons per LBVH leaf on the fast path, 1..16; 0 = default (8) */
+    int tau_steps;             /* optical-depth table steps per ray for grid media; 0 = default (64) */
+} bre_config;
+
+typedef struct {
+    int kind;                  /* 0 = point (lights/point.cpp:61-71), 1 = spot (lights/spot.cpp:64-93) */
+    float pos[3];
+    float I[3];
+    float axis[3];             /* spot only: unit direction the cone points along */
+    float cos_total_width;     /* spot only */
+    float cos_falloff_start;   /* spot only */
+} bre_light;
+
+typedef struct {
+    uint64_t nodes_visited;    /* V: slab tests on the canonical 1-photon/leaf LBVH */
+    uint64_t disk_tests;       /* T: photons whose canonical leaf box passed the slab test */
+    uint64_t hits;             /* H */
+    uint64_t bytes_algorithmic;/* sum over rays of 32 + 32 V + 16 T + 32 H + 16 */
+    uint64_t fast_nodes;       /* 64-byte two-child nodes fetched by the production kernel */
+    uint64_t fast_disk_tests;  /* disk tests done by the production kernel (leaf size > 1) */
+} bre_counters;
+
+typedef struct {
+    uint64_t *offsets;         /* nRays+1 entries, filled by the library */
+    uint32_t *indices;         /* caller buffer for ORIGINAL photon indices, ascending per ray */
+    uint64_t capacity;         /* entries available in `indices` */
+    uint64_t total;            /* out: total hits (if > capacity nothing is written to indices) */
+} bre_hitdump;
+
+/* ---- lifetime ------------------------------------------------------------------ */
+int bre_abi_version(void);
+/* Replaces the construction done in CreatePhotonBeamIntegrator (integrators/photonbeam.cpp:589-611). */
+int bre_create(bre_ctx **ctx, const bre_config *cfg);
+int bre_destroy(bre_ctx *ctx);
+const char *bre_last_error(const bre_ctx *ctx);
+/* cudaStream_t the context issues work on (as void*). */
+void *bre_get_stream(bre_ctx *ctx);
+int bre_synchronize(bre_ctx *ctx);
+/* rank 0 creates the id every rank passes in bre_config.nccl_unique_id (128 bytes). */
+int bre_nccl_unique_id(void *out128);
+
+/* ---- scene inputs --------------------------------------------------------------- */
+/* HomogeneousMedium (media/homogeneous.h, factory core/api.cpp:547-596). */
+int bre_set_medium_homogeneous(bre_ctx *ctx, const float sigma_a[3], const float sigma_s[3], float g);
+/* GridDensityMedium (media/grid.h:51-75): density nx*ny*nz floats, x fastest; world_to_medium row-major 4x4. */
+int bre_set_medium_grid(bre_ctx *ctx, const float sigma_a[3], const float sigma_s[3], float g,
+                        int nx, int ny, int nz, const float *density, const float world_to_medium[16]);
+/* scene.lights + ComputeLightPowerDistribution (core/integrator.cpp:217-225). */
+int bre_set_lights(bre_ctx *ctx, int n, const bre_light *lights);
+/* Absorbing axis-aligned scene box that ends photon paths (stand-in for Scene::Intersect,
+ * core/scene.cpp:50-54, until the triangle intersector of SURVEY.md 8f-1 exists). */
+int bre_set_bounds(bre_ctx *ctx, const float lo[3], const float hi[3]);
+/* Surfaces for photon tracing: not built yet -> BRE_ERR_UNSUPPORTED. */
+int bre_set_triangles(bre_ctx *ctx, uint32_t n_tri, const float *P, const uint32_t *idx, const float *Kd);
+
+/* ---- K1: volume photon tracing ---------------------------------------------------
+ * Replaces the photon pass of PhotonBeamIntegrator::Render (integrators/photonbeam.cpp:365-437,
+ * TracePhotonBeamRecursive :258-325) with the volume-photon deposit rule of
+ * PhotonIntegrator::ShootPhotons (integrators/photonmap.cpp:696-724).
+ * Traces path indices [first_index, first_index+n_paths); photons are appended to the
+ * context's photon store in path-index order (deterministic).  `radius` is the gather
+ * radius given to every new photon.  *n_stored (optional) = photons in the store afterwards. */
+int bre_trace_photons(bre_ctx *ctx, uint64_t first_index, uint64_t n_paths, int max_depth,
+                      float radius, uint64_t *n_stored);
+/* Parity path: load photons dumped from the reference.  AoS float triples as in
+ * struct Photon (integrators/photonmap.cpp:61-70).  radii==NULL -> every photon gets `radius`.
+ * append=0 replaces the store. */
+int bre_upload_photons(bre_ctx *ctx, uint64_t n, const float *p_xyz, const float *alpha_rgb,
+                       const float *wi_xyz, float radius, const float *radii, int append);
+int bre_clear_photons(bre_ctx *ctx);
+int bre_photon_count(bre_ctx *ctx, uint64_t *n);
+/* Copy the photon store back (any pointer may be NULL). */
+int bre_download_photons(bre_ctx *ctx, uint64_t cap, float *p_xyz, float *alpha_rgb, float *wi_xyz,
+                         float *radii);
+/* Set the radius of every stored photon (progressive shrink, integrators/photonbeam.cpp:354-356,562). */
+int bre_set_radius(bre_ctx *ctx, float radius);
+/* Multi-GPU: all-gather every rank's photon store in rank-major order (NCCL over NVLink). */
+int bre_allgather_photons(bre_ctx *ctx);
+
+/* ---- K2-K4: LBVH build -----------------------------------------------------------
+ * Replaces PhotonBeamBVH::PhotonBeamBVH (core/photonbeambvh.cpp:204-248: recursiveBuild :259-425
+ * / HLBVH2Build :427-495 with EncodeMorton3 :134-139, RadixSort :141-182, emitLBVH2 :497-559,
+ * flattenBVH2Tree :663-681) and KdTree<Photon> (core/kdtree.h:101-149). */
+int bre_build(bre_ctx *ctx);
+/* Debug/parity: copy the canonical tree back.  order: n u32 (sorted pos -> photon index);
+ * codes: n u32; node_lo/node_hi: (n-1)*3 floats; node_children: (n-1)*2 int32 (>=0 internal,
+ * <0 = ~sorted leaf position).  Any pointer may be NULL. */
+int bre_download_tree(bre_ctx *ctx, uint32_t *order, uint32_t *codes, float *node_lo, float *node_hi,
+                      int32_t *node_children);
+
+/* ---- K5/K6: beam query -----------------------------------------------------------
+ * Replaces PhotonBeamBVH::Intersect (core/photonbeambvh.cpp:685-723) + the candidate loop of
+ * the camera pass (integrators/photonbeam.cpp:494-508) + Medium::Tr (media/homogeneous.cpp:44-48,
+ * media/grid.cpp:89-121).  o_xyz_tmax: n_rays*4 {ox,oy,oz,tMax}; d_xyz: n_rays*3 unit directions.
+ * n_paths_norm = number of emitted photon paths (integrators/photonmap.cpp:198).
+ * out_rgb: n_rays*3.  hits: optional per-ray hit-index dump (parity). */
+int bre_query(bre_ctx *ctx, uint32_t n_rays, const float *o_xyz_tmax, const float *d_xyz,
+              float n_paths_norm, float *out_rgb, bre_hitdump *hits);
+/* Device-resident variant: rays_o_d / rays_d_d are float4 arrays {ox,oy,oz,tMax} / {dx,dy,dz,0};
+ * out_rgb_d float4 {r,g,b,0}.  Asynchronous on the context stream. */
+int bre_query_d(bre_ctx *ctx, uint32_t n_rays, const void *rays_o_d, const void *rays_d_d,
+                float n_paths_norm, void *out_rgb_d);
+/* Host rays -> device query -> film accumulation on the device, nothing copied back: the call
+ * the pbrt adapter makes once per camera pass (integrators/photonbeam.cpp:444-557).
+ * pixel_idx==NULL -> ray q belongs to pixel q. */
+int bre_query_to_film(bre_ctx *ctx, uint32_t n_rays, const float *o_xyz_tmax, const float *d_xyz,
+                      const uint32_t *pixel_idx, float n_paths_norm);
+/* Counting pass on the canonical tree for the same rays (fills V,T,H,bytes) plus the
+ * production kernel's own counters. */
+int bre_count(bre_ctx *ctx, uint32_t n_rays, const float *o_xyz_tmax, const float *d_xyz);
+int bre_count_d(bre_ctx *ctx, uint32_t n_rays, const void *rays_o_d, const void *rays_d_d);
+int bre_get_counters(bre_ctx *ctx, bre_counters *out);
+
+/* ---- K7: film ---------------------------------------------------------------------
+ * Replaces PhotonBeamPixel::Ld accumulation (integrators/photonbeam.cpp:504), L = Ld/(iter+1)
+ * (:578), Film::SetImage (core/film.cpp:132-140) and the arithmetic of Film::WriteImage
+ * (core/film.cpp:168-204). */
+int bre_film_create(bre_ctx *ctx, uint32_t n_pixels);
+int bre_film_clear(bre_ctx *ctx);
+/* pixel_idx==NULL -> ray q belongs to pixel q.  rgb = n_rays*3 host floats. */
+int bre_film_accumulate(bre_ctx *ctx, uint32_t n_rays, const uint32_t *pixel_idx, const float *rgb);
+/* Device variant: rgb_d float4 per ray; pixel_idx_d may be NULL. */
+int bre_film_accumulate_d(bre_ctx *ctx, uint32_t n_rays, const uint32_t *pixel_idx_d, const void *rgb_d);
+/* rgb_out: n_pixels*3 floats = what Film::WriteImage hands to pbrt::WriteImage. */
+int bre_film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out);
+/* Multi-GPU: after resolve on every rank, gather disjoint pixel ranges to rank 0. */
+
+/* ---- device timing ------------------------------------------------------------------
+ * With timing enabled every phase is bracketed by CUDA events on the context stream.
+ * bre_get_timings synchronises and returns the LAST duration of each phase in milliseconds:
+ * ms[0]=K1 trace, ms[1]=K2-K4 build, ms[2]=K6 optical-depth table, ms[3]=K5 beam query kernel,
+ * ms[4]=K7 film accumulate, ms[5..7] reserved (0). */
+int bre_set_timing(bre_ctx *ctx, int enabled);
+int bre_get_timings(bre_ctx *ctx, float ms[8]);
+
+/* ---- host-side sharding helpers (pure functions, no GPU needed) -------------------- */
+/* Photon path indices [first, first+count) owned by `rank` out of n_ranks. */
+void bre_shard_range(uint64_t n, int n_ranks, int rank, uint64_t *first, uint64_t *count);
+/* Owner rank of a 16x16 image tile (integrators/photonbeam.cpp:345-347) dealt round-robin. */
+int bre_tile_owner(uint32_t tile_x, uint32_t tile_y, uint32_t tiles_x, int n_ranks);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BRE_H */
