@@ -102,6 +102,8 @@ struct Buf {
 struct bre_ctx {
     int device = 0, n_ranks = 1, rank = 0;
     int max_leaf = 8, tau_steps = 64;
+    int query_kernel = 1;     // 1 = warp-cooperative packets (default), 0 = thread per ray
+    int sm_count = 148;
     cudaStream_t stream = nullptr;
     std::string err;
 
@@ -125,6 +127,7 @@ struct bre_ctx {
     float abs_max = 0;
     int root_ref = 0;
     // query scratch
+    bre::Buf packet_ctr;
     bre::Buf rays_o, rays_d, out_rgb, tau, hit_counts, hit_offsets, hit_idx, counters_d, pix_idx;
     bre_counters counters{};
     // film

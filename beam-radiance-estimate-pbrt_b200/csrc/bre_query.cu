@@ -275,6 +275,39 @@ __global__ void __launch_bounds__(QT) k_query(TreeDev t, MediumDev m, uint32_t n
     }
 }
 
+}  // namespace bre
+#include "bre_query_warp.cuh"
+namespace bre {
+
+// Launch the production traversal: warp-cooperative (default) or thread-per-ray (BRE_QUERY_KERNEL=thread).
+template <int MODE, bool COUNT>
+static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, float nPathsNorm,
+                        float4 *out, const float *tau, const float2 *span, uint32_t *hitCounts,
+                        const uint64_t *hitOffsets, uint32_t *hitIdx, unsigned long long *counters) {
+    if (ctx->query_kernel == 0) {
+        k_query<MODE, COUNT><<<(n + QT - 1) / QT, QT, 0, ctx->stream>>>(
+            tree_view(ctx), ctx->medium, n, ro, rd, nPathsNorm, out, tau, span, ctx->tau_steps,
+            hitCounts, hitOffsets, hitIdx, counters);
+    } else {
+        int s;
+        if ((s = ensure(ctx, ctx->packet_ctr, 64)) != BRE_OK) return s;
+        BRE_CUDA(cudaMemsetAsync(ctx->packet_ctr.p, 0, 4, ctx->stream));
+        int perSM = 0;
+        BRE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_query_warp<MODE, COUNT>,
+                                                               WQ_WARPS * 32, 0));
+        if (perSM < 1) perSM = 1;
+        unsigned packets = (n + WQ_P - 1) / WQ_P;
+        unsigned blocks = (unsigned)(ctx->sm_count * perSM);
+        unsigned need = (packets + WQ_WARPS - 1) / WQ_WARPS;
+        if (blocks > need) blocks = need;
+        k_query_warp<MODE, COUNT><<<blocks, WQ_WARPS * 32, 0, ctx->stream>>>(
+            tree_view(ctx), ctx->medium, n, ro, rd, nPathsNorm, out, tau, span, ctx->tau_steps,
+            hitCounts, hitOffsets, hitIdx, counters, (unsigned int *)ctx->packet_ctr.p);
+    }
+    BRE_CUDA(cudaGetLastError());
+    return BRE_OK;
+}
+
 // ---------------------------------------------------------------- canonical counting traversal
 // Walks the 1-photon-per-leaf canonical LBVH exactly like oracle/bre_oracle.c orc_query_ray and
 // counts V (slab tests), T (disk tests), H (hits).  counters[0..2].
@@ -353,12 +386,9 @@ int run_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, floa
     if (s != BRE_OK) return s;
     {
         PhaseTimer pt(ctx, PH_QUERY);
-        k_query<0, false><<<(n + QT - 1) / QT, QT, 0, ctx->stream>>>(
-            tree_view(ctx), ctx->medium, n, ro, rd, nPathsNorm, out, tau, span, ctx->tau_steps, nullptr,
-            nullptr, nullptr, nullptr);
+        s = launch_query<0, false>(ctx, n, ro, rd, nPathsNorm, out, tau, span, nullptr, nullptr, nullptr, nullptr);
     }
-    BRE_CUDA(cudaGetLastError());
-    return BRE_OK;
+    return s;
 }
 
 int run_count(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd) {
@@ -369,9 +399,8 @@ int run_count(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd) {
     if (n > 0) {
         if ((s = ensure(ctx, ctx->hit_counts, (size_t)n * 4)) != BRE_OK) return s;
         k_count_canonical<<<(n + QT - 1) / QT, QT, 0, ctx->stream>>>(tree_view(ctx), n, ro, rd, cd);
-        k_query<1, true><<<(n + QT - 1) / QT, QT, 0, ctx->stream>>>(
-            tree_view(ctx), ctx->medium, n, ro, rd, 1.f, nullptr, nullptr, nullptr, ctx->tau_steps,
-            (uint32_t *)ctx->hit_counts.p, nullptr, nullptr, cd);
+        if ((s = launch_query<1, true>(ctx, n, ro, rd, 1.f, nullptr, nullptr, nullptr,
+                                       (uint32_t *)ctx->hit_counts.p, nullptr, nullptr, cd)) != BRE_OK) return s;
     }
     unsigned long long h[8];
     BRE_CUDA(cudaMemcpyAsync(h, cd, 64, cudaMemcpyDeviceToHost, ctx->stream));
@@ -399,10 +428,8 @@ int run_hitdump(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, br
     int s;
     if ((s = ensure(ctx, ctx->hit_counts, (size_t)n * 4)) != BRE_OK) return s;
     if ((s = ensure(ctx, ctx->hit_offsets, ((size_t)n + 1) * 8)) != BRE_OK) return s;
-    k_query<1, false><<<(n + QT - 1) / QT, QT, 0, ctx->stream>>>(
-        tree_view(ctx), ctx->medium, n, ro, rd, 1.f, nullptr, nullptr, nullptr, ctx->tau_steps,
-        (uint32_t *)ctx->hit_counts.p, nullptr, nullptr, nullptr);
-    BRE_CUDA(cudaGetLastError());
+    if ((s = launch_query<1, false>(ctx, n, ro, rd, 1.f, nullptr, nullptr, nullptr,
+                                    (uint32_t *)ctx->hit_counts.p, nullptr, nullptr, nullptr)) != BRE_OK) return s;
     std::vector<uint32_t> counts(n);
     BRE_CUDA(cudaMemcpyAsync(counts.data(), ctx->hit_counts.p, (size_t)n * 4, cudaMemcpyDeviceToHost,
                              ctx->stream));
@@ -416,10 +443,9 @@ int run_hitdump(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, br
     if ((s = ensure(ctx, ctx->hit_idx, (size_t)hd->total * 4)) != BRE_OK) return s;
     BRE_CUDA(cudaMemcpyAsync(ctx->hit_offsets.p, offs.data(), ((size_t)n + 1) * 8,
                              cudaMemcpyHostToDevice, ctx->stream));
-    k_query<2, false><<<(n + QT - 1) / QT, QT, 0, ctx->stream>>>(
-        tree_view(ctx), ctx->medium, n, ro, rd, 1.f, nullptr, nullptr, nullptr, ctx->tau_steps,
-        nullptr, (const uint64_t *)ctx->hit_offsets.p, (uint32_t *)ctx->hit_idx.p, nullptr);
-    BRE_CUDA(cudaGetLastError());
+    if ((s = launch_query<2, false>(ctx, n, ro, rd, 1.f, nullptr, nullptr, nullptr, nullptr,
+                                    (const uint64_t *)ctx->hit_offsets.p, (uint32_t *)ctx->hit_idx.p,
+                                    nullptr)) != BRE_OK) return s;
     BRE_CUDA(cudaMemcpyAsync(hd->indices, ctx->hit_idx.p, (size_t)hd->total * 4,
                              cudaMemcpyDeviceToHost, ctx->stream));
     BRE_CUDA(cudaStreamSynchronize(ctx->stream));

@@ -241,3 +241,42 @@ def test_trace_photons_statistical(oracle, ctx):
     ctx.trace_photons(npaths // 2, npaths - npaths // 2, 5, 0.05)
     pos2, pw2, dr2, _ = ctx.download_photons()
     assert np.array_equal(pos2, pos) and np.array_equal(pw2, pw) and np.array_equal(dr2, dr)
+
+
+@pytest.mark.parametrize("kernel", ["thread", "warp"])
+def test_both_traversal_kernels(oracle, bre, monkeypatch, kernel):
+    """The thread-per-ray kernel (kept for A/B measurement) and the production warp-cooperative
+    kernel return the same hit sets."""
+    monkeypatch.setenv("BRE_QUERY_KERNEL", kernel)
+    c = bre.Bre(device=0)
+    try:
+        n = 40000
+        setup_uniform(oracle, c, n, 48)
+        ro, rd = oracle.synth_rays_pinhole(50, 37)      # ragged: not a multiple of the packet size
+        ref_rgb, ref_offs, ref_idx, _ = oracle.query(ro, rd, float(n), want_hits=True)
+        rgb, offs, idx = c.query(ro, rd, float(n), want_hits=True)
+        assert np.array_equal(offs, ref_offs) and np.array_equal(idx, ref_idx)
+        assert_radiance(rgb, ref_rgb)
+    finally:
+        c.close()
+
+
+def test_heavy_ray_skew(oracle, ctx):
+    """A ray through a dense photon cluster (light source in view): thousands of hits on one ray."""
+    rng = np.random.default_rng(11)
+    n = 60000
+    pos, pw, dr = oracle.synth_photons_uniform(n)
+    pos[:30000] = (np.array([0.5, 0.5, 0.5]) + rng.normal(0, 0.004, (30000, 3))).astype(np.float32)
+    r = 0.01
+    oracle.set_medium_homogeneous(SA, SS, 0.3)
+    oracle.set_photons(pos, pw, dr, r)
+    oracle.build()
+    ctx.set_medium_homogeneous(SA, SS, 0.3)
+    ctx.upload_photons(pos, pw, dr, radius=r)
+    ctx.build()
+    ro, rd = oracle.synth_rays_pinhole(33, 33)
+    ref_rgb, ref_offs, ref_idx, _ = oracle.query(ro, rd, float(n), want_hits=True)
+    assert np.diff(ref_offs.astype(np.int64)).max() > 5000
+    rgb, offs, idx = ctx.query(ro, rd, float(n), want_hits=True)
+    assert np.array_equal(offs, ref_offs) and np.array_equal(idx, ref_idx)
+    assert_radiance(rgb, ref_rgb)
