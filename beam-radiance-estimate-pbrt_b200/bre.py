@@ -49,7 +49,8 @@ class Light(C.Structure):
 class Counters(C.Structure):
     _fields_ = [("nodes_visited", C.c_uint64), ("disk_tests", C.c_uint64), ("hits", C.c_uint64),
                 ("bytes_algorithmic", C.c_uint64), ("fast_nodes", C.c_uint64),
-                ("fast_disk_tests", C.c_uint64)]
+                ("fast_disk_tests", C.c_uint64), ("leaf_pairs", C.c_uint64),
+                ("pair_queue_overflow", C.c_uint64)]
 
 
 class HitDump(C.Structure):
@@ -240,7 +241,7 @@ class Bre:
     def timings(self):
         ms = (C.c_float * 8)()
         self._ck(self.lib.bre_get_timings(self.ctx, ms))
-        return dict(trace=ms[0], build=ms[1], tau=ms[2], query=ms[3], film=ms[4])
+        return dict(trace=ms[0], build=ms[1], tau=ms[2], query=ms[3], film=ms[4], query_a=ms[5], query_b=ms[6])
 
     def count(self, o_tmax, dirs):
         o = _f32(o_tmax); d = _f32(dirs)

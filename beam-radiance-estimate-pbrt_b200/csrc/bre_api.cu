@@ -121,8 +121,8 @@ int bre_create(bre_ctx **out, const bre_config *cfg) {
         return BRE_ERR_CUDA;
     }
     {
-        const char *qk = getenv("BRE_QUERY_KERNEL");
-        if (qk && strcmp(qk, "thread") == 0) ctx->query_kernel = 0;
+        const char *qc = getenv("BRE_PAIR_QUEUE_CAP");
+        if (qc && atoll(qc) > 0) ctx->pair_queue_cap_override = (uint64_t)atoll(qc);
         cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, ctx->device);
     }
     if (ctx->n_ranks > 1) {
@@ -144,7 +144,7 @@ int bre_destroy(bre_ctx *ctx) {
                    &ctx->node_lo, &ctx->node_hi, &ctx->node_range, &ctx->parent, &ctx->leaf_lo,
                    &ctx->leaf_hi, &ctx->flags, &ctx->fast, &ctx->scratch, &ctx->rays_o, &ctx->rays_d,
                    &ctx->out_rgb, &ctx->tau, &ctx->hit_counts, &ctx->hit_offsets, &ctx->hit_idx,
-                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->film, &ctx->path_counts, &ctx->path_offsets};
+                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->film, &ctx->path_counts, &ctx->path_offsets};
     for (Buf *b : bufs) if (b->p) cudaFree(b->p);
     if (ctx->lights_d) cudaFree(ctx->lights_d);
     for (int i = 0; i < 8; ++i)

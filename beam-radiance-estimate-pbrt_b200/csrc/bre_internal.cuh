@@ -102,8 +102,8 @@ struct Buf {
 struct bre_ctx {
     int device = 0, n_ranks = 1, rank = 0;
     int max_leaf = 8, tau_steps = 64;
-    int query_kernel = 1;     // 1 = warp-cooperative packets (default), 0 = thread per ray
     int sm_count = 148;
+    uint64_t pair_queue_cap_override = 0;   // BRE_PAIR_QUEUE_CAP (tests force the overflow path)
     cudaStream_t stream = nullptr;
     std::string err;
 
@@ -127,7 +127,7 @@ struct bre_ctx {
     float abs_max = 0;
     int root_ref = 0;
     // query scratch
-    bre::Buf packet_ctr;
+    bre::Buf packet_ctr, pair_queue;
     bre::Buf rays_o, rays_d, out_rgb, tau, hit_counts, hit_offsets, hit_idx, counters_d, pix_idx;
     bre_counters counters{};
     // film
@@ -174,7 +174,7 @@ int nccl_unique_id(void *out128);
 
 TreeDev tree_view(const bre_ctx *ctx);
 
-enum Phase { PH_TRACE = 0, PH_BUILD = 1, PH_TAU = 2, PH_QUERY = 3, PH_FILM = 4 };
+enum Phase { PH_TRACE = 0, PH_BUILD = 1, PH_TAU = 2, PH_QUERY = 3, PH_FILM = 4, PH_QUERY_A = 5, PH_QUERY_B = 6 };
 // RAII event bracket around a phase on the context stream (no-op unless timing is enabled)
 struct PhaseTimer {
     bre_ctx *c; int ph;

@@ -178,131 +178,50 @@ __global__ void __launch_bounds__(128) k_tau_table(MediumDev m, uint32_t n,
     span[q] = make_float2(t0, t1);
 }
 
-// ---------------------------------------------------------------- K5: production traversal
-// MODE 0: radiance.  MODE 1: count hits per ray.  MODE 2: write hit indices (store order).
-// COUNT: also accumulate fast_nodes / fast_disk_tests.
-constexpr int QT = 128;
-constexpr int STACK = 64;
-
-template <int MODE, bool COUNT>
-__global__ void __launch_bounds__(QT) k_query(TreeDev t, MediumDev m, uint32_t n,
-                                              const float4 *__restrict__ ro,
-                                              const float4 *__restrict__ rd, float nPathsNorm,
-                                              float4 *__restrict__ out,
-                                              const float *__restrict__ tau,
-                                              const float2 *__restrict__ span, int tauSteps,
-                                              uint32_t *__restrict__ hitCounts,
-                                              const uint64_t *__restrict__ hitOffsets,
-                                              uint32_t *__restrict__ hitIdx,
-                                              unsigned long long *__restrict__ counters) {
-    uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
-    unsigned long long cNodes = 0, cTests = 0;
-    if (q < n) {
-        RayS r = ray_setup(__ldg(ro + q), __ldg(rd + q), t.abs_max);
-        TrState ts;
-        ts.tau = nullptr; ts.t0 = ts.t1 = 0.f; ts.steps = tauSteps;
-        if (MODE == 0 && m.kind == 1) {
-            ts.tau = tau + (size_t)q * (tauSteps + 1);
-            float2 sp = __ldg(span + q);
-            ts.t0 = sp.x; ts.t1 = sp.y;
-        }
-        float L0 = 0.f, L1 = 0.f, L2 = 0.f;
-        uint32_t nh = 0;
-        uint32_t *dst = nullptr;
-        if (MODE == 2) dst = hitIdx + hitOffsets[q];
-        int stack[STACK];
-        int sp = 0;
-        int cur = t.root_ref;
-        bool alive = t.n > 0 && r.tMax > 0.f;
-        while (alive) {
-            if (cur >= 0) {
-                const FastNode *fn = t.fast + cur;
-                float4 a = __ldg(&fn->a), b = __ldg(&fn->b), c = __ldg(&fn->c);
-                int4 d = __ldg(&fn->d);
-                if (COUNT) ++cNodes;
-                bool h0 = slab_hit(r, a.x, a.y, a.z, a.w, b.x, b.y);
-                bool h1 = slab_hit(r, b.z, b.w, c.x, c.y, c.z, c.w);
-                if (h0 && h1) { stack[sp++] = d.y; cur = d.x; }
-                else if (h0) cur = d.x;
-                else if (h1) cur = d.y;
-                else { if (sp == 0) break; cur = stack[--sp]; }
-            } else {
-                uint32_t first = (uint32_t)cur & 0x07ffffffu;
-                uint32_t cnt = (((uint32_t)cur >> 27) & 15u) + 1u;
-                for (uint32_t k = 0; k < cnt; ++k) {
-                    uint32_t s = first + k;
-                    float4 p = __ldg(t.s_pos_r + s);
-                    if (COUNT) ++cTests;
-                    float th, d2;
-                    if (disk_test(r, p, th, d2)) {
-                        if (MODE == 0) {
-                            float r2 = fmul(p.w, p.w);
-                            float sK = fsub(1.f, fdiv(d2, r2));
-                            float kk = fmul(fmul(3.f * BRE_INV_PI, sK), sK);
-                            float wgt = fdiv(kk, fmul(nPathsNorm, r2));
-                            float4 w = __ldg(t.s_dir + s);
-                            float cosT = fadd(fadd(fmul(-r.dx, w.x), fmul(-r.dy, w.y)), fmul(-r.dz, w.z));
-                            float wp = fmul(wgt, phase_hg(cosT, m.g));
-                            float tr[3];
-                            eval_tr(m, ts, th, tr);
-                            float4 pw = __ldg(t.s_pow + s);
-                            L0 = fadd(L0, fmul(fmul(wp, tr[0]), pw.x));
-                            L1 = fadd(L1, fmul(fmul(wp, tr[1]), pw.y));
-                            L2 = fadd(L2, fmul(fmul(wp, tr[2]), pw.z));
-                        } else if (MODE == 2) {
-                            dst[nh] = __ldg(t.order + s);
-                        }
-                        ++nh;
-                    }
-                }
-                if (sp == 0) break;
-                cur = stack[--sp];
-            }
-        }
-        if (MODE == 0) out[q] = make_float4(L0, L1, L2, 0.f);
-        if (MODE == 1) hitCounts[q] = nh;
-    }
-    if (COUNT) {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            cNodes += __shfl_xor_sync(0xffffffffu, cNodes, o);
-            cTests += __shfl_xor_sync(0xffffffffu, cTests, o);
-        }
-        if ((threadIdx.x & 31) == 0) {
-            atomicAdd(counters + 3, cNodes);
-            atomicAdd(counters + 4, cTests);
-        }
-    }
-}
-
 }  // namespace bre
+constexpr int QT = 128;
 #include "bre_query_warp.cuh"
 namespace bre {
 
-// Launch the production traversal: warp-cooperative (default) or thread-per-ray (BRE_QUERY_KERNEL=thread).
+// Launch K5a (traversal -> pair queue) and K5b (pairs -> radiance / hit lists) back to back.
 template <int MODE, bool COUNT>
 static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, float nPathsNorm,
                         float4 *out, const float *tau, const float2 *span, uint32_t *hitCounts,
                         const uint64_t *hitOffsets, uint32_t *hitIdx, unsigned long long *counters) {
-    if (ctx->query_kernel == 0) {
-        k_query<MODE, COUNT><<<(n + QT - 1) / QT, QT, 0, ctx->stream>>>(
-            tree_view(ctx), ctx->medium, n, ro, rd, nPathsNorm, out, tau, span, ctx->tau_steps,
-            hitCounts, hitOffsets, hitIdx, counters);
-    } else {
-        int s;
-        if ((s = ensure(ctx, ctx->packet_ctr, 64)) != BRE_OK) return s;
-        BRE_CUDA(cudaMemsetAsync(ctx->packet_ctr.p, 0, 4, ctx->stream));
+    int s;
+    // pair queue: 48 pairs per ray (mean is ~25 at 8 photons/leaf), at least 1M, at most 256M pairs
+    uint64_t want = (uint64_t)n * 48u;
+    if (want < (1u << 20)) want = 1u << 20;
+    if (want > (1u << 28)) want = 1u << 28;
+    if (ctx->pair_queue_cap_override) want = ctx->pair_queue_cap_override;
+    if ((s = ensure(ctx, ctx->pair_queue, (size_t)want * 8)) != BRE_OK) return s;
+    if ((s = ensure(ctx, ctx->packet_ctr, 64)) != BRE_OK) return s;
+    const unsigned cap = (unsigned)want;
+    unsigned int *ctl = (unsigned int *)ctx->packet_ctr.p;
+    BRE_CUDA(cudaMemsetAsync(ctl, 0, 16, ctx->stream));
+    if (MODE == 0) BRE_CUDA(cudaMemsetAsync(out, 0, (size_t)n * 16, ctx->stream));
+    else BRE_CUDA(cudaMemsetAsync(hitCounts, 0, (size_t)n * 4, ctx->stream));
+    LeafArgs A;
+    A.t = tree_view(ctx); A.m = ctx->medium; A.ro = ro; A.rd = rd; A.nPathsNorm = nPathsNorm;
+    A.out = out; A.tau = tau; A.span = span; A.tauSteps = ctx->tau_steps;
+    A.hitCounts = hitCounts; A.hitOffsets = hitOffsets; A.hitIdx = hitIdx;
+    {
+        PhaseTimer pt(ctx, PH_QUERY_A);
         int perSM = 0;
-        BRE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_query_warp<MODE, COUNT>,
+        BRE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_traverse<MODE, COUNT>,
                                                                WQ_WARPS * 32, 0));
         if (perSM < 1) perSM = 1;
         unsigned packets = (n + WQ_P - 1) / WQ_P;
         unsigned blocks = (unsigned)(ctx->sm_count * perSM);
         unsigned need = (packets + WQ_WARPS - 1) / WQ_WARPS;
         if (blocks > need) blocks = need;
-        k_query_warp<MODE, COUNT><<<blocks, WQ_WARPS * 32, 0, ctx->stream>>>(
-            tree_view(ctx), ctx->medium, n, ro, rd, nPathsNorm, out, tau, span, ctx->tau_steps,
-            hitCounts, hitOffsets, hitIdx, counters, (unsigned int *)ctx->packet_ctr.p);
+        k_traverse<MODE, COUNT><<<blocks, WQ_WARPS * 32, 0, ctx->stream>>>(
+            A, n, (uint2 *)ctx->pair_queue.p, cap, ctl, counters);
+    }
+    {
+        PhaseTimer pt(ctx, PH_QUERY_B);
+        k_leaf_pairs<MODE, COUNT><<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(
+            A, (const uint2 *)ctx->pair_queue.p, cap, ctl, counters);
     }
     BRE_CUDA(cudaGetLastError());
     return BRE_OK;
@@ -411,6 +330,13 @@ int run_count(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd) {
     ctx->counters.bytes_algorithmic = 48ull * n + 32ull * h[0] + 16ull * h[1] + 32ull * h[2];
     ctx->counters.fast_nodes = h[3];
     ctx->counters.fast_disk_tests = h[4];
+    unsigned int ctl[4] = {0, 0, 0, 0};
+    if (n > 0) {
+        BRE_CUDA(cudaMemcpyAsync(ctl, ctx->packet_ctr.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+        BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    ctx->counters.leaf_pairs = ctl[0];
+    ctx->counters.pair_queue_overflow = ctl[2];
     return BRE_OK;
 }
 

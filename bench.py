@@ -245,14 +245,14 @@ def run_ours(args):
     sampler.start()
     # kernel-only timings: collect K5 duration of every timed step via the library's own events
     barrier()
-    k5, ktau, kbuild, ktrace, kfilm = [], [], [], [], []
+    k5, ktau, kbuild, ktrace, kfilm, k5a, k5b = [], [], [], [], [], [], []
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     t0 = time.perf_counter()
     for _ in range(args.steps):
         step_device()
         t = ctx.timings()
-        k5.append(t["query"]); ktau.append(t["tau"]); kbuild.append(t["build"]); ktrace.append(t["trace"]); kfilm.append(t["film"])
+        k5.append(t["query"]); ktau.append(t["tau"]); kbuild.append(t["build"]); ktrace.append(t["trace"]); kfilm.append(t["film"]); k5a.append(t["query_a"]); k5b.append(t["query_b"])
     e1.record(stream)
     barrier()
     ms_total = max(e0.elapsed_time(e1), 0.0)
@@ -304,12 +304,15 @@ def run_ours(args):
                    "mean_hits_per_ray": cnt["hits"] / nq, "mean_V": cnt["nodes_visited"] / nq,
                    "mean_T": cnt["disk_tests"] / nq, "mdisk_tests_per_s": cnt["disk_tests"] / (k5_ms * 1e-3) / 1e6,
                    "phase_ms": {"trace": float(np.mean(ktrace)), "build": float(np.mean(kbuild)),
-                                "tau": float(np.mean(ktau)), "query": k5_ms, "film": float(np.mean(kfilm))}},
+                                "tau": float(np.mean(ktau)), "query": k5_ms, "query_k5a_traverse": float(np.mean(k5a)),
+                                "query_k5b_leaf_pairs": float(np.mean(k5b)), "film": float(np.mean(kfilm))},
+                   "fast_nodes_per_ray": cnt["fast_nodes"] / nq, "fast_disk_tests_per_ray": cnt["fast_disk_tests"] / nq,
+                   "leaf_pairs_per_ray": cnt["leaf_pairs"] / nq, "pair_queue_overflow": cnt["pair_queue_overflow"]},
         "e2e": {"value": e2e_value, "unit": "queries/s", "h2d_bytes_per_step": int(nq * 28),
                 "d2h_bytes_per_step": int(nq * 12), "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches_per_step(world) * args.steps,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": traffic, "kernel": "k_query<0,false>",
+                     "frac": achieved / peak, "traffic": traffic, "kernel": "K5 = k_traverse<0,false> + k_leaf_pairs<0,false>",
                      "kernel_ms": k5_ms, "algorithmic_bytes": int(cnt["bytes_algorithmic"]),
                      "own_structure_bytes": int(fast_bytes), "own_structure_gbs": fast_bytes / (k5_ms * 1e-3) / 1e9,
                      "peak_source": peak_src},

@@ -66,6 +66,8 @@ typedef struct {
     uint64_t bytes_algorithmic;/* sum over rays of 32 + 32 V + 16 T + 32 H + 16 */
     uint64_t fast_nodes;       /* 64-byte two-child nodes fetched by the production kernel */
     uint64_t fast_disk_tests;  /* disk tests done by the production kernel (leaf size > 1) */
+    uint64_t leaf_pairs;       /* (ray, leaf) pairs the traversal kernel produced */
+    uint64_t pair_queue_overflow; /* pairs shaded in place because the pair queue was full */
 } bre_counters;
 
 typedef struct {
@@ -176,8 +178,8 @@ int bre_film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out);
 /* ---- device timing ------------------------------------------------------------------
  * With timing enabled every phase is bracketed by CUDA events on the context stream.
  * bre_get_timings synchronises and returns the LAST duration of each phase in milliseconds:
- * ms[0]=K1 trace, ms[1]=K2-K4 build, ms[2]=K6 optical-depth table, ms[3]=K5 beam query kernel,
- * ms[4]=K7 film accumulate, ms[5..7] reserved (0). */
+ * ms[0]=K1 trace, ms[1]=K2-K4 build, ms[2]=K6 optical-depth table, ms[3]=K5 beam query (K5a+K5b),
+ * ms[4]=K7 film accumulate, ms[5]=K5a traversal kernel, ms[6]=K5b leaf-pair kernel, ms[7]=0. */
 int bre_set_timing(bre_ctx *ctx, int enabled);
 int bre_get_timings(bre_ctx *ctx, float ms[8]);
 

@@ -243,11 +243,12 @@ def test_trace_photons_statistical(oracle, ctx):
     assert np.array_equal(pos2, pos) and np.array_equal(pw2, pw) and np.array_equal(dr2, dr)
 
 
-@pytest.mark.parametrize("kernel", ["thread", "warp"])
-def test_both_traversal_kernels(oracle, bre, monkeypatch, kernel):
-    """The thread-per-ray kernel (kept for A/B measurement) and the production warp-cooperative
-    kernel return the same hit sets."""
-    monkeypatch.setenv("BRE_QUERY_KERNEL", kernel)
+@pytest.mark.parametrize("cap", [0, 1000])
+def test_pair_queue_overflow_path(oracle, bre, monkeypatch, cap):
+    """K5a hands (ray, leaf) pairs to K5b through a queue; with a queue that is far too small
+    (cap=1000 pairs) the overflow pairs are shaded in place -- results must not change."""
+    if cap:
+        monkeypatch.setenv("BRE_PAIR_QUEUE_CAP", str(cap))
     c = bre.Bre(device=0)
     try:
         n = 40000
@@ -257,6 +258,8 @@ def test_both_traversal_kernels(oracle, bre, monkeypatch, kernel):
         rgb, offs, idx = c.query(ro, rd, float(n), want_hits=True)
         assert np.array_equal(offs, ref_offs) and np.array_equal(idx, ref_idx)
         assert_radiance(rgb, ref_rgb)
+        cnt = c.count(ro, rd)
+        assert (cnt["pair_queue_overflow"] > 0) == bool(cap)
     finally:
         c.close()
 
