@@ -172,6 +172,7 @@ int bre_set_medium_homogeneous(bre_ctx *ctx, const float sa[3], const float ss[3
     m.kind = 0;
     for (int k = 0; k < 3; ++k) { m.sigma_a[k] = sa[k]; m.sigma_s[k] = ss[k]; m.sigma_t[k] = sa[k] + ss[k]; }
     m.g = g;
+    m.gray = (m.sigma_t[0] == m.sigma_t[1] && m.sigma_t[1] == m.sigma_t[2]) ? 1 : 0;
     ctx->have_medium = true;
     return BRE_OK;
 }

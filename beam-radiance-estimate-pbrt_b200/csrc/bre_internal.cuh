@@ -46,6 +46,7 @@ struct MediumDev {
     int kind;                 // 0 homogeneous, 1 grid
     float sigma_a[3], sigma_s[3], sigma_t[3];
     float g;
+    int gray;                 // sigma_t equal in all three channels
     int nx, ny, nz;
     const float *density;     // device
     float invMaxDensity;

@@ -189,8 +189,8 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
                         float4 *out, const float *tau, const float2 *span, uint32_t *hitCounts,
                         const uint64_t *hitOffsets, uint32_t *hitIdx, unsigned long long *counters) {
     int s;
-    // pair queue: 48 pairs per ray (mean is ~25 at 8 photons/leaf), at least 1M, at most 256M pairs
-    uint64_t want = (uint64_t)n * 48u;
+    // pair queue: room for 128 pairs per ray (measured means: 25-50), at least 1M, at most 256M pairs
+    uint64_t want = (uint64_t)n * 128u;
     if (want < (1u << 20)) want = 1u << 20;
     if (want > (1u << 28)) want = 1u << 28;
     if (ctx->pair_queue_cap_override) want = ctx->pair_queue_cap_override;
@@ -220,8 +220,16 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     }
     {
         PhaseTimer pt(ctx, PH_QUERY_B);
-        k_leaf_pairs<MODE, COUNT><<<ctx->sm_count * 8, 256, 0, ctx->stream>>>(
-            A, (const uint2 *)ctx->pair_queue.p, cap, ctl, counters);
+        const unsigned gb = (unsigned)ctx->sm_count * 8u;
+        if (ctx->max_leaf <= 4)
+            k_leaf_pairs<MODE, COUNT, 4><<<gb, LP_WARPS * 32, 0, ctx->stream>>>(
+                A, (const uint2 *)ctx->pair_queue.p, cap, ctl, counters);
+        else if (ctx->max_leaf <= 8)
+            k_leaf_pairs<MODE, COUNT, 8><<<gb, LP_WARPS * 32, 0, ctx->stream>>>(
+                A, (const uint2 *)ctx->pair_queue.p, cap, ctl, counters);
+        else
+            k_leaf_pairs<MODE, COUNT, 16><<<gb, LP_WARPS * 32, 0, ctx->stream>>>(
+                A, (const uint2 *)ctx->pair_queue.p, cap, ctl, counters);
     }
     BRE_CUDA(cudaGetLastError());
     return BRE_OK;
@@ -335,7 +343,7 @@ int run_count(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd) {
         BRE_CUDA(cudaMemcpyAsync(ctl, ctx->packet_ctr.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
         BRE_CUDA(cudaStreamSynchronize(ctx->stream));
     }
-    ctx->counters.leaf_pairs = ctl[0];
+    ctx->counters.leaf_pairs = ctl[3];
     ctx->counters.pair_queue_overflow = ctl[2];
     return BRE_OK;
 }
@@ -369,7 +377,7 @@ int run_hitdump(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, br
     if ((s = ensure(ctx, ctx->hit_idx, (size_t)hd->total * 4)) != BRE_OK) return s;
     BRE_CUDA(cudaMemcpyAsync(ctx->hit_offsets.p, offs.data(), ((size_t)n + 1) * 8,
                              cudaMemcpyHostToDevice, ctx->stream));
-    if ((s = launch_query<2, false>(ctx, n, ro, rd, 1.f, nullptr, nullptr, nullptr, nullptr,
+    if ((s = launch_query<2, false>(ctx, n, ro, rd, 1.f, nullptr, nullptr, nullptr, (uint32_t *)ctx->hit_counts.p,
                                     (const uint64_t *)ctx->hit_offsets.p, (uint32_t *)ctx->hit_idx.p,
                                     nullptr)) != BRE_OK) return s;
     BRE_CUDA(cudaMemcpyAsync(hd->indices, ctx->hit_idx.p, (size_t)hd->total * 4,
