@@ -286,10 +286,10 @@ class Bre:
 def shard_range(n, n_ranks, rank, lib=None):
     lib = lib or load_library()
     f, c = C.c_uint64(), C.c_uint64()
-    lib.bre_shard_range(C.c_uint64(n), n_ranks, rank, C.byref(f), C.byref(c))
+    lib.bre_shard_range(C.c_uint64(int(n)), int(n_ranks), int(rank), C.byref(f), C.byref(c))
     return f.value, c.value
 
 
 def tile_owner(tx, ty, tiles_x, n_ranks, lib=None):
     lib = lib or load_library()
-    return lib.bre_tile_owner(tx, ty, tiles_x, n_ranks)
+    return lib.bre_tile_owner(C.c_uint32(int(tx)), C.c_uint32(int(ty)), C.c_uint32(int(tiles_x)), int(n_ranks))

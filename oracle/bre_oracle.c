@@ -391,10 +391,8 @@ typedef struct {
     float oNear[3], oFar[3], invDir[3], tMax;
     int neg[3];
 } ray_slab;
-static void ray_slab_init(ray_slab *rs, const float o[3], const float d[3], float tMax,
-                          float abs_max) {
-    float M = fmaxf_(fmaxf_(fabsf(o[0]), fabsf(o[1])), fabsf(o[2])) + abs_max;
-    float pad = M * 0x1p-18f;
+static void ray_slab_init_pad(ray_slab *rs, const float o[3], const float d[3], float tMax,
+                              float pad) {
     for (int k = 0; k < 3; ++k) {
         rs->invDir[k] = 1 / d[k];
         rs->neg[k] = rs->invDir[k] < 0;
@@ -403,6 +401,11 @@ static void ray_slab_init(ray_slab *rs, const float o[3], const float d[3], floa
         rs->oFar[k] = o[k] - sp;
     }
     rs->tMax = tMax;
+}
+static void ray_slab_init(ray_slab *rs, const float o[3], const float d[3], float tMax,
+                          float abs_max) {
+    float M = fmaxf_(fmaxf_(fabsf(o[0]), fabsf(o[1])), fabsf(o[2])) + abs_max;
+    ray_slab_init_pad(rs, o, d, tMax, M * 0x1p-18f);
 }
 static inline int slab_hit(const ray_slab *rs, const float lo[3], const float hi[3]) {
     const float g3 = 1 + 2 * orc_gamma(3);
@@ -422,6 +425,13 @@ static inline int slab_hit(const ray_slab *rs, const float lo[3], const float hi
     if (tzMin > tMin) tMin = tzMin;
     if (tzMax < tMax) tMax = tzMax;
     return (tMin < rs->tMax) && (tMax > 0);
+}
+
+int orc_slab_test(const float o[3], const float d[3], float tMax, const float lo[3],
+                  const float hi[3], float pad) {
+    ray_slab rs;
+    ray_slab_init_pad(&rs, o, d, tMax, pad);
+    return slab_hit(&rs, lo, hi);
 }
 
 uint32_t orc_query_ray(const orc_lbvh *t, const orc_photons *ph, const orc_medium *m,

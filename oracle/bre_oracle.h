@@ -109,6 +109,11 @@ typedef struct {
 int orc_disk_test(const float o[3], const float d[3], float tMax, const float p[3], float r,
                   float *t_out, float *d2_out);
 
+/* The traversal's slab test: Bounds3::IntersectP(ray, invDir, dirIsNeg), core/geometry.h:1410-1438,
+ * with the ray origin padded by `pad` (conservative cull).  pad = 0 is exactly the reference test. */
+int orc_slab_test(const float o[3], const float d[3], float tMax, const float lo[3],
+                  const float hi[3], float pad);
+
 /* One ray against the canonical LBVH (collect-all traversal, core/photonbeambvh.cpp:685-723,
  * slab test core/geometry.h:1410-1438).  hits (optional) receives ORIGINAL photon indices
  * in traversal order, at most hits_cap; returns the number of hits. */

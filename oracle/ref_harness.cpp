@@ -1,0 +1,600 @@
+// oracle/ref_harness.cpp -- TEST INFRASTRUCTURE ONLY.
+//
+// Links against the UNMODIFIED reference sources compiled by oracle/Makefile (`make ref`) and
+// produces the golden data that pins the CPU oracle (oracle/bre_oracle.c) to the reference:
+//
+//   ref_harness primitives <out.json>
+//        known-answer vectors computed BY REFERENCE CODE for every primitive the hot path is
+//        made of: PCG32 (core/rng.h), sphere/cone sampling (core/sampling.cpp), PhaseHG and
+//        HenyeyGreenstein::p/Sample_p (core/medium.{h,cpp}), HomogeneousMedium::Tr,
+//        GridDensityMedium::Density and ::Tr (media/*.cpp), Bounds3::IntersectP (core/geometry.h),
+//        EncodeMorton3 / RadixSort (core/photonbeambvh.cpp), kernel() (integrators/photonmap.cpp),
+//        Film::SetImage + Film::WriteImage (core/film.cpp).
+//   ref_harness fogbox <out.bin> <nVolumePhotons> <res> <radius> [keepFirst]
+//        builds the fog-box scene of SURVEY.md Appendix A with reference classes, runs the
+//        reference's own PhotonIntegrator::ShootPhotons, generates camera rays with the reference's
+//        PerspectiveCamera + Scene::Intersect, and evaluates the beam radiance estimate over the
+//        dumped photons by BRUTE FORCE with reference vector/phase/medium/kernel code.
+//        out.bin = photons, rays, per-ray hit lists and radiance (format: write_fogbox below).
+//   ref_harness trace <out.bin> <homogeneous|grid> <firstPath> <nPaths> <maxDepth>
+//        the volume-photon deposit loop (integrators/photonmap.cpp:696-724) driven with the
+//        sampler stream of integrators/photonbeam.cpp:386-391 inside an absorbing triangle box,
+//        every step executed by reference classes (Light::Sample_Le, Scene::Intersect,
+//        Medium::Sample, HenyeyGreenstein::Sample_p, MediumInteraction::SpawnRay).
+//
+// All floats are written as raw IEEE-754 bit patterns so the comparison can be bit-exact.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "pbrt.h"
+#include "accelerators/bvh.h"
+#include "cameras/perspective.h"
+#include "film.h"
+#include "filters/box.h"
+#include "geometry.h"
+#include "integrator.h"
+#include "lights/point.h"
+#include "lights/spot.h"
+#include "materials/matte.h"
+#include "media/grid.h"
+#include "media/homogeneous.h"
+#include "medium.h"
+#include "paramset.h"
+#include "memory.h"
+#include "parallel.h"
+#include "rng.h"
+#include "sampler.h"
+#include "sampling.h"
+#include "scene.h"
+#include "shapes/triangle.h"
+#include "spectrum.h"
+#include "textures/constant.h"
+#include "transform.h"
+
+#include "ref_access.h"
+
+using namespace pbrt;
+
+namespace {
+
+uint32_t fbits(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+
+// ---------------------------------------------------------------- tiny JSON writer
+struct Json {
+    FILE *fp;
+    bool firstSection = true;
+    explicit Json(const char *path) : fp(fopen(path, "w")) {
+        if (!fp) { perror(path); exit(1); }
+        fprintf(fp, "{\n");
+    }
+    ~Json() { fprintf(fp, "\n}\n"); fclose(fp); }
+    bool firstKey = true;
+    void begin(const char *name) {
+        fprintf(fp, "%s \"%s\": {", firstSection ? "" : ",\n", name);
+        firstSection = false; firstKey = true;
+    }
+    void end() { fprintf(fp, "}"); }
+    void key(const std::string &k) { fprintf(fp, "%s\n  \"%s\": ", firstKey ? "" : ",", k.c_str()); firstKey = false; }
+    // float arrays are stored as bit patterns under "f:<name>"
+    void floats(const char *name, const std::vector<float> &v) {
+        key(std::string("f:") + name);
+        fputc('[', fp);
+        for (size_t i = 0; i < v.size(); ++i) fprintf(fp, "%s%u", i ? "," : "", fbits(v[i]));
+        fputc(']', fp);
+    }
+    void ints(const char *name, const std::vector<int64_t> &v) {
+        key(std::string("i:") + name);
+        fputc('[', fp);
+        for (size_t i = 0; i < v.size(); ++i) fprintf(fp, "%s%lld", i ? "," : "", (long long)v[i]);
+        fputc(']', fp);
+    }
+};
+
+// A Sampler whose every value is RNG(seq).UniformFloat(): what AwesomeHaltonSampler
+// (integrators/photonbeam.cpp:188-256) degenerates to after its 1000 Halton dimensions have been
+// burnt (photonbeam.cpp:390-391).
+class StreamSampler : public Sampler {
+  public:
+    explicit StreamSampler(uint64_t seq) : Sampler(1), rng(seq) {}
+    Float Get1D() override { return rng.UniformFloat(); }
+    Point2f Get2D() override {
+        Float a = rng.UniformFloat();
+        Float b = rng.UniformFloat();
+        return Point2f(a, b);
+    }
+    std::unique_ptr<Sampler> Clone(int) override { return nullptr; }
+    RNG rng;
+};
+
+void push3(std::vector<float> &v, const Vector3f &a) { v.push_back(a.x); v.push_back(a.y); v.push_back(a.z); }
+void push3(std::vector<float> &v, const Point3f &a) { v.push_back(a.x); v.push_back(a.y); v.push_back(a.z); }
+void pushS(std::vector<float> &v, const Spectrum &s) {
+    Float rgb[3];
+    s.ToRGB(rgb);
+    v.push_back(rgb[0]); v.push_back(rgb[1]); v.push_back(rgb[2]);
+}
+Spectrum rgbS(float r, float g, float b) {
+    Float c[3] = {r, g, b};
+    return Spectrum::FromRGB(c);
+}
+Vector3f unit_from(RNG &r) { return UniformSampleSphere(Point2f(r.UniformFloat(), r.UniformFloat())); }
+
+// ---------------------------------------------------------------- scenes
+// 5x4x3 test grid used by the density / Tr vectors and by `trace grid`
+std::vector<float> test_grid(int nx, int ny, int nz, uint64_t seq) {
+    RNG r(seq);
+    std::vector<float> d((size_t)nx * ny * nz);
+    for (float &x : d) x = r.UniformFloat();
+    return d;
+}
+
+const float kBoxLo[3] = {-4.f, -1.f, -4.f}, kBoxHi[3] = {4.f, 2.f, 4.f};
+
+// Six quads (12 triangles) of the box [kBoxLo, kBoxHi]  (SURVEY.md Appendix A).
+std::vector<std::shared_ptr<Primitive>> box_prims(const std::shared_ptr<Material> &mat,
+                                                  const MediumInterface &mi) {
+    static Transform id;
+    const float *L = kBoxLo, *H = kBoxHi;
+    const Point3f quads[6][4] = {
+        {{L[0], L[1], L[2]}, {H[0], L[1], L[2]}, {H[0], L[1], H[2]}, {L[0], L[1], H[2]}},   // floor
+        {{L[0], H[1], L[2]}, {L[0], H[1], H[2]}, {H[0], H[1], H[2]}, {H[0], H[1], L[2]}},   // ceiling
+        {{L[0], L[1], H[2]}, {H[0], L[1], H[2]}, {H[0], H[1], H[2]}, {L[0], H[1], H[2]}},   // back
+        {{L[0], L[1], L[2]}, {L[0], H[1], L[2]}, {H[0], H[1], L[2]}, {H[0], L[1], L[2]}},   // front
+        {{L[0], L[1], L[2]}, {L[0], L[1], H[2]}, {L[0], H[1], H[2]}, {L[0], H[1], L[2]}},   // left
+        {{H[0], L[1], L[2]}, {H[0], H[1], L[2]}, {H[0], H[1], H[2]}, {H[0], L[1], H[2]}}};  // right
+    const int idx[6] = {0, 1, 2, 0, 2, 3};
+    std::vector<std::shared_ptr<Primitive>> prims;
+    for (int q = 0; q < 6; ++q) {
+        auto tris = CreateTriangleMesh(&id, &id, false, 2, idx, 4, quads[q], nullptr, nullptr,
+                                       nullptr, nullptr, nullptr);
+        for (auto &t : tris) prims.push_back(std::make_shared<GeometricPrimitive>(t, mat, nullptr, mi));
+    }
+    return prims;
+}
+
+std::shared_ptr<Material> matte(float kd) {
+    std::shared_ptr<Texture<Spectrum>> Kd = std::make_shared<ConstantTexture<Spectrum>>(Spectrum(kd));
+    std::shared_ptr<Texture<Float>> sigma = std::make_shared<ConstantTexture<Float>>(0.f);
+    return std::make_shared<MatteMaterial>(Kd, sigma, nullptr);
+}
+
+// ---------------------------------------------------------------- mode: primitives
+void primitives(const char *path) {
+    Json js(path);
+    {   // core/rng.h:60-145
+        js.begin("rng");
+        const uint64_t seqs[] = {0, 1, 2, 12345, (1ull << 40) + 7};
+        std::vector<int64_t> s, u;
+        std::vector<float> f;
+        for (uint64_t q : seqs) {
+            RNG r(q);
+            s.push_back((int64_t)q);
+            for (int i = 0; i < 6; ++i) u.push_back(r.UniformUInt32());
+            for (int i = 0; i < 6; ++i) f.push_back(r.UniformFloat());
+        }
+        js.ints("seq", s); js.ints("u32", u); js.floats("float", f);
+        js.end();
+    }
+    {   // core/sampling.cpp:98-103,136-142
+        js.begin("sampling");
+        RNG r(7);
+        std::vector<float> u, sph, cone;
+        for (int i = 0; i < 64; ++i) {
+            Point2f p(r.UniformFloat(), r.UniformFloat());
+            u.push_back(p.x); u.push_back(p.y);
+            push3(sph, UniformSampleSphere(p));
+            push3(cone, UniformSampleCone(p, 0.8f));
+        }
+        js.floats("u", u); js.floats("sphere", sph); js.floats("cone", cone);
+        js.floats("cosThetaMax", {0.8f});
+        js.end();
+    }
+    {   // core/medium.h:66-69, core/medium.cpp:186-210
+        js.begin("phase");
+        const float gs[] = {-0.7f, 0.f, 0.0005f, 0.3f, 0.9f};
+        std::vector<float> g, c, v, wo, wi, pv, su, swo, swi, sret;
+        RNG r(11);
+        for (float gg : gs)
+            for (int i = 0; i <= 20; ++i) {
+                float ct = -1.f + 0.1f * i;
+                g.push_back(gg); c.push_back(ct); v.push_back(PhaseHG(ct, gg));
+                HenyeyGreenstein hg(gg);
+                Vector3f a = unit_from(r), b = unit_from(r);
+                push3(wo, a); push3(wi, b); pv.push_back(hg.p(a, b));
+                Point2f uu(r.UniformFloat(), r.UniformFloat());
+                Vector3f o2 = unit_from(r), w2;
+                float ret = hg.Sample_p(o2, &w2, uu);
+                su.push_back(uu.x); su.push_back(uu.y);
+                push3(swo, o2); push3(swi, w2); sret.push_back(ret);
+            }
+        js.floats("g", g); js.floats("cosTheta", c); js.floats("PhaseHG", v);
+        js.floats("p_wo", wo); js.floats("p_wi", wi); js.floats("p", pv);
+        js.floats("s_u", su); js.floats("s_wo", swo); js.floats("s_wi", swi); js.floats("s_ret", sret);
+        js.end();
+    }
+    {   // media/homogeneous.cpp:44-48
+        js.begin("homogeneous_tr");
+        const float sa[3] = {0.05f, 0.1f, 0.2f}, ss[3] = {0.4f, 0.4f, 0.5f};
+        HomogeneousMedium med(rgbS(sa[0], sa[1], sa[2]), rgbS(ss[0], ss[1], ss[2]), 0.3f);
+        StreamSampler smp(1);
+        std::vector<float> t, tr;
+        RNG r(13);
+        for (int i = 0; i < 64; ++i) {
+            float tt = 12.f * r.UniformFloat() * r.UniformFloat();
+            Ray ray(Point3f(0.1f, 0.2f, 0.3f), unit_from(r), tt);
+            t.push_back(tt * ray.d.Length());
+            pushS(tr, med.Tr(ray, smp));
+        }
+        js.floats("sigma_a", {sa[0], sa[1], sa[2]}); js.floats("sigma_s", {ss[0], ss[1], ss[2]});
+        js.floats("t", t); js.floats("Tr", tr);
+        js.end();
+    }
+    {   // media/grid.cpp:45-60 (Density), :89-121 (Tr, stochastic -> mean and standard error)
+        js.begin("grid");
+        const int nx = 5, ny = 4, nz = 3;
+        std::vector<float> d = test_grid(nx, ny, nz, 17);
+        Transform m2w = Translate(Vector3f(-1.f, 0.5f, 2.f)) * Scale(2.f, 1.5f, 3.f);
+        Transform w2m = Inverse(m2w);
+        GridDensityMedium med(Spectrum(0.5f), Spectrum(1.5f), 0.3f, nx, ny, nz, m2w, d.data());
+        std::vector<float> w2mf;
+        for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) w2mf.push_back(w2m.GetMatrix().m[i][j]);
+        std::vector<float> p, dens;
+        RNG r(19);
+        for (int i = 0; i < 256; ++i) {
+            Point3f q(-0.2f + 1.4f * r.UniformFloat(), -0.2f + 1.4f * r.UniformFloat(),
+                      -0.2f + 1.4f * r.UniformFloat());
+            push3(p, q); dens.push_back(med.Density(q));
+        }
+        std::vector<float> ro, rd, rt, trMean, trErr;
+        for (int i = 0; i < 8; ++i) {
+            Point3f o(-1.5f + 0.1f * i, 0.4f + 0.2f * i, 1.5f);
+            Vector3f dir = Normalize(Vector3f(0.9f - 0.1f * i, 0.15f, 1.f));
+            float tMax = 1.f + 0.6f * i;
+            double sum = 0, sum2 = 0;
+            const int N = 40000;
+            for (int k = 0; k < N; ++k) {
+                StreamSampler smp(100000ull * (i + 1) + k);
+                Float v = med.Tr(Ray(o, dir, tMax), smp)[0];
+                sum += v; sum2 += (double)v * v;
+            }
+            double mean = sum / N, var = sum2 / N - mean * mean;
+            push3(ro, o); push3(rd, dir); rt.push_back(tMax);
+            trMean.push_back((float)mean); trErr.push_back((float)std::sqrt(var / N));
+        }
+        js.ints("dims", {nx, ny, nz}); js.floats("density", d); js.floats("w2m", w2mf);
+        js.floats("sigma_a", {0.5f}); js.floats("sigma_s", {1.5f});
+        js.floats("p", p); js.floats("Density", dens);
+        js.floats("ray_o", ro); js.floats("ray_d", rd); js.floats("ray_tMax", rt);
+        js.floats("Tr_mean", trMean); js.floats("Tr_stderr", trErr);
+        js.end();
+    }
+    {   // core/geometry.h:1386-1408 and :1410-1438
+        js.begin("bounds");
+        RNG r(23);
+        std::vector<float> lo, hi, o, d, tm, t0s, t1s;
+        std::vector<int64_t> hitP, hitSlab;
+        for (int i = 0; i < 2000; ++i) {
+            Point3f a(r.UniformFloat(), r.UniformFloat(), r.UniformFloat());
+            float sz = (i % 4 == 0) ? 0.5f : 0.02f;
+            Point3f b = a + sz * Vector3f(r.UniformFloat(), r.UniformFloat(), r.UniformFloat());
+            Bounds3f box(a, b);
+            Point3f org(2.f * r.UniformFloat() - 0.5f, 2.f * r.UniformFloat() - 0.5f, -1.5f * r.UniformFloat());
+            // aim near the box so that a useful fraction of the tests are close calls
+            Point3f target = a + Vector3f(r.UniformFloat() * 1.4f - 0.2f, r.UniformFloat() * 1.4f - 0.2f,
+                                          r.UniformFloat() * 1.4f - 0.2f) * sz;
+            Vector3f dir = Normalize(target - org);
+            if (i % 7 == 0) dir.y = 0.f, dir = Normalize(dir);   // axis-parallel component (1/0 = inf)
+            float tMax = (i % 3 == 0) ? (target - org).Length() * (0.5f + r.UniformFloat()) : Infinity;
+            Ray ray(org, dir, tMax);
+            Float t0 = 0, t1 = 0;
+            bool h = box.IntersectP(ray, &t0, &t1);
+            Vector3f invDir(1 / dir.x, 1 / dir.y, 1 / dir.z);
+            int neg[3] = {invDir.x < 0, invDir.y < 0, invDir.z < 0};
+            bool hs = box.IntersectP(ray, invDir, neg);
+            push3(lo, box.pMin); push3(hi, box.pMax); push3(o, org); push3(d, dir); tm.push_back(tMax);
+            hitP.push_back(h); t0s.push_back(h ? t0 : 0.f); t1s.push_back(h ? t1 : 0.f);
+            hitSlab.push_back(hs);
+        }
+        js.floats("lo", lo); js.floats("hi", hi); js.floats("o", o); js.floats("d", d); js.floats("tMax", tm);
+        js.ints("IntersectP", hitP); js.floats("t0", t0s); js.floats("t1", t1s);
+        js.ints("IntersectP_invDir", hitSlab);
+        js.end();
+    }
+    {   // core/photonbeambvh.cpp:109-139, :141-182, :438-445
+        js.begin("morton");
+        RNG r(29);
+        const float lo[3] = {-0.3f, 0.1f, 2.f}, hi[3] = {1.7f, 0.9f, 2.5f};
+        std::vector<float> p;
+        std::vector<int64_t> code;
+        for (int i = 0; i < 512; ++i) {
+            float q[3];
+            for (int k = 0; k < 3; ++k) q[k] = lo[k] + (hi[k] - lo[k]) * r.UniformFloat();
+            if (i < 3) q[i] = hi[i];           // offset exactly 1 -> 1024 -> clamped to 1023
+            if (i == 3) { q[0] = lo[0]; q[1] = lo[1]; q[2] = lo[2]; }
+            p.push_back(q[0]); p.push_back(q[1]); p.push_back(q[2]);
+            code.push_back(refx::morton_of_point(q, lo, hi));
+        }
+        // radix sort of codes with many duplicates: the reference sort is stable
+        std::vector<int> prim(4096);
+        std::vector<uint32_t> codes(4096);
+        std::vector<int64_t> inCodes, outPrim;
+        for (int i = 0; i < 4096; ++i) { prim[i] = i; codes[i] = r.UniformUInt32(1u << 30) & 0x3ff003ffu; inCodes.push_back(codes[i]); }
+        refx::radix_sort(4096, prim.data(), codes.data());
+        for (int i = 0; i < 4096; ++i) outPrim.push_back(prim[i]);
+        js.floats("lo", {lo[0], lo[1], lo[2]}); js.floats("hi", {hi[0], hi[1], hi[2]});
+        js.floats("p", p); js.ints("code", code);
+        js.ints("sort_in_codes", inCodes); js.ints("sort_out_prim", outPrim);
+        js.end();
+    }
+    {   // integrators/photonmap.cpp:170-174
+        js.begin("kernel");
+        RNG r(31);
+        std::vector<float> a, b, md2, k;
+        for (int i = 0; i < 64; ++i) {
+            float pa[3] = {r.UniformFloat(), r.UniformFloat(), r.UniformFloat()};
+            float rad = 0.05f + 0.1f * r.UniformFloat();
+            float pb[3] = {pa[0] + rad * 0.5f * r.UniformFloat(), pa[1] - rad * 0.5f * r.UniformFloat(), pa[2]};
+            for (int c = 0; c < 3; ++c) { a.push_back(pa[c]); b.push_back(pb[c]); }
+            md2.push_back(rad * rad);
+            k.push_back(refx::kernel(pa, pb, rad * rad));
+        }
+        js.floats("photon_p", a); js.floats("p", b); js.floats("maxDist2", md2); js.floats("kernel", k);
+        js.end();
+    }
+    {   // core/film.cpp:132-140 (SetImage), :168-204 (WriteImage), via the PFM writer of ref_glue.cpp
+        js.begin("film");
+        const int W = 8, H = 4;
+        const char *tmp = "/tmp/bre_ref_film.pfm";
+        Film film(Point2i(W, H), Bounds2f(Point2f(0, 0), Point2f(1, 1)),
+                  std::unique_ptr<Filter>(new BoxFilter(Vector2f(0.5f, 0.5f))), 35.f, tmp, 1.5f);
+        RNG r(37);
+        std::vector<Spectrum> img(W * H);
+        std::vector<float> in;
+        for (int i = 0; i < W * H; ++i) {
+            float c[3] = {4.f * r.UniformFloat(), 4.f * r.UniformFloat(), 4.f * r.UniformFloat()};
+            if (i == 5) c[0] = -0.25f;     // negative radiance is clamped by WriteImage
+            if (i == 6) c[1] = 0.f;
+            img[i] = rgbS(c[0], c[1], c[2]);
+            in.push_back(c[0]); in.push_back(c[1]); in.push_back(c[2]);
+        }
+        film.SetImage(img.data());
+        film.WriteImage();
+        // read the PFM back (bottom-to-top scanlines)
+        std::ifstream f(tmp, std::ios::binary);
+        std::string magic; int w, h; float sc;
+        f >> magic >> w >> h >> sc; f.get();
+        std::vector<float> raw((size_t)w * h * 3), out((size_t)w * h * 3);
+        f.read((char *)raw.data(), raw.size() * 4);
+        for (int y = 0; y < h; ++y)
+            memcpy(&out[(size_t)y * w * 3], &raw[(size_t)(h - 1 - y) * w * 3], (size_t)w * 12);
+        js.ints("dims", {W, H}); js.floats("scale", {1.5f});
+        js.floats("rgb_in", in); js.floats("rgb_out", out);
+        js.end();
+        remove(tmp);
+    }
+}
+
+// ---------------------------------------------------------------- binary container
+// "BREF1\n" then records: name[24] (zero padded), dtype[8] ("f4","u4","u8","i4"), count u64, data.
+struct BinWriter {
+    FILE *fp;
+    explicit BinWriter(const char *path) : fp(fopen(path, "wb")) {
+        if (!fp) { perror(path); exit(1); }
+        fwrite("BREF1\n", 1, 6, fp);
+    }
+    ~BinWriter() { fclose(fp); }
+    void add(const char *name, const char *dtype, const void *data, uint64_t count, size_t elem) {
+        char n[24] = {0}, t[8] = {0};
+        strncpy(n, name, 23); strncpy(t, dtype, 7);
+        fwrite(n, 1, 24, fp); fwrite(t, 1, 8, fp); fwrite(&count, 8, 1, fp);
+        if (count) fwrite(data, elem, count, fp);
+    }
+    void f4(const char *name, const std::vector<float> &v) { add(name, "f4", v.data(), v.size(), 4); }
+    void u4(const char *name, const std::vector<uint32_t> &v) { add(name, "u4", v.data(), v.size(), 4); }
+    void u8(const char *name, const std::vector<uint64_t> &v) { add(name, "u8", v.data(), v.size(), 8); }
+};
+
+// ---------------------------------------------------------------- mode: fogbox
+void fogbox(const char *path, int nVolumeWanted, int res, float radius, uint32_t keep) {
+    const float sa = 0.05f, ss = 0.4f, g = 0.3f;
+    HomogeneousMedium fog{Spectrum(sa), Spectrum(ss), g};
+    MediumInterface inFog(&fog, &fog);
+    std::vector<std::shared_ptr<Primitive>> prims = box_prims(matte(0.6f), inFog);
+    std::shared_ptr<BVHAccel> bvh = std::make_shared<BVHAccel>(prims);
+    std::vector<std::shared_ptr<Light>> lights;
+    lights.push_back(std::make_shared<PointLight>(Translate(Vector3f(0.f, 0.9f, 0.f)), inFog, Spectrum(5.f)));
+    Scene scene(bvh, lights);
+
+    Film *film = new Film(Point2i(res, res), Bounds2f(Point2f(0, 0), Point2f(1, 1)),
+                          std::unique_ptr<Filter>(new BoxFilter(Vector2f(0.5f, 0.5f))), 35.f,
+                          "/tmp/bre_ref_fogbox.pfm", 1.f);
+    Transform c2w = Inverse(LookAt(Point3f(0, 0, -3.5f), Point3f(0, 0, 0), Vector3f(0, 1, 0)));
+    AnimatedTransform ac2w(&c2w, 0.f, &c2w, 1.f);
+    std::shared_ptr<const Camera> camera = std::make_shared<PerspectiveCamera>(
+        ac2w, Bounds2f(Point2f(-1, -1), Point2f(1, 1)), 0.f, 1.f, 0.f, 1e6f, 40.f, film, &fog);
+
+    // ---- photon pass: the reference's own ShootPhotons
+    refx::PhotonDump dump;
+    refx::shoot_volume_photons(scene, camera, nVolumeWanted, 5, &dump);
+    // ShootPhotons runs NumSystemCores() tasks of >= 4096 paths each, so the dump is large; the
+    // fixture keeps a PREFIX of it (reference storage order).  n_paths stays the reference's nShot.
+    if (keep && dump.p.size() / 3 > keep) { dump.p.resize(3 * (size_t)keep); dump.alpha.resize(3 * (size_t)keep); dump.wi.resize(3 * (size_t)keep); }
+    const uint32_t n = (uint32_t)(dump.p.size() / 3);
+
+    // ---- camera rays: pixel centres through the reference camera, tMax from Scene::Intersect
+    // (integrators/photonbeam.cpp:465-481)
+    std::vector<float> ro, rd;
+    std::vector<Ray> rays;
+    for (int y = 0; y < res; ++y)
+        for (int x = 0; x < res; ++x) {
+            CameraSample cs;
+            cs.pFilm = Point2f(x + 0.5f, y + 0.5f);
+            cs.pLens = Point2f(0.5f, 0.5f);
+            cs.time = 0.f;
+            RayDifferential ray;
+            camera->GenerateRayDifferential(cs, &ray);
+            SurfaceInteraction isect;
+            scene.Intersect(ray, &isect);   // shortens ray.tMax (core/primitive.cpp:97-101)
+            rays.push_back(ray);
+            ro.push_back(ray.o.x); ro.push_back(ray.o.y); ro.push_back(ray.o.z); ro.push_back(ray.tMax);
+            push3(rd, ray.d);
+        }
+
+    // ---- beam radiance estimate, brute force, reference arithmetic classes
+    const float nPaths = (float)dump.nShot;
+    const float r2 = radius * radius;
+    HenyeyGreenstein hg(g);
+    StreamSampler smp(1);
+    std::vector<uint64_t> offs(1, 0);
+    std::vector<uint32_t> idx;
+    std::vector<float> rgb;
+    for (const Ray &ray : rays) {
+        Spectrum L(0.f);
+        for (uint32_t i = 0; i < n; ++i) {
+            Point3f p(dump.p[3 * i], dump.p[3 * i + 1], dump.p[3 * i + 2]);
+            Vector3f v = p - ray.o;
+            Float t = Dot(v, ray.d);
+            if (!(t > 0 && t < ray.tMax)) continue;
+            Vector3f w = v - t * ray.d;
+            Float d2 = w.LengthSquared();
+            if (!(d2 < r2)) continue;            // strict <, core/kdtree.h:182-184
+            idx.push_back(i);
+            float pp[3] = {p.x, p.y, p.z};
+            Point3f c = ray(t);
+            float cc[3] = {c.x, c.y, c.z};
+            Float k = refx::kernel(pp, cc, r2);   // integrators/photonmap.cpp:170-174
+            Vector3f wi(dump.wi[3 * i], dump.wi[3 * i + 1], dump.wi[3 * i + 2]);
+            Spectrum alpha = rgbS(dump.alpha[3 * i], dump.alpha[3 * i + 1], dump.alpha[3 * i + 2]);
+            Spectrum Tr = fog.Tr(Ray(ray.o, ray.d, t), smp);
+            // photonmap.cpp:198 normalisation, vsppm.cpp:488-489 phase orientation
+            L += (k / (nPaths * r2)) * hg.p(-ray.d, wi) * Tr * alpha;
+        }
+        offs.push_back(idx.size());
+        pushS(rgb, L);
+    }
+
+    BinWriter bw(path);
+    bw.f4("medium", {sa, sa, sa, ss, ss, ss, g});
+    bw.f4("radius", {radius});
+    bw.f4("n_paths", {nPaths});
+    bw.u4("res", {(uint32_t)res, (uint32_t)res});
+    bw.f4("photon_p", dump.p); bw.f4("photon_alpha", dump.alpha); bw.f4("photon_wi", dump.wi);
+    bw.f4("ray_o_tmax", ro); bw.f4("ray_d", rd);
+    bw.u8("hit_offsets", offs); bw.u4("hit_indices", idx); bw.f4("radiance", rgb);
+    fprintf(stderr, "fogbox: %u volume photons from %u paths, %zu rays, %zu hits\n", n, dump.nShot,
+            rays.size(), idx.size());
+}
+
+// ---------------------------------------------------------------- mode: trace
+void trace(const char *path, const char *kind, uint64_t first, uint64_t nPaths, int maxDepth) {
+    const bool grid = strcmp(kind, "grid") == 0;
+    const float sa[3] = {0.05f, 0.05f, 0.05f}, ss[3] = {0.4f, 0.4f, 0.4f};
+    const float g = 0.3f;
+    std::unique_ptr<Medium> med;
+    const int nx = 6, ny = 5, nz = 4;
+    std::vector<float> dens = test_grid(nx, ny, nz, 41);
+    Transform m2w = Translate(Vector3f(kBoxLo[0], kBoxLo[1], kBoxLo[2])) *
+                    Scale(kBoxHi[0] - kBoxLo[0], kBoxHi[1] - kBoxLo[1], kBoxHi[2] - kBoxLo[2]);
+    Transform w2m = Inverse(m2w);
+    if (grid) med.reset(new GridDensityMedium(Spectrum(sa[0]), Spectrum(ss[0] * 4), g, nx, ny, nz, m2w, dens.data()));
+    else med.reset(new HomogeneousMedium(rgbS(sa[0], sa[1], sa[2]), rgbS(ss[0], ss[1], ss[2]), g));
+    MediumInterface in(med.get(), med.get());
+    std::vector<std::shared_ptr<Primitive>> prims = box_prims(nullptr, in);
+    std::shared_ptr<BVHAccel> bvh = std::make_shared<BVHAccel>(prims);
+    std::vector<std::shared_ptr<Light>> lights;
+    lights.push_back(std::make_shared<PointLight>(Translate(Vector3f(0.f, 0.9f, 0.f)), in, rgbS(5.f, 4.f, 3.f)));
+    // spot light aimed along (0.3,-1,0.2), built exactly as a scene file would (lights/spot.cpp:104-125)
+    const Point3f spotFrom(1.f, 1.9f, -1.f), spotTo(1.3f, 0.9f, -0.8f);
+    {
+        ParamSet ps;
+        std::unique_ptr<Point3f[]> from(new Point3f[1]), to(new Point3f[1]);
+        from[0] = spotFrom; to[0] = spotTo;
+        std::unique_ptr<Float[]> I(new Float[3]), ca(new Float[1]), cd(new Float[1]);
+        I[0] = 30.f; I[1] = 30.f; I[2] = 20.f; ca[0] = 35.f; cd[0] = 10.f;
+        ps.AddPoint3f("from", std::move(from), 1); ps.AddPoint3f("to", std::move(to), 1);
+        ps.AddRGBSpectrum("I", std::move(I), 3);
+        ps.AddFloat("coneangle", std::move(ca), 1); ps.AddFloat("conedeltaangle", std::move(cd), 1);
+        lights.push_back(CreateSpotLight(Transform(), med.get(), ps));
+    }
+    Scene scene(bvh, lights);
+    std::unique_ptr<Distribution1D> lightDistr = ComputeLightPowerDistribution(scene);
+
+    std::vector<float> pp, pa, pw;
+    std::vector<uint32_t> pid;
+    MemoryArena arena;
+    for (uint64_t pi = first; pi < first + nPaths; ++pi) {
+        StreamSampler sampler(pi + 1);                       // photonbeam.cpp:386-391
+        Float lightPdf;
+        int lightNum = lightDistr->SampleDiscrete(sampler.Get1D(), &lightPdf);   // :394-398
+        const std::shared_ptr<Light> &light = scene.lights[lightNum];
+        Point2f uLight0 = sampler.Get2D();
+        Point2f uLight1 = sampler.Get2D();
+        Float uLightTime = sampler.Get1D();
+        RayDifferential photonRay;
+        Normal3f nLight;
+        Float pdfPos, pdfDir;
+        Spectrum Le = light->Sample_Le(uLight0, uLight1, uLightTime, &photonRay, &nLight, &pdfPos, &pdfDir);
+        if (pdfPos == 0 || pdfDir == 0 || Le.IsBlack()) continue;
+        Spectrum alpha = (AbsDot(nLight, photonRay.d) * Le) / (lightPdf * pdfPos * pdfDir);   // :413-414
+        if (alpha.IsBlack()) continue;
+        SurfaceInteraction sisect;
+        int nIntersections = 0;
+        while (scene.Intersect(photonRay, &sisect)) {        // photonmap.cpp:696
+            ++nIntersections;
+            MediumInteraction misect;
+            if (photonRay.medium) alpha *= photonRay.medium->Sample(photonRay, sampler, arena, &misect);
+            if (alpha.IsBlack()) break;
+            if (!misect.IsValid()) break;                    // reached the absorbing wall
+            const Vector3f wo = -photonRay.d;
+            Vector3f wi;
+            misect.phase->Sample_p(wo, &wi, sampler.Get2D());
+            push3(pp, misect.p); pushS(pa, alpha); push3(pw, wo);   // Photon(misect.p, alpha, wo) :720-723
+            pid.push_back((uint32_t)pi);
+            photonRay = misect.SpawnRay(wi);
+            if (nIntersections >= maxDepth) break;           // :794
+            Float sample = sampler.Get1D();                  // RR draw, continueProb == 1 (:799-804)
+            if (sample > 1.f) break;
+        }
+        arena.Reset();
+    }
+    std::vector<float> w2mf;
+    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) w2mf.push_back(w2m.GetMatrix().m[i][j]);
+    std::vector<float> lightAxis;
+    push3(lightAxis, Normalize(spotTo - spotFrom));
+    BinWriter bw(path);
+    bw.u4("kind", {(uint32_t)grid});
+    bw.f4("sigma_a", {sa[0], sa[1], sa[2]});
+    if (grid) bw.f4("sigma_s", {ss[0] * 4, ss[0] * 4, ss[0] * 4}); else bw.f4("sigma_s", {ss[0], ss[1], ss[2]});
+    bw.f4("g", {g});
+    bw.u4("grid_dims", {(uint32_t)nx, (uint32_t)ny, (uint32_t)nz});
+    bw.f4("grid_density", dens); bw.f4("w2m", w2mf);
+    bw.f4("box_lo", {kBoxLo[0], kBoxLo[1], kBoxLo[2]}); bw.f4("box_hi", {kBoxHi[0], kBoxHi[1], kBoxHi[2]});
+    bw.f4("spot_axis", lightAxis);
+    bw.u8("range", {first, nPaths, (uint64_t)maxDepth});
+    bw.f4("photon_p", pp); bw.f4("photon_alpha", pa); bw.f4("photon_wi", pw); bw.u4("path_id", pid);
+    fprintf(stderr, "trace %s: %zu photons from %llu paths\n", kind, pid.size(), (unsigned long long)nPaths);
+}
+
+}  // namespace
+
+int main(int argc, char **argv) {
+    PbrtOptions.quiet = true;
+    PbrtOptions.nThreads = 1;   // ShootPhotons claims blocks under a mutex: one thread = one order
+    if (argc >= 3 && !strcmp(argv[1], "primitives")) { primitives(argv[2]); return 0; }
+    if (argc >= 6 && !strcmp(argv[1], "fogbox")) {
+        fogbox(argv[2], atoi(argv[3]), atoi(argv[4]), (float)atof(argv[5]), argc >= 7 ? (uint32_t)atoi(argv[6]) : 0u);
+        return 0;
+    }
+    if (argc >= 7 && !strcmp(argv[1], "trace")) {
+        trace(argv[2], argv[3], strtoull(argv[4], 0, 10), strtoull(argv[5], 0, 10), atoi(argv[6]));
+        return 0;
+    }
+    fprintf(stderr, "usage: ref_harness primitives out.json | fogbox out.bin nPhotons res radius [keepFirst] | "
+                    "trace out.bin homogeneous|grid first nPaths maxDepth\n");
+    return 2;
+}

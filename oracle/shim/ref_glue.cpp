@@ -2,8 +2,9 @@
 // Link-time glue for the reference subset built by oracle/Makefile.  The
 // reference's core/imageio.cpp needs OpenEXR/lodepng/targa and core/api.cpp
 // drags in every plugin; neither is on the beam-radiance hot path, so this
-// file supplies the three symbols the subset still needs from them:
+// file supplies the symbols the subset still needs from them:
 //   pbrt::PbrtOptions               (defined in core/api.cpp:130 upstream)
+//   pbrt::line_num / current_file   (parser state read by core/error.cpp; defined in core/parser.cpp)
 //   pbrt::WriteImage / ReadImage    (core/imageio.h:49-56) -- float32 PFM only
 #include "pbrt.h"
 #include "geometry.h"
@@ -14,6 +15,8 @@
 namespace pbrt {
 
 Options PbrtOptions;
+int line_num = 0;
+std::string current_file;
 
 void WriteImage(const std::string &name, const Float *rgb,
                 const Bounds2i &outputBounds, const Point2i &) {

@@ -1,0 +1,247 @@
+"""CPU tests: the oracle (oracle/bre_oracle.c) against golden vectors computed by REFERENCE code.
+
+tests/golden/*.npz were produced by oracle/ref_harness.cpp linked against the unmodified reference
+sources (tests/golden/make_golden.py).  These tests pin every primitive of the restatement, the
+photon-deposit loop, and the composed beam radiance estimate on a photon set dumped from the
+reference's own PhotonIntegrator::ShootPhotons.  Nothing here needs a GPU.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLD = os.path.join(HERE, "golden")
+
+
+def gold(name):
+    return np.load(os.path.join(GOLD, name))
+
+
+def bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+def fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+def f3(v):
+    return (C.c_float * 3)(*[float(x) for x in v])
+
+
+@pytest.fixture(scope="module")
+def prim():
+    return gold("ref_primitives.npz")
+
+
+def test_pcg32_matches_reference(orc, prim):
+    lib = orc.load()
+    seqs, u32, fl = prim["rng/seq"], prim["rng/u32"].reshape(-1, 6), prim["rng/float"].reshape(-1, 6)
+    for i, s in enumerate(seqs):
+        r = orc.Rng()
+        lib.orc_rng_seed(C.byref(r), C.c_uint64(int(s)))
+        got_u = [lib.orc_rng_u32(C.byref(r)) for _ in range(6)]
+        got_f = np.array([lib.orc_rng_float(C.byref(r)) for _ in range(6)], np.float32)
+        assert got_u == [int(x) for x in u32[i]]
+        assert np.array_equal(bits(got_f), bits(fl[i]))
+
+
+def test_sphere_cone_sampling_bit_exact(orc, prim):
+    lib = orc.load()
+    u = prim["sampling/u"].reshape(-1, 2)
+    sph, cone = prim["sampling/sphere"].reshape(-1, 3), prim["sampling/cone"].reshape(-1, 3)
+    ct = float(prim["sampling/cosThetaMax"][0])
+    out = (C.c_float * 3)()
+    for i in range(u.shape[0]):
+        lib.orc_uniform_sample_sphere(C.c_float(u[i, 0]), C.c_float(u[i, 1]), out)
+        assert np.array_equal(bits(np.array(out[:], np.float32)), bits(sph[i]))
+        lib.orc_uniform_sample_cone(C.c_float(u[i, 0]), C.c_float(u[i, 1]), C.c_float(ct), out)
+        assert np.array_equal(bits(np.array(out[:], np.float32)), bits(cone[i]))
+
+
+def test_phase_function_bit_exact(orc, prim):
+    lib = orc.load()
+    g, c, v = prim["phase/g"], prim["phase/cosTheta"], prim["phase/PhaseHG"]
+    got = np.array([lib.orc_phase_hg(float(c[i]), float(g[i])) for i in range(len(g))], np.float32)
+    assert np.array_equal(bits(got), bits(v))
+    # HenyeyGreenstein::p(wo, wi) = PhaseHG(Dot(wo, wi), g)
+    wo, wi, p = prim["phase/p_wo"].reshape(-1, 3), prim["phase/p_wi"].reshape(-1, 3), prim["phase/p"]
+    for i in range(len(p)):
+        a, b = wo[i], wi[i]
+        cos = np.float32(np.float32(np.float32(a[0] * b[0]) + np.float32(a[1] * b[1])) + np.float32(a[2] * b[2]))
+        assert bits(np.float32(lib.orc_phase_hg(float(cos), float(g[i])))) == bits(p[i])
+
+
+def test_hg_sample_p_bit_exact(orc, prim):
+    lib = orc.load()
+    g = prim["phase/g"]
+    u, wo = prim["phase/s_u"].reshape(-1, 2), prim["phase/s_wo"].reshape(-1, 3)
+    wi, ret = prim["phase/s_wi"].reshape(-1, 3), prim["phase/s_ret"]
+    out = (C.c_float * 3)()
+    for i in range(len(ret)):
+        r = lib.orc_hg_sample_p(f3(wo[i]), C.c_float(g[i]), C.c_float(u[i, 0]), C.c_float(u[i, 1]), out)
+        assert np.array_equal(bits(np.array(out[:], np.float32)), bits(wi[i])), i
+        assert bits(np.float32(r)) == bits(ret[i])
+
+
+def test_homogeneous_tr_bit_exact(oracle, prim):
+    oracle.set_medium_homogeneous(prim["homogeneous_tr/sigma_a"], prim["homogeneous_tr/sigma_s"], 0.3)
+    t, tr = prim["homogeneous_tr/t"], prim["homogeneous_tr/Tr"].reshape(-1, 3)
+    out = (C.c_float * 3)()
+    for i in range(len(t)):
+        oracle.lib.orc_homogeneous_tr(C.byref(oracle.medium), C.c_float(t[i]), out)
+        assert np.array_equal(bits(np.array(out[:], np.float32)), bits(tr[i]))
+
+
+def _grid_oracle(oracle, prim):
+    nx, ny, nz = [int(x) for x in prim["grid/dims"]]
+    dens = prim["grid/density"].reshape(nz, ny, nx)
+    sa, ss = float(prim["grid/sigma_a"][0]), float(prim["grid/sigma_s"][0])
+    oracle.set_medium_grid([sa] * 3, [ss] * 3, 0.3, dens, prim["grid/w2m"].reshape(4, 4))
+    return sa + ss
+
+
+def test_grid_density_bit_exact(oracle, prim):
+    _grid_oracle(oracle, prim)
+    p, d = prim["grid/p"].reshape(-1, 3), prim["grid/Density"]
+    got = np.array([oracle.lib.orc_grid_density(C.byref(oracle.medium), f3(p[i])) for i in range(len(d))], np.float32)
+    assert np.array_equal(bits(got), bits(d))
+
+
+def test_grid_transmittance_matches_ratio_tracking_mean(oracle, prim):
+    """GridDensityMedium::Tr is stochastic (ratio tracking + RR, media/grid.cpp:89-121); the oracle's
+    deterministic optical-depth table must agree with the mean of 40000 reference samples within
+    5 standard errors + 0.5 % (midpoint-rule error of the table)."""
+    sigma_t = _grid_oracle(oracle, prim)
+    o, d, tm = prim["grid/ray_o"].reshape(-1, 3), prim["grid/ray_d"].reshape(-1, 3), prim["grid/ray_tMax"]
+    mean, se = prim["grid/Tr_mean"], prim["grid/Tr_stderr"]
+    steps = 2048
+    tau = (C.c_float * (steps + 1))()
+    t0, t1 = C.c_float(), C.c_float()
+    for i in range(len(tm)):
+        hit = oracle.lib.orc_grid_tau_table(C.byref(oracle.medium), f3(o[i]), f3(d[i]), C.c_float(tm[i]), steps,
+                                            tau, C.byref(t0), C.byref(t1))
+        tr = np.exp(-sigma_t * tau[steps]) if hit else 1.0
+        assert abs(tr - mean[i]) <= 5 * se[i] + 5e-3 * mean[i], (i, tr, mean[i], se[i])
+
+
+def test_bounds_intersect_bit_exact(orc, prim):
+    lib = orc.load()
+    lo, hi = prim["bounds/lo"].reshape(-1, 3), prim["bounds/hi"].reshape(-1, 3)
+    o, d, tm = prim["bounds/o"].reshape(-1, 3), prim["bounds/d"].reshape(-1, 3), prim["bounds/tMax"]
+    hp, t0g, t1g, hs = prim["bounds/IntersectP"], prim["bounds/t0"], prim["bounds/t1"], prim["bounds/IntersectP_invDir"]
+    assert 0.1 < hs.mean() < 0.9          # the vectors exercise both outcomes
+    t0, t1 = C.c_float(), C.c_float()
+    for i in range(len(tm)):
+        h = lib.orc_ray_box(f3(o[i]), f3(d[i]), C.c_float(tm[i]), f3(lo[i]), f3(hi[i]), C.byref(t0), C.byref(t1))
+        assert h == hp[i], i
+        if h:
+            assert bits(np.float32(t0.value)) == bits(t0g[i]) and bits(np.float32(t1.value)) == bits(t1g[i])
+        s = lib.orc_slab_test(f3(o[i]), f3(d[i]), C.c_float(tm[i]), f3(lo[i]), f3(hi[i]), C.c_float(0.0))
+        assert s == hs[i], i
+
+
+def test_morton_codes_and_sort_order(orc, prim):
+    lib = orc.load()
+    lo, hi = prim["morton/lo"], prim["morton/hi"]
+    p, code = prim["morton/p"].reshape(-1, 3), prim["morton/code"]
+    got = [lib.orc_morton30(f3(p[i]), f3(lo), f3(hi)) for i in range(len(code))]
+    assert got == [int(c) for c in code]
+    # the reference RadixSort (photonbeambvh.cpp:141-182) is a stable sort by code: that equals the
+    # oracle's / the GPU build's ordering by the 64-bit key (code << 32 | index)
+    codes_in, prim_out = prim["morton/sort_in_codes"], prim["morton/sort_out_prim"]
+    key = (codes_in.astype(np.uint64) << np.uint64(32)) | np.arange(len(codes_in), dtype=np.uint64)
+    assert np.array_equal(np.argsort(key, kind="stable"), prim_out)
+
+
+def test_kernel_matches_reference(prim):
+    """kernel() photonmap.cpp:170-174 = 3/pi (1 - d^2/r^2)^2; the oracle evaluates the same expression
+    with d^2 from its disk predicate."""
+    a, b = prim["kernel/photon_p"].reshape(-1, 3), prim["kernel/p"].reshape(-1, 3)
+    md2, k = prim["kernel/maxDist2"], prim["kernel/kernel"]
+    d = (a - b).astype(np.float32)
+    d2 = (d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]).astype(np.float32) + d[:, 2] * d[:, 2]
+    s = np.float32(1) - d2 / md2
+    ours = np.float32(3) * np.float32(0.31830988618379067154) * s * s
+    assert np.array_equal(bits(ours), bits(k))
+
+
+def test_film_resolve_bit_exact(oracle, prim):
+    w, h = [int(x) for x in prim["film/dims"]]
+    rgb_in, rgb_out = prim["film/rgb_in"].reshape(-1, 3), prim["film/rgb_out"].reshape(-1, 3)
+    got = oracle.film_resolve(rgb_in, 0, float(prim["film/scale"][0]))
+    assert got.shape == (w * h, 3)
+    assert np.array_equal(bits(got), bits(rgb_out))
+    assert (rgb_out >= 0).all() and (rgb_out[5] == 0).any()   # the negative input was clamped
+
+
+# ------------------------------------------------------------------ photon deposit loop
+def _trace_lights(g):
+    ax = [float(x) for x in g["spot_axis"]]
+    return [dict(kind=0, pos=(0.0, 0.9, 0.0), I=(5.0, 4.0, 3.0)),
+            dict(kind=1, pos=(1.0, 1.9, -1.0), I=(30.0, 30.0, 20.0), axis=ax,
+                 cos_total_width=float(np.cos(np.radians(np.float32(35.0)), dtype=np.float32)),
+                 cos_falloff_start=float(np.cos(np.radians(np.float32(25.0)), dtype=np.float32)))]
+
+
+@pytest.mark.parametrize("kind", ["homogeneous", "grid"])
+def test_trace_matches_reference_classes(oracle, kind):
+    """Same path indices, same PCG32 streams: the oracle's photon records must equal the records the
+    reference classes deposit.  The reference intersects 12 triangles, the oracle an axis-aligned
+    box, so a wall distance can differ in the last ulp; that only matters for a free-flight distance
+    within an ulp of the wall (a path then has a different photon count)."""
+    g = gold(f"ref_trace_{kind}.npz")
+    first, n_paths, depth = [int(x) for x in g["range"]]
+    if kind == "grid":
+        nx, ny, nz = [int(x) for x in g["grid_dims"]]
+        oracle.set_medium_grid(g["sigma_a"], g["sigma_s"], float(g["g"][0]), g["grid_density"].reshape(nz, ny, nx),
+                               g["w2m"].reshape(4, 4))
+    else:
+        oracle.set_medium_homogeneous(g["sigma_a"], g["sigma_s"], float(g["g"][0]))
+    pos, pw, dr, pid = oracle.trace(_trace_lights(g), g["box_lo"], g["box_hi"], first, n_paths, depth)
+    rp, ra, rw, rid = g["photon_p"].reshape(-1, 3), g["photon_alpha"].reshape(-1, 3), g["photon_wi"].reshape(-1, 3), g["path_id"]
+    exact = close = 0
+    for p in range(first, first + n_paths):
+        a, b = pid == p, rid == p
+        if a.sum() != b.sum():
+            continue
+        if np.array_equal(bits(pos[a]), bits(rp[b])) and np.array_equal(bits(pw[a]), bits(ra[b])) and \
+                np.array_equal(bits(dr[a]), bits(rw[b])):
+            exact += 1
+        if np.allclose(pos[a], rp[b], rtol=0, atol=2e-5) and np.allclose(pw[a], ra[b], rtol=2e-3, atol=0) and \
+                np.allclose(dr[a], rw[b], rtol=0, atol=2e-6):
+            close += 1
+    # Point-light paths are bit-identical.  Spot-light directions go through the reference's
+    # LightToWorld = Inverse(dirToZ) (a numerically inverted 4x4, lights/spot.cpp:112-121) where the
+    # oracle multiplies by the CoordinateSystem frame directly: 1-ulp direction differences, which the
+    # smoothstep^4 falloff (spot.cpp:64-73) amplifies to <= 1e-3 relative in alpha near the cone edge.
+    assert exact >= 0.55 * n_paths, f"{exact}/{n_paths} paths bit-identical"
+    assert close >= 0.998 * n_paths, f"{close}/{n_paths} paths within tolerance"
+    assert abs(len(pid) - len(rid)) <= 0.002 * len(rid)
+
+
+# ------------------------------------------------------------------ composed estimate on reference photons
+def test_beam_estimate_on_reference_photon_dump(oracle):
+    """Photons dumped from the reference's PhotonIntegrator::ShootPhotons, camera rays from the
+    reference's PerspectiveCamera + Scene::Intersect.  Golden = brute force with reference classes.
+    Oracle (LBVH traversal AND brute force): hit-index sets bit-exact, radiance within 1e-5."""
+    g = gold("ref_fogbox.npz")
+    m = g["medium"]
+    oracle.set_medium_homogeneous(m[0:3], m[3:6], float(m[6]))
+    oracle.set_photons(g["photon_p"], g["photon_alpha"], g["photon_wi"], float(g["radius"][0]))
+    oracle.build()
+    ro, rd = g["ray_o_tmax"].reshape(-1, 4), g["ray_d"].reshape(-1, 3)
+    ref_rgb = g["radiance"].reshape(-1, 3)
+    for brute in (False, True):
+        if brute:
+            rgb, offs, idx, _ = oracle.query(ro, rd, float(g["n_paths"][0]), want_hits=True, brute=True)
+        else:
+            rgb, offs, idx, cnt = oracle.query(ro, rd, float(g["n_paths"][0]), want_hits=True)
+            assert cnt["hits"] == len(g["hit_indices"])
+        assert np.array_equal(offs, g["hit_offsets"])
+        assert np.array_equal(idx, g["hit_indices"])      # both ascending per ray
+        err = np.abs(rgb.astype(np.float64) - ref_rgb)
+        assert err.max() <= 1e-5 * np.abs(ref_rgb).max()
+        assert err.mean() <= 1e-6 * np.abs(ref_rgb).mean()
