@@ -8,7 +8,7 @@
 // Pipeline (all on the context stream, no host round trip except one 4-byte read of abs_max):
 //   k_bounds      min/max of photon positions                  (centroid bounds, :431-436)
 //   k_morton      30-bit Morton code per photon                 (:438-445)
-//   radix sort    4 x 8-bit stable LSD passes of (code, index)  (integer; hist / scan / scatter)
+//   radix sort    4 x 8-bit stable LSD passes of (code, index)  (integer; hist / 3-launch scan / scatter)
 //   k_gather      photon SoA -> Morton order, leaf boxes, max |coord|
 //   k_karras      binary radix tree over keys (code<<32 | index): one thread per internal node
 //   k_refit       bottom-up AABB union with per-node arrival counters
@@ -114,16 +114,42 @@ __global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const uint32_t *__restri
     hist[threadIdx.x * numBlocks + blockIdx.x] = sh[threadIdx.x];
 }
 
-// exclusive scan of `len` counters in place, single block
-__global__ void __launch_bounds__(1024) k_rs_scan(uint32_t *__restrict__ hist, uint32_t len) {
-    __shared__ uint32_t warpSums[32];
-    __shared__ uint32_t carry;
-    uint32_t per = (len + blockDim.x - 1) / blockDim.x;
-    uint32_t b = threadIdx.x * per, e = min(b + per, len);
+// Exclusive scan of `len` u32 counters in place, three launches: per-tile sums (tiles of 2048),
+// a single-block scan of the tile sums, and the in-tile scan with the tile offset applied.
+constexpr int SCN_T = 256, SCN_I = 8, SCN_TILE = SCN_T * SCN_I;
+
+__global__ void __launch_bounds__(SCN_T) k_rs_scan_reduce(const uint32_t *__restrict__ in,
+                                                          uint32_t len,
+                                                          uint32_t *__restrict__ tileSums) {
+    __shared__ uint32_t ws[SCN_T / 32];
+    const uint32_t base = blockIdx.x * SCN_TILE;
     uint32_t sum = 0;
-    for (uint32_t i = b; i < e; ++i) sum += hist[i];
-    // block exclusive scan of `sum`
-    uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < SCN_I; ++k) {
+        uint32_t i = base + k * SCN_T + threadIdx.x;
+        if (i < len) sum += __ldg(in + i);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+#pragma unroll
+        for (int i = 0; i < SCN_T / 32; ++i) t += ws[i];
+        tileSums[blockIdx.x] = t;
+    }
+}
+
+// single block of 1024 threads: exclusive scan of nTiles tile sums in place
+__global__ void __launch_bounds__(1024) k_rs_scan_tiles(uint32_t *__restrict__ tileSums,
+                                                        uint32_t nTiles) {
+    __shared__ uint32_t warpSums[32];
+    const uint32_t per = (nTiles + blockDim.x - 1) / blockDim.x;
+    const uint32_t b = threadIdx.x * per, e = min(b + per, nTiles);
+    uint32_t sum = 0;
+    for (uint32_t i = b; i < e; ++i) sum += tileSums[i];
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     uint32_t incl = sum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -131,7 +157,6 @@ __global__ void __launch_bounds__(1024) k_rs_scan(uint32_t *__restrict__ hist, u
         if (lane >= o) incl += t;
     }
     if (lane == 31) warpSums[w] = incl;
-    if (threadIdx.x == 0) carry = 0;
     __syncthreads();
     if (w == 0) {
         uint32_t v = warpSums[lane], iv = v;
@@ -145,9 +170,35 @@ __global__ void __launch_bounds__(1024) k_rs_scan(uint32_t *__restrict__ hist, u
     __syncthreads();
     uint32_t run = warpSums[w] + incl - sum;
     for (uint32_t i = b; i < e; ++i) {
-        uint32_t v = hist[i];
-        hist[i] = run;
+        uint32_t v = tileSums[i];
+        tileSums[i] = run;
         run += v;
+    }
+}
+
+__global__ void __launch_bounds__(SCN_T) k_rs_scan_apply(uint32_t *__restrict__ data, uint32_t len,
+                                                         const uint32_t *__restrict__ tileOff) {
+    __shared__ uint32_t ws[SCN_T / 32];
+    const uint32_t base = blockIdx.x * SCN_TILE + threadIdx.x * SCN_I;   // SCN_I consecutive elements
+    uint32_t v[SCN_I], sum = 0;
+#pragma unroll
+    for (int k = 0; k < SCN_I; ++k) { v[k] = (base + k < len) ? data[base + k] : 0u; sum += v[k]; }
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint32_t incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) ws[w] = incl;
+    __syncthreads();
+    uint32_t woff = 0;
+    for (uint32_t i = 0; i < w; ++i) woff += ws[i];
+    uint32_t run = __ldg(tileOff + blockIdx.x) + woff + incl - sum;
+#pragma unroll
+    for (int k = 0; k < SCN_I; ++k) {
+        if (base + k < len) data[base + k] = run;
+        run += v[k];
     }
 }
 
@@ -371,13 +422,16 @@ int build_tree(bre_ctx *ctx) {
     ENS(flags, (size_t)n * 4); ENS(fast, (size_t)n * sizeof(FastNode));
     ENS(scratch, 64);
     const uint32_t numBlocks = (n + RS_TILE - 1) / RS_TILE;
-    ENS(hist, (size_t)256 * numBlocks * 4);
+    const uint32_t histLen = 256u * numBlocks;
+    const uint32_t scanTiles = (histLen + SCN_TILE - 1) / SCN_TILE;
+    ENS(hist, ((size_t)histLen + scanTiles) * 4);
 #undef ENS
     uint32_t *bnd = (uint32_t *)ctx->scratch.p;
     const float4 *pos_r = (const float4 *)ctx->pos_r.p;
     uint32_t *codes = (uint32_t *)ctx->codes.p, *order = (uint32_t *)ctx->order.p;
     uint32_t *kalt = (uint32_t *)ctx->keys_alt.p, *valt = (uint32_t *)ctx->vals_alt.p;
     uint32_t *hist = (uint32_t *)ctx->hist.p;
+    uint32_t *tileSums = hist + histLen;
     const int g256 = (int)((n + 255) / 256);
 
     PhaseTimer *pt = new PhaseTimer(ctx, PH_BUILD);
@@ -389,7 +443,9 @@ int build_tree(bre_ctx *ctx) {
     for (int pass = 0; pass < 4; ++pass) {
         int shift = 8 * pass;
         k_rs_hist<<<numBlocks, RS_THREADS, 0, st>>>(kin, n, shift, hist, numBlocks);
-        k_rs_scan<<<1, 1024, 0, st>>>(hist, 256u * numBlocks);
+        k_rs_scan_reduce<<<scanTiles, SCN_T, 0, st>>>(hist, histLen, tileSums);
+        k_rs_scan_tiles<<<1, 1024, 0, st>>>(tileSums, scanTiles);
+        k_rs_scan_apply<<<scanTiles, SCN_T, 0, st>>>(hist, histLen, tileSums);
         k_rs_scatter<<<numBlocks, RS_THREADS, 0, st>>>(kin, vin, kout, vout, n, shift, hist,
                                                        numBlocks, pass == 0);
         uint32_t *t = kin; kin = kout; kout = t;

@@ -128,7 +128,7 @@ struct bre_ctx {
     float abs_max = 0;
     int root_ref = 0;
     // query scratch
-    bre::Buf packet_ctr, pair_queue;
+    bre::Buf packet_ctr, pair_queue, spill;
     bre::Buf rays_o, rays_d, out_rgb, tau, hit_counts, hit_offsets, hit_idx, counters_d, pix_idx;
     bre_counters counters{};
     // film

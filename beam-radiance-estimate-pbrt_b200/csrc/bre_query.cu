@@ -195,10 +195,14 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     if (want > (1u << 28)) want = 1u << 28;
     if (ctx->pair_queue_cap_override) want = ctx->pair_queue_cap_override;
     if ((s = ensure(ctx, ctx->pair_queue, (size_t)want * 8)) != BRE_OK) return s;
-    if ((s = ensure(ctx, ctx->packet_ctr, 64)) != BRE_OK) return s;
+    // control words | continuation-unit ready flags ; continuation units
+    const size_t ctlBytes = 64 + (size_t)SPILL_CAP * 4;
+    if ((s = ensure(ctx, ctx->packet_ctr, ctlBytes)) != BRE_OK) return s;
+    if ((s = ensure(ctx, ctx->spill, (size_t)SPILL_CAP * sizeof(SpillUnit))) != BRE_OK) return s;
     const unsigned cap = (unsigned)want;
     unsigned int *ctl = (unsigned int *)ctx->packet_ctr.p;
-    BRE_CUDA(cudaMemsetAsync(ctl, 0, 16, ctx->stream));
+    unsigned int *spillReady = ctl + 16;
+    BRE_CUDA(cudaMemsetAsync(ctl, 0, ctlBytes, ctx->stream));
     if (MODE == 0) BRE_CUDA(cudaMemsetAsync(out, 0, (size_t)n * 16, ctx->stream));
     else BRE_CUDA(cudaMemsetAsync(hitCounts, 0, (size_t)n * 4, ctx->stream));
     LeafArgs A;
@@ -207,6 +211,7 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     A.hitCounts = hitCounts; A.hitOffsets = hitOffsets; A.hitIdx = hitIdx;
     {
         PhaseTimer pt(ctx, PH_QUERY_A);
+        // persistent grid: every block is resident, idle warps wait for continuation units
         int perSM = 0;
         BRE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_traverse<MODE, COUNT>,
                                                                WQ_WARPS * 32, 0));
@@ -216,7 +221,7 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
         unsigned need = (packets + WQ_WARPS - 1) / WQ_WARPS;
         if (blocks > need) blocks = need;
         k_traverse<MODE, COUNT><<<blocks, WQ_WARPS * 32, 0, ctx->stream>>>(
-            A, n, (uint2 *)ctx->pair_queue.p, cap, ctl, counters);
+            A, n, (uint2 *)ctx->pair_queue.p, cap, ctl, (SpillUnit *)ctx->spill.p, spillReady, counters);
     }
     {
         PhaseTimer pt(ctx, PH_QUERY_B);
@@ -338,13 +343,14 @@ int run_count(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd) {
     ctx->counters.bytes_algorithmic = 48ull * n + 32ull * h[0] + 16ull * h[1] + 32ull * h[2];
     ctx->counters.fast_nodes = h[3];
     ctx->counters.fast_disk_tests = h[4];
-    unsigned int ctl[4] = {0, 0, 0, 0};
+    unsigned int ctl[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (n > 0) {
-        BRE_CUDA(cudaMemcpyAsync(ctl, ctx->packet_ctr.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+        BRE_CUDA(cudaMemcpyAsync(ctl, ctx->packet_ctr.p, 32, cudaMemcpyDeviceToHost, ctx->stream));
         BRE_CUDA(cudaStreamSynchronize(ctx->stream));
     }
-    ctx->counters.leaf_pairs = ctl[3];
-    ctx->counters.pair_queue_overflow = ctl[2];
+    ctx->counters.leaf_pairs = ctl[QC_EMITTED];
+    ctx->counters.pair_queue_overflow = ctl[QC_INPLACE];
+    ctx->counters.continuation_units = ctl[QC_SPILL_TAIL] < SPILL_CAP ? ctl[QC_SPILL_TAIL] : SPILL_CAP;
     return BRE_OK;
 }
 
