@@ -13,7 +13,7 @@ OBJS := $(patsubst %.cu,$(OBJDIR)/%.o,$(SRCS)) $(OBJDIR)/bre_nccl.o
 all: lib oracle
 lib: $(PKG)/libbre.so
 
-$(OBJDIR)/%.o: $(CSRC)/%.cu $(CSRC)/bre_internal.cuh include/bre.h
+$(OBJDIR)/%.o: $(CSRC)/%.cu $(CSRC)/bre_internal.cuh $(CSRC)/bre_query_warp.cuh include/bre.h
 	@mkdir -p $(OBJDIR)
 	$(NVCC) $(NVFLAGS) -Xptxas -v -c $< -o $@ 2> $(OBJDIR)/$*.ptxas.log || (cat $(OBJDIR)/$*.ptxas.log; false)
 

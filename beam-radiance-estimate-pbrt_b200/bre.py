@@ -50,7 +50,7 @@ class Counters(C.Structure):
     _fields_ = [("nodes_visited", C.c_uint64), ("disk_tests", C.c_uint64), ("hits", C.c_uint64),
                 ("bytes_algorithmic", C.c_uint64), ("fast_nodes", C.c_uint64),
                 ("fast_disk_tests", C.c_uint64), ("leaf_pairs", C.c_uint64),
-                ("pair_queue_overflow", C.c_uint64), ("continuation_units", C.c_uint64)]
+                ("pair_queue_overflow", C.c_uint64)]
 
 
 class HitDump(C.Structure):

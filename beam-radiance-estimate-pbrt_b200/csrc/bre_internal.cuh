@@ -128,7 +128,11 @@ struct bre_ctx {
     float abs_max = 0;
     int root_ref = 0;
     // query scratch
-    bre::Buf packet_ctr, pair_queue, spill;
+    bre::Buf packet_ctr, pair_queue, heavy;
+    // heavy-first packet order fed from one radiance query to the next (bre_query.cu)
+    size_t heavy_half = 0;
+    uint32_t heavy_rays = 0;
+    int heavy_parity = 0;
     bre::Buf rays_o, rays_d, out_rgb, tau, hit_counts, hit_offsets, hit_idx, counters_d, pix_idx;
     bre_counters counters{};
     // film

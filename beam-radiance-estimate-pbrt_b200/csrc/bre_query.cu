@@ -6,6 +6,9 @@
 // :198), PhaseHG (core/medium.h:66-69) and Medium::Tr (media/homogeneous.cpp:44-48; for grid media a
 // deterministic optical-depth table instead of the stochastic media/grid.cpp:89-121).
 #include "bre_internal.cuh"
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
 
 namespace bre {
 
@@ -195,33 +198,54 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     if (want > (1u << 28)) want = 1u << 28;
     if (ctx->pair_queue_cap_override) want = ctx->pair_queue_cap_override;
     if ((s = ensure(ctx, ctx->pair_queue, (size_t)want * 8)) != BRE_OK) return s;
-    // control words | continuation-unit ready flags ; continuation units
-    const size_t ctlBytes = 64 + (size_t)SPILL_CAP * 4;
-    if ((s = ensure(ctx, ctx->packet_ctr, ctlBytes)) != BRE_OK) return s;
-    if ((s = ensure(ctx, ctx->spill, (size_t)SPILL_CAP * sizeof(SpillUnit))) != BRE_OK) return s;
+    // packet_ctr layout: control words (64 B) | zero word + 2 heavy counters (64 B) | LeafArgs copy
+    const size_t argsOff = 256;
+    if ((s = ensure(ctx, ctx->packet_ctr, argsOff + sizeof(LeafArgs))) != BRE_OK) return s;
     const unsigned cap = (unsigned)want;
     unsigned int *ctl = (unsigned int *)ctx->packet_ctr.p;
-    unsigned int *spillReady = ctl + 16;
-    BRE_CUDA(cudaMemsetAsync(ctl, 0, ctlBytes, ctx->stream));
+    unsigned int *heavyCnt = ctl + 16;      // [0] always zero, [1 + parity] heavy packets of a launch
+    BRE_CUDA(cudaMemsetAsync(ctl, 0, 68, ctx->stream));
     if (MODE == 0) BRE_CUDA(cudaMemsetAsync(out, 0, (size_t)n * 16, ctx->stream));
     else BRE_CUDA(cudaMemsetAsync(hitCounts, 0, (size_t)n * 4, ctx->stream));
     LeafArgs A;
     A.t = tree_view(ctx); A.m = ctx->medium; A.ro = ro; A.rd = rd; A.nPathsNorm = nPathsNorm;
     A.out = out; A.tau = tau; A.span = span; A.tauSteps = ctx->tau_steps;
     A.hitCounts = hitCounts; A.hitOffsets = hitOffsets; A.hitIdx = hitIdx;
+    LeafArgs *Ag = (LeafArgs *)((char *)ctx->packet_ctr.p + argsOff);   // copy for the cold overflow path
+    k_store_args<<<1, 1, 0, ctx->stream>>>(A, Ag);
+    // heavy-first feedback between consecutive radiance queries over the same ray count
+    const unsigned packets = (n + WQ_P - 1) / WQ_P;
+    const unsigned *heavyIn = nullptr, *heavyFlagIn = nullptr, *nHeavyIn = heavyCnt;
+    unsigned *heavyOut = nullptr, *heavyFlagOut = nullptr, *nHeavyOut = heavyCnt;
+    unsigned heavyCap = 0;
+    if (MODE == 0 && !COUNT) {
+        const size_t flagWords = (packets + 31) / 32;
+        const size_t half = ((size_t)HEAVY_CAP + flagWords) * 4;
+        if ((s = ensure(ctx, ctx->heavy, 2 * half)) != BRE_OK) return s;
+        if (ctx->heavy_half != half) { ctx->heavy_half = half; ctx->heavy_rays = 0; }   // buffer re-laid out
+        const int cur = ctx->heavy_parity, prev = cur ^ 1;
+        unsigned *bufCur = (unsigned *)((char *)ctx->heavy.p + cur * half);
+        unsigned *bufPrev = (unsigned *)((char *)ctx->heavy.p + prev * half);
+        heavyOut = bufCur; heavyFlagOut = bufCur + HEAVY_CAP; nHeavyOut = heavyCnt + 1 + cur;
+        heavyCap = HEAVY_CAP;
+        BRE_CUDA(cudaMemsetAsync(heavyFlagOut, 0, flagWords * 4, ctx->stream));
+        BRE_CUDA(cudaMemsetAsync(nHeavyOut, 0, 4, ctx->stream));
+        if (ctx->heavy_rays == n) { heavyIn = bufPrev; heavyFlagIn = bufPrev + HEAVY_CAP; nHeavyIn = heavyCnt + 1 + prev; }
+        ctx->heavy_rays = n;
+        ctx->heavy_parity = prev;
+    }
     {
         PhaseTimer pt(ctx, PH_QUERY_A);
-        // persistent grid: every block is resident, idle warps wait for continuation units
         int perSM = 0;
         BRE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_traverse<MODE, COUNT>,
                                                                WQ_WARPS * 32, 0));
         if (perSM < 1) perSM = 1;
-        unsigned packets = (n + WQ_P - 1) / WQ_P;
         unsigned blocks = (unsigned)(ctx->sm_count * perSM);
-        unsigned need = (packets + WQ_WARPS - 1) / WQ_WARPS;
+        const unsigned need = (packets + WQ_WARPS - 1) / WQ_WARPS;
         if (blocks > need) blocks = need;
         k_traverse<MODE, COUNT><<<blocks, WQ_WARPS * 32, 0, ctx->stream>>>(
-            A, n, (uint2 *)ctx->pair_queue.p, cap, ctl, (SpillUnit *)ctx->spill.p, spillReady, counters);
+            A, Ag, n, (uint2 *)ctx->pair_queue.p, cap, ctl, heavyIn, nHeavyIn, heavyFlagIn, heavyOut,
+            heavyFlagOut, nHeavyOut, heavyCap, counters);
     }
     {
         PhaseTimer pt(ctx, PH_QUERY_B);
@@ -350,7 +374,6 @@ int run_count(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd) {
     }
     ctx->counters.leaf_pairs = ctl[QC_EMITTED];
     ctx->counters.pair_queue_overflow = ctl[QC_INPLACE];
-    ctx->counters.continuation_units = ctl[QC_SPILL_TAIL] < SPILL_CAP ? ctl[QC_SPILL_TAIL] : SPILL_CAP;
     return BRE_OK;
 }
 

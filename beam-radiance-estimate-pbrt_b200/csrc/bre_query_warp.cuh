@@ -5,18 +5,14 @@
 //  K5a k_traverse   warp-cooperative collect-all walk of the photon LBVH for a PACKET of P
 //                   consecutive camera rays at once.  Per warp, in shared memory: a LIFO node
 //                   stack of (node ref, ray slot) entries and a table of the P precomputed rays.
-//                   Every step up to 64 entries are popped -- TWO 64-byte two-child nodes per
-//                   lane (8 x LDG.128 in flight) -- all four child boxes are slab-tested, and the
-//                   warp compacts surviving internal children back onto the stack and surviving
+//                   Every step up to 32 entries are popped -- one 64-byte two-child node per
+//                   lane (4 x LDG.128) -- both child boxes are slab-tested (one FMA per plane), and
+//                   the warp compacts surviving internal children back onto the stack and surviving
 //                   LEAVES (<= max_leaf contiguous photons) into the global pair queue with
 //                   ballot/popc.  Queue space is reserved one 256-pair chunk per warp at a time
-//                   (one atomicAdd per chunk); packets are claimed dynamically from a counter.
+//                   (one atomicAdd per chunk); packets are claimed dynamically from a counter,
+//                   the packets that were heaviest in the previous launch first.
 //                   No photon is touched here.
-//                   Load balance: a packet whose rays look into a light source walks 10^5 nodes.
-//                   Once the packet counter is exhausted and some warp is idle, a warp whose stack
-//                   is deep hands the BOTTOM 128 entries (the largest subtrees) to a global
-//                   continuation queue as one unit {packet base, entries}; idle warps pop units,
-//                   redo the 8-ray packet setup and continue the walk (and may spill again).
 //  K5b k_leaf_pairs LW lanes per (ray, leaf) pair, one photon per lane: 64 pairs are fetched per
 //                   warp with two coalesced loads, then four pair-groups at a time the photon
 //                   {pos,radius} records (contiguous in Morton order) and rays are loaded BEFORE
@@ -28,8 +24,9 @@
 //
 // Why two kernels: through the queue every leaf becomes an independent work item, so the heavy
 // rays spread over the whole chip (profiles/r01_k5_warp_v1.md: 72 % of a fused kernel was tail).
-// If the pair queue is full a warp shades its leaves in place; if the continuation queue is full
-// a warp keeps its stack: too-small queues cost speed, never correctness.
+// If the pair queue is full a warp shades its leaves in place: a too-small queue costs speed,
+// never correctness.  (A continuation queue that split deep stacks between warps was tried and
+// measured slower: DFS stacks stay shallow, see profiles/r01_k5_v4_experiments.md.)
 #pragma once
 
 namespace bre {
@@ -37,22 +34,14 @@ namespace bre {
 constexpr int WQ_P = 8;          // rays per packet
 constexpr int WQ_NCAP = 512;     // node stack entries per warp
 constexpr int WQ_WARPS = 4;      // warps per block
-constexpr int WQ_RAYW = 16;      // floats per ray-table row (slab-test data only)
+constexpr int WQ_RAYW = 12;      // floats per ray-table row (slab-test data only)
 constexpr unsigned WQ_CHUNK = 256;  // pair-queue slots reserved per atomicAdd
 constexpr unsigned PAIR_NONE = 0xffffffffu;  // padding pair (ray index) in a partly used chunk
-constexpr int SPILL_N = 128;     // stack entries handed over per continuation unit
-constexpr int SPILL_HI = 320;    // spill only from stacks at least this deep
-constexpr unsigned SPILL_CAP = 32768;   // continuation units per launch
+constexpr unsigned HEAVY_STEPS = 256;   // a packet this long is claimed first by the next launch
+constexpr unsigned HEAVY_CAP = 65536;   // heavy packets remembered per launch
 
 // queueCtl words (zeroed before every launch)
-enum { QC_PAIR_TAIL = 0, QC_PACKET = 1, QC_INPLACE = 2, QC_EMITTED = 3, QC_SPILL_TAIL = 4,
-       QC_SPILL_HEAD = 5, QC_BUSY = 6, QC_EXITED = 7, QC_WORDS = 8 };
-
-struct __align__(16) SpillUnit {
-    unsigned base, count, pad0, pad1;
-    int ref[SPILL_N];
-    unsigned char slot[SPILL_N];
-};
+enum { QC_PAIR_TAIL = 0, QC_PACKET = 1, QC_INPLACE = 2, QC_EMITTED = 3, QC_WORDS = 8 };
 
 struct __align__(16) WarpSmem {
     int nref[WQ_NCAP];
@@ -65,13 +54,12 @@ struct __align__(16) WarpSmem {
 // so the test is restated with one FMA per plane:  t = plane * inv + c,  c = -(o +- pad) * inv.
 // The rounding error of that form is <= 2^-22 |o| |inv|, 16x below what the origin padding of
 // 2^-18 (|o|_inf + max|coord|) already grants (DESIGN.md "conservative cull"); the far planes carry
-// the reference's 1 + 2 gamma(3) widening folded into invF / cF.  inv of a zero direction
+// the reference's 1 + 2 gamma(3) widening.  inv of a zero direction
 // component is clamped to +-2^100 so that plane * inv + c never evaluates inf - inf.
 struct RayF {
     float ix, iy, iz;        // 1/d (clamped)
-    float fx, fy, fz;        // 1/d * (1 + 2 gamma3)
-    float cnx, cny, cnz;     // near-plane constants
-    float cfx, cfy, cfz;     // far-plane constants
+    float cnx, cny, cnz;     // near-plane constants  -(o + pad) / d
+    float cfx, cfy, cfz;     // far-plane constants   -(o - pad) / d
     float tMax;
     int sgn;                 // bit k: direction component k negative
 };
@@ -86,37 +74,35 @@ __device__ __forceinline__ RayF rayf_setup(float4 o, float4 d, float absMax) {
     const float pad = fmul(M, 0x1p-18f);
     const float px = (r.sgn & 1) ? -pad : pad, py = (r.sgn & 2) ? -pad : pad, pz = (r.sgn & 4) ? -pad : pad;
     r.ix = ix; r.iy = iy; r.iz = iz;
-    r.fx = fmul(ix, BRE_SLAB_WIDEN); r.fy = fmul(iy, BRE_SLAB_WIDEN); r.fz = fmul(iz, BRE_SLAB_WIDEN);
     r.cnx = -fmul(fadd(o.x, px), ix); r.cny = -fmul(fadd(o.y, py), iy); r.cnz = -fmul(fadd(o.z, pz), iz);
-    r.cfx = -fmul(fsub(o.x, px), r.fx); r.cfy = -fmul(fsub(o.y, py), r.fy); r.cfz = -fmul(fsub(o.z, pz), r.fz);
+    r.cfx = -fmul(fsub(o.x, px), ix); r.cfy = -fmul(fsub(o.y, py), iy); r.cfz = -fmul(fsub(o.z, pz), iz);
     r.tMax = o.w;
     return r;
 }
 __device__ __forceinline__ void rayf_store(float *row, const RayF &r) {
     float4 *v = reinterpret_cast<float4 *>(row);
     v[0] = make_float4(r.ix, r.iy, r.iz, r.tMax);
-    v[1] = make_float4(r.fx, r.fy, r.fz, __int_as_float(r.sgn));
-    v[2] = make_float4(r.cnx, r.cny, r.cnz, 0.f);
-    v[3] = make_float4(r.cfx, r.cfy, r.cfz, 0.f);
+    v[1] = make_float4(r.cnx, r.cny, r.cnz, __int_as_float(r.sgn));
+    v[2] = make_float4(r.cfx, r.cfy, r.cfz, 0.f);
 }
 __device__ __forceinline__ RayF rayf_load(const float *row) {
     const float4 *v = reinterpret_cast<const float4 *>(row);
-    const float4 a = v[0], b = v[1], c = v[2], d = v[3];
+    const float4 a = v[0], b = v[1], c = v[2];
     RayF r;
     r.ix = a.x; r.iy = a.y; r.iz = a.z; r.tMax = a.w;
-    r.fx = b.x; r.fy = b.y; r.fz = b.z; r.sgn = __float_as_int(b.w);
-    r.cnx = c.x; r.cny = c.y; r.cnz = c.z;
-    r.cfx = d.x; r.cfy = d.y; r.cfz = d.z;
+    r.cnx = b.x; r.cny = b.y; r.cnz = b.z; r.sgn = __float_as_int(b.w);
+    r.cfx = c.x; r.cfy = c.y; r.cfz = c.z;
     return r;
 }
 __device__ __forceinline__ bool slab_hit_f(const RayF &r, float lox, float loy, float loz, float hix,
                                            float hiy, float hiz) {
     const bool sx = r.sgn & 1, sy = r.sgn & 2, sz = r.sgn & 4;
-    const float tx0 = __fmaf_rn(sx ? hix : lox, r.ix, r.cnx), tx1 = __fmaf_rn(sx ? lox : hix, r.fx, r.cfx);
-    const float ty0 = __fmaf_rn(sy ? hiy : loy, r.iy, r.cny), ty1 = __fmaf_rn(sy ? loy : hiy, r.fy, r.cfy);
-    const float tz0 = __fmaf_rn(sz ? hiz : loz, r.iz, r.cnz), tz1 = __fmaf_rn(sz ? loz : hiz, r.fz, r.cfz);
+    const float tx0 = __fmaf_rn(sx ? hix : lox, r.ix, r.cnx), tx1 = __fmaf_rn(sx ? lox : hix, r.ix, r.cfx);
+    const float ty0 = __fmaf_rn(sy ? hiy : loy, r.iy, r.cny), ty1 = __fmaf_rn(sy ? loy : hiy, r.iy, r.cfy);
+    const float tz0 = __fmaf_rn(sz ? hiz : loz, r.iz, r.cnz), tz1 = __fmaf_rn(sz ? loz : hiz, r.iz, r.cfz);
     const float tMin = fmaxf(fmaxf(tx0, ty0), tz0);
-    const float tMax = fminf(fminf(tx1, ty1), tz1);
+    // the reference widens every far distance by 1 + 2 gamma(3); min commutes with that scaling
+    const float tMax = fmul(fminf(fminf(tx1, ty1), tz1), BRE_SLAB_WIDEN);
     // same acceptance as geometry.h:1410-1438: intervals overlap, tMin < ray.tMax, tMax > 0
     return tMin <= tMax && tMin < r.tMax && tMax > 0.f;
 }
@@ -218,9 +204,12 @@ __device__ __forceinline__ void record_hit(const LeafArgs &A, int mode, uint32_t
     if (mode == 2) A.hitIdx[A.hitOffsets[q] + pos] = __ldg(A.t.order + s);
 }
 
-// Cold path of K5a: the pair queue is full, handle one (ray, leaf) pair in place.
+// Cold path of K5a: the pair queue is full, handle one (ray, leaf) pair in place.  Takes the
+// arguments through a pointer to their copy in global memory: passing the kernel-parameter struct
+// itself would force a 296-byte local-memory copy of it into every thread of the hot kernel.
 template <int MODE>
-__device__ __noinline__ void process_pair_inplace(const LeafArgs &A, uint32_t q, int ref) {
+__device__ __noinline__ void process_pair_inplace(const LeafArgs *Ag, uint32_t q, int ref) {
+    const LeafArgs &A = *Ag;
     const float4 o = __ldg(A.ro + q), d = __ldg(A.rd + q);
     RayS r;
     r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tMax = o.w;
@@ -235,88 +224,60 @@ __device__ __noinline__ void process_pair_inplace(const LeafArgs &A, uint32_t q,
         }
     }
 }
+__global__ void k_store_args(LeafArgs A, LeafArgs *dst) { *dst = A; }
 
 __device__ __forceinline__ unsigned ld_volatile_u32(const unsigned *p) {
     return *reinterpret_cast<const volatile unsigned *>(p);
 }
 
 // ---------------------------------------------------------------- K5a
+// queueCtl: [QC_PAIR_TAIL] pair slots reserved, [QC_PACKET] claim counter, [QC_INPLACE] pairs handled
+// in place, [QC_EMITTED] pairs emitted (COUNT).
+// Heavy-first order: a packet that needed >= HEAVY_STEPS steps is appended to heavyOut; the next
+// launch over the same ray count claims those packets FIRST (heavyIn, nHeavyIn), so the 10^5-node
+// packets that look into a light source no longer finish last (measured: one such packet kept a
+// single warp busy for 2.8 ms of a 4.6 ms kernel).  Progressive rendering repeats the same camera
+// every iteration; with unrelated rays the list is merely a harmless permutation.
 template <int MODE, bool COUNT>
 __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
-    LeafArgs A, uint32_t n, uint2 *__restrict__ queue, unsigned int queueCap,
-    unsigned int *__restrict__ queueCtl, SpillUnit *__restrict__ spill,
-    unsigned int *__restrict__ spillReady, unsigned long long *__restrict__ counters) {
+    LeafArgs A, const LeafArgs *__restrict__ Ag, uint32_t n, uint2 *__restrict__ queue,
+    unsigned int queueCap, unsigned int *__restrict__ queueCtl,
+    const unsigned int *__restrict__ heavyIn, const unsigned int *__restrict__ nHeavyInPtr,
+    const unsigned int *__restrict__ heavyFlagIn, unsigned int *__restrict__ heavyOut,
+    unsigned int *__restrict__ heavyFlagOut, unsigned int *__restrict__ nHeavyOut,
+    unsigned int heavyCap,
+    unsigned long long *__restrict__ counters) {
     __shared__ WarpSmem smemAll[WQ_WARPS];
     WarpSmem &sm = smemAll[threadIdx.x >> 5];
     const TreeDev &t = A.t;
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt = (1u << lane) - 1u;
     const unsigned FULL = 0xffffffffu;
-    const unsigned totalWarps = gridDim.x * WQ_WARPS;
+    const unsigned nPackets = (n + WQ_P - 1) / WQ_P;
+    const unsigned nHeavyIn = min(__ldg(nHeavyInPtr), HEAVY_CAP);
     unsigned long long cNodes = 0;
     unsigned nEmitted = 0, nInplace = 0;
     unsigned chunkPos = 0, chunkEnd = 0;   // this warp's reserved queue slots [chunkPos, chunkEnd)
-    bool havePackets = true;
-    bool counted = true;                   // this warp is included in queueCtl[QC_BUSY]
-    bool idleSeen = false;                 // some warp is waiting for work (refreshed while spilling)
-    bool spillOff = false;
-    unsigned pollCtr = 0;
-    if (lane == 0) atomicAdd(queueCtl + QC_BUSY, 1u);
 
     for (;;) {
-        // ================= acquire work: a fresh packet, else a continuation unit
-        unsigned base = 0;
-        int nsize = 0;
-        int unit = -1;
-        if (havePackets) {
-            if (lane == 0) base = atomicAdd(queueCtl + QC_PACKET, (unsigned)WQ_P);
-            base = __shfl_sync(FULL, base, 0);
-            if (base >= n) havePackets = false;
-        }
-        if (!havePackets) {
-            int res = 0;   // 1 = got a unit, 2 = everything is done
+        // ---- claim a packet: last launch's heavy packets first, then the rest in order
+        unsigned pk = 0;
+        if (lane == 0) {
             for (;;) {
-                int cnt2 = counted ? 1 : 0;
-                if (lane == 0) {
-                    res = 0;
-                    const unsigned tl = min(ld_volatile_u32(queueCtl + QC_SPILL_TAIL), SPILL_CAP);
-                    const unsigned hd = ld_volatile_u32(queueCtl + QC_SPILL_HEAD);
-                    if (hd < tl) {
-                        // become busy BEFORE claiming, so "busy == 0" implies nobody holds work
-                        if (!cnt2) { atomicAdd(queueCtl + QC_BUSY, 1u); cnt2 = 1; }
-                        if (atomicCAS(queueCtl + QC_SPILL_HEAD, hd, hd + 1u) == hd) { res = 1; unit = (int)hd; }
-                    } else {
-                        if (cnt2) { atomicSub(queueCtl + QC_BUSY, 1u); cnt2 = 0; }
-                        if (ld_volatile_u32(queueCtl + QC_BUSY) == 0u &&
-                            ld_volatile_u32(queueCtl + QC_SPILL_HEAD) >=
-                                min(ld_volatile_u32(queueCtl + QC_SPILL_TAIL), SPILL_CAP))
-                            res = 2;
-                    }
-                }
-                res = __shfl_sync(FULL, res, 0);
-                unit = __shfl_sync(FULL, unit, 0);
-                counted = __shfl_sync(FULL, cnt2, 0) != 0;
-                if (res != 0) break;
-                if (!counted) __nanosleep(200);
-            }
-            if (res == 2) break;
-            // wait until the unit has been published, then read it through L2
-            if (lane == 0) {
-                while (ld_volatile_u32(spillReady + unit) == 0u) __nanosleep(40);
-                __threadfence();
-            }
-            __syncwarp();
-            const SpillUnit *su = spill + unit;
-            base = __ldcg(&su->base);
-            nsize = (int)__ldcg(&su->count);
-            for (int i = lane; i < nsize; i += 32) {
-                sm.nref[i] = __ldcg(&su->ref[i]);
-                sm.nslot[i] = __ldcg(&su->slot[i]);
+                const unsigned c = atomicAdd(queueCtl + QC_PACKET, 1u);
+                if (c < nHeavyIn) { pk = __ldg(heavyIn + c); break; }
+                pk = c - nHeavyIn;
+                if (pk >= nPackets) { pk = 0xffffffffu; break; }
+                if (nHeavyIn == 0 || !((__ldg(heavyFlagIn + (pk >> 5)) >> (pk & 31u)) & 1u)) break;
             }
         }
+        pk = __shfl_sync(FULL, pk, 0);
+        if (pk == 0xffffffffu) break;
+        const unsigned base = pk * WQ_P;
         const unsigned np = min((unsigned)WQ_P, n - base);
+        unsigned steps = 0;
 
-        // ================= packet setup: lane s < np prepares ray base+s
+        // ---- packet setup: lane s < np prepares ray base+s and pushes the root for it
         bool live = false;
         if (lane < np) {
             const float4 o = __ldg(A.ro + base + lane);
@@ -324,152 +285,91 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
             rayf_store(sm.ray[lane], r);
             live = t.n > 0 && r.tMax > 0.f;
         }
-        bool rootLeaf = false;
-        if (unit < 0) {       // fresh packet: push the root for every live ray
+        int nsize = 0;
+        bool e0 = false, e1 = false;   // leaf children to emit this step
+        int c0 = 0, c1 = 0, slot = (int)lane;
+        {
             const unsigned mlive = __ballot_sync(FULL, live);
             if (t.root_ref >= 0) {
                 if (live) { int pos = __popc(mlive & lt); sm.nref[pos] = t.root_ref; sm.nslot[pos] = (unsigned char)lane; }
                 nsize = __popc(mlive);
-            } else {
-                rootLeaf = live;   // the whole tree is one leaf
+            } else {            // the whole tree is one leaf
+                e0 = live; c0 = t.root_ref;
             }
         }
         __syncwarp();
 
         for (;;) {
-            // ---- node step: up to two 64-byte two-child nodes per lane.  Popping k entries can
-            // push at most 2k, so k <= room keeps the stack inside WQ_NCAP-64; with no room left
-            // the walk degrades to depth-first (k = 1), which needs at most tree-depth more.
-            bool e[4] = {rootLeaf, false, false, false};    // leaf children to emit
-            int c[4] = {t.root_ref, 0, 0, 0};
-            int slot[2] = {(int)lane, 0};
-            bool push[4] = {false, false, false, false};
-            const bool haveNodes = nsize > 0;
-            if (haveNodes) {
-                const int room = WQ_NCAP - 64 - nsize;
-                const int k = room >= 1 ? min(min(64, nsize), room) : 1;
-                bool act[2];
-                int ref[2] = {0, 0};
-#pragma unroll
-                for (int u = 0; u < 2; ++u) {
-                    act[u] = (int)lane + 32 * u < k;
-                    if (act[u]) {
-                        const int idx = nsize - 1 - (int)lane - 32 * u;
-                        ref[u] = sm.nref[idx];
-                        slot[u] = sm.nslot[idx];
-                    }
-                }
-                nsize -= k;
-                float4 na[2], nb[2], nc[2];
-                int4 nd[2];
-#pragma unroll
-                for (int u = 0; u < 2; ++u)
-                    if (act[u]) {
-                        const FastNode *fn = t.fast + ref[u];
-                        na[u] = __ldg(&fn->a); nb[u] = __ldg(&fn->b); nc[u] = __ldg(&fn->c);
-                        nd[u] = __ldg(&fn->d);
-                    }
-#pragma unroll
-                for (int u = 0; u < 2; ++u)
-                    if (act[u]) {
-                        const RayF r = rayf_load(sm.ray[slot[u]]);
-                        const bool h0 = slab_hit_f(r, na[u].x, na[u].y, na[u].z, na[u].w, nb[u].x, nb[u].y);
-                        const bool h1 = slab_hit_f(r, nb[u].z, nb[u].w, nc[u].x, nc[u].y, nc[u].z, nc[u].w);
-                        c[2 * u] = nd[u].x; c[2 * u + 1] = nd[u].y;
-                        push[2 * u] = h0 && nd[u].x >= 0; push[2 * u + 1] = h1 && nd[u].y >= 0;
-                        e[2 * u] = h0 && nd[u].x < 0; e[2 * u + 1] = h1 && nd[u].y < 0;
-                        if (COUNT) ++cNodes;
-                    }
-                __syncwarp();   // all pops are done before anyone pushes
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const unsigned m = __ballot_sync(FULL, push[j]);
-                    if (push[j]) {
-                        const int p = nsize + __popc(m & lt);
-                        sm.nref[p] = c[j];
-                        sm.nslot[p] = (unsigned char)slot[j >> 1];
-                    }
-                    nsize += __popc(m);
-                }
-                __syncwarp();
-            }
-            rootLeaf = false;
             // ---- emit surviving leaves as (ray, leaf) pairs
-            unsigned me[4], nl = 0;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) { me[j] = __ballot_sync(FULL, e[j]); nl += __popc(me[j]); }
+            const unsigned ml0 = __ballot_sync(FULL, e0), ml1 = __ballot_sync(FULL, e1);
+            const unsigned nl = __popc(ml0) + __popc(ml1);
             if (nl) {
                 if (chunkPos + nl > chunkEnd) {
                     // pad what is left of the old chunk, reserve a new one
                     for (unsigned p = chunkPos + lane; p < chunkEnd; p += 32)
                         if (p < queueCap) queue[p] = make_uint2(PAIR_NONE, 0u);
-                    unsigned nb2 = 0;
-                    if (lane == 0) nb2 = atomicAdd(queueCtl + QC_PAIR_TAIL, WQ_CHUNK);
-                    chunkPos = __shfl_sync(FULL, nb2, 0);
+                    unsigned nb = 0;
+                    if (lane == 0) nb = atomicAdd(queueCtl + QC_PAIR_TAIL, WQ_CHUNK);
+                    chunkPos = __shfl_sync(FULL, nb, 0);
                     chunkEnd = chunkPos + WQ_CHUNK;
                 }
-                unsigned off = chunkPos;
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    if (e[j]) {
-                        const unsigned p = off + __popc(me[j] & lt);
-                        const unsigned q = base + (unsigned)slot[j >> 1];
-                        if (p < queueCap) queue[p] = make_uint2(q, (unsigned)c[j]);
-                        else { process_pair_inplace<MODE>(A, q, c[j]); ++nInplace; }
-                        if (COUNT) ++nEmitted;
-                    }
-                    off += __popc(me[j]);
-                }
+                const unsigned p0 = chunkPos + __popc(ml0 & lt);
+                const unsigned p1 = chunkPos + __popc(ml0) + __popc(ml1 & lt);
                 chunkPos += nl;
+                if (e0) {
+                    if (p0 < queueCap) queue[p0] = make_uint2(base + slot, (unsigned)c0);
+                    else { process_pair_inplace<MODE>(Ag, base + slot, c0); ++nInplace; }
+                }
+                if (e1) {
+                    if (p1 < queueCap) queue[p1] = make_uint2(base + slot, (unsigned)c1);
+                    else { process_pair_inplace<MODE>(Ag, base + slot, c1); ++nInplace; }
+                }
+                if (COUNT) nEmitted += (e0 ? 1u : 0u) + (e1 ? 1u : 0u);
             }
             if (nsize == 0) break;
-            // ---- load balance: hand the bottom of a deep stack to idle warps
-            if (nsize >= SPILL_HI && !spillOff) {
-                if ((pollCtr++ & 7u) == 0u) {
-                    unsigned waiting = 0;
-                    if (lane == 0) {
-                        const unsigned busy = ld_volatile_u32(queueCtl + QC_BUSY);
-                        const unsigned gone = ld_volatile_u32(queueCtl + QC_EXITED);
-                        const unsigned pk = ld_volatile_u32(queueCtl + QC_PACKET);
-                        waiting = (pk >= n && busy + gone < totalWarps) ? 1u : 0u;
-                    }
-                    idleSeen = __shfl_sync(FULL, waiting, 0) != 0u;
-                }
-                if (idleSeen) {
-                    unsigned u = 0;
-                    if (lane == 0) u = atomicAdd(queueCtl + QC_SPILL_TAIL, 1u);
-                    u = __shfl_sync(FULL, u, 0);
-                    if (u < SPILL_CAP) {
-                        SpillUnit *su = spill + u;
-                        for (int i = lane; i < SPILL_N; i += 32) {
-                            su->ref[i] = sm.nref[i];
-                            su->slot[i] = sm.nslot[i];
-                        }
-                        if (lane == 0) { su->base = base; su->count = SPILL_N; }
-                        __threadfence();
-                        __syncwarp();
-                        if (lane == 0) atomicExch(spillReady + u, 1u);
-                        const int rem = nsize - SPILL_N;
-                        for (int i0 = 0; i0 < rem; i0 += 32) {
-                            const int i = i0 + (int)lane;
-                            int rr = 0; unsigned char ss = 0;
-                            if (i < rem) { rr = sm.nref[i + SPILL_N]; ss = sm.nslot[i + SPILL_N]; }
-                            __syncwarp();
-                            if (i < rem) { sm.nref[i] = rr; sm.nslot[i] = ss; }
-                            __syncwarp();
-                        }
-                        nsize = rem;
-                    } else {
-                        spillOff = true;    // continuation queue exhausted for this launch
-                    }
-                }
+            // ---- node step: one 64-byte two-child node per lane.  Popping k entries can push
+            // at most 2k, so k <= room keeps the stack inside WQ_NCAP-64; with no room left the
+            // walk degrades to depth-first (k = 1), which needs at most tree-depth (< 64) more.
+            const int room = WQ_NCAP - 64 - nsize;
+            const int k = room >= 1 ? min(min(32, nsize), room) : 1;
+            const bool act = (int)lane < k;
+            int ref = 0;
+            if (act) { ref = sm.nref[nsize - 1 - lane]; slot = sm.nslot[nsize - 1 - lane]; }
+            nsize -= k;
+            ++steps;
+            bool h0 = false, h1 = false;
+            if (act) {
+                const FastNode *fn = t.fast + ref;
+                const float4 a = __ldg(&fn->a), b = __ldg(&fn->b), c = __ldg(&fn->c);
+                const int4 d = __ldg(&fn->d);
+                const RayF r = rayf_load(sm.ray[slot]);
+                h0 = slab_hit_f(r, a.x, a.y, a.z, a.w, b.x, b.y);
+                h1 = slab_hit_f(r, b.z, b.w, c.x, c.y, c.z, c.w);
+                c0 = d.x; c1 = d.y;
+                if (COUNT) ++cNodes;
+            }
+            __syncwarp();   // all pops are done before anyone pushes
+            const bool n0 = h0 && c0 >= 0, n1 = h1 && c1 >= 0;
+            e0 = h0 && c0 < 0; e1 = h1 && c1 < 0;
+            const unsigned mn0 = __ballot_sync(FULL, n0), mn1 = __ballot_sync(FULL, n1);
+            if (n0) { int p = nsize + __popc(mn0 & lt); sm.nref[p] = c0; sm.nslot[p] = (unsigned char)slot; }
+            if (n1) { int p = nsize + __popc(mn0) + __popc(mn1 & lt); sm.nref[p] = c1; sm.nslot[p] = (unsigned char)slot; }
+            nsize += __popc(mn0) + __popc(mn1);
+            __syncwarp();
+        }
+        // ---- remember heavy packets for the next launch
+        if (steps >= HEAVY_STEPS && lane == 0) {
+            const unsigned pos = heavyCap ? atomicAdd(nHeavyOut, 1u) : 0u;
+            if (pos < heavyCap) {
+                heavyOut[pos] = pk;
+                atomicOr(heavyFlagOut + (pk >> 5), 1u << (pk & 31u));
             }
         }
     }
     // pad the unused tail of this warp's last chunk
     for (unsigned p = chunkPos + lane; p < chunkEnd; p += 32)
         if (p < queueCap) queue[p] = make_uint2(PAIR_NONE, 0u);
-    if (lane == 0) atomicAdd(queueCtl + QC_EXITED, 1u);
+    if (nInplace) atomicAdd(queueCtl + QC_INPLACE, nInplace);
     if (COUNT) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -481,9 +381,6 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
             atomicAdd(queueCtl + QC_EMITTED, nEmitted);
         }
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) nInplace += __shfl_xor_sync(FULL, nInplace, o);
-    if (lane == 0 && nInplace) atomicAdd(queueCtl + QC_INPLACE, nInplace);
 }
 
 // ---------------------------------------------------------------- K5b
@@ -496,7 +393,7 @@ struct __align__(16) HitBuf {
 
 // LW lanes per pair (LW >= photons per leaf), G = 32/LW pairs per group, U groups in flight.
 template <int MODE, bool COUNT, int LW>
-__global__ void __launch_bounds__(LP_WARPS * 32) k_leaf_pairs(LeafArgs A,
+__global__ void __launch_bounds__(LP_WARPS * 32, 4) k_leaf_pairs(LeafArgs A,
                                                               const uint2 *__restrict__ queue,
                                                               unsigned int queueCap,
                                                               const unsigned int *__restrict__ queueCtl,
@@ -504,7 +401,9 @@ __global__ void __launch_bounds__(LP_WARPS * 32) k_leaf_pairs(LeafArgs A,
     __shared__ HitBuf bufAll[LP_WARPS];
     HitBuf &hb = bufAll[threadIdx.x >> 5];
     constexpr unsigned G = 32 / LW;
-    constexpr int U = 4;
+    constexpr int U = 4;             // pair groups whose photon loads are in flight together
+    constexpr bool SEG = true;       // segmented reduction before the atomics
+    constexpr bool RAYPF = false;    // rays are L1 hits (consecutive pairs share them): load at use
     const unsigned FULL = 0xffffffffu;
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt = (1u << lane) - 1u;
@@ -537,8 +436,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32) k_leaf_pairs(LeafArgs A,
                 on[u] = qx != PAIR_NONE && j < cnt;
                 if (on[u]) {
                     p[u] = __ldg(A.t.s_pos_r + first[u] + j);
-                    o[u] = __ldg(A.ro + qx);
-                    d[u] = __ldg(A.rd + qx);
+                    if (RAYPF) { o[u] = __ldg(A.ro + qx); d[u] = __ldg(A.rd + qx); }
                 }
             }
             // ---- disk predicates, hit compaction
@@ -547,6 +445,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32) k_leaf_pairs(LeafArgs A,
                 bool hit = false;
                 float th = 0.f, d2 = 0.f;
                 if (on[u]) {
+                    if (!RAYPF) { o[u] = __ldg(A.ro + q[u]); d[u] = __ldg(A.rd + q[u]); }
                     RayS r;
                     r.ox = o[u].x; r.oy = o[u].y; r.oz = o[u].z; r.tMax = o[u].w;
                     r.dx = d[u].x; r.dy = d[u].y; r.dz = d[u].z;
@@ -567,7 +466,8 @@ __global__ void __launch_bounds__(LP_WARPS * 32) k_leaf_pairs(LeafArgs A,
                 __syncwarp();
                 if (nbuf >= 32) {   // shade the 32 newest buffered hits, one per lane
                     const unsigned e = nbuf - 32 + lane;
-                    shade_hits_warp(A, lane, 32u, hb.s[e], hb.q[e], hb.th[e], hb.d2[e]);
+                    if (SEG) shade_hits_warp(A, lane, 32u, hb.s[e], hb.q[e], hb.th[e], hb.d2[e]);
+                    else shade_hit(A, hb.s[e], hb.q[e], hb.th[e], hb.d2[e]);
                     nbuf -= 32;
                     __syncwarp();
                 }
@@ -577,7 +477,8 @@ __global__ void __launch_bounds__(LP_WARPS * 32) k_leaf_pairs(LeafArgs A,
     if (MODE == 0 && nbuf) {
         uint32_t s = 0, q = 0; float th = 0.f, d2 = 0.f;
         if (lane < nbuf) { s = hb.s[lane]; q = hb.q[lane]; th = hb.th[lane]; d2 = hb.d2[lane]; }
-        shade_hits_warp(A, lane, nbuf, s, q, th, d2);
+        if (SEG) shade_hits_warp(A, lane, nbuf, s, q, th, d2);
+        else if (lane < nbuf) shade_hit(A, s, q, th, d2);
     }
     if (COUNT) {
 #pragma unroll

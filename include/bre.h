@@ -68,7 +68,6 @@ typedef struct {
     uint64_t fast_disk_tests;  /* disk tests done by the production kernel (leaf size > 1) */
     uint64_t leaf_pairs;       /* (ray, leaf) pairs the traversal kernel produced */
     uint64_t pair_queue_overflow; /* pairs shaded in place because the pair queue was full */
-    uint64_t continuation_units;  /* deep-stack units handed to idle warps by the traversal kernel */
 } bre_counters;
 
 typedef struct {
