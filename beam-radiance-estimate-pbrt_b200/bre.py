@@ -23,7 +23,7 @@ SYMBOLS = [
     "bre_upload_photons", "bre_clear_photons", "bre_photon_count", "bre_download_photons",
     "bre_set_radius", "bre_allgather_photons", "bre_build", "bre_download_tree", "bre_query",
     "bre_query_d", "bre_count", "bre_count_d", "bre_get_counters", "bre_film_create",
-    "bre_film_clear", "bre_film_accumulate", "bre_film_accumulate_d", "bre_film_resolve",
+    "bre_film_clear", "bre_film_accumulate", "bre_film_accumulate_d", "bre_film_resolve", "bre_film_mean",
     "bre_query_to_film", "bre_set_timing", "bre_get_timings", "bre_shard_range", "bre_tile_owner",
 ]
 
@@ -280,6 +280,11 @@ class Bre:
     def film_resolve(self, it, scale=1.0):
         out = np.zeros((self._npix, 3), np.float32)
         self._ck(self.lib.bre_film_resolve(self.ctx, it, C.c_float(scale), _fp(out)))
+        return out
+
+    def film_mean(self, it):
+        out = np.zeros((self._npix, 3), np.float32)
+        self._ck(self.lib.bre_film_mean(self.ctx, it, _fp(out)))
         return out
 
 

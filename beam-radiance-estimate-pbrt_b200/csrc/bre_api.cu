@@ -500,7 +500,12 @@ int bre_film_accumulate_d(bre_ctx *ctx, uint32_t n, const uint32_t *pix_d, const
 int bre_film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out) {
     CTX_CHECK();
     if (!rgb_out || iter < 0) return set_err(ctx, BRE_ERR_INVALID, "bad resolve arguments");
-    return film_resolve(ctx, iter, scale, rgb_out);
+    return film_resolve(ctx, iter, scale, rgb_out, 0);
+}
+int bre_film_mean(bre_ctx *ctx, int iter, float *rgb_out) {
+    CTX_CHECK();
+    if (!rgb_out || iter < 0) return set_err(ctx, BRE_ERR_INVALID, "bad resolve arguments");
+    return film_resolve(ctx, iter, 1.f, rgb_out, 1);
 }
 
 // ---------------------------------------------------------------- timing

@@ -25,12 +25,16 @@ __global__ void __launch_bounds__(256) k_film_add(float4 *__restrict__ film, uin
 }
 
 __global__ void __launch_bounds__(256) k_film_resolve(const float4 *__restrict__ film, uint32_t n,
-                                                      float inv, float scale,
+                                                      float inv, float scale, int meanOnly,
                                                       float *__restrict__ out) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float4 f = __ldg(film + i);
     float r = fmul(f.x, inv), g = fmul(f.y, inv), b = fmul(f.z, inv);
+    if (meanOnly) {   // L = Ld / (iter+1), photonbeam.cpp:578: what the host hands to Film::SetImage
+        out[3 * (size_t)i + 0] = r; out[3 * (size_t)i + 1] = g; out[3 * (size_t)i + 2] = b;
+        return;
+    }
     // RGBToXYZ spectrum.h:62-66
     float X = fadd(fadd(fmul(0.412453f, r), fmul(0.357580f, g)), fmul(0.180423f, b));
     float Y = fadd(fadd(fmul(0.212671f, r), fmul(0.715160f, g)), fmul(0.072169f, b));
@@ -58,14 +62,14 @@ int film_accumulate(bre_ctx *ctx, uint32_t n, const uint32_t *pix_d, const float
     return BRE_OK;
 }
 
-int film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out_host) {
+int film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int meanOnly) {
     if (!ctx->film.p) return set_err(ctx, BRE_ERR_INVALID, "bre_film_create has not been called");
     uint32_t n = ctx->n_pixels;
     int s;
     if ((s = ensure(ctx, ctx->out_rgb, (size_t)n * 12)) != BRE_OK) return s;
     float inv = 1.f / (float)(iter + 1);
     k_film_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, n, inv,
-                                                             scale, (float *)ctx->out_rgb.p);
+                                                             scale, meanOnly, (float *)ctx->out_rgb.p);
     BRE_CUDA(cudaGetLastError());
     BRE_CUDA(cudaMemcpyAsync(rgb_out_host, ctx->out_rgb.p, (size_t)n * 12, cudaMemcpyDeviceToHost,
                              ctx->stream));

@@ -168,7 +168,7 @@ int run_count(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd);
 int run_hitdump(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, bre_hitdump *hd);
 // film.cu
 int film_accumulate(bre_ctx *ctx, uint32_t n, const uint32_t *pix_d, const float4 *rgb_d);
-int film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out_host);
+int film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int meanOnly);
 // trace.cu
 int trace_photons(bre_ctx *ctx, uint64_t first, uint64_t nPaths, int maxDepth, float radius);
 // nccl.cpp

@@ -1,0 +1,299 @@
+// bre_integrator.cpp -- pbrt-side adapter of libbre.so (see bre_integrator.h).
+//
+// Needs read access to a few private members of the fork's media and lights (sigma_a, sigma_s, g,
+// density grid, WorldToMedium; pLight, I, cone cosines): INTEGRATION.md adds
+// `friend class BreIntegrator;` to media/homogeneous.h, media/grid.h, lights/point.h, lights/spot.h.
+#include "bre_integrator.h"
+
+#include "bre.h"   // the C ABI (include/bre.h of the B200 library)
+
+#include "film.h"
+#include "interaction.h"
+#include "lowdiscrepancy.h"
+#include "parallel.h"
+#include "lights/point.h"
+#include "lights/spot.h"
+#include "media/grid.h"
+#include "media/homogeneous.h"
+#include "memory.h"
+#include "paramset.h"
+#include "progressreporter.h"
+#include "reflection.h"
+#include "rng.h"
+#include "sampler.h"
+#include "sampling.h"
+#include "scene.h"
+#include "stats.h"
+
+namespace pbrt {
+
+namespace {
+
+// Every sample of a photon path is PCG32 of stream pathIndex+1: what the reference's
+// AwesomeHaltonSampler yields once its 1000 Halton dimensions are burnt (photonbeam.cpp:386-391).
+class PathSampler : public Sampler {
+  public:
+    explicit PathSampler(uint64_t seq) : Sampler(1), rng(seq) {}
+    Float Get1D() override { return rng.UniformFloat(); }
+    Point2f Get2D() override {
+        Float a = rng.UniformFloat();
+        Float b = rng.UniformFloat();
+        return Point2f(a, b);
+    }
+    std::unique_ptr<Sampler> Clone(int) override { return nullptr; }
+    RNG rng;
+};
+
+bool Check(bre_ctx *ctx, int status, const char *what) {
+    if (status == BRE_OK) return true;
+    Error("bre: %s failed (%d): %s", what, status, bre_last_error(ctx));
+    return false;
+}
+
+void ToRGB3(const Spectrum &s, float out[3]) {
+    Float rgb[3];
+    s.ToRGB(rgb);
+    out[0] = rgb[0]; out[1] = rgb[1]; out[2] = rgb[2];
+}
+
+}  // namespace
+
+// ---- scene -> C ABI ------------------------------------------------------------------------
+bool BreIntegrator::SetupMedium(bre_ctx *ctx, const Medium *medium) const {
+    if (const HomogeneousMedium *h = dynamic_cast<const HomogeneousMedium *>(medium)) {
+        float sa[3], ss[3];
+        ToRGB3(h->sigma_a, sa); ToRGB3(h->sigma_s, ss);
+        return Check(ctx, bre_set_medium_homogeneous(ctx, sa, ss, h->g), "bre_set_medium_homogeneous");
+    }
+    if (const GridDensityMedium *g = dynamic_cast<const GridDensityMedium *>(medium)) {
+        float sa[3], ss[3], w2m[16];
+        ToRGB3(g->sigma_a, sa); ToRGB3(g->sigma_s, ss);
+        const Matrix4x4 &m = g->WorldToMedium.GetMatrix();
+        for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) w2m[4 * i + j] = m.m[i][j];
+        return Check(ctx, bre_set_medium_grid(ctx, sa, ss, g->g, g->nx, g->ny, g->nz,
+                                              g->density.get(), w2m), "bre_set_medium_grid");
+    }
+    Error("bre: the camera must be inside a \"homogeneous\" or \"heterogeneous\" medium");
+    return false;
+}
+
+bool BreIntegrator::SetupLights(bre_ctx *ctx, const Scene &scene) const {
+    std::vector<bre_light> lights;
+    for (const std::shared_ptr<Light> &l : scene.lights) {
+        bre_light b = {};
+        if (const PointLight *p = dynamic_cast<const PointLight *>(l.get())) {
+            b.kind = 0;
+            b.pos[0] = p->pLight.x; b.pos[1] = p->pLight.y; b.pos[2] = p->pLight.z;
+            ToRGB3(p->I, b.I);
+        } else if (const SpotLight *s = dynamic_cast<const SpotLight *>(l.get())) {
+            b.kind = 1;
+            b.pos[0] = s->pLight.x; b.pos[1] = s->pLight.y; b.pos[2] = s->pLight.z;
+            ToRGB3(s->I, b.I);
+            Vector3f axis = Normalize(s->LightToWorld(Vector3f(0, 0, 1)));
+            b.axis[0] = axis.x; b.axis[1] = axis.y; b.axis[2] = axis.z;
+            b.cos_total_width = s->cosTotalWidth;
+            b.cos_falloff_start = s->cosFalloffStart;
+        } else {
+            Error("bre: the device photon tracer supports point and spot lights only "
+                  "(use \"string photontracer\" \"host\")");
+            return false;
+        }
+        lights.push_back(b);
+    }
+    return Check(ctx, bre_set_lights(ctx, (int)lights.size(), lights.data()), "bre_set_lights");
+}
+
+// ---- host photon tracer ----------------------------------------------------------------------
+// Photon paths walked by pbrt's own Scene / Medium / BSDF code; the volume photons they deposit are
+// uploaded through bre_upload_photons.  Deposit rule: Photon(mi.p, beta, -ray.d) at every medium
+// scattering event (integrators/photonmap.cpp:696-724, without its surface-cosine line :718);
+// surface bounce and Russian roulette as integrators/photonbeam.cpp:296-323.
+uint64_t BreIntegrator::TracePhotonsHost(bre_ctx *ctx, const Scene &scene,
+                                         const Distribution1D &lightDistr, uint64_t firstIndex,
+                                         uint64_t nPaths, Float radius) {
+    std::vector<float> pp, pa, pw;
+    MemoryArena arena;
+    for (uint64_t pi = firstIndex; pi < firstIndex + nPaths; ++pi) {
+        PathSampler sampler(pi + 1);
+        Float lightPdf;
+        int lightNum = lightDistr.SampleDiscrete(sampler.Get1D(), &lightPdf);
+        const std::shared_ptr<Light> &light = scene.lights[lightNum];
+        Point2f uLight0 = sampler.Get2D();
+        Point2f uLight1 = sampler.Get2D();
+        Float uLightTime = Lerp(sampler.Get1D(), camera->shutterOpen, camera->shutterClose);
+        RayDifferential ray;
+        Normal3f nLight;
+        Float pdfPos, pdfDir;
+        Spectrum Le = light->Sample_Le(uLight0, uLight1, uLightTime, &ray, &nLight, &pdfPos, &pdfDir);
+        if (pdfPos == 0 || pdfDir == 0 || Le.IsBlack()) continue;
+        Spectrum beta = (AbsDot(nLight, ray.d) * Le) / (lightPdf * pdfPos * pdfDir);
+        if (beta.IsBlack()) continue;
+        SurfaceInteraction isect;
+        for (int depth = 0; depth < maxDepth; ++depth) {
+            if (!scene.Intersect(ray, &isect)) break;
+            MediumInteraction mi;
+            if (ray.medium) beta *= ray.medium->Sample(ray, sampler, arena, &mi);
+            if (beta.IsBlack()) break;
+            if (mi.IsValid()) {
+                const Vector3f wo = -ray.d;
+                Vector3f wi;
+                mi.phase->Sample_p(wo, &wi, sampler.Get2D());
+                float a[3];
+                ToRGB3(beta, a);
+                pp.push_back(mi.p.x); pp.push_back(mi.p.y); pp.push_back(mi.p.z);
+                pa.push_back(a[0]); pa.push_back(a[1]); pa.push_back(a[2]);
+                pw.push_back(wo.x); pw.push_back(wo.y); pw.push_back(wo.z);
+                ray = mi.SpawnRay(wi);
+                if (depth + 1 >= maxDepth) break;
+                (void)sampler.Get1D();   // roulette draw with continue probability 1 (photonmap.cpp:799-804)
+                continue;
+            }
+            isect.ComputeScatteringFunctions(ray, arena, true, TransportMode::Importance);
+            if (!isect.bsdf) {           // medium boundary without a material: photonbeam.cpp:300-304
+                --depth;
+                ray = isect.SpawnRay(ray.d);
+                continue;
+            }
+            Vector3f wo = -ray.d, wi;
+            Float pdf;
+            BxDFType flags;
+            Spectrum fr = isect.bsdf->Sample_f(wo, &wi, sampler.Get2D(), &pdf, BSDF_ALL, &flags);
+            if (fr.IsBlack() || pdf == 0.f) break;
+            Spectrum betaNew = beta * fr * AbsDot(wi, isect.shading.n) / pdf;
+            ray = (RayDifferential)isect.SpawnRay(wi);
+            Float q = std::max((Float)0, 1 - betaNew.y() / beta.y());
+            if (sampler.Get1D() < q) break;
+            beta = betaNew / (1 - q);
+        }
+        arena.Reset();
+    }
+    const uint64_t n = pp.size() / 3;
+    if (n && !Check(ctx, bre_upload_photons(ctx, n, pp.data(), pa.data(), pw.data(), radius, nullptr, 1),
+                    "bre_upload_photons"))
+        return 0;
+    lastPhotons.clear();
+    lastPhotons.reserve(9 * n);
+    for (uint64_t i = 0; i < n; ++i) {
+        for (int k = 0; k < 3; ++k) lastPhotons.push_back(pp[3 * i + k]);
+        for (int k = 0; k < 3; ++k) lastPhotons.push_back(pa[3 * i + k]);
+        for (int k = 0; k < 3; ++k) lastPhotons.push_back(pw[3 * i + k]);
+    }
+    return n;
+}
+
+// ---- Render: replaces PhotonBeamIntegrator::Render (integrators/photonbeam.cpp:328-587) ---------
+void BreIntegrator::Render(const Scene &scene) {
+    ProfilePhase p(Prof::IntegratorRender);
+    const Medium *medium = camera->medium;
+    if (!medium || !renderMedia) {
+        Error("bre: nothing to render (camera outside any medium, or rendermedia false)");
+        return;
+    }
+    bre_ctx *ctx = nullptr;
+    bre_config cfg = {};
+    cfg.device = device; cfg.n_ranks = 1;
+    int st = bre_create(&ctx, &cfg);
+    if (st != BRE_OK) {
+        Error("bre: bre_create failed (%d): a CUDA device is required, there is no CPU fallback", st);
+        return;
+    }
+    if (!SetupMedium(ctx, medium)) { bre_destroy(ctx); return; }
+    std::unique_ptr<Distribution1D> lightDistr = ComputeLightPowerDistribution(scene);
+    if (!lightDistr) { Error("bre: the scene has no lights"); bre_destroy(ctx); return; }
+    if (deviceTracer) {
+        const Bounds3f wb = scene.WorldBound();
+        float lo[3] = {wb.pMin.x, wb.pMin.y, wb.pMin.z}, hi[3] = {wb.pMax.x, wb.pMax.y, wb.pMax.z};
+        if (!SetupLights(ctx, scene) || !Check(ctx, bre_set_bounds(ctx, lo, hi), "bre_set_bounds")) {
+            bre_destroy(ctx);
+            return;
+        }
+    }
+    const Bounds2i pixelBounds = camera->film->croppedPixelBounds;
+    const Vector2i ext = pixelBounds.Diagonal();
+    const uint32_t nPixels = (uint32_t)(ext.x * ext.y);
+    const uint64_t nPaths = photonsPerIteration > 0 ? (uint64_t)photonsPerIteration : nPixels;
+    std::vector<float> rayO(4 * (size_t)nPixels), rayD(3 * (size_t)nPixels), mean(3 * (size_t)nPixels);
+    std::unique_ptr<Spectrum[]> image(new Spectrum[nPixels]);
+    if (!Check(ctx, bre_film_create(ctx, nPixels), "bre_film_create")) { bre_destroy(ctx); return; }
+
+    Float radius = initialRadius;
+    ProgressReporter progress(nIterations, "Rendering (bre)");
+    for (int iter = 0; iter < nIterations; ++iter) {
+        // ---- photon pass (photonbeam.cpp:365-437): path indices iter*nPaths .. as :386-388
+        bool ok = Check(ctx, bre_clear_photons(ctx), "bre_clear_photons");
+        uint64_t stored = 0;
+        if (ok && deviceTracer)
+            ok = Check(ctx, bre_trace_photons(ctx, (uint64_t)iter * nPaths, nPaths, maxDepth, radius, &stored),
+                       "bre_trace_photons");
+        else if (ok)
+            stored = TracePhotonsHost(ctx, scene, *lightDistr, (uint64_t)iter * nPaths, nPaths, radius);
+        lastPathsEmitted = nPaths;
+        // ---- photon structure (photonbeam.cpp:438)
+        ok = ok && Check(ctx, bre_build(ctx), "bre_build");
+        // ---- camera pass (photonbeam.cpp:444-557): one query segment per pixel
+        if (ok) {
+            // iteration 0 looks through the pixel centres, later ones use a (2,3) Halton offset
+            const Point2f off = iter == 0 ? Point2f(0.5f, 0.5f)
+                                          : Point2f(RadicalInverse(0, iter), RadicalInverse(1, iter));
+            ParallelFor([&](int64_t y) {
+                for (int x = 0; x < ext.x; ++x) {
+                    const size_t q = (size_t)y * ext.x + x;
+                    CameraSample cs;
+                    cs.pFilm = Point2f(pixelBounds.pMin.x + x + off.x, pixelBounds.pMin.y + y + off.y);
+                    cs.pLens = Point2f(0.5f, 0.5f);
+                    cs.time = camera->shutterOpen;
+                    RayDifferential ray;
+                    Float w = camera->GenerateRayDifferential(cs, &ray);
+                    SurfaceInteraction isect;
+                    scene.Intersect(ray, &isect);          // shortens ray.tMax (photonbeam.cpp:481)
+                    const Float len = ray.d.Length();
+                    const Vector3f d = ray.d / len;
+                    rayO[4 * q + 0] = ray.o.x; rayO[4 * q + 1] = ray.o.y; rayO[4 * q + 2] = ray.o.z;
+                    rayO[4 * q + 3] = (w > 0 && ray.medium) ? std::min(ray.tMax * len, MaxFloat) : 0.f;
+                    rayD[3 * q + 0] = d.x; rayD[3 * q + 1] = d.y; rayD[3 * q + 2] = d.z;
+                }
+            }, ext.y, 4);
+            ok = Check(ctx, bre_query_to_film(ctx, nPixels, rayO.data(), rayD.data(), nullptr, (float)nPaths),
+                       "bre_query_to_film");
+        }
+        if (!ok) break;
+        // ---- progressive radius (photonbeam.cpp:562)
+        radius *= (iter + alpha) / (iter + 1);
+        // ---- film (photonbeam.cpp:565-584)
+        if (iter + 1 == nIterations || ((iter + 1) % writeFrequency) == 0) {
+            if (!Check(ctx, bre_film_mean(ctx, iter, mean.data()), "bre_film_mean")) break;
+            for (uint32_t i = 0; i < nPixels; ++i) {
+                Float rgb[3] = {mean[3 * i], mean[3 * i + 1], mean[3 * i + 2]};
+                image[i] = Spectrum::FromRGB(rgb);
+            }
+            camera->film->SetImage(image.get());
+            camera->film->WriteImage();
+        }
+        progress.Update();
+        (void)stored;
+    }
+    progress.Done();
+    bre_destroy(ctx);
+}
+
+Integrator *CreateBreIntegrator(const ParamSet &params, std::shared_ptr<const Camera> camera) {
+    int nIterations = params.FindOneInt("iterations", params.FindOneInt("numiterations", 64));
+    int maxDepth = params.FindOneInt("maxdepth", params.FindOneInt("maxphotondepth", 5));
+    int photonsPerIter = params.FindOneInt("photonsperiteration", params.FindOneInt("volumephotons", -1));
+    int writeFreq = params.FindOneInt("imagewritefrequency", 1 << 31);
+    Float radius = params.FindOneFloat("initialbeamradius",
+                                       params.FindOneFloat("radius", params.FindOneFloat("maxdist", 1.f)));
+    Float alpha = params.FindOneFloat("alpha", 0.5f);
+    if (PbrtOptions.quickRender) nIterations = std::max(1, nIterations / 16);
+    bool renderMedia = params.FindOneBool("rendermedia", true);
+    std::string tracer = params.FindOneString("photontracer", "host");
+    int device = params.FindOneInt("device", 0);
+    if (tracer != "host" && tracer != "device") {
+        Error("bre: unknown photontracer \"%s\"", tracer.c_str());
+        return nullptr;
+    }
+    return new BreIntegrator(camera, nIterations, photonsPerIter, maxDepth, radius, alpha,
+                             std::max(1, writeFreq), renderMedia, tracer == "device", device);
+}
+
+}  // namespace pbrt

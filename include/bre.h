@@ -173,6 +173,9 @@ int bre_film_accumulate(bre_ctx *ctx, uint32_t n_rays, const uint32_t *pixel_idx
 int bre_film_accumulate_d(bre_ctx *ctx, uint32_t n_rays, const uint32_t *pixel_idx_d, const void *rgb_d);
 /* rgb_out: n_pixels*3 floats = what Film::WriteImage hands to pbrt::WriteImage. */
 int bre_film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out);
+/* rgb_out: n_pixels*3 floats = L = Ld/(iter+1) (integrators/photonbeam.cpp:578), no colour conversion:
+ * the array a pbrt host passes to Film::SetImage (core/film.cpp:132-140) before Film::WriteImage. */
+int bre_film_mean(bre_ctx *ctx, int iter, float *rgb_out);
 /* Multi-GPU: after resolve on every rank, gather disjoint pixel ranges to rank 0. */
 
 /* ---- device timing ------------------------------------------------------------------
