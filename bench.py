@@ -331,10 +331,14 @@ def ctx_leaf(args):
 
 
 def launches_per_step(world):
-    # trace: k_trace, k_scan_reduce, k_scan_tiles, k_scan_apply, k_compact (x chunks, >= 1)
-    # build: bounds_init, bounds, morton, 4 x (hist, scan, scatter), gather, karras, refit, emit_fast
-    # query: tau_table, query ; film: film_add
-    return 5 + 3 + 12 + 4 + 2 + 1
+    """Kernels of libbre.so launched per step (profiles/r01_launches_*.csv lists them):
+    trace: k_trace, k_scan_reduce, k_scan_tiles, k_scan_apply, k_compact (one chunk of <= 4M paths)   5
+    build: k_bounds_init, k_bounds, k_morton, 4 x (k_rs_hist, 3 scan launches, k_rs_scatter),
+           k_gather, k_karras, k_refit, k_emit_fast                                                   27
+    query: k_tau_table, k_store_args, k_traverse, k_leaf_pairs                                        4
+    film:  k_film_add                                                                                 1
+    (NCCL's own kernels at N > 1 are not counted.)"""
+    return 5 + 27 + 4 + 1
 
 
 def cpu_baseline_port(ctx, wl, ro_h, rd_h, n_paths, seconds):
@@ -437,7 +441,7 @@ def main():
     ap.add_argument("--leaf", type=int, default=0)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
-    ap.add_argument("--ref-rays", type=int, default=8192)
+    ap.add_argument("--ref-rays", type=int, default=65536)
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
