@@ -826,3 +826,323 @@ void orc_synth_rays_incoherent(uint32_t n, float *o_tmax, float *dirs) {
         o_tmax[4 * (size_t)q + 3] = tMax;
     }
 }
+
+/* ===================================================================================
+ * Surfaces: triangle intersector, Lambertian bounce, camera rays.
+ * Restates, in float32 with the reference's operation order:
+ *   Triangle::Intersect            shapes/triangle.cpp:177-392 (watertight test, hit point, error bounds)
+ *   OffsetRayOrigin / SpawnRay     core/geometry.h:1438-1458, core/interaction.h:64-67
+ *   GeometricPrimitive::Intersect  core/primitive.cpp:97-109 (medium interface of the hit)
+ *   MatteMaterial (sigma == 0)     materials/matte.cpp:55-60 -> LambertianReflection
+ *   BSDF::Sample_f / BxDF::Sample_f core/reflection.cpp:703-760, :378-389
+ *   ConcentricSampleDisk / CosineSampleHemisphere  core/sampling.cpp:113-130, sampling.h:159-163
+ *   PerspectiveCamera::GenerateRayDifferential     cameras/perspective.cpp:95-103,
+ *   Transform::operator()(Ray)     core/transform.h:251-264 (+ :278-300 error bound of the origin)
+ * =================================================================================== */
+static inline float dot3(const float a[3], const float b[3]) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+static inline void cross3(const float a[3], const float b[3], float out[3]) { /* geometry.h Cross: in double */
+    double ax = a[0], ay = a[1], az = a[2], bx = b[0], by = b[1], bz = b[2];
+    out[0] = (float)((ay * bz) - (az * by));
+    out[1] = (float)((az * bx) - (ax * bz));
+    out[2] = (float)((ax * by) - (ay * bx));
+}
+static inline void normalize3(float v[3]) { /* v / Length(): multiplies by the reciprocal */
+    float inv = 1.f / sqrtf(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+    v[0] *= inv; v[1] *= inv; v[2] *= inv;
+}
+static inline float next_up_(float x) { return nextafterf(x, INFINITY); }
+static inline float next_down_(float x) { return nextafterf(x, -INFINITY); }
+static inline float max3abs(float a, float b, float c) {
+    a = fabsf(a); b = fabsf(b); c = fabsf(c);
+    return a > b ? (a > c ? a : c) : (b > c ? b : c);
+}
+
+int orc_intersect_triangle(const float o[3], const float d[3], float tMax, const float p0[3],
+                           const float p1[3], const float p2[3], float *tHit, float bary[3]) {
+    /* translate to the ray origin, permute so that |d| is largest along z, shear (triangle.cpp:191-215) */
+    float ad[3] = {fabsf(d[0]), fabsf(d[1]), fabsf(d[2])};
+    int kz = ad[0] > ad[1] ? (ad[0] > ad[2] ? 0 : 2) : (ad[1] > ad[2] ? 1 : 2); /* MaxDimension */
+    int kx = kz + 1 == 3 ? 0 : kz + 1, ky = kx + 1 == 3 ? 0 : kx + 1;
+    float dx = d[kx], dy = d[ky], dz = d[kz];
+    float a[3] = {p0[kx] - o[kx], p0[ky] - o[ky], p0[kz] - o[kz]};
+    float b[3] = {p1[kx] - o[kx], p1[ky] - o[ky], p1[kz] - o[kz]};
+    float c[3] = {p2[kx] - o[kx], p2[ky] - o[ky], p2[kz] - o[kz]};
+    float Sx = -dx / dz, Sy = -dy / dz, Sz = 1.f / dz;
+    a[0] += Sx * a[2]; a[1] += Sy * a[2];
+    b[0] += Sx * b[2]; b[1] += Sy * b[2];
+    c[0] += Sx * c[2]; c[1] += Sy * c[2];
+    /* edge functions, double fallback on exact zeros (:218-234) */
+    float e0 = b[0] * c[1] - b[1] * c[0];
+    float e1 = c[0] * a[1] - c[1] * a[0];
+    float e2 = a[0] * b[1] - a[1] * b[0];
+    if (e0 == 0.f || e1 == 0.f || e2 == 0.f) {
+        e0 = (float)((double)c[1] * (double)b[0] - (double)c[0] * (double)b[1]);
+        e1 = (float)((double)a[1] * (double)c[0] - (double)a[0] * (double)c[1]);
+        e2 = (float)((double)b[1] * (double)a[0] - (double)b[0] * (double)a[1]);
+    }
+    if ((e0 < 0 || e1 < 0 || e2 < 0) && (e0 > 0 || e1 > 0 || e2 > 0)) return 0;
+    float det = e0 + e1 + e2;
+    if (det == 0) return 0;
+    a[2] *= Sz; b[2] *= Sz; c[2] *= Sz;
+    float tScaled = e0 * a[2] + e1 * b[2] + e2 * c[2];
+    if (det < 0 && (tScaled >= 0 || tScaled < tMax * det)) return 0;
+    else if (det > 0 && (tScaled <= 0 || tScaled > tMax * det)) return 0;
+    float invDet = 1 / det;
+    float t = tScaled * invDet;
+    /* conservative t > 0 check (:262-280) */
+    float maxZt = max3abs(a[2], b[2], c[2]);
+    float deltaZ = orc_gamma(3) * maxZt;
+    float maxXt = max3abs(a[0], b[0], c[0]);
+    float maxYt = max3abs(a[1], b[1], c[1]);
+    float deltaX = orc_gamma(5) * (maxXt + maxZt);
+    float deltaY = orc_gamma(5) * (maxYt + maxZt);
+    float deltaE = 2 * (orc_gamma(2) * maxXt * maxYt + deltaY * maxXt + deltaX * maxYt);
+    float maxE = max3abs(e0, e1, e2);
+    float deltaT = 3 * (orc_gamma(3) * maxE * maxZt + deltaE * maxZt + deltaZ * maxE) * fabsf(invDet);
+    if (t <= deltaT) return 0;
+    bary[0] = e0 * invDet; bary[1] = e1 * invDet; bary[2] = e2 * invDet;
+    *tHit = t;
+    return 1;
+}
+
+static void mesh_tri(const orc_mesh *mesh, uint32_t i, const float **p0, const float **p1, const float **p2) {
+    *p0 = mesh->P + 3 * (size_t)mesh->idx[3 * (size_t)i];
+    *p1 = mesh->P + 3 * (size_t)mesh->idx[3 * (size_t)i + 1];
+    *p2 = mesh->P + 3 * (size_t)mesh->idx[3 * (size_t)i + 2];
+}
+
+int orc_mesh_intersect(const orc_mesh *mesh, const float o[3], const float d[3], float tMax,
+                       orc_surface_hit *hit) {
+    /* Scene::Intersect (core/scene.cpp:50-54): closest hit; every primitive is tested against the
+     * ray's CURRENT tMax (core/primitive.cpp:97-101), here in index order instead of BVH order. */
+    int found = -1;
+    float bestB[3] = {0, 0, 0};
+    for (uint32_t i = 0; i < mesh->n_tri; ++i) {
+        const float *p0, *p1, *p2;
+        float t, b[3];
+        mesh_tri(mesh, i, &p0, &p1, &p2);
+        if (orc_intersect_triangle(o, d, tMax, p0, p1, p2, &t, b)) {
+            tMax = t; found = (int)i; memcpy(bestB, b, 12);
+        }
+    }
+    if (found < 0) return 0;
+    if (!hit) return 1;
+    const float *p0, *p1, *p2;
+    mesh_tri(mesh, (uint32_t)found, &p0, &p1, &p2);
+    hit->t = tMax;
+    hit->tri = (uint32_t)found;
+    for (int k = 0; k < 3; ++k) {
+        /* pHit = b0*p0 + b1*p1 + b2*p2, pError = gamma(7) * sum |b_i p_i| (:302-311) */
+        hit->p[k] = bestB[0] * p0[k] + bestB[1] * p1[k] + bestB[2] * p2[k];
+        hit->pError[k] = orc_gamma(7) * (fabsf(bestB[0] * p0[k]) + fabsf(bestB[1] * p1[k]) + fabsf(bestB[2] * p2[k]));
+    }
+    float dp02[3], dp12[3], dpdu[3];
+    for (int k = 0; k < 3; ++k) { dp02[k] = p0[k] - p2[k]; dp12[k] = p1[k] - p2[k]; }
+    /* default uv (0,0),(1,0),(1,1): dpdu = (duv12[1]*dp02 - duv02[1]*dp12) * 1 = -dp02 + dp12 (:288-295) */
+    for (int k = 0; k < 3; ++k) dpdu[k] = (-1.f * dp02[k] - -1.f * dp12[k]) * 1.f;
+    cross3(dp02, dp12, hit->n);
+    normalize3(hit->n); /* :328 */
+    uint8_t attr = mesh->attr ? mesh->attr[found] : 0;
+    if (attr & ORC_TRI_FLIP_NORMAL) for (int k = 0; k < 3; ++k) hit->n[k] = -hit->n[k]; /* :387-388 */
+    memcpy(hit->ss, dpdu, 12);
+    normalize3(hit->ss); /* BSDF::ss = Normalize(shading.dpdu), reflection.h BSDF ctor */
+    return 1;
+}
+
+void orc_offset_ray_origin(const float p[3], const float pError[3], const float n[3], const float w[3],
+                           float out[3]) {
+    /* geometry.h:1438-1458 */
+    float dd = fabsf(n[0]) * pError[0] + fabsf(n[1]) * pError[1] + fabsf(n[2]) * pError[2];
+    float off[3] = {dd * n[0], dd * n[1], dd * n[2]};
+    if (dot3(w, n) < 0) for (int k = 0; k < 3; ++k) off[k] = -off[k];
+    for (int k = 0; k < 3; ++k) {
+        float po = p[k] + off[k];
+        if (off[k] > 0) po = next_up_(po);
+        else if (off[k] < 0) po = next_down_(po);
+        out[k] = po;
+    }
+}
+
+/* medium state of a ray leaving triangle `attr` towards w: Interaction::GetMedium (interaction.h:86-88)
+ * over the interface chosen by GeometricPrimitive::Intersect (primitive.cpp:104-109) */
+static int medium_after(uint8_t attr, const float w[3], const float n[3], int current) {
+    int side = attr & 3;
+    if (side == ORC_TRI_MEDIUM_INHERIT) return current;
+    int outside = dot3(w, n) > 0;
+    return side == ORC_TRI_MEDIUM_OUTSIDE ? outside : !outside;
+}
+
+void orc_concentric_sample_disk(float u0, float u1, float out[2]) { /* sampling.cpp:113-130 */
+    float ux = 2.f * u0 - 1, uy = 2.f * u1 - 1;
+    if (ux == 0 && uy == 0) { out[0] = out[1] = 0; return; }
+    float theta, r;
+    if (fabsf(ux) > fabsf(uy)) { r = ux; theta = (ORC_PI / 4) * (uy / ux); }
+    else { r = uy; theta = (ORC_PI / 2) - (ORC_PI / 4) * (ux / uy); }
+    out[0] = r * cosf(theta); out[1] = r * sinf(theta);
+}
+
+/* BSDF::Sample_f for a single LambertianReflection lobe of reflectance R (reflection.cpp:703-760).
+ * Returns 0 when the sample carries nothing (f black or pdf 0); else fills wi (world), f, pdf. */
+int orc_lambert_sample(const orc_surface_hit *h, const float R[3], const float woW[3], float u0,
+                       float u1, float wiW[3], float f[3], float *pdf) {
+    if (R[0] == 0 && R[1] == 0 && R[2] == 0) return 0; /* matte.cpp:57: no lobe added */
+    const float *ns = h->n, *ss = h->ss;
+    float ts[3];
+    cross3(ns, ss, ts);
+    float wo[3] = {dot3(woW, ss), dot3(woW, ts), dot3(woW, ns)};
+    if (wo[2] == 0) return 0;
+    float dsk[2];
+    orc_concentric_sample_disk(fminf_(u0 * 1 - 0, ORC_ONE_MINUS_EPS), u1, dsk);
+    float z = sqrtf(fmaxf_(0.f, 1 - dsk[0] * dsk[0] - dsk[1] * dsk[1]));
+    float wi[3] = {dsk[0], dsk[1], z};
+    if (wo[2] < 0) wi[2] *= -1;
+    *pdf = (wo[2] * wi[2] > 0) ? fabsf(wi[2]) * ORC_INV_PI : 0;
+    if (*pdf == 0) return 0;
+    for (int k = 0; k < 3; ++k) wiW[k] = ss[k] * wi[0] + ts[k] * wi[1] + ns[k] * wi[2];
+    /* one matching lobe: the geometric-normal reflect/transmit filter of :756-765 is skipped */
+    for (int c = 0; c < 3; ++c) f[c] = R[c] * ORC_INV_PI;
+    return 1;
+}
+
+uint64_t orc_trace_photons_mesh(const orc_medium *m, const orc_light *lights, int nLights,
+                                const orc_mesh *mesh, int lightsInMedium, uint64_t first,
+                                uint64_t nPaths, int maxDepth, float *pos, float *power, float *dir,
+                                uint32_t *path_id, uint64_t cap) {
+    /* Path loop of TracePhotonBeamRecursive (integrators/photonbeam.cpp:258-325) unrolled into the
+     * iteration of the pbrt-side adapter's host tracer, with the volume-photon deposit rule of
+     * photonmap.cpp:696-724: emission as orc_trace_photons; then per segment Scene::Intersect,
+     * Medium::Sample, deposit + phase scatter, or surface bounce + Russian roulette (:296-323). */
+    float cdf[65];
+    if (nLights > 64) nLights = 64;
+    cdf[0] = 0;
+    for (int i = 0; i < nLights; ++i) cdf[i + 1] = cdf[i] + light_power_y(&lights[i]) / nLights;
+    float funcInt = cdf[nLights];
+    if (funcInt == 0) for (int i = 1; i <= nLights; ++i) cdf[i] = (float)i / (float)nLights;
+    else for (int i = 1; i <= nLights; ++i) cdf[i] /= funcInt;
+    uint64_t stored = 0;
+    for (uint64_t pi = first; pi < first + nPaths; ++pi) {
+        orc_rng rng;
+        orc_rng_seed(&rng, pi + 1);
+        float uPick = orc_rng_float(&rng);
+        int li = 0;
+        for (int i = 0; i < nLights; ++i) if (cdf[i] <= uPick) li = i;
+        float func = light_power_y(&lights[li]);
+        float lightPdf = funcInt > 0 ? func / (funcInt * nLights) : 1.f / nLights;
+        float u0 = orc_rng_float(&rng), u1 = orc_rng_float(&rng);
+        (void)orc_rng_float(&rng); (void)orc_rng_float(&rng);
+        (void)orc_rng_float(&rng);
+        const orc_light *L = &lights[li];
+        float o[3] = {L->pos[0], L->pos[1], L->pos[2]}, d[3], Le[3], pdfDir;
+        if (L->kind == 0) {
+            orc_uniform_sample_sphere(u0, u1, d);
+            pdfDir = ORC_INV4PI;
+            for (int c = 0; c < 3; ++c) Le[c] = L->I[c];
+        } else {
+            float w[3], ax[3], ay[3];
+            orc_uniform_sample_cone(u0, u1, L->cosTotalWidth, w);
+            coordinate_system(L->axis, ax, ay);
+            for (int k = 0; k < 3; ++k) d[k] = w[0] * ax[k] + w[1] * ay[k] + w[2] * L->axis[k];
+            pdfDir = 1 / (2 * ORC_PI * (1 - L->cosTotalWidth));
+            float f = spot_falloff(L, d);
+            for (int c = 0; c < 3; ++c) Le[c] = L->I[c] * f;
+        }
+        if (pdfDir == 0 || is_black(Le)) continue;
+        float nd = fabsf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+        float beta[3];
+        float denom = lightPdf * 1.f * pdfDir;
+        for (int c = 0; c < 3; ++c) beta[c] = (nd * Le[c]) / denom;
+        if (is_black(beta)) continue;
+        int inMedium = lightsInMedium;
+        for (int depth = 0; depth < maxDepth; ++depth) {
+            orc_surface_hit hit;
+            if (!orc_mesh_intersect(mesh, o, d, INFINITY, &hit)) break; /* escaped the scene */
+            int scattered = 0;
+            float ts = 0, w[3];
+            if (inMedium) {
+                scattered = medium_sample(m, &rng, o, d, hit.t, &ts, w);
+                for (int c = 0; c < 3; ++c) beta[c] *= w[c];
+            }
+            if (is_black(beta)) break;
+            if (scattered) {
+                float p[3] = {o[0] + d[0] * ts, o[1] + d[1] * ts, o[2] + d[2] * ts};
+                float wo[3] = {-d[0], -d[1], -d[2]}, wi[3];
+                if (stored < cap) {
+                    memcpy(pos + 3 * stored, p, 12);
+                    memcpy(power + 3 * stored, beta, 12);
+                    memcpy(dir + 3 * stored, wo, 12);
+                    if (path_id) path_id[stored] = (uint32_t)pi;
+                }
+                ++stored;
+                float ua = orc_rng_float(&rng), ub = orc_rng_float(&rng);
+                orc_hg_sample_p(wo, m->g, ua, ub, wi);
+                memcpy(o, p, 12); memcpy(d, wi, 12);
+                if (depth + 1 >= maxDepth) break;
+                (void)orc_rng_float(&rng); /* roulette draw, continue probability 1 */
+                continue;
+            }
+            uint8_t attr = mesh->attr ? mesh->attr[hit.tri] : 0;
+            const float *Kd = mesh->Kd + 3 * (size_t)hit.tri;
+            if ((attr & ORC_TRI_NO_MATERIAL) || Kd[0] < 0) { /* photonbeam.cpp:300-304 */
+                --depth;
+                float no[3];
+                orc_offset_ray_origin(hit.p, hit.pError, hit.n, d, no);
+                inMedium = medium_after(attr, d, hit.n, inMedium);
+                memcpy(o, no, 12);
+                continue;
+            }
+            float R[3], woW[3] = {-d[0], -d[1], -d[2]}, wiW[3], f[3], pdf;
+            for (int c = 0; c < 3; ++c) R[c] = Kd[c] < 0 ? 0 : (Kd[c] > INFINITY ? INFINITY : Kd[c]); /* Clamp() */
+            float ub0 = orc_rng_float(&rng), ub1 = orc_rng_float(&rng);
+            if (!orc_lambert_sample(&hit, R, woW, ub0, ub1, wiW, f, &pdf)) break;
+            float betaNew[3], absdot = fabsf(dot3(wiW, hit.n));
+            for (int c = 0; c < 3; ++c) betaNew[c] = beta[c] * f[c] * absdot / pdf;
+            float no[3];
+            orc_offset_ray_origin(hit.p, hit.pError, hit.n, wiW, no);
+            inMedium = medium_after(attr, wiW, hit.n, inMedium);
+            memcpy(o, no, 12); memcpy(d, wiW, 12);
+            float q = fmaxf_(0.f, 1 - lum_y(betaNew) / lum_y(beta));
+            if (orc_rng_float(&rng) < q) break;
+            for (int c = 0; c < 3; ++c) beta[c] = betaNew[c] / (1 - q);
+        }
+    }
+    return stored;
+}
+
+void orc_camera_rays(const float r2c[16], const float c2w[16], int x0, int y0, int w, int h,
+                     float offx, float offy, const orc_mesh *mesh, int cameraInMedium,
+                     float *o_tmax, float *dirs) {
+    /* pinhole PerspectiveCamera (lensRadius 0), one ray per pixel of [x0,x0+w) x [y0,y0+h);
+     * then what the adapter's camera pass does (integrators/photonbeam.cpp:465-481): Scene::Intersect
+     * shortens tMax, direction normalised, tMax scaled by its length; tMax = 0 outside the medium. */
+    float oErr[3];
+    for (int r = 0; r < 3; ++r) /* transform.h:288-294 for p = (0,0,0) */
+        oErr[r] = orc_gamma(3) * (fabsf(c2w[4 * r] * 0.f) + fabsf(c2w[4 * r + 1] * 0.f) + fabsf(c2w[4 * r + 2] * 0.f) + fabsf(c2w[4 * r + 3]));
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x) {
+            size_t q = (size_t)y * w + x;
+            float fx = (float)(x0 + x) + offx, fy = (float)(y0 + y) + offy, fz = 0.f;
+            float pc[3];
+            for (int r = 0; r < 3; ++r) pc[r] = r2c[4 * r] * fx + r2c[4 * r + 1] * fy + r2c[4 * r + 2] * fz + r2c[4 * r + 3];
+            float wp = r2c[12] * fx + r2c[13] * fy + r2c[14] * fz + r2c[15];
+            if (wp != 1) { float inv = 1 / wp; pc[0] *= inv; pc[1] *= inv; pc[2] *= inv; }
+            normalize3(pc);
+            float o[3], d[3];
+            for (int r = 0; r < 3; ++r) {
+                o[r] = c2w[4 * r] * 0.f + c2w[4 * r + 1] * 0.f + c2w[4 * r + 2] * 0.f + c2w[4 * r + 3];
+                d[r] = c2w[4 * r] * pc[0] + c2w[4 * r + 1] * pc[1] + c2w[4 * r + 2] * pc[2];
+            }
+            float l2 = d[0] * d[0] + d[1] * d[1] + d[2] * d[2];
+            float tMax = INFINITY;
+            if (l2 > 0) { /* transform.h:256-262 */
+                float dt = (fabsf(d[0]) * oErr[0] + fabsf(d[1]) * oErr[1] + fabsf(d[2]) * oErr[2]) / l2;
+                for (int r = 0; r < 3; ++r) o[r] += d[r] * dt;
+                tMax -= dt;
+            }
+            orc_surface_hit hit;
+            if (mesh && mesh->n_tri && orc_mesh_intersect(mesh, o, d, tMax, &hit)) tMax = hit.t;
+            float len = sqrtf(l2), inv = 1 / len;
+            o_tmax[4 * q] = o[0]; o_tmax[4 * q + 1] = o[1]; o_tmax[4 * q + 2] = o[2];
+            o_tmax[4 * q + 3] = cameraInMedium ? fminf_(tMax * len, 3.402823466e+38f) : 0.f;
+            dirs[3 * q] = d[0] * inv; dirs[3 * q + 1] = d[1] * inv; dirs[3 * q + 2] = d[2] * inv;
+        }
+}

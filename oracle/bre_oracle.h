@@ -156,6 +156,45 @@ uint64_t orc_trace_photons(const orc_medium *m, const orc_light *lights, int nLi
                            int maxDepth, float *pos, float *power, float *dir, uint32_t *path_id,
                            uint64_t cap);
 
+/* ---- surfaces: triangle intersector, Lambertian bounce, camera rays ---- */
+#define ORC_TRI_MEDIUM_INHERIT 0  /* no medium transition: the ray keeps its medium (primitive.cpp:104-109) */
+#define ORC_TRI_MEDIUM_INSIDE 1   /* MediumInterface "M" "": medium on the side opposite the normal */
+#define ORC_TRI_MEDIUM_OUTSIDE 2  /* MediumInterface "" "M": medium on the normal's side */
+#define ORC_TRI_FLIP_NORMAL 4     /* reverseOrientation ^ transformSwapsHandedness (triangle.cpp:387-388) */
+#define ORC_TRI_NO_MATERIAL 8     /* interface-only surface, photons pass through (photonbeam.cpp:300-304) */
+typedef struct {
+    uint32_t n_tri;
+    const float *P;        /* vertex positions xyz */
+    const uint32_t *idx;   /* 3 per triangle */
+    const float *Kd;       /* 3 per triangle, Lambertian reflectance; Kd[0] < 0: no material */
+    const uint8_t *attr;   /* ORC_TRI_* bits per triangle, may be NULL (all 0) */
+} orc_mesh;
+typedef struct {
+    float t;
+    uint32_t tri;
+    float p[3], pError[3];
+    float n[3];            /* geometric = shading normal, after the orientation flip */
+    float ss[3];           /* Normalize(dpdu) */
+} orc_surface_hit;
+int orc_intersect_triangle(const float o[3], const float d[3], float tMax, const float p0[3],
+                           const float p1[3], const float p2[3], float *tHit, float bary[3]);
+int orc_mesh_intersect(const orc_mesh *mesh, const float o[3], const float d[3], float tMax,
+                       orc_surface_hit *hit);
+void orc_offset_ray_origin(const float p[3], const float pError[3], const float n[3], const float w[3],
+                           float out[3]);
+void orc_concentric_sample_disk(float u0, float u1, float out[2]);
+int orc_lambert_sample(const orc_surface_hit *h, const float R[3], const float woW[3], float u0,
+                       float u1, float wiW[3], float f[3], float *pdf);
+/* As orc_trace_photons, with Scene::Intersect over a triangle mesh instead of the absorbing box. */
+uint64_t orc_trace_photons_mesh(const orc_medium *m, const orc_light *lights, int nLights,
+                                const orc_mesh *mesh, int lightsInMedium, uint64_t first,
+                                uint64_t nPaths, int maxDepth, float *pos, float *power, float *dir,
+                                uint32_t *path_id, uint64_t cap);
+/* Pinhole camera rays + first-surface tMax; o_tmax 4 floats per pixel, dirs 3 (unit length). */
+void orc_camera_rays(const float raster_to_camera[16], const float camera_to_world[16], int x0, int y0,
+                     int w, int h, float offx, float offy, const orc_mesh *mesh, int cameraInMedium,
+                     float *o_tmax, float *dirs);
+
 /* ---- synthetic workloads ---- */
 void orc_synth_photons_uniform(uint32_t n, float *pos, float *power, float *dir);
 void orc_synth_rays_pinhole(int w, int h, float *o_tmax, float *dirs);

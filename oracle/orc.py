@@ -49,6 +49,11 @@ class LightS(C.Structure):
                 ("axis", C.c_float * 3), ("cosTotalWidth", C.c_float), ("cosFalloffStart", C.c_float)]
 
 
+class MeshS(C.Structure):
+    _fields_ = [("n_tri", C.c_uint32), ("P", C.POINTER(C.c_float)), ("idx", C.POINTER(C.c_uint32)),
+                ("Kd", C.POINTER(C.c_float)), ("attr", C.POINTER(C.c_uint8))]
+
+
 def build_library():
     subprocess.check_call(["make", "-C", _HERE, "oracle"], stdout=subprocess.DEVNULL)
 
@@ -66,6 +71,7 @@ def load():
     lib.orc_morton30.restype = C.c_uint32
     lib.orc_lbvh_build.restype = C.POINTER(Lbvh)
     lib.orc_trace_photons.restype = C.c_uint64
+    lib.orc_trace_photons_mesh.restype = C.c_uint64
     return lib
 
 
@@ -180,6 +186,45 @@ class Oracle:
                                        _fp(dr), pid.ctypes.data_as(C.POINTER(C.c_uint32)), C.c_uint64(cap))
         n = min(int(n), cap)
         return pos[:n], pw[:n], dr[:n], pid[:n]
+
+    def _lights(self, lights):
+        arr = (LightS * len(lights))()
+        for i, L in enumerate(lights):
+            arr[i].kind = L.get("kind", 0)
+            arr[i].pos = (C.c_float * 3)(*L["pos"]); arr[i].I = (C.c_float * 3)(*L["I"])
+            arr[i].axis = (C.c_float * 3)(*L.get("axis", (0, 0, 1)))
+            arr[i].cosTotalWidth = L.get("cos_total_width", 0.0)
+            arr[i].cosFalloffStart = L.get("cos_falloff_start", 0.0)
+        return arr
+
+    # ---- surfaces
+    def set_mesh(self, P, idx, Kd, attr=None):
+        P, Kd = _f32(P).reshape(-1, 3), _f32(Kd).reshape(-1, 3)
+        idx = np.ascontiguousarray(idx, np.uint32).reshape(-1, 3)
+        a = np.zeros(idx.shape[0], np.uint8) if attr is None else np.ascontiguousarray(attr, np.uint8)
+        self._mesh_arrays = (P, idx, Kd, a)
+        self.mesh = MeshS(idx.shape[0], _fp(P), idx.ctypes.data_as(C.POINTER(C.c_uint32)), _fp(Kd),
+                          a.ctypes.data_as(C.POINTER(C.c_uint8)))
+
+    def trace_mesh(self, lights, first, n_paths, max_depth, lights_in_medium=True, cap=None):
+        arr = self._lights(lights)
+        cap = cap or n_paths * max_depth
+        pos = np.zeros((cap, 3), np.float32); pw = np.zeros((cap, 3), np.float32)
+        dr = np.zeros((cap, 3), np.float32); pid = np.zeros(cap, np.uint32)
+        n = self.lib.orc_trace_photons_mesh(C.byref(self.medium), arr, len(lights), C.byref(self.mesh),
+                                            int(lights_in_medium), C.c_uint64(first), C.c_uint64(n_paths),
+                                            max_depth, _fp(pos), _fp(pw), _fp(dr),
+                                            pid.ctypes.data_as(C.POINTER(C.c_uint32)), C.c_uint64(cap))
+        n = min(int(n), cap)
+        return pos[:n], pw[:n], dr[:n], pid[:n]
+
+    def camera_rays(self, r2c, c2w, x0, y0, w, h, offx, offy, use_mesh=True, camera_in_medium=True):
+        r2c, c2w = _f32(r2c).reshape(16), _f32(c2w).reshape(16)
+        o = np.zeros((w * h, 4), np.float32); d = np.zeros((w * h, 3), np.float32)
+        mesh = C.byref(self.mesh) if use_mesh else None
+        self.lib.orc_camera_rays(_fp(r2c), _fp(c2w), x0, y0, w, h, C.c_float(offx), C.c_float(offy), mesh,
+                                 int(camera_in_medium), _fp(o), _fp(d))
+        return o, d
 
     # ---- synthetic workloads
     def synth_photons_uniform(self, n):

@@ -22,6 +22,11 @@
 //        every step executed by reference classes (Light::Sample_Le, Scene::Intersect,
 //        Medium::Sample, HenyeyGreenstein::Sample_p, MediumInteraction::SpawnRay).
 //
+//   ref_harness surfaces <out.bin> <firstPath> <nPaths> <maxDepth> <resX> <resY>
+//        photon paths through a fog box with matte walls (Lambertian bounce + Russian roulette,
+//        integrators/photonbeam.cpp:296-323), a reverse-orientation wall and an interface-only
+//        medium boundary, plus camera rays of a cropped PerspectiveCamera with first-hit tMax.
+//
 // All floats are written as raw IEEE-754 bit patterns so the comparison can be bit-exact.
 #include <cstdio>
 #include <cstdlib>
@@ -580,6 +585,162 @@ void trace(const char *path, const char *kind, uint64_t first, uint64_t nPaths, 
     fprintf(stderr, "trace %s: %zu photons from %llu paths\n", kind, pid.size(), (unsigned long long)nPaths);
 }
 
+// ---------------------------------------------------------------- mode: surfaces
+// Fog box with matte walls of different reflectance, one reverse-orientation wall, and an
+// interface-only quad (no material, MediumInterface inside = fog, outside = vacuum) at x = 1.5 that
+// leaves the region x > 1.5 empty.  Photon paths are walked by REFERENCE classes with the loop of
+// integrators/photonbeam.cpp:258-325 (surface bounce, interface skip, Russian roulette) and the
+// volume-photon deposit rule of integrators/photonmap.cpp:696-724; camera rays come from the
+// reference's PerspectiveCamera + Scene::Intersect over a cropped pixel window.
+void surfaces(const char *path, uint64_t first, uint64_t nPaths, int maxDepth, int resX, int resY) {
+    const float sa[3] = {0.05f, 0.06f, 0.07f}, ss[3] = {0.4f, 0.35f, 0.3f}, g = 0.3f;
+    HomogeneousMedium fog{rgbS(sa[0], sa[1], sa[2]), rgbS(ss[0], ss[1], ss[2]), g};
+    MediumInterface inFog(&fog, &fog);
+    static Transform id;
+    const float *L = kBoxLo, *H = kBoxHi;
+    const Point3f quads[7][4] = {
+        {{L[0], L[1], L[2]}, {H[0], L[1], L[2]}, {H[0], L[1], H[2]}, {L[0], L[1], H[2]}},
+        {{L[0], H[1], L[2]}, {L[0], H[1], H[2]}, {H[0], H[1], H[2]}, {H[0], H[1], L[2]}},
+        {{L[0], L[1], H[2]}, {H[0], L[1], H[2]}, {H[0], H[1], H[2]}, {L[0], H[1], H[2]}},
+        {{L[0], L[1], L[2]}, {L[0], H[1], L[2]}, {H[0], H[1], L[2]}, {H[0], L[1], L[2]}},
+        {{L[0], L[1], L[2]}, {L[0], L[1], H[2]}, {L[0], H[1], H[2]}, {L[0], H[1], L[2]}},
+        {{H[0], L[1], L[2]}, {H[0], H[1], L[2]}, {H[0], H[1], H[2]}, {H[0], L[1], H[2]}},
+        {{1.5f, L[1], L[2]}, {1.5f, H[1], L[2]}, {1.5f, H[1], H[2]}, {1.5f, L[1], H[2]}}};   // interface
+    const float kd[7][3] = {{.6f, .6f, .6f}, {.7f, .7f, .7f}, {.2f, .5f, .8f}, {.5f, .5f, .5f},
+                            {.8f, .3f, .2f}, {.3f, .8f, .3f}, {-1.f, -1.f, -1.f}};
+    const int idx[6] = {0, 1, 2, 0, 2, 3};
+    std::vector<std::shared_ptr<Primitive>> prims;
+    std::vector<float> P, Kd;
+    std::vector<uint32_t> I, attr;
+    for (int q = 0; q < 7; ++q) {
+        const bool reverse = (q == 4);
+        const bool iface = (q == 6);
+        auto tris = CreateTriangleMesh(&id, &id, reverse, 2, idx, 4, quads[q], nullptr, nullptr,
+                                       nullptr, nullptr, nullptr);
+        std::shared_ptr<Material> mat;
+        if (!iface) {
+            std::shared_ptr<Texture<Spectrum>> t = std::make_shared<ConstantTexture<Spectrum>>(rgbS(kd[q][0], kd[q][1], kd[q][2]));
+            std::shared_ptr<Texture<Float>> sg = std::make_shared<ConstantTexture<Float>>(0.f);
+            mat = std::make_shared<MatteMaterial>(t, sg, nullptr);
+        }
+        MediumInterface mi = iface ? MediumInterface(&fog, nullptr) : inFog;
+        for (auto &t : tris) prims.push_back(std::make_shared<GeometricPrimitive>(t, mat, nullptr, mi));
+        for (int v = 0; v < 4; ++v) push3(P, quads[q][v]);
+        for (int t = 0; t < 2; ++t) {
+            for (int k = 0; k < 3; ++k) I.push_back((uint32_t)(4 * q + idx[3 * t + k]));
+            for (int c = 0; c < 3; ++c) Kd.push_back(kd[q][c]);
+            // bits as include/bre.h BRE_TRI_*: 1 = medium inside, 4 = flip normal, 8 = no material
+            attr.push_back((iface ? 1u : 0u) | (reverse ? 4u : 0u) | (iface ? 8u : 0u));
+        }
+    }
+    std::shared_ptr<BVHAccel> bvh = std::make_shared<BVHAccel>(prims);
+    std::vector<std::shared_ptr<Light>> lights;
+    lights.push_back(std::make_shared<PointLight>(Translate(Vector3f(0.f, 0.9f, 0.f)), inFog, rgbS(5.f, 4.f, 3.f)));
+    Scene scene(bvh, lights);
+    std::unique_ptr<Distribution1D> lightDistr = ComputeLightPowerDistribution(scene);
+
+    std::vector<float> pp, pa, pw;
+    std::vector<uint32_t> pid;
+    MemoryArena arena;
+    for (uint64_t pi = first; pi < first + nPaths; ++pi) {
+        StreamSampler sampler(pi + 1);
+        Float lightPdf;
+        int lightNum = lightDistr->SampleDiscrete(sampler.Get1D(), &lightPdf);
+        const std::shared_ptr<Light> &light = scene.lights[lightNum];
+        Point2f uLight0 = sampler.Get2D();
+        Point2f uLight1 = sampler.Get2D();
+        Float uLightTime = sampler.Get1D();
+        RayDifferential ray;
+        Normal3f nLight;
+        Float pdfPos, pdfDir;
+        Spectrum Le = light->Sample_Le(uLight0, uLight1, uLightTime, &ray, &nLight, &pdfPos, &pdfDir);
+        if (pdfPos == 0 || pdfDir == 0 || Le.IsBlack()) continue;
+        Spectrum beta = (AbsDot(nLight, ray.d) * Le) / (lightPdf * pdfPos * pdfDir);
+        if (beta.IsBlack()) continue;
+        SurfaceInteraction isect;
+        for (int depth = 0; depth < maxDepth; ++depth) {
+            if (!scene.Intersect(ray, &isect)) break;
+            MediumInteraction mi;
+            if (ray.medium) beta *= ray.medium->Sample(ray, sampler, arena, &mi);
+            if (beta.IsBlack()) break;
+            if (mi.IsValid()) {
+                const Vector3f wo = -ray.d;
+                Vector3f wi;
+                mi.phase->Sample_p(wo, &wi, sampler.Get2D());
+                push3(pp, mi.p); pushS(pa, beta); push3(pw, wo);
+                pid.push_back((uint32_t)pi);
+                ray = mi.SpawnRay(wi);
+                if (depth + 1 >= maxDepth) break;
+                (void)sampler.Get1D();
+                continue;
+            }
+            isect.ComputeScatteringFunctions(ray, arena, true, TransportMode::Importance);
+            if (!isect.bsdf) {                       // photonbeam.cpp:300-304
+                --depth;
+                ray = isect.SpawnRay(ray.d);
+                continue;
+            }
+            Vector3f wo = -ray.d, wi;
+            Float pdf;
+            BxDFType flags;
+            Spectrum fr = isect.bsdf->Sample_f(wo, &wi, sampler.Get2D(), &pdf, BSDF_ALL, &flags);   // :313
+            if (fr.IsBlack() || pdf == 0.f) break;
+            Spectrum betaNew = beta * fr * AbsDot(wi, isect.shading.n) / pdf;
+            ray = (RayDifferential)isect.SpawnRay(wi);
+            Float q = std::max((Float)0, 1 - betaNew.y() / beta.y());                               // :321
+            if (sampler.Get1D() < q) break;
+            beta = betaNew / (1 - q);
+        }
+        arena.Reset();
+    }
+
+    // ---- camera rays over a cropped window
+    Film *film = new Film(Point2i(resX, resY), Bounds2f(Point2f(0.125f, 0.25f), Point2f(1, 0.875f)),
+                          std::unique_ptr<Filter>(new BoxFilter(Vector2f(0.5f, 0.5f))), 35.f,
+                          "/tmp/bre_ref_surfaces.pfm", 1.f);
+    Transform c2w = Inverse(LookAt(Point3f(0.3f, 0.2f, -3.5f), Point3f(0, 0.1f, 0), Vector3f(0, 1, 0)));
+    AnimatedTransform ac2w(&c2w, 0.f, &c2w, 1.f);
+    const Float frame = (Float)resX / (Float)resY;
+    std::shared_ptr<const PerspectiveCamera> camera = std::make_shared<PerspectiveCamera>(
+        ac2w, Bounds2f(Point2f(-frame, -1), Point2f(frame, 1)), 0.f, 1.f, 0.f, 1e6f, 40.f, film, &fog);
+    const Bounds2i pb = film->croppedPixelBounds;
+    const Point2f off(0.25f, 0.625f);
+    std::vector<float> ro, rd;
+    for (int y = pb.pMin.y; y < pb.pMax.y; ++y)
+        for (int x = pb.pMin.x; x < pb.pMax.x; ++x) {
+            CameraSample cs;
+            cs.pFilm = Point2f(x + off.x, y + off.y);
+            cs.pLens = Point2f(0.5f, 0.5f);
+            cs.time = 0.f;
+            RayDifferential ray;
+            Float w = camera->GenerateRayDifferential(cs, &ray);
+            SurfaceInteraction si;
+            scene.Intersect(ray, &si);
+            const Float len = ray.d.Length();
+            const Vector3f d = ray.d / len;
+            ro.push_back(ray.o.x); ro.push_back(ray.o.y); ro.push_back(ray.o.z);
+            ro.push_back((w > 0 && ray.medium) ? std::min(ray.tMax * len, MaxFloat) : 0.f);
+            push3(rd, d);
+        }
+    std::vector<float> r2cf, c2wf;
+    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) {
+        r2cf.push_back(camera->RasterToCamera.GetMatrix().m[i][j]);
+        c2wf.push_back(c2w.GetMatrix().m[i][j]);
+    }
+    BinWriter bw(path);
+    bw.f4("sigma_a", {sa[0], sa[1], sa[2]}); bw.f4("sigma_s", {ss[0], ss[1], ss[2]}); bw.f4("g", {g});
+    bw.f4("light_pos", {0.f, 0.9f, 0.f}); bw.f4("light_I", {5.f, 4.f, 3.f});
+    bw.f4("mesh_P", P); bw.u4("mesh_idx", I); bw.f4("mesh_Kd", Kd); bw.u4("mesh_attr", attr);
+    bw.u8("range", {first, nPaths, (uint64_t)maxDepth});
+    bw.f4("photon_p", pp); bw.f4("photon_alpha", pa); bw.f4("photon_wi", pw); bw.u4("path_id", pid);
+    bw.f4("raster_to_camera", r2cf); bw.f4("camera_to_world", c2wf);
+    bw.u4("window", {(uint32_t)pb.pMin.x, (uint32_t)pb.pMin.y, (uint32_t)(pb.pMax.x - pb.pMin.x), (uint32_t)(pb.pMax.y - pb.pMin.y)});
+    bw.f4("pixel_offset", {off.x, off.y});
+    bw.f4("ray_o_tmax", ro); bw.f4("ray_d", rd);
+    fprintf(stderr, "surfaces: %zu photons from %llu paths, %zu camera rays\n", pid.size(),
+            (unsigned long long)nPaths, ro.size() / 4);
+}
+
 }  // namespace
 
 int main(int argc, char **argv) {
@@ -594,7 +755,11 @@ int main(int argc, char **argv) {
         trace(argv[2], argv[3], strtoull(argv[4], 0, 10), strtoull(argv[5], 0, 10), atoi(argv[6]));
         return 0;
     }
+    if (argc >= 8 && !strcmp(argv[1], "surfaces")) {
+        surfaces(argv[2], strtoull(argv[3], 0, 10), strtoull(argv[4], 0, 10), atoi(argv[5]), atoi(argv[6]), atoi(argv[7]));
+        return 0;
+    }
     fprintf(stderr, "usage: ref_harness primitives out.json | fogbox out.bin nPhotons res radius [keepFirst] | "
-                    "trace out.bin homogeneous|grid first nPaths maxDepth\n");
+                    "trace out.bin homogeneous|grid first nPaths maxDepth | surfaces out.bin first nPaths maxDepth resX resY\n");
     return 2;
 }

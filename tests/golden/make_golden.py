@@ -13,6 +13,9 @@ compressed .npz fixtures.  The fixtures travel to the GPU box; /root/reference d
                              beam radiance estimate evaluated with reference arithmetic classes
   ref_trace_homogeneous.npz  volume-photon deposit loop executed by reference classes
   ref_trace_grid.npz         (sampler stream of photonbeam.cpp:386-391, deposit rule photonmap.cpp:696-724)
+  ref_surfaces.npz           photon paths bouncing off matte triangle walls (photonbeam.cpp:296-323) and
+                             crossing an interface-only medium boundary, walked by reference classes;
+                             camera rays of a cropped PerspectiveCamera with first-hit tMax
 """
 import json
 import os
@@ -69,6 +72,10 @@ def main():
         tb = os.path.join(tmp, f"trace_{kind}.bin")
         subprocess.check_call([HARNESS, "trace", tb, kind, str(first), str(n), "5"])
         np.savez_compressed(os.path.join(HERE, f"ref_trace_{kind}.npz"), **read_bref(tb))
+    # surfaces: matte walls, reversed wall, interface-only boundary + cropped camera window
+    sb = os.path.join(tmp, "surfaces.bin")
+    subprocess.check_call([HARNESS, "surfaces", sb, "0", "4000", "6", "64", "48"])
+    np.savez_compressed(os.path.join(HERE, "ref_surfaces.npz"), **read_bref(sb))
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)), "bytes")
