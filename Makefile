@@ -6,14 +6,14 @@ OBJDIR := build/obj
 # -fmad=false: the disk predicate / Morton code / slab test must round exactly like the CPU oracle.
 NVFLAGS := -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -fmad=false \
            -Xcompiler -fPIC,-ffp-contract=off -Iinclude
-SRCS := bre_api.cu bre_build.cu bre_query.cu bre_film.cu bre_trace.cu
+SRCS := bre_api.cu bre_build.cu bre_query.cu bre_film.cu bre_trace.cu bre_camera.cu
 OBJS := $(patsubst %.cu,$(OBJDIR)/%.o,$(SRCS)) $(OBJDIR)/bre_nccl.o
 
 .PHONY: all lib oracle ref clean
 all: lib oracle
 lib: $(PKG)/libbre.so
 
-$(OBJDIR)/%.o: $(CSRC)/%.cu $(CSRC)/bre_internal.cuh $(CSRC)/bre_query_warp.cuh include/bre.h
+$(OBJDIR)/%.o: $(CSRC)/%.cu $(CSRC)/bre_internal.cuh $(CSRC)/bre_query_warp.cuh $(CSRC)/bre_surface.cuh include/bre.h
 	@mkdir -p $(OBJDIR)
 	$(NVCC) $(NVFLAGS) -Xptxas -v -c $< -o $@ 2> $(OBJDIR)/$*.ptxas.log || (cat $(OBJDIR)/$*.ptxas.log; false)
 

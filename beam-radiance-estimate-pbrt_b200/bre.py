@@ -25,6 +25,8 @@ SYMBOLS = [
     "bre_query_d", "bre_count", "bre_count_d", "bre_get_counters", "bre_film_create",
     "bre_film_clear", "bre_film_accumulate", "bre_film_accumulate_d", "bre_film_resolve", "bre_film_mean",
     "bre_query_to_film", "bre_set_timing", "bre_get_timings", "bre_shard_range", "bre_tile_owner",
+    "bre_set_triangle_attrs", "bre_set_lights_in_medium", "bre_set_camera", "bre_camera_rays",
+    "bre_query_camera_to_film",
 ]
 
 
@@ -51,6 +53,12 @@ class Counters(C.Structure):
                 ("bytes_algorithmic", C.c_uint64), ("fast_nodes", C.c_uint64),
                 ("fast_disk_tests", C.c_uint64), ("leaf_pairs", C.c_uint64),
                 ("pair_queue_overflow", C.c_uint64)]
+
+
+class Camera(C.Structure):
+    _fields_ = [("raster_to_camera", C.c_float * 16), ("camera_to_world", C.c_float * 16),
+                ("x0", C.c_int32), ("y0", C.c_int32), ("width", C.c_int32), ("height", C.c_int32),
+                ("in_medium", C.c_int32)]
 
 
 class HitDump(C.Structure):
@@ -145,6 +153,35 @@ class Bre:
     def set_bounds(self, lo, hi):
         lo, hi = _f32(lo, (3,)), _f32(hi, (3,))
         self._ck(self.lib.bre_set_bounds(self.ctx, _fp(lo), _fp(hi)))
+
+    def set_triangles(self, P, idx, Kd, attrs=None):
+        P, Kd = _f32(P), _f32(Kd)
+        idx = np.ascontiguousarray(idx, dtype=np.uint32)
+        n = idx.size // 3
+        self._ck(self.lib.bre_set_triangles(self.ctx, n, _fp(P), idx.ctypes.data_as(C.POINTER(C.c_uint32)), _fp(Kd)))
+        if attrs is not None and n:
+            a = np.ascontiguousarray(attrs, dtype=np.uint8)
+            self._ck(self.lib.bre_set_triangle_attrs(self.ctx, n, a.ctypes.data_as(C.POINTER(C.c_uint8))))
+
+    def set_lights_in_medium(self, flag):
+        self._ck(self.lib.bre_set_lights_in_medium(self.ctx, int(flag)))
+
+    def set_camera(self, raster_to_camera, camera_to_world, x0, y0, width, height, in_medium=True):
+        cam = Camera()
+        cam.raster_to_camera = (C.c_float * 16)(*_f32(raster_to_camera, (16,)))
+        cam.camera_to_world = (C.c_float * 16)(*_f32(camera_to_world, (16,)))
+        cam.x0, cam.y0, cam.width, cam.height, cam.in_medium = x0, y0, width, height, int(in_medium)
+        self._ck(self.lib.bre_set_camera(self.ctx, C.byref(cam)))
+        self._cam_n = width * height
+
+    def camera_rays(self, offx=0.5, offy=0.5):
+        n = getattr(self, "_cam_n", 0)     # 0: no camera yet -> the library reports the error
+        o = np.zeros((n, 4), np.float32); d = np.zeros((n, 3), np.float32)
+        self._ck(self.lib.bre_camera_rays(self.ctx, C.c_float(offx), C.c_float(offy), _fp(o), _fp(d)))
+        return o, d
+
+    def query_camera_to_film(self, n_paths_norm, offx=0.5, offy=0.5):
+        self._ck(self.lib.bre_query_camera_to_film(self.ctx, C.c_float(offx), C.c_float(offy), C.c_float(n_paths_norm)))
 
     # ---- photons
     def trace_photons(self, first_index, n_paths, max_depth, radius):

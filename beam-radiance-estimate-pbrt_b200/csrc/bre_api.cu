@@ -144,7 +144,7 @@ int bre_destroy(bre_ctx *ctx) {
                    &ctx->node_lo, &ctx->node_hi, &ctx->node_range, &ctx->parent, &ctx->leaf_lo,
                    &ctx->leaf_hi, &ctx->flags, &ctx->fast, &ctx->scratch, &ctx->rays_o, &ctx->rays_d,
                    &ctx->out_rgb, &ctx->tau, &ctx->hit_counts, &ctx->hit_offsets, &ctx->hit_idx,
-                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->film, &ctx->path_counts, &ctx->path_offsets};
+                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb};
     for (Buf *b : bufs) if (b->p) cudaFree(b->p);
     if (ctx->lights_d) cudaFree(ctx->lights_d);
     for (int i = 0; i < 8; ++i)
@@ -248,12 +248,6 @@ int bre_set_bounds(bre_ctx *ctx, const float lo[3], const float hi[3]) {
     }
     ctx->have_bounds = true;
     return BRE_OK;
-}
-
-int bre_set_triangles(bre_ctx *ctx, uint32_t, const float *, const uint32_t *, const float *) {
-    if (!ctx) return BRE_ERR_INVALID;
-    return set_err(ctx, BRE_ERR_UNSUPPORTED,
-                   "surface photon tracing is not built yet (SURVEY.md 8f-1); use bre_set_bounds or bre_upload_photons");
 }
 
 // ---------------------------------------------------------------- photons
@@ -432,6 +426,37 @@ int bre_query_to_film(bre_ctx *ctx, uint32_t n, const float *o4, const float *d3
     if ((s = run_query(ctx, n, (const float4 *)ctx->rays_o.p, (const float4 *)ctx->rays_d.p, nPathsNorm,
                        (float4 *)ctx->out_rgb.p)) != BRE_OK) return s;
     return film_accumulate(ctx, n, pd, (const float4 *)ctx->out_rgb.p);
+}
+
+int bre_camera_rays(bre_ctx *ctx, float offx, float offy, float *o4, float *d3) {
+    CTX_CHECK();
+    int s = camera_rays(ctx, offx, offy);
+    if (s != BRE_OK) return s;
+    const uint32_t n = (uint32_t)ctx->camera.width * (uint32_t)ctx->camera.height;
+    if (o4) BRE_CUDA(cudaMemcpyAsync(o4, ctx->rays_o.p, (size_t)n * 16, cudaMemcpyDeviceToHost, ctx->stream));
+    if (d3) {
+        if ((s = ensure(ctx, ctx->scratch, (size_t)n * 12 + 64)) != BRE_OK) return s;
+        k_unpack3<<<(n + 255) / 256, 256, 0, ctx->stream>>>((const float4 *)ctx->rays_d.p, n, (float *)ctx->scratch.p, nullptr);
+        BRE_CUDA(cudaGetLastError());
+        BRE_CUDA(cudaMemcpyAsync(d3, ctx->scratch.p, (size_t)n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return BRE_OK;
+}
+
+int bre_query_camera_to_film(bre_ctx *ctx, float offx, float offy, float nPathsNorm) {
+    CTX_CHECK();
+    int s = query_ready(ctx);
+    if (s != BRE_OK) return s;
+    if (!ctx->have_camera) return set_err(ctx, BRE_ERR_INVALID, "bre_set_camera has not been called");
+    const uint32_t n = (uint32_t)ctx->camera.width * (uint32_t)ctx->camera.height;
+    if (!ctx->film.p || ctx->n_pixels != n)
+        return set_err(ctx, BRE_ERR_INVALID, "bre_film_create(width*height) has not been called");
+    if ((s = camera_rays(ctx, offx, offy)) != BRE_OK) return s;
+    if ((s = ensure(ctx, ctx->out_rgb, (size_t)n * 16)) != BRE_OK) return s;
+    if ((s = run_query(ctx, n, (const float4 *)ctx->rays_o.p, (const float4 *)ctx->rays_d.p, nPathsNorm,
+                       (float4 *)ctx->out_rgb.p)) != BRE_OK) return s;
+    return film_accumulate(ctx, n, nullptr, (const float4 *)ctx->out_rgb.p);
 }
 
 int bre_count(bre_ctx *ctx, uint32_t n, const float *o4, const float *d3) {

@@ -116,6 +116,12 @@ struct bre_ctx {
     int n_lights = 0;
     float blo[3] = {0, 0, 0}, bhi[3] = {0, 0, 0};
     bool have_bounds = false;
+    // surfaces (bre_surface.cuh) and camera (bre_camera.cu)
+    uint32_t n_tri = 0;
+    bre::Buf tri, tri_kdb;
+    int lights_in_medium = 1;
+    bre_camera camera{};
+    bool have_camera = false;
 
     // photon store (store order)
     uint64_t n_photons = 0;
@@ -169,6 +175,8 @@ int run_hitdump(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, br
 // film.cu
 int film_accumulate(bre_ctx *ctx, uint32_t n, const uint32_t *pix_d, const float4 *rgb_d);
 int film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int meanOnly);
+// camera.cu
+int camera_rays(bre_ctx *ctx, float offx, float offy);
 // trace.cu
 int trace_photons(bre_ctx *ctx, uint64_t first, uint64_t nPaths, int maxDepth, float radius);
 // nccl.cpp

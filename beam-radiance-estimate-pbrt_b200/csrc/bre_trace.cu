@@ -13,6 +13,7 @@
 // per-path counts and a compaction kernel then append them to the photon store in path-index
 // order, so the store is deterministic and identical on every rank / run.
 #include "bre_internal.cuh"
+#include "bre_surface.cuh"
 
 namespace bre {
 
@@ -174,7 +175,9 @@ __device__ __forceinline__ float spot_falloff(const LightDev &L, const float w[3
     return fmul(fmul(delta, delta), fmul(delta, delta));
 }
 
+template <bool MESH>
 __global__ void __launch_bounds__(128) k_trace(MediumDev m, const LightsDev *__restrict__ lights,
+                                               MeshDev mesh, int lightsInMedium,
                                                float blo0, float blo1, float blo2, float bhi0,
                                                float bhi1, float bhi2, uint64_t first,
                                                uint32_t nPaths, int maxDepth, float radius,
@@ -228,6 +231,68 @@ __global__ void __launch_bounds__(128) k_trace(MediumDev m, const LightsDev *__r
         ok = !(alpha[0] == 0.f && alpha[1] == 0.f && alpha[2] == 0.f);
     }
     const size_t base = (size_t)pid * maxDepth;
+    if (MESH) {
+        // photonbeam.cpp:258-325 as a loop: Scene::Intersect, Medium::Sample, deposit + phase
+        // scatter, or surface bounce (:296-323).  `guard` bounds the interface pass-throughs.
+        bool inMedium = lightsInMedium != 0;
+        int guard = 64 + 8 * maxDepth;
+        for (int depth = 0; ok && depth < maxDepth && guard > 0; ++depth, --guard) {
+            SurfHit h;
+            if (!mesh_intersect(mesh, o, d, __int_as_float(0x7f800000), h, true)) break;
+            bool scattered = false;
+            float ts = 0.f, w[3];
+            if (inMedium) {
+                scattered = medium_sample(m, rng, o, d, h.t, ts, w);
+#pragma unroll
+                for (int c = 0; c < 3; ++c) alpha[c] = fmul(alpha[c], w[c]);
+            }
+            if (alpha[0] == 0.f && alpha[1] == 0.f && alpha[2] == 0.f) break;
+            if (scattered) {
+                float p[3] = {fadd(o[0], fmul(d[0], ts)), fadd(o[1], fmul(d[1], ts)), fadd(o[2], fmul(d[2], ts))};
+                float wo[3] = {-d[0], -d[1], -d[2]}, wi[3];
+                slot_pos[base + stored] = make_float4(p[0], p[1], p[2], radius);
+                slot_pow[base + stored] = make_float4(alpha[0], alpha[1], alpha[2], 0.f);
+                slot_dir[base + stored] = make_float4(wo[0], wo[1], wo[2], 0.f);
+                ++stored;
+                float ua = rng.f(), ub = rng.f();
+                hg_sample(wo, m.g, ua, ub, wi);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) { o[k] = p[k]; d[k] = wi[k]; }
+                if (depth + 1 >= maxDepth) break;
+                rng.f();   // roulette draw with continue probability 1
+                continue;
+            }
+            if ((h.attr & BRE_TRI_NO_MATERIAL) || h.Kd[0] < 0.f) {   // photonbeam.cpp:300-304
+                --depth;
+                float no[3];
+                offset_ray_origin(h.p, h.pError, h.n, d, no);
+                inMedium = medium_after(h.attr, d, h.n, inMedium);
+                o[0] = no[0]; o[1] = no[1]; o[2] = no[2];
+                continue;
+            }
+            float R[3], woW[3] = {-d[0], -d[1], -d[2]}, wiW[3], f[3], pdf;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) R[c] = h.Kd[c] < 0.f ? 0.f : h.Kd[c];
+            float ub0 = rng.f(), ub1 = rng.f();
+            if (!lambert_sample(h, R, woW, ub0, ub1, wiW, f, pdf)) break;
+            float betaNew[3], absdot = fabsf(dot3(wiW, h.n));
+#pragma unroll
+            for (int c = 0; c < 3; ++c) betaNew[c] = alpha[c] * f[c] * absdot / pdf;
+            float no[3];
+            offset_ray_origin(h.p, h.pError, h.n, wiW, no);
+            inMedium = medium_after(h.attr, wiW, h.n, inMedium);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { o[k] = no[k]; d[k] = wiW[k]; }
+            float yNew = 0.212671f * betaNew[0] + 0.715160f * betaNew[1] + 0.072169f * betaNew[2];
+            float yOld = 0.212671f * alpha[0] + 0.715160f * alpha[1] + 0.072169f * alpha[2];
+            float q = fmaxf(0.f, 1 - yNew / yOld);   // photonbeam.cpp:321-323
+            if (rng.f() < q) break;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) alpha[c] = betaNew[c] / (1 - q);
+        }
+        counts[pid] = stored;
+        return;
+    }
     for (int nInt = 1; ok; ++nInt) {
         float t0, t1;
         if (!ray_box(o, d, __int_as_float(0x7f800000), blo, bhi, t0, t1) || t0 > 0.f) break;
@@ -367,7 +432,10 @@ int grow_photon_store(bre_ctx *ctx, uint64_t newCount) { return grow_store(ctx, 
 int trace_photons(bre_ctx *ctx, uint64_t first, uint64_t nPathsTotal, int maxDepth, float radius) {
     if (!ctx->have_medium) return set_err(ctx, BRE_ERR_INVALID, "no medium set");
     if (!ctx->lights_d || ctx->n_lights == 0) return set_err(ctx, BRE_ERR_INVALID, "no lights set");
-    if (!ctx->have_bounds) return set_err(ctx, BRE_ERR_INVALID, "no scene bounds set (bre_set_bounds)");
+    const bool useMesh = ctx->n_tri > 0;
+    if (!useMesh && !ctx->have_bounds)
+        return set_err(ctx, BRE_ERR_INVALID, "no surfaces set (bre_set_triangles or bre_set_bounds)");
+    MeshDev mesh{ctx->n_tri, (const float4 *)ctx->tri.p, (const float *)ctx->tri_kdb.p};
     if (maxDepth < 1) return set_err(ctx, BRE_ERR_INVALID, "max_depth must be >= 1");
     const uint64_t CHUNK = 1u << 22;
     ctx->built = false;
@@ -391,9 +459,14 @@ int trace_photons(bre_ctx *ctx, uint64_t first, uint64_t nPathsTotal, int maxDep
         uint32_t *tileSums = (uint32_t *)(base + oTs);
         uint64_t *tileOff = (uint64_t *)(base + oTo);
         uint64_t *total = (uint64_t *)(base + oTot);
-        k_trace<<<(nPaths + 127) / 128, 128, 0, ctx->stream>>>(
-            ctx->medium, ctx->lights_d, ctx->blo[0], ctx->blo[1], ctx->blo[2], ctx->bhi[0],
-            ctx->bhi[1], ctx->bhi[2], first + done, nPaths, maxDepth, radius, sp, sw, sd, counts);
+        if (useMesh)
+            k_trace<true><<<(nPaths + 127) / 128, 128, 0, ctx->stream>>>(
+                ctx->medium, ctx->lights_d, mesh, ctx->lights_in_medium, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f,
+                first + done, nPaths, maxDepth, radius, sp, sw, sd, counts);
+        else
+            k_trace<false><<<(nPaths + 127) / 128, 128, 0, ctx->stream>>>(
+                ctx->medium, ctx->lights_d, mesh, 1, ctx->blo[0], ctx->blo[1], ctx->blo[2], ctx->bhi[0],
+                ctx->bhi[1], ctx->bhi[2], first + done, nPaths, maxDepth, radius, sp, sw, sd, counts);
         k_scan_reduce<<<nTiles, SC_T, 0, ctx->stream>>>(counts, nPaths, tileSums);
         k_scan_tiles<<<1, 1024, 0, ctx->stream>>>(tileSums, nTiles, tileOff, total);
         k_scan_apply<<<nTiles, SC_T, 0, ctx->stream>>>(counts, nPaths, tileOff, offs);

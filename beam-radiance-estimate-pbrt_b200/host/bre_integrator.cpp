@@ -7,11 +7,17 @@
 
 #include "bre.h"   // the C ABI (include/bre.h of the B200 library)
 
+#include "accelerators/bvh.h"
+#include "cameras/perspective.h"
 #include "film.h"
 #include "interaction.h"
 #include "lowdiscrepancy.h"
 #include "parallel.h"
 #include "lights/point.h"
+#include "materials/matte.h"
+#include "primitive.h"
+#include "shapes/triangle.h"
+#include "textures/constant.h"
 #include "lights/spot.h"
 #include "media/grid.h"
 #include "media/homogeneous.h"
@@ -101,6 +107,72 @@ bool BreIntegrator::SetupLights(bre_ctx *ctx, const Scene &scene) const {
         lights.push_back(b);
     }
     return Check(ctx, bre_set_lights(ctx, (int)lights.size(), lights.data()), "bre_set_lights");
+}
+
+// Scene::aggregate -> triangles for the device photon tracer and the device camera rays.  Supported:
+// a BVHAccel of GeometricPrimitives over Triangle shapes with MatteMaterial (constant Kd, sigma 0)
+// or no material, no area lights; medium interfaces that are either no transition or a transition
+// between the camera's medium and vacuum.  Anything else returns false (the caller then keeps pbrt's
+// own host code for that stage).
+bool BreIntegrator::SetupSurfaces(bre_ctx *ctx, const Scene &scene, const Medium *medium) const {
+    const BVHAccel *bvh = dynamic_cast<const BVHAccel *>(scene.aggregate.get());
+    if (!bvh) return false;
+    std::vector<float> P, Kd;
+    std::vector<uint32_t> idx;
+    std::vector<uint8_t> attrs;
+    for (const std::shared_ptr<Primitive> &prim : bvh->primitives) {
+        const GeometricPrimitive *gp = dynamic_cast<const GeometricPrimitive *>(prim.get());
+        if (!gp || gp->areaLight) return false;
+        const Triangle *tri = dynamic_cast<const Triangle *>(gp->shape.get());
+        if (!tri || tri->mesh->alphaMask || tri->mesh->n || tri->mesh->s || tri->mesh->uv) return false;
+        uint8_t a = 0;
+        float kd[3] = {-1.f, -1.f, -1.f};
+        if (gp->material) {
+            const MatteMaterial *mm = dynamic_cast<const MatteMaterial *>(gp->material.get());
+            if (!mm || mm->bumpMap) return false;
+            const ConstantTexture<Spectrum> *k = dynamic_cast<const ConstantTexture<Spectrum> *>(mm->Kd.get());
+            const ConstantTexture<Float> *sg = dynamic_cast<const ConstantTexture<Float> *>(mm->sigma.get());
+            if (!k || !sg || sg->value != 0) return false;
+            ToRGB3(k->value.Clamp(), kd);
+        } else
+            a |= BRE_TRI_NO_MATERIAL;
+        const MediumInterface &mi = gp->mediumInterface;
+        if (mi.IsMediumTransition()) {
+            if (mi.inside == medium && !mi.outside) a |= BRE_TRI_MEDIUM_INSIDE;
+            else if (mi.outside == medium && !mi.inside) a |= BRE_TRI_MEDIUM_OUTSIDE;
+            else return false;
+        }
+        if (tri->reverseOrientation ^ tri->transformSwapsHandedness) a |= BRE_TRI_FLIP_NORMAL;
+        for (int v = 0; v < 3; ++v) {
+            const Point3f &p = tri->mesh->p[tri->v[v]];
+            idx.push_back((uint32_t)(P.size() / 3));
+            P.push_back(p.x); P.push_back(p.y); P.push_back(p.z);
+        }
+        Kd.push_back(kd[0]); Kd.push_back(kd[1]); Kd.push_back(kd[2]);
+        attrs.push_back(a);
+    }
+    if (attrs.empty()) return false;
+    return Check(ctx, bre_set_triangles(ctx, (uint32_t)attrs.size(), P.data(), idx.data(), Kd.data()), "bre_set_triangles") &&
+           Check(ctx, bre_set_triangle_attrs(ctx, (uint32_t)attrs.size(), attrs.data()), "bre_set_triangle_attrs");
+}
+
+// Pinhole PerspectiveCamera -> bre_set_camera (rays are then generated by the K0 kernel).
+bool BreIntegrator::SetupCamera(bre_ctx *ctx, const Bounds2i &pixelBounds) const {
+    const PerspectiveCamera *pc = dynamic_cast<const PerspectiveCamera *>(camera.get());
+    if (!pc || pc->lensRadius > 0 || pc->CameraToWorld.actuallyAnimated) return false;
+    bre_camera cam = {};
+    const Matrix4x4 &r2c = pc->RasterToCamera.GetMatrix();
+    const Matrix4x4 &c2w = pc->CameraToWorld.startTransform->GetMatrix();
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j) {
+            cam.raster_to_camera[4 * i + j] = r2c.m[i][j];
+            cam.camera_to_world[4 * i + j] = c2w.m[i][j];
+        }
+    cam.x0 = pixelBounds.pMin.x; cam.y0 = pixelBounds.pMin.y;
+    cam.width = pixelBounds.pMax.x - pixelBounds.pMin.x;
+    cam.height = pixelBounds.pMax.y - pixelBounds.pMin.y;
+    cam.in_medium = camera->medium != nullptr;
+    return bre_set_camera(ctx, &cam) == BRE_OK;
 }
 
 // ---- host photon tracer ----------------------------------------------------------------------
@@ -200,15 +272,25 @@ void BreIntegrator::Render(const Scene &scene) {
     if (!SetupMedium(ctx, medium)) { bre_destroy(ctx); return; }
     std::unique_ptr<Distribution1D> lightDistr = ComputeLightPowerDistribution(scene);
     if (!lightDistr) { Error("bre: the scene has no lights"); bre_destroy(ctx); return; }
+    // surfaces on the device: needed by the device photon tracer (else: absorbing world box) and by
+    // the device camera rays (else: rays generated by pbrt's camera on the host)
+    const bool haveSurfaces = (deviceTracer || deviceCamera) && SetupSurfaces(ctx, scene, medium);
     if (deviceTracer) {
         const Bounds3f wb = scene.WorldBound();
         float lo[3] = {wb.pMin.x, wb.pMin.y, wb.pMin.z}, hi[3] = {wb.pMax.x, wb.pMax.y, wb.pMax.z};
+        if (!haveSurfaces)
+            Warning("bre: scene surfaces are not all matte triangles; the device photon tracer treats "
+                    "the world bound as an absorbing box");
         if (!SetupLights(ctx, scene) || !Check(ctx, bre_set_bounds(ctx, lo, hi), "bre_set_bounds")) {
             bre_destroy(ctx);
             return;
         }
+        for (const std::shared_ptr<Light> &l : scene.lights)
+            if (l->mediumInterface.inside != medium) bre_set_lights_in_medium(ctx, 0);
     }
     const Bounds2i pixelBounds = camera->film->croppedPixelBounds;
+    const bool cameraOnDevice = deviceCamera && haveSurfaces && SetupCamera(ctx, pixelBounds);
+    usedDeviceCamera = cameraOnDevice;
     const Vector2i ext = pixelBounds.Diagonal();
     const uint32_t nPixels = (uint32_t)(ext.x * ext.y);
     const uint64_t nPaths = photonsPerIteration > 0 ? (uint64_t)photonsPerIteration : nPixels;
@@ -235,6 +317,9 @@ void BreIntegrator::Render(const Scene &scene) {
             // iteration 0 looks through the pixel centres, later ones use a (2,3) Halton offset
             const Point2f off = iter == 0 ? Point2f(0.5f, 0.5f)
                                           : Point2f(RadicalInverse(0, iter), RadicalInverse(1, iter));
+            if (cameraOnDevice)
+                ok = Check(ctx, bre_query_camera_to_film(ctx, off.x, off.y, (float)nPaths), "bre_query_camera_to_film");
+            else {
             ParallelFor([&](int64_t y) {
                 for (int x = 0; x < ext.x; ++x) {
                     const size_t q = (size_t)y * ext.x + x;
@@ -255,6 +340,7 @@ void BreIntegrator::Render(const Scene &scene) {
             }, ext.y, 4);
             ok = Check(ctx, bre_query_to_film(ctx, nPixels, rayO.data(), rayD.data(), nullptr, (float)nPaths),
                        "bre_query_to_film");
+            }
         }
         if (!ok) break;
         // ---- progressive radius (photonbeam.cpp:562)
@@ -288,12 +374,14 @@ Integrator *CreateBreIntegrator(const ParamSet &params, std::shared_ptr<const Ca
     bool renderMedia = params.FindOneBool("rendermedia", true);
     std::string tracer = params.FindOneString("photontracer", "host");
     int device = params.FindOneInt("device", 0);
-    if (tracer != "host" && tracer != "device") {
-        Error("bre: unknown photontracer \"%s\"", tracer.c_str());
+    std::string camrays = params.FindOneString("camerarays", "device");
+    if ((tracer != "host" && tracer != "device") || (camrays != "host" && camrays != "device")) {
+        Error("bre: photontracer and camerarays must be \"host\" or \"device\"");
         return nullptr;
     }
     return new BreIntegrator(camera, nIterations, photonsPerIter, maxDepth, radius, alpha,
-                             std::max(1, writeFreq), renderMedia, tracer == "device", device);
+                             std::max(1, writeFreq), renderMedia, tracer == "device", camrays == "device",
+                             device);
 }
 
 }  // namespace pbrt

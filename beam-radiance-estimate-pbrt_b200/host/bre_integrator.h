@@ -21,7 +21,11 @@
 //   "integer iterations"|"numiterations", "float alpha", "integer imagewritefrequency",
 //   "bool rendermedia" as in photonbeam.cpp:590-603
 //   new: "string photontracer" ["host"|"device"]  host = photon paths traced by pbrt's own
-//        Scene/Medium/BSDF code (any scene), device = K1 kernel (media inside an absorbing box).
+//        Scene/Medium/BSDF code (any scene), device = K1 kernel (matte triangle scenes with point /
+//        spot lights; other scenes: media inside the absorbing world box).
+//   new: "string camerarays" ["device"|"host"]  device (default) = K0 kernel for a pinhole
+//        PerspectiveCamera over matte triangle scenes (bit-identical rays, no PCIe ray traffic);
+//        falls back to pbrt's camera + Scene::Intersect on the host for anything else.
 #ifndef PBRT_INTEGRATORS_BRE_H
 #define PBRT_INTEGRATORS_BRE_H
 
@@ -37,20 +41,23 @@ class BreIntegrator : public Integrator {
   public:
     BreIntegrator(std::shared_ptr<const Camera> camera, int nIterations, int photonsPerIteration,
                   int maxDepth, Float initialRadius, Float alpha, int writeFrequency,
-                  bool renderMedia, bool deviceTracer, int device)
+                  bool renderMedia, bool deviceTracer, bool deviceCamera, int device)
         : camera(camera), nIterations(nIterations), photonsPerIteration(photonsPerIteration),
           maxDepth(maxDepth), initialRadius(initialRadius), alpha(alpha),
           writeFrequency(writeFrequency), renderMedia(renderMedia), deviceTracer(deviceTracer),
-          device(device) {}
+          deviceCamera(deviceCamera), device(device) {}
     void Render(const Scene &scene);
 
     // test hook: after Render, photons of the last iteration in reference layout (p, alpha, wi)
     std::vector<float> lastPhotons;
     uint64_t lastPathsEmitted = 0;
+    bool usedDeviceCamera = false;
 
   private:
     bool SetupMedium(bre_ctx *ctx, const Medium *medium) const;
     bool SetupLights(bre_ctx *ctx, const Scene &scene) const;
+    bool SetupSurfaces(bre_ctx *ctx, const Scene &scene, const Medium *medium) const;
+    bool SetupCamera(bre_ctx *ctx, const Bounds2i &pixelBounds) const;
     uint64_t TracePhotonsHost(bre_ctx *ctx, const Scene &scene, const Distribution1D &lightDistr,
                               uint64_t firstIndex, uint64_t nPaths, Float radius);
 
@@ -58,7 +65,7 @@ class BreIntegrator : public Integrator {
     const int nIterations, photonsPerIteration, maxDepth;
     const Float initialRadius, alpha;
     const int writeFrequency;
-    const bool renderMedia, deviceTracer;
+    const bool renderMedia, deviceTracer, deviceCamera;
     const int device;
 };
 

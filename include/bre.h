@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define BRE_ABI_VERSION 1
+#define BRE_ABI_VERSION 2
 
 typedef enum {
     BRE_OK = 0,
@@ -100,8 +100,42 @@ int bre_set_lights(bre_ctx *ctx, int n, const bre_light *lights);
 /* Absorbing axis-aligned scene box that ends photon paths (stand-in for Scene::Intersect,
  * core/scene.cpp:50-54, until the triangle intersector of SURVEY.md 8f-1 exists). */
 int bre_set_bounds(bre_ctx *ctx, const float lo[3], const float hi[3]);
-/* Surfaces for photon tracing: not built yet -> BRE_ERR_UNSUPPORTED. */
+/* Surfaces: Scene::Intersect (core/scene.cpp:50-54) over triangle shapes (shapes/triangle.cpp:177-392)
+ * for device photon tracing (K1) and device camera rays (K0).  P = vertex positions xyz (as many as
+ * idx references), idx = 3 vertex indices per triangle, Kd = 3 floats per triangle: the reflectance
+ * of MatteMaterial with sigma 0 (materials/matte.cpp:55-60); Kd[0] < 0 = no material.  n_tri = 0
+ * removes the mesh (photon tracing then falls back to the absorbing box of bre_set_bounds).
+ * Triangles are tested by brute force: intended for box-like scenes of tens of triangles. */
 int bre_set_triangles(bre_ctx *ctx, uint32_t n_tri, const float *P, const uint32_t *idx, const float *Kd);
+/* Per-triangle attribute bits (optional, default 0), after bre_set_triangles with the same n_tri. */
+#define BRE_TRI_MEDIUM_INHERIT 0  /* not a medium transition: a ray keeps its medium (core/primitive.cpp:104-109) */
+#define BRE_TRI_MEDIUM_INSIDE 1   /* MediumInterface "M" "": medium on the side opposite the normal */
+#define BRE_TRI_MEDIUM_OUTSIDE 2  /* MediumInterface "" "M": medium on the normal's side */
+#define BRE_TRI_FLIP_NORMAL 4     /* reverseOrientation ^ transformSwapsHandedness (shapes/triangle.cpp:387-388) */
+#define BRE_TRI_NO_MATERIAL 8     /* interface-only surface: photons pass through (integrators/photonbeam.cpp:300-304) */
+int bre_set_triangle_attrs(bre_ctx *ctx, uint32_t n_tri, const uint8_t *attrs);
+/* Whether light sources sit inside the medium (Light::mediumInterface.inside); default 1. */
+int bre_set_lights_in_medium(bre_ctx *ctx, int in_medium);
+
+/* ---- K0: camera rays ---------------------------------------------------------------
+ * Replaces the camera feed of the camera pass (integrators/photonbeam.cpp:444-481):
+ * PerspectiveCamera::GenerateRayDifferential for a pinhole (cameras/perspective.cpp:95-103),
+ * Transform::operator()(Ray) (core/transform.h:251-264), Scene::Intersect shortening tMax
+ * (core/primitive.cpp:97-101).  One ray per pixel of the window, pixel (x,y) -> ray y*width + x. */
+typedef struct {
+    float raster_to_camera[16];  /* ProjectiveCamera::RasterToCamera, row major */
+    float camera_to_world[16];   /* Camera::CameraToWorld (not animated), row major */
+    int32_t x0, y0, width, height; /* Film::croppedPixelBounds */
+    int32_t in_medium;           /* camera->medium != nullptr; 0 -> every tMax = 0 (nothing gathered) */
+} bre_camera;
+int bre_set_camera(bre_ctx *ctx, const bre_camera *cam);
+/* Generate the rays of sample position (x + offset_x, y + offset_y) on the device; any output
+ * pointer may be NULL (the rays stay resident for bre_query_camera_to_film either way).
+ * o_xyz_tmax: width*height*4, d_xyz: width*height*3. */
+int bre_camera_rays(bre_ctx *ctx, float offset_x, float offset_y, float *o_xyz_tmax, float *d_xyz);
+/* K0 + K5/K6 + K7 without any host<->device ray traffic: generate, query, accumulate into the film
+ * (created with width*height pixels). */
+int bre_query_camera_to_film(bre_ctx *ctx, float offset_x, float offset_y, float n_paths_norm);
 
 /* ---- K1: volume photon tracing ---------------------------------------------------
  * Replaces the photon pass of PhotonBeamIntegrator::Render (integrators/photonbeam.cpp:365-437,

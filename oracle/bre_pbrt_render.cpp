@@ -5,7 +5,7 @@
 // integrator is created the way core/api.cpp:1444-1468 would (CreateBreIntegrator(ParamSet, camera)),
 // Render() runs -- photon paths by pbrt host code or by the K1 kernel, everything else on the GPU
 // through libbre.so -- and the reference's Film writes the image (PFM through oracle/shim).
-//   bre_pbrt_render <out.pfm> <dump.bin> <host|device> <res> <nPaths> <radius> [iterations]
+//   bre_pbrt_render <out.pfm> <dump.bin> <host|device> <res> <nPaths> <radius> [iterations [camerarays host|device]]
 // dump.bin (BREF1 container, see ref_harness.cpp) holds the photons of the last iteration and the
 // camera rays, so that tests can evaluate the same estimate with the CPU oracle.
 #include <cstdio>
@@ -49,6 +49,7 @@ int main(int argc, char **argv) {
     const int res = atoi(argv[4]), nPaths = atoi(argv[5]);
     const float radius = (float)atof(argv[6]);
     const int iterations = argc > 7 ? atoi(argv[7]) : 1;
+    const char *camrays = argc > 8 ? argv[8] : "device";
     PbrtOptions.quiet = true;
     PbrtOptions.nThreads = 0;
     ParallelInit();
@@ -91,6 +92,7 @@ int main(int argc, char **argv) {
     addInt("iterations", iterations); addInt("photonsperiteration", nPaths); addInt("maxdepth", 5);
     { std::unique_ptr<Float[]> a(new Float[1]); a[0] = radius; ps.AddFloat("initialbeamradius", std::move(a), 1); }
     { std::unique_ptr<std::string[]> a(new std::string[1]); a[0] = tracer; ps.AddString("photontracer", std::move(a), 1); }
+    { std::unique_ptr<std::string[]> a(new std::string[1]); a[0] = camrays; ps.AddString("camerarays", std::move(a), 1); }
     std::unique_ptr<Integrator> integ(CreateBreIntegrator(ps, camera));
     if (!integ) return 1;
     integ->Render(scene);
@@ -114,6 +116,8 @@ int main(int argc, char **argv) {
     fwrite("BREF1\n", 1, 6, fp);
     const float med[7] = {sa, sa, sa, ss, ss, ss, g}, rad = radius, np = (float)bi->lastPathsEmitted;
     add(fp, "medium", "f4", med, 7, 4); add(fp, "radius", "f4", &rad, 1, 4); add(fp, "n_paths", "f4", &np, 1, 4);
+    const uint32_t devCam = bi->usedDeviceCamera ? 1u : 0u;
+    add(fp, "used_device_camera", "u4", &devCam, 1, 4);
     add(fp, "photons9", "f4", bi->lastPhotons.data(), bi->lastPhotons.size(), 4);
     add(fp, "ray_o_tmax", "f4", ro.data(), ro.size(), 4); add(fp, "ray_d", "f4", rd.data(), rd.size(), 4);
     fclose(fp);

@@ -27,15 +27,32 @@ def read_pfm(path):
 
 
 @pytest.mark.skipif(not os.path.exists(BIN), reason="oracle/_ref/bre_pbrt_render not built (needs /root/reference)")
-@pytest.mark.parametrize("tracer", ["host", "device"])
-def test_pbrt_adapter_renders_fog_box(tmp_path, oracle, bre, tracer):
+def fog_box_mesh():
+    """The 12 matte triangles bre_pbrt_render builds, in the same order."""
+    L, H = (-4.0, -1.0, -4.0), (4.0, 2.0, 4.0)
+    quads = [
+        [(L[0], L[1], L[2]), (H[0], L[1], L[2]), (H[0], L[1], H[2]), (L[0], L[1], H[2])],
+        [(L[0], H[1], L[2]), (L[0], H[1], H[2]), (H[0], H[1], H[2]), (H[0], H[1], L[2])],
+        [(L[0], L[1], H[2]), (H[0], L[1], H[2]), (H[0], H[1], H[2]), (L[0], H[1], H[2])],
+        [(L[0], L[1], L[2]), (L[0], H[1], L[2]), (H[0], H[1], L[2]), (H[0], L[1], L[2])],
+        [(L[0], L[1], L[2]), (L[0], L[1], H[2]), (L[0], H[1], H[2]), (L[0], H[1], L[2])],
+        [(H[0], L[1], L[2]), (H[0], H[1], L[2]), (H[0], H[1], H[2]), (H[0], L[1], H[2])]]
+    P = np.asarray(quads, np.float32).reshape(-1, 3)
+    idx = np.concatenate([[4 * q + k for k in (0, 1, 2, 0, 2, 3)] for q in range(6)]).astype(np.uint32)
+    Kd = np.full((12, 3), 0.6, np.float32)
+    return P, idx, Kd
+
+
+@pytest.mark.parametrize("tracer,camrays", [("host", "host"), ("host", "device"), ("device", "device")])
+def test_pbrt_adapter_renders_fog_box(tmp_path, oracle, bre, tracer, camrays):
     from make_golden import read_bref
     pfm, dump = str(tmp_path / "out.pfm"), str(tmp_path / "dump.bin")
     res, n_paths, radius = 32, 6000, 0.2
-    subprocess.run([BIN, pfm, dump, tracer, str(res), str(n_paths), str(radius)], check=True, timeout=300)
+    subprocess.run([BIN, pfm, dump, tracer, str(res), str(n_paths), str(radius), "1", camrays], check=True, timeout=300)
     img = read_pfm(pfm)
     d = read_bref(dump)
     m = d["medium"]
+    assert int(d["used_device_camera"][0]) == (camrays == "device")
     ro, rd = d["ray_o_tmax"].reshape(-1, 4), d["ray_d"].reshape(-1, 3)
     if tracer == "host":
         ph = d["photons9"].reshape(-1, 9)
@@ -45,7 +62,7 @@ def test_pbrt_adapter_renders_fog_box(tmp_path, oracle, bre, tracer):
         ctx = bre.Bre(device=0)
         ctx.set_medium_homogeneous(m[0:3], m[3:6], float(m[6]))
         ctx.set_lights([dict(kind=0, pos=(0.0, 0.9, 0.0), I=(5.0, 5.0, 5.0))])
-        ctx.set_bounds([-4, -1, -4], [4, 2, 4])
+        ctx.set_triangles(*fog_box_mesh())     # what the adapter extracts from the pbrt scene
         ctx.trace_photons(0, n_paths, 5, radius)
         pos, pw, dr, _ = ctx.download_photons()
         ctx.close()
