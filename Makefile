@@ -6,7 +6,7 @@ OBJDIR := build/obj
 # -fmad=false: the disk predicate / Morton code / slab test must round exactly like the CPU oracle.
 NVFLAGS := -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -fmad=false \
            -Xcompiler -fPIC,-ffp-contract=off -Iinclude
-SRCS := bre_api.cu bre_build.cu bre_query.cu bre_film.cu bre_trace.cu bre_camera.cu
+SRCS := bre_api.cu bre_build.cu bre_query.cu bre_film.cu bre_trace.cu bre_camera.cu bre_io.cu
 OBJS := $(patsubst %.cu,$(OBJDIR)/%.o,$(SRCS)) $(OBJDIR)/bre_nccl.o
 
 .PHONY: all lib oracle ref clean

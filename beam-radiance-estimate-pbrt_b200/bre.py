@@ -26,7 +26,8 @@ SYMBOLS = [
     "bre_film_clear", "bre_film_accumulate", "bre_film_accumulate_d", "bre_film_resolve", "bre_film_mean",
     "bre_query_to_film", "bre_set_timing", "bre_get_timings", "bre_shard_range", "bre_tile_owner",
     "bre_set_triangle_attrs", "bre_set_lights_in_medium", "bre_set_camera", "bre_camera_rays",
-    "bre_query_camera_to_film",
+    "bre_query_camera_to_film", "bre_last_build_kind",
+    "bre_save_photons", "bre_load_photons", "bre_film_save", "bre_film_load",
 ]
 
 
@@ -212,6 +213,22 @@ class Bre:
         self._ck(self.lib.bre_download_photons(self.ctx, C.c_uint64(n), _fp(pos), _fp(pw), _fp(dr), _fp(rad)))
         return pos, pw, dr, rad
 
+    def save_photons(self, path, n_paths=0):
+        self._ck(self.lib.bre_save_photons(self.ctx, os.fsencode(path), C.c_uint64(n_paths)))
+
+    def load_photons(self, path, append=False):
+        n, npaths = C.c_uint64(), C.c_uint64()
+        self._ck(self.lib.bre_load_photons(self.ctx, os.fsencode(path), int(append), C.byref(n), C.byref(npaths)))
+        return n.value, npaths.value
+
+    def film_save(self, path, iterations_done, radius):
+        self._ck(self.lib.bre_film_save(self.ctx, os.fsencode(path), C.c_uint64(iterations_done), C.c_float(radius)))
+
+    def film_load(self, path):
+        it, r = C.c_uint64(), C.c_float()
+        self._ck(self.lib.bre_film_load(self.ctx, os.fsencode(path), C.byref(it), C.byref(r)))
+        return it.value, r.value
+
     def set_radius(self, r):
         self._ck(self.lib.bre_set_radius(self.ctx, C.c_float(r)))
 
@@ -221,6 +238,9 @@ class Bre:
     # ---- build
     def build(self):
         self._ck(self.lib.bre_build(self.ctx))
+
+    def last_build_kind(self):
+        return self.lib.bre_last_build_kind(self.ctx)
 
     def download_tree(self):
         n = self.photon_count()

@@ -268,7 +268,7 @@ int bre_upload_photons(bre_ctx *ctx, uint64_t n, const float *p, const float *al
     if (n > 0 && (!p || !alpha || !wi)) return set_err(ctx, BRE_ERR_INVALID, "null photon arrays");
     if (!radii && n > 0 && !(radius > 0.f)) return set_err(ctx, BRE_ERR_INVALID, "radius must be > 0");
     if (!append) ctx->n_photons = 0;
-    ctx->built = false;
+    ctx->built = false; ctx->topo_valid = false;
     if (n == 0) return BRE_OK;
     int s = grow_photon_store(ctx, ctx->n_photons + n);
     if (s != BRE_OK) return s;
@@ -283,7 +283,7 @@ int bre_upload_photons(bre_ctx *ctx, uint64_t n, const float *p, const float *al
 int bre_clear_photons(bre_ctx *ctx) {
     CTX_CHECK();
     ctx->n_photons = 0;
-    ctx->built = false;
+    ctx->built = false; ctx->topo_valid = false;
     return BRE_OK;
 }
 
@@ -316,7 +316,7 @@ int bre_download_photons(bre_ctx *ctx, uint64_t cap, float *p, float *alpha, flo
 int bre_set_radius(bre_ctx *ctx, float radius) {
     CTX_CHECK();
     if (!(radius > 0.f)) return set_err(ctx, BRE_ERR_INVALID, "radius must be > 0");
-    ctx->built = false;
+    ctx->built = false;   // topology stays valid: the next bre_build only refits
     if (ctx->n_photons)
         k_set_w<<<(unsigned)((ctx->n_photons + 255) / 256), 256, 0, ctx->stream>>>((float4 *)ctx->pos_r.p, ctx->n_photons, radius);
     BRE_CUDA(cudaGetLastError());
@@ -326,7 +326,7 @@ int bre_set_radius(bre_ctx *ctx, float radius) {
 int bre_allgather_photons(bre_ctx *ctx) {
     CTX_CHECK();
     if (ctx->n_ranks == 1) return BRE_OK;
-    ctx->built = false;
+    ctx->built = false; ctx->topo_valid = false;
     return nccl_allgather_photons(ctx);
 }
 
@@ -335,6 +335,8 @@ int bre_build(bre_ctx *ctx) {
     CTX_CHECK();
     return build_tree(ctx);
 }
+
+int bre_last_build_kind(bre_ctx *ctx) { return ctx ? ctx->last_build_kind : BRE_ERR_INVALID; }
 
 int bre_download_tree(bre_ctx *ctx, uint32_t *order, uint32_t *codes, float *node_lo, float *node_hi,
                       int32_t *node_children) {

@@ -289,6 +289,36 @@ __global__ void __launch_bounds__(256) k_gather(
     if ((threadIdx.x & 31) == 0 && amax > 0.f) atomicMax(bnd + 6, __float_as_uint(amax));
 }
 
+// Refit-only update: positions, Morton order and topology are unchanged, only the
+// radii moved (progressive shrink, integrators/photonbeam.cpp:354-356,562).  Re-reads each photon's
+// radius from the store and rewrites the sorted record's .w and the leaf box -- the same arithmetic
+// as k_gather, so the refitted tree is bit-identical to a full rebuild.
+__global__ void __launch_bounds__(256) k_releaf(const float4 *__restrict__ pos_r,
+                                                const uint32_t *__restrict__ order, uint32_t n,
+                                                float4 *__restrict__ s_pos_r, float4 *__restrict__ leaf_lo,
+                                                float4 *__restrict__ leaf_hi, uint32_t *__restrict__ bnd) {
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    float amax = 0.f;
+    if (s < n) {
+        float4 p = s_pos_r[s];
+        p.w = __ldg(&pos_r[__ldg(order + s)].w);
+        s_pos_r[s] = p;
+        float rp = fmul(p.w, 1.000002f);
+        float4 lo, hi;
+        lo.x = next_down(fsub(p.x, rp)); hi.x = next_up(fadd(p.x, rp));
+        lo.y = next_down(fsub(p.y, rp)); hi.y = next_up(fadd(p.y, rp));
+        lo.z = next_down(fsub(p.z, rp)); hi.z = next_up(fadd(p.z, rp));
+        lo.w = 0.f; hi.w = 0.f;
+        leaf_lo[s] = lo;
+        leaf_hi[s] = hi;
+        amax = fmaxf(fmaxf(fmaxf(fabsf(lo.x), fabsf(hi.x)), fmaxf(fabsf(lo.y), fabsf(hi.y))),
+                     fmaxf(fabsf(lo.z), fabsf(hi.z)));
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    if ((threadIdx.x & 31) == 0 && amax > 0.f) atomicMax(bnd + 6, __float_as_uint(amax));
+}
+
 // ---------------------------------------------------------------- Karras radix tree
 __device__ __forceinline__ int delta64(const uint32_t *__restrict__ codes,
                                        const uint32_t *__restrict__ order, uint64_t ki, int j,
@@ -400,8 +430,44 @@ __global__ void __launch_bounds__(256) k_emit_fast(int n, int maxLeaf,
 }
 
 // ---------------------------------------------------------------- host driver
+static int refit_tree(bre_ctx *ctx) {
+    const uint32_t n = ctx->n_built;
+    cudaStream_t st = ctx->stream;
+    const int g256 = (int)((n + 255) / 256);
+    uint32_t *bnd = (uint32_t *)ctx->scratch.p;
+    {
+        PhaseTimer pt(ctx, PH_BUILD);
+        BRE_CUDA(cudaMemsetAsync(bnd + 6, 0, 4, st));
+        k_releaf<<<g256, 256, 0, st>>>((const float4 *)ctx->pos_r.p, (const uint32_t *)ctx->order.p, n,
+                                       (float4 *)ctx->s_pos_r.p, (float4 *)ctx->leaf_lo.p,
+                                       (float4 *)ctx->leaf_hi.p, bnd);
+        if (n > 1) {
+            BRE_CUDA(cudaMemsetAsync(ctx->flags.p, 0, (size_t)n * 4, st));
+            k_refit<<<g256, 256, 0, st>>>((int)n, (float4 *)ctx->node_lo.p, (float4 *)ctx->node_hi.p,
+                                          (const float4 *)ctx->leaf_lo.p, (const float4 *)ctx->leaf_hi.p,
+                                          (const int *)ctx->parent.p, (uint32_t *)ctx->flags.p);
+            k_emit_fast<<<g256, 256, 0, st>>>((int)n, ctx->max_leaf, (const float4 *)ctx->node_lo.p,
+                                              (const float4 *)ctx->node_hi.p,
+                                              (const int2 *)ctx->node_range.p,
+                                              (const float4 *)ctx->leaf_lo.p,
+                                              (const float4 *)ctx->leaf_hi.p, (FastNode *)ctx->fast.p);
+        }
+    }
+    BRE_CUDA(cudaGetLastError());
+    uint32_t amaxBits = 0;
+    BRE_CUDA(cudaMemcpyAsync(&amaxBits, bnd + 6, 4, cudaMemcpyDeviceToHost, st));
+    BRE_CUDA(cudaStreamSynchronize(st));
+    memcpy(&ctx->abs_max, &amaxBits, 4);
+    ctx->built = true;
+    ctx->last_build_kind = 2;
+    return BRE_OK;
+}
+
 int build_tree(bre_ctx *ctx) {
     ctx->built = false;
+    // only radii changed since the last full build (bre_set_radius): keep order and topology
+    if (ctx->topo_valid && ctx->n_built == ctx->n_photons && ctx->n_built > 0) return refit_tree(ctx);
+    ctx->topo_valid = false;
     if (ctx->n_photons >= BRE_MAX_PHOTONS)
         return set_err(ctx, BRE_ERR_UNSUPPORTED, "photon count exceeds 2^27 (leaf reference encoding)");
     const uint32_t n = (uint32_t)ctx->n_photons;
@@ -478,6 +544,8 @@ int build_tree(bre_ctx *ctx) {
     memcpy(&ctx->abs_max, &amaxBits, 4);
     ctx->root_ref = (n <= (uint32_t)ctx->max_leaf) ? leaf_ref(0u, n) : 0;
     ctx->built = true;
+    ctx->topo_valid = true;
+    ctx->last_build_kind = 1;
     return BRE_OK;
 }
 

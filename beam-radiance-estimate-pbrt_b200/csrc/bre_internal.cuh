@@ -128,6 +128,8 @@ struct bre_ctx {
     bre::Buf pos_r, pow, dir;
     // build products
     bool built = false;
+    bool topo_valid = false;     // order/topology of the last full build still match the photon positions
+    int last_build_kind = 0;     // 0 none, 1 full build, 2 refit only
     uint32_t n_built = 0;
     bre::Buf s_pos_r, s_pow, s_dir, order, codes, keys_alt, vals_alt, hist, node_lo, node_hi,
         node_range, parent, leaf_lo, leaf_hi, flags, fast, scratch;

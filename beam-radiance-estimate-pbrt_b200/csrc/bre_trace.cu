@@ -438,7 +438,7 @@ int trace_photons(bre_ctx *ctx, uint64_t first, uint64_t nPathsTotal, int maxDep
     MeshDev mesh{ctx->n_tri, (const float4 *)ctx->tri.p, (const float *)ctx->tri_kdb.p};
     if (maxDepth < 1) return set_err(ctx, BRE_ERR_INVALID, "max_depth must be >= 1");
     const uint64_t CHUNK = 1u << 22;
-    ctx->built = false;
+    ctx->built = false; ctx->topo_valid = false;
     PhaseTimer pt(ctx, PH_TRACE);
     for (uint64_t done = 0; done < nPathsTotal; done += CHUNK) {
         uint32_t nPaths = (uint32_t)((nPathsTotal - done) < CHUNK ? (nPathsTotal - done) : CHUNK);

@@ -302,9 +302,14 @@ void BreIntegrator::Render(const Scene &scene) {
     ProgressReporter progress(nIterations, "Rendering (bre)");
     for (int iter = 0; iter < nIterations; ++iter) {
         // ---- photon pass (photonbeam.cpp:365-437): path indices iter*nPaths .. as :386-388
-        bool ok = Check(ctx, bre_clear_photons(ctx), "bre_clear_photons");
+        // "reusephotons": the photon map of iteration 0 is kept and only its radius shrinks, so
+        // bre_build degenerates to a refit of the existing LBVH
+        const bool retrace = iter == 0 || !reusePhotons;
+        bool ok = retrace ? Check(ctx, bre_clear_photons(ctx), "bre_clear_photons")
+                          : Check(ctx, bre_set_radius(ctx, radius), "bre_set_radius");
         uint64_t stored = 0;
-        if (ok && deviceTracer)
+        if (!retrace) {
+        } else if (ok && deviceTracer)
             ok = Check(ctx, bre_trace_photons(ctx, (uint64_t)iter * nPaths, nPaths, maxDepth, radius, &stored),
                        "bre_trace_photons");
         else if (ok)
@@ -381,7 +386,7 @@ Integrator *CreateBreIntegrator(const ParamSet &params, std::shared_ptr<const Ca
     }
     return new BreIntegrator(camera, nIterations, photonsPerIter, maxDepth, radius, alpha,
                              std::max(1, writeFreq), renderMedia, tracer == "device", camrays == "device",
-                             device);
+                             params.FindOneBool("reusephotons", false), device);
 }
 
 }  // namespace pbrt

@@ -26,6 +26,8 @@
 //   new: "string camerarays" ["device"|"host"]  device (default) = K0 kernel for a pinhole
 //        PerspectiveCamera over matte triangle scenes (bit-identical rays, no PCIe ray traffic);
 //        falls back to pbrt's camera + Scene::Intersect on the host for anything else.
+//   new: "bool reusephotons" [false]  true = trace photons once, later iterations only shrink the
+//        radius (photonbeam.cpp:562) and refit the LBVH instead of re-tracing and rebuilding.
 #ifndef PBRT_INTEGRATORS_BRE_H
 #define PBRT_INTEGRATORS_BRE_H
 
@@ -41,11 +43,11 @@ class BreIntegrator : public Integrator {
   public:
     BreIntegrator(std::shared_ptr<const Camera> camera, int nIterations, int photonsPerIteration,
                   int maxDepth, Float initialRadius, Float alpha, int writeFrequency,
-                  bool renderMedia, bool deviceTracer, bool deviceCamera, int device)
+                  bool renderMedia, bool deviceTracer, bool deviceCamera, bool reusePhotons, int device)
         : camera(camera), nIterations(nIterations), photonsPerIteration(photonsPerIteration),
           maxDepth(maxDepth), initialRadius(initialRadius), alpha(alpha),
           writeFrequency(writeFrequency), renderMedia(renderMedia), deviceTracer(deviceTracer),
-          deviceCamera(deviceCamera), device(device) {}
+          deviceCamera(deviceCamera), reusePhotons(reusePhotons), device(device) {}
     void Render(const Scene &scene);
 
     // test hook: after Render, photons of the last iteration in reference layout (p, alpha, wi)
@@ -65,7 +67,7 @@ class BreIntegrator : public Integrator {
     const int nIterations, photonsPerIteration, maxDepth;
     const Float initialRadius, alpha;
     const int writeFrequency;
-    const bool renderMedia, deviceTracer, deviceCamera;
+    const bool renderMedia, deviceTracer, deviceCamera, reusePhotons;
     const int device;
 };
 

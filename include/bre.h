@@ -166,6 +166,11 @@ int bre_allgather_photons(bre_ctx *ctx);
  * / HLBVH2Build :427-495 with EncodeMorton3 :134-139, RadixSort :141-182, emitLBVH2 :497-559,
  * flattenBVH2Tree :663-681) and KdTree<Photon> (core/kdtree.h:101-149). */
 int bre_build(bre_ctx *ctx);
+/* When only bre_set_radius was called since the last full build (progressive radius shrink,
+ * integrators/photonbeam.cpp:354-356,562) bre_build keeps the Morton order and the topology and only
+ * refits the boxes; the result is bit-identical to a full rebuild.  Returns 0 = never built,
+ * 1 = the last bre_build was a full build, 2 = it was a refit. */
+int bre_last_build_kind(bre_ctx *ctx);
 /* Debug/parity: copy the canonical tree back.  order: n u32 (sorted pos -> photon index);
  * codes: n u32; node_lo/node_hi: (n-1)*3 floats; node_children: (n-1)*2 int32 (>=0 internal,
  * <0 = ~sorted leaf position).  Any pointer may be NULL. */
@@ -211,6 +216,19 @@ int bre_film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out);
  * the array a pbrt host passes to Film::SetImage (core/film.cpp:132-140) before Film::WriteImage. */
 int bre_film_mean(bre_ctx *ctx, int iter, float *rgb_out);
 /* Multi-GPU: after resolve on every rank, gather disjoint pixel ranges to rank 0. */
+
+/* ---- on-disk interchange -----------------------------------------------
+ * Photon file: 64-byte header {"BREPHOT\0", u32 version = 1, u32 0, u64 n, u64 n_paths, zeros} then
+ * the three float4 arrays pos_r {x,y,z,radius}, pow {r,g,b,0}, dir {wx,wy,wz,0}, little endian.
+ * n_paths = emitted photon paths (the estimate's normaliser), carried for the consumer. */
+int bre_save_photons(bre_ctx *ctx, const char *path, uint64_t n_paths);
+int bre_load_photons(bre_ctx *ctx, const char *path, int append, uint64_t *n_loaded, uint64_t *n_paths);
+/* Film checkpoint: 64-byte header {"BREFILM\0", u32 version = 1, u32 n_pixels, u64 iterations_done,
+ * u64 0, f32 radius, zeros} then the float4 accumulators.  Makes a multi-iteration render resumable
+ * (the reference's "startiteration", integrators/photonbeam.cpp:354-356,594-595, only restores the
+ * radius).  A failed load leaves the film untouched. */
+int bre_film_save(bre_ctx *ctx, const char *path, uint64_t iterations_done, float radius);
+int bre_film_load(bre_ctx *ctx, const char *path, uint64_t *iterations_done, float *radius);
 
 /* ---- device timing ------------------------------------------------------------------
  * With timing enabled every phase is bracketed by CUDA events on the context stream.

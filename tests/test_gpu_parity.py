@@ -283,3 +283,35 @@ def test_heavy_ray_skew(oracle, ctx):
     rgb, offs, idx = ctx.query(ro, rd, float(n), want_hits=True)
     assert np.array_equal(offs, ref_offs) and np.array_equal(idx, ref_idx)
     assert_radiance(rgb, ref_rgb)
+
+
+@pytest.mark.parametrize("n", [1, 5, 30000])
+def test_progressive_radius_refit_only(oracle, ctx, n):
+    """after bre_set_radius (r <- r*(i+alpha)/(i+1), integrators/photonbeam.cpp:354-356,562)
+    bre_build keeps order and topology and only refits.  The refitted tree must be bit-identical to
+    a full build at the new radius (= the oracle's), hit sets and radiance must follow the new radius."""
+    pos, pw, dr = setup_uniform(oracle, ctx, n, 24)
+    assert ctx.last_build_kind() == 1
+    r = radius_for(n, 24)
+    ro, rd = oracle.synth_rays_pinhole(40, 30)
+    for it in range(3):
+        r = r * (it + 0.7) / (it + 1)
+        ctx.set_radius(r)
+        with pytest.raises(Exception):
+            ctx.query(ro, rd, float(n))          # stale tree: loud failure, not stale hits
+        ctx.build()
+        assert ctx.last_build_kind() == 2
+        oracle.set_photons(pos, pw, dr, r)
+        oracle.build()
+        for a, b in zip(ctx.download_tree(), oracle.tree_arrays()):
+            assert np.array_equal(np.ascontiguousarray(a).view(np.uint32), np.ascontiguousarray(b).view(np.uint32))
+        ref_rgb, ref_offs, ref_idx, ref_cnt = oracle.query(ro, rd, float(n), want_hits=True)
+        rgb, offs, idx = ctx.query(ro, rd, float(n), want_hits=True)
+        assert np.array_equal(offs, ref_offs) and np.array_equal(idx, ref_idx)
+        assert_radiance(rgb, ref_rgb)
+        cnt = ctx.count(ro, rd)
+        assert cnt["nodes_visited"] == ref_cnt["nodes_visited"] and cnt["disk_tests"] == ref_cnt["disk_tests"]
+    # changing the photons drops the topology: full build again
+    ctx.upload_photons(pos, pw, dr, radius=r)
+    ctx.build()
+    assert ctx.last_build_kind() == 1
