@@ -123,6 +123,8 @@ int bre_create(bre_ctx **out, const bre_config *cfg) {
     {
         const char *qc = getenv("BRE_PAIR_QUEUE_CAP");
         if (qc && atoll(qc) > 0) ctx->pair_queue_cap_override = (uint64_t)atoll(qc);
+        const char *rb = getenv("BRE_RAY_BATCH");
+        if (rb && atoll(rb) > 0) ctx->ray_batch_override = (uint32_t)atoll(rb);
         cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, ctx->device);
     }
     if (ctx->n_ranks > 1) {
@@ -147,6 +149,12 @@ int bre_destroy(bre_ctx *ctx) {
                    &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb};
     for (Buf *b : bufs) if (b->p) cudaFree(b->p);
     if (ctx->lights_d) cudaFree(ctx->lights_d);
+    if (ctx->est_host) cudaFreeHost(ctx->est_host);
+    if (ctx->stream2) {
+        cudaStreamSynchronize(ctx->stream2);
+        for (int i = 0; i < 4; ++i) if (ctx->qev[i]) cudaEventDestroy(ctx->qev[i]);
+        cudaStreamDestroy(ctx->stream2);
+    }
     for (int i = 0; i < 8; ++i)
         for (int j = 0; j < 2; ++j) if (ctx->ev[i][j]) cudaEventDestroy(ctx->ev[i][j]);
     cudaStreamDestroy(ctx->stream);

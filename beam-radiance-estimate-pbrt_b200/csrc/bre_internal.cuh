@@ -141,6 +141,13 @@ struct bre_ctx {
     size_t heavy_half = 0;
     uint32_t heavy_rays = 0;
     int heavy_parity = 0;
+    // ray batching of K5 (bre_query.cu launch_query)
+    uint32_t ray_batch_override = 0;        // BRE_RAY_BATCH (experiments)
+    uint32_t ctr_batches = 0, ctr_batch_rays = 0, ctr_rays = 0;
+    unsigned int *est_host = nullptr;       // pinned copy of the last batch's queue control words
+    uint32_t est_rays = 0;
+    cudaStream_t stream2 = nullptr;
+    cudaEvent_t qev[4] = {};
     bre::Buf rays_o, rays_d, out_rgb, tau, hit_counts, hit_offsets, hit_idx, counters_d, pix_idx;
     bre_counters counters{};
     // film

@@ -8,6 +8,7 @@
 #include "bre_internal.cuh"
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 namespace bre {
@@ -186,80 +187,167 @@ constexpr int QT = 128;
 #include "bre_query_warp.cuh"
 namespace bre {
 
-// Launch K5a (traversal -> pair queue) and K5b (pairs -> radiance / hit lists) back to back.
+// One block of launch state per ray batch, in ctx->packet_ctr (stride QB_STRIDE bytes):
+//   +0   queue control words (QC_*), zeroed before every launch
+//   +64  zero word + the two heavy-packet counters (persist from launch to launch)
+//   +128 this batch's LeafArgs (read by the cold in-place path of K5a)
+constexpr size_t QB_STRIDE = 512, QB_HEAVY = 64, QB_ARGS = 128;
+static_assert(QB_ARGS + sizeof(LeafArgs) <= QB_STRIDE, "batch block too small");
+
+__host__ __device__ inline LeafArgs shift_args(LeafArgs A, size_t off) {
+    A.ro += off; A.rd += off;
+    if (A.out) A.out += off;
+    if (A.tau) A.tau += off * (size_t)(A.tauSteps + 1);
+    if (A.span) A.span += off;
+    if (A.hitCounts) A.hitCounts += off;
+    if (A.hitOffsets) A.hitOffsets += off;
+    return A;
+}
+__global__ void k_store_batch_args(LeafArgs A, char *blocks, unsigned batchRays, unsigned nBatches) {
+    unsigned b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nBatches) return;
+    *reinterpret_cast<LeafArgs *>(blocks + b * QB_STRIDE + QB_ARGS) = shift_args(A, (size_t)b * batchRays);
+}
+
+// Launch K5a (traversal -> pair queue) and K5b (pairs -> radiance / hit lists).
+//
+// Rays are processed in BATCHES so that the pair queue stays bounded whatever the ray count
+// (a 4K camera emits ~5e8 pairs): batch size = queue capacity / (pairs per ray measured on the
+// previous launch, +30 %).  With more than one batch the queue is split in two halves and the
+// batches are software-pipelined over two streams -- K5b of batch i runs while K5a of batch i+1
+// walks the tree -- so the tail of one kernel (a few heavy packets / the last waves) is filled by
+// the other.  A single batch runs exactly as before on the context stream.
 template <int MODE, bool COUNT>
 static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, float nPathsNorm,
                         float4 *out, const float *tau, const float2 *span, uint32_t *hitCounts,
                         const uint64_t *hitOffsets, uint32_t *hitIdx, unsigned long long *counters) {
     int s;
-    // pair queue: room for 128 pairs per ray (measured means: 25-50), at least 1M, at most 256M pairs
+    // ---- pair queue capacity: 128 pairs per ray, at least 1M, at most 256M pairs (2 GiB)
     uint64_t want = (uint64_t)n * 128u;
     if (want < (1u << 20)) want = 1u << 20;
     if (want > (1u << 28)) want = 1u << 28;
     if (ctx->pair_queue_cap_override) want = ctx->pair_queue_cap_override;
+    // ---- batch size from the last launch's measured demand (pinned host copy of its control words)
+    if (!ctx->est_host) {
+        BRE_CUDA(cudaHostAlloc((void **)&ctx->est_host, 64, cudaHostAllocDefault));
+        memset(ctx->est_host, 0, 64);
+    }
+    double est = 128.0;
+    if (ctx->est_rays && ctx->est_host[QC_PAIR_TAIL]) {
+        est = 1.3 * (double)ctx->est_host[QC_PAIR_TAIL] / (double)ctx->est_rays;
+        if (est < 16.0) est = 16.0;
+    }
+    uint32_t batchRays = n;
+    if ((double)n * est > (double)want) {
+        // two halves in flight: each batch must fit half the queue
+        uint64_t fit = (uint64_t)((double)(want / 2) / est);
+        fit &= ~(uint64_t)(WQ_P * WQ_WARPS - 1);
+        if (fit < 4096) fit = 4096;
+        if (fit < n) batchRays = (uint32_t)fit;
+    }
+    if (ctx->ray_batch_override && ctx->ray_batch_override < n)
+        batchRays = (ctx->ray_batch_override + WQ_P - 1) / WQ_P * WQ_P;
+    const uint32_t nBatches = (n + batchRays - 1) / batchRays;
+    const bool piped = nBatches > 1;
+    const unsigned cap = (unsigned)(piped ? want / 2 : want);
     if ((s = ensure(ctx, ctx->pair_queue, (size_t)want * 8)) != BRE_OK) return s;
-    // packet_ctr layout: control words (64 B) | zero word + 2 heavy counters (64 B) | LeafArgs copy
-    const size_t argsOff = 256;
-    if ((s = ensure(ctx, ctx->packet_ctr, argsOff + sizeof(LeafArgs))) != BRE_OK) return s;
-    const unsigned cap = (unsigned)want;
-    unsigned int *ctl = (unsigned int *)ctx->packet_ctr.p;
-    unsigned int *heavyCnt = ctl + 16;      // [0] always zero, [1 + parity] heavy packets of a launch
-    BRE_CUDA(cudaMemsetAsync(ctl, 0, 68, ctx->stream));
+    if ((s = ensure(ctx, ctx->packet_ctr, (size_t)nBatches * QB_STRIDE)) != BRE_OK) return s;
+    if (ctx->ctr_batches != nBatches || ctx->ctr_batch_rays != batchRays || ctx->ctr_rays != n) {
+        // new batch layout: the persistent heavy counters of the old one mean nothing
+        BRE_CUDA(cudaMemsetAsync(ctx->packet_ctr.p, 0, (size_t)nBatches * QB_STRIDE, ctx->stream));
+        ctx->ctr_batches = nBatches; ctx->ctr_batch_rays = batchRays; ctx->ctr_rays = n;
+        ctx->heavy_rays = 0;
+    }
+    char *blocks = (char *)ctx->packet_ctr.p;
+    BRE_CUDA(cudaMemset2DAsync(blocks, QB_STRIDE, 0, QB_HEAVY + 4, nBatches, ctx->stream));
     if (MODE == 0) BRE_CUDA(cudaMemsetAsync(out, 0, (size_t)n * 16, ctx->stream));
     else BRE_CUDA(cudaMemsetAsync(hitCounts, 0, (size_t)n * 4, ctx->stream));
     LeafArgs A;
     A.t = tree_view(ctx); A.m = ctx->medium; A.ro = ro; A.rd = rd; A.nPathsNorm = nPathsNorm;
     A.out = out; A.tau = tau; A.span = span; A.tauSteps = ctx->tau_steps;
     A.hitCounts = hitCounts; A.hitOffsets = hitOffsets; A.hitIdx = hitIdx;
-    LeafArgs *Ag = (LeafArgs *)((char *)ctx->packet_ctr.p + argsOff);   // copy for the cold overflow path
-    k_store_args<<<1, 1, 0, ctx->stream>>>(A, Ag);
-    // heavy-first feedback between consecutive radiance queries over the same ray count
-    const unsigned packets = (n + WQ_P - 1) / WQ_P;
-    const unsigned *heavyIn = nullptr, *heavyFlagIn = nullptr, *nHeavyIn = heavyCnt;
-    unsigned *heavyOut = nullptr, *heavyFlagOut = nullptr, *nHeavyOut = heavyCnt;
-    unsigned heavyCap = 0;
-    if (MODE == 0 && !COUNT) {
-        const size_t flagWords = (packets + 31) / 32;
-        const size_t half = ((size_t)HEAVY_CAP + flagWords) * 4;
-        if ((s = ensure(ctx, ctx->heavy, 2 * half)) != BRE_OK) return s;
+    k_store_batch_args<<<(nBatches + 63) / 64, 64, 0, ctx->stream>>>(A, blocks, batchRays, nBatches);
+
+    // ---- heavy-first feedback between consecutive radiance queries over the same rays
+    const unsigned batchPackets = (batchRays + WQ_P - 1) / WQ_P;
+    const size_t flagWords = (batchPackets + 31) / 32;
+    const size_t half = ((size_t)HEAVY_CAP + flagWords) * 4;
+    const bool feedback = MODE == 0 && !COUNT;
+    bool haveIn = false;
+    int cur = 0, prev = 1;
+    if (feedback) {
+        if ((s = ensure(ctx, ctx->heavy, (size_t)nBatches * 2 * half)) != BRE_OK) return s;
         if (ctx->heavy_half != half) { ctx->heavy_half = half; ctx->heavy_rays = 0; }   // buffer re-laid out
-        const int cur = ctx->heavy_parity, prev = cur ^ 1;
-        unsigned *bufCur = (unsigned *)((char *)ctx->heavy.p + cur * half);
-        unsigned *bufPrev = (unsigned *)((char *)ctx->heavy.p + prev * half);
-        heavyOut = bufCur; heavyFlagOut = bufCur + HEAVY_CAP; nHeavyOut = heavyCnt + 1 + cur;
-        heavyCap = HEAVY_CAP;
-        BRE_CUDA(cudaMemsetAsync(heavyFlagOut, 0, flagWords * 4, ctx->stream));
-        BRE_CUDA(cudaMemsetAsync(nHeavyOut, 0, 4, ctx->stream));
-        if (ctx->heavy_rays == n) { heavyIn = bufPrev; heavyFlagIn = bufPrev + HEAVY_CAP; nHeavyIn = heavyCnt + 1 + prev; }
+        cur = ctx->heavy_parity; prev = cur ^ 1;
+        haveIn = ctx->heavy_rays == n;
         ctx->heavy_rays = n;
         ctx->heavy_parity = prev;
     }
-    {
-        PhaseTimer pt(ctx, PH_QUERY_A);
-        int perSM = 0;
-        BRE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_traverse<MODE, COUNT>,
-                                                               WQ_WARPS * 32, 0));
-        if (perSM < 1) perSM = 1;
-        unsigned blocks = (unsigned)(ctx->sm_count * perSM);
-        const unsigned need = (packets + WQ_WARPS - 1) / WQ_WARPS;
-        if (blocks > need) blocks = need;
-        k_traverse<MODE, COUNT><<<blocks, WQ_WARPS * 32, 0, ctx->stream>>>(
-            A, Ag, n, (uint2 *)ctx->pair_queue.p, cap, ctl, heavyIn, nHeavyIn, heavyFlagIn, heavyOut,
-            heavyFlagOut, nHeavyOut, heavyCap, counters);
+    // ---- second stream + events for the pipelined case
+    if (piped && !ctx->stream2) {
+        BRE_CUDA(cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
+        for (int i = 0; i < 4; ++i) BRE_CUDA(cudaEventCreateWithFlags(&ctx->qev[i], cudaEventDisableTiming));
     }
-    {
-        PhaseTimer pt(ctx, PH_QUERY_B);
-        const unsigned gb = (unsigned)ctx->sm_count * 8u;
+    int perSM = 0;
+    BRE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_traverse<MODE, COUNT>, WQ_WARPS * 32, 0));
+    if (perSM < 1) perSM = 1;
+    const unsigned gb = (unsigned)ctx->sm_count * 8u;
+    if (ctx->timing) cudaEventRecord(ctx->ev[PH_QUERY_A][0], ctx->stream);
+    for (uint32_t b = 0; b < nBatches; ++b) {
+        const uint32_t r0 = b * batchRays, nb = (n - r0 < batchRays) ? n - r0 : batchRays;
+        const LeafArgs Ab = shift_args(A, r0);
+        unsigned int *ctl = (unsigned int *)(blocks + b * QB_STRIDE);
+        unsigned int *heavyCnt = (unsigned int *)(blocks + b * QB_STRIDE + QB_HEAVY);
+        const LeafArgs *Ag = (const LeafArgs *)(blocks + b * QB_STRIDE + QB_ARGS);
+        uint2 *queue = (uint2 *)ctx->pair_queue.p + (piped ? (size_t)(b & 1u) * cap : 0);
+        const unsigned *heavyIn = nullptr, *heavyFlagIn = nullptr, *nHeavyIn = heavyCnt;
+        unsigned *heavyOut = nullptr, *heavyFlagOut = nullptr, *nHeavyOut = heavyCnt;
+        unsigned heavyCap = 0;
+        if (feedback) {
+            unsigned *bufCur = (unsigned *)((char *)ctx->heavy.p + ((size_t)b * 2 + cur) * half);
+            unsigned *bufPrev = (unsigned *)((char *)ctx->heavy.p + ((size_t)b * 2 + prev) * half);
+            heavyOut = bufCur; heavyFlagOut = bufCur + HEAVY_CAP; nHeavyOut = heavyCnt + 1 + cur;
+            heavyCap = HEAVY_CAP;
+            BRE_CUDA(cudaMemsetAsync(heavyFlagOut, 0, flagWords * 4, ctx->stream));
+            BRE_CUDA(cudaMemsetAsync(nHeavyOut, 0, 4, ctx->stream));
+            if (haveIn) { heavyIn = bufPrev; heavyFlagIn = bufPrev + HEAVY_CAP; nHeavyIn = heavyCnt + 1 + prev; }
+        }
+        // the queue half of batch b was last read by K5b of batch b-2
+        if (piped && b >= 2) BRE_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->qev[2 + (b & 1u)], 0));
+        unsigned blocksA = (unsigned)(ctx->sm_count * perSM);
+        const unsigned need = ((nb + WQ_P - 1) / WQ_P + WQ_WARPS - 1) / WQ_WARPS;
+        if (blocksA > need) blocksA = need;
+        k_traverse<MODE, COUNT><<<blocksA, WQ_WARPS * 32, 0, ctx->stream>>>(
+            Ab, Ag, nb, queue, cap, ctl, heavyIn, nHeavyIn, heavyFlagIn, heavyOut, heavyFlagOut, nHeavyOut,
+            heavyCap, counters);
+        cudaStream_t sb = ctx->stream;
+        if (piped) {
+            BRE_CUDA(cudaEventRecord(ctx->qev[b & 1u], ctx->stream));
+            BRE_CUDA(cudaStreamWaitEvent(ctx->stream2, ctx->qev[b & 1u], 0));
+            sb = ctx->stream2;
+        }
+        if (b + 1 == nBatches) {
+            // demand of this launch -> batch size of the next one
+            BRE_CUDA(cudaMemcpyAsync(ctx->est_host, ctl, 32, cudaMemcpyDeviceToHost, ctx->stream));
+            ctx->est_rays = nb;
+            if (ctx->timing) {
+                cudaEventRecord(ctx->ev[PH_QUERY_A][1], ctx->stream); ctx->ev_valid[PH_QUERY_A] = true;
+                cudaEventRecord(ctx->ev[PH_QUERY_B][0], ctx->stream);
+            }
+        }
         if (ctx->max_leaf <= 4)
-            k_leaf_pairs<MODE, COUNT, 4><<<gb, LP_WARPS * 32, 0, ctx->stream>>>(
-                A, (const uint2 *)ctx->pair_queue.p, cap, ctl, counters);
+            k_leaf_pairs<MODE, COUNT, 4><<<gb, LP_WARPS * 32, 0, sb>>>(Ab, queue, cap, ctl, counters);
         else if (ctx->max_leaf <= 8)
-            k_leaf_pairs<MODE, COUNT, 8><<<gb, LP_WARPS * 32, 0, ctx->stream>>>(
-                A, (const uint2 *)ctx->pair_queue.p, cap, ctl, counters);
+            k_leaf_pairs<MODE, COUNT, 8><<<gb, LP_WARPS * 32, 0, sb>>>(Ab, queue, cap, ctl, counters);
         else
-            k_leaf_pairs<MODE, COUNT, 16><<<gb, LP_WARPS * 32, 0, ctx->stream>>>(
-                A, (const uint2 *)ctx->pair_queue.p, cap, ctl, counters);
+            k_leaf_pairs<MODE, COUNT, 16><<<gb, LP_WARPS * 32, 0, sb>>>(Ab, queue, cap, ctl, counters);
+        if (piped) BRE_CUDA(cudaEventRecord(ctx->qev[2 + (b & 1u)], ctx->stream2));
     }
+    if (piped) {   // join: everything K5b did is ordered before what follows on the context stream
+        BRE_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->qev[2], 0));
+        BRE_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->qev[3], 0));
+    }
+    if (ctx->timing) { cudaEventRecord(ctx->ev[PH_QUERY_B][1], ctx->stream); ctx->ev_valid[PH_QUERY_B] = true; }
     BRE_CUDA(cudaGetLastError());
     return BRE_OK;
 }
@@ -367,13 +455,18 @@ int run_count(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd) {
     ctx->counters.bytes_algorithmic = 48ull * n + 32ull * h[0] + 16ull * h[1] + 32ull * h[2];
     ctx->counters.fast_nodes = h[3];
     ctx->counters.fast_disk_tests = h[4];
-    unsigned int ctl[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    uint64_t emitted = 0, inplace = 0;
     if (n > 0) {
-        BRE_CUDA(cudaMemcpyAsync(ctl, ctx->packet_ctr.p, 32, cudaMemcpyDeviceToHost, ctx->stream));
+        std::vector<unsigned int> ctl((size_t)ctx->ctr_batches * QB_STRIDE / 4);
+        BRE_CUDA(cudaMemcpyAsync(ctl.data(), ctx->packet_ctr.p, ctl.size() * 4, cudaMemcpyDeviceToHost, ctx->stream));
         BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+        for (uint32_t b = 0; b < ctx->ctr_batches; ++b) {
+            emitted += ctl[b * QB_STRIDE / 4 + QC_EMITTED];
+            inplace += ctl[b * QB_STRIDE / 4 + QC_INPLACE];
+        }
     }
-    ctx->counters.leaf_pairs = ctl[QC_EMITTED];
-    ctx->counters.pair_queue_overflow = ctl[QC_INPLACE];
+    ctx->counters.leaf_pairs = emitted;
+    ctx->counters.pair_queue_overflow = inplace;
     return BRE_OK;
 }
 

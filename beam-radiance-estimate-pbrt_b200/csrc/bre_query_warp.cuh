@@ -224,7 +224,6 @@ __device__ __noinline__ void process_pair_inplace(const LeafArgs *Ag, uint32_t q
         }
     }
 }
-__global__ void k_store_args(LeafArgs A, LeafArgs *dst) { *dst = A; }
 
 __device__ __forceinline__ unsigned ld_volatile_u32(const unsigned *p) {
     return *reinterpret_cast<const volatile unsigned *>(p);
