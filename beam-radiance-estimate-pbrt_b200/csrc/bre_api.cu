@@ -352,6 +352,10 @@ int bre_download_tree(bre_ctx *ctx, uint32_t *order, uint32_t *codes, float *nod
     if (!ctx->built) return set_err(ctx, BRE_ERR_INVALID, "bre_build has not been called");
     uint32_t n = ctx->n_built;
     if (n == 0) return BRE_OK;
+    {
+        int s = ensure_canonical(ctx);
+        if (s != BRE_OK) return s;
+    }
     if (order) BRE_CUDA(cudaMemcpyAsync(order, ctx->order.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
     if (codes) BRE_CUDA(cudaMemcpyAsync(codes, ctx->codes.p, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
     BRE_CUDA(cudaStreamSynchronize(ctx->stream));

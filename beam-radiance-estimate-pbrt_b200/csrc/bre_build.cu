@@ -259,11 +259,26 @@ __global__ void __launch_bounds__(RS_THREADS) k_rs_scatter(
 }
 
 // ---------------------------------------------------------------- gather to Morton order
+// leaf box: sphere bound p +- r*(1+2e-6), then one ulp outward (DESIGN.md "conservative cull")
+__device__ __forceinline__ void leaf_box(const float4 p, float4 &lo, float4 &hi) {
+    const float rp = fmul(p.w, 1.000002f);
+    lo.x = next_down(fsub(p.x, rp)); hi.x = next_up(fadd(p.x, rp));
+    lo.y = next_down(fsub(p.y, rp)); hi.y = next_up(fadd(p.y, rp));
+    lo.z = next_down(fsub(p.z, rp)); hi.z = next_up(fadd(p.z, rp));
+    lo.w = 0.f; hi.w = 0.f;
+}
+__device__ __forceinline__ float box_abs_max(const float4 lo, const float4 hi) {
+    return fmaxf(fmaxf(fmaxf(fabsf(lo.x), fabsf(hi.x)), fmaxf(fabsf(lo.y), fabsf(hi.y))),
+                 fmaxf(fabsf(lo.z), fabsf(hi.z)));
+}
+
+// The per-photon leaf boxes are NOT stored on the hot path: the production tree's boxes are
+// derived from the Morton-ordered photons directly (k_refit_fast, k_emit_fast); the canonical
+// 1-photon-per-leaf boxes are materialised on demand (ensure_canonical) for counting / parity.
 __global__ void __launch_bounds__(256) k_gather(
     const float4 *__restrict__ pos_r, const float4 *__restrict__ pw, const float4 *__restrict__ dr,
     const uint32_t *__restrict__ order, uint32_t n, float4 *__restrict__ s_pos_r,
-    float4 *__restrict__ s_pow, float4 *__restrict__ s_dir, float4 *__restrict__ leaf_lo,
-    float4 *__restrict__ leaf_hi, uint32_t *__restrict__ bnd) {
+    float4 *__restrict__ s_pow, float4 *__restrict__ s_dir, uint32_t *__restrict__ bnd) {
     uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     float amax = 0.f;
     if (s < n) {
@@ -272,21 +287,24 @@ __global__ void __launch_bounds__(256) k_gather(
         s_pos_r[s] = p;
         s_pow[s] = __ldg(pw + i);
         s_dir[s] = __ldg(dr + i);
-        // leaf box: sphere bound p +- r*(1+2e-6), then one ulp outward (DESIGN.md "conservative cull")
-        float rp = fmul(p.w, 1.000002f);
         float4 lo, hi;
-        lo.x = next_down(fsub(p.x, rp)); hi.x = next_up(fadd(p.x, rp));
-        lo.y = next_down(fsub(p.y, rp)); hi.y = next_up(fadd(p.y, rp));
-        lo.z = next_down(fsub(p.z, rp)); hi.z = next_up(fadd(p.z, rp));
-        lo.w = 0.f; hi.w = 0.f;
-        leaf_lo[s] = lo;
-        leaf_hi[s] = hi;
-        amax = fmaxf(fmaxf(fmaxf(fabsf(lo.x), fabsf(hi.x)), fmaxf(fabsf(lo.y), fabsf(hi.y))),
-                     fmaxf(fabsf(lo.z), fabsf(hi.z)));
+        leaf_box(p, lo, hi);
+        amax = box_abs_max(lo, hi);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
     if ((threadIdx.x & 31) == 0 && amax > 0.f) atomicMax(bnd + 6, __float_as_uint(amax));
+}
+
+__global__ void __launch_bounds__(256) k_leafboxes(const float4 *__restrict__ s_pos_r, uint32_t n,
+                                                   float4 *__restrict__ leaf_lo,
+                                                   float4 *__restrict__ leaf_hi) {
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    float4 lo, hi;
+    leaf_box(__ldg(s_pos_r + s), lo, hi);
+    leaf_lo[s] = lo;
+    leaf_hi[s] = hi;
 }
 
 // Refit-only update: positions, Morton order and topology are unchanged, only the
@@ -295,24 +313,16 @@ __global__ void __launch_bounds__(256) k_gather(
 // as k_gather, so the refitted tree is bit-identical to a full rebuild.
 __global__ void __launch_bounds__(256) k_releaf(const float4 *__restrict__ pos_r,
                                                 const uint32_t *__restrict__ order, uint32_t n,
-                                                float4 *__restrict__ s_pos_r, float4 *__restrict__ leaf_lo,
-                                                float4 *__restrict__ leaf_hi, uint32_t *__restrict__ bnd) {
+                                                float4 *__restrict__ s_pos_r, uint32_t *__restrict__ bnd) {
     uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
     float amax = 0.f;
     if (s < n) {
         float4 p = s_pos_r[s];
         p.w = __ldg(&pos_r[__ldg(order + s)].w);
         s_pos_r[s] = p;
-        float rp = fmul(p.w, 1.000002f);
         float4 lo, hi;
-        lo.x = next_down(fsub(p.x, rp)); hi.x = next_up(fadd(p.x, rp));
-        lo.y = next_down(fsub(p.y, rp)); hi.y = next_up(fadd(p.y, rp));
-        lo.z = next_down(fsub(p.z, rp)); hi.z = next_up(fadd(p.z, rp));
-        lo.w = 0.f; hi.w = 0.f;
-        leaf_lo[s] = lo;
-        leaf_hi[s] = hi;
-        amax = fmaxf(fmaxf(fmaxf(fabsf(lo.x), fabsf(hi.x)), fmaxf(fabsf(lo.y), fabsf(hi.y))),
-                     fmaxf(fabsf(lo.z), fabsf(hi.z)));
+        leaf_box(p, lo, hi);
+        amax = box_abs_max(lo, hi);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
@@ -392,12 +402,69 @@ __global__ void __launch_bounds__(256) k_refit(int n, float4 *node_lo, float4 *n
     }
 }
 
+// Hot-path refit: only the nodes the production tree keeps.  A "fat leaf" is a subtree of
+// <= maxLeaf photons whose parent is larger; its box is the union of its photons' boxes, computed
+// straight from the Morton-ordered records (contiguous, <= 128 bytes).  Threads [0, n-1) are
+// internal nodes -- fat-leaf roots write their box and start a climb; threads [n-1, 2n-1) are
+// single photons hanging directly off a large node -- they only start a climb.  Climbing is the
+// usual second-arrival-continues scheme.  Nodes inside fat leaves are never touched (7/8 of the
+// tree at maxLeaf 8).  min/max are exact, so every box equals the canonical bottom-up union.
+__global__ void __launch_bounds__(256) k_refit_fast(int n, int maxLeaf, float4 *node_lo, float4 *node_hi,
+                                                    const int2 *__restrict__ node_range,
+                                                    const int *__restrict__ parent,
+                                                    const float4 *__restrict__ s_pos_r,
+                                                    uint32_t *__restrict__ flags) {
+    int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= 2 * n - 1) return;
+    int cur;
+    if (tid < n - 1) {
+        const int2 rg = __ldg(node_range + tid);
+        if (rg.y - rg.x + 1 > maxLeaf) return;
+        cur = __ldg(parent + tid);
+        if (cur >= 0) {
+            const int2 pr = __ldg(node_range + cur);
+            if (pr.y - pr.x + 1 <= maxLeaf) return;   // strictly inside a fat leaf
+        }
+        float4 lo, hi;
+        leaf_box(__ldg(s_pos_r + rg.x), lo, hi);
+        for (int q = rg.x + 1; q <= rg.y; ++q) {
+            float4 l, h;
+            leaf_box(__ldg(s_pos_r + q), l, h);
+            lo.x = fminf(lo.x, l.x); lo.y = fminf(lo.y, l.y); lo.z = fminf(lo.z, l.z);
+            hi.x = fmaxf(hi.x, h.x); hi.y = fmaxf(hi.y, h.y); hi.z = fmaxf(hi.z, h.z);
+        }
+        lo.w = __ldcg(&node_lo[tid].w); hi.w = __ldcg(&node_hi[tid].w);
+        __stcg(node_lo + tid, lo);
+        __stcg(node_hi + tid, hi);
+    } else {
+        cur = __ldg(parent + tid);     // parent[n-1+s]
+        const int2 pr = __ldg(node_range + cur);
+        if (pr.y - pr.x + 1 <= maxLeaf) return;
+    }
+    while (cur >= 0) {
+        __threadfence();
+        if (atomicAdd(flags + cur, 1u) == 0u) return;  // first arrival: sibling not done yet
+        __threadfence();
+        float4 nlo = __ldcg(node_lo + cur), nhi = __ldcg(node_hi + cur);
+        const int left = __float_as_int(nlo.w), right = __float_as_int(nhi.w);
+        float4 llo, lhi, rlo, rhi;
+        if (left >= 0) { llo = __ldcg(node_lo + left); lhi = __ldcg(node_hi + left); }
+        else leaf_box(__ldg(s_pos_r + ~left), llo, lhi);
+        if (right >= 0) { rlo = __ldcg(node_lo + right); rhi = __ldcg(node_hi + right); }
+        else leaf_box(__ldg(s_pos_r + ~right), rlo, rhi);
+        nlo.x = fminf(llo.x, rlo.x); nlo.y = fminf(llo.y, rlo.y); nlo.z = fminf(llo.z, rlo.z);
+        nhi.x = fmaxf(lhi.x, rhi.x); nhi.y = fmaxf(lhi.y, rhi.y); nhi.z = fmaxf(lhi.z, rhi.z);
+        __stcg(node_lo + cur, nlo);
+        __stcg(node_hi + cur, nhi);
+        cur = __ldg(parent + cur);
+    }
+}
+
 __global__ void __launch_bounds__(256) k_emit_fast(int n, int maxLeaf,
                                                    const float4 *__restrict__ node_lo,
                                                    const float4 *__restrict__ node_hi,
                                                    const int2 *__restrict__ node_range,
-                                                   const float4 *__restrict__ leaf_lo,
-                                                   const float4 *__restrict__ leaf_hi,
+                                                   const float4 *__restrict__ s_pos_r,
                                                    FastNode *__restrict__ fast) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
@@ -416,8 +483,7 @@ __global__ void __launch_bounds__(256) k_emit_fast(int n, int maxLeaf,
             int cnt = cr.y - cr.x + 1;
             ref[k] = cnt <= maxLeaf ? leaf_ref((uint32_t)cr.x, (uint32_t)cnt) : ch[k];
         } else {
-            lo[k] = __ldg(leaf_lo + ~ch[k]);
-            hi[k] = __ldg(leaf_hi + ~ch[k]);
+            leaf_box(__ldg(s_pos_r + ~ch[k]), lo[k], hi[k]);
             ref[k] = leaf_ref((uint32_t)~ch[k], 1u);
         }
     }
@@ -430,6 +496,44 @@ __global__ void __launch_bounds__(256) k_emit_fast(int n, int maxLeaf,
 }
 
 // ---------------------------------------------------------------- host driver
+// production-tree boxes: fat-leaf roots and everything above them, then the 64-byte nodes
+static int launch_refit_emit(bre_ctx *ctx) {
+    const uint32_t n = ctx->n_built;
+    cudaStream_t st = ctx->stream;
+    BRE_CUDA(cudaMemsetAsync(ctx->flags.p, 0, (size_t)n * 4, st));
+    k_refit_fast<<<(int)((2 * (size_t)n - 1 + 255) / 256), 256, 0, st>>>(
+        (int)n, ctx->max_leaf, (float4 *)ctx->node_lo.p, (float4 *)ctx->node_hi.p,
+        (const int2 *)ctx->node_range.p, (const int *)ctx->parent.p, (const float4 *)ctx->s_pos_r.p,
+        (uint32_t *)ctx->flags.p);
+    k_emit_fast<<<(int)((n + 255) / 256), 256, 0, st>>>(
+        (int)n, ctx->max_leaf, (const float4 *)ctx->node_lo.p, (const float4 *)ctx->node_hi.p,
+        (const int2 *)ctx->node_range.p, (const float4 *)ctx->s_pos_r.p, (FastNode *)ctx->fast.p);
+    return BRE_OK;
+}
+
+// Canonical 1-photon-per-leaf boxes (leaf boxes + every internal node), materialised on demand for
+// the counting kernel, bre_download_tree and parity tests; not part of the render path.
+int ensure_canonical(bre_ctx *ctx) {
+    if (ctx->canon_valid || !ctx->built || ctx->n_built == 0) return BRE_OK;
+    const uint32_t n = ctx->n_built;
+    cudaStream_t st = ctx->stream;
+    int s;
+    if ((s = ensure(ctx, ctx->leaf_lo, (size_t)n * 16)) != BRE_OK) return s;
+    if ((s = ensure(ctx, ctx->leaf_hi, (size_t)n * 16)) != BRE_OK) return s;
+    const int g256 = (int)((n + 255) / 256);
+    k_leafboxes<<<g256, 256, 0, st>>>((const float4 *)ctx->s_pos_r.p, n, (float4 *)ctx->leaf_lo.p,
+                                      (float4 *)ctx->leaf_hi.p);
+    if (n > 1) {
+        BRE_CUDA(cudaMemsetAsync(ctx->flags.p, 0, (size_t)n * 4, st));
+        k_refit<<<g256, 256, 0, st>>>((int)n, (float4 *)ctx->node_lo.p, (float4 *)ctx->node_hi.p,
+                                      (const float4 *)ctx->leaf_lo.p, (const float4 *)ctx->leaf_hi.p,
+                                      (const int *)ctx->parent.p, (uint32_t *)ctx->flags.p);
+    }
+    BRE_CUDA(cudaGetLastError());
+    ctx->canon_valid = true;
+    return BRE_OK;
+}
+
 static int refit_tree(bre_ctx *ctx) {
     const uint32_t n = ctx->n_built;
     cudaStream_t st = ctx->stream;
@@ -439,18 +543,10 @@ static int refit_tree(bre_ctx *ctx) {
         PhaseTimer pt(ctx, PH_BUILD);
         BRE_CUDA(cudaMemsetAsync(bnd + 6, 0, 4, st));
         k_releaf<<<g256, 256, 0, st>>>((const float4 *)ctx->pos_r.p, (const uint32_t *)ctx->order.p, n,
-                                       (float4 *)ctx->s_pos_r.p, (float4 *)ctx->leaf_lo.p,
-                                       (float4 *)ctx->leaf_hi.p, bnd);
+                                       (float4 *)ctx->s_pos_r.p, bnd);
         if (n > 1) {
-            BRE_CUDA(cudaMemsetAsync(ctx->flags.p, 0, (size_t)n * 4, st));
-            k_refit<<<g256, 256, 0, st>>>((int)n, (float4 *)ctx->node_lo.p, (float4 *)ctx->node_hi.p,
-                                          (const float4 *)ctx->leaf_lo.p, (const float4 *)ctx->leaf_hi.p,
-                                          (const int *)ctx->parent.p, (uint32_t *)ctx->flags.p);
-            k_emit_fast<<<g256, 256, 0, st>>>((int)n, ctx->max_leaf, (const float4 *)ctx->node_lo.p,
-                                              (const float4 *)ctx->node_hi.p,
-                                              (const int2 *)ctx->node_range.p,
-                                              (const float4 *)ctx->leaf_lo.p,
-                                              (const float4 *)ctx->leaf_hi.p, (FastNode *)ctx->fast.p);
+            int s2 = launch_refit_emit(ctx);
+            if (s2 != BRE_OK) return s2;
         }
     }
     BRE_CUDA(cudaGetLastError());
@@ -459,6 +555,7 @@ static int refit_tree(bre_ctx *ctx) {
     BRE_CUDA(cudaStreamSynchronize(st));
     memcpy(&ctx->abs_max, &amaxBits, 4);
     ctx->built = true;
+    ctx->canon_valid = false;
     ctx->last_build_kind = 2;
     return BRE_OK;
 }
@@ -482,7 +579,6 @@ int build_tree(bre_ctx *ctx) {
     ENS(s_pos_r, n4); ENS(s_pow, n4); ENS(s_dir, n4);
     ENS(order, (size_t)n * 4); ENS(codes, (size_t)n * 4);
     ENS(keys_alt, (size_t)n * 4); ENS(vals_alt, (size_t)n * 4);
-    ENS(leaf_lo, n4); ENS(leaf_hi, n4);
     ENS(node_lo, n4); ENS(node_hi, n4);
     ENS(node_range, (size_t)n * 8); ENS(parent, (size_t)2 * n * 4);
     ENS(flags, (size_t)n * 4); ENS(fast, (size_t)n * sizeof(FastNode));
@@ -520,21 +616,12 @@ int build_tree(bre_ctx *ctx) {
     // after 4 passes kin == codes, vin == order
     k_gather<<<g256, 256, 0, st>>>(pos_r, (const float4 *)ctx->pow.p, (const float4 *)ctx->dir.p,
                                    order, n, (float4 *)ctx->s_pos_r.p, (float4 *)ctx->s_pow.p,
-                                   (float4 *)ctx->s_dir.p, (float4 *)ctx->leaf_lo.p,
-                                   (float4 *)ctx->leaf_hi.p, bnd);
+                                   (float4 *)ctx->s_dir.p, bnd);
     if (n > 1) {
-        BRE_CUDA(cudaMemsetAsync(ctx->flags.p, 0, (size_t)n * 4, st));
         k_karras<<<g256, 256, 0, st>>>(codes, order, (int)n, (float4 *)ctx->node_lo.p,
                                        (float4 *)ctx->node_hi.p, (int2 *)ctx->node_range.p,
                                        (int *)ctx->parent.p);
-        k_refit<<<g256, 256, 0, st>>>((int)n, (float4 *)ctx->node_lo.p, (float4 *)ctx->node_hi.p,
-                                      (const float4 *)ctx->leaf_lo.p, (const float4 *)ctx->leaf_hi.p,
-                                      (const int *)ctx->parent.p, (uint32_t *)ctx->flags.p);
-        k_emit_fast<<<g256, 256, 0, st>>>((int)n, ctx->max_leaf, (const float4 *)ctx->node_lo.p,
-                                          (const float4 *)ctx->node_hi.p,
-                                          (const int2 *)ctx->node_range.p,
-                                          (const float4 *)ctx->leaf_lo.p,
-                                          (const float4 *)ctx->leaf_hi.p, (FastNode *)ctx->fast.p);
+        if ((s = launch_refit_emit(ctx)) != BRE_OK) { delete pt; return s; }
     }
     delete pt;
     BRE_CUDA(cudaGetLastError());
@@ -544,6 +631,7 @@ int build_tree(bre_ctx *ctx) {
     memcpy(&ctx->abs_max, &amaxBits, 4);
     ctx->root_ref = (n <= (uint32_t)ctx->max_leaf) ? leaf_ref(0u, n) : 0;
     ctx->built = true;
+    ctx->canon_valid = false;
     ctx->topo_valid = true;
     ctx->last_build_kind = 1;
     return BRE_OK;

@@ -128,6 +128,7 @@ struct bre_ctx {
     bre::Buf pos_r, pow, dir;
     // build products
     bool built = false;
+    bool canon_valid = false;    // canonical leaf / small-node boxes materialised (ensure_canonical)
     bool topo_valid = false;     // order/topology of the last full build still match the photon positions
     int last_build_kind = 0;     // 0 none, 1 full build, 2 refit only
     uint32_t n_built = 0;
@@ -176,6 +177,7 @@ int check_cuda(bre_ctx *c, cudaError_t e, const char *what);
 
 // build.cu
 int build_tree(bre_ctx *ctx);
+int ensure_canonical(bre_ctx *ctx);
 // query.cu
 int run_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, float nPathsNorm,
               float4 *out);

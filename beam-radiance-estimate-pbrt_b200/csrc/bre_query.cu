@@ -441,6 +441,7 @@ int run_count(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd) {
     unsigned long long *cd = (unsigned long long *)ctx->counters_d.p;
     BRE_CUDA(cudaMemsetAsync(cd, 0, 64, ctx->stream));
     if (n > 0) {
+        if ((s = ensure_canonical(ctx)) != BRE_OK) return s;
         if ((s = ensure(ctx, ctx->hit_counts, (size_t)n * 4)) != BRE_OK) return s;
         k_count_canonical<<<(n + QT - 1) / QT, QT, 0, ctx->stream>>>(tree_view(ctx), n, ro, rd, cd);
         if ((s = launch_query<1, true>(ctx, n, ro, rd, 1.f, nullptr, nullptr, nullptr,
