@@ -345,7 +345,8 @@ __global__ void __launch_bounds__(256) k_karras(const uint32_t *__restrict__ cod
                                                 float4 *__restrict__ node_lo,
                                                 float4 *__restrict__ node_hi,
                                                 int2 *__restrict__ node_range,
-                                                int *__restrict__ parent) {
+                                                int *__restrict__ parent, int maxLeaf,
+                                                unsigned char *__restrict__ entry) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
     uint64_t ki = ((uint64_t)__ldg(codes + i) << 32) | __ldg(order + i);
@@ -373,6 +374,12 @@ __global__ void __launch_bounds__(256) k_karras(const uint32_t *__restrict__ cod
     if (left >= 0) parent[left] = i; else parent[n - 1 + gamma] = i;
     if (right >= 0) parent[right] = i; else parent[n - 1 + gamma + 1] = i;
     if (i == 0) parent[0] = -1;
+    // entry points of the production tree: children of <= maxLeaf photons under a larger node
+    // (a fat-leaf root, or a single photon).  k_refit_fast starts from exactly these.
+    const bool big = last - first + 1 > maxLeaf;
+    entry[left >= 0 ? left : n - 1 + gamma] = big && (gamma - first + 1 <= maxLeaf);
+    entry[right >= 0 ? right : n - 1 + gamma + 1] = big && (last - gamma <= maxLeaf);
+    if (i == 0) entry[0] = !big;
 }
 
 __global__ void __launch_bounds__(256) k_refit(int n, float4 *node_lo, float4 *node_hi,
@@ -406,25 +413,22 @@ __global__ void __launch_bounds__(256) k_refit(int n, float4 *node_lo, float4 *n
 // <= maxLeaf photons whose parent is larger; its box is the union of its photons' boxes, computed
 // straight from the Morton-ordered records (contiguous, <= 128 bytes).  Threads [0, n-1) are
 // internal nodes -- fat-leaf roots write their box and start a climb; threads [n-1, 2n-1) are
-// single photons hanging directly off a large node -- they only start a climb.  Climbing is the
+// single photons hanging directly off a large node -- they only start a climb.  Which threads
+// are such entry points was tagged by k_karras (entry[], one byte each).  Climbing is the
 // usual second-arrival-continues scheme.  Nodes inside fat leaves are never touched (7/8 of the
 // tree at maxLeaf 8).  min/max are exact, so every box equals the canonical bottom-up union.
 __global__ void __launch_bounds__(256) k_refit_fast(int n, int maxLeaf, float4 *node_lo, float4 *node_hi,
                                                     const int2 *__restrict__ node_range,
                                                     const int *__restrict__ parent,
                                                     const float4 *__restrict__ s_pos_r,
+                                                    const unsigned char *__restrict__ entry,
                                                     uint32_t *__restrict__ flags) {
     int tid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tid >= 2 * n - 1) return;
-    int cur;
+    if (tid >= 2 * n - 1 || !__ldg(entry + tid)) return;
+    const int cur0 = __ldg(parent + tid);
+    int cur = cur0;
     if (tid < n - 1) {
         const int2 rg = __ldg(node_range + tid);
-        if (rg.y - rg.x + 1 > maxLeaf) return;
-        cur = __ldg(parent + tid);
-        if (cur >= 0) {
-            const int2 pr = __ldg(node_range + cur);
-            if (pr.y - pr.x + 1 <= maxLeaf) return;   // strictly inside a fat leaf
-        }
         float4 lo, hi;
         leaf_box(__ldg(s_pos_r + rg.x), lo, hi);
         for (int q = rg.x + 1; q <= rg.y; ++q) {
@@ -436,10 +440,6 @@ __global__ void __launch_bounds__(256) k_refit_fast(int n, int maxLeaf, float4 *
         lo.w = __ldcg(&node_lo[tid].w); hi.w = __ldcg(&node_hi[tid].w);
         __stcg(node_lo + tid, lo);
         __stcg(node_hi + tid, hi);
-    } else {
-        cur = __ldg(parent + tid);     // parent[n-1+s]
-        const int2 pr = __ldg(node_range + cur);
-        if (pr.y - pr.x + 1 <= maxLeaf) return;
     }
     while (cur >= 0) {
         __threadfence();
@@ -504,7 +504,7 @@ static int launch_refit_emit(bre_ctx *ctx) {
     k_refit_fast<<<(int)((2 * (size_t)n - 1 + 255) / 256), 256, 0, st>>>(
         (int)n, ctx->max_leaf, (float4 *)ctx->node_lo.p, (float4 *)ctx->node_hi.p,
         (const int2 *)ctx->node_range.p, (const int *)ctx->parent.p, (const float4 *)ctx->s_pos_r.p,
-        (uint32_t *)ctx->flags.p);
+        (const unsigned char *)ctx->entry.p, (uint32_t *)ctx->flags.p);
     k_emit_fast<<<(int)((n + 255) / 256), 256, 0, st>>>(
         (int)n, ctx->max_leaf, (const float4 *)ctx->node_lo.p, (const float4 *)ctx->node_hi.p,
         (const int2 *)ctx->node_range.p, (const float4 *)ctx->s_pos_r.p, (FastNode *)ctx->fast.p);
@@ -581,7 +581,7 @@ int build_tree(bre_ctx *ctx) {
     ENS(keys_alt, (size_t)n * 4); ENS(vals_alt, (size_t)n * 4);
     ENS(node_lo, n4); ENS(node_hi, n4);
     ENS(node_range, (size_t)n * 8); ENS(parent, (size_t)2 * n * 4);
-    ENS(flags, (size_t)n * 4); ENS(fast, (size_t)n * sizeof(FastNode));
+    ENS(entry, (size_t)2 * n); ENS(flags, (size_t)n * 4); ENS(fast, (size_t)n * sizeof(FastNode));
     ENS(scratch, 64);
     const uint32_t numBlocks = (n + RS_TILE - 1) / RS_TILE;
     const uint32_t histLen = 256u * numBlocks;
@@ -620,7 +620,7 @@ int build_tree(bre_ctx *ctx) {
     if (n > 1) {
         k_karras<<<g256, 256, 0, st>>>(codes, order, (int)n, (float4 *)ctx->node_lo.p,
                                        (float4 *)ctx->node_hi.p, (int2 *)ctx->node_range.p,
-                                       (int *)ctx->parent.p);
+                                       (int *)ctx->parent.p, ctx->max_leaf, (unsigned char *)ctx->entry.p);
         if ((s = launch_refit_emit(ctx)) != BRE_OK) { delete pt; return s; }
     }
     delete pt;
