@@ -110,7 +110,7 @@ int bre_create(bre_ctx **out, const bre_config *cfg) {
         if (cfg->max_leaf_photons > 0) ctx->max_leaf = cfg->max_leaf_photons;
         if (cfg->tau_steps > 0) ctx->tau_steps = cfg->tau_steps;
     }
-    if (ctx->device < 0 || ctx->device >= nDev || ctx->max_leaf > 16 || ctx->rank < 0 ||
+    if (ctx->device < 0 || ctx->device >= nDev || ctx->max_leaf > 16 || ctx->tau_steps > 384 || ctx->rank < 0 ||
         ctx->rank >= ctx->n_ranks) {
         delete ctx;
         return BRE_ERR_INVALID;

@@ -119,10 +119,24 @@ __device__ float grid_density(const MediumDev &m, float px, float py, float pz) 
     float fx = floorf(sx), fy = floorf(sy), fz = floorf(sz);
     int ix = (int)fx, iy = (int)fy, iz = (int)fz;
     float dx = fsub(sx, fx), dy = fsub(sy, fy), dz = fsub(sz, fz);
-    float d00 = lerp1(dx, grid_D(m, ix, iy, iz), grid_D(m, ix + 1, iy, iz));
-    float d10 = lerp1(dx, grid_D(m, ix, iy + 1, iz), grid_D(m, ix + 1, iy + 1, iz));
-    float d01 = lerp1(dx, grid_D(m, ix, iy, iz + 1), grid_D(m, ix + 1, iy, iz + 1));
-    float d11 = lerp1(dx, grid_D(m, ix, iy + 1, iz + 1), grid_D(m, ix + 1, iy + 1, iz + 1));
+    float v000, v100, v010, v110, v001, v101, v011, v111;
+    if ((unsigned)ix < (unsigned)(m.nx - 1) && (unsigned)iy < (unsigned)(m.ny - 1) &&
+        (unsigned)iz < (unsigned)(m.nz - 1)) {
+        // all eight taps inside the grid: same values as grid_D without the 48 bounds compares
+        const float *b = m.density + ((size_t)iz * m.ny + iy) * m.nx + ix;
+        const size_t ys = (size_t)m.nx, zs = (size_t)m.nx * m.ny;
+        v000 = __ldg(b); v100 = __ldg(b + 1); v010 = __ldg(b + ys); v110 = __ldg(b + ys + 1);
+        v001 = __ldg(b + zs); v101 = __ldg(b + zs + 1); v011 = __ldg(b + zs + ys); v111 = __ldg(b + zs + ys + 1);
+    } else {
+        v000 = grid_D(m, ix, iy, iz); v100 = grid_D(m, ix + 1, iy, iz);
+        v010 = grid_D(m, ix, iy + 1, iz); v110 = grid_D(m, ix + 1, iy + 1, iz);
+        v001 = grid_D(m, ix, iy, iz + 1); v101 = grid_D(m, ix + 1, iy, iz + 1);
+        v011 = grid_D(m, ix, iy + 1, iz + 1); v111 = grid_D(m, ix + 1, iy + 1, iz + 1);
+    }
+    float d00 = lerp1(dx, v000, v100);
+    float d10 = lerp1(dx, v010, v110);
+    float d01 = lerp1(dx, v001, v101);
+    float d11 = lerp1(dx, v011, v111);
     return lerp1(dz, lerp1(dy, d00, d10), lerp1(dy, d01, d11));
 }
 // Bounds3::IntersectP(ray,&t0,&t1) against the unit cube, geometry.h:1386-1408
@@ -152,34 +166,45 @@ __device__ __forceinline__ void to_medium(const MediumDev &m, const float o[3], 
     }
 }
 
+// One thread per ray; the block's rows are staged in shared memory (row stride steps+1, odd for
+// the default 64 steps -> conflict-free both ways) and written out as one contiguous, fully
+// coalesced slab instead of 65 stores per thread with a 260-byte stride.
 __global__ void __launch_bounds__(128) k_tau_table(MediumDev m, uint32_t n,
                                                    const float4 *__restrict__ ro,
                                                    const float4 *__restrict__ rd, int steps,
                                                    float *__restrict__ tau,
                                                    float2 *__restrict__ span) {
-    uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= n) return;
-    float4 o4 = __ldg(ro + q), d4 = __ldg(rd + q);
-    float o[3] = {o4.x, o4.y, o4.z}, d[3] = {d4.x, d4.y, d4.z}, om[3], dm[3];
-    to_medium(m, o, d, om, dm);
-    float *row = tau + (size_t)q * (steps + 1);
-    float t0, t1;
-    if (!unit_box(om, dm, o4.w, t0, t1)) {
-        for (int k = 0; k <= steps; ++k) row[k] = 0.f;
-        span[q] = make_float2(0.f, 0.f);
-        return;
+    extern __shared__ float rows[];
+    const uint32_t q0 = blockIdx.x * blockDim.x, q = q0 + threadIdx.x;
+    const int stride = steps + 1;
+    float *row = rows + (size_t)threadIdx.x * stride;
+    if (q < n) {
+        float4 o4 = __ldg(ro + q), d4 = __ldg(rd + q);
+        float o[3] = {o4.x, o4.y, o4.z}, d[3] = {d4.x, d4.y, d4.z}, om[3], dm[3];
+        to_medium(m, o, d, om, dm);
+        float t0, t1;
+        if (!unit_box(om, dm, o4.w, t0, t1)) {
+            for (int k = 0; k <= steps; ++k) row[k] = 0.f;
+            span[q] = make_float2(0.f, 0.f);
+        } else {
+            float dt = fdiv(fsub(t1, t0), (float)steps);
+            float acc = 0.f;
+            row[0] = 0.f;
+            for (int k = 0; k < steps; ++k) {
+                float t = fadd(t0, fmul(fadd((float)k, 0.5f), dt));
+                float dens = grid_density(m, fadd(om[0], fmul(dm[0], t)), fadd(om[1], fmul(dm[1], t)),
+                                          fadd(om[2], fmul(dm[2], t)));
+                acc = fadd(acc, fmul(dens, dt));
+                row[k + 1] = acc;
+            }
+            span[q] = make_float2(t0, t1);
+        }
     }
-    float dt = fdiv(fsub(t1, t0), (float)steps);
-    float acc = 0.f;
-    row[0] = 0.f;
-    for (int k = 0; k < steps; ++k) {
-        float t = fadd(t0, fmul(fadd((float)k, 0.5f), dt));
-        float dens = grid_density(m, fadd(om[0], fmul(dm[0], t)), fadd(om[1], fmul(dm[1], t)),
-                                  fadd(om[2], fmul(dm[2], t)));
-        acc = fadd(acc, fmul(dens, dt));
-        row[k + 1] = acc;
-    }
-    span[q] = make_float2(t0, t1);
+    __syncthreads();
+    const uint32_t rowsHere = min((uint32_t)blockDim.x, n - q0);
+    const uint32_t cnt = rowsHere * (uint32_t)stride;
+    float *dst = tau + (size_t)q0 * stride;
+    for (uint32_t i = threadIdx.x; i < cnt; i += blockDim.x) dst[i] = rows[i];
 }
 
 }  // namespace bre
@@ -416,7 +441,11 @@ static int prepare_tau(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 
     float2 *sp = (float2 *)((char *)ctx->tau.p + offSpan);
     {
         PhaseTimer pt(ctx, PH_TAU);
-        k_tau_table<<<(n + 127) / 128, 128, 0, ctx->stream>>>(ctx->medium, n, ro, rd, ctx->tau_steps, tp, sp);
+        const size_t smem = (size_t)128 * (ctx->tau_steps + 1) * 4;   // tau_steps <= 384 (bre_create)
+        if (smem > 48 * 1024)
+            BRE_CUDA(cudaFuncSetAttribute(k_tau_table, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_tau_table<<<(n + 127) / 128, 128, smem, ctx->stream>>>(
+            ctx->medium, n, ro, rd, ctx->tau_steps, tp, sp);
     }
     *tau = tp; *span = sp;
     return BRE_OK;

@@ -107,10 +107,23 @@ __device__ float grid_density_t(const MediumDev &m, float px, float py, float pz
     float fx = floorf(sx), fy = floorf(sy), fz = floorf(sz);
     int ix = (int)fx, iy = (int)fy, iz = (int)fz;
     float dx = fsub(sx, fx), dy = fsub(sy, fy), dz = fsub(sz, fz);
-    float d00 = lerpf(dx, gridD(m, ix, iy, iz), gridD(m, ix + 1, iy, iz));
-    float d10 = lerpf(dx, gridD(m, ix, iy + 1, iz), gridD(m, ix + 1, iy + 1, iz));
-    float d01 = lerpf(dx, gridD(m, ix, iy, iz + 1), gridD(m, ix + 1, iy, iz + 1));
-    float d11 = lerpf(dx, gridD(m, ix, iy + 1, iz + 1), gridD(m, ix + 1, iy + 1, iz + 1));
+    float v000, v100, v010, v110, v001, v101, v011, v111;
+    if ((unsigned)ix < (unsigned)(m.nx - 1) && (unsigned)iy < (unsigned)(m.ny - 1) &&
+        (unsigned)iz < (unsigned)(m.nz - 1)) {   // interior: no bounds compares
+        const float *b = m.density + ((size_t)iz * m.ny + iy) * m.nx + ix;
+        const size_t ys = (size_t)m.nx, zs = (size_t)m.nx * m.ny;
+        v000 = __ldg(b); v100 = __ldg(b + 1); v010 = __ldg(b + ys); v110 = __ldg(b + ys + 1);
+        v001 = __ldg(b + zs); v101 = __ldg(b + zs + 1); v011 = __ldg(b + zs + ys); v111 = __ldg(b + zs + ys + 1);
+    } else {
+        v000 = gridD(m, ix, iy, iz); v100 = gridD(m, ix + 1, iy, iz);
+        v010 = gridD(m, ix, iy + 1, iz); v110 = gridD(m, ix + 1, iy + 1, iz);
+        v001 = gridD(m, ix, iy, iz + 1); v101 = gridD(m, ix + 1, iy, iz + 1);
+        v011 = gridD(m, ix, iy + 1, iz + 1); v111 = gridD(m, ix + 1, iy + 1, iz + 1);
+    }
+    float d00 = lerpf(dx, v000, v100);
+    float d10 = lerpf(dx, v010, v110);
+    float d01 = lerpf(dx, v001, v101);
+    float d11 = lerpf(dx, v011, v111);
     return lerpf(dz, lerpf(dy, d00, d10), lerpf(dy, d01, d11));
 }
 

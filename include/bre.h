@@ -47,7 +47,7 @@ typedef struct {
     int rank;
     const void *nccl_unique_id; /* 128-byte ncclUniqueId shared by all ranks, or NULL when n_ranks==1 */
     int max_leaf_photons;      /* photons per LBVH leaf on the fast path, 1..16; 0 = default (8) */
-    int tau_steps;             /* optical-depth table steps per ray for grid media; 0 = default (64) */
+    int tau_steps;             /* optical-depth table steps per ray for grid media, <= 384; 0 = default (64) */
 } bre_config;
 
 typedef struct {
