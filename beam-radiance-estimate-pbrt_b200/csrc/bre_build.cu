@@ -202,11 +202,13 @@ __global__ void __launch_bounds__(SCN_T) k_rs_scan_apply(uint32_t *__restrict__ 
     }
 }
 
-__global__ void __launch_bounds__(RS_THREADS) k_rs_scatter(
+__global__ void __launch_bounds__(RS_THREADS, 4) k_rs_scatter(
     const uint32_t *__restrict__ keysIn, const uint32_t *__restrict__ valsIn,
     uint32_t *__restrict__ keysOut, uint32_t *__restrict__ valsOut, uint32_t n, int shift,
     const uint32_t *__restrict__ hist, uint32_t numBlocks, int iotaVals) {
     __shared__ uint32_t whist[RS_THREADS / 32][256];
+    __shared__ uint32_t binLocal[256], binGlobal[256], wsum[RS_THREADS / 32];
+    __shared__ uint32_t skey[RS_TILE], sval[RS_TILE];
     const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < (RS_THREADS / 32) * 256; i += RS_THREADS) (&whist[0][0])[i] = 0;
     __syncthreads();
@@ -235,26 +237,53 @@ __global__ void __launch_bounds__(RS_THREADS) k_rs_scatter(
         __syncwarp();
     }
     __syncthreads();
-    {   // digit threadIdx.x: exclusive prefix over warps + global base
-        uint32_t d = threadIdx.x;
-        uint32_t run = __ldg(hist + d * numBlocks + blockIdx.x);
+    // digit threadIdx.x: exclusive prefix over warps (whist), the tile's exclusive prefix over
+    // digits (binLocal) and the global destination of the tile's first key of that digit.
+    {
+        const uint32_t d = threadIdx.x;
+        uint32_t run = 0;
 #pragma unroll
         for (int ww = 0; ww < RS_THREADS / 32; ++ww) {
             uint32_t c = whist[ww][d];
             whist[ww][d] = run;
             run += c;
         }
+        uint32_t incl = run;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) wsum[w] = incl;
+        __syncthreads();
+        uint32_t woff = 0;
+        for (uint32_t i = 0; i < w; ++i) woff += wsum[i];
+        const uint32_t excl = woff + incl - run;
+        binLocal[d] = excl;
+        binGlobal[d] = __ldg(hist + d * numBlocks + blockIdx.x) - excl;   // dst = binGlobal[d] + tile position
     }
     __syncthreads();
+    // stage the tile in shared memory in its sorted (digit, original index) order ...
 #pragma unroll
     for (int k = 0; k < RS_ITEMS; ++k) {
         uint32_t idx = base + k * 32 + lane;
         if (idx < n) {
             uint32_t d = (key[k] >> shift) & 255u;
-            uint32_t dst = whist[w][d] + rank[k];
-            keysOut[dst] = key[k];
-            valsOut[dst] = iotaVals ? idx : __ldg(valsIn + idx);
+            uint32_t lpos = binLocal[d] + whist[w][d] + rank[k];
+            skey[lpos] = key[k];
+            sval[lpos] = iotaVals ? idx : __ldg(valsIn + idx);
         }
+    }
+    __syncthreads();
+    // ... and write it out in runs: neighbouring threads hit neighbouring addresses within a digit
+    // (full sectors instead of 4096 scattered 4-byte stores per array)
+    const uint32_t tile0 = blockIdx.x * RS_TILE;
+    const uint32_t nValid = n - tile0 < (uint32_t)RS_TILE ? n - tile0 : (uint32_t)RS_TILE;
+    for (uint32_t i = threadIdx.x; i < nValid; i += RS_THREADS) {
+        uint32_t kk = skey[i];
+        uint32_t dst = binGlobal[(kk >> shift) & 255u] + i;
+        keysOut[dst] = kk;
+        valsOut[dst] = sval[i];
     }
 }
 
