@@ -27,7 +27,7 @@ SYMBOLS = [
     "bre_query_to_film", "bre_set_timing", "bre_get_timings", "bre_shard_range", "bre_tile_owner",
     "bre_set_triangle_attrs", "bre_set_lights_in_medium", "bre_set_camera", "bre_camera_rays",
     "bre_query_camera_to_film", "bre_last_build_kind",
-    "bre_save_photons", "bre_load_photons", "bre_film_save", "bre_film_load",
+    "bre_alloc_pinned", "bre_free_pinned", "bre_stage_rays", "bre_query_staged_to_film", "bre_save_photons", "bre_load_photons", "bre_film_save", "bre_film_load",
 ]
 
 
@@ -73,6 +73,10 @@ def load_library(path=LIB_PATH):
     lib = C.CDLL(path)
     lib.bre_last_error.restype = C.c_char_p
     lib.bre_get_stream.restype = C.c_void_p
+    lib.bre_alloc_pinned.restype = C.c_void_p
+    lib.bre_alloc_pinned.argtypes = [C.c_size_t]
+    lib.bre_free_pinned.restype = None
+    lib.bre_free_pinned.argtypes = [C.c_void_p]
     lib.bre_shard_range.restype = None
     return lib
 
@@ -288,6 +292,22 @@ class Bre:
     def query_to_film_ptr(self, n, o_ptr, d_ptr, n_paths_norm):
         self._ck(self.lib.bre_query_to_film(self.ctx, n, C.cast(o_ptr, C.POINTER(C.c_float)),
                                             C.cast(d_ptr, C.POINTER(C.c_float)), None, C.c_float(n_paths_norm)))
+
+    def stage_rays_ptr(self, n, o_ptr, d_ptr):
+        self._ck(self.lib.bre_stage_rays(self.ctx, n, C.cast(o_ptr, C.POINTER(C.c_float)),
+                                         C.cast(d_ptr, C.POINTER(C.c_float))))
+
+    def stage_rays(self, o_tmax, dirs):
+        self._staged = (_f32(o_tmax), _f32(dirs))       # keep the host arrays alive until the query
+        o, d = self._staged
+        self._ck(self.lib.bre_stage_rays(self.ctx, o.size // 4, _fp(o), _fp(d)))
+
+    def query_staged_to_film(self, n_paths_norm, pixel_idx=None):
+        p = None
+        if pixel_idx is not None:
+            pixel_idx = np.ascontiguousarray(pixel_idx, dtype=np.uint32)
+            p = pixel_idx.ctypes.data_as(C.POINTER(C.c_uint32))
+        self._ck(self.lib.bre_query_staged_to_film(self.ctx, p, C.c_float(n_paths_norm)))
 
     def film_resolve_ptr(self, it, scale, out_ptr):
         self._ck(self.lib.bre_film_resolve(self.ctx, it, C.c_float(scale), C.cast(out_ptr, C.POINTER(C.c_float))))

@@ -123,6 +123,8 @@ int bre_create(bre_ctx **out, const bre_config *cfg) {
     {
         const char *qc = getenv("BRE_PAIR_QUEUE_CAP");
         if (qc && atoll(qc) > 0) ctx->pair_queue_cap_override = (uint64_t)atoll(qc);
+        const char *lf = getenv("BRE_L2_FETCH");   // experiment: 32 / 64 / 128 byte L2 fetch granularity
+        if (lf && atoi(lf) > 0) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(lf));
         const char *tn = getenv("BRE_TRACE_NESTED");
         ctx->trace_nested = tn && atoi(tn) != 0;
         const char *rb = getenv("BRE_RAY_BATCH");
@@ -148,10 +150,15 @@ int bre_destroy(bre_ctx *ctx) {
                    &ctx->node_lo, &ctx->node_hi, &ctx->node_range, &ctx->parent, &ctx->leaf_lo,
                    &ctx->leaf_hi, &ctx->flags, &ctx->fast, &ctx->scratch, &ctx->rays_o, &ctx->rays_d,
                    &ctx->out_rgb, &ctx->tau, &ctx->hit_counts, &ctx->hit_offsets, &ctx->hit_idx,
-                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb, &ctx->entry};
+                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb, &ctx->entry, &ctx->rays_stage};
     for (Buf *b : bufs) if (b->p) cudaFree(b->p);
     if (ctx->lights_d) cudaFree(ctx->lights_d);
     if (ctx->est_host) cudaFreeHost(ctx->est_host);
+    if (ctx->copy_stream) {
+        cudaStreamSynchronize(ctx->copy_stream);
+        cudaEventDestroy(ctx->ev_stage); cudaEventDestroy(ctx->ev_main);
+        cudaStreamDestroy(ctx->copy_stream);
+    }
     if (ctx->stream2) {
         cudaStreamSynchronize(ctx->stream2);
         for (int i = 0; i < 4; ++i) if (ctx->qev[i]) cudaEventDestroy(ctx->qev[i]);
@@ -172,6 +179,12 @@ int bre_synchronize(bre_ctx *ctx) {
     return BRE_OK;
 }
 int bre_nccl_unique_id(void *out128) { return nccl_unique_id(out128); }
+
+void *bre_alloc_pinned(size_t bytes) {
+    void *p = nullptr;
+    return cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) == cudaSuccess ? p : nullptr;
+}
+void bre_free_pinned(void *p) { if (p) cudaFreeHost(p); }
 
 // ---------------------------------------------------------------- scene
 int bre_set_medium_homogeneous(bre_ctx *ctx, const float sa[3], const float ss[3], float g) {
@@ -432,6 +445,57 @@ int bre_query_to_film(bre_ctx *ctx, uint32_t n, const float *o4, const float *d3
     if (n == 0) return BRE_OK;
     if (!o4 || !d3) return set_err(ctx, BRE_ERR_INVALID, "null ray arrays");
     if ((s = upload_rays(ctx, n, o4, d3)) != BRE_OK) return s;
+    if ((s = ensure(ctx, ctx->out_rgb, (size_t)n * 16)) != BRE_OK) return s;
+    const uint32_t *pd = nullptr;
+    if (pix) {
+        if ((s = ensure(ctx, ctx->pix_idx, (size_t)n * 4)) != BRE_OK) return s;
+        BRE_CUDA(cudaMemcpyAsync(ctx->pix_idx.p, pix, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+        pd = (const uint32_t *)ctx->pix_idx.p;
+    }
+    if ((s = run_query(ctx, n, (const float4 *)ctx->rays_o.p, (const float4 *)ctx->rays_d.p, nPathsNorm,
+                       (float4 *)ctx->out_rgb.p)) != BRE_OK) return s;
+    return film_accumulate(ctx, n, pd, (const float4 *)ctx->out_rgb.p);
+}
+
+// Asynchronous ray upload on a copy stream: the camera rays of a pass do not depend on the photon
+// pass, so a host can hand them over first and let the PCIe transfer overlap K1 and the LBVH build.
+int bre_stage_rays(bre_ctx *ctx, uint32_t n, const float *o4, const float *d3) {
+    CTX_CHECK();
+    if (n == 0 || !o4 || !d3) return set_err(ctx, BRE_ERR_INVALID, "bad ray arrays");
+    int s;
+    if ((s = ensure(ctx, ctx->rays_o, (size_t)n * 16)) != BRE_OK) return s;
+    if ((s = ensure(ctx, ctx->rays_d, (size_t)n * 16)) != BRE_OK) return s;
+    if ((s = ensure(ctx, ctx->rays_stage, (size_t)n * 12)) != BRE_OK) return s;
+    if (!ctx->copy_stream) {
+        BRE_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        BRE_CUDA(cudaEventCreateWithFlags(&ctx->ev_stage, cudaEventDisableTiming));
+        BRE_CUDA(cudaEventCreateWithFlags(&ctx->ev_main, cudaEventDisableTiming));
+    }
+    // the ray buffers may still be read by work already queued on the context stream
+    BRE_CUDA(cudaEventRecord(ctx->ev_main, ctx->stream));
+    BRE_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_main, 0));
+    BRE_CUDA(cudaMemcpyAsync(ctx->rays_o.p, o4, (size_t)n * 16, cudaMemcpyHostToDevice, ctx->copy_stream));
+    BRE_CUDA(cudaMemcpyAsync(ctx->rays_stage.p, d3, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->copy_stream));
+    k_pack3<<<(n + 255) / 256, 256, 0, ctx->copy_stream>>>((const float *)ctx->rays_stage.p, n, nullptr, 0.f,
+                                                           (float4 *)ctx->rays_d.p);
+    BRE_CUDA(cudaGetLastError());
+    BRE_CUDA(cudaEventRecord(ctx->ev_stage, ctx->copy_stream));
+    ctx->staged_rays = n;
+    return BRE_OK;
+}
+
+int bre_query_staged_to_film(bre_ctx *ctx, const uint32_t *pix, float nPathsNorm) {
+    CTX_CHECK();
+    int s = query_ready(ctx);
+    if (s != BRE_OK) return s;
+    if (!ctx->film.p) return set_err(ctx, BRE_ERR_INVALID, "bre_film_create has not been called");
+    const uint32_t n = ctx->staged_rays;
+    if (n == 0) return set_err(ctx, BRE_ERR_INVALID, "bre_stage_rays has not been called");
+    ctx->staged_rays = 0;
+    // the upload finished long ago in practice; waiting on the host too makes the caller's ray
+    // arrays reusable as soon as this call returns
+    BRE_CUDA(cudaEventSynchronize(ctx->ev_stage));
+    BRE_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_stage, 0));
     if ((s = ensure(ctx, ctx->out_rgb, (size_t)n * 16)) != BRE_OK) return s;
     const uint32_t *pd = nullptr;
     if (pix) {

@@ -367,6 +367,8 @@ __device__ __forceinline__ int delta64(const uint32_t *__restrict__ codes,
     return __clzll((long long)(ki ^ kj));
 }
 
+constexpr int REFIT_DIRECT = 64;   // nodes up to this many photons: box computed directly (k_refit_fast)
+
 // node_lo[i].w / node_hi[i].w hold the left / right child refs (>=0 internal, <0 = ~leaf).
 // parent[0..n-2] internal parents, parent[n-1+s] leaf parents.  node_range[i] = {first,last}.
 __global__ void __launch_bounds__(256) k_karras(const uint32_t *__restrict__ codes,
@@ -405,10 +407,15 @@ __global__ void __launch_bounds__(256) k_karras(const uint32_t *__restrict__ cod
     if (i == 0) parent[0] = -1;
     // entry points of the production tree: children of <= maxLeaf photons under a larger node
     // (a fat-leaf root, or a single photon).  k_refit_fast starts from exactly these.
-    const bool big = last - first + 1 > maxLeaf;
-    entry[left >= 0 ? left : n - 1 + gamma] = big && (gamma - first + 1 <= maxLeaf);
-    entry[right >= 0 ? right : n - 1 + gamma + 1] = big && (last - gamma <= maxLeaf);
-    if (i == 0) entry[0] = !big;
+    // bit 1: where the atomic climb starts -- children of <= REFIT_DIRECT photons under a larger node
+    // (everything at or below that size gets its box straight from the photons, no atomics).
+    const int cnt = last - first + 1, cl = gamma - first + 1, cr = last - gamma;
+    const bool big = cnt > maxLeaf, huge = cnt > REFIT_DIRECT;
+    entry[left >= 0 ? left : n - 1 + gamma] =
+        (unsigned char)((big && cl <= maxLeaf ? 1 : 0) | (huge && cl <= REFIT_DIRECT ? 2 : 0));
+    entry[right >= 0 ? right : n - 1 + gamma + 1] =
+        (unsigned char)((big && cr <= maxLeaf ? 1 : 0) | (huge && cr <= REFIT_DIRECT ? 2 : 0));
+    if (i == 0) entry[0] = (unsigned char)((big ? 0 : 1) | 0);
 }
 
 __global__ void __launch_bounds__(256) k_refit(int n, float4 *node_lo, float4 *node_hi,
@@ -453,27 +460,33 @@ __global__ void __launch_bounds__(256) k_refit_fast(int n, int maxLeaf, float4 *
                                                     const unsigned char *__restrict__ entry,
                                                     uint32_t *__restrict__ flags) {
     int tid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tid >= 2 * n - 1 || !__ldg(entry + tid)) return;
-    const int cur0 = __ldg(parent + tid);
-    int cur = cur0;
+    if (tid >= 2 * n - 1) return;
+    const unsigned tag = __ldg(entry + tid);
     if (tid < n - 1) {
+        // every kept node of <= REFIT_DIRECT photons: union of its photons' boxes (contiguous
+        // Morton range, shared with its neighbours through L1/L2) -- no dependency, no atomics
         const int2 rg = __ldg(node_range + tid);
-        float4 lo, hi;
-        leaf_box(__ldg(s_pos_r + rg.x), lo, hi);
-        for (int q = rg.x + 1; q <= rg.y; ++q) {
-            float4 l, h;
-            leaf_box(__ldg(s_pos_r + q), l, h);
-            lo.x = fminf(lo.x, l.x); lo.y = fminf(lo.y, l.y); lo.z = fminf(lo.z, l.z);
-            hi.x = fmaxf(hi.x, h.x); hi.y = fmaxf(hi.y, h.y); hi.z = fmaxf(hi.z, h.z);
+        const int cnt = rg.y - rg.x + 1;
+        const bool kept = cnt > maxLeaf || (tag & 1u);
+        if (cnt <= REFIT_DIRECT && kept) {
+            float4 lo, hi;
+            leaf_box(__ldg(s_pos_r + rg.x), lo, hi);
+            for (int q = rg.x + 1; q <= rg.y; ++q) {
+                float4 l, h;
+                leaf_box(__ldg(s_pos_r + q), l, h);
+                lo.x = fminf(lo.x, l.x); lo.y = fminf(lo.y, l.y); lo.z = fminf(lo.z, l.z);
+                hi.x = fmaxf(hi.x, h.x); hi.y = fmaxf(hi.y, h.y); hi.z = fmaxf(hi.z, h.z);
+            }
+            lo.w = __ldcg(&node_lo[tid].w); hi.w = __ldcg(&node_hi[tid].w);
+            __stcg(node_lo + tid, lo);
+            __stcg(node_hi + tid, hi);
         }
-        lo.w = __ldcg(&node_lo[tid].w); hi.w = __ldcg(&node_hi[tid].w);
-        __stcg(node_lo + tid, lo);
-        __stcg(node_hi + tid, hi);
     }
+    if (!(tag & 2u)) return;
+    int cur = __ldg(parent + tid);
     while (cur >= 0) {
-        __threadfence();
+        __threadfence();   // my stores (or my child's) are visible before the arrival is counted
         if (atomicAdd(flags + cur, 1u) == 0u) return;  // first arrival: sibling not done yet
-        __threadfence();
         float4 nlo = __ldcg(node_lo + cur), nhi = __ldcg(node_hi + cur);
         const int left = __float_as_int(nlo.w), right = __float_as_int(nhi.w);
         float4 llo, lhi, rlo, rhi;

@@ -148,6 +148,11 @@ struct bre_ctx {
     uint32_t ctr_batches = 0, ctr_batch_rays = 0, ctr_rays = 0;
     unsigned int *est_host = nullptr;       // pinned copy of the last batch's queue control words
     uint32_t est_rays = 0;
+    // asynchronous ray staging (bre_stage_rays)
+    bre::Buf rays_stage;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_stage = nullptr, ev_main = nullptr;
+    uint32_t staged_rays = 0;
     cudaStream_t stream2 = nullptr;
     cudaEvent_t qev[4] = {};
     bre::Buf rays_o, rays_d, out_rgb, tau, hit_counts, hit_offsets, hit_idx, counters_d, pix_idx;

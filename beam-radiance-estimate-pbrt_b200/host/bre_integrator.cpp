@@ -294,37 +294,26 @@ void BreIntegrator::Render(const Scene &scene) {
     const Vector2i ext = pixelBounds.Diagonal();
     const uint32_t nPixels = (uint32_t)(ext.x * ext.y);
     const uint64_t nPaths = photonsPerIteration > 0 ? (uint64_t)photonsPerIteration : nPixels;
-    std::vector<float> rayO(4 * (size_t)nPixels), rayD(3 * (size_t)nPixels), mean(3 * (size_t)nPixels);
+    std::vector<float> mean(3 * (size_t)nPixels);
+    // host-generated rays live in page-locked memory so that bre_stage_rays overlaps the photon pass
+    float *rayO = nullptr, *rayD = nullptr;
+    if (!cameraOnDevice) {
+        rayO = (float *)bre_alloc_pinned(sizeof(float) * 4 * (size_t)nPixels);
+        rayD = (float *)bre_alloc_pinned(sizeof(float) * 3 * (size_t)nPixels);
+        if (!rayO || !rayD) { Error("bre: cannot allocate page-locked ray buffers"); bre_destroy(ctx); return; }
+    }
     std::unique_ptr<Spectrum[]> image(new Spectrum[nPixels]);
     if (!Check(ctx, bre_film_create(ctx, nPixels), "bre_film_create")) { bre_destroy(ctx); return; }
 
     Float radius = initialRadius;
     ProgressReporter progress(nIterations, "Rendering (bre)");
     for (int iter = 0; iter < nIterations; ++iter) {
-        // ---- photon pass (photonbeam.cpp:365-437): path indices iter*nPaths .. as :386-388
-        // "reusephotons": the photon map of iteration 0 is kept and only its radius shrinks, so
-        // bre_build degenerates to a refit of the existing LBVH (SURVEY.md 8f-3)
-        const bool retrace = iter == 0 || !reusePhotons;
-        bool ok = retrace ? Check(ctx, bre_clear_photons(ctx), "bre_clear_photons")
-                          : Check(ctx, bre_set_radius(ctx, radius), "bre_set_radius");
-        uint64_t stored = 0;
-        if (!retrace) {
-        } else if (ok && deviceTracer)
-            ok = Check(ctx, bre_trace_photons(ctx, (uint64_t)iter * nPaths, nPaths, maxDepth, radius, &stored),
-                       "bre_trace_photons");
-        else if (ok)
-            stored = TracePhotonsHost(ctx, scene, *lightDistr, (uint64_t)iter * nPaths, nPaths, radius);
-        lastPathsEmitted = nPaths;
-        // ---- photon structure (photonbeam.cpp:438)
-        ok = ok && Check(ctx, bre_build(ctx), "bre_build");
-        // ---- camera pass (photonbeam.cpp:444-557): one query segment per pixel
-        if (ok) {
-            // iteration 0 looks through the pixel centres, later ones use a (2,3) Halton offset
-            const Point2f off = iter == 0 ? Point2f(0.5f, 0.5f)
-                                          : Point2f(RadicalInverse(0, iter), RadicalInverse(1, iter));
-            if (cameraOnDevice)
-                ok = Check(ctx, bre_query_camera_to_film(ctx, off.x, off.y, (float)nPaths), "bre_query_camera_to_film");
-            else {
+        // iteration 0 looks through the pixel centres, later ones use a (2,3) Halton offset
+        const Point2f off = iter == 0 ? Point2f(0.5f, 0.5f)
+                                      : Point2f(RadicalInverse(0, iter), RadicalInverse(1, iter));
+        // ---- camera rays first (photonbeam.cpp:444-481): they do not depend on the photons, so the
+        // host generates them now and the upload overlaps the photon pass and the LBVH build
+        if (!cameraOnDevice) {
             ParallelFor([&](int64_t y) {
                 for (int x = 0; x < ext.x; ++x) {
                     const size_t q = (size_t)y * ext.x + x;
@@ -343,9 +332,30 @@ void BreIntegrator::Render(const Scene &scene) {
                     rayD[3 * q + 0] = d.x; rayD[3 * q + 1] = d.y; rayD[3 * q + 2] = d.z;
                 }
             }, ext.y, 4);
-            ok = Check(ctx, bre_query_to_film(ctx, nPixels, rayO.data(), rayD.data(), nullptr, (float)nPaths),
-                       "bre_query_to_film");
-            }
+            if (!Check(ctx, bre_stage_rays(ctx, nPixels, rayO, rayD), "bre_stage_rays")) break;
+        }
+        // ---- photon pass (photonbeam.cpp:365-437): path indices iter*nPaths .. as :386-388
+        // "reusephotons": the photon map of iteration 0 is kept and only its radius shrinks, so
+        // bre_build degenerates to a refit of the existing LBVH (SURVEY.md 8f-3)
+        const bool retrace = iter == 0 || !reusePhotons;
+        bool ok = retrace ? Check(ctx, bre_clear_photons(ctx), "bre_clear_photons")
+                          : Check(ctx, bre_set_radius(ctx, radius), "bre_set_radius");
+        uint64_t stored = 0;
+        if (!retrace) {
+        } else if (ok && deviceTracer)
+            ok = Check(ctx, bre_trace_photons(ctx, (uint64_t)iter * nPaths, nPaths, maxDepth, radius, &stored),
+                       "bre_trace_photons");
+        else if (ok)
+            stored = TracePhotonsHost(ctx, scene, *lightDistr, (uint64_t)iter * nPaths, nPaths, radius);
+        lastPathsEmitted = nPaths;
+        // ---- photon structure (photonbeam.cpp:438)
+        ok = ok && Check(ctx, bre_build(ctx), "bre_build");
+        // ---- camera pass (photonbeam.cpp:444-557): one query segment per pixel
+        if (ok) {
+            if (cameraOnDevice)
+                ok = Check(ctx, bre_query_camera_to_film(ctx, off.x, off.y, (float)nPaths), "bre_query_camera_to_film");
+            else
+                ok = Check(ctx, bre_query_staged_to_film(ctx, nullptr, (float)nPaths), "bre_query_staged_to_film");
         }
         if (!ok) break;
         // ---- progressive radius (photonbeam.cpp:562)
@@ -365,6 +375,8 @@ void BreIntegrator::Render(const Scene &scene) {
     }
     progress.Done();
     bre_destroy(ctx);
+    bre_free_pinned(rayO);
+    bre_free_pinned(rayD);
 }
 
 Integrator *CreateBreIntegrator(const ParamSet &params, std::shared_ptr<const Camera> camera) {

@@ -10,8 +10,9 @@ heterogeneous GridDensityMedium smoke volume (64^3 grid of 8 seeded Gaussian blo
 photons, 1920x1080 camera rays, fixed gather radius.
 
 `value`   = beam queries/s, whole job, inputs resident in HBM (device-timed, CUDA events).
-`e2e`     = the same step through the host C-ABI: pinned host rays -> bre_query_to_film ->
-            bre_film_resolve to a host image, host<->device copies inside the timed region.
+`e2e`     = the same step through the host C-ABI: pinned host rays -> bre_stage_rays (async H2D) ->
+            photon pass -> build -> bre_query_staged_to_film -> bre_film_resolve to a host image;
+            host<->device copies inside the timed region.
 `roofline`= K5 query kernel: algorithmic bytes (48 + 32 V + 16 T + 32 H per ray,
             V/T/H counted on the canonical 1-photon-per-leaf LBVH) / kernel time, vs the measured
             HBM copy bandwidth in MEASURED_PEAKS.json.
@@ -206,12 +207,15 @@ def run_ours(args):
         ctx.film_accumulate_d(nq, out_d.data_ptr())
 
     def step_e2e():
+        # the calls the pbrt adapter makes: rays handed over first (async upload from pinned host
+        # memory overlaps the photon pass), photon pass, build, camera pass, image back to the host
+        ctx.stage_rays_ptr(nq, ro_pin.data_ptr(), rd_pin.data_ptr())
         ctx.clear_photons()
         ctx.trace_photons(p_first, p_count, MAX_DEPTH, radius)
         if world > 1:
             ctx.allgather_photons()
         ctx.build()
-        ctx.query_to_film_ptr(nq, ro_pin.data_ptr(), rd_pin.data_ptr(), float(n_paths))
+        ctx.query_staged_to_film(float(n_paths))
         ctx.film_resolve_ptr(0, 1.0, img_pin.data_ptr())
 
     def barrier():

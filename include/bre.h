@@ -88,6 +88,10 @@ void *bre_get_stream(bre_ctx *ctx);
 int bre_synchronize(bre_ctx *ctx);
 /* rank 0 creates the id every rank passes in bre_config.nccl_unique_id (128 bytes). */
 int bre_nccl_unique_id(void *out128);
+/* Page-locked host memory for arrays handed to bre_stage_rays / bre_film_resolve (truly
+ * asynchronous, full-rate PCIe copies).  NULL on failure.  Needs no context. */
+void *bre_alloc_pinned(size_t bytes);
+void bre_free_pinned(void *p);
 
 /* ---- scene inputs --------------------------------------------------------------- */
 /* HomogeneousMedium (media/homogeneous.h, factory core/api.cpp:547-596). */
@@ -194,6 +198,13 @@ int bre_query_d(bre_ctx *ctx, uint32_t n_rays, const void *rays_o_d, const void 
  * pixel_idx==NULL -> ray q belongs to pixel q. */
 int bre_query_to_film(bre_ctx *ctx, uint32_t n_rays, const float *o_xyz_tmax, const float *d_xyz,
                       const uint32_t *pixel_idx, float n_paths_norm);
+/* The same camera pass in two calls, so that the ray upload overlaps the photon pass: the rays of a
+ * pass do not depend on the photons, so a host generates them first, calls bre_stage_rays (returns
+ * at once; the copy runs on its own stream -- use page-locked host arrays and keep them untouched
+ * until bre_query_staged_to_film has returned), then traces / builds, then calls
+ * bre_query_staged_to_film. */
+int bre_stage_rays(bre_ctx *ctx, uint32_t n_rays, const float *o_xyz_tmax, const float *d_xyz);
+int bre_query_staged_to_film(bre_ctx *ctx, const uint32_t *pixel_idx, float n_paths_norm);
 /* Counting pass on the canonical tree for the same rays (fills V,T,H,bytes) plus the
  * production kernel's own counters. */
 int bre_count(bre_ctx *ctx, uint32_t n_rays, const float *o_xyz_tmax, const float *d_xyz);

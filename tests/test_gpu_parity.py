@@ -315,3 +315,24 @@ def test_progressive_radius_refit_only(oracle, ctx, n):
     ctx.upload_photons(pos, pw, dr, radius=r)
     ctx.build()
     assert ctx.last_build_kind() == 1
+
+
+def test_staged_rays_equal_direct_upload(oracle, ctx, bre):
+    """bre_stage_rays (async upload on the copy stream, issued BEFORE the photons exist) followed by
+    bre_query_staged_to_film gives the film of bre_query_to_film; a second query without staging fails."""
+    n = 30000
+    pos, pw, dr = oracle.synth_photons_uniform(n)
+    ro, rd = oracle.synth_rays_pinhole(48, 36)
+    ctx.set_medium_homogeneous(SA, SS, 0.3)
+    ctx.film_create(48 * 36)
+    ctx.stage_rays(ro, rd)                       # rays first ...
+    ctx.upload_photons(pos, pw, dr, radius=radius_for(n, 32))
+    ctx.build()                                  # ... photon structure afterwards
+    ctx.query_staged_to_film(float(n))
+    a = ctx.film_mean(0)
+    ctx.film_clear()
+    ctx.query_to_film(ro, rd, float(n))
+    b = ctx.film_mean(0)
+    assert a.max() > 0 and np.allclose(a, b, rtol=1e-5, atol=1e-9 * a.max())
+    with pytest.raises(bre.BreError):
+        ctx.query_staged_to_film(float(n))
