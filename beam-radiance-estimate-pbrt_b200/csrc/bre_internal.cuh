@@ -147,7 +147,7 @@ struct bre_ctx {
     uint32_t ray_batch_override = 0;        // BRE_RAY_BATCH (experiments)
     uint32_t ctr_batches = 0, ctr_batch_rays = 0, ctr_rays = 0;
     unsigned int *est_host = nullptr;       // pinned copy of the last batch's queue control words
-    uint32_t est_rays = 0;
+    uint32_t est_batches = 0, est_batch_rays = 0, est_n = 0;
     // asynchronous ray staging (bre_stage_rays)
     bre::Buf rays_stage;
     cudaStream_t copy_stream = nullptr;

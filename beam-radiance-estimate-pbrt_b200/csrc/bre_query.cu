@@ -217,6 +217,7 @@ namespace bre {
 //   +64  zero word + the two heavy-packet counters (persist from launch to launch)
 //   +128 this batch's LeafArgs (read by the cold in-place path of K5a)
 constexpr size_t QB_STRIDE = 512, QB_HEAVY = 64, QB_ARGS = 128;
+constexpr uint32_t EST_MAX_BATCHES = 128;   // batches whose demand is read back for the next launch
 static_assert(QB_ARGS + sizeof(LeafArgs) <= QB_STRIDE, "batch block too small");
 
 __host__ __device__ inline LeafArgs shift_args(LeafArgs A, size_t off) {
@@ -254,12 +255,20 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     if (ctx->pair_queue_cap_override) want = ctx->pair_queue_cap_override;
     // ---- batch size from the last launch's measured demand (pinned host copy of its control words)
     if (!ctx->est_host) {
-        BRE_CUDA(cudaHostAlloc((void **)&ctx->est_host, 64, cudaHostAllocDefault));
-        memset(ctx->est_host, 0, 64);
+        BRE_CUDA(cudaHostAlloc((void **)&ctx->est_host, EST_MAX_BATCHES * QB_STRIDE, cudaHostAllocDefault));
+        memset(ctx->est_host, 0, EST_MAX_BATCHES * QB_STRIDE);
     }
+    // densest batch of the previous launch (image regions differ: the last batch alone misleads)
     double est = 128.0;
-    if (ctx->est_rays && ctx->est_host[QC_PAIR_TAIL]) {
-        est = 1.3 * (double)ctx->est_host[QC_PAIR_TAIL] / (double)ctx->est_rays;
+    if (ctx->est_batches) {
+        double worst = 0.0;
+        for (uint32_t b = 0; b < ctx->est_batches; ++b) {
+            const uint32_t r0 = b * ctx->est_batch_rays;
+            const uint32_t nb = ctx->est_n - r0 < ctx->est_batch_rays ? ctx->est_n - r0 : ctx->est_batch_rays;
+            const double v = (double)ctx->est_host[b * (QB_STRIDE / 4) + QC_PAIR_TAIL] / (double)(nb ? nb : 1);
+            if (v > worst) worst = v;
+        }
+        if (worst > 0.0) est = 1.3 * worst;
         if (est < 16.0) est = 16.0;
     }
     uint32_t batchRays = n;
@@ -352,9 +361,11 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
             sb = ctx->stream2;
         }
         if (b + 1 == nBatches) {
-            // demand of this launch -> batch size of the next one
-            BRE_CUDA(cudaMemcpyAsync(ctx->est_host, ctl, 32, cudaMemcpyDeviceToHost, ctx->stream));
-            ctx->est_rays = nb;
+            // demand of this launch (every batch's control words) -> batch size of the next one
+            const uint32_t nCopy = nBatches < EST_MAX_BATCHES ? nBatches : EST_MAX_BATCHES;
+            BRE_CUDA(cudaMemcpyAsync(ctx->est_host, blocks, (size_t)nCopy * QB_STRIDE, cudaMemcpyDeviceToHost,
+                                     ctx->stream));
+            ctx->est_batches = nCopy; ctx->est_batch_rays = batchRays; ctx->est_n = n;
             if (ctx->timing) {
                 cudaEventRecord(ctx->ev[PH_QUERY_A][1], ctx->stream); ctx->ev_valid[PH_QUERY_A] = true;
                 cudaEventRecord(ctx->ev[PH_QUERY_B][0], ctx->stream);
