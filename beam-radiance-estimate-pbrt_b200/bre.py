@@ -27,7 +27,7 @@ SYMBOLS = [
     "bre_query_to_film", "bre_set_timing", "bre_get_timings", "bre_shard_range", "bre_tile_owner",
     "bre_set_triangle_attrs", "bre_set_lights_in_medium", "bre_set_camera", "bre_camera_rays",
     "bre_query_camera_to_film", "bre_last_build_kind",
-    "bre_alloc_pinned", "bre_free_pinned", "bre_stage_rays", "bre_query_staged_to_film", "bre_save_photons", "bre_load_photons", "bre_film_save", "bre_film_load",
+    "bre_trace_exchange_photons", "bre_alloc_pinned", "bre_free_pinned", "bre_stage_rays", "bre_query_staged_to_film", "bre_save_photons", "bre_load_photons", "bre_film_save", "bre_film_load",
 ]
 
 
@@ -235,6 +235,12 @@ class Bre:
 
     def set_radius(self, r):
         self._ck(self.lib.bre_set_radius(self.ctx, C.c_float(r)))
+
+    def trace_exchange_photons(self, n_paths_total, max_depth, radius):
+        n = C.c_uint64()
+        self._ck(self.lib.bre_trace_exchange_photons(self.ctx, C.c_uint64(n_paths_total), max_depth,
+                                                     C.c_float(radius), C.byref(n)))
+        return n.value
 
     def allgather_photons(self):
         self._ck(self.lib.bre_allgather_photons(self.ctx))

@@ -125,6 +125,8 @@ int bre_create(bre_ctx **out, const bre_config *cfg) {
         if (qc && atoll(qc) > 0) ctx->pair_queue_cap_override = (uint64_t)atoll(qc);
         const char *lf = getenv("BRE_L2_FETCH");   // experiment: 32 / 64 / 128 byte L2 fetch granularity
         if (lf && atoi(lf) > 0) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(lf));
+        const char *np = getenv("BRE_NO_P2P");
+        ctx->p2p_disabled = np && atoi(np) != 0;
         const char *tn = getenv("BRE_TRACE_NESTED");
         ctx->trace_nested = tn && atoi(tn) != 0;
         const char *rb = getenv("BRE_RAY_BATCH");
@@ -150,7 +152,7 @@ int bre_destroy(bre_ctx *ctx) {
                    &ctx->node_lo, &ctx->node_hi, &ctx->node_range, &ctx->parent, &ctx->leaf_lo,
                    &ctx->leaf_hi, &ctx->flags, &ctx->fast, &ctx->scratch, &ctx->rays_o, &ctx->rays_d,
                    &ctx->out_rgb, &ctx->tau, &ctx->hit_counts, &ctx->hit_offsets, &ctx->hit_idx,
-                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb, &ctx->entry, &ctx->rays_stage};
+                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb, &ctx->entry, &ctx->rays_stage, &ctx->p2p_scratch};
     for (Buf *b : bufs) if (b->p) cudaFree(b->p);
     if (ctx->lights_d) cudaFree(ctx->lights_d);
     if (ctx->est_host) cudaFreeHost(ctx->est_host);
@@ -343,6 +345,26 @@ int bre_set_radius(bre_ctx *ctx, float radius) {
     if (ctx->n_photons)
         k_set_w<<<(unsigned)((ctx->n_photons + 255) / 256), 256, 0, ctx->stream>>>((float4 *)ctx->pos_r.p, ctx->n_photons, radius);
     BRE_CUDA(cudaGetLastError());
+    return BRE_OK;
+}
+
+int bre_trace_exchange_photons(bre_ctx *ctx, uint64_t nPathsTotal, int maxDepth, float radius,
+                               uint64_t *nStored) {
+    CTX_CHECK();
+    if (!(radius > 0.f)) return set_err(ctx, BRE_ERR_INVALID, "radius must be > 0");
+    uint64_t first = 0, count = nPathsTotal;
+    bre_shard_range(nPathsTotal, ctx->n_ranks, ctx->rank, &first, &count);
+    int s;
+    if (ctx->n_ranks > 1 && !ctx->p2p_disabled && ctx->n_ranks <= 8 && count <= TRACE_CHUNK) {
+        s = trace_exchange_p2p(ctx, nPathsTotal, maxDepth, radius);
+    } else {
+        ctx->n_photons = 0;
+        s = trace_photons(ctx, first, count, maxDepth, radius);
+        if (s == BRE_OK && ctx->n_ranks > 1) s = nccl_allgather_photons(ctx);
+    }
+    if (s != BRE_OK) return s;
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (nStored) *nStored = ctx->n_photons;
     return BRE_OK;
 }
 

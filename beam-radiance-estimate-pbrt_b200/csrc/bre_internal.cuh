@@ -10,6 +10,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <string>
+#include <vector>
 #include "../../include/bre.h"
 
 namespace bre {
@@ -164,6 +165,13 @@ struct bre_ctx {
     bre::Buf path_counts, path_offsets;
     // nccl
     void *nccl_comm = nullptr;
+    // CUDA-IPC mappings of every rank's photon store (fused trace + push, bre_nccl.cpp)
+    void *p2p_peer[8][3] = {};
+    void *p2p_exported[3] = {};
+    bool p2p_open = false;
+    bool p2p_disabled = false;             // BRE_NO_P2P=1, or IPC mapping failed once
+    bre::Buf p2p_scratch;
+    std::vector<void *> p2p_zombies;       // exported stores replaced since: freed once peers closed them
     // per-phase device timing (bre_set_timing)
     bool timing = false;
     cudaEvent_t ev[8][2] = {};
@@ -195,10 +203,21 @@ int film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int m
 // camera.cu
 int camera_rays(bre_ctx *ctx, float offx, float offy);
 // trace.cu
+constexpr uint64_t TRACE_CHUNK = 1u << 22;   // paths per trace launch (bounds the slot scratch)
+struct SlotView {
+    float4 *sp, *sw, *sd;      // per-path slots: path * maxDepth + k
+    uint32_t *counts;          // photons deposited per path
+    uint64_t *offs;            // exclusive scan of counts
+    uint64_t total;
+    uint32_t nPaths;
+    int maxDepth;
+};
+int trace_to_slots(bre_ctx *ctx, uint64_t first, uint32_t nPaths, int maxDepth, float radius, SlotView *out);
 int trace_photons(bre_ctx *ctx, uint64_t first, uint64_t nPaths, int maxDepth, float radius);
 // nccl.cpp
 int nccl_init(bre_ctx *ctx, const void *uid);
 int nccl_allgather_photons(bre_ctx *ctx);
+int trace_exchange_p2p(bre_ctx *ctx, uint64_t nPathsTotal, int maxDepth, float radius);
 void nccl_destroy(bre_ctx *ctx);
 int nccl_unique_id(void *out128);
 

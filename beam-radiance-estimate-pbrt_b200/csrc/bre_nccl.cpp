@@ -89,7 +89,9 @@ int nccl_init(bre_ctx *ctx, const void *uid) {
     return BRE_OK;
 }
 
+void p2p_destroy(bre_ctx *ctx);
 void nccl_destroy(bre_ctx *ctx) {
+    p2p_destroy(ctx);
     if (ctx->nccl_comm && g.ok) g.CommDestroy((ncclComm_p)ctx->nccl_comm);
     ctx->nccl_comm = nullptr;
 }
@@ -99,6 +101,9 @@ void nccl_destroy(bre_ctx *ctx) {
 // rank-major offset -- no padding, no second compaction pass.
 int nccl_allgather_photons(bre_ctx *ctx) {
     if (!ctx->nccl_comm) return set_err(ctx, BRE_ERR_INVALID, "context was created without NCCL");
+    if (ctx->p2p_open)
+        return set_err(ctx, BRE_ERR_INVALID, "this context exchanges photons over P2P (bre_trace_exchange_photons); "
+                                             "set BRE_NO_P2P=1 to use the NCCL all-gather instead");
     ncclComm_p comm = (ncclComm_p)ctx->nccl_comm;
     const int R = ctx->n_ranks;
     int s;
@@ -130,6 +135,165 @@ int nccl_allgather_photons(bre_ctx *ctx) {
     if ((r = g.GroupEnd()) != 0) return nccl_err(ctx, r, "ncclGroupEnd");
     BRE_CUDA(cudaStreamSynchronize(ctx->stream));
     for (int a = 0; a < 3; ++a) { Buf t = *store[a]; *store[a] = *stage[a]; *stage[a] = t; }
+    ctx->n_photons = total;
+    return BRE_OK;
+}
+
+
+// ---------------------------------------------------------------- fused trace + push (NVLink P2P)
+// The NCCL path above is compute (K1 + compaction) FOLLOWED by a collective.  Here the two are one
+// kernel: after tracing its slice into per-path slots every rank knows its photon count; the counts
+// are all-gathered (8 bytes per rank -- also the barrier that says "nobody reads its store any
+// more"), and the compaction kernel then writes every photon record straight to its final,
+// rank-major position in the store of EVERY rank -- the local one and the peers' through CUDA-IPC
+// mappings over NVLink / NVSwitch.  No staging slab, no broadcast; the transfer overlaps the
+// compaction pass record by record.  A one-word all-gather afterwards is the arrival barrier.
+// Stores are exported once (and again whenever any rank had to reallocate: the decision rides on
+// the count all-gather so that it is collective).
+constexpr int MAX_P2P_RANKS = 8;
+struct PeerStores {
+    float4 *pos[MAX_P2P_RANKS], *pw[MAX_P2P_RANKS], *dr[MAX_P2P_RANKS];
+};
+
+__global__ void __launch_bounds__(256) k_compact_push(uint32_t nPaths, int maxDepth,
+                                                      const uint32_t *__restrict__ counts,
+                                                      const uint64_t *__restrict__ offs,
+                                                      const float4 *__restrict__ slot_pos,
+                                                      const float4 *__restrict__ slot_pow,
+                                                      const float4 *__restrict__ slot_dir,
+                                                      PeerStores peers, int nRanks, int self,
+                                                      uint64_t rankBase) {
+    uint32_t pid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pid >= nPaths) return;
+    const uint32_t c = __ldg(counts + pid);
+    const uint64_t dst = rankBase + __ldg(offs + pid);
+    const size_t src = (size_t)pid * maxDepth;
+    for (uint32_t k = 0; k < c; ++k) {
+        const float4 a = __ldg(slot_pos + src + k), b = __ldg(slot_pow + src + k), d = __ldg(slot_dir + src + k);
+        // start with the neighbour so that the R ranks do not all hammer rank 0 first
+        for (int i = 0; i < nRanks; ++i) {
+            const int r = (self + 1 + i) % nRanks;
+            peers.pos[r][dst + k] = a;
+            peers.pw[r][dst + k] = b;
+            peers.dr[r][dst + k] = d;
+        }
+    }
+}
+
+static void p2p_close(bre_ctx *ctx) {
+    for (int r = 0; r < MAX_P2P_RANKS; ++r)
+        for (int a = 0; a < 3; ++a)
+            if (ctx->p2p_peer[r][a] && r != ctx->rank) { cudaIpcCloseMemHandle(ctx->p2p_peer[r][a]); ctx->p2p_peer[r][a] = nullptr; }
+    ctx->p2p_open = false;
+}
+void p2p_destroy(bre_ctx *ctx) {
+    const bool was = ctx->p2p_open;
+    p2p_close(ctx);
+    if (was && ctx->nccl_comm) {
+        // peers must have unmapped this rank's store before bre_destroy frees it
+        uint64_t *cnt_d = (uint64_t *)ctx->counters_d.p;
+        const int R = ctx->n_ranks;
+        if (cnt_d && g.AllGather(cnt_d + 2 * R, cnt_d, 1, kNcclUint64, (ncclComm_p)ctx->nccl_comm, ctx->stream) == 0)
+            cudaStreamSynchronize(ctx->stream);
+    }
+    for (void *z : ctx->p2p_zombies) cudaFree(z);
+    ctx->p2p_zombies.clear();
+}
+
+// all ranks: export the three store arrays, all-gather the handles, map the peers' arrays
+static int p2p_exchange_handles(bre_ctx *ctx) {
+    ncclComm_p comm = (ncclComm_p)ctx->nccl_comm;
+    const int R = ctx->n_ranks;
+    p2p_close(ctx);
+    cudaIpcMemHandle_t mine[3];
+    void *store[3] = {ctx->pos_r.p, ctx->pow.p, ctx->dir.p};
+    for (int a = 0; a < 3; ++a) BRE_CUDA(cudaIpcGetMemHandle(&mine[a], store[a]));
+    const size_t hb = sizeof(mine);   // 192 bytes per rank
+    int s;
+    if ((s = ensure(ctx, ctx->p2p_scratch, hb * (size_t)(R + 1))) != BRE_OK) return s;
+    char *d = (char *)ctx->p2p_scratch.p;
+    BRE_CUDA(cudaMemcpyAsync(d + hb * R, mine, hb, cudaMemcpyHostToDevice, ctx->stream));
+    int r = g.AllGather(d + hb * R, d, hb, 0 /* ncclChar */, comm, ctx->stream);
+    if (r != 0) return nccl_err(ctx, r, "ncclAllGather(ipc handles)");
+    std::vector<cudaIpcMemHandle_t> all(3 * (size_t)R);
+    BRE_CUDA(cudaMemcpyAsync(all.data(), d, hb * R, cudaMemcpyDeviceToHost, ctx->stream));
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (int q = 0; q < R; ++q)
+        for (int a = 0; a < 3; ++a) {
+            if (q == ctx->rank) { ctx->p2p_peer[q][a] = store[a]; continue; }
+            void *ptr = nullptr;
+            cudaError_t e = cudaIpcOpenMemHandle(&ptr, all[3 * q + a], cudaIpcMemLazyEnablePeerAccess);
+            if (e != cudaSuccess) {
+                cudaGetLastError();
+                return set_err(ctx, BRE_ERR_CUDA, std::string("cudaIpcOpenMemHandle: ") + cudaGetErrorString(e));
+            }
+            ctx->p2p_peer[q][a] = ptr;
+        }
+    for (int a = 0; a < 3; ++a) ctx->p2p_exported[a] = store[a];
+    ctx->p2p_open = true;
+    return BRE_OK;
+}
+
+// Trace this rank's slice of [0, nPathsTotal) and deliver all photons of all ranks into every
+// rank's store (replaces bre_clear_photons + bre_trace_photons + bre_allgather_photons).
+int trace_exchange_p2p(bre_ctx *ctx, uint64_t nPathsTotal, int maxDepth, float radius) {
+    ncclComm_p comm = (ncclComm_p)ctx->nccl_comm;
+    const int R = ctx->n_ranks;
+    uint64_t first = 0, count = 0;
+    bre_shard_range(nPathsTotal, R, ctx->rank, &first, &count);
+    ctx->built = false; ctx->topo_valid = false;
+    ctx->n_photons = 0;
+    SlotView v;
+    int s;
+    {
+        PhaseTimer pt(ctx, PH_TRACE);
+        if ((s = trace_to_slots(ctx, first, (uint32_t)count, maxDepth, radius, &v)) != BRE_OK) return s;
+    }
+    // ---- counts (+ "my store moved" flag) to everyone; doubles as the pre-push barrier
+    if ((s = ensure(ctx, ctx->counters_d, 16 * (size_t)(R + 1) + 64)) != BRE_OK) return s;
+    uint64_t *cnt_d = (uint64_t *)ctx->counters_d.p;
+    const bool moved = !ctx->p2p_open || ctx->p2p_exported[0] != ctx->pos_r.p ||
+                       ctx->p2p_exported[1] != ctx->pow.p || ctx->p2p_exported[2] != ctx->dir.p;
+    uint64_t mine[2] = {v.total, moved ? 1ull : 0ull};
+    BRE_CUDA(cudaMemcpyAsync(cnt_d + 2 * R, mine, 16, cudaMemcpyHostToDevice, ctx->stream));
+    int r = g.AllGather(cnt_d + 2 * R, cnt_d, 2, kNcclUint64, comm, ctx->stream);
+    if (r != 0) return nccl_err(ctx, r, "ncclAllGather(counts)");
+    std::vector<uint64_t> got(2 * (size_t)R), off(R + 1, 0);
+    BRE_CUDA(cudaMemcpyAsync(got.data(), cnt_d, 16 * (size_t)R, cudaMemcpyDeviceToHost, ctx->stream));
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    bool anyMoved = false;
+    for (int i = 0; i < R; ++i) { off[i + 1] = off[i] + got[2 * i]; anyMoved |= got[2 * i + 1] != 0; }
+    const uint64_t total = off[R];
+    if (total >= BRE_MAX_PHOTONS) return set_err(ctx, BRE_ERR_UNSUPPORTED, "photon count exceeds 2^27");
+    // ---- capacity: the same decision on every rank (total is global), with 25 % head room
+    const size_t need = (size_t)total * 16;
+    const bool grow = ctx->pos_r.cap < need || ctx->pow.cap < need || ctx->dir.cap < need;
+    if (grow || anyMoved) {
+        // everyone unmaps everyone first; only then may an exported store be freed
+        p2p_close(ctx);
+        r = g.AllGather(cnt_d + 2 * R, cnt_d, 1, kNcclUint64, comm, ctx->stream);
+        if (r != 0) return nccl_err(ctx, r, "ncclAllGather(unmap barrier)");
+        BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+        for (void *z : ctx->p2p_zombies) cudaFree(z);
+        ctx->p2p_zombies.clear();
+        if (grow && (s = grow_photon_store(ctx, total + total / 4)) != BRE_OK) return s;
+        if ((s = p2p_exchange_handles(ctx)) != BRE_OK) return s;
+    }
+    // ---- fused compaction + push
+    PeerStores ps;
+    for (int q = 0; q < MAX_P2P_RANKS; ++q) {
+        ps.pos[q] = (float4 *)ctx->p2p_peer[q < R ? q : ctx->rank][0];
+        ps.pw[q] = (float4 *)ctx->p2p_peer[q < R ? q : ctx->rank][1];
+        ps.dr[q] = (float4 *)ctx->p2p_peer[q < R ? q : ctx->rank][2];
+    }
+    if (count > 0)
+        k_compact_push<<<(unsigned)((count + 255) / 256), 256, 0, ctx->stream>>>(
+            (uint32_t)count, maxDepth, v.counts, v.offs, v.sp, v.sw, v.sd, ps, R, ctx->rank, off[ctx->rank]);
+    BRE_CUDA(cudaGetLastError());
+    // ---- arrival barrier: every rank's push kernel has completed before anyone builds
+    r = g.AllGather(cnt_d + 2 * R, cnt_d, 1, kNcclUint64, comm, ctx->stream);
+    if (r != 0) return nccl_err(ctx, r, "ncclAllGather(barrier)");
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->n_photons = total;
     return BRE_OK;
 }

@@ -546,77 +546,93 @@ static int grow_store(bre_ctx *ctx, uint64_t newCount) {
         if (b->p && ctx->n_photons)
             cudaMemcpyAsync(np, b->p, (size_t)ctx->n_photons * sizeof(float4), cudaMemcpyDeviceToDevice, ctx->stream);
         cudaStreamSynchronize(ctx->stream);
-        if (b->p) cudaFree(b->p);
+        // a store exported over CUDA IPC may still be mapped by the peers: free it only after the
+        // next collective handle exchange has made everyone close it (bre_nccl.cpp)
+        bool exported = false;
+        for (int a = 0; a < 3; ++a) exported |= ctx->p2p_open && b->p && b->p == ctx->p2p_exported[a];
+        if (exported) ctx->p2p_zombies.push_back(b->p);
+        else if (b->p) cudaFree(b->p);
         b->p = np; b->cap = cap;
     }
     return BRE_OK;
 }
 int grow_photon_store(bre_ctx *ctx, uint64_t newCount) { return grow_store(ctx, newCount); }
 
-int trace_photons(bre_ctx *ctx, uint64_t first, uint64_t nPathsTotal, int maxDepth, float radius) {
+// Trace paths [first, first + nPaths) into per-path slots and scan the per-path counts.  Returns a
+// view of the scratch arrays (valid until the next call) and the number of photons deposited.
+// nPaths <= TRACE_CHUNK bounds the slot scratch (nPaths * maxDepth * 48 bytes).
+int trace_to_slots(bre_ctx *ctx, uint64_t first, uint32_t nPaths, int maxDepth, float radius, SlotView *out) {
     if (!ctx->have_medium) return set_err(ctx, BRE_ERR_INVALID, "no medium set");
     if (!ctx->lights_d || ctx->n_lights == 0) return set_err(ctx, BRE_ERR_INVALID, "no lights set");
     const bool useMesh = ctx->n_tri > 0;
     if (!useMesh && !ctx->have_bounds)
         return set_err(ctx, BRE_ERR_INVALID, "no surfaces set (bre_set_triangles or bre_set_bounds)");
-    MeshDev mesh{ctx->n_tri, (const float4 *)ctx->tri.p, (const float *)ctx->tri_kdb.p};
     if (maxDepth < 1) return set_err(ctx, BRE_ERR_INVALID, "max_depth must be >= 1");
-    const uint64_t CHUNK = 1u << 22;
+    MeshDev mesh{ctx->n_tri, (const float4 *)ctx->tri.p, (const float *)ctx->tri_kdb.p};
+    size_t slots = (size_t)nPaths * maxDepth;
+    uint32_t nTiles = (nPaths + SC_TILE - 1) / SC_TILE;
+    int s;
+    // scratch layout: 3 slot arrays | counts | offsets(u64) | tileSums | tileOff(u64) | total(u64) | nextPath
+    size_t oSlots = 0, oCounts = oSlots + 3 * slots * sizeof(float4);
+    size_t oOffs = (oCounts + (size_t)nPaths * 4 + 15) & ~(size_t)15;
+    size_t oTs = oOffs + (size_t)nPaths * 8;
+    size_t oTo = (oTs + (size_t)nTiles * 4 + 15) & ~(size_t)15;
+    size_t oTot = oTo + (size_t)nTiles * 8;
+    if ((s = ensure(ctx, ctx->path_counts, oTot + 32)) != BRE_OK) return s;
+    char *base = (char *)ctx->path_counts.p;
+    float4 *sp = (float4 *)(base + oSlots), *sw = sp + slots, *sd = sw + slots;
+    uint32_t *counts = (uint32_t *)(base + oCounts);
+    uint64_t *offs = (uint64_t *)(base + oOffs);
+    uint32_t *tileSums = (uint32_t *)(base + oTs);
+    uint64_t *tileOff = (uint64_t *)(base + oTo);
+    uint64_t *total = (uint64_t *)(base + oTot);
+    unsigned int *nextPath = (unsigned int *)(base + oTot + 16);
+    if (useMesh)
+        k_trace<true><<<(nPaths + 127) / 128, 128, 0, ctx->stream>>>(
+            ctx->medium, ctx->lights_d, mesh, ctx->lights_in_medium, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f,
+            first, nPaths, maxDepth, radius, sp, sw, sd, counts);
+    else if (ctx->trace_nested)
+        k_trace<false><<<(nPaths + 127) / 128, 128, 0, ctx->stream>>>(
+            ctx->medium, ctx->lights_d, mesh, 1, ctx->blo[0], ctx->blo[1], ctx->blo[2], ctx->bhi[0],
+            ctx->bhi[1], ctx->bhi[2], first, nPaths, maxDepth, radius, sp, sw, sd, counts);
+    else {
+        // persistent threads: as many blocks as fit, each lane claims paths from nextPath
+        int perSM = 0;
+        BRE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_trace_flat, 128, 0));
+        if (perSM < 1) perSM = 1;
+        unsigned blocks = (unsigned)(ctx->sm_count * perSM);
+        if (blocks > (nPaths + 127) / 128) blocks = (nPaths + 127) / 128;
+        BRE_CUDA(cudaMemsetAsync(nextPath, 0, 4, ctx->stream));
+        k_trace_flat<<<blocks, 128, 0, ctx->stream>>>(
+            ctx->medium, ctx->lights_d, ctx->blo[0], ctx->blo[1], ctx->blo[2], ctx->bhi[0], ctx->bhi[1],
+            ctx->bhi[2], first, nPaths, maxDepth, radius, sp, sw, sd, counts, nextPath);
+    }
+    k_scan_reduce<<<nTiles, SC_T, 0, ctx->stream>>>(counts, nPaths, tileSums);
+    k_scan_tiles<<<1, 1024, 0, ctx->stream>>>(tileSums, nTiles, tileOff, total);
+    k_scan_apply<<<nTiles, SC_T, 0, ctx->stream>>>(counts, nPaths, tileOff, offs);
+    BRE_CUDA(cudaGetLastError());
+    uint64_t hTotal = 0;
+    BRE_CUDA(cudaMemcpyAsync(&hTotal, total, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    out->sp = sp; out->sw = sw; out->sd = sd; out->counts = counts; out->offs = offs;
+    out->total = hTotal; out->nPaths = nPaths; out->maxDepth = maxDepth;
+    return BRE_OK;
+}
+
+int trace_photons(bre_ctx *ctx, uint64_t first, uint64_t nPathsTotal, int maxDepth, float radius) {
     ctx->built = false; ctx->topo_valid = false;
     PhaseTimer pt(ctx, PH_TRACE);
-    for (uint64_t done = 0; done < nPathsTotal; done += CHUNK) {
-        uint32_t nPaths = (uint32_t)((nPathsTotal - done) < CHUNK ? (nPathsTotal - done) : CHUNK);
-        size_t slots = (size_t)nPaths * maxDepth;
-        uint32_t nTiles = (nPaths + SC_TILE - 1) / SC_TILE;
-        int s;
-        // scratch layout: 3 slot arrays | counts | offsets(u64) | tileSums | tileOff(u64) | total(u64)
-        size_t oSlots = 0, oCounts = oSlots + 3 * slots * sizeof(float4);
-        size_t oOffs = (oCounts + (size_t)nPaths * 4 + 15) & ~(size_t)15;
-        size_t oTs = oOffs + (size_t)nPaths * 8;
-        size_t oTo = (oTs + (size_t)nTiles * 4 + 15) & ~(size_t)15;
-        size_t oTot = oTo + (size_t)nTiles * 8;
-        if ((s = ensure(ctx, ctx->path_counts, oTot + 32)) != BRE_OK) return s;
-        char *base = (char *)ctx->path_counts.p;
-        float4 *sp = (float4 *)(base + oSlots), *sw = sp + slots, *sd = sw + slots;
-        uint32_t *counts = (uint32_t *)(base + oCounts);
-        uint64_t *offs = (uint64_t *)(base + oOffs);
-        uint32_t *tileSums = (uint32_t *)(base + oTs);
-        uint64_t *tileOff = (uint64_t *)(base + oTo);
-        uint64_t *total = (uint64_t *)(base + oTot);
-        unsigned int *nextPath = (unsigned int *)(base + oTot + 16);
-        if (useMesh)
-            k_trace<true><<<(nPaths + 127) / 128, 128, 0, ctx->stream>>>(
-                ctx->medium, ctx->lights_d, mesh, ctx->lights_in_medium, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f,
-                first + done, nPaths, maxDepth, radius, sp, sw, sd, counts);
-        else if (ctx->trace_nested)
-            k_trace<false><<<(nPaths + 127) / 128, 128, 0, ctx->stream>>>(
-                ctx->medium, ctx->lights_d, mesh, 1, ctx->blo[0], ctx->blo[1], ctx->blo[2], ctx->bhi[0],
-                ctx->bhi[1], ctx->bhi[2], first + done, nPaths, maxDepth, radius, sp, sw, sd, counts);
-        else {
-            // persistent threads: as many blocks as fit, each lane claims paths from nextPath
-            int perSM = 0;
-            BRE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_trace_flat, 128, 0));
-            if (perSM < 1) perSM = 1;
-            unsigned blocks = (unsigned)(ctx->sm_count * perSM);
-            if (blocks > (nPaths + 127) / 128) blocks = (nPaths + 127) / 128;
-            BRE_CUDA(cudaMemsetAsync(nextPath, 0, 4, ctx->stream));
-            k_trace_flat<<<blocks, 128, 0, ctx->stream>>>(
-                ctx->medium, ctx->lights_d, ctx->blo[0], ctx->blo[1], ctx->blo[2], ctx->bhi[0], ctx->bhi[1],
-                ctx->bhi[2], first + done, nPaths, maxDepth, radius, sp, sw, sd, counts, nextPath);
-        }
-        k_scan_reduce<<<nTiles, SC_T, 0, ctx->stream>>>(counts, nPaths, tileSums);
-        k_scan_tiles<<<1, 1024, 0, ctx->stream>>>(tileSums, nTiles, tileOff, total);
-        k_scan_apply<<<nTiles, SC_T, 0, ctx->stream>>>(counts, nPaths, tileOff, offs);
-        BRE_CUDA(cudaGetLastError());
-        uint64_t hTotal = 0;
-        BRE_CUDA(cudaMemcpyAsync(&hTotal, total, 8, cudaMemcpyDeviceToHost, ctx->stream));
-        BRE_CUDA(cudaStreamSynchronize(ctx->stream));
-        if ((s = grow_store(ctx, ctx->n_photons + hTotal)) != BRE_OK) return s;
+    for (uint64_t done = 0; done < nPathsTotal; done += TRACE_CHUNK) {
+        uint32_t nPaths = (uint32_t)((nPathsTotal - done) < TRACE_CHUNK ? (nPathsTotal - done) : TRACE_CHUNK);
+        SlotView v;
+        int s = trace_to_slots(ctx, first + done, nPaths, maxDepth, radius, &v);
+        if (s != BRE_OK) return s;
+        if ((s = grow_store(ctx, ctx->n_photons + v.total)) != BRE_OK) return s;
         k_compact<<<(nPaths + 255) / 256, 256, 0, ctx->stream>>>(
-            nPaths, maxDepth, counts, offs, sp, sw, sd, (float4 *)ctx->pos_r.p, (float4 *)ctx->pow.p,
+            nPaths, maxDepth, v.counts, v.offs, v.sp, v.sw, v.sd, (float4 *)ctx->pos_r.p, (float4 *)ctx->pow.p,
             (float4 *)ctx->dir.p, ctx->n_photons);
         BRE_CUDA(cudaGetLastError());
-        ctx->n_photons += hTotal;
+        ctx->n_photons += v.total;
     }
     return BRE_OK;
 }

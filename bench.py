@@ -197,11 +197,18 @@ def run_ours(args):
     ctx.set_timing(True)
     stream = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", local))
 
-    def step_device():
+    def photon_pass():
+        # N > 1: fused trace + push over NVLink P2P (--exchange p2p, default) or trace + NCCL all-gather
+        if world > 1 and args.exchange == "p2p":
+            ctx.trace_exchange_photons(n_paths, MAX_DEPTH, radius)
+            return
         ctx.clear_photons()
         ctx.trace_photons(p_first, p_count, MAX_DEPTH, radius)
         if world > 1:
             ctx.allgather_photons()
+
+    def step_device():
+        photon_pass()
         ctx.build()
         ctx.query_d(nq, ro_d.data_ptr(), rd_d.data_ptr(), float(n_paths), out_d.data_ptr())
         ctx.film_accumulate_d(nq, out_d.data_ptr())
@@ -210,10 +217,7 @@ def run_ours(args):
         # the calls the pbrt adapter makes: rays handed over first (async upload from pinned host
         # memory overlaps the photon pass), photon pass, build, camera pass, image back to the host
         ctx.stage_rays_ptr(nq, ro_pin.data_ptr(), rd_pin.data_ptr())
-        ctx.clear_photons()
-        ctx.trace_photons(p_first, p_count, MAX_DEPTH, radius)
-        if world > 1:
-            ctx.allgather_photons()
+        photon_pass()
         ctx.build()
         ctx.query_staged_to_film(float(n_paths))
         ctx.film_resolve_ptr(0, 1.0, img_pin.data_ptr())
@@ -304,7 +308,8 @@ def run_ours(args):
         "config": {"workload": args.workload, "photons": int(n_photons), "photon_paths": int(n_paths),
                    "rays_per_gpu": int(nq), "resolution": [W, H], "radius": radius, "grid": wl["grid"],
                    "max_leaf_photons": ctx_leaf(args), "l2": "inputs larger than L2 (photon SoA + tree >> 126 MB at 10M)",
-                   "step": "K1 trace + [allgather] + K2-4 build + K6 tau + K5 query + K7 film",
+                   "step": "K1 trace + [exchange] + K2-4 build + K6 tau + K5 query + K7 film",
+                   "exchange": (args.exchange if world > 1 else None),
                    "mean_hits_per_ray": cnt["hits"] / nq, "mean_V": cnt["nodes_visited"] / nq,
                    "mean_T": cnt["disk_tests"] / nq, "mdisk_tests_per_s": cnt["disk_tests"] / (k5_ms * 1e-3) / 1e6,
                    "phase_ms": {"trace": float(np.mean(ktrace)), "build": float(np.mean(kbuild)),
@@ -443,6 +448,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="smoke10m_1080p", choices=sorted(WORKLOADS))
     ap.add_argument("--leaf", type=int, default=0)
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"])
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--ref-rays", type=int, default=65536)

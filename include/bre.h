@@ -162,6 +162,15 @@ int bre_download_photons(bre_ctx *ctx, uint64_t cap, float *p_xyz, float *alpha_
                          float *radii);
 /* Set the radius of every stored photon (progressive shrink, integrators/photonbeam.cpp:354-356,562). */
 int bre_set_radius(bre_ctx *ctx, float radius);
+/* Multi-GPU, fused: trace this rank's slice (bre_shard_range) of path indices [0, n_paths_total) and
+ * deliver the photons of ALL ranks into every rank's store in rank-major (= path index) order.
+ * One kernel compacts the traced records and writes them straight into the local store and, through
+ * CUDA-IPC mappings over NVLink / NVSwitch, into the peers' stores; NCCL carries only the counts
+ * and the barriers.  Collective: every rank of the communicator must call it with the same
+ * arguments.  Replaces bre_clear_photons + bre_trace_photons + bre_allgather_photons; with one rank
+ * it is clear + trace.  BRE_NO_P2P=1 in the environment selects the NCCL all-gather instead. */
+int bre_trace_exchange_photons(bre_ctx *ctx, uint64_t n_paths_total, int max_depth, float radius,
+                               uint64_t *n_stored);
 /* Multi-GPU: all-gather every rank's photon store in rank-major order (NCCL over NVLink). */
 int bre_allgather_photons(bre_ctx *ctx);
 
