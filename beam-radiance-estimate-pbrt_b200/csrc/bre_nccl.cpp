@@ -155,7 +155,10 @@ struct PeerStores {
     float4 *pos[MAX_P2P_RANKS], *pw[MAX_P2P_RANKS], *dr[MAX_P2P_RANKS];
 };
 
-__global__ void __launch_bounds__(256) k_compact_push(uint32_t nPaths, int maxDepth,
+// One block = a tile of `tilePaths` consecutive paths.  Their photons are consecutive in the output,
+// so the tile is compacted into shared memory first and then written to every rank as contiguous,
+// fully coalesced 16-byte-per-lane runs (NVLink moves full packets instead of scattered 16-byte stores).
+__global__ void __launch_bounds__(256) k_compact_push(uint32_t nPaths, int maxDepth, uint32_t tilePaths,
                                                       const uint32_t *__restrict__ counts,
                                                       const uint64_t *__restrict__ offs,
                                                       const float4 *__restrict__ slot_pos,
@@ -163,20 +166,30 @@ __global__ void __launch_bounds__(256) k_compact_push(uint32_t nPaths, int maxDe
                                                       const float4 *__restrict__ slot_dir,
                                                       PeerStores peers, int nRanks, int self,
                                                       uint64_t rankBase) {
-    uint32_t pid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (pid >= nPaths) return;
-    const uint32_t c = __ldg(counts + pid);
-    const uint64_t dst = rankBase + __ldg(offs + pid);
-    const size_t src = (size_t)pid * maxDepth;
-    for (uint32_t k = 0; k < c; ++k) {
-        const float4 a = __ldg(slot_pos + src + k), b = __ldg(slot_pow + src + k), d = __ldg(slot_dir + src + k);
-        // start with the neighbour so that the R ranks do not all hammer rank 0 first
-        for (int i = 0; i < nRanks; ++i) {
-            const int r = (self + 1 + i) % nRanks;
-            peers.pos[r][dst + k] = a;
-            peers.pw[r][dst + k] = b;
-            peers.dr[r][dst + k] = d;
+    extern __shared__ float4 tile[];
+    const uint32_t cap = tilePaths * (uint32_t)maxDepth;
+    float4 *tp = tile, *tw = tile + cap, *td = tile + 2 * cap;
+    const uint32_t p0 = blockIdx.x * tilePaths;
+    const uint32_t pEnd = min(p0 + tilePaths, nPaths);
+    const uint64_t base = __ldg(offs + p0);
+    for (uint32_t pid = p0 + threadIdx.x; pid < pEnd; pid += blockDim.x) {
+        const uint32_t c = __ldg(counts + pid);
+        const uint32_t o = (uint32_t)(__ldg(offs + pid) - base);
+        const size_t src = (size_t)pid * maxDepth;
+        for (uint32_t k = 0; k < c; ++k) {
+            tp[o + k] = __ldg(slot_pos + src + k);
+            tw[o + k] = __ldg(slot_pow + src + k);
+            td[o + k] = __ldg(slot_dir + src + k);
         }
+    }
+    __syncthreads();
+    const uint32_t n = (uint32_t)(__ldg(offs + pEnd - 1) + __ldg(counts + pEnd - 1) - base);
+    const uint64_t dst = rankBase + base;
+    // start with the neighbour so that the R ranks do not all write to rank 0 at the same time
+    for (int i = 0; i < nRanks; ++i) {
+        const int r = (self + 1 + i) % nRanks;
+        float4 *dp = peers.pos[r] + dst, *dw = peers.pw[r] + dst, *dd = peers.dr[r] + dst;
+        for (uint32_t j = threadIdx.x; j < n; j += blockDim.x) { dp[j] = tp[j]; dw[j] = tw[j]; dd[j] = td[j]; }
     }
 }
 
@@ -286,9 +299,17 @@ int trace_exchange_p2p(bre_ctx *ctx, uint64_t nPathsTotal, int maxDepth, float r
         ps.pw[q] = (float4 *)ctx->p2p_peer[q < R ? q : ctx->rank][1];
         ps.dr[q] = (float4 *)ctx->p2p_peer[q < R ? q : ctx->rank][2];
     }
-    if (count > 0)
-        k_compact_push<<<(unsigned)((count + 255) / 256), 256, 0, ctx->stream>>>(
-            (uint32_t)count, maxDepth, v.counts, v.offs, v.sp, v.sw, v.sd, ps, R, ctx->rank, off[ctx->rank]);
+    if (count > 0) {
+        // tile of paths per block, bounded by 200 KB of shared memory (3 x 16 B x tilePaths x maxDepth)
+        uint32_t tilePaths = 256;
+        while (tilePaths > 1 && (size_t)tilePaths * maxDepth * 48 > 200 * 1024) tilePaths >>= 1;
+        const size_t smem = (size_t)tilePaths * maxDepth * 48;
+        if (smem > 200 * 1024) return set_err(ctx, BRE_ERR_UNSUPPORTED, "max_depth too large for the push kernel");
+        BRE_CUDA(cudaFuncSetAttribute(k_compact_push, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_compact_push<<<(unsigned)((count + tilePaths - 1) / tilePaths), 256, smem, ctx->stream>>>(
+            (uint32_t)count, maxDepth, tilePaths, v.counts, v.offs, v.sp, v.sw, v.sd, ps, R, ctx->rank,
+            off[ctx->rank]);
+    }
     BRE_CUDA(cudaGetLastError());
     // ---- arrival barrier: every rank's push kernel has completed before anyone builds
     r = g.AllGather(cnt_d + 2 * R, cnt_d, 1, kNcclUint64, comm, ctx->stream);
