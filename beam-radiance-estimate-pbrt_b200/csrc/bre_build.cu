@@ -367,7 +367,8 @@ __device__ __forceinline__ int delta64(const uint32_t *__restrict__ codes,
     return __clzll((long long)(ki ^ kj));
 }
 
-constexpr int REFIT_DIRECT = 64;   // nodes up to this many photons: box computed directly (k_refit_fast)
+// ctx->refit_direct (default 16, env BRE_REFIT_DIRECT): nodes up to this many photons get their box
+// directly from the photons in k_refit_fast; measured 8/16/32/64/128 -> build 2.71/2.65/2.67/2.78/2.97 ms
 
 // node_lo[i].w / node_hi[i].w hold the left / right child refs (>=0 internal, <0 = ~leaf).
 // parent[0..n-2] internal parents, parent[n-1+s] leaf parents.  node_range[i] = {first,last}.
@@ -376,7 +377,7 @@ __global__ void __launch_bounds__(256) k_karras(const uint32_t *__restrict__ cod
                                                 float4 *__restrict__ node_lo,
                                                 float4 *__restrict__ node_hi,
                                                 int2 *__restrict__ node_range,
-                                                int *__restrict__ parent, int maxLeaf,
+                                                int *__restrict__ parent, int maxLeaf, int directMax,
                                                 unsigned char *__restrict__ entry) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
@@ -407,14 +408,14 @@ __global__ void __launch_bounds__(256) k_karras(const uint32_t *__restrict__ cod
     if (i == 0) parent[0] = -1;
     // entry points of the production tree: children of <= maxLeaf photons under a larger node
     // (a fat-leaf root, or a single photon).  k_refit_fast starts from exactly these.
-    // bit 1: where the atomic climb starts -- children of <= REFIT_DIRECT photons under a larger node
+    // bit 1: where the atomic climb starts -- children of <= refit_direct photons under a larger node
     // (everything at or below that size gets its box straight from the photons, no atomics).
     const int cnt = last - first + 1, cl = gamma - first + 1, cr = last - gamma;
-    const bool big = cnt > maxLeaf, huge = cnt > REFIT_DIRECT;
+    const bool big = cnt > maxLeaf, huge = cnt > directMax;
     entry[left >= 0 ? left : n - 1 + gamma] =
-        (unsigned char)((big && cl <= maxLeaf ? 1 : 0) | (huge && cl <= REFIT_DIRECT ? 2 : 0));
+        (unsigned char)((big && cl <= maxLeaf ? 1 : 0) | (huge && cl <= directMax ? 2 : 0));
     entry[right >= 0 ? right : n - 1 + gamma + 1] =
-        (unsigned char)((big && cr <= maxLeaf ? 1 : 0) | (huge && cr <= REFIT_DIRECT ? 2 : 0));
+        (unsigned char)((big && cr <= maxLeaf ? 1 : 0) | (huge && cr <= directMax ? 2 : 0));
     if (i == 0) entry[0] = (unsigned char)((big ? 0 : 1) | 0);
 }
 
@@ -453,7 +454,7 @@ __global__ void __launch_bounds__(256) k_refit(int n, float4 *node_lo, float4 *n
 // are such entry points was tagged by k_karras (entry[], one byte each).  Climbing is the
 // usual second-arrival-continues scheme.  Nodes inside fat leaves are never touched (7/8 of the
 // tree at maxLeaf 8).  min/max are exact, so every box equals the canonical bottom-up union.
-__global__ void __launch_bounds__(256) k_refit_fast(int n, int maxLeaf, float4 *node_lo, float4 *node_hi,
+__global__ void __launch_bounds__(256) k_refit_fast(int n, int maxLeaf, int directMax, float4 *node_lo, float4 *node_hi,
                                                     const int2 *__restrict__ node_range,
                                                     const int *__restrict__ parent,
                                                     const float4 *__restrict__ s_pos_r,
@@ -463,12 +464,12 @@ __global__ void __launch_bounds__(256) k_refit_fast(int n, int maxLeaf, float4 *
     if (tid >= 2 * n - 1) return;
     const unsigned tag = __ldg(entry + tid);
     if (tid < n - 1) {
-        // every kept node of <= REFIT_DIRECT photons: union of its photons' boxes (contiguous
+        // every kept node of <= refit_direct photons: union of its photons' boxes (contiguous
         // Morton range, shared with its neighbours through L1/L2) -- no dependency, no atomics
         const int2 rg = __ldg(node_range + tid);
         const int cnt = rg.y - rg.x + 1;
         const bool kept = cnt > maxLeaf || (tag & 1u);
-        if (cnt <= REFIT_DIRECT && kept) {
+        if (cnt <= directMax && kept) {
             float4 lo, hi;
             leaf_box(__ldg(s_pos_r + rg.x), lo, hi);
             for (int q = rg.x + 1; q <= rg.y; ++q) {
@@ -544,7 +545,7 @@ static int launch_refit_emit(bre_ctx *ctx) {
     cudaStream_t st = ctx->stream;
     BRE_CUDA(cudaMemsetAsync(ctx->flags.p, 0, (size_t)n * 4, st));
     k_refit_fast<<<(int)((2 * (size_t)n - 1 + 255) / 256), 256, 0, st>>>(
-        (int)n, ctx->max_leaf, (float4 *)ctx->node_lo.p, (float4 *)ctx->node_hi.p,
+        (int)n, ctx->max_leaf, ctx->refit_direct, (float4 *)ctx->node_lo.p, (float4 *)ctx->node_hi.p,
         (const int2 *)ctx->node_range.p, (const int *)ctx->parent.p, (const float4 *)ctx->s_pos_r.p,
         (const unsigned char *)ctx->entry.p, (uint32_t *)ctx->flags.p);
     k_emit_fast<<<(int)((n + 255) / 256), 256, 0, st>>>(
@@ -662,7 +663,7 @@ int build_tree(bre_ctx *ctx) {
     if (n > 1) {
         k_karras<<<g256, 256, 0, st>>>(codes, order, (int)n, (float4 *)ctx->node_lo.p,
                                        (float4 *)ctx->node_hi.p, (int2 *)ctx->node_range.p,
-                                       (int *)ctx->parent.p, ctx->max_leaf, (unsigned char *)ctx->entry.p);
+                                       (int *)ctx->parent.p, ctx->max_leaf, ctx->refit_direct, (unsigned char *)ctx->entry.p);
         if ((s = launch_refit_emit(ctx)) != BRE_OK) { delete pt; return s; }
     }
     delete pt;

@@ -104,6 +104,7 @@ struct Buf {
 struct bre_ctx {
     int device = 0, n_ranks = 1, rank = 0;
     int max_leaf = 8, tau_steps = 64;
+    int refit_direct = 16;                  // nodes up to this many photons get their box straight from the photons
     int sm_count = 148;
     uint64_t pair_queue_cap_override = 0;   // BRE_PAIR_QUEUE_CAP (tests force the overflow path)
     cudaStream_t stream = nullptr;
@@ -139,13 +140,14 @@ struct bre_ctx {
     float abs_max = 0;
     int root_ref = 0;
     // query scratch
-    bre::Buf packet_ctr, pair_queue, heavy;
+    bre::Buf packet_ctr, pair_queue, heavy, frames;
     // heavy-first packet order fed from one radiance query to the next (bre_query.cu)
     size_t heavy_half = 0;
     uint32_t heavy_rays = 0;
     int heavy_parity = 0;
     // ray batching of K5 (bre_query.cu launch_query)
     uint32_t ray_batch_override = 0;        // BRE_RAY_BATCH (experiments)
+    float fat_spread = 1.f / 64.f;          // BRE_FAT_SPREAD: largest |d_i - d_0| of a packet walked as one fat ray (0 = off)
     uint32_t ctr_batches = 0, ctr_batch_rays = 0, ctr_rays = 0;
     unsigned int *est_host = nullptr;       // pinned copy of the last batch's queue control words
     uint32_t est_batches = 0, est_batch_rays = 0, est_n = 0;

@@ -227,6 +227,7 @@ __host__ __device__ inline LeafArgs shift_args(LeafArgs A, size_t off) {
     if (A.span) A.span += off;
     if (A.hitCounts) A.hitCounts += off;
     if (A.hitOffsets) A.hitOffsets += off;
+    if (A.frames) A.frames += off / WQ_P * 4;
     return A;
 }
 __global__ void k_store_batch_args(LeafArgs A, char *blocks, unsigned batchRays, unsigned nBatches) {
@@ -300,6 +301,11 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     A.t = tree_view(ctx); A.m = ctx->medium; A.ro = ro; A.rd = rd; A.nPathsNorm = nPathsNorm;
     A.out = out; A.tau = tau; A.span = span; A.tauSteps = ctx->tau_steps;
     A.hitCounts = hitCounts; A.hitOffsets = hitOffsets; A.hitIdx = hitIdx;
+    A.frames = nullptr;
+    if (ctx->fat_spread > 0.f) {   // one 64-byte frame per packet
+        if ((s = ensure(ctx, ctx->frames, ((size_t)n / WQ_P + 1) * 64)) != BRE_OK) return s;
+        A.frames = (float4 *)ctx->frames.p;
+    }
     k_store_batch_args<<<(nBatches + 63) / 64, 64, 0, ctx->stream>>>(A, blocks, batchRays, nBatches);
 
     // ---- heavy-first feedback between consecutive radiance queries over the same rays
@@ -353,7 +359,7 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
         if (blocksA > need) blocksA = need;
         k_traverse<MODE, COUNT><<<blocksA, WQ_WARPS * 32, 0, ctx->stream>>>(
             Ab, Ag, nb, queue, cap, ctl, heavyIn, nHeavyIn, heavyFlagIn, heavyOut, heavyFlagOut, nHeavyOut,
-            heavyCap, counters);
+            heavyCap, ctx->fat_spread, counters);
         cudaStream_t sb = ctx->stream;
         if (piped) {
             BRE_CUDA(cudaEventRecord(ctx->qev[b & 1u], ctx->stream));
@@ -371,12 +377,17 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
                 cudaEventRecord(ctx->ev[PH_QUERY_B][0], ctx->stream);
             }
         }
-        if (ctx->max_leaf <= 4)
+        // both leaf kernels scan the queue; each leaves at once if K5a emitted no pair of its kind
+        if (ctx->max_leaf <= 4) {
+            k_leaf_fat<MODE, COUNT, 4><<<gb, LP_WARPS * 32, 0, sb>>>(Ab, queue, cap, ctl, counters);
             k_leaf_pairs<MODE, COUNT, 4><<<gb, LP_WARPS * 32, 0, sb>>>(Ab, queue, cap, ctl, counters);
-        else if (ctx->max_leaf <= 8)
+        } else if (ctx->max_leaf <= 8) {
+            k_leaf_fat<MODE, COUNT, 8><<<gb, LP_WARPS * 32, 0, sb>>>(Ab, queue, cap, ctl, counters);
             k_leaf_pairs<MODE, COUNT, 8><<<gb, LP_WARPS * 32, 0, sb>>>(Ab, queue, cap, ctl, counters);
-        else
+        } else {
+            k_leaf_fat<MODE, COUNT, 16><<<gb, LP_WARPS * 32, 0, sb>>>(Ab, queue, cap, ctl, counters);
             k_leaf_pairs<MODE, COUNT, 16><<<gb, LP_WARPS * 32, 0, sb>>>(Ab, queue, cap, ctl, counters);
+        }
         if (piped) BRE_CUDA(cudaEventRecord(ctx->qev[2 + (b & 1u)], ctx->stream2));
     }
     if (piped) {   // join: everything K5b did is ordered before what follows on the context stream

@@ -37,15 +37,18 @@ constexpr int WQ_WARPS = 4;      // warps per block
 constexpr int WQ_RAYW = 12;      // floats per ray-table row (slab-test data only)
 constexpr unsigned WQ_CHUNK = 256;  // pair-queue slots reserved per atomicAdd
 constexpr unsigned PAIR_NONE = 0xffffffffu;  // padding pair (ray index) in a partly used chunk
+constexpr unsigned PAIR_FAT = 0x80000000u;   // pair.x bit: the pair stands for all WQ_P rays of a coherent packet
 constexpr unsigned HEAVY_STEPS = 256;   // a packet this long is claimed first by the next launch
 constexpr unsigned HEAVY_CAP = 65536;   // heavy packets remembered per launch
 
 // queueCtl words (zeroed before every launch)
-enum { QC_PAIR_TAIL = 0, QC_PACKET = 1, QC_INPLACE = 2, QC_EMITTED = 3, QC_WORDS = 8 };
+enum { QC_PAIR_TAIL = 0, QC_PACKET = 1, QC_INPLACE = 2, QC_EMITTED = 3, QC_KINDS = 4, QC_WORDS = 8 };
+enum { KIND_THIN = 1u, KIND_FAT = 2u };   // QC_KINDS bits: which kinds of pair K5a put into the queue
 
 struct __align__(16) WarpSmem {
     int nref[WQ_NCAP];
     float ray[WQ_P][WQ_RAYW];
+    float fat[24];               // FatRay of a coherent packet
     unsigned char nslot[WQ_NCAP];
 };
 
@@ -107,6 +110,98 @@ __device__ __forceinline__ bool slab_hit_f(const RayF &r, float lox, float loy, 
     return tMin <= tMax && tMin < r.tMax && tMax > 0.f;
 }
 
+// Coherent packets ("fat ray").  When the WQ_P rays of a packet leave (nearly) one point in (nearly)
+// one direction -- camera rays of neighbouring pixels -- the walk is done ONCE for the packet with an
+// interval version of the slab test and emits (packet, leaf) pairs; K5b then runs the exact disk
+// predicate for every ray of the packet, so hit sets are unchanged (the walk is only a cull).
+// Per axis, with all inv_i of one sign and x the plane offset from the padded common origin,
+//   near_i = x_i * inv_i >= min(x * invLo, x * invHi),   far_i <= max(x' * invLo, x' * invHi)
+// because the pad (the per-ray pad plus the spread of the origins) moves x below every x_i (above,
+// for the far plane).  If any ray passes its own slab test then every near_k <= far_l of that ray,
+// hence of these bounds: the fat test never culls a box a member ray would enter.
+struct FatRay {
+    float ax, ay, az;        // smallest 1/d per axis over the packet
+    float bx, by, bz;        // largest
+    float nax, nay, naz, nbx, nby, nbz;   // near constants for a / b
+    float fax, fay, faz, fbx, fby, fbz;   // far constants
+    float tMax;              // largest tMax of the packet
+    int sgn;
+};
+__device__ __forceinline__ void fat_store(float *row, const FatRay &r) {
+    float4 *v = reinterpret_cast<float4 *>(row);
+    v[0] = make_float4(r.ax, r.ay, r.az, r.tMax);
+    v[1] = make_float4(r.bx, r.by, r.bz, __int_as_float(r.sgn));
+    v[2] = make_float4(r.nax, r.nay, r.naz, r.nbx);
+    v[3] = make_float4(r.nby, r.nbz, r.fax, r.fay);
+    v[4] = make_float4(r.faz, r.fbx, r.fby, r.fbz);
+}
+__device__ __forceinline__ FatRay fat_load(const float *row) {
+    const float4 *v = reinterpret_cast<const float4 *>(row);
+    const float4 a = v[0], b = v[1], c = v[2], d = v[3], e = v[4];
+    FatRay r;
+    r.ax = a.x; r.ay = a.y; r.az = a.z; r.tMax = a.w;
+    r.bx = b.x; r.by = b.y; r.bz = b.z; r.sgn = __float_as_int(b.w);
+    r.nax = c.x; r.nay = c.y; r.naz = c.z; r.nbx = c.w;
+    r.nby = d.x; r.nbz = d.y; r.fax = d.z; r.fay = d.w;
+    r.faz = e.x; r.fbx = e.y; r.fby = e.z; r.fbz = e.w;
+    return r;
+}
+__device__ __forceinline__ bool slab_hit_fat(const FatRay &r, float lox, float loy, float loz, float hix,
+                                             float hiy, float hiz) {
+    const bool sx = r.sgn & 1, sy = r.sgn & 2, sz = r.sgn & 4;
+    const float nx = sx ? hix : lox, fx = sx ? lox : hix;
+    const float ny = sy ? hiy : loy, fy = sy ? loy : hiy;
+    const float nz = sz ? hiz : loz, fz = sz ? loz : hiz;
+    const float tx0 = fminf(__fmaf_rn(nx, r.ax, r.nax), __fmaf_rn(nx, r.bx, r.nbx));
+    const float ty0 = fminf(__fmaf_rn(ny, r.ay, r.nay), __fmaf_rn(ny, r.by, r.nby));
+    const float tz0 = fminf(__fmaf_rn(nz, r.az, r.naz), __fmaf_rn(nz, r.bz, r.nbz));
+    const float tx1 = fmaxf(__fmaf_rn(fx, r.ax, r.fax), __fmaf_rn(fx, r.bx, r.fbx));
+    const float ty1 = fmaxf(__fmaf_rn(fy, r.ay, r.fay), __fmaf_rn(fy, r.by, r.fby));
+    const float tz1 = fmaxf(__fmaf_rn(fz, r.az, r.faz), __fmaf_rn(fz, r.bz, r.fbz));
+    const float tMin = fmaxf(fmaxf(tx0, ty0), tz0);
+    const float tMax = fmul(fminf(fminf(tx1, ty1), tz1), BRE_SLAB_WIDEN);
+    return tMin <= tMax && tMin < r.tMax && tMax > 0.f;
+}
+// min / max over the 8 lanes of a packet (lanes 0..WQ_P-1 hold the rays)
+__device__ __forceinline__ float pk_min(float v) {
+#pragma unroll
+    for (int o = 1; o < WQ_P; o <<= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ float pk_max(float v) {
+#pragma unroll
+    for (int o = 1; o < WQ_P; o <<= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// Photon pretest of a coherent packet (k_leaf_fat).  K5a fits an orthonormal frame (u, v, n) to the
+// packet -- u the bisector of its first and last direction, v the direction the rays fan out in, n
+// their common normal -- and stores, in this frame, the range [mLo, mHi] of the slopes m_i =
+// (d_i.v)/(d_i.u), 1/kappa with kappa = min_i (d_i.u)/|(d_i.u, d_i.v)|, and hT = max_i|d_i.n| * tau
+// + slack (tau bounds the ray parameter of any hit).  For P' = P - o and ANY orthonormal frame
+//   dist(P, ray_i) >= |P'.n| - |d_i.n| tau_i          and   dist(P, ray_i) >= |P'.v - m_i P'.u| kappa_i,
+// so a photon with |P'.n| > r + hT, or with P'.v outside [min(mLo t, mHi t) - R, max(..) + R],
+// R = r / kappa + hT, t = P'.u, is missed by every ray of the packet.  The slack (4 x origin spread
+// + 2^-16 x coordinate scale) covers the origins' differences and every rounding error of this test
+// and of the exact predicate by more than 10x.  Only photons that pass are tested exactly, per ray.
+struct PacketFrame {
+    float4 a;   // o.xyz, hT
+    float4 b;   // u.xyz, 1/kappa
+    float4 c;   // v.xyz, mLo
+    float4 d;   // n.xyz, mHi
+};
+__device__ __forceinline__ bool frame_may_hit(const float4 fa, const float4 fb, const float4 fc, const float4 fd,
+                                              const float4 p) {
+    const float x = p.x - fa.x, y = p.y - fa.y, z = p.z - fa.z;
+    const float h = __fmaf_rn(z, fd.z, __fmaf_rn(y, fd.y, x * fd.x));
+    const float t = __fmaf_rn(z, fb.z, __fmaf_rn(y, fb.y, x * fb.x));
+    const float s = __fmaf_rn(z, fc.z, __fmaf_rn(y, fc.y, x * fc.x));
+    const float R = __fmaf_rn(p.w, fb.w, fa.w);
+    const float m0 = t * fc.w, m1 = t * fd.w;
+    // written so that a NaN anywhere keeps the photon
+    return !(fabsf(h) > p.w + fa.w) && !(s > fmaxf(m0, m1) + R) && !(s < fminf(m0, m1) - R);
+}
+
 // Everything K5b needs besides the pair itself.
 struct LeafArgs {
     TreeDev t;
@@ -120,6 +215,7 @@ struct LeafArgs {
     uint32_t *hitCounts;         // MODE 1: per-ray hit counts; MODE 2: per-ray write cursors
     const uint64_t *hitOffsets;  // MODE 2
     uint32_t *hitIdx;            // MODE 2
+    float4 *frames;              // 4 float4 per packet: PacketFrame of coherent packets (K5a -> k_leaf_fat)
 };
 
 // Radiance of one hit (photon s, ray q, ray parameter th, squared distance d2).
@@ -208,19 +304,22 @@ __device__ __forceinline__ void record_hit(const LeafArgs &A, int mode, uint32_t
 // arguments through a pointer to their copy in global memory: passing the kernel-parameter struct
 // itself would force a 296-byte local-memory copy of it into every thread of the hot kernel.
 template <int MODE>
-__device__ __noinline__ void process_pair_inplace(const LeafArgs *Ag, uint32_t q, int ref) {
+__device__ __noinline__ void process_pair_inplace(const LeafArgs *Ag, uint32_t px, int ref) {
     const LeafArgs &A = *Ag;
-    const float4 o = __ldg(A.ro + q), d = __ldg(A.rd + q);
-    RayS r;
-    r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tMax = o.w;
-    r.dx = d.x; r.dy = d.y; r.dz = d.z;
+    const uint32_t q0 = px & ~PAIR_FAT, nq = (px & PAIR_FAT) ? (uint32_t)WQ_P : 1u;
     const uint32_t first = (uint32_t)ref & 0x07ffffffu;
     const uint32_t cnt = (((uint32_t)ref >> 27) & 15u) + 1u;
-    for (uint32_t j = 0; j < cnt; ++j) {
-        float th, d2;
-        if (disk_test(r, __ldg(A.t.s_pos_r + first + j), th, d2)) {
-            if (MODE == 0) shade_hit(A, first + j, q, th, d2);
-            else record_hit(A, MODE, first + j, q);
+    for (uint32_t q = q0; q < q0 + nq; ++q) {
+        const float4 o = __ldg(A.ro + q), d = __ldg(A.rd + q);
+        RayS r;
+        r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tMax = o.w;
+        r.dx = d.x; r.dy = d.y; r.dz = d.z;
+        for (uint32_t j = 0; j < cnt; ++j) {
+            float th, d2;
+            if (disk_test(r, __ldg(A.t.s_pos_r + first + j), th, d2)) {
+                if (MODE == 0) shade_hit(A, first + j, q, th, d2);
+                else record_hit(A, MODE, first + j, q);
+            }
         }
     }
 }
@@ -244,7 +343,7 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
     const unsigned int *__restrict__ heavyIn, const unsigned int *__restrict__ nHeavyInPtr,
     const unsigned int *__restrict__ heavyFlagIn, unsigned int *__restrict__ heavyOut,
     unsigned int *__restrict__ heavyFlagOut, unsigned int *__restrict__ nHeavyOut,
-    unsigned int heavyCap,
+    unsigned int heavyCap, float fatSpread,
     unsigned long long *__restrict__ counters) {
     __shared__ WarpSmem smemAll[WQ_WARPS];
     WarpSmem &sm = smemAll[threadIdx.x >> 5];
@@ -255,7 +354,7 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
     const unsigned nPackets = (n + WQ_P - 1) / WQ_P;
     const unsigned nHeavyIn = min(__ldg(nHeavyInPtr), HEAVY_CAP);
     unsigned long long cNodes = 0;
-    unsigned nEmitted = 0, nInplace = 0;
+    unsigned nEmitted = 0, nInplace = 0, kinds = 0;
     unsigned chunkPos = 0, chunkEnd = 0;   // this warp's reserved queue slots [chunkPos, chunkEnd)
 
     for (;;) {
@@ -277,17 +376,90 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
         unsigned steps = 0;
 
         // ---- packet setup: lane s < np prepares ray base+s and pushes the root for it
+        // (with a full packet every group of WQ_P lanes loads the same rays, so the packet-wide
+        // reductions below leave the same value in all lanes)
         bool live = false;
-        if (lane < np) {
-            const float4 o = __ldg(A.ro + base + lane);
-            RayF r = rayf_setup(o, __ldg(A.rd + base + lane), t.abs_max);
-            rayf_store(sm.ray[lane], r);
-            live = t.n > 0 && r.tMax > 0.f;
+        const bool full = np == WQ_P;
+        float4 o = make_float4(0.f, 0.f, 0.f, 0.f), d = make_float4(0.f, 0.f, 1.f, 0.f);
+        RayF r;
+        if (lane < np || full) {
+            o = __ldg(A.ro + base + (lane & (WQ_P - 1)));
+            d = __ldg(A.rd + base + (lane & (WQ_P - 1)));
+            r = rayf_setup(o, d, t.abs_max);
+            if (lane < np) rayf_store(sm.ray[lane], r);
+            live = lane < np && t.n > 0 && r.tMax > 0.f;
+        }
+        bool fat = false;
+        if (full && fatSpread > 0.f && t.n > 0) {
+            const float ox0 = __shfl_sync(FULL, o.x, 0), oy0 = __shfl_sync(FULL, o.y, 0), oz0 = __shfl_sync(FULL, o.z, 0);
+            const float dx0 = __shfl_sync(FULL, d.x, 0), dy0 = __shfl_sync(FULL, d.y, 0), dz0 = __shfl_sync(FULL, d.z, 0);
+            const int sgn0 = __shfl_sync(FULL, r.sgn, 0);
+            const float oSpread = pk_max(fmaxf(fmaxf(fabsf(o.x - ox0), fabsf(o.y - oy0)), fabsf(o.z - oz0)));
+            const float dSpread = pk_max(fmaxf(fmaxf(fabsf(d.x - dx0), fabsf(d.y - dy0)), fabsf(d.z - dz0)));
+            const float M = pk_max(fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z))) + t.abs_max;
+            const float tMaxAll = pk_max(r.tMax);
+            // NaNs fail the comparisons and fall back to the per-ray walk
+            fat = __all_sync(FULL, r.sgn == sgn0) && dSpread <= fatSpread && oSpread <= M * 0x1p-10f &&
+                  tMaxAll > 0.f;
+            if (fat) {
+                FatRay f;
+                f.ax = pk_min(r.ix); f.ay = pk_min(r.iy); f.az = pk_min(r.iz);
+                f.bx = pk_max(r.ix); f.by = pk_max(r.iy); f.bz = pk_max(r.iz);
+                const float pad = 2.f * (M * 0x1p-18f) + 2.f * oSpread;
+                const float px = (sgn0 & 1) ? -pad : pad, py = (sgn0 & 2) ? -pad : pad, pz = (sgn0 & 4) ? -pad : pad;
+                const float nx = fadd(ox0, px), ny = fadd(oy0, py), nz = fadd(oz0, pz);
+                const float fx = fsub(ox0, px), fy = fsub(oy0, py), fz = fsub(oz0, pz);
+                f.nax = -fmul(nx, f.ax); f.nay = -fmul(ny, f.ay); f.naz = -fmul(nz, f.az);
+                f.nbx = -fmul(nx, f.bx); f.nby = -fmul(ny, f.by); f.nbz = -fmul(nz, f.bz);
+                f.fax = -fmul(fx, f.ax); f.fay = -fmul(fy, f.ay); f.faz = -fmul(fz, f.az);
+                f.fbx = -fmul(fx, f.bx); f.fby = -fmul(fy, f.by); f.fbz = -fmul(fz, f.bz);
+                f.tMax = tMaxAll; f.sgn = sgn0;
+                if (lane == 0) fat_store(sm.fat, f);
+                // the packet's frame for k_leaf_fat (not bit-critical: any orthonormal frame is valid)
+                const float d7x = __shfl_sync(FULL, d.x, WQ_P - 1), d7y = __shfl_sync(FULL, d.y, WQ_P - 1),
+                            d7z = __shfl_sync(FULL, d.z, WQ_P - 1);
+                float ux = dx0 + d7x, uy = dy0 + d7y, uz = dz0 + d7z;
+                const float ul = rsqrtf(ux * ux + uy * uy + uz * uz);
+                ux *= ul; uy *= ul; uz *= ul;
+                float wx = d7x - dx0, wy = d7y - dy0, wz = d7z - dz0;
+                const float wu = wx * ux + wy * uy + wz * uz;
+                wx -= wu * ux; wy -= wu * uy; wz -= wu * uz;
+                float wl = wx * wx + wy * wy + wz * wz;
+                if (!(wl > 1e-24f)) {        // all directions equal: any perpendicular will do
+                    const float ax = fabsf(ux), ay = fabsf(uy), az = fabsf(uz);
+                    if (ax <= ay && ax <= az) { wx = 0.f; wy = -uz; wz = uy; }
+                    else if (ay <= az) { wx = uz; wy = 0.f; wz = -ux; }
+                    else { wx = -uy; wy = ux; wz = 0.f; }
+                    wl = wx * wx + wy * wy + wz * wz;
+                }
+                const float wi = rsqrtf(wl);
+                const float vx = wx * wi, vy = wy * wi, vz = wz * wi;
+                const float nx2 = uy * vz - uz * vy, ny2 = uz * vx - ux * vz, nz2 = ux * vy - uy * vx;
+                const float da = d.x * ux + d.y * uy + d.z * uz, db = d.x * vx + d.y * vy + d.z * vz,
+                            dc = d.x * nx2 + d.y * ny2 + d.z * nz2;
+                const float m = __fdividef(db, da);
+                const float kap = da * rsqrtf(da * da + db * db);
+                const float aMin = pk_min(da), kMin = pk_min(kap), cMax = pk_max(fabsf(dc));
+                const float mLo = pk_min(m), mHi = pk_max(m);
+                const float tau = fminf(tMaxAll, 4.f * M);
+                if (!(aMin > 0.5f)) fat = false;       // (never with the spread limit; NaN-safe)
+                else if (lane == 0) {
+                    const float hT = 1.01f * cMax * tau + 4.f * oSpread + M * 0x1p-16f;
+                    float4 *fr = A.frames + (size_t)pk * 4;
+                    fr[0] = make_float4(ox0, oy0, oz0, hT);
+                    fr[1] = make_float4(ux, uy, uz, 1.001f * __fdividef(1.f, kMin));
+                    fr[2] = make_float4(vx, vy, vz, mLo);
+                    fr[3] = make_float4(nx2, ny2, nz2, mHi);
+                }
+            }
         }
         int nsize = 0;
         bool e0 = false, e1 = false;   // leaf children to emit this step
         int c0 = 0, c1 = 0, slot = (int)lane;
-        {
+        if (fat) {              // one walk for the whole packet
+            if (t.root_ref >= 0) { if (lane == 0) sm.nref[0] = t.root_ref; nsize = 1; }
+            else { e0 = lane == 0; c0 = t.root_ref; }
+        } else {
             const unsigned mlive = __ballot_sync(FULL, live);
             if (t.root_ref >= 0) {
                 if (live) { int pos = __popc(mlive & lt); sm.nref[pos] = t.root_ref; sm.nslot[pos] = (unsigned char)lane; }
@@ -315,13 +487,15 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
                 const unsigned p0 = chunkPos + __popc(ml0 & lt);
                 const unsigned p1 = chunkPos + __popc(ml0) + __popc(ml1 & lt);
                 chunkPos += nl;
+                const unsigned px = fat ? (base | PAIR_FAT) : base + slot;
+                kinds |= fat ? KIND_FAT : KIND_THIN;
                 if (e0) {
-                    if (p0 < queueCap) queue[p0] = make_uint2(base + slot, (unsigned)c0);
-                    else { process_pair_inplace<MODE>(Ag, base + slot, c0); ++nInplace; }
+                    if (p0 < queueCap) queue[p0] = make_uint2(px, (unsigned)c0);
+                    else { process_pair_inplace<MODE>(Ag, px, c0); ++nInplace; }
                 }
                 if (e1) {
-                    if (p1 < queueCap) queue[p1] = make_uint2(base + slot, (unsigned)c1);
-                    else { process_pair_inplace<MODE>(Ag, base + slot, c1); ++nInplace; }
+                    if (p1 < queueCap) queue[p1] = make_uint2(px, (unsigned)c1);
+                    else { process_pair_inplace<MODE>(Ag, px, c1); ++nInplace; }
                 }
                 if (COUNT) nEmitted += (e0 ? 1u : 0u) + (e1 ? 1u : 0u);
             }
@@ -341,9 +515,15 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
                 const FastNode *fn = t.fast + ref;
                 const float4 a = __ldg(&fn->a), b = __ldg(&fn->b), c = __ldg(&fn->c);
                 const int4 d = __ldg(&fn->d);
-                const RayF r = rayf_load(sm.ray[slot]);
-                h0 = slab_hit_f(r, a.x, a.y, a.z, a.w, b.x, b.y);
-                h1 = slab_hit_f(r, b.z, b.w, c.x, c.y, c.z, c.w);
+                if (fat) {
+                    const FatRay f = fat_load(sm.fat);
+                    h0 = slab_hit_fat(f, a.x, a.y, a.z, a.w, b.x, b.y);
+                    h1 = slab_hit_fat(f, b.z, b.w, c.x, c.y, c.z, c.w);
+                } else {
+                    const RayF r = rayf_load(sm.ray[slot]);
+                    h0 = slab_hit_f(r, a.x, a.y, a.z, a.w, b.x, b.y);
+                    h1 = slab_hit_f(r, b.z, b.w, c.x, c.y, c.z, c.w);
+                }
                 c0 = d.x; c1 = d.y;
                 if (COUNT) ++cNodes;
             }
@@ -369,6 +549,7 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
     for (unsigned p = chunkPos + lane; p < chunkEnd; p += 32)
         if (p < queueCap) queue[p] = make_uint2(PAIR_NONE, 0u);
     if (nInplace) atomicAdd(queueCtl + QC_INPLACE, nInplace);
+    if (lane == 0 && kinds) atomicOr(queueCtl + QC_KINDS, kinds);
     if (COUNT) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -407,6 +588,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, 4) k_leaf_pairs(LeafArgs A,
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt = (1u << lane) - 1u;
     const unsigned sub = lane / LW, j = lane % LW;
+    if (!(__ldg(queueCtl + QC_KINDS) & KIND_THIN)) return;
     const unsigned total = min(__ldg(queueCtl + QC_PAIR_TAIL), queueCap);
     const unsigned warpsTotal = gridDim.x * LP_WARPS;
     const unsigned warpId = blockIdx.x * LP_WARPS + (threadIdx.x >> 5);
@@ -417,6 +599,9 @@ __global__ void __launch_bounds__(LP_WARPS * 32, 4) k_leaf_pairs(LeafArgs A,
         uint2 pr0 = make_uint2(PAIR_NONE, 0u), pr1 = make_uint2(PAIR_NONE, 0u);
         if (run + lane < total) pr0 = __ldg(queue + run + lane);
         if (run + 32 + lane < total) pr1 = __ldg(queue + run + 32 + lane);
+        // pairs of coherent packets (PAIR_FAT) belong to k_leaf_fat; a run is almost always all of
+        // one kind (a K5a warp fills its chunks packet by packet)
+        if (!__any_sync(FULL, !(pr0.x & PAIR_FAT) || !(pr1.x & PAIR_FAT))) continue;
 #pragma unroll 1
         for (unsigned g0 = 0; g0 < LP_RUN / G; g0 += U) {
             // ---- issue every load of U pair-groups before the first use
@@ -432,7 +617,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, 4) k_leaf_pairs(LeafArgs A,
                 q[u] = qx;
                 first[u] = qy & 0x07ffffffu;
                 const uint32_t cnt = ((qy >> 27) & 15u) + 1u;
-                on[u] = qx != PAIR_NONE && j < cnt;
+                on[u] = !(qx & PAIR_FAT) && j < cnt;      // PAIR_NONE has the bit set too
                 if (on[u]) {
                     p[u] = __ldg(A.t.s_pos_r + first[u] + j);
                     if (RAYPF) { o[u] = __ldg(A.ro + qx); d[u] = __ldg(A.rd + qx); }
@@ -478,6 +663,139 @@ __global__ void __launch_bounds__(LP_WARPS * 32, 4) k_leaf_pairs(LeafArgs A,
         if (lane < nbuf) { s = hb.s[lane]; q = hb.q[lane]; th = hb.th[lane]; d2 = hb.d2[lane]; }
         if (SEG) shade_hits_warp(A, lane, nbuf, s, q, th, d2);
         else if (lane < nbuf) shade_hit(A, s, q, th, d2);
+    }
+    if (COUNT) {
+#pragma unroll
+        for (int o2 = 16; o2 > 0; o2 >>= 1) cTests += __shfl_xor_sync(FULL, cTests, o2);
+        if (lane == 0 && cTests) atomicAdd(counters + 4, cTests);
+    }
+}
+
+// ---------------------------------------------------------------- K5b for coherent packets
+// (packet, leaf) pairs, two stages per warp:
+//  1. one photon per lane (LW lanes per pair, like k_leaf_pairs): the photon is tested ONCE against
+//     the packet's frame (frame_may_hit); survivors are compacted into a shared-memory buffer.
+//  2. whenever 4 survivors are buffered: lane = (ray of the packet, survivor) runs the exact disk
+//     predicate, 32 per pass with every lane busy.  Hits go through the same buffer / warp shading
+//     as in k_leaf_pairs.
+// On the bench scene 30 % of the photons of a packet's leaves survive stage 1, so a photon costs
+// ~1 + 0.3 x 8 predicates instead of 8.
+struct __align__(16) FatBuf {
+    float4 p[64];        // surviving photon {pos, radius}
+    uint32_t s[64];      // its index
+    uint32_t base[64];   // first ray of its packet
+};
+template <int MODE, bool COUNT, int LW>
+__global__ void __launch_bounds__(LP_WARPS * 32, 3) k_leaf_fat(LeafArgs A, const uint2 *__restrict__ queue,
+                                                            unsigned int queueCap,
+                                                            const unsigned int *__restrict__ queueCtl,
+                                                            unsigned long long *__restrict__ counters) {
+    __shared__ HitBuf bufAll[LP_WARPS];
+    __shared__ FatBuf fatAll[LP_WARPS];
+    HitBuf &hb = bufAll[threadIdx.x >> 5];
+    FatBuf &fb = fatAll[threadIdx.x >> 5];
+    constexpr unsigned G = 32 / LW;
+    constexpr int U = 2;
+    constexpr unsigned SLOTS = 32 / WQ_P;              // survivors per stage-2 pass
+    const unsigned FULL = 0xffffffffu;
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt = (1u << lane) - 1u;
+    const unsigned sub = lane / LW, j = lane % LW;
+    const unsigned ray = lane / SLOTS, slot = lane % SLOTS;
+    if (!(__ldg(queueCtl + QC_KINDS) & KIND_FAT)) return;
+    const unsigned total = min(__ldg(queueCtl + QC_PAIR_TAIL), queueCap);
+    const unsigned warpsTotal = gridDim.x * LP_WARPS;
+    const unsigned warpId = blockIdx.x * LP_WARPS + (threadIdx.x >> 5);
+    unsigned long long cTests = 0;
+    unsigned nbuf = 0, npb = 0;
+
+    // stage 2 over the newest `take` survivors (take <= SLOTS)
+    auto exact_pass = [&](unsigned take) {
+        bool hit = false;
+        float th = 0.f, d2 = 0.f;
+        uint32_t s = 0, q = 0;
+        if (slot < take) {
+            const unsigned e = npb - take + slot;
+            const float4 p = fb.p[e];
+            s = fb.s[e];
+            q = fb.base[e] + ray;
+            const float4 o = __ldg(A.ro + q), d = __ldg(A.rd + q);
+            RayS r;
+            r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tMax = o.w;
+            r.dx = d.x; r.dy = d.y; r.dz = d.z;
+            hit = disk_test(r, p, th, d2);
+            if (COUNT) ++cTests;
+        }
+        npb -= take;
+        if (MODE != 0) {
+            if (hit) record_hit(A, MODE, s, q);
+            return;
+        }
+        const unsigned mh = __ballot_sync(FULL, hit);
+        if (mh == 0u) return;
+        if (hit) {
+            const unsigned pos = nbuf + __popc(mh & lt);
+            hb.s[pos] = s; hb.q[pos] = q; hb.th[pos] = th; hb.d2[pos] = d2;
+        }
+        nbuf += __popc(mh);
+        __syncwarp();
+        if (nbuf >= 32) {
+            const unsigned e = nbuf - 32 + lane;
+            shade_hits_warp(A, lane, 32u, hb.s[e], hb.q[e], hb.th[e], hb.d2[e]);
+            nbuf -= 32;
+            __syncwarp();
+        }
+    };
+
+    for (unsigned run = warpId * LP_RUN; run < total; run += warpsTotal * LP_RUN) {
+        uint2 pr0 = make_uint2(PAIR_NONE, 0u), pr1 = make_uint2(PAIR_NONE, 0u);
+        if (run + lane < total) pr0 = __ldg(queue + run + lane);
+        if (run + 32 + lane < total) pr1 = __ldg(queue + run + 32 + lane);
+        if (!__any_sync(FULL, (pr0.x != PAIR_NONE && (pr0.x & PAIR_FAT)) || (pr1.x != PAIR_NONE && (pr1.x & PAIR_FAT))))
+            continue;
+#pragma unroll 1
+        for (unsigned g0 = 0; g0 < LP_RUN / G; g0 += U) {
+            uint32_t base[U], first[U];
+            bool on[U];
+            float4 p[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const unsigned idx = (g0 + u) * G + sub;
+                const bool lower = (g0 + u) * G < 32u;             // warp-uniform
+                const unsigned qx = __shfl_sync(FULL, lower ? pr0.x : pr1.x, idx & 31u);
+                const unsigned qy = __shfl_sync(FULL, lower ? pr0.y : pr1.y, idx & 31u);
+                base[u] = qx & ~PAIR_FAT;
+                first[u] = qy & 0x07ffffffu;
+                const uint32_t cnt = ((qy >> 27) & 15u) + 1u;
+                on[u] = qx != PAIR_NONE && (qx & PAIR_FAT) && j < cnt;
+                if (on[u]) p[u] = __ldg(A.t.s_pos_r + first[u] + j);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                bool keep = false;
+                if (on[u]) {
+                    const float4 *fr = A.frames + (size_t)(base[u] / WQ_P) * 4;
+                    keep = frame_may_hit(__ldg(fr), __ldg(fr + 1), __ldg(fr + 2), __ldg(fr + 3), p[u]);
+                    if (COUNT) ++cTests;
+                }
+                const unsigned mk = __ballot_sync(FULL, keep);
+                if (mk == 0u) continue;
+                if (keep) {
+                    const unsigned pos = npb + __popc(mk & lt);
+                    fb.p[pos] = p[u]; fb.s[pos] = first[u] + j; fb.base[pos] = base[u];
+                }
+                npb += __popc(mk);
+                __syncwarp();
+                while (npb >= SLOTS) exact_pass(SLOTS);
+                __syncwarp();
+            }
+        }
+    }
+    if (npb) exact_pass(npb);
+    if (MODE == 0 && nbuf) {
+        uint32_t s = 0, q = 0; float th = 0.f, d2 = 0.f;
+        if (lane < nbuf) { s = hb.s[lane]; q = hb.q[lane]; th = hb.th[lane]; d2 = hb.d2[lane]; }
+        shade_hits_warp(A, lane, nbuf, s, q, th, d2);
     }
     if (COUNT) {
 #pragma unroll

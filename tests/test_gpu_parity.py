@@ -264,6 +264,47 @@ def test_pair_queue_overflow_path(oracle, bre, monkeypatch, cap):
         c.close()
 
 
+def narrow_pinhole(w, h, pitch=7e-4):
+    """Rays of a pinhole at (0.5, 0.5, -1.5) through a w x h window of `pitch` rad pixels."""
+    x, y = np.meshgrid(np.arange(w, dtype=np.float32), np.arange(h, dtype=np.float32))
+    d = np.stack([(x - 0.5 * (w - 1)) * pitch, (y - 0.5 * (h - 1)) * pitch * 40, np.ones_like(x)], -1).reshape(-1, 3)
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    o = np.empty((w * h, 4), np.float32)
+    o[:, :3] = (0.5, 0.5, -1.5)
+    o[:, 3] = 3.0
+    return o, d
+
+
+@pytest.mark.parametrize("cap", [0, 3000])
+@pytest.mark.parametrize("spread", ["default", "0.5", "0"])
+@pytest.mark.parametrize("leaf", [4, 8, 16])
+def test_coherent_packets_walked_as_one_fat_ray(oracle, bre, monkeypatch, spread, leaf, cap):
+    """Neighbouring camera rays are walked once per packet of 8 (interval slab test) and resolved
+    per ray by the exact disk predicate: hit sets must not depend on whether a packet took the fat
+    walk (default threshold, a huge threshold that makes every same-octant packet fat, or off),
+    also through the in-place overflow path."""
+    if spread != "default":
+        monkeypatch.setenv("BRE_FAT_SPREAD", spread)
+    if cap:
+        monkeypatch.setenv("BRE_PAIR_QUEUE_CAP", str(cap))
+    c = bre.Bre(device=0, max_leaf_photons=leaf)
+    try:
+        n = 60000
+        setup_uniform(oracle, c, n, 32)
+        ro, rd = narrow_pinhole(1029, 3)                # 7e-4 rad between neighbours, ragged tail
+        ro[100:108, 3] = 0.0                            # a dead packet
+        ro[200:204, 3] = 0.0                            # and a half-dead one
+        ref_rgb, ref_offs, ref_idx, _ = oracle.query(ro, rd, float(n), want_hits=True)
+        rgb, offs, idx = c.query(ro, rd, float(n), want_hits=True)
+        assert ref_offs[-1] > 0
+        assert np.array_equal(offs, ref_offs) and np.array_equal(idx, ref_idx)
+        assert_radiance(rgb, ref_rgb)
+        cnt = c.count(ro, rd)
+        assert (cnt["pair_queue_overflow"] > 0) == bool(cap)
+    finally:
+        c.close()
+
+
 def test_heavy_ray_skew(oracle, ctx):
     """A ray through a dense photon cluster (light source in view): thousands of hits on one ray."""
     rng = np.random.default_rng(11)
