@@ -2,16 +2,18 @@
 NVCC ?= /usr/local/cuda/bin/nvcc
 PKG := beam-radiance-estimate-pbrt_b200
 CSRC := $(PKG)/csrc
-OBJDIR := build/obj
+OBJDIR ?= build/obj
+LIBOUT ?= $(PKG)/libbre.so
+NVEXTRA ?=
 # -fmad=false: the disk predicate / Morton code / slab test must round exactly like the CPU oracle.
 NVFLAGS := -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -fmad=false \
-           -Xcompiler -fPIC,-ffp-contract=off -Iinclude
+           -Xcompiler -fPIC,-ffp-contract=off -Iinclude $(NVEXTRA)
 SRCS := bre_api.cu bre_build.cu bre_query.cu bre_film.cu bre_trace.cu bre_camera.cu bre_io.cu
 OBJS := $(patsubst %.cu,$(OBJDIR)/%.o,$(SRCS)) $(OBJDIR)/bre_nccl.o
 
 .PHONY: all lib oracle ref clean
 all: lib oracle
-lib: $(PKG)/libbre.so
+lib: $(LIBOUT)
 
 $(OBJDIR)/%.o: $(CSRC)/%.cu $(CSRC)/bre_internal.cuh $(CSRC)/bre_query_warp.cuh $(CSRC)/bre_surface.cuh include/bre.h
 	@mkdir -p $(OBJDIR)
@@ -21,7 +23,7 @@ $(OBJDIR)/bre_nccl.o: $(CSRC)/bre_nccl.cpp $(CSRC)/bre_internal.cuh include/bre.
 	@mkdir -p $(OBJDIR)
 	$(NVCC) $(NVFLAGS) -x cu -c $< -o $@
 
-$(PKG)/libbre.so: $(OBJS)
+$(LIBOUT): $(OBJS)
 	$(NVCC) -shared -o $@ $(OBJS) -lcudart -ldl
 
 oracle:

@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbre.so")
+LIB_PATH = os.environ.get("BRE_LIB_PATH") or os.path.join(_HERE, "libbre.so")   # override: kernel-variant experiments
 
 BRE_OK = 0
 ERR_NAMES = {0: "BRE_OK", -1: "BRE_ERR_INVALID", -2: "BRE_ERR_NO_DEVICE", -3: "BRE_ERR_CUDA",

@@ -28,6 +28,7 @@
 // never correctness.  (A continuation queue that split deep stacks between warps was tried and
 // measured slower: DFS stacks stay shallow, see profiles/r01_k5_v4_experiments.md.)
 #pragma once
+#include <type_traits>
 
 namespace bre {
 
@@ -470,6 +471,8 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
         }
         __syncwarp();
 
+        auto walk = [&](auto fatTag) {
+        constexpr bool FAT = decltype(fatTag)::value;
         for (;;) {
             // ---- emit surviving leaves as (ray, leaf) pairs
             const unsigned ml0 = __ballot_sync(FULL, e0), ml1 = __ballot_sync(FULL, e1);
@@ -487,8 +490,8 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
                 const unsigned p0 = chunkPos + __popc(ml0 & lt);
                 const unsigned p1 = chunkPos + __popc(ml0) + __popc(ml1 & lt);
                 chunkPos += nl;
-                const unsigned px = fat ? (base | PAIR_FAT) : base + slot;
-                kinds |= fat ? KIND_FAT : KIND_THIN;
+                const unsigned px = FAT ? (base | PAIR_FAT) : base + slot;
+                kinds |= FAT ? KIND_FAT : KIND_THIN;
                 if (e0) {
                     if (p0 < queueCap) queue[p0] = make_uint2(px, (unsigned)c0);
                     else { process_pair_inplace<MODE>(Ag, px, c0); ++nInplace; }
@@ -507,7 +510,7 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
             const int k = room >= 1 ? min(min(32, nsize), room) : 1;
             const bool act = (int)lane < k;
             int ref = 0;
-            if (act) { ref = sm.nref[nsize - 1 - lane]; slot = sm.nslot[nsize - 1 - lane]; }
+            if (act) { ref = sm.nref[nsize - 1 - lane]; if (!FAT) slot = sm.nslot[nsize - 1 - lane]; }
             nsize -= k;
             ++steps;
             bool h0 = false, h1 = false;
@@ -515,7 +518,7 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
                 const FastNode *fn = t.fast + ref;
                 const float4 a = __ldg(&fn->a), b = __ldg(&fn->b), c = __ldg(&fn->c);
                 const int4 d = __ldg(&fn->d);
-                if (fat) {
+                if (FAT) {
                     const FatRay f = fat_load(sm.fat);
                     h0 = slab_hit_fat(f, a.x, a.y, a.z, a.w, b.x, b.y);
                     h1 = slab_hit_fat(f, b.z, b.w, c.x, c.y, c.z, c.w);
@@ -531,11 +534,13 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
             const bool n0 = h0 && c0 >= 0, n1 = h1 && c1 >= 0;
             e0 = h0 && c0 < 0; e1 = h1 && c1 < 0;
             const unsigned mn0 = __ballot_sync(FULL, n0), mn1 = __ballot_sync(FULL, n1);
-            if (n0) { int p = nsize + __popc(mn0 & lt); sm.nref[p] = c0; sm.nslot[p] = (unsigned char)slot; }
-            if (n1) { int p = nsize + __popc(mn0) + __popc(mn1 & lt); sm.nref[p] = c1; sm.nslot[p] = (unsigned char)slot; }
+            if (n0) { int p = nsize + __popc(mn0 & lt); sm.nref[p] = c0; if (!FAT) sm.nslot[p] = (unsigned char)slot; }
+            if (n1) { int p = nsize + __popc(mn0) + __popc(mn1 & lt); sm.nref[p] = c1; if (!FAT) sm.nslot[p] = (unsigned char)slot; }
             nsize += __popc(mn0) + __popc(mn1);
             __syncwarp();
         }
+        };
+        if (fat) walk(std::true_type{}); else walk(std::false_type{});
         // ---- remember heavy packets for the next launch
         if (steps >= HEAVY_STEPS && lane == 0) {
             const unsigned pos = heavyCap ? atomicAdd(nHeavyOut, 1u) : 0u;
@@ -685,8 +690,24 @@ struct __align__(16) FatBuf {
     uint32_t s[64];      // its index
     uint32_t base[64];   // first ray of its packet
 };
+// Tuning knobs (make NVEXTRA=-D...), measured on smoke10m_1080p, K5b ms:
+//   U=2,MINB=3,SEG=1 2.88 | U=4 2.75 | MINB=4 2.39 | SEG=0 2.35 | SEG=0,MINB=5 2.36 | SEG=0,MINB=6 2.65
+//   | SEG=0,U=4,MINB=4 2.24 (default).  Occupancy is what pays: stage 2 hands same-ray hits to
+//   non-adjacent lanes, so the segmented reduction merges little and only costs registers.
+#ifndef FAT_U
+#define FAT_U 4
+#endif
+#ifndef FAT_MINB
+#define FAT_MINB 4
+#endif
+#ifndef FAT_SEG
+#define FAT_SEG 0
+#endif
+#ifndef FAT_PREF
+#define FAT_PREF 0
+#endif
 template <int MODE, bool COUNT, int LW>
-__global__ void __launch_bounds__(LP_WARPS * 32, 3) k_leaf_fat(LeafArgs A, const uint2 *__restrict__ queue,
+__global__ void __launch_bounds__(LP_WARPS * 32, FAT_MINB) k_leaf_fat(LeafArgs A, const uint2 *__restrict__ queue,
                                                             unsigned int queueCap,
                                                             const unsigned int *__restrict__ queueCtl,
                                                             unsigned long long *__restrict__ counters) {
@@ -695,7 +716,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, 3) k_leaf_fat(LeafArgs A, const
     HitBuf &hb = bufAll[threadIdx.x >> 5];
     FatBuf &fb = fatAll[threadIdx.x >> 5];
     constexpr unsigned G = 32 / LW;
-    constexpr int U = 2;
+    constexpr int U = FAT_U;
     constexpr unsigned SLOTS = 32 / WQ_P;              // survivors per stage-2 pass
     const unsigned FULL = 0xffffffffu;
     const unsigned lane = threadIdx.x & 31u;
@@ -741,7 +762,8 @@ __global__ void __launch_bounds__(LP_WARPS * 32, 3) k_leaf_fat(LeafArgs A, const
         __syncwarp();
         if (nbuf >= 32) {
             const unsigned e = nbuf - 32 + lane;
-            shade_hits_warp(A, lane, 32u, hb.s[e], hb.q[e], hb.th[e], hb.d2[e]);
+            if (FAT_SEG) shade_hits_warp(A, lane, 32u, hb.s[e], hb.q[e], hb.th[e], hb.d2[e]);
+            else shade_hit(A, hb.s[e], hb.q[e], hb.th[e], hb.d2[e]);
             nbuf -= 32;
             __syncwarp();
         }
@@ -758,6 +780,9 @@ __global__ void __launch_bounds__(LP_WARPS * 32, 3) k_leaf_fat(LeafArgs A, const
             uint32_t base[U], first[U];
             bool on[U];
             float4 p[U];
+#if FAT_PREF
+            float4 f0[U], f1[U], f2[U], f3[U];
+#endif
 #pragma unroll
             for (int u = 0; u < U; ++u) {
                 const unsigned idx = (g0 + u) * G + sub;
@@ -768,14 +793,24 @@ __global__ void __launch_bounds__(LP_WARPS * 32, 3) k_leaf_fat(LeafArgs A, const
                 first[u] = qy & 0x07ffffffu;
                 const uint32_t cnt = ((qy >> 27) & 15u) + 1u;
                 on[u] = qx != PAIR_NONE && (qx & PAIR_FAT) && j < cnt;
-                if (on[u]) p[u] = __ldg(A.t.s_pos_r + first[u] + j);
+                if (on[u]) {
+                    p[u] = __ldg(A.t.s_pos_r + first[u] + j);
+#if FAT_PREF
+                    const float4 *fr = A.frames + (size_t)(base[u] / WQ_P) * 4;
+                    f0[u] = __ldg(fr); f1[u] = __ldg(fr + 1); f2[u] = __ldg(fr + 2); f3[u] = __ldg(fr + 3);
+#endif
+                }
             }
 #pragma unroll
             for (int u = 0; u < U; ++u) {
                 bool keep = false;
                 if (on[u]) {
+#if FAT_PREF
+                    keep = frame_may_hit(f0[u], f1[u], f2[u], f3[u], p[u]);
+#else
                     const float4 *fr = A.frames + (size_t)(base[u] / WQ_P) * 4;
                     keep = frame_may_hit(__ldg(fr), __ldg(fr + 1), __ldg(fr + 2), __ldg(fr + 3), p[u]);
+#endif
                     if (COUNT) ++cTests;
                 }
                 const unsigned mk = __ballot_sync(FULL, keep);
@@ -795,7 +830,8 @@ __global__ void __launch_bounds__(LP_WARPS * 32, 3) k_leaf_fat(LeafArgs A, const
     if (MODE == 0 && nbuf) {
         uint32_t s = 0, q = 0; float th = 0.f, d2 = 0.f;
         if (lane < nbuf) { s = hb.s[lane]; q = hb.q[lane]; th = hb.th[lane]; d2 = hb.d2[lane]; }
-        shade_hits_warp(A, lane, nbuf, s, q, th, d2);
+        if (FAT_SEG) shade_hits_warp(A, lane, nbuf, s, q, th, d2);
+        else if (lane < nbuf) shade_hit(A, s, q, th, d2);
     }
     if (COUNT) {
 #pragma unroll

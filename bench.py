@@ -321,7 +321,7 @@ def run_ours(args):
                 "d2h_bytes_per_step": int(nq * 12), "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches_per_step(world) * args.steps,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": traffic, "kernel": "K5 = k_traverse<0,false> + k_leaf_pairs<0,false>",
+                     "frac": achieved / peak, "traffic": traffic, "kernel": "K5 = k_traverse<0,false> + k_leaf_fat<0,false,8> (+ k_leaf_pairs<0,false,8> for incoherent packets)",
                      "kernel_ms": k5_ms, "algorithmic_bytes": int(cnt["bytes_algorithmic"]),
                      "own_structure_bytes": int(fast_bytes), "own_structure_gbs": fast_bytes / (k5_ms * 1e-3) / 1e9,
                      "peak_source": peak_src},
@@ -344,10 +344,11 @@ def launches_per_step(world):
     trace: k_trace, k_scan_reduce, k_scan_tiles, k_scan_apply, k_compact (one chunk of <= 4M paths)   5
     build: k_bounds_init, k_bounds, k_morton, 4 x (k_rs_hist, 3 scan launches, k_rs_scatter),
            k_gather, k_karras, k_refit, k_emit_fast                                                   27
-    query: k_tau_table, k_store_args, k_traverse, k_leaf_pairs                                        4
+    query: k_tau_table, k_store_args, k_traverse, k_leaf_fat, k_leaf_pairs (returns at once when
+           every packet was coherent)                                                                 5
     film:  k_film_add                                                                                 1
     (NCCL's own kernels at N > 1 are not counted.)"""
-    return 5 + 27 + 4 + 1
+    return 5 + 27 + 5 + 1
 
 
 def cpu_baseline_port(ctx, wl, ro_h, rd_h, n_paths, seconds):
