@@ -32,14 +32,26 @@
 
 namespace bre {
 
-constexpr int WQ_P = 8;          // rays per packet
-constexpr int WQ_NCAP = 512;     // node stack entries per warp
+// rays per packet: 8 / 16 / 32 measured on smoke10m_1080p -> K5a 1.40 / 1.39 / 1.65 ms (coherent),
+// 3.45 / 4.78 / 6.35 ms (per-ray walk): more rays per packet means more distinct ray rows per
+// shared-memory load (bank conflicts instead of broadcasts) and heavier tail packets
+#ifndef BRE_WQ_P
+#define BRE_WQ_P 8
+#endif
+#ifndef BRE_WQ_NCAP
+#define BRE_WQ_NCAP 512
+#endif
+constexpr int WQ_P = BRE_WQ_P;   // rays per packet (lane s < WQ_P prepares ray s)
+constexpr int FAT_P = 8;         // rays per coherent group ("fat ray"): WQ_P / FAT_P groups per packet
+constexpr int WQ_NCAP = BRE_WQ_NCAP;   // node stack entries per warp
 constexpr int WQ_WARPS = 4;      // warps per block
 constexpr int WQ_RAYW = 12;      // floats per ray-table row (slab-test data only)
 constexpr unsigned WQ_CHUNK = 256;  // pair-queue slots reserved per atomicAdd
 constexpr unsigned PAIR_NONE = 0xffffffffu;  // padding pair (ray index) in a partly used chunk
-constexpr unsigned PAIR_FAT = 0x80000000u;   // pair.x bit: the pair stands for all WQ_P rays of a coherent packet
-constexpr unsigned HEAVY_STEPS = 256;   // a packet this long is claimed first by the next launch
+constexpr unsigned PAIR_FAT = 0x80000000u;   // pair.x bit: the pair stands for the FAT_P rays of a coherent group
+constexpr unsigned HEAVY_STEPS = 512;   // a per-ray packet this long is claimed first by the next launch
+constexpr unsigned HEAVY_STEPS_FAT = 256;   // same for a coherent packet (measured: 256 / 512 -> K5a 1.31 / 1.40 ms
+                                            // coherent, 3.78 / 3.45 ms per-ray)
 constexpr unsigned HEAVY_CAP = 65536;   // heavy packets remembered per launch
 
 // queueCtl words (zeroed before every launch)
@@ -49,7 +61,7 @@ enum { KIND_THIN = 1u, KIND_FAT = 2u };   // QC_KINDS bits: which kinds of pair 
 struct __align__(16) WarpSmem {
     int nref[WQ_NCAP];
     float ray[WQ_P][WQ_RAYW];
-    float fat[24];               // FatRay of a coherent packet
+    float fat[WQ_P / FAT_P][24]; // FatRay of each coherent group
     unsigned char nslot[WQ_NCAP];
 };
 
@@ -163,15 +175,15 @@ __device__ __forceinline__ bool slab_hit_fat(const FatRay &r, float lox, float l
     const float tMax = fmul(fminf(fminf(tx1, ty1), tz1), BRE_SLAB_WIDEN);
     return tMin <= tMax && tMin < r.tMax && tMax > 0.f;
 }
-// min / max over the 8 lanes of a packet (lanes 0..WQ_P-1 hold the rays)
+// min / max over the FAT_P lanes of a group (lane = ray of the packet)
 __device__ __forceinline__ float pk_min(float v) {
 #pragma unroll
-    for (int o = 1; o < WQ_P; o <<= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    for (int o = 1; o < FAT_P; o <<= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
 }
 __device__ __forceinline__ float pk_max(float v) {
 #pragma unroll
-    for (int o = 1; o < WQ_P; o <<= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    for (int o = 1; o < FAT_P; o <<= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
     return v;
 }
 
@@ -307,7 +319,7 @@ __device__ __forceinline__ void record_hit(const LeafArgs &A, int mode, uint32_t
 template <int MODE>
 __device__ __noinline__ void process_pair_inplace(const LeafArgs *Ag, uint32_t px, int ref) {
     const LeafArgs &A = *Ag;
-    const uint32_t q0 = px & ~PAIR_FAT, nq = (px & PAIR_FAT) ? (uint32_t)WQ_P : 1u;
+    const uint32_t q0 = px & ~PAIR_FAT, nq = (px & PAIR_FAT) ? (uint32_t)FAT_P : 1u;
     const uint32_t first = (uint32_t)ref & 0x07ffffffu;
     const uint32_t cnt = (((uint32_t)ref >> 27) & 15u) + 1u;
     for (uint32_t q = q0; q < q0 + nq; ++q) {
@@ -376,36 +388,69 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
         const unsigned np = min((unsigned)WQ_P, n - base);
         unsigned steps = 0;
 
-        // ---- packet setup: lane s < np prepares ray base+s and pushes the root for it
-        // (with a full packet every group of WQ_P lanes loads the same rays, so the packet-wide
-        // reductions below leave the same value in all lanes)
+        // ---- packet setup: lane s < np prepares ray base+s.  A full packet whose groups of FAT_P
+        // rays (one group with the default WQ_P = 8) are each coherent or dead is walked with one
+        // fat ray per group; any other packet with one stack entry stream per ray.
         bool live = false;
-        const bool full = np == WQ_P;
         float4 o = make_float4(0.f, 0.f, 0.f, 0.f), d = make_float4(0.f, 0.f, 1.f, 0.f);
         RayF r;
-        if (lane < np || full) {
-            o = __ldg(A.ro + base + (lane & (WQ_P - 1)));
-            d = __ldg(A.rd + base + (lane & (WQ_P - 1)));
+        r.sgn = 0; r.tMax = 0.f; r.ix = r.iy = r.iz = 1.f;
+        if (lane < np) {
+            o = __ldg(A.ro + base + lane);
+            d = __ldg(A.rd + base + lane);
             r = rayf_setup(o, d, t.abs_max);
-            if (lane < np) rayf_store(sm.ray[lane], r);
-            live = lane < np && t.n > 0 && r.tMax > 0.f;
+            rayf_store(sm.ray[lane], r);
+            live = t.n > 0 && r.tMax > 0.f;
         }
         bool fat = false;
-        if (full && fatSpread > 0.f && t.n > 0) {
-            const float ox0 = __shfl_sync(FULL, o.x, 0), oy0 = __shfl_sync(FULL, o.y, 0), oz0 = __shfl_sync(FULL, o.z, 0);
-            const float dx0 = __shfl_sync(FULL, d.x, 0), dy0 = __shfl_sync(FULL, d.y, 0), dz0 = __shfl_sync(FULL, d.z, 0);
-            const int sgn0 = __shfl_sync(FULL, r.sgn, 0);
+        bool grpLive = false;      // my group takes part in the fat walk
+        if (np == WQ_P && fatSpread > 0.f && t.n > 0) {
+            const unsigned g0 = lane & ~(unsigned)(FAT_P - 1), gl = g0 + FAT_P - 1;   // first / last lane of my group
+            const float ox0 = __shfl_sync(FULL, o.x, g0), oy0 = __shfl_sync(FULL, o.y, g0), oz0 = __shfl_sync(FULL, o.z, g0);
+            const float dx0 = __shfl_sync(FULL, d.x, g0), dy0 = __shfl_sync(FULL, d.y, g0), dz0 = __shfl_sync(FULL, d.z, g0);
+            const int sgn0 = __shfl_sync(FULL, r.sgn, g0);
             const float oSpread = pk_max(fmaxf(fmaxf(fabsf(o.x - ox0), fabsf(o.y - oy0)), fabsf(o.z - oz0)));
             const float dSpread = pk_max(fmaxf(fmaxf(fabsf(d.x - dx0), fabsf(d.y - dy0)), fabsf(d.z - dz0)));
             const float M = pk_max(fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z))) + t.abs_max;
             const float tMaxAll = pk_max(r.tMax);
+            const unsigned sameSgn = __ballot_sync(FULL, r.sgn == sgn0);
+            const unsigned grpBits = ((1u << FAT_P) - 1u) << g0;
+            // the group's frame for k_leaf_fat (not bit-critical: any orthonormal frame is valid)
+            const float d7x = __shfl_sync(FULL, d.x, gl), d7y = __shfl_sync(FULL, d.y, gl), d7z = __shfl_sync(FULL, d.z, gl);
+            float ux = dx0 + d7x, uy = dy0 + d7y, uz = dz0 + d7z;
+            const float ul = rsqrtf(ux * ux + uy * uy + uz * uz);
+            ux *= ul; uy *= ul; uz *= ul;
+            float wx = d7x - dx0, wy = d7y - dy0, wz = d7z - dz0;
+            const float wu = wx * ux + wy * uy + wz * uz;
+            wx -= wu * ux; wy -= wu * uy; wz -= wu * uz;
+            float wl = wx * wx + wy * wy + wz * wz;
+            if (!(wl > 1e-24f)) {        // all directions equal: any perpendicular will do
+                const float ax = fabsf(ux), ay = fabsf(uy), az = fabsf(uz);
+                if (ax <= ay && ax <= az) { wx = 0.f; wy = -uz; wz = uy; }
+                else if (ay <= az) { wx = uz; wy = 0.f; wz = -ux; }
+                else { wx = -uy; wy = ux; wz = 0.f; }
+                wl = wx * wx + wy * wy + wz * wz;
+            }
+            const float wi = rsqrtf(wl);
+            const float vx = wx * wi, vy = wy * wi, vz = wz * wi;
+            const float nx2 = uy * vz - uz * vy, ny2 = uz * vx - ux * vz, nz2 = ux * vy - uy * vx;
+            const float da = d.x * ux + d.y * uy + d.z * uz, db = d.x * vx + d.y * vy + d.z * vz,
+                        dc = d.x * nx2 + d.y * ny2 + d.z * nz2;
+            const float m = __fdividef(db, da);
+            const float kap = da * rsqrtf(da * da + db * db);
+            const float aMin = pk_min(da), kMin = pk_min(kap), cMax = pk_max(fabsf(dc));
+            const float mLo = pk_min(m), mHi = pk_max(m);
             // NaNs fail the comparisons and fall back to the per-ray walk
-            fat = __all_sync(FULL, r.sgn == sgn0) && dSpread <= fatSpread && oSpread <= M * 0x1p-10f &&
-                  tMaxAll > 0.f;
-            if (fat) {
-                FatRay f;
-                f.ax = pk_min(r.ix); f.ay = pk_min(r.iy); f.az = pk_min(r.iz);
-                f.bx = pk_max(r.ix); f.by = pk_max(r.iy); f.bz = pk_max(r.iz);
+            const bool dead = !(tMaxAll > 0.f) && tMaxAll == tMaxAll;
+            const bool coh = (sameSgn & grpBits) == grpBits && dSpread <= fatSpread && oSpread <= M * 0x1p-10f &&
+                             aMin > 0.5f && tMaxAll > 0.f;
+            fat = __all_sync(FULL, dead || coh);
+            grpLive = fat && coh;
+            // (group reductions use full-mask shuffles: every lane must execute them)
+            FatRay f;
+            f.ax = pk_min(r.ix); f.ay = pk_min(r.iy); f.az = pk_min(r.iz);
+            f.bx = pk_max(r.ix); f.by = pk_max(r.iy); f.bz = pk_max(r.iz);
+            if (grpLive) {
                 const float pad = 2.f * (M * 0x1p-18f) + 2.f * oSpread;
                 const float px = (sgn0 & 1) ? -pad : pad, py = (sgn0 & 2) ? -pad : pad, pz = (sgn0 & 4) ? -pad : pad;
                 const float nx = fadd(ox0, px), ny = fadd(oy0, py), nz = fadd(oz0, pz);
@@ -415,38 +460,11 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
                 f.fax = -fmul(fx, f.ax); f.fay = -fmul(fy, f.ay); f.faz = -fmul(fz, f.az);
                 f.fbx = -fmul(fx, f.bx); f.fby = -fmul(fy, f.by); f.fbz = -fmul(fz, f.bz);
                 f.tMax = tMaxAll; f.sgn = sgn0;
-                if (lane == 0) fat_store(sm.fat, f);
-                // the packet's frame for k_leaf_fat (not bit-critical: any orthonormal frame is valid)
-                const float d7x = __shfl_sync(FULL, d.x, WQ_P - 1), d7y = __shfl_sync(FULL, d.y, WQ_P - 1),
-                            d7z = __shfl_sync(FULL, d.z, WQ_P - 1);
-                float ux = dx0 + d7x, uy = dy0 + d7y, uz = dz0 + d7z;
-                const float ul = rsqrtf(ux * ux + uy * uy + uz * uz);
-                ux *= ul; uy *= ul; uz *= ul;
-                float wx = d7x - dx0, wy = d7y - dy0, wz = d7z - dz0;
-                const float wu = wx * ux + wy * uy + wz * uz;
-                wx -= wu * ux; wy -= wu * uy; wz -= wu * uz;
-                float wl = wx * wx + wy * wy + wz * wz;
-                if (!(wl > 1e-24f)) {        // all directions equal: any perpendicular will do
-                    const float ax = fabsf(ux), ay = fabsf(uy), az = fabsf(uz);
-                    if (ax <= ay && ax <= az) { wx = 0.f; wy = -uz; wz = uy; }
-                    else if (ay <= az) { wx = uz; wy = 0.f; wz = -ux; }
-                    else { wx = -uy; wy = ux; wz = 0.f; }
-                    wl = wx * wx + wy * wy + wz * wz;
-                }
-                const float wi = rsqrtf(wl);
-                const float vx = wx * wi, vy = wy * wi, vz = wz * wi;
-                const float nx2 = uy * vz - uz * vy, ny2 = uz * vx - ux * vz, nz2 = ux * vy - uy * vx;
-                const float da = d.x * ux + d.y * uy + d.z * uz, db = d.x * vx + d.y * vy + d.z * vz,
-                            dc = d.x * nx2 + d.y * ny2 + d.z * nz2;
-                const float m = __fdividef(db, da);
-                const float kap = da * rsqrtf(da * da + db * db);
-                const float aMin = pk_min(da), kMin = pk_min(kap), cMax = pk_max(fabsf(dc));
-                const float mLo = pk_min(m), mHi = pk_max(m);
-                const float tau = fminf(tMaxAll, 4.f * M);
-                if (!(aMin > 0.5f)) fat = false;       // (never with the spread limit; NaN-safe)
-                else if (lane == 0) {
+                if (lane == g0) {
+                    fat_store(sm.fat[lane / FAT_P], f);
+                    const float tau = fminf(tMaxAll, 4.f * M);
                     const float hT = 1.01f * cMax * tau + 4.f * oSpread + M * 0x1p-16f;
-                    float4 *fr = A.frames + (size_t)pk * 4;
+                    float4 *fr = A.frames + ((size_t)pk * (WQ_P / FAT_P) + lane / FAT_P) * 4;
                     fr[0] = make_float4(ox0, oy0, oz0, hT);
                     fr[1] = make_float4(ux, uy, uz, 1.001f * __fdividef(1.f, kMin));
                     fr[2] = make_float4(vx, vy, vz, mLo);
@@ -457,16 +475,16 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
         int nsize = 0;
         bool e0 = false, e1 = false;   // leaf children to emit this step
         int c0 = 0, c1 = 0, slot = (int)lane;
-        if (fat) {              // one walk for the whole packet
-            if (t.root_ref >= 0) { if (lane == 0) sm.nref[0] = t.root_ref; nsize = 1; }
-            else { e0 = lane == 0; c0 = t.root_ref; }
-        } else {
-            const unsigned mlive = __ballot_sync(FULL, live);
+        {
+            // fat walk: one root entry per live group (slot = group); per-ray walk: one per live ray
+            const bool push = fat ? (grpLive && (lane & (FAT_P - 1)) == 0) : live;
+            if (fat) slot = (int)(lane / FAT_P);
+            const unsigned mpush = __ballot_sync(FULL, push);
             if (t.root_ref >= 0) {
-                if (live) { int pos = __popc(mlive & lt); sm.nref[pos] = t.root_ref; sm.nslot[pos] = (unsigned char)lane; }
-                nsize = __popc(mlive);
+                if (push) { int pos = __popc(mpush & lt); sm.nref[pos] = t.root_ref; sm.nslot[pos] = (unsigned char)slot; }
+                nsize = __popc(mpush);
             } else {            // the whole tree is one leaf
-                e0 = live; c0 = t.root_ref;
+                e0 = push; c0 = t.root_ref;
             }
         }
         __syncwarp();
@@ -490,7 +508,7 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
                 const unsigned p0 = chunkPos + __popc(ml0 & lt);
                 const unsigned p1 = chunkPos + __popc(ml0) + __popc(ml1 & lt);
                 chunkPos += nl;
-                const unsigned px = FAT ? (base | PAIR_FAT) : base + slot;
+                const unsigned px = FAT ? ((base + FAT_P * slot) | PAIR_FAT) : base + slot;
                 kinds |= FAT ? KIND_FAT : KIND_THIN;
                 if (e0) {
                     if (p0 < queueCap) queue[p0] = make_uint2(px, (unsigned)c0);
@@ -510,7 +528,7 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
             const int k = room >= 1 ? min(min(32, nsize), room) : 1;
             const bool act = (int)lane < k;
             int ref = 0;
-            if (act) { ref = sm.nref[nsize - 1 - lane]; if (!FAT) slot = sm.nslot[nsize - 1 - lane]; }
+            if (act) { ref = sm.nref[nsize - 1 - lane]; slot = sm.nslot[nsize - 1 - lane]; }
             nsize -= k;
             ++steps;
             bool h0 = false, h1 = false;
@@ -519,7 +537,7 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
                 const float4 a = __ldg(&fn->a), b = __ldg(&fn->b), c = __ldg(&fn->c);
                 const int4 d = __ldg(&fn->d);
                 if (FAT) {
-                    const FatRay f = fat_load(sm.fat);
+                    const FatRay f = fat_load(sm.fat[slot]);
                     h0 = slab_hit_fat(f, a.x, a.y, a.z, a.w, b.x, b.y);
                     h1 = slab_hit_fat(f, b.z, b.w, c.x, c.y, c.z, c.w);
                 } else {
@@ -534,15 +552,15 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
             const bool n0 = h0 && c0 >= 0, n1 = h1 && c1 >= 0;
             e0 = h0 && c0 < 0; e1 = h1 && c1 < 0;
             const unsigned mn0 = __ballot_sync(FULL, n0), mn1 = __ballot_sync(FULL, n1);
-            if (n0) { int p = nsize + __popc(mn0 & lt); sm.nref[p] = c0; if (!FAT) sm.nslot[p] = (unsigned char)slot; }
-            if (n1) { int p = nsize + __popc(mn0) + __popc(mn1 & lt); sm.nref[p] = c1; if (!FAT) sm.nslot[p] = (unsigned char)slot; }
+            if (n0) { int p = nsize + __popc(mn0 & lt); sm.nref[p] = c0; sm.nslot[p] = (unsigned char)slot; }
+            if (n1) { int p = nsize + __popc(mn0) + __popc(mn1 & lt); sm.nref[p] = c1; sm.nslot[p] = (unsigned char)slot; }
             nsize += __popc(mn0) + __popc(mn1);
             __syncwarp();
         }
         };
         if (fat) walk(std::true_type{}); else walk(std::false_type{});
         // ---- remember heavy packets for the next launch
-        if (steps >= HEAVY_STEPS && lane == 0) {
+        if (steps >= (fat ? HEAVY_STEPS_FAT : HEAVY_STEPS) && lane == 0) {
             const unsigned pos = heavyCap ? atomicAdd(nHeavyOut, 1u) : 0u;
             if (pos < heavyCap) {
                 heavyOut[pos] = pk;
@@ -717,7 +735,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, FAT_MINB) k_leaf_fat(LeafArgs A
     FatBuf &fb = fatAll[threadIdx.x >> 5];
     constexpr unsigned G = 32 / LW;
     constexpr int U = FAT_U;
-    constexpr unsigned SLOTS = 32 / WQ_P;              // survivors per stage-2 pass
+    constexpr unsigned SLOTS = 32 / FAT_P;             // survivors per stage-2 pass
     const unsigned FULL = 0xffffffffu;
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt = (1u << lane) - 1u;
@@ -796,7 +814,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, FAT_MINB) k_leaf_fat(LeafArgs A
                 if (on[u]) {
                     p[u] = __ldg(A.t.s_pos_r + first[u] + j);
 #if FAT_PREF
-                    const float4 *fr = A.frames + (size_t)(base[u] / WQ_P) * 4;
+                    const float4 *fr = A.frames + (size_t)(base[u] / FAT_P) * 4;
                     f0[u] = __ldg(fr); f1[u] = __ldg(fr + 1); f2[u] = __ldg(fr + 2); f3[u] = __ldg(fr + 3);
 #endif
                 }
@@ -808,7 +826,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, FAT_MINB) k_leaf_fat(LeafArgs A
 #if FAT_PREF
                     keep = frame_may_hit(f0[u], f1[u], f2[u], f3[u], p[u]);
 #else
-                    const float4 *fr = A.frames + (size_t)(base[u] / WQ_P) * 4;
+                    const float4 *fr = A.frames + (size_t)(base[u] / FAT_P) * 4;
                     keep = frame_may_hit(__ldg(fr), __ldg(fr + 1), __ldg(fr + 2), __ldg(fr + 3), p[u]);
 #endif
                     if (COUNT) ++cTests;
