@@ -350,7 +350,20 @@ __global__ void __launch_bounds__(128) k_trace(MediumDev m, const LightsDev *__r
 // claims the next path index from a global counter (persistent threads), so lanes neither wait for
 // the longest rejection loop of a segment nor for the longest path of the warp.  Deposits still go
 // to the slots of their path index, so the photon store is unchanged.
-enum { TS_NEW = 0, TS_SEG = 1, TS_TRACK = 2, TS_DONE = 3 };
+// The rare, long bodies (NEW: seed + emission, SEG: two ray-box clips, SCAT: deposit + phase sample)
+// are BATCHED: a lane that needs one waits until TS_BATCH lanes of the warp need the same body (or
+// fewer than TS_STARVE lanes are still tracking), so that each of them runs with many lanes instead
+// of 1-5 per iteration; the tracking step runs every iteration with whoever is tracking.  Paths are
+// independent (own PCG stream, own slots), so the schedule does not change any record.
+enum { TS_NEW = 0, TS_SEG = 1, TS_TRACK = 2, TS_DONE = 3, TS_SCAT = 4 };
+// measured (trace phase, ms): no batching 1.71-1.83 | BATCH 4 / 8 / 12 / 16 / 24 -> 1.71 / 1.58 / 1.51 / 1.61 / 1.81
+// | STARVE 4 / 8 / 16 at BATCH 12 -> 1.50 / 1.50 / 1.58
+#ifndef TS_BATCH
+#define TS_BATCH 12
+#endif
+#ifndef TS_STARVE
+#define TS_STARVE 8
+#endif
 
 __global__ void __launch_bounds__(128) k_trace_flat(MediumDev m, const LightsDev *__restrict__ lights,
                                                     float blo0, float blo1, float blo2, float bhi0,
@@ -363,38 +376,62 @@ __global__ void __launch_bounds__(128) k_trace_flat(MediumDev m, const LightsDev
                                                     unsigned int *__restrict__ nextPath) {
     const float blo[3] = {blo0, blo1, blo2}, bhi[3] = {bhi0, bhi1, bhi2};
     const float INF = __int_as_float(0x7f800000);
+    const unsigned FULL = 0xffffffffu;
     Pcg rng;
     rng.state = 0; rng.inc = 1;
     float o[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 1.f}, alpha[3] = {0.f, 0.f, 0.f};
     float om[3] = {0.f, 0.f, 0.f}, dm[3] = {0.f, 0.f, 0.f};
-    float tt = 0.f, tEnd = 0.f;
+    float tt = 0.f, tEnd = 0.f, ts = 0.f;
     uint32_t pid = 0, stored = 0;
     int nInt = 1, state = TS_NEW;
     for (;;) {
-        if (state == TS_NEW) {
+        // one convergence point per iteration: who is where, which bodies run this time
+        const unsigned mNew = __ballot_sync(FULL, state == TS_NEW), mSeg = __ballot_sync(FULL, state == TS_SEG);
+        const unsigned mScat = __ballot_sync(FULL, state == TS_SCAT), mTrack = __ballot_sync(FULL, state == TS_TRACK);
+        if ((mNew | mSeg | mScat | mTrack) == 0u) break;
+        const bool starved = __popc(mTrack) < TS_STARVE;   // too few trackers: run whatever is waiting
+        const bool runScat = mScat && (starved || __popc(mScat) >= TS_BATCH);
+        const bool runNew = mNew && (starved || __popc(mNew) >= TS_BATCH);
+        const bool runSeg = starved || __popc(mSeg) + (runScat ? __popc(mScat) : 0) + (runNew ? __popc(mNew) : 0) >= TS_BATCH;
+        if (runScat && state == TS_SCAT) {
+            const size_t slot = (size_t)pid * maxDepth + stored;
+            float p[3] = {fadd(o[0], fmul(d[0], ts)), fadd(o[1], fmul(d[1], ts)), fadd(o[2], fmul(d[2], ts))};
+            float wo[3] = {-d[0], -d[1], -d[2]}, wi[3];
+            slot_pos[slot] = make_float4(p[0], p[1], p[2], radius);   // Photon(misect.p, alpha, wo)
+            slot_pow[slot] = make_float4(alpha[0], alpha[1], alpha[2], 0.f);
+            slot_dir[slot] = make_float4(wo[0], wo[1], wo[2], 0.f);
+            ++stored;
+            float ua = rng.f(), ub = rng.f();
+            hg_sample(wo, m.g, ua, ub, wi);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { o[k] = p[k]; d[k] = wi[k]; }
+            if (nInt >= maxDepth || rng.f() > 1.f) {           // photonmap.cpp:794; roulette with continueProb == 1, :799-804
+                counts[pid] = stored; state = TS_NEW;          // (claims its next path in a later iteration)
+            } else { ++nInt; state = TS_SEG; }
+        }
+        if (runNew && (mNew >> (threadIdx.x & 31u) & 1u)) {
             pid = atomicAdd(nextPath, 1u);
             if (pid >= nPaths) state = TS_DONE;
             else {
                 rng.seed(first + pid + 1);  // photonbeam.cpp:386-391
                 stored = 0; nInt = 1;
                 if (emit_photon(lights, rng, o, d, alpha)) state = TS_SEG;
-                else counts[pid] = 0;
+                else counts[pid] = 0;       // stays TS_NEW: next batch
             }
         }
-        if (__ballot_sync(0xffffffffu, state != TS_DONE) == 0u) break;
-        bool scatter = false, endPath = false;
-        float ts = 0.f;
-        if (state == TS_SEG) {
+        if (runSeg && state == TS_SEG) {
+            bool endPath = false;
             // scene.Intersect stand-in: distance to the absorbing box wall
             float t0, t1;
             if (!ray_box(o, d, INF, blo, bhi, t0, t1) || t0 > 0.f) endPath = true;
             else if (m.kind == 0) {
                 float w[3];
-                scatter = medium_sample(m, rng, o, d, t1, ts, w);
+                const bool sc = medium_sample(m, rng, o, d, t1, ts, w);
 #pragma unroll
                 for (int c = 0; c < 3; ++c) alpha[c] = fmul(alpha[c], w[c]);
-                if (alpha[0] == 0.f && alpha[1] == 0.f && alpha[2] == 0.f) { scatter = false; endPath = true; }
-                else if (!scatter) endPath = true;   // reached the wall: absorbed
+                if (alpha[0] == 0.f && alpha[1] == 0.f && alpha[2] == 0.f) endPath = true;
+                else if (!sc) endPath = true;   // reached the wall: absorbed
+                else state = TS_SCAT;
             } else {   // grid.cpp:62-75: ray into medium space, clip to the unit cube
 #pragma unroll
                 for (int r = 0; r < 3; ++r) {
@@ -407,39 +444,23 @@ __global__ void __launch_bounds__(128) k_trace_flat(MediumDev m, const LightsDev
                 if (!ray_box(om, dm, t1, lo, hi, tMin, tEnd)) endPath = true;
                 else { tt = tMin; state = TS_TRACK; }
             }
+            if (endPath) { counts[pid] = stored; state = TS_NEW; }
         }
         if (state == TS_TRACK) {   // one delta-tracking step, grid.cpp:76-86
             const float st = m.sigma_t[0];
             tt = fsub(tt, fdiv(fmul(logf(fsub(1.f, rng.f())), m.invMaxDensity), st));
-            if (tt >= tEnd) endPath = true;
+            if (tt >= tEnd) { counts[pid] = stored; state = TS_NEW; }
             else {
                 float dens = grid_density_t(m, fadd(om[0], fmul(dm[0], tt)), fadd(om[1], fmul(dm[1], tt)),
                                             fadd(om[2], fmul(dm[2], tt)));
                 if (fmul(dens, m.invMaxDensity) > rng.f()) {
 #pragma unroll
                     for (int c = 0; c < 3; ++c) alpha[c] = fmul(alpha[c], fdiv(m.sigma_s[c], st));
-                    if (alpha[0] == 0.f && alpha[1] == 0.f && alpha[2] == 0.f) endPath = true;
-                    else { scatter = true; ts = tt; }
+                    if (alpha[0] == 0.f && alpha[1] == 0.f && alpha[2] == 0.f) { counts[pid] = stored; state = TS_NEW; }
+                    else { ts = tt; state = TS_SCAT; }
                 }
             }
         }
-        if (scatter) {
-            const size_t slot = (size_t)pid * maxDepth + stored;
-            float p[3] = {fadd(o[0], fmul(d[0], ts)), fadd(o[1], fmul(d[1], ts)), fadd(o[2], fmul(d[2], ts))};
-            float wo[3] = {-d[0], -d[1], -d[2]}, wi[3];
-            slot_pos[slot] = make_float4(p[0], p[1], p[2], radius);   // Photon(misect.p, alpha, wo)
-            slot_pow[slot] = make_float4(alpha[0], alpha[1], alpha[2], 0.f);
-            slot_dir[slot] = make_float4(wo[0], wo[1], wo[2], 0.f);
-            ++stored;
-            float ua = rng.f(), ub = rng.f();
-            hg_sample(wo, m.g, ua, ub, wi);
-#pragma unroll
-            for (int k = 0; k < 3; ++k) { o[k] = p[k]; d[k] = wi[k]; }
-            if (nInt >= maxDepth) endPath = true;          // photonmap.cpp:794
-            else if (rng.f() > 1.f) endPath = true;        // roulette with continueProb == 1, :799-804
-            else { ++nInt; state = TS_SEG; }
-        }
-        if (endPath) { counts[pid] = stored; state = TS_NEW; }
     }
 }
 
