@@ -372,51 +372,81 @@ __device__ __forceinline__ int delta64(const uint32_t *__restrict__ codes,
 
 // node_lo[i].w / node_hi[i].w hold the left / right child refs (>=0 internal, <0 = ~leaf).
 // parent[0..n-2] internal parents, parent[n-1+s] leaf parents.  node_range[i] = {first,last}.
+// Work lists for the hot-path refit (k_refit_direct / k_refit_climb), appended block by block:
+//   dlist: kept nodes of <= directMax photons -- fat-leaf roots (<= maxLeaf photons under a larger
+//          node) and small internal nodes; their box comes straight from the photons
+//   clist: where the atomic climb starts -- children (node, or n-1+s for a single photon s) of
+//          <= directMax photons under a larger node
+// lists[0] = |dlist|, lists[1] = |clist|, dlist at lists+16, clist at lists+16+n.
 __global__ void __launch_bounds__(256) k_karras(const uint32_t *__restrict__ codes,
                                                 const uint32_t *__restrict__ order, int n,
                                                 float4 *__restrict__ node_lo,
                                                 float4 *__restrict__ node_hi,
                                                 int2 *__restrict__ node_range,
                                                 int *__restrict__ parent, int maxLeaf, int directMax,
-                                                unsigned char *__restrict__ entry) {
+                                                int *__restrict__ lists) {
+    __shared__ int wsum[2][8];
+    __shared__ int bbase[2];
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n - 1) return;
-    uint64_t ki = ((uint64_t)__ldg(codes + i) << 32) | __ldg(order + i);
-    int d = delta64(codes, order, ki, i + 1, n) - delta64(codes, order, ki, i - 1, n) > 0 ? 1 : -1;
-    int dmin = delta64(codes, order, ki, i - d, n);
-    int lmax = 2;
-    while (delta64(codes, order, ki, i + lmax * d, n) > dmin) lmax <<= 1;
-    int l = 0;
-    for (int t = lmax >> 1; t >= 1; t >>= 1)
-        if (delta64(codes, order, ki, i + (l + t) * d, n) > dmin) l += t;
-    int j = i + l * d;
-    int dnode = delta64(codes, order, ki, j, n);
-    int s = 0, t = l;
-    do {
-        t = (t + 1) >> 1;
-        if (delta64(codes, order, ki, i + (s + t) * d, n) > dnode) s += t;
-    } while (t > 1);
-    int gamma = i + s * d + min(d, 0);
-    int first = min(i, j), last = max(i, j);
-    int left = (first == gamma) ? ~gamma : gamma;
-    int right = (last == gamma + 1) ? ~(gamma + 1) : gamma + 1;
-    node_lo[i].w = __int_as_float(left);
-    node_hi[i].w = __int_as_float(right);
-    node_range[i] = make_int2(first, last);
-    if (left >= 0) parent[left] = i; else parent[n - 1 + gamma] = i;
-    if (right >= 0) parent[right] = i; else parent[n - 1 + gamma + 1] = i;
-    if (i == 0) parent[0] = -1;
-    // entry points of the production tree: children of <= maxLeaf photons under a larger node
-    // (a fat-leaf root, or a single photon).  k_refit_fast starts from exactly these.
-    // bit 1: where the atomic climb starts -- children of <= refit_direct photons under a larger node
-    // (everything at or below that size gets its box straight from the photons, no atomics).
-    const int cnt = last - first + 1, cl = gamma - first + 1, cr = last - gamma;
-    const bool big = cnt > maxLeaf, huge = cnt > directMax;
-    entry[left >= 0 ? left : n - 1 + gamma] =
-        (unsigned char)((big && cl <= maxLeaf ? 1 : 0) | (huge && cl <= directMax ? 2 : 0));
-    entry[right >= 0 ? right : n - 1 + gamma + 1] =
-        (unsigned char)((big && cr <= maxLeaf ? 1 : 0) | (huge && cr <= directMax ? 2 : 0));
-    if (i == 0) entry[0] = (unsigned char)((big ? 0 : 1) | 0);
+    int dItem[3] = {-1, -1, -1}, cItem[2] = {-1, -1};
+    if (i < n - 1) {
+        uint64_t ki = ((uint64_t)__ldg(codes + i) << 32) | __ldg(order + i);
+        int d = delta64(codes, order, ki, i + 1, n) - delta64(codes, order, ki, i - 1, n) > 0 ? 1 : -1;
+        int dmin = delta64(codes, order, ki, i - d, n);
+        int lmax = 2;
+        while (delta64(codes, order, ki, i + lmax * d, n) > dmin) lmax <<= 1;
+        int l = 0;
+        for (int t = lmax >> 1; t >= 1; t >>= 1)
+            if (delta64(codes, order, ki, i + (l + t) * d, n) > dmin) l += t;
+        int j = i + l * d;
+        int dnode = delta64(codes, order, ki, j, n);
+        int s = 0, t = l;
+        do {
+            t = (t + 1) >> 1;
+            if (delta64(codes, order, ki, i + (s + t) * d, n) > dnode) s += t;
+        } while (t > 1);
+        int gamma = i + s * d + min(d, 0);
+        int first = min(i, j), last = max(i, j);
+        int left = (first == gamma) ? ~gamma : gamma;
+        int right = (last == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+        node_lo[i].w = __int_as_float(left);
+        node_hi[i].w = __int_as_float(right);
+        node_range[i] = make_int2(first, last);
+        if (left >= 0) parent[left] = i; else parent[n - 1 + gamma] = i;
+        if (right >= 0) parent[right] = i; else parent[n - 1 + gamma + 1] = i;
+        if (i == 0) parent[0] = -1;
+        const int cnt = last - first + 1, cl = gamma - first + 1, cr = last - gamma;
+        const bool big = cnt > maxLeaf, huge = cnt > directMax;
+        if (big && left >= 0 && cl <= directMax) dItem[0] = left;
+        if (big && right >= 0 && cr <= directMax) dItem[1] = right;
+        if (i == 0 && !huge) dItem[2] = 0;   // the whole tree is small: root box direct
+        if (huge && cl <= directMax) cItem[0] = left >= 0 ? left : n - 1 + gamma;
+        if (huge && cr <= directMax) cItem[1] = right >= 0 ? right : n - 1 + gamma + 1;
+    }
+    // block-aggregated append: one atomicAdd per list per block
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    int nd = (dItem[0] >= 0) + (dItem[1] >= 0) + (dItem[2] >= 0), nc = (cItem[0] >= 0) + (cItem[1] >= 0);
+    int pd = nd, pc = nc;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int a = __shfl_up_sync(0xffffffffu, pd, o), c = __shfl_up_sync(0xffffffffu, pc, o);
+        if ((int)lane >= o) { pd += a; pc += c; }
+    }
+    if (lane == 31) { wsum[0][warp] = pd; wsum[1][warp] = pc; }
+    __syncthreads();
+    if (threadIdx.x < 2) {
+        int tot = 0;
+        for (int w = 0; w < 8; ++w) { int v = wsum[threadIdx.x][w]; wsum[threadIdx.x][w] = tot; tot += v; }
+        bbase[threadIdx.x] = tot ? atomicAdd(lists + threadIdx.x, tot) : 0;
+    }
+    __syncthreads();
+    int od = bbase[0] + wsum[0][warp] + pd - nd, oc = bbase[1] + wsum[1][warp] + pc - nc;
+    int *dlist = lists + 16, *clist = lists + 16 + n;
+    if (dItem[0] >= 0) dlist[od++] = dItem[0];
+    if (dItem[1] >= 0) dlist[od++] = dItem[1];
+    if (dItem[2] >= 0) dlist[od] = dItem[2];
+    if (cItem[0] >= 0) clist[oc++] = cItem[0];
+    if (cItem[1] >= 0) clist[oc] = cItem[1];
 }
 
 __global__ void __launch_bounds__(256) k_refit(int n, float4 *node_lo, float4 *node_hi,
@@ -448,45 +478,45 @@ __global__ void __launch_bounds__(256) k_refit(int n, float4 *node_lo, float4 *n
 
 // Hot-path refit: only the nodes the production tree keeps.  A "fat leaf" is a subtree of
 // <= maxLeaf photons whose parent is larger; its box is the union of its photons' boxes, computed
-// straight from the Morton-ordered records (contiguous, <= 128 bytes).  Threads [0, n-1) are
-// internal nodes -- fat-leaf roots write their box and start a climb; threads [n-1, 2n-1) are
-// single photons hanging directly off a large node -- they only start a climb.  Which threads
-// are such entry points was tagged by k_karras (entry[], one byte each).  Climbing is the
-// usual second-arrival-continues scheme.  Nodes inside fat leaves are never touched (7/8 of the
+// straight from the Morton-ordered records (contiguous, <= 128 bytes), and so is the box of every
+// kept node of <= directMax photons (k_refit_direct, one thread per entry of the list k_karras
+// appended: full warps instead of one busy lane in six).  k_refit_climb then starts from the
+// children of <= directMax photons under larger nodes with the usual second-arrival-continues
+// scheme.  Nodes inside fat leaves are never touched (7/8 of the
 // tree at maxLeaf 8).  min/max are exact, so every box equals the canonical bottom-up union.
-__global__ void __launch_bounds__(256) k_refit_fast(int n, int maxLeaf, int directMax, float4 *node_lo, float4 *node_hi,
-                                                    const int2 *__restrict__ node_range,
-                                                    const int *__restrict__ parent,
-                                                    const float4 *__restrict__ s_pos_r,
-                                                    const unsigned char *__restrict__ entry,
-                                                    uint32_t *__restrict__ flags) {
-    int tid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tid >= 2 * n - 1) return;
-    const unsigned tag = __ldg(entry + tid);
-    if (tid < n - 1) {
-        // every kept node of <= refit_direct photons: union of its photons' boxes (contiguous
-        // Morton range, shared with its neighbours through L1/L2) -- no dependency, no atomics
-        const int2 rg = __ldg(node_range + tid);
-        const int cnt = rg.y - rg.x + 1;
-        const bool kept = cnt > maxLeaf || (tag & 1u);
-        if (cnt <= directMax && kept) {
-            float4 lo, hi;
-            leaf_box(__ldg(s_pos_r + rg.x), lo, hi);
-            for (int q = rg.x + 1; q <= rg.y; ++q) {
-                float4 l, h;
-                leaf_box(__ldg(s_pos_r + q), l, h);
-                lo.x = fminf(lo.x, l.x); lo.y = fminf(lo.y, l.y); lo.z = fminf(lo.z, l.z);
-                hi.x = fmaxf(hi.x, h.x); hi.y = fmaxf(hi.y, h.y); hi.z = fmaxf(hi.z, h.z);
-            }
-            lo.w = __ldcg(&node_lo[tid].w); hi.w = __ldcg(&node_hi[tid].w);
-            __stcg(node_lo + tid, lo);
-            __stcg(node_hi + tid, hi);
-        }
+__global__ void __launch_bounds__(256) k_refit_direct(const int *__restrict__ lists, float4 *node_lo, float4 *node_hi,
+                                                      const int2 *__restrict__ node_range,
+                                                      const float4 *__restrict__ s_pos_r) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= __ldg(lists)) return;
+    const int id = __ldg(lists + 16 + k);
+    // union of the node's photons' boxes (contiguous Morton range, shared with its neighbours
+    // through L1/L2) -- no dependency, no atomics
+    const int2 rg = __ldg(node_range + id);
+    float4 lo, hi;
+    leaf_box(__ldg(s_pos_r + rg.x), lo, hi);
+    for (int q = rg.x + 1; q <= rg.y; ++q) {
+        float4 l, h;
+        leaf_box(__ldg(s_pos_r + q), l, h);
+        lo.x = fminf(lo.x, l.x); lo.y = fminf(lo.y, l.y); lo.z = fminf(lo.z, l.z);
+        hi.x = fmaxf(hi.x, h.x); hi.y = fmaxf(hi.y, h.y); hi.z = fmaxf(hi.z, h.z);
     }
-    if (!(tag & 2u)) return;
-    int cur = __ldg(parent + tid);
+    lo.w = __ldcg(&node_lo[id].w); hi.w = __ldcg(&node_hi[id].w);
+    __stcg(node_lo + id, lo);
+    __stcg(node_hi + id, hi);
+}
+
+// second-arrival climb above the direct nodes (their boxes are complete: previous launch)
+__global__ void __launch_bounds__(256) k_refit_climb(int n, const int *__restrict__ lists, float4 *node_lo, float4 *node_hi,
+                                                     const int *__restrict__ parent,
+                                                     const float4 *__restrict__ s_pos_r,
+                                                     uint32_t *__restrict__ flags) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= __ldg(lists + 1)) return;
+    int cur = __ldg(parent + __ldg(lists + 16 + n + k));
+    bool fence = false;     // nothing of mine to publish before the first arrival
     while (cur >= 0) {
-        __threadfence();   // my stores (or my child's) are visible before the arrival is counted
+        if (fence) __threadfence();   // my stores are visible before the arrival is counted
         if (atomicAdd(flags + cur, 1u) == 0u) return;  // first arrival: sibling not done yet
         float4 nlo = __ldcg(node_lo + cur), nhi = __ldcg(node_hi + cur);
         const int left = __float_as_int(nlo.w), right = __float_as_int(nhi.w);
@@ -499,6 +529,7 @@ __global__ void __launch_bounds__(256) k_refit_fast(int n, int maxLeaf, int dire
         nhi.x = fmaxf(lhi.x, rhi.x); nhi.y = fmaxf(lhi.y, rhi.y); nhi.z = fmaxf(lhi.z, rhi.z);
         __stcg(node_lo + cur, nlo);
         __stcg(node_hi + cur, nhi);
+        fence = true;
         cur = __ldg(parent + cur);
     }
 }
@@ -544,10 +575,14 @@ static int launch_refit_emit(bre_ctx *ctx) {
     const uint32_t n = ctx->n_built;
     cudaStream_t st = ctx->stream;
     BRE_CUDA(cudaMemsetAsync(ctx->flags.p, 0, (size_t)n * 4, st));
-    k_refit_fast<<<(int)((2 * (size_t)n - 1 + 255) / 256), 256, 0, st>>>(
-        (int)n, ctx->max_leaf, ctx->refit_direct, (float4 *)ctx->node_lo.p, (float4 *)ctx->node_hi.p,
-        (const int2 *)ctx->node_range.p, (const int *)ctx->parent.p, (const float4 *)ctx->s_pos_r.p,
-        (const unsigned char *)ctx->entry.p, (uint32_t *)ctx->flags.p);
+    // list lengths live on the device: both kernels are launched for the worst case (n items) and
+    // the surplus blocks return at once
+    const int gl = (int)((n + 255) / 256);
+    k_refit_direct<<<gl, 256, 0, st>>>((const int *)ctx->entry.p, (float4 *)ctx->node_lo.p, (float4 *)ctx->node_hi.p,
+                                       (const int2 *)ctx->node_range.p, (const float4 *)ctx->s_pos_r.p);
+    k_refit_climb<<<gl, 256, 0, st>>>((int)n, (const int *)ctx->entry.p, (float4 *)ctx->node_lo.p,
+                                      (float4 *)ctx->node_hi.p, (const int *)ctx->parent.p,
+                                      (const float4 *)ctx->s_pos_r.p, (uint32_t *)ctx->flags.p);
     k_emit_fast<<<(int)((n + 255) / 256), 256, 0, st>>>(
         (int)n, ctx->max_leaf, (const float4 *)ctx->node_lo.p, (const float4 *)ctx->node_hi.p,
         (const int2 *)ctx->node_range.p, (const float4 *)ctx->s_pos_r.p, (FastNode *)ctx->fast.p);
@@ -624,7 +659,7 @@ int build_tree(bre_ctx *ctx) {
     ENS(keys_alt, (size_t)n * 4); ENS(vals_alt, (size_t)n * 4);
     ENS(node_lo, n4); ENS(node_hi, n4);
     ENS(node_range, (size_t)n * 8); ENS(parent, (size_t)2 * n * 4);
-    ENS(entry, (size_t)2 * n); ENS(flags, (size_t)n * 4); ENS(fast, (size_t)n * sizeof(FastNode));
+    ENS(entry, (size_t)8 * n + 64); ENS(flags, (size_t)n * 4); ENS(fast, (size_t)n * sizeof(FastNode));
     ENS(scratch, 64);
     const uint32_t numBlocks = (n + RS_TILE - 1) / RS_TILE;
     const uint32_t histLen = 256u * numBlocks;
@@ -661,9 +696,10 @@ int build_tree(bre_ctx *ctx) {
                                    order, n, (float4 *)ctx->s_pos_r.p, (float4 *)ctx->s_pow.p,
                                    (float4 *)ctx->s_dir.p, bnd);
     if (n > 1) {
+        BRE_CUDA(cudaMemsetAsync(ctx->entry.p, 0, 64, st));
         k_karras<<<g256, 256, 0, st>>>(codes, order, (int)n, (float4 *)ctx->node_lo.p,
                                        (float4 *)ctx->node_hi.p, (int2 *)ctx->node_range.p,
-                                       (int *)ctx->parent.p, ctx->max_leaf, ctx->refit_direct, (unsigned char *)ctx->entry.p);
+                                       (int *)ctx->parent.p, ctx->max_leaf, ctx->refit_direct, (int *)ctx->entry.p);
         if ((s = launch_refit_emit(ctx)) != BRE_OK) { delete pt; return s; }
     }
     delete pt;
