@@ -38,6 +38,9 @@ namespace bre {
 #ifndef BRE_WQ_P
 #define BRE_WQ_P 8
 #endif
+#ifndef BRE_RED_V4
+#define BRE_RED_V4 0      // 1: shade_hit adds a hit with one vector atomic (RED.128) instead of three scalar ones
+#endif
 #ifndef BRE_WQ_NCAP
 #define BRE_WQ_NCAP 512
 #endif
@@ -274,10 +277,14 @@ __device__ __forceinline__ float3 hit_radiance(const LeafArgs &A, uint32_t s, ui
 }
 __device__ __forceinline__ void shade_hit(const LeafArgs &A, uint32_t s, uint32_t q, float th, float d2) {
     const float3 v = hit_radiance(A, s, q, th, d2);
+#if BRE_RED_V4
+    atomicAdd(A.out + q, make_float4(v.x, v.y, v.z, 0.f));   // one RED.128 instead of three REDs
+#else
     float *dst = reinterpret_cast<float *>(A.out + q);
     atomicAdd(dst + 0, v.x);
     atomicAdd(dst + 1, v.y);
     atomicAdd(dst + 2, v.z);
+#endif
 }
 // Whole-warp version: lanes < cnt hold one hit each.  Maximal runs of consecutive lanes with the
 // same ray index are summed with a segmented shuffle reduction; the first lane of each run issues
@@ -724,6 +731,10 @@ struct __align__(16) FatBuf {
 #ifndef FAT_PREF
 #define FAT_PREF 0
 #endif
+#ifndef FAT_RAYCACHE
+#define FAT_RAYCACHE 0
+#endif
+
 template <int MODE, bool COUNT, int LW>
 __global__ void __launch_bounds__(LP_WARPS * 32, FAT_MINB) k_leaf_fat(LeafArgs A, const uint2 *__restrict__ queue,
                                                             unsigned int queueCap,
@@ -748,6 +759,10 @@ __global__ void __launch_bounds__(LP_WARPS * 32, FAT_MINB) k_leaf_fat(LeafArgs A
     unsigned long long cTests = 0;
     unsigned nbuf = 0, npb = 0;
 
+#if FAT_RAYCACHE
+    unsigned curBase = 0xffffffffu;
+    float4 co = make_float4(0.f, 0.f, 0.f, 0.f), cd = co;
+#endif
     // stage 2 over the newest `take` survivors (take <= SLOTS)
     auto exact_pass = [&](unsigned take) {
         bool hit = false;
@@ -757,8 +772,16 @@ __global__ void __launch_bounds__(LP_WARPS * 32, FAT_MINB) k_leaf_fat(LeafArgs A
             const unsigned e = npb - take + slot;
             const float4 p = fb.p[e];
             s = fb.s[e];
+#if FAT_RAYCACHE
+            // this lane always tests ray `ray` of a packet: keep it in registers while the packet lasts
+            const unsigned b = fb.base[e];
+            if (b != curBase) { curBase = b; co = __ldg(A.ro + b + ray); cd = __ldg(A.rd + b + ray); }
+            q = b + ray;
+            const float4 o = co, d = cd;
+#else
             q = fb.base[e] + ray;
             const float4 o = __ldg(A.ro + q), d = __ldg(A.rd + q);
+#endif
             RayS r;
             r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tMax = o.w;
             r.dx = d.x; r.dy = d.y; r.dz = d.z;

@@ -127,6 +127,39 @@ __device__ float grid_density_t(const MediumDev &m, float px, float py, float pz
     return lerpf(dz, lerpf(dy, d00, d10), lerpf(dy, d01, d11));
 }
 
+// Tracking step of k_trace_flat (TS_FAST, default): the same trilinear interpolant with fused
+// lerps a + t (b - a) and fused coordinate arithmetic.  K1 is compared with the reference
+// statistically and path by path within a tolerance (its logf / sincosf already differ from the
+// host's), so only the rounding of the density changes (~1e-7 relative); the hit DECISIONS of the
+// query are not involved.  k_trace<MESH> keeps the reference-order form.
+#ifndef TS_FAST
+#define TS_FAST 1
+#endif
+__device__ __forceinline__ float lerp_fused(float t, float a, float b) { return __fmaf_rn(t, b - a, a); }
+__device__ __forceinline__ float grid_density_fused(const MediumDev &m, float px, float py, float pz) {
+    const float sx = __fmaf_rn(px, (float)m.nx, -.5f), sy = __fmaf_rn(py, (float)m.ny, -.5f),
+                sz = __fmaf_rn(pz, (float)m.nz, -.5f);
+    const float fx = floorf(sx), fy = floorf(sy), fz = floorf(sz);
+    const int ix = (int)fx, iy = (int)fy, iz = (int)fz;
+    const float dx = sx - fx, dy = sy - fy, dz = sz - fz;
+    float v000, v100, v010, v110, v001, v101, v011, v111;
+    if ((unsigned)ix < (unsigned)(m.nx - 1) && (unsigned)iy < (unsigned)(m.ny - 1) &&
+        (unsigned)iz < (unsigned)(m.nz - 1)) {
+        const float *b = m.density + ((size_t)iz * m.ny + iy) * m.nx + ix;
+        const size_t ys = (size_t)m.nx, zs = (size_t)m.nx * m.ny;
+        v000 = __ldg(b); v100 = __ldg(b + 1); v010 = __ldg(b + ys); v110 = __ldg(b + ys + 1);
+        v001 = __ldg(b + zs); v101 = __ldg(b + zs + 1); v011 = __ldg(b + zs + ys); v111 = __ldg(b + zs + ys + 1);
+    } else {
+        v000 = gridD(m, ix, iy, iz); v100 = gridD(m, ix + 1, iy, iz);
+        v010 = gridD(m, ix, iy + 1, iz); v110 = gridD(m, ix + 1, iy + 1, iz);
+        v001 = gridD(m, ix, iy, iz + 1); v101 = gridD(m, ix + 1, iy, iz + 1);
+        v011 = gridD(m, ix, iy + 1, iz + 1); v111 = gridD(m, ix + 1, iy + 1, iz + 1);
+    }
+    const float d00 = lerp_fused(dx, v000, v100), d10 = lerp_fused(dx, v010, v110);
+    const float d01 = lerp_fused(dx, v001, v101), d11 = lerp_fused(dx, v011, v111);
+    return lerp_fused(dz, lerp_fused(dy, d00, d10), lerp_fused(dy, d01, d11));
+}
+
 // Medium::Sample for a unit-direction ray segment [0,tMax).  Returns true when a scattering
 // event was sampled at t; w multiplies the path weight.
 __device__ bool medium_sample(const MediumDev &m, Pcg &rng, const float o[3], const float d[3],
@@ -384,6 +417,7 @@ __global__ void __launch_bounds__(128) k_trace_flat(MediumDev m, const LightsDev
     float tt = 0.f, tEnd = 0.f, ts = 0.f;
     uint32_t pid = 0, stored = 0;
     int nInt = 1, state = TS_NEW;
+    const float stepScale = fdiv(m.invMaxDensity, m.sigma_t[0]);   // free-flight scale of a tracking step (TS_FAST)
     for (;;) {
         // one convergence point per iteration: who is where, which bodies run this time
         const unsigned mNew = __ballot_sync(FULL, state == TS_NEW), mSeg = __ballot_sync(FULL, state == TS_SEG);
@@ -448,11 +482,20 @@ __global__ void __launch_bounds__(128) k_trace_flat(MediumDev m, const LightsDev
         }
         if (state == TS_TRACK) {   // one delta-tracking step, grid.cpp:76-86
             const float st = m.sigma_t[0];
+#if TS_FAST
+            tt = __fmaf_rn(-__logf(fsub(1.f, rng.f())), stepScale, tt);
+#else
             tt = fsub(tt, fdiv(fmul(logf(fsub(1.f, rng.f())), m.invMaxDensity), st));
+#endif
             if (tt >= tEnd) { counts[pid] = stored; state = TS_NEW; }
             else {
+#if TS_FAST
+                float dens = grid_density_fused(m, __fmaf_rn(dm[0], tt, om[0]), __fmaf_rn(dm[1], tt, om[1]),
+                                                __fmaf_rn(dm[2], tt, om[2]));
+#else
                 float dens = grid_density_t(m, fadd(om[0], fmul(dm[0], tt)), fadd(om[1], fmul(dm[1], tt)),
                                             fadd(om[2], fmul(dm[2], tt)));
+#endif
                 if (fmul(dens, m.invMaxDensity) > rng.f()) {
 #pragma unroll
                     for (int c = 0; c < 3; ++c) alpha[c] = fmul(alpha[c], fdiv(m.sigma_s[c], st));
