@@ -40,6 +40,10 @@ WORKLOADS = {
     # name: (target photons, width, height, expected hits/ray knob h, grid n)
     "smoke10m_1080p": dict(photons=10_000_000, w=1920, h=1080, hits=64, grid=64),
     "smoke1m_540p": dict(photons=1_000_000, w=960, h=540, hits=64, grid=32),
+    # BASELINE configs[1]: spotlight through homogeneous fog, 1 M photons, 1080p, fixed radius
+    "fog1m_1080p": dict(photons=1_000_000, w=1920, h=1080, hits=64, grid=0),
+    # BASELINE configs[3]: 4K camera against 50 M photons (all-gathered over NVLink for N > 1)
+    "smoke50m_4k": dict(photons=50_000_000, w=3840, h=2160, hits=64, grid=256),
     "smoke100k_128": dict(photons=100_000, w=128, h=72, hits=32, grid=16),
 }
 SIGMA_A, SIGMA_S, G = [0.4] * 3, [3.6] * 3, 0.3   # sigma_t = 4 (SURVEY 8d S-smoke)
@@ -136,12 +140,27 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def setup_scene(ctx, wl):
+def scene_lights(wl):
+    spot = dict(kind=1, pos=(0.5, 0.98, 0.5), I=(30, 30, 30), axis=(0, -1, 0),
+                cos_total_width=math.cos(math.radians(35)), cos_falloff_start=math.cos(math.radians(25)))
+    if not wl["grid"]:
+        return [spot]                       # homogeneous fog: the spotlight alone (configs[1])
+    return [dict(kind=0, pos=(0.5, 0.5, 0.5), I=(8, 8, 8)), spot]
+
+
+def set_medium(obj, wl):
+    """Same call on the library context and on the oracle; returns the density grid (None = homogeneous)."""
+    if not wl["grid"]:
+        obj.set_medium_homogeneous(SIGMA_A, SIGMA_S, G)
+        return None
     dens = smoke_density(wl["grid"])
-    ctx.set_medium_grid(SIGMA_A, SIGMA_S, G, dens, world_to_medium())
-    ctx.set_lights([dict(kind=0, pos=(0.5, 0.5, 0.5), I=(8, 8, 8)),
-                    dict(kind=1, pos=(0.5, 0.98, 0.5), I=(30, 30, 30), axis=(0, -1, 0),
-                         cos_total_width=math.cos(math.radians(35)), cos_falloff_start=math.cos(math.radians(25)))])
+    obj.set_medium_grid(SIGMA_A, SIGMA_S, G, dens, world_to_medium())
+    return dens
+
+
+def setup_scene(ctx, wl):
+    dens = set_medium(ctx, wl)
+    ctx.set_lights(scene_lights(wl))
     ctx.set_bounds(BOX_LO, BOX_HI)
     return dens
 
@@ -319,7 +338,7 @@ def run_ours(args):
                    "leaf_pairs_per_ray": cnt["leaf_pairs"] / nq, "pair_queue_overflow": cnt["pair_queue_overflow"]},
         "e2e": {"value": e2e_value, "unit": "queries/s", "h2d_bytes_per_step": int(nq * 28),
                 "d2h_bytes_per_step": int(nq * 12), "ms_per_step": ms_e2e / args.steps},
-        "gpu_launches": launches_per_step(world) * args.steps,
+        "gpu_launches": launches_per_step(world, wl) * args.steps,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "kernel": "K5 = k_traverse<0,false> + k_leaf_fat<0,false,8> (+ k_leaf_pairs<0,false,8> for incoherent packets)",
                      "kernel_ms": k5_ms, "algorithmic_bytes": int(cnt["bytes_algorithmic"]),
@@ -339,16 +358,18 @@ def ctx_leaf(args):
     return args.leaf if args.leaf > 0 else 8
 
 
-def launches_per_step(world):
+def launches_per_step(world, wl=None):
     """Kernels of libbre.so launched per step (profiles/r01_launches_*.csv lists them):
-    trace: k_trace, k_scan_reduce, k_scan_tiles, k_scan_apply, k_compact (one chunk of <= 4M paths)   5
+    trace: k_trace_flat, k_scan_reduce, k_scan_tiles, k_scan_apply, k_compact (per chunk of <= 4M paths) 5
     build: k_bounds_init, k_bounds, k_morton, 4 x (k_rs_hist, 3 scan launches, k_rs_scatter),
-           k_gather, k_karras, k_refit, k_emit_fast                                                   27
-    query: k_tau_table, k_store_args, k_traverse, k_leaf_fat, k_leaf_pairs (returns at once when
-           every packet was coherent)                                                                 5
+           k_gather, k_karras, k_refit_direct, k_refit_climb, k_emit_fast                             28
+    query: k_tau_table (grid media), k_store_batch_args, then per ray batch k_traverse, k_leaf_fat,
+           k_leaf_pairs (returns at once when every packet was coherent)                              5
     film:  k_film_add                                                                                 1
-    (NCCL's own kernels at N > 1 are not counted.)"""
-    return 5 + 27 + 5 + 1
+    Counted for one trace chunk and one ray batch (the 10 M-photon 1080p step); larger workloads launch
+    more (one set per chunk / batch), so this is a lower bound there.  NCCL's own kernels are not counted."""
+    tau = 1 if (wl is None or wl.get("grid")) else 0
+    return 5 + 28 + 4 + tau + 1
 
 
 def cpu_baseline_port(ctx, wl, ro_h, rd_h, n_paths, seconds):
@@ -357,11 +378,11 @@ def cpu_baseline_port(ctx, wl, ro_h, rd_h, n_paths, seconds):
     orc = ge.load_orc()
     o = orc.Oracle()
     pos, pw, dr, rad = ctx.download_photons()
-    return _cpu_run(o, pos, pw, dr, rad, ro_h, rd_h, n_paths, seconds, smoke_density(wl["grid"]))
+    return _cpu_run(o, pos, pw, dr, rad, ro_h, rd_h, n_paths, seconds, wl)
 
 
-def _cpu_run(o, pos, pw, dr, rad, ro_h, rd_h, n_paths, seconds, dens):
-    o.set_medium_grid(SIGMA_A, SIGMA_S, G, dens, world_to_medium())
+def _cpu_run(o, pos, pw, dr, rad, ro_h, rd_h, n_paths, seconds, wl):
+    set_medium(o, wl)
     o.set_photons(pos, pw, dr, rad)
     t0 = time.perf_counter()
     o.build()
@@ -393,11 +414,8 @@ def run_reference(args):
     orc = ge.load_orc()
     wl = WORKLOADS[args.workload]
     o = orc.Oracle()
-    dens = smoke_density(wl["grid"])
-    o.set_medium_grid(SIGMA_A, SIGMA_S, G, dens, world_to_medium())
-    lights = [dict(kind=0, pos=(0.5, 0.5, 0.5), I=(8, 8, 8)),
-              dict(kind=1, pos=(0.5, 0.98, 0.5), I=(30, 30, 30), axis=(0, -1, 0),
-                   cos_total_width=math.cos(math.radians(35)), cos_falloff_start=math.cos(math.radians(25)))]
+    set_medium(o, wl)
+    lights = scene_lights(wl)
     vol = float(np.prod(BOX_HI - BOX_LO))
     radius = math.sqrt(wl["hits"] * vol / (math.pi * wl["photons"]))
     # photon pass on the CPU (single thread, like the reference's NumTasks=1 photon pass)
