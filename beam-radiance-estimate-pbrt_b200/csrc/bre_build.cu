@@ -534,6 +534,71 @@ __global__ void __launch_bounds__(256) k_refit_climb(int n, const int *__restric
     }
 }
 
+#if BRE_WIDE
+// One slot of a wide node: child c of a kept node is a single photon (c < 0), a fat-leaf root
+// (<= maxLeaf photons) or a kept internal node.
+__device__ __forceinline__ int emit_slot(int c, int maxLeaf, const float4 *__restrict__ node_lo,
+                                         const float4 *__restrict__ node_hi, const int2 *__restrict__ node_range,
+                                         const float4 *__restrict__ s_pos_r, float4 &lo, float4 &hi) {
+    if (c < 0) {
+        leaf_box(__ldg(s_pos_r + ~c), lo, hi);
+        return leaf_ref((uint32_t)~c, 1u);
+    }
+    lo = __ldg(node_lo + c);
+    hi = __ldg(node_hi + c);
+    const int2 cr = __ldg(node_range + c);
+    const int cnt = cr.y - cr.x + 1;
+    return cnt <= maxLeaf ? leaf_ref((uint32_t)cr.x, (uint32_t)cnt) : c;
+}
+// Every kept internal node gets a wide node (only those an even number of levels below the root
+// are ever visited; telling them apart would need a top-down pass over the Karras tree).
+__global__ void __launch_bounds__(256) k_emit_fast(int n, int maxLeaf,
+                                                   const float4 *__restrict__ node_lo,
+                                                   const float4 *__restrict__ node_hi,
+                                                   const int2 *__restrict__ node_range,
+                                                   const float4 *__restrict__ s_pos_r,
+                                                   FastNode *__restrict__ fast) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int2 rg = __ldg(node_range + i);
+    if (rg.y - rg.x + 1 <= maxLeaf && i != 0) return;  // inside a fat leaf: never visited
+    const int ch[2] = {__float_as_int(__ldg(&node_lo[i].w)), __float_as_int(__ldg(&node_hi[i].w))};
+    // slots 0,1 come from child 0 and slots 2,3 from child 1 (fixed positions: registers only)
+    float bx[4][6];
+    int ref[4] = {FAST_NONE, FAST_NONE, FAST_NONE, FAST_NONE};
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+        for (int j = 0; j < 6; ++j) bx[k][j] = 0.f;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        float4 lo, hi;
+        const int r = emit_slot(ch[k], maxLeaf, node_lo, node_hi, node_range, s_pos_r, lo, hi);
+        if (r < 0) {   // leaf: one slot
+            bx[2 * k][0] = lo.x; bx[2 * k][1] = lo.y; bx[2 * k][2] = lo.z;
+            bx[2 * k][3] = hi.x; bx[2 * k][4] = hi.y; bx[2 * k][5] = hi.z;
+            ref[2 * k] = r;
+        } else {       // kept internal child: its two children take its place
+            const int g[2] = {__float_as_int(lo.w), __float_as_int(hi.w)};
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                float4 glo, ghi;
+                ref[2 * k + j] = emit_slot(g[j], maxLeaf, node_lo, node_hi, node_range, s_pos_r, glo, ghi);
+                bx[2 * k + j][0] = glo.x; bx[2 * k + j][1] = glo.y; bx[2 * k + j][2] = glo.z;
+                bx[2 * k + j][3] = ghi.x; bx[2 * k + j][4] = ghi.y; bx[2 * k + j][5] = ghi.z;
+            }
+        }
+    }
+    FastNode *f = fast + i;
+    f->q[0] = make_float4(bx[0][0], bx[0][1], bx[0][2], bx[0][3]);
+    f->q[1] = make_float4(bx[0][4], bx[0][5], bx[1][0], bx[1][1]);
+    f->q[2] = make_float4(bx[1][2], bx[1][3], bx[1][4], bx[1][5]);
+    f->q[3] = make_float4(bx[2][0], bx[2][1], bx[2][2], bx[2][3]);
+    f->q[4] = make_float4(bx[2][4], bx[2][5], bx[3][0], bx[3][1]);
+    f->q[5] = make_float4(bx[3][2], bx[3][3], bx[3][4], bx[3][5]);
+    f->ref = make_int4(ref[0], ref[1], ref[2], ref[3]);
+}
+#else
 __global__ void __launch_bounds__(256) k_emit_fast(int n, int maxLeaf,
                                                    const float4 *__restrict__ node_lo,
                                                    const float4 *__restrict__ node_hi,
@@ -568,6 +633,8 @@ __global__ void __launch_bounds__(256) k_emit_fast(int n, int maxLeaf,
     f.d = make_int4(ref[0], ref[1], 0, 0);
     fast[i] = f;
 }
+
+#endif
 
 // ---------------------------------------------------------------- host driver
 // production-tree boxes: fat-leaf roots and everything above them, then the 64-byte nodes

@@ -68,14 +68,34 @@ struct LightsDev {
     LightDev l[BRE_MAX_LIGHTS];
 };
 
-// 64-byte node of the production tree: boxes of both children + child references.
+// Node of the production tree.
+// Default: the 64-byte two-child node (boxes of both children + child references).
+// BRE_WIDE=1 (make NVEXTRA=-DBRE_WIDE=1): 128 bytes = one cache line, up to FOUR children -- the two
+// children of the binary radix-tree node, each replaced by ITS two children when it is itself a
+// kept internal node.  Box k = floats [6k, 6k+6) of q: lo.x lo.y lo.z hi.x hi.y hi.z; unused slots
+// have ref FAST_NONE.  Measured on smoke10m_1080p: nodes per ray 34.0 -> 17.0, half the walk steps,
+// but the SAME number of box tests (68 per ray) and the same bytes: K5a 1.31 -> 1.31 ms, k_emit_fast
+// +0.10 ms.  K5a is bound by the slab-test instructions, not by step overhead; parity tests pass
+// with either layout.
 // ref >= 0: internal node index;  ref < 0: leaf, see leaf_ref().
+#ifndef BRE_WIDE
+#define BRE_WIDE 0
+#endif
+#define FAST_NONE 0x7fffffff
+#if BRE_WIDE
+struct __align__(16) FastNode {
+    float4 q[6];
+    int4 ref;
+    int4 pad;
+};
+#else
 struct __align__(16) FastNode {
     float4 a;  // c0.lo.x c0.lo.y c0.lo.z c0.hi.x
     float4 b;  // c0.hi.y c0.hi.z c1.lo.x c1.lo.y
     float4 c;  // c1.lo.z c1.hi.x c1.hi.y c1.hi.z
     int4 d;    // ref0 ref1 - -
 };
+#endif
 // leaf reference: bit31 set, (count-1) in bits 27..30, first sorted photon in bits 0..26
 __host__ __device__ __forceinline__ int leaf_ref(uint32_t first, uint32_t count) {
     return (int)(0x80000000u | ((count - 1u) << 27) | first);

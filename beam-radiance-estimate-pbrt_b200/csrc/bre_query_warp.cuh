@@ -52,8 +52,8 @@ constexpr int WQ_RAYW = 12;      // floats per ray-table row (slab-test data onl
 constexpr unsigned WQ_CHUNK = 256;  // pair-queue slots reserved per atomicAdd
 constexpr unsigned PAIR_NONE = 0xffffffffu;  // padding pair (ray index) in a partly used chunk
 constexpr unsigned PAIR_FAT = 0x80000000u;   // pair.x bit: the pair stands for the FAT_P rays of a coherent group
-constexpr unsigned HEAVY_STEPS = 512;   // a per-ray packet this long is claimed first by the next launch
-constexpr unsigned HEAVY_STEPS_FAT = 256;   // same for a coherent packet (measured: 256 / 512 -> K5a 1.31 / 1.40 ms
+constexpr unsigned HEAVY_STEPS = BRE_WIDE ? 256 : 512;   // a per-ray packet this long is claimed first by the next launch
+constexpr unsigned HEAVY_STEPS_FAT = BRE_WIDE ? 128 : 256;   // same for a coherent packet (measured: 256 / 512 -> K5a 1.31 / 1.40 ms
                                             // coherent, 3.78 / 3.45 ms per-ray)
 constexpr unsigned HEAVY_CAP = 65536;   // heavy packets remembered per launch
 
@@ -479,6 +479,107 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
                 }
             }
         }
+#if BRE_WIDE
+        int nsize = 0;
+        unsigned eMask = 0;            // bit k: child k of my node is a leaf to emit this step
+        int c[4] = {0, 0, 0, 0};
+        int slot = (int)lane;
+        {
+            // fat walk: one root entry per live group (slot = group); per-ray walk: one per live ray
+            const bool push = fat ? (grpLive && (lane & (FAT_P - 1)) == 0) : live;
+            if (fat) slot = (int)(lane / FAT_P);
+            const unsigned mpush = __ballot_sync(FULL, push);
+            if (t.root_ref >= 0) {
+                if (push) { int pos = __popc(mpush & lt); sm.nref[pos] = t.root_ref; sm.nslot[pos] = (unsigned char)slot; }
+                nsize = __popc(mpush);
+            } else {            // the whole tree is one leaf
+                eMask = push ? 1u : 0u; c[0] = t.root_ref;
+            }
+        }
+        __syncwarp();
+
+        auto walk = [&](auto fatTag) {
+        constexpr bool FAT = decltype(fatTag)::value;
+        for (;;) {
+            // ---- emit surviving leaves as (ray, leaf) pairs
+            unsigned ml[4], nl = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { ml[k] = __ballot_sync(FULL, (eMask >> k) & 1u); nl += __popc(ml[k]); }
+            if (nl) {
+                if (chunkPos + nl > chunkEnd) {
+                    // pad what is left of the old chunk, reserve a new one
+                    for (unsigned p = chunkPos + lane; p < chunkEnd; p += 32)
+                        if (p < queueCap) queue[p] = make_uint2(PAIR_NONE, 0u);
+                    unsigned nb = 0;
+                    if (lane == 0) nb = atomicAdd(queueCtl + QC_PAIR_TAIL, WQ_CHUNK);
+                    chunkPos = __shfl_sync(FULL, nb, 0);
+                    chunkEnd = chunkPos + WQ_CHUNK;
+                }
+                const unsigned px = FAT ? ((base + FAT_P * slot) | PAIR_FAT) : base + slot;
+                kinds |= FAT ? KIND_FAT : KIND_THIN;
+                unsigned off = chunkPos;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    if ((eMask >> k) & 1u) {
+                        const unsigned p = off + __popc(ml[k] & lt);
+                        if (p < queueCap) queue[p] = make_uint2(px, (unsigned)c[k]);
+                        else { process_pair_inplace<MODE>(Ag, px, c[k]); ++nInplace; }
+                        if (COUNT) ++nEmitted;
+                    }
+                    off += __popc(ml[k]);
+                }
+                chunkPos += nl;
+            }
+            if (nsize == 0) break;
+            // ---- node step: one 128-byte four-child node per lane.  Popping k entries can push at
+            // most 4k, so 3k <= room keeps the stack inside WQ_NCAP-192; with no room left the walk
+            // degrades to depth-first (k = 1), which needs at most 3 x wide-tree depth (< 64) more.
+            const int room = (WQ_NCAP - 192 - nsize) / 3;
+            const int k = room >= 1 ? min(min(32, nsize), room) : 1;
+            const bool act = (int)lane < k;
+            int ref = 0;
+            if (act) { ref = sm.nref[nsize - 1 - lane]; slot = sm.nslot[nsize - 1 - lane]; }
+            nsize -= k;
+            ++steps;
+            unsigned hit = 0;
+            if (act) {
+                const FastNode *fn = t.fast + ref;
+                const float4 q0 = __ldg(&fn->q[0]), q1 = __ldg(&fn->q[1]), q2 = __ldg(&fn->q[2]);
+                const float4 q3 = __ldg(&fn->q[3]), q4 = __ldg(&fn->q[4]), q5 = __ldg(&fn->q[5]);
+                const int4 r4 = __ldg(&fn->ref);
+                c[0] = r4.x; c[1] = r4.y; c[2] = r4.z; c[3] = r4.w;
+                if (FAT) {
+                    const FatRay f = fat_load(sm.fat[slot]);
+                    hit = (slab_hit_fat(f, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y) ? 1u : 0u) |
+                          (slab_hit_fat(f, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w) ? 2u : 0u) |
+                          (slab_hit_fat(f, q3.x, q3.y, q3.z, q3.w, q4.x, q4.y) ? 4u : 0u) |
+                          (slab_hit_fat(f, q4.z, q4.w, q5.x, q5.y, q5.z, q5.w) ? 8u : 0u);
+                } else {
+                    const RayF r = rayf_load(sm.ray[slot]);
+                    hit = (slab_hit_f(r, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y) ? 1u : 0u) |
+                          (slab_hit_f(r, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w) ? 2u : 0u) |
+                          (slab_hit_f(r, q3.x, q3.y, q3.z, q3.w, q4.x, q4.y) ? 4u : 0u) |
+                          (slab_hit_f(r, q4.z, q4.w, q5.x, q5.y, q5.z, q5.w) ? 8u : 0u);
+                }
+                hit &= (c[0] != FAST_NONE ? 1u : 0u) | (c[1] != FAST_NONE ? 2u : 0u) |
+                       (c[2] != FAST_NONE ? 4u : 0u) | (c[3] != FAST_NONE ? 8u : 0u);
+                if (COUNT) ++cNodes;
+            }
+            __syncwarp();   // all pops are done before anyone pushes
+            const unsigned leafBits = (c[0] < 0 ? 1u : 0u) | (c[1] < 0 ? 2u : 0u) | (c[2] < 0 ? 4u : 0u) | (c[3] < 0 ? 8u : 0u);
+            eMask = hit & leafBits;
+            const unsigned nMask = hit & ~leafBits;
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+                const bool on = (nMask >> kk) & 1u;
+                const unsigned mn = __ballot_sync(FULL, on);
+                if (on) { int p = nsize + __popc(mn & lt); sm.nref[p] = c[kk]; sm.nslot[p] = (unsigned char)slot; }
+                nsize += __popc(mn);
+            }
+            __syncwarp();
+        }
+        };
+#else
         int nsize = 0;
         bool e0 = false, e1 = false;   // leaf children to emit this step
         int c0 = 0, c1 = 0, slot = (int)lane;
@@ -565,6 +666,7 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
             __syncwarp();
         }
         };
+#endif
         if (fat) walk(std::true_type{}); else walk(std::false_type{});
         // ---- remember heavy packets for the next launch
         if (steps >= (fat ? HEAVY_STEPS_FAT : HEAVY_STEPS) && lane == 0) {
