@@ -131,6 +131,8 @@ int bre_create(bre_ctx **out, const bre_config *cfg) {
         if (rd && atoi(rd) > 0) ctx->refit_direct = atoi(rd) < ctx->max_leaf ? ctx->max_leaf : atoi(rd);
         const char *np = getenv("BRE_NO_P2P");
         ctx->p2p_disabled = np && atoi(np) != 0;
+        const char *ga = getenv("BRE_GATHER_AOS");
+        ctx->gather_aos = !(ga && atoi(ga) == 0);
         const char *tn = getenv("BRE_TRACE_NESTED");
         ctx->trace_nested = tn && atoi(tn) != 0;
         const char *rb = getenv("BRE_RAY_BATCH");
@@ -156,7 +158,7 @@ int bre_destroy(bre_ctx *ctx) {
                    &ctx->node_lo, &ctx->node_hi, &ctx->node_range, &ctx->parent, &ctx->leaf_lo,
                    &ctx->leaf_hi, &ctx->flags, &ctx->fast, &ctx->scratch, &ctx->rays_o, &ctx->rays_d,
                    &ctx->out_rgb, &ctx->tau, &ctx->hit_counts, &ctx->hit_offsets, &ctx->hit_idx,
-                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->frames, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb, &ctx->entry, &ctx->rays_stage, &ctx->p2p_scratch};
+                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->frames, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb, &ctx->entry, &ctx->rays_stage, &ctx->p2p_scratch, &ctx->aos};
     for (Buf *b : bufs) if (b->p) cudaFree(b->p);
     if (ctx->lights_d) cudaFree(ctx->lights_d);
     if (ctx->est_host) cudaFreeHost(ctx->est_host);

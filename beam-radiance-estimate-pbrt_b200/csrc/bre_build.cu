@@ -325,6 +325,35 @@ __global__ void __launch_bounds__(256) k_gather(
     if ((threadIdx.x & 31) == 0 && amax > 0.f) atomicMax(bnd + 6, __float_as_uint(amax));
 }
 
+// The random 16-byte gathers of k_gather cost a 64-byte DRAM access each (ncu: 2.65 GB moved for
+// 0.48 GB of payload, 0.89 ms at 10 M photons).  Interleaving the three store arrays first (one
+// streaming pass, 0.15 ms) makes a photon one 48-byte run, 1.5 accesses on average instead of 3:
+// k_gather_aos 0.68 ms, build 2.47 -> 2.40 ms.  BRE_GATHER_AOS=0 restores the direct gather.
+__global__ void __launch_bounds__(256) k_interleave(const float4 *__restrict__ pos_r, const float4 *__restrict__ pw,
+                                                    const float4 *__restrict__ dr, uint32_t n, float4 *__restrict__ aos) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 *r = aos + (size_t)3 * i;
+    r[0] = __ldg(pos_r + i); r[1] = __ldg(pw + i); r[2] = __ldg(dr + i);
+}
+__global__ void __launch_bounds__(256) k_gather_aos(const float4 *__restrict__ aos, const uint32_t *__restrict__ order,
+                                                    uint32_t n, float4 *__restrict__ s_pos_r, float4 *__restrict__ s_pow,
+                                                    float4 *__restrict__ s_dir, uint32_t *__restrict__ bnd) {
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    float amax = 0.f;
+    if (s < n) {
+        const float4 *r = aos + (size_t)3 * __ldg(order + s);
+        const float4 p = __ldg(r), a = __ldg(r + 1), b = __ldg(r + 2);
+        s_pos_r[s] = p; s_pow[s] = a; s_dir[s] = b;
+        float4 lo, hi;
+        leaf_box(p, lo, hi);
+        amax = box_abs_max(lo, hi);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    if ((threadIdx.x & 31) == 0 && amax > 0.f) atomicMax(bnd + 6, __float_as_uint(amax));
+}
+
 __global__ void __launch_bounds__(256) k_leafboxes(const float4 *__restrict__ s_pos_r, uint32_t n,
                                                    float4 *__restrict__ leaf_lo,
                                                    float4 *__restrict__ leaf_hi) {
@@ -759,6 +788,13 @@ int build_tree(bre_ctx *ctx) {
         t = vin; vin = vout; vout = t;
     }
     // after 4 passes kin == codes, vin == order
+    if (ctx->gather_aos) {
+        if ((s = ensure(ctx, ctx->aos, (size_t)n * 48)) != BRE_OK) { delete pt; return s; }
+        k_interleave<<<g256, 256, 0, st>>>(pos_r, (const float4 *)ctx->pow.p, (const float4 *)ctx->dir.p, n,
+                                           (float4 *)ctx->aos.p);
+        k_gather_aos<<<g256, 256, 0, st>>>((const float4 *)ctx->aos.p, order, n, (float4 *)ctx->s_pos_r.p,
+                                           (float4 *)ctx->s_pow.p, (float4 *)ctx->s_dir.p, bnd);
+    } else
     k_gather<<<g256, 256, 0, st>>>(pos_r, (const float4 *)ctx->pow.p, (const float4 *)ctx->dir.p,
                                    order, n, (float4 *)ctx->s_pos_r.p, (float4 *)ctx->s_pow.p,
                                    (float4 *)ctx->s_dir.p, bnd);

@@ -142,6 +142,7 @@ struct bre_ctx {
     uint32_t n_tri = 0;
     bre::Buf tri, tri_kdb;
     int lights_in_medium = 1;
+    bool gather_aos = true;                 // BRE_GATHER_AOS=0: gather straight from the three store arrays
     bool trace_nested = false;              // BRE_TRACE_NESTED=1: the nested-loop K1 (A/B experiments)
     bre_camera camera{};
     bool have_camera = false;
@@ -156,7 +157,7 @@ struct bre_ctx {
     int last_build_kind = 0;     // 0 none, 1 full build, 2 refit only
     uint32_t n_built = 0;
     bre::Buf s_pos_r, s_pow, s_dir, order, codes, keys_alt, vals_alt, hist, node_lo, node_hi,
-        node_range, parent, leaf_lo, leaf_hi, flags, fast, scratch, entry;
+        node_range, parent, leaf_lo, leaf_hi, flags, fast, scratch, entry, aos;
     float abs_max = 0;
     int root_ref = 0;
     // query scratch
