@@ -356,8 +356,11 @@ __device__ __forceinline__ unsigned ld_volatile_u32(const unsigned *p) {
 // packets that look into a light source no longer finish last (measured: one such packet kept a
 // single warp busy for 2.8 ms of a 4.6 ms kernel).  Progressive rendering repeats the same camera
 // every iteration; with unrelated rays the list is merely a harmless permutation.
+#ifndef WQ_MINB
+#define WQ_MINB 1
+#endif
 template <int MODE, bool COUNT>
-__global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
+__global__ void __launch_bounds__(WQ_WARPS * 32, WQ_MINB) k_traverse(
     LeafArgs A, const LeafArgs *__restrict__ Ag, uint32_t n, uint2 *__restrict__ queue,
     unsigned int queueCap, unsigned int *__restrict__ queueCtl,
     const unsigned int *__restrict__ heavyIn, const unsigned int *__restrict__ nHeavyInPtr,
