@@ -336,7 +336,22 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     int perSM = 0;
     BRE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_traverse<MODE, COUNT>, WQ_WARPS * 32, 0));
     if (perSM < 1) perSM = 1;
-    const unsigned gb = (unsigned)ctx->sm_count * 8u;
+    // K5b grid.  The leaf kernels walk the pair queue, whose length is only known on the device, in
+    // runs of 64 pairs.  With a static stride the cost of a warp's runs varies with their hits and the
+    // chip waits for the unluckiest warp: blocks/SM 4 / 8 / 32 / 128 / 512 / 2048 -> K5b 2.29 / 2.23 / 2.18 /
+    // 2.115 / 2.15 / 2.39 ms at 2 M rays (and 512 blocks/SM cost a 65 K-ray launch +0.07 ms in empty
+    // blocks).  LP_DYNAMIC (default): resident blocks claim runs from a counter instead.
+    unsigned gb;
+    if (ctx->k5b_blocks_per_sm > 0) gb = (unsigned)ctx->sm_count * (unsigned)ctx->k5b_blocks_per_sm;
+#if LP_DYNAMIC
+    else gb = (unsigned)ctx->sm_count * 8u;
+#else
+    else {
+        const unsigned lo = (unsigned)ctx->sm_count * 8u, hi = (unsigned)ctx->sm_count * 128u;
+        const unsigned want = (unsigned)std::min<uint64_t>((uint64_t)batchRays / 32u + 1u, hi);
+        gb = want < lo ? lo : want;
+    }
+#endif
     if (ctx->timing) cudaEventRecord(ctx->ev[PH_QUERY_A][0], ctx->stream);
     for (uint32_t b = 0; b < nBatches; ++b) {
         const uint32_t r0 = b * batchRays, nb = (n - r0 < batchRays) ? n - r0 : batchRays;

@@ -58,7 +58,7 @@ constexpr unsigned HEAVY_STEPS_FAT = BRE_WIDE ? 128 : 256;   // same for a coher
 constexpr unsigned HEAVY_CAP = 65536;   // heavy packets remembered per launch
 
 // queueCtl words (zeroed before every launch)
-enum { QC_PAIR_TAIL = 0, QC_PACKET = 1, QC_INPLACE = 2, QC_EMITTED = 3, QC_KINDS = 4, QC_WORDS = 8 };
+enum { QC_PAIR_TAIL = 0, QC_PACKET = 1, QC_INPLACE = 2, QC_EMITTED = 3, QC_KINDS = 4, QC_RUN_THIN = 5, QC_RUN_FAT = 6, QC_WORDS = 8 };
 enum { KIND_THIN = 1u, KIND_FAT = 2u };   // QC_KINDS bits: which kinds of pair K5a put into the queue
 
 struct __align__(16) WarpSmem {
@@ -701,6 +701,9 @@ __global__ void __launch_bounds__(WQ_WARPS * 32, WQ_MINB) k_traverse(
 // ---------------------------------------------------------------- K5b
 constexpr int LP_WARPS = 8;
 constexpr unsigned LP_RUN = 64;     // consecutive pairs a warp fetches at once
+#ifndef LP_DYNAMIC
+#define LP_DYNAMIC 1
+#endif
 struct __align__(16) HitBuf {
     uint32_t s[64], q[64];
     float th[64], d2[64];
@@ -711,7 +714,7 @@ template <int MODE, bool COUNT, int LW>
 __global__ void __launch_bounds__(LP_WARPS * 32, 4) k_leaf_pairs(LeafArgs A,
                                                               const uint2 *__restrict__ queue,
                                                               unsigned int queueCap,
-                                                              const unsigned int *__restrict__ queueCtl,
+                                                              unsigned int *__restrict__ queueCtl,
                                                               unsigned long long *__restrict__ counters) {
     __shared__ HitBuf bufAll[LP_WARPS];
     HitBuf &hb = bufAll[threadIdx.x >> 5];
@@ -727,9 +730,29 @@ __global__ void __launch_bounds__(LP_WARPS * 32, 4) k_leaf_pairs(LeafArgs A,
     const unsigned total = min(__ldg(queueCtl + QC_PAIR_TAIL), queueCap);
     const unsigned warpsTotal = gridDim.x * LP_WARPS;
     const unsigned warpId = blockIdx.x * LP_WARPS + (threadIdx.x >> 5);
+    (void)warpId;
     unsigned long long cTests = 0;
     unsigned nbuf = 0;
+#if LP_DYNAMIC
+    // Runs of LP_RUN pairs are claimed from a counter: the cost of a run varies with its hits, a
+    // static stride leaves the chip waiting for the unluckiest warp.  A claim takes `rpc` runs so
+    // that a launch issues ~16 claims per warp however long the queue is (one claim per run made
+    // the counter itself the bottleneck of a 180 M-pair queue: K5b 6.4 -> 8.7 ms).
+    const unsigned totalRuns = (total + LP_RUN - 1) / LP_RUN;
+    const unsigned rpc = max(1u, min(64u, totalRuns / (warpsTotal * 16u)));
+    unsigned cur = 0, curEnd = 0;      // runs [cur, curEnd) belong to this warp
+    for (;;) {
+        if (cur == curEnd) {
+            unsigned c = 0;
+            if (lane == 0) c = atomicAdd(queueCtl + QC_RUN_THIN, rpc);
+            cur = __shfl_sync(FULL, c, 0);
+            if (cur >= totalRuns) break;
+            curEnd = min(cur + rpc, totalRuns);
+        }
+        const unsigned run = (cur++) * LP_RUN;
+#else
     for (unsigned run = warpId * LP_RUN; run < total; run += warpsTotal * LP_RUN) {
+#endif
         // 64 pairs, two coalesced 256-byte loads
         uint2 pr0 = make_uint2(PAIR_NONE, 0u), pr1 = make_uint2(PAIR_NONE, 0u);
         if (run + lane < total) pr0 = __ldg(queue + run + lane);
@@ -843,7 +866,7 @@ struct __align__(16) FatBuf {
 template <int MODE, bool COUNT, int LW>
 __global__ void __launch_bounds__(LP_WARPS * 32, FAT_MINB) k_leaf_fat(LeafArgs A, const uint2 *__restrict__ queue,
                                                             unsigned int queueCap,
-                                                            const unsigned int *__restrict__ queueCtl,
+                                                            unsigned int *__restrict__ queueCtl,
                                                             unsigned long long *__restrict__ counters) {
     __shared__ HitBuf bufAll[LP_WARPS];
     __shared__ FatBuf fatAll[LP_WARPS];
@@ -861,6 +884,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, FAT_MINB) k_leaf_fat(LeafArgs A
     const unsigned total = min(__ldg(queueCtl + QC_PAIR_TAIL), queueCap);
     const unsigned warpsTotal = gridDim.x * LP_WARPS;
     const unsigned warpId = blockIdx.x * LP_WARPS + (threadIdx.x >> 5);
+    (void)warpId;
     unsigned long long cTests = 0;
     unsigned nbuf = 0, npb = 0;
 
@@ -915,7 +939,26 @@ __global__ void __launch_bounds__(LP_WARPS * 32, FAT_MINB) k_leaf_fat(LeafArgs A
         }
     };
 
+#if LP_DYNAMIC
+    // Runs of LP_RUN pairs are claimed from a counter: the cost of a run varies with its hits, a
+    // static stride leaves the chip waiting for the unluckiest warp.  A claim takes `rpc` runs so
+    // that a launch issues ~16 claims per warp however long the queue is (one claim per run made
+    // the counter itself the bottleneck of a 180 M-pair queue: K5b 6.4 -> 8.7 ms).
+    const unsigned totalRuns = (total + LP_RUN - 1) / LP_RUN;
+    const unsigned rpc = max(1u, min(64u, totalRuns / (warpsTotal * 16u)));
+    unsigned cur = 0, curEnd = 0;      // runs [cur, curEnd) belong to this warp
+    for (;;) {
+        if (cur == curEnd) {
+            unsigned c = 0;
+            if (lane == 0) c = atomicAdd(queueCtl + QC_RUN_FAT, rpc);
+            cur = __shfl_sync(FULL, c, 0);
+            if (cur >= totalRuns) break;
+            curEnd = min(cur + rpc, totalRuns);
+        }
+        const unsigned run = (cur++) * LP_RUN;
+#else
     for (unsigned run = warpId * LP_RUN; run < total; run += warpsTotal * LP_RUN) {
+#endif
         uint2 pr0 = make_uint2(PAIR_NONE, 0u), pr1 = make_uint2(PAIR_NONE, 0u);
         if (run + lane < total) pr0 = __ldg(queue + run + lane);
         if (run + 32 + lane < total) pr1 = __ldg(queue + run + 32 + lane);
