@@ -127,6 +127,8 @@ int bre_create(bre_ctx **out, const bre_config *cfg) {
         if (lf && atoi(lf) > 0) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(lf));
         const char *fs = getenv("BRE_FAT_SPREAD");
         if (fs) ctx->fat_spread = (float)atof(fs);
+        const char *ka = getenv("BRE_K5A_BLOCKS");
+        if (ka && atoi(ka) > 0) ctx->k5a_blocks_per_sm = atoi(ka);
         const char *kb = getenv("BRE_K5B_BLOCKS");
         if (kb && atoi(kb) > 0) ctx->k5b_blocks_per_sm = atoi(kb);
         const char *rd = getenv("BRE_REFIT_DIRECT");

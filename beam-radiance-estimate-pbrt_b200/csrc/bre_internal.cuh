@@ -168,6 +168,7 @@ struct bre_ctx {
     int heavy_parity = 0;
     // ray batching of K5 (bre_query.cu launch_query)
     uint32_t ray_batch_override = 0;        // BRE_RAY_BATCH (experiments)
+    int k5a_blocks_per_sm = 0;              // BRE_K5A_BLOCKS: cap on resident K5a blocks per SM (0 = what fits)
     int k5b_blocks_per_sm = 0;              // BRE_K5B_BLOCKS: K5b grid = SMs x this; 0 = from the ray count (bre_query.cu)
     float fat_spread = 1.f / 64.f;          // BRE_FAT_SPREAD: largest |d_i - d_0| of a packet walked as one fat ray (0 = off)
     uint32_t ctr_batches = 0, ctr_batch_rays = 0, ctr_rays = 0;

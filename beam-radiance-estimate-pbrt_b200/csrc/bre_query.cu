@@ -336,6 +336,7 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     int perSM = 0;
     BRE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_traverse<MODE, COUNT>, WQ_WARPS * 32, 0));
     if (perSM < 1) perSM = 1;
+    if (ctx->k5a_blocks_per_sm > 0 && perSM > ctx->k5a_blocks_per_sm) perSM = ctx->k5a_blocks_per_sm;
     // K5b grid.  The leaf kernels walk the pair queue, whose length is only known on the device, in
     // runs of 64 pairs.  With a static stride the cost of a warp's runs varies with their hits and the
     // chip waits for the unluckiest warp: blocks/SM 4 / 8 / 32 / 128 / 512 / 2048 -> K5b 2.29 / 2.23 / 2.18 /

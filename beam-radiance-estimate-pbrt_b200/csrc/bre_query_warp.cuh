@@ -49,11 +49,18 @@ constexpr int FAT_P = 8;         // rays per coherent group ("fat ray"): WQ_P / 
 constexpr int WQ_NCAP = BRE_WQ_NCAP;   // node stack entries per warp
 constexpr int WQ_WARPS = 4;      // warps per block
 constexpr int WQ_RAYW = 12;      // floats per ray-table row (slab-test data only)
-constexpr unsigned WQ_CHUNK = 256;  // pair-queue slots reserved per atomicAdd
+#ifndef BRE_WQ_CHUNK
+#define BRE_WQ_CHUNK 256
+#endif
+constexpr unsigned WQ_CHUNK = BRE_WQ_CHUNK;  // pair-queue slots reserved per atomicAdd (>= 64: a step emits up to 64 pairs);
+                                             // 64 / 128 / 256 / 512 -> K5a 1.50 / 1.36 / 1.31 / 1.30, K5b 2.02 / 1.96 / 1.95 / 1.97 ms
 constexpr unsigned PAIR_NONE = 0xffffffffu;  // padding pair (ray index) in a partly used chunk
 constexpr unsigned PAIR_FAT = 0x80000000u;   // pair.x bit: the pair stands for the FAT_P rays of a coherent group
 constexpr unsigned HEAVY_STEPS = BRE_WIDE ? 256 : 512;   // a per-ray packet this long is claimed first by the next launch
-constexpr unsigned HEAVY_STEPS_FAT = BRE_WIDE ? 128 : 256;   // same for a coherent packet (measured: 256 / 512 -> K5a 1.31 / 1.40 ms
+#ifndef BRE_HEAVY_FAT
+#define BRE_HEAVY_FAT (BRE_WIDE ? 128 : 256)
+#endif
+constexpr unsigned HEAVY_STEPS_FAT = BRE_HEAVY_FAT;   // same for a coherent packet (measured: 256 / 512 -> K5a 1.31 / 1.40 ms
                                             // coherent, 3.78 / 3.45 ms per-ray)
 constexpr unsigned HEAVY_CAP = 65536;   // heavy packets remembered per launch
 
@@ -356,11 +363,14 @@ __device__ __forceinline__ unsigned ld_volatile_u32(const unsigned *p) {
 // packets that look into a light source no longer finish last (measured: one such packet kept a
 // single warp busy for 2.8 ms of a 4.6 ms kernel).  Progressive rendering repeats the same camera
 // every iteration; with unrelated rays the list is merely a harmless permutation.
-#ifndef WQ_MINB
-#define WQ_MINB 1
-#endif
+// WQ_MINB (make NVEXTRA=-DWQ_MINB=n) forces n blocks per SM: 10 / 12 (48 / 40 registers) spill and measured
+// 1.79 / 2.19 ms against 1.31 ms for the compiler's own 56 registers (9 blocks of 4 warps per SM)
 template <int MODE, bool COUNT>
+#ifdef WQ_MINB
 __global__ void __launch_bounds__(WQ_WARPS * 32, WQ_MINB) k_traverse(
+#else
+__global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
+#endif
     LeafArgs A, const LeafArgs *__restrict__ Ag, uint32_t n, uint2 *__restrict__ queue,
     unsigned int queueCap, unsigned int *__restrict__ queueCtl,
     const unsigned int *__restrict__ heavyIn, const unsigned int *__restrict__ nHeavyInPtr,
@@ -382,6 +392,10 @@ __global__ void __launch_bounds__(WQ_WARPS * 32, WQ_MINB) k_traverse(
 
     for (;;) {
         // ---- claim a packet: last launch's heavy packets first, then the rest in order
+        // (Other claim orders were measured and lost, K5a ms against 1.31: 2 / 4 / 8 consecutive packets per
+        // claim 1.35 / 1.54 / 1.84; the image walked in vertical strips of 8..120 packets 1.38-1.43; the
+        // next claim issued one packet ahead 1.39.  Row order with single-packet claims keeps the
+        // packets in flight closest together in the tree.)
         unsigned pk = 0;
         if (lane == 0) {
             for (;;) {
@@ -743,6 +757,8 @@ __global__ void __launch_bounds__(LP_WARPS * 32, 4) k_leaf_pairs(LeafArgs A,
     unsigned cur = 0, curEnd = 0;      // runs [cur, curEnd) belong to this warp
     for (;;) {
         if (cur == curEnd) {
+            // (claiming the NEXT batch of runs early, to hide the counter's round trip, measured
+            // slower: K5b 1.90 -> 2.00 ms)
             unsigned c = 0;
             if (lane == 0) c = atomicAdd(queueCtl + QC_RUN_THIN, rpc);
             cur = __shfl_sync(FULL, c, 0);
@@ -949,6 +965,8 @@ __global__ void __launch_bounds__(LP_WARPS * 32, FAT_MINB) k_leaf_fat(LeafArgs A
     unsigned cur = 0, curEnd = 0;      // runs [cur, curEnd) belong to this warp
     for (;;) {
         if (cur == curEnd) {
+            // (claiming the NEXT batch of runs early, to hide the counter's round trip, measured
+            // slower: K5b 1.90 -> 2.00 ms)
             unsigned c = 0;
             if (lane == 0) c = atomicAdd(queueCtl + QC_RUN_FAT, rpc);
             cur = __shfl_sync(FULL, c, 0);

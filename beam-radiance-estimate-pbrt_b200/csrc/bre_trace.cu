@@ -444,7 +444,7 @@ __global__ void __launch_bounds__(128) k_trace_flat(MediumDev m, const LightsDev
             } else { ++nInt; state = TS_SEG; }
         }
         if (runNew && (mNew >> (threadIdx.x & 31u) & 1u)) {
-            pid = atomicAdd(nextPath, 1u);
+            pid = atomicAdd(nextPath, 1u);   // (claiming one path ahead to hide the round trip: 1.454 -> 1.475 ms, not kept)
             if (pid >= nPaths) state = TS_DONE;
             else {
                 rng.seed(first + pid + 1);  // photonbeam.cpp:386-391
