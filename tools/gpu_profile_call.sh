@@ -1,3 +1,5 @@
+# One gpurun call: GPU tests, smoke, bench (both arms), K5a block sweep, ncu launch list and full capture, other workloads.
+# Outputs land in gpurun_out/; the summaries kept for the record are copied to profiles/ (r01_*_v15*).
 mkdir -p gpurun_out
 run() { timeout 200 python bench.py --no-cpu > gpurun_out/ab_$1.json 2>/dev/null; }
 (timeout 600 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu_v15.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest_gpu_v15.log)
