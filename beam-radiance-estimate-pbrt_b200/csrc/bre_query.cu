@@ -232,7 +232,7 @@ __host__ __device__ inline LeafArgs shift_args(LeafArgs A, size_t off) {
     if (A.span) A.span += off;
     if (A.hitCounts) A.hitCounts += off;
     if (A.hitOffsets) A.hitOffsets += off;
-    if (A.frames) A.frames += off / FAT_P * 4;
+    if (A.frames) A.frames += off / FAT_P * FRAME_V4;
     return A;
 }
 __global__ void k_store_batch_args(LeafArgs A, char *blocks, unsigned batchRays, unsigned nBatches) {
@@ -308,7 +308,7 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     A.hitCounts = hitCounts; A.hitOffsets = hitOffsets; A.hitIdx = hitIdx;
     A.frames = nullptr;
     if (ctx->fat_spread > 0.f) {   // one 64-byte frame per packet
-        if ((s = ensure(ctx, ctx->frames, ((size_t)n / FAT_P + WQ_P / FAT_P) * 64)) != BRE_OK) return s;
+        if ((s = ensure(ctx, ctx->frames, ((size_t)n / FAT_P + WQ_P / FAT_P) * 16 * FRAME_V4)) != BRE_OK) return s;
         A.frames = (float4 *)ctx->frames.p;
     }
     k_store_batch_args<<<(nBatches + 63) / 64, 64, 0, ctx->stream>>>(A, blocks, batchRays, nBatches);

@@ -207,6 +207,7 @@ __device__ __forceinline__ float pk_max(float v) {
 // R = r / kappa + hT, t = P'.u, is missed by every ray of the packet.  The slack (4 x origin spread
 // + 2^-16 x coordinate scale) covers the origins' differences and every rounding error of this test
 // and of the exact predicate by more than 10x.  Only photons that pass are tested exactly, per ray.
+constexpr int FRAME_V4 = 5;      // float4 per packet frame: a, b, c, d below + the slope ranges of the two half packets
 struct PacketFrame {
     float4 a;   // o.xyz, hT
     float4 b;   // u.xyz, 1/kappa
@@ -225,6 +226,22 @@ __device__ __forceinline__ bool frame_may_hit(const float4 fa, const float4 fb, 
     return !(fabsf(h) > p.w + fa.w) && !(s > fmaxf(m0, m1) + R) && !(s < fminf(m0, m1) - R);
 }
 
+// Same test, then per half packet (rays 0-3: slopes [fe.x, fe.y], rays 4-7: [fe.z, fe.w]): bit 0 / bit 1 set
+// when the photon may reach that half.  0 = no ray of the packet can hit.  NaNs keep both halves.
+__device__ __forceinline__ unsigned frame_halves(const float4 fa, const float4 fb, const float4 fc, const float4 fd,
+                                                 const float4 fe, const float4 p) {
+    const float x = p.x - fa.x, y = p.y - fa.y, z = p.z - fa.z;
+    const float h = __fmaf_rn(z, fd.z, __fmaf_rn(y, fd.y, x * fd.x));
+    const float t = __fmaf_rn(z, fb.z, __fmaf_rn(y, fb.y, x * fb.x));
+    const float s = __fmaf_rn(z, fc.z, __fmaf_rn(y, fc.y, x * fc.x));
+    const float R = __fmaf_rn(p.w, fb.w, fa.w);
+    if (fabsf(h) > p.w + fa.w) return 0u;
+    const float a0 = t * fe.x, a1 = t * fe.y, b0 = t * fe.z, b1 = t * fe.w;
+    const bool inA = !(s > fmaxf(a0, a1) + R) && !(s < fminf(a0, a1) - R);
+    const bool inB = !(s > fmaxf(b0, b1) + R) && !(s < fminf(b0, b1) - R);
+    return (inA ? 1u : 0u) | (inB ? 2u : 0u);
+}
+
 // Everything K5b needs besides the pair itself.
 struct LeafArgs {
     TreeDev t;
@@ -238,7 +255,7 @@ struct LeafArgs {
     uint32_t *hitCounts;         // MODE 1: per-ray hit counts; MODE 2: per-ray write cursors
     const uint64_t *hitOffsets;  // MODE 2
     uint32_t *hitIdx;            // MODE 2
-    float4 *frames;              // 4 float4 per packet: PacketFrame of coherent packets (K5a -> k_leaf_fat)
+    float4 *frames;              // FRAME_V4 float4 per packet: PacketFrame of coherent packets (K5a -> k_leaf_fat)
 };
 
 // Radiance of one hit (photon s, ray q, ray parameter th, squared distance d2).
@@ -463,7 +480,19 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
             const float m = __fdividef(db, da);
             const float kap = da * rsqrtf(da * da + db * db);
             const float aMin = pk_min(da), kMin = pk_min(kap), cMax = pk_max(fabsf(dc));
-            const float mLo = pk_min(m), mHi = pk_max(m);
+            // slope range of the packet and of its two halves (rays 0-3, 4-7): k_leaf_fat runs the exact
+            // predicate only for the half packet(s) a photon can reach.  The butterfly's first two steps
+            // are the half-group reductions, its last step joins the halves.
+            static_assert(FAT_P == 8, "half-packet slope ranges assume 8 rays per group");
+            float hLo = m, hHi = m;
+#pragma unroll
+            for (int o2 = 1; o2 < FAT_P / 2; o2 <<= 1) {
+                hLo = fminf(hLo, __shfl_xor_sync(FULL, hLo, o2));
+                hHi = fmaxf(hHi, __shfl_xor_sync(FULL, hHi, o2));
+            }
+            const float loB = __shfl_sync(FULL, hLo, g0 + FAT_P / 2), hiB = __shfl_sync(FULL, hHi, g0 + FAT_P / 2);
+            const float mLo = fminf(hLo, __shfl_xor_sync(FULL, hLo, FAT_P / 2));
+            const float mHi = fmaxf(hHi, __shfl_xor_sync(FULL, hHi, FAT_P / 2));
             // NaNs fail the comparisons and fall back to the per-ray walk
             const bool dead = !(tMaxAll > 0.f) && tMaxAll == tMaxAll;
             const bool coh = (sameSgn & grpBits) == grpBits && dSpread <= fatSpread && oSpread <= M * 0x1p-10f &&
@@ -488,11 +517,12 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
                     fat_store(sm.fat[lane / FAT_P], f);
                     const float tau = fminf(tMaxAll, 4.f * M);
                     const float hT = 1.01f * cMax * tau + 4.f * oSpread + M * 0x1p-16f;
-                    float4 *fr = A.frames + ((size_t)pk * (WQ_P / FAT_P) + lane / FAT_P) * 4;
+                    float4 *fr = A.frames + ((size_t)pk * (WQ_P / FAT_P) + lane / FAT_P) * FRAME_V4;
                     fr[0] = make_float4(ox0, oy0, oz0, hT);
                     fr[1] = make_float4(ux, uy, uz, 1.001f * __fdividef(1.f, kMin));
                     fr[2] = make_float4(vx, vy, vz, mLo);
                     fr[3] = make_float4(nx2, ny2, nz2, mHi);
+                    fr[4] = make_float4(hLo, hHi, loB, hiB);     // (lane g0 holds the first half's range)
                 }
             }
         }
@@ -854,10 +884,10 @@ __global__ void __launch_bounds__(LP_WARPS * 32, 4) k_leaf_pairs(LeafArgs A,
 //     as in k_leaf_pairs.
 // On the bench scene 30 % of the photons of a packet's leaves survive stage 1, so a photon costs
 // ~1 + 0.3 x 8 predicates instead of 8.
-struct __align__(16) FatBuf {
-    float4 p[64];        // surviving photon {pos, radius}
-    uint32_t s[64];      // its index
-    uint32_t base[64];   // first ray of its packet
+struct __align__(16) FatBuf {      // one entry per (surviving photon, half packet it may reach)
+    float4 p[96];        // photon {pos, radius}
+    uint32_t s[96];      // its index
+    uint32_t base[96];   // first ray of the HALF packet (packet base, +4 for the second half)
 };
 // Tuning knobs (make NVEXTRA=-D...), measured on smoke10m_1080p, K5b ms:
 //   U=2,MINB=3,SEG=1 2.88 | U=4 2.75 | MINB=4 2.39 | SEG=0 2.35 | SEG=0,MINB=5 2.36 | SEG=0,MINB=6 2.65
@@ -875,9 +905,6 @@ struct __align__(16) FatBuf {
 #ifndef FAT_PREF
 #define FAT_PREF 0
 #endif
-#ifndef FAT_RAYCACHE
-#define FAT_RAYCACHE 0
-#endif
 
 template <int MODE, bool COUNT, int LW>
 __global__ void __launch_bounds__(LP_WARPS * 32, FAT_MINB) k_leaf_fat(LeafArgs A, const uint2 *__restrict__ queue,
@@ -890,12 +917,13 @@ __global__ void __launch_bounds__(LP_WARPS * 32, FAT_MINB) k_leaf_fat(LeafArgs A
     FatBuf &fb = fatAll[threadIdx.x >> 5];
     constexpr unsigned G = 32 / LW;
     constexpr int U = FAT_U;
-    constexpr unsigned SLOTS = 32 / FAT_P;             // survivors per stage-2 pass
+    constexpr unsigned HALF = FAT_P / 2;               // rays of a half packet
+    constexpr unsigned SLOTS = 32 / HALF;              // (survivor, half packet) entries per stage-2 pass
     const unsigned FULL = 0xffffffffu;
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt = (1u << lane) - 1u;
     const unsigned sub = lane / LW, j = lane % LW;
-    const unsigned ray = lane / SLOTS, slot = lane % SLOTS;
+    const unsigned slot = lane / HALF, ray = lane % HALF;   // stage 2: entry `slot` of the pass, ray `ray` of its half packet
     if (!(__ldg(queueCtl + QC_KINDS) & KIND_FAT)) return;
     const unsigned total = min(__ldg(queueCtl + QC_PAIR_TAIL), queueCap);
     const unsigned warpsTotal = gridDim.x * LP_WARPS;
@@ -904,11 +932,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, FAT_MINB) k_leaf_fat(LeafArgs A
     unsigned long long cTests = 0;
     unsigned nbuf = 0, npb = 0;
 
-#if FAT_RAYCACHE
-    unsigned curBase = 0xffffffffu;
-    float4 co = make_float4(0.f, 0.f, 0.f, 0.f), cd = co;
-#endif
-    // stage 2 over the newest `take` survivors (take <= SLOTS)
+    // stage 2 over the newest `take` entries (take <= SLOTS): HALF rays each
     auto exact_pass = [&](unsigned take) {
         bool hit = false;
         float th = 0.f, d2 = 0.f;
@@ -917,16 +941,8 @@ __global__ void __launch_bounds__(LP_WARPS * 32, FAT_MINB) k_leaf_fat(LeafArgs A
             const unsigned e = npb - take + slot;
             const float4 p = fb.p[e];
             s = fb.s[e];
-#if FAT_RAYCACHE
-            // this lane always tests ray `ray` of a packet: keep it in registers while the packet lasts
-            const unsigned b = fb.base[e];
-            if (b != curBase) { curBase = b; co = __ldg(A.ro + b + ray); cd = __ldg(A.rd + b + ray); }
-            q = b + ray;
-            const float4 o = co, d = cd;
-#else
             q = fb.base[e] + ray;
             const float4 o = __ldg(A.ro + q), d = __ldg(A.rd + q);
-#endif
             RayS r;
             r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tMax = o.w;
             r.dx = d.x; r.dy = d.y; r.dz = d.z;
@@ -1003,30 +1019,35 @@ __global__ void __launch_bounds__(LP_WARPS * 32, FAT_MINB) k_leaf_fat(LeafArgs A
                 if (on[u]) {
                     p[u] = __ldg(A.t.s_pos_r + first[u] + j);
 #if FAT_PREF
-                    const float4 *fr = A.frames + (size_t)(base[u] / FAT_P) * 4;
+                    const float4 *fr = A.frames + (size_t)(base[u] / FAT_P) * FRAME_V4;
                     f0[u] = __ldg(fr); f1[u] = __ldg(fr + 1); f2[u] = __ldg(fr + 2); f3[u] = __ldg(fr + 3);
 #endif
                 }
             }
 #pragma unroll
             for (int u = 0; u < U; ++u) {
-                bool keep = false;
+                unsigned halves = 0;       // bit 0: rays 0-3 of the packet may hit this photon, bit 1: rays 4-7
                 if (on[u]) {
 #if FAT_PREF
-                    keep = frame_may_hit(f0[u], f1[u], f2[u], f3[u], p[u]);
+                    const float4 f4 = __ldg(A.frames + (size_t)(base[u] / FAT_P) * FRAME_V4 + 4);
+                    halves = frame_halves(f0[u], f1[u], f2[u], f3[u], f4, p[u]);
 #else
-                    const float4 *fr = A.frames + (size_t)(base[u] / FAT_P) * 4;
-                    keep = frame_may_hit(__ldg(fr), __ldg(fr + 1), __ldg(fr + 2), __ldg(fr + 3), p[u]);
+                    const float4 *fr = A.frames + (size_t)(base[u] / FAT_P) * FRAME_V4;
+                    halves = frame_halves(__ldg(fr), __ldg(fr + 1), __ldg(fr + 2), __ldg(fr + 3), __ldg(fr + 4), p[u]);
 #endif
                     if (COUNT) ++cTests;
                 }
-                const unsigned mk = __ballot_sync(FULL, keep);
-                if (mk == 0u) continue;
-                if (keep) {
-                    const unsigned pos = npb + __popc(mk & lt);
+                const unsigned mkA = __ballot_sync(FULL, halves & 1u), mkB = __ballot_sync(FULL, halves & 2u);
+                if ((mkA | mkB) == 0u) continue;
+                if (halves & 1u) {
+                    const unsigned pos = npb + __popc(mkA & lt);
                     fb.p[pos] = p[u]; fb.s[pos] = first[u] + j; fb.base[pos] = base[u];
                 }
-                npb += __popc(mk);
+                if (halves & 2u) {
+                    const unsigned pos = npb + __popc(mkA) + __popc(mkB & lt);
+                    fb.p[pos] = p[u]; fb.s[pos] = first[u] + j; fb.base[pos] = base[u] + HALF;
+                }
+                npb += __popc(mkA) + __popc(mkB);
                 __syncwarp();
                 while (npb >= SLOTS) exact_pass(SLOTS);
                 __syncwarp();
