@@ -878,12 +878,14 @@ __global__ void __launch_bounds__(LP_WARPS * 32, 4) k_leaf_pairs(LeafArgs A,
 // ---------------------------------------------------------------- K5b for coherent packets
 // (packet, leaf) pairs, two stages per warp:
 //  1. one photon per lane (LW lanes per pair, like k_leaf_pairs): the photon is tested ONCE against
-//     the packet's frame (frame_may_hit); survivors are compacted into a shared-memory buffer.
-//  2. whenever 4 survivors are buffered: lane = (ray of the packet, survivor) runs the exact disk
+//     the packet's frame and the slope ranges of its two half packets (frame_halves); it is entered
+//     into a shared-memory buffer once per half packet (rays 0-3, 4-7) it may reach.
+//  2. whenever 8 entries are buffered: lane = (entry, ray of its half packet) runs the exact disk
 //     predicate, 32 per pass with every lane busy.  Hits go through the same buffer / warp shading
 //     as in k_leaf_pairs.
-// On the bench scene 30 % of the photons of a packet's leaves survive stage 1, so a photon costs
-// ~1 + 0.3 x 8 predicates instead of 8.
+// On the bench scene 28 % of the photons of a packet's leaves survive stage 1 and reach 1.2 half
+// packets on average, so a photon costs ~1 + 0.28 x 1.2 x 4 predicates instead of 8.
+// Work distribution: resident warps claim runs of LP_RUN pairs from a counter, in queue order.
 struct __align__(16) FatBuf {      // one entry per (surviving photon, half packet it may reach)
     float4 p[96];        // photon {pos, radius}
     uint32_t s[96];      // its index
