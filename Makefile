@@ -15,7 +15,7 @@ OBJS := $(patsubst %.cu,$(OBJDIR)/%.o,$(SRCS)) $(OBJDIR)/bre_nccl.o
 all: lib oracle
 lib: $(LIBOUT)
 
-$(OBJDIR)/%.o: $(CSRC)/%.cu $(CSRC)/bre_internal.cuh $(CSRC)/bre_query_warp.cuh $(CSRC)/bre_surface.cuh include/bre.h
+$(OBJDIR)/%.o: $(CSRC)/%.cu $(CSRC)/bre_internal.cuh $(CSRC)/bre_query_warp.cuh $(CSRC)/bre_query_tile.cuh $(CSRC)/bre_surface.cuh include/bre.h
 	@mkdir -p $(OBJDIR)
 	$(NVCC) $(NVFLAGS) -Xptxas -v -c $< -o $@ 2> $(OBJDIR)/$*.ptxas.log || (cat $(OBJDIR)/$*.ptxas.log; false)
 

@@ -28,6 +28,7 @@ SYMBOLS = [
     "bre_set_triangle_attrs", "bre_set_lights_in_medium", "bre_set_camera", "bre_camera_rays",
     "bre_query_camera_to_film", "bre_last_build_kind",
     "bre_trace_exchange_photons", "bre_alloc_pinned", "bre_free_pinned", "bre_stage_rays", "bre_query_staged_to_film", "bre_save_photons", "bre_load_photons", "bre_film_save", "bre_film_load",
+    "bre_set_ray_grid", "bre_set_tile_sharding",
 ]
 
 
@@ -281,6 +282,12 @@ class Bre:
                      idx.ctypes.data_as(C.POINTER(C.c_uint32)), total, 0)
         self._ck(self.lib.bre_query(self.ctx, n, _fp(o), _fp(d), C.c_float(n_paths_norm), None, C.byref(hd)))
         return out, offs, idx[:total]
+
+    def set_ray_grid(self, width, height):
+        self._ck(self.lib.bre_set_ray_grid(self.ctx, C.c_uint32(int(width)), C.c_uint32(int(height))))
+
+    def set_tile_sharding(self, on=True):
+        self._ck(self.lib.bre_set_tile_sharding(self.ctx, int(on)))
 
     def query_d(self, n, rays_o_ptr, rays_d_ptr, n_paths_norm, out_ptr):
         self._ck(self.lib.bre_query_d(self.ctx, n, C.c_void_p(rays_o_ptr), C.c_void_p(rays_d_ptr),

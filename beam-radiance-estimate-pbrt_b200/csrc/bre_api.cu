@@ -108,7 +108,7 @@ int bre_create(bre_ctx **out, const bre_config *cfg) {
         ctx->n_ranks = cfg->n_ranks > 0 ? cfg->n_ranks : 1;
         ctx->rank = cfg->rank;
         if (cfg->max_leaf_photons > 0) ctx->max_leaf = cfg->max_leaf_photons;
-        if (cfg->tau_steps > 0) ctx->tau_steps = cfg->tau_steps;
+        if (cfg->tau_steps > 0) { ctx->tau_steps = cfg->tau_steps; ctx->tau_auto = false; }
     }
     if (ctx->device < 0 || ctx->device >= nDev || ctx->max_leaf > 16 || ctx->tau_steps > 384 || ctx->rank < 0 ||
         ctx->rank >= ctx->n_ranks) {
@@ -139,6 +139,10 @@ int bre_create(bre_ctx **out, const bre_config *cfg) {
         ctx->gather_aos = !(ga && atoi(ga) == 0);
         const char *tn = getenv("BRE_TRACE_NESTED");
         ctx->trace_nested = tn && atoi(tn) != 0;
+        const char *tp = getenv("BRE_TILE");
+        ctx->tile_path = !(tp && atoi(tp) == 0);
+        const char *kt = getenv("BRE_K5T_BLOCKS");
+        if (kt && atoi(kt) > 0) ctx->k5t_blocks_per_sm = atoi(kt);
         const char *rb = getenv("BRE_RAY_BATCH");
         if (rb && atoll(rb) > 0) ctx->ray_batch_override = (uint32_t)atoll(rb);
         cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, ctx->device);
@@ -162,10 +166,11 @@ int bre_destroy(bre_ctx *ctx) {
                    &ctx->node_lo, &ctx->node_hi, &ctx->node_range, &ctx->parent, &ctx->leaf_lo,
                    &ctx->leaf_hi, &ctx->flags, &ctx->fast, &ctx->scratch, &ctx->rays_o, &ctx->rays_d,
                    &ctx->out_rgb, &ctx->tau, &ctx->hit_counts, &ctx->hit_offsets, &ctx->hit_idx,
-                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->frames, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb, &ctx->entry, &ctx->rays_stage, &ctx->p2p_scratch, &ctx->aos};
+                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->frames, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb, &ctx->entry, &ctx->rays_stage, &ctx->p2p_scratch, &ctx->aos, &ctx->tframes, &ctx->tile_state, &ctx->top_cut};
     for (Buf *b : bufs) if (b->p) cudaFree(b->p);
     if (ctx->lights_d) cudaFree(ctx->lights_d);
     if (ctx->est_host) cudaFreeHost(ctx->est_host);
+    if (ctx->ev_est) cudaEventDestroy(ctx->ev_est);
     if (ctx->copy_stream) {
         cudaStreamSynchronize(ctx->copy_stream);
         cudaEventDestroy(ctx->ev_stage); cudaEventDestroy(ctx->ev_main);
@@ -235,6 +240,15 @@ int bre_set_medium_grid(bre_ctx *ctx, const float sa[3], const float ss[3], floa
     m.density = (const float *)ctx->density.p;
     m.invMaxDensity = 1 / maxDensity;
     memcpy(m.w2m, w2m, 12 * sizeof(float));
+    if (ctx->tau_auto) {
+        // 1.5 table steps per voxel of the longest axis, a multiple of 32 within [64, 128]: a step equal to the
+        // voxel pitch aliases with the trilinear lattice (64 steps through 64^3: 1.3e-3 error of Tr, 96: 1.5e-4;
+        // pinned against the reference's GridDensityMedium::Tr by tests/golden/ref_gridtr.npz)
+        int mx = nx > ny ? nx : ny;
+        if (nz > mx) mx = nz;
+        int st = (3 * mx / 2 + 31) / 32 * 32;
+        ctx->tau_steps = st < 64 ? 64 : (st > 128 ? 128 : st);
+    }
     return BRE_OK;
 }
 
@@ -468,6 +482,19 @@ int bre_query_d(bre_ctx *ctx, uint32_t n, const void *ro, const void *rd, float 
     return run_query(ctx, n, (const float4 *)ro, (const float4 *)rd, nPathsNorm, (float4 *)out);
 }
 
+int bre_set_ray_grid(bre_ctx *ctx, uint32_t width, uint32_t height) {
+    CTX_CHECK();
+    if ((width == 0) != (height == 0)) return set_err(ctx, BRE_ERR_INVALID, "width and height must both be 0 or both be set");
+    ctx->grid_w = width; ctx->grid_h = height;
+    return BRE_OK;
+}
+
+int bre_set_tile_sharding(bre_ctx *ctx, int enabled) {
+    CTX_CHECK();
+    ctx->tile_shard = enabled != 0;
+    return BRE_OK;
+}
+
 int bre_query_to_film(bre_ctx *ctx, uint32_t n, const float *o4, const float *d3, const uint32_t *pix,
                       float nPathsNorm) {
     CTX_CHECK();
@@ -566,8 +593,13 @@ int bre_query_camera_to_film(bre_ctx *ctx, float offx, float offy, float nPathsN
         return set_err(ctx, BRE_ERR_INVALID, "bre_film_create(width*height) has not been called");
     if ((s = camera_rays(ctx, offx, offy)) != BRE_OK) return s;
     if ((s = ensure(ctx, ctx->out_rgb, (size_t)n * 16)) != BRE_OK) return s;
-    if ((s = run_query(ctx, n, (const float4 *)ctx->rays_o.p, (const float4 *)ctx->rays_d.p, nPathsNorm,
-                       (float4 *)ctx->out_rgb.p)) != BRE_OK) return s;
+    // K0's rays are a width x height image by construction: the tile path applies whatever the caller's grid hint says
+    const uint32_t gw = ctx->grid_w, gh = ctx->grid_h;
+    ctx->grid_w = (uint32_t)ctx->camera.width; ctx->grid_h = (uint32_t)ctx->camera.height;
+    s = run_query(ctx, n, (const float4 *)ctx->rays_o.p, (const float4 *)ctx->rays_d.p, nPathsNorm,
+                  (float4 *)ctx->out_rgb.p);
+    ctx->grid_w = gw; ctx->grid_h = gh;
+    if (s != BRE_OK) return s;
     return film_accumulate(ctx, n, nullptr, (const float4 *)ctx->out_rgb.p);
 }
 

@@ -665,6 +665,89 @@ __global__ void __launch_bounds__(256) k_emit_fast(int n, int maxLeaf,
 
 #endif
 
+// ---------------------------------------------------------------- top cut
+// The tile walk of K5 (bre_query_tile.cuh) starts from a CUT through the top of the production tree
+// instead of its root: up to TOP_CUT = 512 (box, ref) entries that together cover every photon,
+// staged into shared memory with one TMA bulk copy per block and tested in one step by the 256
+// threads of a tile -- no ramp-up through ten nearly empty levels, no L2 round trip for the top of
+// the tree.  One block refines the cut breadth-first; when a whole level no longer fits, the
+// entries with the largest surface area are opened first (the reference's HLBVH also treats the top
+// of the tree separately: treelets on the high Morton bits, core/photonbeambvh.cpp:456-493).
+// Layout: cut[2k] = {lo.xyz, ref}, cut[2k+1] = {hi.xyz, 0}; cut[2 * TOP_CUT].x = number of entries.
+constexpr int TOP_CUT_N = TOP_CUT;
+#if !BRE_WIDE
+__global__ void __launch_bounds__(TOP_CUT_N) k_top_cut(const FastNode *__restrict__ fast, int rootRef,
+                                                      float4 *__restrict__ cut) {
+    __shared__ float4 slo[TOP_CUT_N], shi[TOP_CUT_N];
+    __shared__ float sarea[TOP_CUT_N];
+    __shared__ int wsum[TOP_CUT_N / 32];
+    __shared__ int ssize;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) ssize = 0;
+    if (rootRef >= 0 && tid == 0) {
+        const FastNode f = fast[rootRef];
+        slo[0] = make_float4(f.a.x, f.a.y, f.a.z, __int_as_float(f.d.x));
+        shi[0] = make_float4(f.a.w, f.b.x, f.b.y, 0.f);
+        slo[1] = make_float4(f.b.z, f.b.w, f.c.x, __int_as_float(f.d.y));
+        shi[1] = make_float4(f.c.y, f.c.z, f.c.w, 0.f);
+        ssize = 2;
+    }
+    __syncthreads();
+    for (int round = 0; round < 64; ++round) {
+        const int sz = ssize;
+        if (sz >= TOP_CUT_N || sz == 0) break;
+        const bool internal = tid < sz && __float_as_int(slo[tid].w) >= 0;
+        float a = -1.f;
+        if (internal) {
+            const float dx = shi[tid].x - slo[tid].x, dy = shi[tid].y - slo[tid].y, dz = shi[tid].z - slo[tid].z;
+            a = dx * dy + dy * dz + dz * dx;
+            if (!(a >= 0.f)) a = 0.f;
+        }
+        sarea[tid] = a;
+        const int m = __syncthreads_count(internal);
+        if (m == 0) break;
+        const int avail = TOP_CUT_N - sz;
+        bool expand = internal;
+        if (m > avail) {
+            int rank = 0;
+            for (int k = 0; k < sz; ++k) {
+                const float b = sarea[k];
+                rank += (b > a || (b == a && k < tid)) ? 1 : 0;
+            }
+            expand = internal && rank < avail;
+        }
+        // block-wide exclusive prefix of `expand`
+        const unsigned mb = __ballot_sync(0xffffffffu, expand);
+        if (lane == 0) wsum[warp] = __popc(mb);
+        __syncthreads();
+        int pos = __popc(mb & ((1u << lane) - 1u)), tot = 0;
+        for (int w = 0; w < TOP_CUT_N / 32; ++w) {
+            if (w < warp) pos += wsum[w];
+            tot += wsum[w];
+        }
+        if (expand) {
+            const FastNode *fn = fast + __float_as_int(slo[tid].w);
+            const float4 fa = __ldg(&fn->a), fb = __ldg(&fn->b), fc = __ldg(&fn->c);
+            const int4 fd = __ldg(&fn->d);
+            slo[tid] = make_float4(fa.x, fa.y, fa.z, __int_as_float(fd.x));
+            shi[tid] = make_float4(fa.w, fb.x, fb.y, 0.f);
+            slo[sz + pos] = make_float4(fb.z, fb.w, fc.x, __int_as_float(fd.y));
+            shi[sz + pos] = make_float4(fc.y, fc.z, fc.w, 0.f);
+        }
+        __syncthreads();
+        if (tid == 0) ssize = sz + tot;
+        __syncthreads();
+    }
+    const int sz = ssize;
+    if (tid < sz) { cut[2 * tid] = slo[tid]; cut[2 * tid + 1] = shi[tid]; }
+    else {
+        cut[2 * tid] = make_float4(3.0e38f, 3.0e38f, 3.0e38f, __int_as_float(FAST_NONE));
+        cut[2 * tid + 1] = make_float4(-3.0e38f, -3.0e38f, -3.0e38f, 0.f);
+    }
+    if (tid == 0) cut[2 * TOP_CUT_N] = make_float4(__uint_as_float((unsigned)sz), 0.f, 0.f, 0.f);
+}
+#endif
+
 // ---------------------------------------------------------------- host driver
 // production-tree boxes: fat-leaf roots and everything above them, then the 64-byte nodes
 static int launch_refit_emit(bre_ctx *ctx) {
@@ -682,6 +765,14 @@ static int launch_refit_emit(bre_ctx *ctx) {
     k_emit_fast<<<(int)((n + 255) / 256), 256, 0, st>>>(
         (int)n, ctx->max_leaf, (const float4 *)ctx->node_lo.p, (const float4 *)ctx->node_hi.p,
         (const int2 *)ctx->node_range.p, (const float4 *)ctx->s_pos_r.p, (FastNode *)ctx->fast.p);
+#if !BRE_WIDE
+    {
+        int s = ensure(ctx, ctx->top_cut, (size_t)(2 * TOP_CUT_N + 1) * 16);
+        if (s != BRE_OK) return s;
+        const int rootRef = (n <= (uint32_t)ctx->max_leaf) ? -1 : 0;
+        k_top_cut<<<1, TOP_CUT_N, 0, st>>>((const FastNode *)ctx->fast.p, rootRef, (float4 *)ctx->top_cut.p);
+    }
+#endif
     return BRE_OK;
 }
 

@@ -101,6 +101,8 @@ __host__ __device__ __forceinline__ int leaf_ref(uint32_t first, uint32_t count)
     return (int)(0x80000000u | ((count - 1u) << 27) | first);
 }
 #define BRE_MAX_PHOTONS (1u << 27)
+// entries of the top cut of the production tree (k_top_cut in bre_build.cu, staged by TMA in k_traverse_tile)
+constexpr int TOP_CUT = 512;
 
 struct TreeDev {
     uint32_t n;               // photons
@@ -124,6 +126,7 @@ struct Buf {
 struct bre_ctx {
     int device = 0, n_ranks = 1, rank = 0;
     int max_leaf = 8, tau_steps = 64;
+    bool tau_auto = true;                   // bre_config.tau_steps == 0: chosen from the grid in bre_set_medium_grid
     int refit_direct = 16;                  // nodes up to this many photons get their box straight from the photons
     int sm_count = 148;
     uint64_t pair_queue_cap_override = 0;   // BRE_PAIR_QUEUE_CAP (tests force the overflow path)
@@ -162,10 +165,18 @@ struct bre_ctx {
     int root_ref = 0;
     // query scratch
     bre::Buf packet_ctr, pair_queue, heavy, frames;
+    // image-tile path of K5 (bre_query_tile.cuh): ray q = pixel (q % grid_w, q / grid_w) when grid_w * grid_h == n
+    uint32_t grid_w = 0, grid_h = 0;
+    bool tile_path = true;                  // BRE_TILE=0: always the packet walk
+    bool tile_shard = false;                // bre_set_tile_sharding: this rank answers only the tiles bre_tile_owner gives it
+    int k5t_blocks_per_sm = 0;              // BRE_K5T_BLOCKS: cap on resident k_traverse_tile blocks per SM
+    cudaEvent_t ev_est = nullptr;           // recorded after the copy of the queue control words into est_host
+    bre::Buf tframes, tile_state, top_cut;
     // heavy-first packet order fed from one radiance query to the next (bre_query.cu)
     size_t heavy_half = 0;
     uint32_t heavy_rays = 0;
     int heavy_parity = 0;
+    bool heavy_tile = false;                // the heavy lists hold tile indices (tile path) instead of packet indices
     // ray batching of K5 (bre_query.cu launch_query)
     uint32_t ray_batch_override = 0;        // BRE_RAY_BATCH (experiments)
     int k5a_blocks_per_sm = 0;              // BRE_K5A_BLOCKS: cap on resident K5a blocks per SM (0 = what fits)
@@ -174,6 +185,7 @@ struct bre_ctx {
     uint32_t ctr_batches = 0, ctr_batch_rays = 0, ctr_rays = 0;
     unsigned int *est_host = nullptr;       // pinned copy of the last batch's queue control words
     uint32_t est_batches = 0, est_batch_rays = 0, est_n = 0;
+    bool est_tile = false;                  // the estimate was measured on the tile path
     // asynchronous ray staging (bre_stage_rays)
     bre::Buf rays_stage;
     cudaStream_t copy_stream = nullptr;

@@ -215,6 +215,7 @@ __global__ void __launch_bounds__(128) k_tau_table(MediumDev m, uint32_t n,
 }  // namespace bre
 constexpr int QT = 128;
 #include "bre_query_warp.cuh"
+#include "bre_query_tile.cuh"
 namespace bre {
 
 // One block of launch state per ray batch, in ctx->packet_ctr (stride QB_STRIDE bytes):
@@ -254,6 +255,12 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
                         float4 *out, const float *tau, const float2 *span, uint32_t *hitCounts,
                         const uint64_t *hitOffsets, uint32_t *hitIdx, unsigned long long *counters) {
     int s;
+    if (n >= (1u << 30)) return set_err(ctx, BRE_ERR_UNSUPPORTED, "more than 2^30 rays in one query");
+    // ---- image-tile path: the caller declared the rays to be a grid_w x grid_h image (bre_set_ray_grid / K0)
+    const bool tileMode = !BRE_WIDE && ctx->tile_path && ctx->grid_w >= 2 && ctx->grid_h >= 2 &&
+                          (uint64_t)ctx->grid_w * ctx->grid_h == n && ctx->n_built > 0;
+    const uint32_t imgW = tileMode ? ctx->grid_w : 0, imgH = tileMode ? ctx->grid_h : 0;
+    const uint32_t tilesX = tileMode ? (imgW + TILE_W - 1) / TILE_W : 0, tilesY = tileMode ? (imgH + TILE_H - 1) / TILE_H : 0;
     // ---- pair queue capacity: 128 pairs per ray, at least 1M, at most 256M pairs (2 GiB)
     uint64_t want = (uint64_t)n * 128u;
     if (want < (1u << 20)) want = 1u << 20;
@@ -263,10 +270,14 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     if (!ctx->est_host) {
         BRE_CUDA(cudaHostAlloc((void **)&ctx->est_host, EST_MAX_BATCHES * QB_STRIDE, cudaHostAllocDefault));
         memset(ctx->est_host, 0, EST_MAX_BATCHES * QB_STRIDE);
+        BRE_CUDA(cudaEventCreateWithFlags(&ctx->ev_est, cudaEventDisableTiming));
+    } else if (ctx->est_batches) {
+        // the previous launch's copy of its control words into est_host must have landed before it is read
+        BRE_CUDA(cudaEventSynchronize(ctx->ev_est));
     }
     // densest batch of the previous launch (image regions differ: the last batch alone misleads)
-    double est = 128.0;
-    if (ctx->est_batches) {
+    double est = tileMode ? 16.0 : 128.0;
+    if (ctx->est_batches && ctx->est_tile == tileMode) {
         double worst = 0.0;
         for (uint32_t b = 0; b < ctx->est_batches; ++b) {
             const uint32_t r0 = b * ctx->est_batch_rays;
@@ -287,6 +298,12 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     }
     if (ctx->ray_batch_override && ctx->ray_batch_override < n)
         batchRays = (ctx->ray_batch_override + WQ_P - 1) / WQ_P * WQ_P;
+    if (tileMode && batchRays < n) {
+        // a batch is a band of whole tile rows
+        const uint32_t band = imgW * TILE_H;
+        batchRays = batchRays / band * band;
+        if (batchRays == 0) batchRays = band;
+    }
     const uint32_t nBatches = (n + batchRays - 1) / batchRays;
     const bool piped = nBatches > 1;
     const unsigned cap = (unsigned)(piped ? want / 2 : want);
@@ -307,7 +324,18 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     A.out = out; A.tau = tau; A.span = span; A.tauSteps = ctx->tau_steps;
     A.hitCounts = hitCounts; A.hitOffsets = hitOffsets; A.hitIdx = hitIdx;
     A.frames = nullptr;
-    if (ctx->fat_spread > 0.f) {   // one 64-byte frame per packet
+    TileArgs TA{};
+    if (tileMode) {
+        const size_t nT = (size_t)tilesX * tilesY;
+        if ((s = ensure(ctx, ctx->tframes, nT * 16 * TFRAME_V4)) != BRE_OK) return s;
+        if ((s = ensure(ctx, ctx->tile_state, nT)) != BRE_OK) return s;
+        TA.cut = (const float4 *)ctx->top_cut.p;
+        TA.nCut = (ctx->top_cut.p && ctx->n_built > 1) ? 1u : 0u;      // the kernel reads the entry count from the cut's header
+        TA.tframes = (float4 *)ctx->tframes.p;
+        TA.tileState = (unsigned char *)ctx->tile_state.p;
+        TA.imgW = imgW; TA.imgH = imgH; TA.tilesX = tilesX; TA.tilesY = tilesY;
+    }
+    if (ctx->fat_spread > 0.f && !tileMode) {   // one 64-byte frame per packet
         if ((s = ensure(ctx, ctx->frames, ((size_t)n / FAT_P + WQ_P / FAT_P) * 16 * FRAME_V4)) != BRE_OK) return s;
         A.frames = (float4 *)ctx->frames.p;
     }
@@ -322,7 +350,9 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     int cur = 0, prev = 1;
     if (feedback) {
         if ((s = ensure(ctx, ctx->heavy, (size_t)nBatches * 2 * half)) != BRE_OK) return s;
-        if (ctx->heavy_half != half) { ctx->heavy_half = half; ctx->heavy_rays = 0; }   // buffer re-laid out
+        if (ctx->heavy_half != half || ctx->heavy_tile != tileMode) {   // buffer re-laid out / other id space
+            ctx->heavy_half = half; ctx->heavy_tile = tileMode; ctx->heavy_rays = 0;
+        }
         cur = ctx->heavy_parity; prev = cur ^ 1;
         haveIn = ctx->heavy_rays == n;
         ctx->heavy_rays = n;
@@ -333,9 +363,17 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
         BRE_CUDA(cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
         for (int i = 0; i < 4; ++i) BRE_CUDA(cudaEventCreateWithFlags(&ctx->qev[i], cudaEventDisableTiming));
     }
-    int perSM = 0;
+    int perSM = 0, perSMT = 1;
     BRE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k_traverse<MODE, COUNT>, WQ_WARPS * 32, 0));
     if (perSM < 1) perSM = 1;
+    const int shardMod = (tileMode && ctx->tile_shard && ctx->n_ranks > 1) ? ctx->n_ranks : 1;
+    if (tileMode) {
+        BRE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSMT, k_traverse_tile<MODE, COUNT>, TT_THREADS,
+                                                               sizeof(TileSmem)));
+        if (perSMT < 1) perSMT = 1;
+        if (ctx->k5t_blocks_per_sm > 0 && perSMT > ctx->k5t_blocks_per_sm) perSMT = ctx->k5t_blocks_per_sm;
+    } else if (ctx->tile_shard && ctx->n_ranks > 1)
+        return set_err(ctx, BRE_ERR_INVALID, "tile sharding needs a ray grid (bre_set_ray_grid) and the tile path");
     if (ctx->k5a_blocks_per_sm > 0 && perSM > ctx->k5a_blocks_per_sm) perSM = ctx->k5a_blocks_per_sm;
     // K5b grid.  The leaf kernels walk the pair queue, whose length is only known on the device, in
     // runs of 64 pairs.  With a static stride the cost of a warp's runs varies with their hits and the
@@ -378,9 +416,24 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
         unsigned blocksA = (unsigned)(ctx->sm_count * perSM);
         const unsigned need = ((nb + WQ_P - 1) / WQ_P + WQ_WARPS - 1) / WQ_WARPS;
         if (blocksA > need) blocksA = need;
+        if (tileMode) {
+            // K5a': one block per image tile of this band (absolute ray indices: the unshifted arguments of batch 0)
+            const uint32_t tile0 = (r0 / imgW / TILE_H) * tilesX;
+            const uint32_t nT = ((nb / imgW + TILE_H - 1) / TILE_H) * tilesX;
+            unsigned blocksT = (unsigned)(ctx->sm_count * perSMT);
+            if (blocksT > (nT + TT_WARPS - 1) / TT_WARPS) blocksT = (nT + TT_WARPS - 1) / TT_WARPS;
+            const LeafArgs *Ag0 = (const LeafArgs *)(blocks + QB_ARGS);
+            k_traverse_tile<MODE, COUNT><<<blocksT, TT_THREADS, sizeof(TileSmem), ctx->stream>>>(
+                A, Ag0, TA, tile0, nT, queue, cap, ctl, heavyIn, nHeavyIn, heavyFlagIn, heavyOut, heavyFlagOut,
+                nHeavyOut, heavyCap, shardMod, ctx->rank, counters);
+            // rays of tiles flagged incoherent: per-ray walk (returns at once when there is none)
+            k_traverse<MODE, COUNT><<<blocksA, WQ_WARPS * 32, 0, ctx->stream>>>(
+                Ab, Ag, nb, queue, cap, ctl, nullptr, heavyCnt, nullptr, nullptr, nullptr, heavyCnt, 0u, 0.f,
+                TA.tileState, imgW, tilesX, r0, counters);
+        } else
         k_traverse<MODE, COUNT><<<blocksA, WQ_WARPS * 32, 0, ctx->stream>>>(
             Ab, Ag, nb, queue, cap, ctl, heavyIn, nHeavyIn, heavyFlagIn, heavyOut, heavyFlagOut, nHeavyOut,
-            heavyCap, ctx->fat_spread, counters);
+            heavyCap, ctx->fat_spread, nullptr, 0u, 0u, 0u, counters);
         cudaStream_t sb = ctx->stream;
         if (piped) {
             BRE_CUDA(cudaEventRecord(ctx->qev[b & 1u], ctx->stream));
@@ -392,13 +445,19 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
             const uint32_t nCopy = nBatches < EST_MAX_BATCHES ? nBatches : EST_MAX_BATCHES;
             BRE_CUDA(cudaMemcpyAsync(ctx->est_host, blocks, (size_t)nCopy * QB_STRIDE, cudaMemcpyDeviceToHost,
                                      ctx->stream));
-            ctx->est_batches = nCopy; ctx->est_batch_rays = batchRays; ctx->est_n = n;
+            ctx->est_batches = nCopy; ctx->est_batch_rays = batchRays; ctx->est_n = n; ctx->est_tile = tileMode;
+            BRE_CUDA(cudaEventRecord(ctx->ev_est, ctx->stream));
             if (ctx->timing) {
                 cudaEventRecord(ctx->ev[PH_QUERY_A][1], ctx->stream); ctx->ev_valid[PH_QUERY_A] = true;
                 cudaEventRecord(ctx->ev[PH_QUERY_B][0], ctx->stream);
             }
         }
-        // both leaf kernels scan the queue; each leaves at once if K5a emitted no pair of its kind
+        // the leaf kernels scan the queue; each leaves at once if K5a emitted no pair of its kind
+        if (tileMode) {
+            if (ctx->max_leaf <= 4) k_leaf_tile<MODE, COUNT, 4><<<gb, LP_WARPS * 32, 0, sb>>>(A, TA.tframes, imgW, queue, cap, ctl, counters);
+            else if (ctx->max_leaf <= 8) k_leaf_tile<MODE, COUNT, 8><<<gb, LP_WARPS * 32, 0, sb>>>(A, TA.tframes, imgW, queue, cap, ctl, counters);
+            else k_leaf_tile<MODE, COUNT, 16><<<gb, LP_WARPS * 32, 0, sb>>>(A, TA.tframes, imgW, queue, cap, ctl, counters);
+        }
         if (ctx->max_leaf <= 4) {
             k_leaf_fat<MODE, COUNT, 4><<<gb, LP_WARPS * 32, 0, sb>>>(Ab, queue, cap, ctl, counters);
             k_leaf_pairs<MODE, COUNT, 4><<<gb, LP_WARPS * 32, 0, sb>>>(Ab, queue, cap, ctl, counters);

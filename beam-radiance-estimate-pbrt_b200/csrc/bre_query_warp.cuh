@@ -65,8 +65,9 @@ constexpr unsigned HEAVY_STEPS_FAT = BRE_HEAVY_FAT;   // same for a coherent pac
 constexpr unsigned HEAVY_CAP = 65536;   // heavy packets remembered per launch
 
 // queueCtl words (zeroed before every launch)
-enum { QC_PAIR_TAIL = 0, QC_PACKET = 1, QC_INPLACE = 2, QC_EMITTED = 3, QC_KINDS = 4, QC_RUN_THIN = 5, QC_RUN_FAT = 6, QC_WORDS = 8 };
-enum { KIND_THIN = 1u, KIND_FAT = 2u };   // QC_KINDS bits: which kinds of pair K5a put into the queue
+enum { QC_PAIR_TAIL = 0, QC_PACKET = 1, QC_INPLACE = 2, QC_EMITTED = 3, QC_KINDS = 4, QC_RUN_THIN = 5, QC_RUN_FAT = 6,
+       QC_RUN_TILE = 7, QC_NINCOH = 8, QC_TILE = 9, QC_WORDS = 16 };
+enum { KIND_THIN = 1u, KIND_FAT = 2u, KIND_TILE = 4u };   // QC_KINDS bits: which kinds of pair K5a put into the queue
 
 struct __align__(16) WarpSmem {
     int nref[WQ_NCAP];
@@ -394,8 +395,11 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
     const unsigned int *__restrict__ heavyFlagIn, unsigned int *__restrict__ heavyOut,
     unsigned int *__restrict__ heavyFlagOut, unsigned int *__restrict__ nHeavyOut,
     unsigned int heavyCap, float fatSpread,
+    const unsigned char *__restrict__ tileState, uint32_t imgW, uint32_t tilesX, uint32_t rayOffset,
     unsigned long long *__restrict__ counters) {
     __shared__ WarpSmem smemAll[WQ_WARPS];
+    // tile mode (bre_query_tile.cuh): only the rays of tiles k_traverse_tile flagged incoherent are walked here
+    if (tileState && ld_volatile_u32(queueCtl + QC_NINCOH) == 0u) return;
     WarpSmem &sm = smemAll[threadIdx.x >> 5];
     const TreeDev &t = A.t;
     const unsigned lane = threadIdx.x & 31u;
@@ -442,7 +446,12 @@ __global__ void __launch_bounds__(WQ_WARPS * 32) k_traverse(
             r = rayf_setup(o, d, t.abs_max);
             rayf_store(sm.ray[lane], r);
             live = t.n > 0 && r.tMax > 0.f;
+            if (tileState) {
+                const uint32_t qa = rayOffset + base + lane;
+                live = live && tileState[(qa / imgW / 16u) * tilesX + (qa % imgW) / 16u] != 0;
+            }
         }
+        if (tileState && !__any_sync(FULL, live)) continue;
         bool fat = false;
         bool grpLive = false;      // my group takes part in the fat walk
         if (np == WQ_P && fatSpread > 0.f && t.n > 0) {
@@ -805,7 +814,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, 4) k_leaf_pairs(LeafArgs A,
         if (run + 32 + lane < total) pr1 = __ldg(queue + run + 32 + lane);
         // pairs of coherent packets (PAIR_FAT) belong to k_leaf_fat; a run is almost always all of
         // one kind (a K5a warp fills its chunks packet by packet)
-        if (!__any_sync(FULL, !(pr0.x & PAIR_FAT) || !(pr1.x & PAIR_FAT))) continue;
+        if (!__any_sync(FULL, !(pr0.x & 0xc0000000u) || !(pr1.x & 0xc0000000u))) continue;   // (bit 30: tile pairs, k_leaf_tile)
 #pragma unroll 1
         for (unsigned g0 = 0; g0 < LP_RUN / G; g0 += U) {
             // ---- issue every load of U pair-groups before the first use
@@ -821,7 +830,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, 4) k_leaf_pairs(LeafArgs A,
                 q[u] = qx;
                 first[u] = qy & 0x07ffffffu;
                 const uint32_t cnt = ((qy >> 27) & 15u) + 1u;
-                on[u] = !(qx & PAIR_FAT) && j < cnt;      // PAIR_NONE has the bit set too
+                on[u] = !(qx & 0xc0000000u) && j < cnt;   // PAIR_NONE has the bits set too
                 if (on[u]) {
                     p[u] = __ldg(A.t.s_pos_r + first[u] + j);
                     if (RAYPF) { o[u] = __ldg(A.ro + qx); d[u] = __ldg(A.rd + qx); }

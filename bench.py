@@ -214,6 +214,8 @@ def run_ours(args):
     out_d = torch.empty((nq, 4), dtype=torch.float32, device="cuda")
     ctx.film_create(nq)
     ctx.set_timing(True)
+    if not args.no_tile:
+        ctx.set_ray_grid(W, H)          # the rays are a W x H image: K5 walks the LBVH once per 16x16 tile
     stream = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", local))
 
     def photon_pass():
@@ -469,6 +471,7 @@ def main():
     ap.add_argument("--leaf", type=int, default=0)
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"])
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-tile", action="store_true", help="K5 packet walk instead of the image-tile walk (A/B)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--ref-rays", type=int, default=65536)
     args = ap.parse_args()

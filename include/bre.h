@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define BRE_ABI_VERSION 2
+#define BRE_ABI_VERSION 3
 
 typedef enum {
     BRE_OK = 0,
@@ -47,7 +47,8 @@ typedef struct {
     int rank;
     const void *nccl_unique_id; /* 128-byte ncclUniqueId shared by all ranks, or NULL when n_ranks==1 */
     int max_leaf_photons;      /* photons per LBVH leaf on the fast path, 1..16; 0 = default (8) */
-    int tau_steps;             /* optical-depth table steps per ray for grid media, <= 384; 0 = default (64) */
+    int tau_steps;             /* optical-depth table steps per ray for grid media, <= 384; 0 = from the grid:
+                                  1.5 steps per voxel of the longest axis, a multiple of 32 in [64, 128] */
 } bre_config;
 
 typedef struct {
@@ -214,6 +215,18 @@ int bre_query_to_film(bre_ctx *ctx, uint32_t n_rays, const float *o_xyz_tmax, co
  * bre_query_staged_to_film. */
 int bre_stage_rays(bre_ctx *ctx, uint32_t n_rays, const float *o_xyz_tmax, const float *d_xyz);
 int bre_query_staged_to_film(bre_ctx *ctx, const uint32_t *pixel_idx, float n_paths_norm);
+/* Ray layout hint for every query entry point: when width * height == n_rays, ray q is pixel
+ * (q % width, q / width) of an image, the way the reference's camera pass visits them tile by tile
+ * (16x16 pixels, integrators/photonbeam.cpp:345-347,444-477).  The query then walks the photon LBVH
+ * once per 16x16 tile with the tile's frustum and tests each photon only against the pixels its disk
+ * projects onto (exact predicate per candidate: hit sets do not change).  Tiles whose rays are not a
+ * near-regular fan from one point fall back to the per-ray walk.  0, 0 removes the hint.
+ * bre_query_camera_to_film always uses its camera's own width x height. */
+int bre_set_ray_grid(bre_ctx *ctx, uint32_t width, uint32_t height);
+/* Multi-GPU camera pass: when enabled on a context with n_ranks > 1, a query over a ray grid answers
+ * only the 16x16 tiles bre_tile_owner() gives to this rank (the other pixels' radiance stays 0);
+ * bre_film_gather() then assembles the image on rank 0. */
+int bre_set_tile_sharding(bre_ctx *ctx, int enabled);
 /* Counting pass on the canonical tree for the same rays (fills V,T,H,bytes) plus the
  * production kernel's own counters. */
 int bre_count(bre_ctx *ctx, uint32_t n_rays, const float *o_xyz_tmax, const float *d_xyz);

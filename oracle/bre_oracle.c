@@ -6,6 +6,7 @@
  * /root/reference/src/.
  */
 #include "bre_oracle.h"
+#define ORC_TAU_STEPS_MAX 384
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
@@ -128,6 +129,19 @@ void orc_medium_grid(orc_medium *m, const float sa[3], const float ss[3], float 
     for (long i = 0; i < (long)nx * ny * nz; ++i) maxDensity = fmaxf_(maxDensity, density[i]);
     m->invMaxDensity = 1 / maxDensity;
     memcpy(m->w2m, w2m, sizeof(float) * 16);
+    m->tau_steps = orc_tau_steps_auto(nx, ny, nz);
+}
+/* Steps of the per-ray optical-depth table (the rule libbre.so applies when bre_config.tau_steps == 0):
+ * 1.5 table steps per voxel of the longest grid axis, rounded up to a multiple of 32, within [64, 128].
+ * A step that EQUALS the voxel pitch aliases with the lattice of the trilinear interpolant (64 steps
+ * through a 64^3 grid: 1.3e-3 relative error of Tr; 96 steps: 1.5e-4, tests/test_oracle_golden.py). */
+int orc_tau_steps_auto(int nx, int ny, int nz) {
+    int m = nx > ny ? nx : ny;
+    if (nz > m) m = nz;
+    int s = (3 * m / 2 + 31) / 32 * 32;
+    if (s < 64) s = 64;
+    if (s > 128) s = 128;
+    return s;
 }
 static inline float grid_D(const orc_medium *m, int x, int y, int z) { /* grid.h:78-82 */
     if (x < 0 || y < 0 || z < 0 || x >= m->nx || y >= m->ny || z >= m->nz) return 0;
@@ -216,6 +230,16 @@ static void grid_tr_from_table(const orc_medium *m, const float *tau, int nSteps
         }
     }
     for (int k = 0; k < 3; ++k) tr[k] = expf(-m->sigma_t[k] * od);
+}
+
+/* Tr(o -> o + t d) of a grid medium exactly as the query evaluates it: nSteps-step table over the
+ * ray's overlap with the medium box, linear interpolation at t. */
+void orc_grid_tr_table(const orc_medium *m, const float o[3], const float d[3], float tMax, float t,
+                       int nSteps, float tr[3]) {
+    float tau[ORC_TAU_STEPS_MAX + 1], t0, t1;
+    if (nSteps < 1 || nSteps > ORC_TAU_STEPS_MAX) nSteps = 64;
+    orc_grid_tau_table(m, o, d, tMax, nSteps, tau, &t0, &t1);
+    grid_tr_from_table(m, tau, nSteps, t0, t1, t, tr);
 }
 
 /* ------------------------------------------------------------------ Morton */
@@ -369,21 +393,22 @@ static inline void accumulate_hit(const orc_photons *ph, uint32_t i, const float
     (void)t;
 }
 
-#define ORC_TAU_STEPS 64
 
 typedef struct {
     const orc_medium *m;
-    float tau[ORC_TAU_STEPS + 1];
+    float tau[ORC_TAU_STEPS_MAX + 1];
+    int steps;
     float t0, t1;
 } ray_tr_state;
 static void ray_tr_init(ray_tr_state *s, const orc_medium *m, const float o[3], const float d[3],
                         float tMax) {
     s->m = m;
-    if (m->kind == 1) orc_grid_tau_table(m, o, d, tMax, ORC_TAU_STEPS, s->tau, &s->t0, &s->t1);
+    s->steps = (m->tau_steps >= 1 && m->tau_steps <= ORC_TAU_STEPS_MAX) ? m->tau_steps : 64;
+    if (m->kind == 1) orc_grid_tau_table(m, o, d, tMax, s->steps, s->tau, &s->t0, &s->t1);
 }
 static void ray_tr_eval(const ray_tr_state *s, float t, float tr[3]) {
     if (s->m->kind == 0) orc_homogeneous_tr(s->m, t, tr);
-    else grid_tr_from_table(s->m, s->tau, ORC_TAU_STEPS, s->t0, s->t1, t, tr);
+    else grid_tr_from_table(s->m, s->tau, s->steps, s->t0, s->t1, t, tr);
 }
 
 /* slab test of geometry.h:1410-1438 with per-ray padded origins (DESIGN.md "conservative cull") */

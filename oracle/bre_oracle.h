@@ -49,6 +49,7 @@ typedef struct {
     const float *density;  /* nx*ny*nz, x fastest */
     float invMaxDensity;
     float w2m[16];         /* world -> medium, row major 4x4 (affine) */
+    int tau_steps;         /* steps of the per-ray optical-depth table (orc_medium_grid sets orc_tau_steps_auto) */
 } orc_medium;
 void orc_medium_homogeneous(orc_medium *m, const float sa[3], const float ss[3], float g);
 void orc_medium_grid(orc_medium *m, const float sa[3], const float ss[3], float g, int nx, int ny,
@@ -63,6 +64,9 @@ void orc_homogeneous_tr(const orc_medium *m, float t, float tr[3]);
  * tau[0]=0) and the overlap interval. Returns 0 if the ray misses the box. */
 int orc_grid_tau_table(const orc_medium *m, const float o[3], const float d[3], float tMax,
                        int nSteps, float *tau, float *t0, float *t1);
+int orc_tau_steps_auto(int nx, int ny, int nz);
+void orc_grid_tr_table(const orc_medium *m, const float o[3], const float d[3], float tMax, float t,
+                       int nSteps, float tr[3]);
 
 /* ---- photon map container ---- */
 typedef struct {

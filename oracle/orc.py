@@ -20,7 +20,7 @@ class Medium(C.Structure):
     _fields_ = [("kind", C.c_int), ("sigma_a", C.c_float * 3), ("sigma_s", C.c_float * 3),
                 ("sigma_t", C.c_float * 3), ("g", C.c_float), ("nx", C.c_int), ("ny", C.c_int),
                 ("nz", C.c_int), ("density", C.POINTER(C.c_float)), ("invMaxDensity", C.c_float),
-                ("w2m", C.c_float * 16)]
+                ("w2m", C.c_float * 16), ("tau_steps", C.c_int)]
 
 
 class Photons(C.Structure):
@@ -101,6 +101,10 @@ class Oracle:
         nz, ny, nx = d.shape
         self._keep += [d]
         self.lib.orc_medium_grid(C.byref(self.medium), _fp(sa), _fp(ss), C.c_float(g), nx, ny, nz, _fp(d), _fp(w))
+
+    def set_tau_steps(self, steps):
+        """Steps of the per-ray optical-depth table (default: orc_tau_steps_auto of the grid, like libbre.so)."""
+        self.medium.tau_steps = int(steps)
 
     # ---- photons / tree
     def set_photons(self, pos, power, dirs, radius):

@@ -62,6 +62,8 @@
 #include "transform.h"
 
 #include "ref_access.h"
+#include <atomic>
+#include <thread>
 
 using namespace pbrt;
 
@@ -741,6 +743,83 @@ void surfaces(const char *path, uint64_t first, uint64_t nPaths, int maxDepth, i
             (unsigned long long)nPaths, ro.size() / 4);
 }
 
+// ---------------------------------------------------------------- mode: gridtr
+// Pins the deterministic optical-depth table of the product (K6) at the grid sizes the benchmarks run:
+// for rays {o, d, t} read from <rays.bin> (8 floats per ray: o, d, t, 0) through the density grid read
+// from <density.bin> (nx*ny*nz floats, x fastest) it stores
+//   Tr_mean / Tr_stderr   nSamples evaluations of the reference's GridDensityMedium::Tr (media/grid.cpp:89-121,
+//                         ratio tracking + Russian roulette) of Ray(o, d, tMax = t)
+//   tau_fine              the optical depth sum Density(p) dt over 65536 midpoint steps of the ray's overlap with
+//                         the medium box, Density = the reference's own trilinear lookup (media/grid.cpp:45-60),
+//                         accumulated in double: what ratio tracking estimates without bias
+void gridtr(const char *path, const char *densPath, int nx, int ny, int nz, const char *raysPath, int nSamples,
+            float sigA, float sigS, float aspect, float boxLoX) {
+    std::vector<float> dens((size_t)nx * ny * nz);
+    {
+        FILE *f = fopen(densPath, "rb");
+        if (!f || fread(dens.data(), 4, dens.size(), f) != dens.size()) { perror(densPath); exit(1); }
+        fclose(f);
+    }
+    std::vector<float> rays;
+    {
+        FILE *f = fopen(raysPath, "rb");
+        if (!f) { perror(raysPath); exit(1); }
+        float v[8];
+        while (fread(v, 4, 8, f) == 8) rays.insert(rays.end(), v, v + 8);
+        fclose(f);
+    }
+    const size_t nRays = rays.size() / 8;
+    // medium box = [boxLoX, boxLoX + aspect] x [0,1] x [0,1]   (bench.py world_to_medium)
+    Transform m2w = Translate(Vector3f(boxLoX, 0.f, 0.f)) * Scale(aspect, 1.f, 1.f);
+    Transform w2m = Inverse(m2w);
+    GridDensityMedium med(Spectrum(sigA), Spectrum(sigS), 0.3f, nx, ny, nz, m2w, dens.data());
+    std::vector<float> trMean(nRays), trErr(nRays), tauFine(nRays), w2mf;
+    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) w2mf.push_back(w2m.GetMatrix().m[i][j]);
+    std::vector<std::thread> pool;
+    std::atomic<size_t> next(0);
+    const unsigned nThreads = std::max(1u, std::thread::hardware_concurrency());
+    for (unsigned tIdx = 0; tIdx < nThreads; ++tIdx)
+        pool.emplace_back([&]() {
+            for (size_t i = next++; i < nRays; i = next++) {
+                const float *v = &rays[8 * i];
+                Point3f o(v[0], v[1], v[2]);
+                Vector3f dir(v[3], v[4], v[5]);
+                const float t = v[6];
+                double sum = 0, sum2 = 0;
+                for (int k = 0; k < nSamples; ++k) {
+                    StreamSampler smp(1000000007ull * (i + 1) + (uint64_t)k);
+                    Float tr = med.Tr(Ray(o, dir, t), smp)[0];
+                    sum += tr; sum2 += (double)tr * tr;
+                }
+                const double mean = sum / nSamples, var = std::max(0.0, sum2 / nSamples - mean * mean);
+                trMean[i] = (float)mean; trErr[i] = (float)std::sqrt(var / nSamples);
+                // fine integral of the reference's Density() over the overlap with the unit cube in medium space
+                Ray rm = w2m(Ray(o, dir, t));
+                Float t0, t1;
+                double tau = 0;
+                if (Bounds3f(Point3f(0, 0, 0), Point3f(1, 1, 1)).IntersectP(rm, &t0, &t1)) {
+                    const int N = 65536;
+                    const double dt = ((double)t1 - (double)t0) / N;
+                    for (int k = 0; k < N; ++k) {
+                        const double tt = (double)t0 + (k + 0.5) * dt;
+                        Point3f pm((Float)(rm.o.x + rm.d.x * tt), (Float)(rm.o.y + rm.d.y * tt), (Float)(rm.o.z + rm.d.z * tt));
+                        tau += (double)med.Density(pm) * dt;
+                    }
+                }
+                tauFine[i] = (float)tau;
+            }
+        });
+    for (auto &th : pool) th.join();
+    BinWriter bw(path);
+    bw.u4("dims", {(uint32_t)nx, (uint32_t)ny, (uint32_t)nz});
+    bw.f4("sigma", {sigA, sigS});
+    bw.f4("w2m", w2mf);
+    bw.f4("rays", rays);
+    bw.f4("Tr_mean", trMean); bw.f4("Tr_stderr", trErr); bw.f4("tau_fine", tauFine);
+    bw.u4("nSamples", {(uint32_t)nSamples});
+    fprintf(stderr, "gridtr: %zu rays, %d samples each, grid %dx%dx%d\n", nRays, nSamples, nx, ny, nz);
+}
+
 }  // namespace
 
 int main(int argc, char **argv) {
@@ -759,7 +838,13 @@ int main(int argc, char **argv) {
         surfaces(argv[2], strtoull(argv[3], 0, 10), strtoull(argv[4], 0, 10), atoi(argv[5]), atoi(argv[6]), atoi(argv[7]));
         return 0;
     }
+    if (argc >= 13 && !strcmp(argv[1], "gridtr")) {
+        gridtr(argv[2], argv[3], atoi(argv[4]), atoi(argv[5]), atoi(argv[6]), argv[7], atoi(argv[8]), (float)atof(argv[9]),
+               (float)atof(argv[10]), (float)atof(argv[11]), (float)atof(argv[12]));
+        return 0;
+    }
     fprintf(stderr, "usage: ref_harness primitives out.json | fogbox out.bin nPhotons res radius [keepFirst] | "
-                    "trace out.bin homogeneous|grid first nPaths maxDepth | surfaces out.bin first nPaths maxDepth resX resY\n");
+                    "trace out.bin homogeneous|grid first nPaths maxDepth | surfaces out.bin first nPaths maxDepth resX resY | "
+                    "gridtr out.bin density.bin nx ny nz rays.bin nSamples sigma_a sigma_s aspect boxLoX\n");
     return 2;
 }

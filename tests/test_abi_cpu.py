@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol(bre):
     lib = bre.load_library()
     missing = [s for s in header_symbols() if not hasattr(lib, s)]
     assert not missing, missing
-    assert lib.bre_abi_version() == 2
+    assert lib.bre_abi_version() == 3
 
 
 def test_no_cpu_fallback(bre):
