@@ -141,6 +141,8 @@ int bre_create(bre_ctx **out, const bre_config *cfg) {
         ctx->trace_nested = tn && atoi(tn) != 0;
         const char *tp = getenv("BRE_TILE");
         ctx->tile_path = !(tp && atoi(tp) == 0);
+        const char *wq = getenv("BRE_TILE_WQ_CAP");
+        if (wq && atoll(wq) > 0) ctx->tile_wq_cap_override = (uint64_t)atoll(wq);
         const char *kt = getenv("BRE_K5T_BLOCKS");
         if (kt && atoi(kt) > 0) ctx->k5t_blocks_per_sm = atoi(kt);
         const char *rb = getenv("BRE_RAY_BATCH");
@@ -166,7 +168,7 @@ int bre_destroy(bre_ctx *ctx) {
                    &ctx->node_lo, &ctx->node_hi, &ctx->node_range, &ctx->parent, &ctx->leaf_lo,
                    &ctx->leaf_hi, &ctx->flags, &ctx->fast, &ctx->scratch, &ctx->rays_o, &ctx->rays_d,
                    &ctx->out_rgb, &ctx->tau, &ctx->hit_counts, &ctx->hit_offsets, &ctx->hit_idx,
-                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->frames, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb, &ctx->entry, &ctx->rays_stage, &ctx->p2p_scratch, &ctx->aos, &ctx->tframes, &ctx->tile_state, &ctx->top_cut};
+                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->frames, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb, &ctx->entry, &ctx->rays_stage, &ctx->p2p_scratch, &ctx->aos, &ctx->tframes, &ctx->tile_state, &ctx->top_cut, &ctx->tile_wq};
     for (Buf *b : bufs) if (b->p) cudaFree(b->p);
     if (ctx->lights_d) cudaFree(ctx->lights_d);
     if (ctx->est_host) cudaFreeHost(ctx->est_host);

@@ -325,6 +325,7 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     A.hitCounts = hitCounts; A.hitOffsets = hitOffsets; A.hitIdx = hitIdx;
     A.frames = nullptr;
     TileArgs TA{};
+    unsigned wqCap = 0;
     if (tileMode) {
         const size_t nT = (size_t)tilesX * tilesY;
         if ((s = ensure(ctx, ctx->tframes, nT * 16 * TFRAME_V4)) != BRE_OK) return s;
@@ -334,6 +335,18 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
         TA.tframes = (float4 *)ctx->tframes.p;
         TA.tileState = (unsigned char *)ctx->tile_state.p;
         TA.imgW = imgW; TA.imgH = imgH; TA.tilesX = tilesX; TA.tilesY = tilesY;
+        // global work queue of the tile walk: 4 items per photon (frontier of a breadth-first sweep; more is
+        // walked depth-first by the producer).  Slots are EMPTY between launches: consumers reset them.
+        uint64_t wc = (uint64_t)ctx->n_built * 4u;
+        if (wc < (1u << 20)) wc = 1u << 20;
+        if (wc > 0xfffffff0ull - 64) wc = 0xfffffff0ull - 64;
+        if (ctx->tile_wq_cap_override) wc = ctx->tile_wq_cap_override;
+        if (ctx->tile_wq.cap < wc * 8 || ctx->tile_wq_items != wc) {
+            if ((s = ensure(ctx, ctx->tile_wq, (size_t)wc * 8)) != BRE_OK) return s;
+            BRE_CUDA(cudaMemsetAsync(ctx->tile_wq.p, 0xff, ctx->tile_wq.cap, ctx->stream));
+            ctx->tile_wq_items = wc;
+        }
+        wqCap = (unsigned)wc;
     }
     if (ctx->fat_spread > 0.f && !tileMode) {   // one 64-byte frame per packet
         if ((s = ensure(ctx, ctx->frames, ((size_t)n / FAT_P + WQ_P / FAT_P) * 16 * FRAME_V4)) != BRE_OK) return s;
@@ -368,7 +381,7 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     if (perSM < 1) perSM = 1;
     const int shardMod = (tileMode && ctx->tile_shard && ctx->n_ranks > 1) ? ctx->n_ranks : 1;
     if (tileMode) {
-        BRE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSMT, k_traverse_tile<MODE, COUNT>, TT_THREADS,
+        BRE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSMT, k_tile_walk<MODE, COUNT>, TT_THREADS,
                                                                sizeof(TileSmem)));
         if (perSMT < 1) perSMT = 1;
         if (ctx->k5t_blocks_per_sm > 0 && perSMT > ctx->k5t_blocks_per_sm) perSMT = ctx->k5t_blocks_per_sm;
@@ -420,11 +433,12 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
             // K5a': one block per image tile of this band (absolute ray indices: the unshifted arguments of batch 0)
             const uint32_t tile0 = (r0 / imgW / TILE_H) * tilesX;
             const uint32_t nT = ((nb / imgW + TILE_H - 1) / TILE_H) * tilesX;
+            const LeafArgs *Ag0 = (const LeafArgs *)(blocks + QB_ARGS);
+            WalkQueue WQ{(uint2 *)ctx->tile_wq.p, wqCap, ctl + QC_WQ_HEAD};
             unsigned blocksT = (unsigned)(ctx->sm_count * perSMT);
             if (blocksT > (nT + TT_WARPS - 1) / TT_WARPS) blocksT = (nT + TT_WARPS - 1) / TT_WARPS;
-            const LeafArgs *Ag0 = (const LeafArgs *)(blocks + QB_ARGS);
-            k_traverse_tile<MODE, COUNT><<<blocksT, TT_THREADS, sizeof(TileSmem), ctx->stream>>>(
-                A, Ag0, TA, tile0, nT, queue, cap, ctl, heavyIn, nHeavyIn, heavyFlagIn, heavyOut, heavyFlagOut,
+            k_tile_walk<MODE, COUNT><<<blocksT, TT_THREADS, sizeof(TileSmem), ctx->stream>>>(
+                A, Ag0, TA, WQ, tile0, nT, queue, cap, ctl, heavyIn, nHeavyIn, heavyFlagIn, heavyOut, heavyFlagOut,
                 nHeavyOut, heavyCap, shardMod, ctx->rank, counters);
             // rays of tiles flagged incoherent: per-ray walk (returns at once when there is none)
             k_traverse<MODE, COUNT><<<blocksA, WQ_WARPS * 32, 0, ctx->stream>>>(

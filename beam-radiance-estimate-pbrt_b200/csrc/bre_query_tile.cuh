@@ -5,17 +5,16 @@
 // (bre_set_ray_grid, or the K0 camera path) the rays of a tile leave (nearly) one point through a
 // (nearly) regular grid of directions, and the query is organised around that:
 //
-//  K5a' k_traverse_tile  one BLOCK per tile.  Thread (i, j) loads ray (i, j); the block fits an
-//                        orthonormal frame (u, v, n) to the tile (u = central direction, v = along
-//                        image rows), maps every ray to gnomonic coordinates (s, t) = (d.v, d.n)/(d.u),
-//                        fits the affine model (s, t) = (s0, t0) + i (As, At) + j (Bs, Bt) through
-//                        three corner rays and measures how far the real rays deviate from it (dev).
-//                        The tile's rays lie inside the pyramid s in [sLo, sHi], t in [tLo, tHi],
-//                        0 < depth <= tFar: the block walks the production LBVH with that frustum
-//                        (six "max corner" plane tests per box, up to 256 nodes per step from a
-//                        shared-memory stack; the first step starts from the TOP CUT of the tree,
-//                        staged into shared memory with one TMA bulk copy per block) and emits
-//                        (tile, leaf) pairs into the pair queue.
+//  K5a' k_tile_setup      one WARP per tile fits an orthonormal frame (u, v, n) to the tile (u = central
+//                        direction, v = along image rows), maps every ray to gnomonic coordinates
+//                        (s, t) = (d.v, d.n)/(d.u), fits the affine model (s, t) = (s0, t0) + i (As, At)
+//                        + j (Bs, Bt) through three corner rays and measures how far the real rays
+//                        deviate from it (dev).  The tile's rays lie inside the pyramid s in [sLo, sHi],
+//                        t in [tLo, tHi], 0 < depth <= tFar: six "max corner" plane tests per box.  The
+//                        TOP CUT of the production LBVH (<= 512 boxes, staged into shared memory with
+//                        one TMA bulk copy per block) is tested first.
+//       k_tile_walk      then sweeps the tree below the cut breadth-first through ONE global queue of
+//                        (tile, node) items and emits (tile, leaf) pairs into the pair queue.
 //  K5b' k_leaf_tile      one photon per lane: the photon is projected into the tile's pixel grid;
 //                        a true hit of ray (i, j) implies |(s_ij, t_ij) - (sp, tp)| <= rho with
 //                        rho = (r / z) k_phi + slack (derivation below), so only the pixels of the
@@ -47,7 +46,6 @@ constexpr int TT_WARPS = TT_THREADS / 32;
 constexpr unsigned PAIR_TILE = 0x40000000u;      // pair.x bit (with bit 31 clear): the pair stands for all rays of tile (pair.x & TILE_MASK)
 constexpr unsigned TILE_MASK = 0x3fffffffu;
 constexpr int TFRAME_V4 = 14;                    // float4 per tile frame: 8 for k_leaf_tile + the 6 frustum planes
-constexpr unsigned HEAVY_STEPS_TILE = 24;        // a tile walk this long is claimed first by the next launch
 // tile state bytes
 enum { TS_TILE = 0, TS_INCOHERENT = 1 };
 
@@ -132,18 +130,35 @@ __device__ __noinline__ void process_tile_pair_inplace(const LeafArgs *Ag, uint3
         }
 }
 
-// Shared memory of one k_traverse_tile block: TT_WARPS tile walks in flight, one per warp.
+// ---------------------------------------------------------------- K5a'
+// Photon maps are extremely uneven on the screen (smoke10m_1080p: the tile that looks into the point
+// light holds 284 000 photons, 230x the mean; 8 of 8 160 tiles hold 12 % of the map), so a per-tile
+// unit of work alone leaves the chip waiting for a handful of walks:
+//   a block per tile, 256 nodes per step                                      K5a' 0.85 ms
+//   a warp per tile, wide walks give work to the other warps of their block        0.73 ms (SMs busy 23 % of it)
+//   one global breadth-first queue of (tile, node) items, 32 per claim             1.17 ms (3-4 same-address
+//                                                     atomics per 32 nodes: the counters serialise the chip)
+// Kept: a WARP per tile walk (deque of node refs in shared memory, up to 32 nodes per step, the TOP CUT
+// of the tree tested first from shared memory, where one TMA bulk copy per block put it), and a walk
+// whose deque grows past DONATE_MIN appends its 32 OLDEST entries -- the largest subtrees -- as one
+// batch to a GLOBAL queue (one atomicAdd per batch).  A warp that finds no tile left claims the next
+// batch position and waits until it is written (or until `pending` -- walks in progress + batches not
+// yet finished -- reads 0).  Consumers reset the slots to EMPTY, so the queue is clean for the next launch.
 constexpr int TW_STACK = 512;            // node refs per warp (a deque: donated from the bottom, popped from the top)
-constexpr int OVF_BATCHES = 16;          // donated batches of 32 node refs waiting for a thief
 constexpr int DONATE_MIN = 96;           // a walk with this many pending nodes gives 32 away
+constexpr unsigned HEAVY_STEPS_TILE = 24; // a tile walk this long (or one that gave work away) is claimed first by the next launch
 struct __align__(16) TileSmem {
     float4 cut[2 * TOP_CUT];
     float4 planes[TT_WARPS][6];
     int stack[TT_WARPS][TW_STACK];
-    int ovfRef[OVF_BATCHES][32];
-    unsigned ovfTile[OVF_BATCHES];
-    int ovfCount, lock, busy, tilesDone;
+    int tilesDone;
     uint64_t bar;
+};
+constexpr unsigned WQ_EMPTY = 0xffffffffu;
+struct WalkQueue {
+    uint2 *items;            // {tile, node ref}, batches of 32
+    unsigned cap;
+    unsigned *ctl;           // [0] head (claimed), [1] tail (reserved), [2] pending
 };
 
 __device__ __forceinline__ float warp_max(float v) {
@@ -158,15 +173,9 @@ __device__ __forceinline__ float warp_min(float v) {
 }
 __device__ __forceinline__ int ld_vol_s(const int *p) { return *reinterpret_cast<const volatile int *>(p); }
 
-// ---------------------------------------------------------------- K5a'
-// One WARP per tile walk, TT_WARPS walks per block.  A walk whose deque of pending nodes grows past
-// DONATE_MIN hands its 32 OLDEST entries (the largest subtrees) to a block-shared list; a warp that
-// runs out of work takes such a batch (the tile's planes come from its frame in global memory)
-// before it claims a new tile, so the few tiles that look into a light source -- 60x the photons of
-// an average tile -- are walked by all warps of the block instead of one.
 template <int MODE, bool COUNT>
-__global__ void __launch_bounds__(TT_THREADS) k_traverse_tile(
-    LeafArgs A, const LeafArgs *__restrict__ Ag, TileArgs T, uint32_t tile0, uint32_t nTiles,
+__global__ void __launch_bounds__(TT_THREADS) k_tile_walk(
+    LeafArgs A, const LeafArgs *__restrict__ Ag, TileArgs T, WalkQueue W, uint32_t tile0, uint32_t nTiles,
     uint2 *__restrict__ queue, unsigned int queueCap, unsigned int *__restrict__ queueCtl,
     const unsigned int *__restrict__ heavyIn, const unsigned int *__restrict__ nHeavyInPtr,
     const unsigned int *__restrict__ heavyFlagIn, unsigned int *__restrict__ heavyOut,
@@ -189,7 +198,7 @@ __global__ void __launch_bounds__(TT_THREADS) k_traverse_tile(
     // ---- stage the top cut of the tree into shared memory: one TMA bulk copy per block
     const unsigned nCut = T.nCut ? min(__float_as_uint(__ldg(&T.cut[2 * TOP_CUT].x)), (unsigned)TOP_CUT) : 0u;
     if (tid == 0) {
-        sm.ovfCount = 0; sm.lock = 0; sm.busy = 0; sm.tilesDone = 0;
+        sm.tilesDone = 0;
         if (nCut) mbar_init(&sm.bar, 1);
     }
     __syncthreads();
@@ -230,30 +239,12 @@ __global__ void __launch_bounds__(TT_THREADS) k_traverse_tile(
     };
 
     for (;;) {
-        // ================= get work: a donated batch, else a new tile, else wait for the block to drain
+        // ================= get work: a new tile while there are any, else a donated batch from the global queue
         unsigned tile = 0xffffffffu;
         unsigned nbot = 0, ntop = 0;       // deque [nbot, ntop) of node refs, indices mod TW_STACK
         bool stolen = false;
         unsigned pkClaimed = 0xffffffffu;
-        for (;;) {
-            if (__shfl_sync(FULL, ld_vol_s(&sm.ovfCount), 0) > 0) {
-                if (lane == 0) while (atomicCAS(&sm.lock, 0, 1) != 0) {}
-                __syncwarp();
-                const int cnt = __shfl_sync(FULL, ld_vol_s(&sm.ovfCount), 0);
-                if (cnt > 0) {
-                    const int b = cnt - 1;
-                    stack[lane] = ld_vol_s(&sm.ovfRef[b][lane]);
-                    tile = *reinterpret_cast<volatile unsigned *>(&sm.ovfTile[b]);
-                    __syncwarp();
-                    if (lane == 0) { *reinterpret_cast<volatile int *>(&sm.ovfCount) = b; atomicAdd(&sm.busy, 1); }
-                    stolen = true;
-                }
-                __threadfence_block();
-                __syncwarp();
-                if (lane == 0) atomicExch(&sm.lock, 0);
-                if (stolen) { ntop = 32; break; }
-            }
-            // claim a tile (heavy tiles of the previous launch first)
+        {
             unsigned pk = 0xffffffffu;
             if (lane == 0 && ld_vol_s(&sm.tilesDone) == 0) {
                 for (;;) {
@@ -263,15 +254,32 @@ __global__ void __launch_bounds__(TT_THREADS) k_traverse_tile(
                     if (pk >= nTiles) { pk = 0xffffffffu; *reinterpret_cast<volatile int *>(&sm.tilesDone) = 1; break; }
                     if (nHeavyIn == 0 || !((__ldg(heavyFlagIn + (pk >> 5)) >> (pk & 31u)) & 1u)) break;
                 }
-                if (pk != 0xffffffffu) atomicAdd(&sm.busy, 1);
+                if (pk != 0xffffffffu) atomicAdd(W.ctl + 2, 1u);      // a walk in progress
             }
             pk = __shfl_sync(FULL, pk, 0);
-            if (pk != 0xffffffffu) { pkClaimed = pk; tile = tile0 + pk; break; }
-            // nothing to claim: leave when nobody in the block can donate any more
-            const int busy = __shfl_sync(FULL, ld_vol_s(&sm.busy), 0);
-            const int pend = __shfl_sync(FULL, ld_vol_s(&sm.ovfCount), 0);
-            if (busy == 0 && pend == 0) break;
-            __nanosleep(200);
+            if (pk != 0xffffffffu) { pkClaimed = pk; tile = tile0 + pk; }
+        }
+        if (tile == 0xffffffffu) {
+            // no tile left: take the next batch of 32 (tile, node) items some wide walk gives away -- it may not
+            // have been written yet: wait for it, or for the end (no walk in progress, nothing pending)
+            unsigned h = 0;
+            if (lane == 0) h = atomicAdd(W.ctl + 0, 32u);
+            h = __shfl_sync(FULL, h, 0);
+            if (h + 32u <= W.cap) {
+                uint2 it = make_uint2(WQ_EMPTY, WQ_EMPTY);
+                for (;;) {
+                    if (it.x == WQ_EMPTY) it = __ldcv(W.items + h + lane);
+                    if (__all_sync(FULL, it.x != WQ_EMPTY)) { stolen = true; break; }
+                    if (__shfl_sync(FULL, *reinterpret_cast<volatile unsigned *>(W.ctl + 2), 0) == 0u) break;
+                    __nanosleep(200);
+                }
+                if (stolen) {
+                    __stcg(W.items + h + lane, make_uint2(WQ_EMPTY, WQ_EMPTY));   // clean for the next launch
+                    tile = __shfl_sync(FULL, it.x, 0);
+                    stack[lane] = (int)it.y;
+                    ntop = 32;
+                }
+            }
         }
         if (tile == 0xffffffffu) break;
 
@@ -309,23 +317,19 @@ __global__ void __launch_bounds__(TT_THREADS) k_traverse_tile(
             if (n1) stack[(ntop + __popc(mn0) + __popc(mn1 & lt)) & (TW_STACK - 1)] = c1;
             ntop += __popc(mn0) + __popc(mn1);
             __syncwarp();
-            // ---- donate the 32 oldest entries when the walk is wide and the shared list is short
-            if (ntop - nbot >= (unsigned)DONATE_MIN && __shfl_sync(FULL, ld_vol_s(&sm.ovfCount), 0) < 4) {
-                if (lane == 0) while (atomicCAS(&sm.lock, 0, 1) != 0) {}
-                __syncwarp();
-                const int cnt = __shfl_sync(FULL, ld_vol_s(&sm.ovfCount), 0);
-                if (cnt < OVF_BATCHES) {
-                    *reinterpret_cast<volatile int *>(&sm.ovfRef[cnt][lane]) = stack[(nbot + lane) & (TW_STACK - 1)];
-                    if (lane == 0) {
-                        *reinterpret_cast<volatile unsigned *>(&sm.ovfTile[cnt]) = tile;
-                        *reinterpret_cast<volatile int *>(&sm.ovfCount) = cnt + 1;
-                    }
+            // ---- a wide walk gives its 32 OLDEST entries (the largest subtrees) to the global queue
+            if (ntop - nbot >= (unsigned)DONATE_MIN) {
+                unsigned base = 0;
+                if (lane == 0) {
+                    atomicAdd(W.ctl + 2, 1u);                 // pending first: the count never reads 0 while a batch is unprocessed
+                    base = atomicAdd(W.ctl + 1, 32u);
+                }
+                base = __shfl_sync(FULL, base, 0);
+                if (base + 32u <= W.cap) {
+                    __stcg(W.items + base + lane, make_uint2(tile, (unsigned)stack[(nbot + lane) & (TW_STACK - 1)]));
                     nbot += 32;
                     ++donated;
-                }
-                __threadfence_block();
-                __syncwarp();
-                if (lane == 0) atomicExch(&sm.lock, 0);
+                } else if (lane == 0) atomicSub(W.ctl + 2, 1u);   // queue full: keep walking it here
             }
         };
         auto drain = [&](unsigned limit) { while (ntop - nbot > limit) step(); };
@@ -489,7 +493,7 @@ __global__ void __launch_bounds__(TT_THREADS) k_traverse_tile(
 
         // ================= walk until the deque is empty
         if (walk) drain(0u);
-        if (lane == 0) atomicSub(&sm.busy, 1);
+        if (lane == 0) atomicSub(W.ctl + 2, 1u);
         if (!stolen && lane == 0 && (steps >= HEAVY_STEPS_TILE || donated)) {
             const unsigned pos = heavyCap ? atomicAdd(nHeavyOut, 1u) : 0u;
             if (pos < heavyCap) {

@@ -179,10 +179,12 @@ def test_tile_path_grid_medium_radiance(oracle, ctx):
 
 
 @pytest.mark.parametrize("env", [{"BRE_PAIR_QUEUE_CAP": "2048"}, {"BRE_RAY_BATCH": "2048"},
-                                 {"BRE_RAY_BATCH": "1500", "BRE_PAIR_QUEUE_CAP": "65536"}])
+                                 {"BRE_RAY_BATCH": "1500", "BRE_PAIR_QUEUE_CAP": "65536"},
+                                 {"BRE_TILE_WQ_CAP": "200"}, {"BRE_TILE_WQ_CAP": "3000", "BRE_PAIR_QUEUE_CAP": "4096"}])
 def test_tile_path_overflow_and_batches(oracle, bre, env):
-    """Queue overflow (pairs handled in place) and the multi-batch pipeline (bands of tile rows on two
-    streams), in every mode: radiance, hit counts, hit indices; a second call reuses the heavy list."""
+    """Pair-queue overflow (pairs handled in place), work-queue overflow of the tile walk (subtrees walked
+    depth-first by their producer) and the multi-batch pipeline (bands of tile rows on two streams), in
+    every mode: radiance, hit counts, hit indices; a second call reuses queues and the heavy list."""
     old = {k: os.environ.get(k) for k in env}
     os.environ.update(env)
     try:
