@@ -212,11 +212,57 @@ __global__ void __launch_bounds__(128) k_tau_table(MediumDev m, uint32_t n,
     for (uint32_t i = threadIdx.x; i < cnt; i += blockDim.x) dst[i] = rows[i];
 }
 
+// K6 for a ray grid (tile path of K5): one block per 16x16 image tile, thread = pixel of the tile.  The table is
+// laid out [tile][step][pixel]: every step the block writes 256 consecutive floats (no shared-memory staging),
+// and the hits of one photon -- a few neighbouring pixels at one depth -- read neighbouring words instead of one
+// cache line per ray (K5b' is bound by L1 wavefronts, not by bytes).  Tiles of other ranks are skipped.
+__global__ void __launch_bounds__(256) k_tau_tile(MediumDev m, uint32_t imgW, uint32_t imgH, uint32_t tilesX,
+                                                  const float4 *__restrict__ ro, const float4 *__restrict__ rd,
+                                                  int steps, float *__restrict__ tau, float2 *__restrict__ span,
+                                                  int rankMod, int rankId) {
+    const uint32_t tile = blockIdx.x;
+    if (rankMod > 1 && (int)(tile % (uint32_t)rankMod) != rankId) return;
+    const uint32_t x = (tile % tilesX) * 16u + (threadIdx.x & 15u), y = (tile / tilesX) * 16u + (threadIdx.x >> 4);
+    if (x >= imgW || y >= imgH) return;
+    const uint32_t q = y * imgW + x;
+    float *col = tau + (size_t)tile * (size_t)(steps + 1) * 256u + threadIdx.x;
+    const float4 o4 = __ldg(ro + q), d4 = __ldg(rd + q);
+    float o[3] = {o4.x, o4.y, o4.z}, d[3] = {d4.x, d4.y, d4.z}, om[3], dm[3];
+    to_medium(m, o, d, om, dm);
+    float t0, t1;
+    if (!unit_box(om, dm, o4.w, t0, t1)) {
+        for (int k = 0; k <= steps; ++k) col[(size_t)k * 256u] = 0.f;
+        span[q] = make_float2(0.f, 0.f);
+        return;
+    }
+    const float dt = fdiv(fsub(t1, t0), (float)steps);
+    const float th = __fmaf_rn(0.5f, dt, t0);                 // first midpoint
+    const float nx = (float)m.nx, ny = (float)m.ny, nz = (float)m.nz;
+    const float s0x = __fmaf_rn(__fmaf_rn(dm[0], th, om[0]), nx, -0.5f), dsx = dm[0] * dt * nx;
+    const float s0y = __fmaf_rn(__fmaf_rn(dm[1], th, om[1]), ny, -0.5f), dsy = dm[1] * dt * ny;
+    const float s0z = __fmaf_rn(__fmaf_rn(dm[2], th, om[2]), nz, -0.5f), dsz = dm[2] * dt * nz;
+    float acc = 0.f;
+    col[0] = 0.f;
+    for (int k = 0; k < steps; ++k) {
+        const float kf = (float)k;
+        const float dens = grid_density_s(m, __fmaf_rn(kf, dsx, s0x), __fmaf_rn(kf, dsy, s0y), __fmaf_rn(kf, dsz, s0z));
+        acc = __fmaf_rn(dens, dt, acc);
+        col[(size_t)(k + 1) * 256u] = acc;
+    }
+    span[q] = make_float2(t0, t1);
+}
+
 }  // namespace bre
 constexpr int QT = 128;
 #include "bre_query_warp.cuh"
 #include "bre_query_tile.cuh"
 namespace bre {
+
+// image-tile path: the caller declared the rays to be a grid_w x grid_h image (bre_set_ray_grid / K0)
+static bool tile_mode(const bre_ctx *ctx, uint32_t n) {
+    return !BRE_WIDE && ctx->tile_path && ctx->grid_w >= 2 && ctx->grid_h >= 2 &&
+           (uint64_t)ctx->grid_w * ctx->grid_h == n && ctx->n_built > 0;
+}
 
 // One block of launch state per ray batch, in ctx->packet_ctr (stride QB_STRIDE bytes):
 //   +0   queue control words (QC_*), zeroed before every launch
@@ -228,8 +274,9 @@ static_assert(QB_ARGS + sizeof(LeafArgs) <= QB_STRIDE, "batch block too small");
 
 __host__ __device__ inline LeafArgs shift_args(LeafArgs A, size_t off) {
     A.ro += off; A.rd += off;
+    A.rayBase += (uint32_t)off;
     if (A.out) A.out += off;
-    if (A.tau) A.tau += off * (size_t)(A.tauSteps + 1);
+    if (A.tau && !A.tauW) A.tau += off * (size_t)(A.tauSteps + 1);   // (the tile-blocked table is indexed by absolute pixel)
     if (A.span) A.span += off;
     if (A.hitCounts) A.hitCounts += off;
     if (A.hitOffsets) A.hitOffsets += off;
@@ -257,8 +304,7 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     int s;
     if (n >= (1u << 30)) return set_err(ctx, BRE_ERR_UNSUPPORTED, "more than 2^30 rays in one query");
     // ---- image-tile path: the caller declared the rays to be a grid_w x grid_h image (bre_set_ray_grid / K0)
-    const bool tileMode = !BRE_WIDE && ctx->tile_path && ctx->grid_w >= 2 && ctx->grid_h >= 2 &&
-                          (uint64_t)ctx->grid_w * ctx->grid_h == n && ctx->n_built > 0;
+    const bool tileMode = tile_mode(ctx, n);
     const uint32_t imgW = tileMode ? ctx->grid_w : 0, imgH = tileMode ? ctx->grid_h : 0;
     const uint32_t tilesX = tileMode ? (imgW + TILE_W - 1) / TILE_W : 0, tilesY = tileMode ? (imgH + TILE_H - 1) / TILE_H : 0;
     // ---- pair queue capacity: 128 pairs per ray, at least 1M, at most 256M pairs (2 GiB)
@@ -322,6 +368,7 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     LeafArgs A;
     A.t = tree_view(ctx); A.m = ctx->medium; A.ro = ro; A.rd = rd; A.nPathsNorm = nPathsNorm;
     A.out = out; A.tau = tau; A.span = span; A.tauSteps = ctx->tau_steps;
+    A.tauW = (tileMode && tau) ? imgW : 0u; A.tauTilesX = tilesX; A.rayBase = 0;
     A.hitCounts = hitCounts; A.hitOffsets = hitOffsets; A.hitIdx = hitIdx;
     A.frames = nullptr;
     TileArgs TA{};
@@ -468,9 +515,16 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
         }
         // the leaf kernels scan the queue; each leaves at once if K5a emitted no pair of its kind
         if (tileMode) {
-            if (ctx->max_leaf <= 4) k_leaf_tile<MODE, COUNT, 4><<<gb, LP_WARPS * 32, 0, sb>>>(A, TA.tframes, imgW, queue, cap, ctl, counters);
-            else if (ctx->max_leaf <= 8) k_leaf_tile<MODE, COUNT, 8><<<gb, LP_WARPS * 32, 0, sb>>>(A, TA.tframes, imgW, queue, cap, ctl, counters);
-            else k_leaf_tile<MODE, COUNT, 16><<<gb, LP_WARPS * 32, 0, sb>>>(A, TA.tframes, imgW, queue, cap, ctl, counters);
+            if (ctx->max_leaf <= 4) {
+                BRE_CUDA(cudaFuncSetAttribute(k_leaf_tile<MODE, COUNT, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LEAF_TILE_SMEM));
+                k_leaf_tile<MODE, COUNT, 4><<<gb, LP_WARPS * 32, LEAF_TILE_SMEM, sb>>>(A, TA.tframes, imgW, queue, cap, ctl, counters);
+            } else if (ctx->max_leaf <= 8) {
+                BRE_CUDA(cudaFuncSetAttribute(k_leaf_tile<MODE, COUNT, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LEAF_TILE_SMEM));
+                k_leaf_tile<MODE, COUNT, 8><<<gb, LP_WARPS * 32, LEAF_TILE_SMEM, sb>>>(A, TA.tframes, imgW, queue, cap, ctl, counters);
+            } else {
+                BRE_CUDA(cudaFuncSetAttribute(k_leaf_tile<MODE, COUNT, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LEAF_TILE_SMEM));
+                k_leaf_tile<MODE, COUNT, 16><<<gb, LP_WARPS * 32, LEAF_TILE_SMEM, sb>>>(A, TA.tframes, imgW, queue, cap, ctl, counters);
+            }
         }
         if (ctx->max_leaf <= 4) {
             k_leaf_fat<MODE, COUNT, 4><<<gb, LP_WARPS * 32, 0, sb>>>(Ab, queue, cap, ctl, counters);
@@ -552,10 +606,25 @@ static int prepare_tau(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 
     int s;
     size_t rowBytes = (size_t)(ctx->tau_steps + 1) * 4;
     size_t offSpan = ((size_t)n * rowBytes + 15) & ~(size_t)15;
-    if ((s = ensure(ctx, ctx->tau, offSpan + (size_t)n * 8)) != BRE_OK) return s;
-    float *tp = (float *)ctx->tau.p;
-    float2 *sp = (float2 *)((char *)ctx->tau.p + offSpan);
-    {
+    float *tp = nullptr;
+    float2 *sp = nullptr;
+    const bool grid = tile_mode(ctx, n);
+    if (grid) {
+        // tile-blocked table (k_tau_tile): [tile][step][256 pixels]
+        const uint32_t tX = (ctx->grid_w + 15) / 16, tY = (ctx->grid_h + 15) / 16;
+        const size_t tab = (size_t)tX * tY * rowBytes * 256;
+        offSpan = (tab + 15) & ~(size_t)15;
+        if ((s = ensure(ctx, ctx->tau, offSpan + (size_t)n * 8)) != BRE_OK) return s;
+        tp = (float *)ctx->tau.p;
+        sp = (float2 *)((char *)ctx->tau.p + offSpan);
+        PhaseTimer pt(ctx, PH_TAU);
+        const int shardMod = (ctx->tile_shard && ctx->n_ranks > 1) ? ctx->n_ranks : 1;
+        k_tau_tile<<<tX * tY, 256, 0, ctx->stream>>>(ctx->medium, ctx->grid_w, ctx->grid_h, tX, ro, rd, ctx->tau_steps,
+                                                   tp, sp, shardMod, ctx->rank);
+    } else {
+        if ((s = ensure(ctx, ctx->tau, offSpan + (size_t)n * 8)) != BRE_OK) return s;
+        tp = (float *)ctx->tau.p;
+        sp = (float2 *)((char *)ctx->tau.p + offSpan);
         PhaseTimer pt(ctx, PH_TAU);
         const size_t smem = (size_t)128 * (ctx->tau_steps + 1) * 4;   // tau_steps <= 384 (bre_create)
         if (smem > 48 * 1024)

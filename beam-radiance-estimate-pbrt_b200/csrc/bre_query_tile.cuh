@@ -535,46 +535,35 @@ struct __align__(16) TileEnt {      // stage-1 results (entry = sub-pass * 32 + 
     float q12[TE_N];
     uint32_t s[TE_N];      // sorted photon index
     uint32_t rb[TE_N];     // ray index of the tile's pixel (0, 0)
+    uint32_t tl[TE_N];     // tile index
     uint32_t rect[TE_N];   // i0 | j0 << 8 | w << 16 | h << 24
 };
 struct __align__(16) TileHits {
-    uint32_t e[64], q[64];
-    float th[64], d2[64];
+    uint32_t e[64], q[64];   // e = entry | pixel-in-tile << 8
+    float th[64], d2[64], ct[64];
 };
 #ifndef TILE_MINB
 #define TILE_MINB 4
 #endif
+constexpr size_t LEAF_TILE_SMEM = LP_WARPS * (sizeof(TileEnt) + sizeof(TileHits));
 
-// radiance of one hit, photon data passed in (see hit_radiance)
-__device__ __forceinline__ float3 hit_radiance_p(const LeafArgs &A, float radius, const float4 w, const float4 pw,
-                                                 uint32_t q, float th, float d2) {
-    const float4 d = __ldg(A.rd + q);
+// radiance of one hit of the tile path: photon data from the entry, cos(theta) from the candidate pass,
+// optical depth from the tile-blocked table (see hit_radiance for the formula)
+__device__ __forceinline__ float3 hit_radiance_p(const LeafArgs &A, float radius, const float4 pw, float cosT,
+                                                 uint32_t q, uint32_t tile, uint32_t pp, float th, float d2) {
     const float r2 = radius * radius;
     const float invr2 = __fdividef(1.f, r2);
-    const float sK = 1.f - d2 * invr2;                       // kernel(): photonmap.cpp:170-174
+    const float sK = __fmaf_rn(-d2, invr2, 1.f);             // kernel(): photonmap.cpp:170-174
     const float wgt = (3.f * BRE_INV_PI) * sK * sK * invr2 * __fdividef(1.f, A.nPathsNorm);
-    const float cosT = -(d.x * w.x + d.y * w.y + d.z * w.z); // Dot(wo = -d, wi)
     const float g = A.m.g;
-    const float denom = 1.f + g * g + 2.f * g * cosT;        // PhaseHG medium.h:66-69
+    const float denom = __fmaf_rn(2.f * g, cosT, __fmaf_rn(g, g, 1.f));   // PhaseHG medium.h:66-69
     const float rs = rsqrtf(denom);
-    const float wp = wgt * BRE_INV4PI * (1.f - g * g) * rs * rs * rs;
+    const float wp = wgt * BRE_INV4PI * __fmaf_rn(-g, g, 1.f) * rs * rs * rs;
     float od = th;
     if (A.m.kind == 1) {
         const float2 sp = __ldg(A.span + q);
-        const float *tau = A.tau + (size_t)q * (A.tauSteps + 1);
-        od = 0.f;
-        if (sp.y > sp.x) {
-            float sc = (th - sp.x) * __fdividef((float)A.tauSteps, sp.y - sp.x);
-            if (sc > 0.f) {
-                if (sc >= (float)A.tauSteps) od = __ldg(tau + A.tauSteps);
-                else {
-                    int k = (int)sc;
-                    float f = sc - (float)k;
-                    float a = __ldg(tau + k), b = __ldg(tau + k + 1);
-                    od = a + f * (b - a);
-                }
-            }
-        }
+        if (A.tauW) od = optical_depth_at(A, sp, A.tau + (size_t)tile * (size_t)(A.tauSteps + 1) * 256u + pp, 256, th);
+        else od = optical_depth_at(A, sp, A.tau + (size_t)q * (A.tauSteps + 1), 1, th);
     }
     float t0, t1, t2;
     t0 = __expf(-A.m.sigma_t[0] * od);
@@ -590,10 +579,9 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                                                                     unsigned int queueCap,
                                                                     unsigned int *__restrict__ queueCtl,
                                                                     unsigned long long *__restrict__ counters) {
-    __shared__ TileHits bufAll[LP_WARPS];
-    __shared__ TileEnt entAll[LP_WARPS];
-    TileHits &hb = bufAll[threadIdx.x >> 5];
-    TileEnt &te = entAll[threadIdx.x >> 5];
+    extern __shared__ __align__(16) unsigned char lt_smem_raw[];     // LP_WARPS x (TileEnt + TileHits): > 48 KB
+    TileEnt &te = reinterpret_cast<TileEnt *>(lt_smem_raw)[threadIdx.x >> 5];
+    TileHits &hb = reinterpret_cast<TileHits *>(lt_smem_raw + LP_WARPS * sizeof(TileEnt))[threadIdx.x >> 5];
     constexpr unsigned G = 32 / LW;
     const unsigned FULL = 0xffffffffu;
     const unsigned lane = threadIdx.x & 31u;
@@ -608,9 +596,10 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
     // shade `cnt` buffered hits starting at hb[from], one per lane
     auto shade = [&](unsigned from, unsigned cnt) {
         if (lane < cnt) {
-            const unsigned e = hb.e[from + lane], q = hb.q[from + lane];
-            const float4 pp = te.p[e];
-            const float3 v = hit_radiance_p(A, pp.w, te.dr[e], te.pw[e], q, hb.th[from + lane], hb.d2[from + lane]);
+            const unsigned ep = hb.e[from + lane], q = hb.q[from + lane];
+            const unsigned e = ep & 255u;
+            const float3 v = hit_radiance_p(A, te.p[e].w, te.pw[e], hb.ct[from + lane], q, te.tl[e], ep >> 8,
+                                            hb.th[from + lane], hb.d2[from + lane]);
             atomicAdd(A.out + q, make_float4(v.x, v.y, v.z, 0.f));   // RED.E.ADD.F32x4
         }
     };
@@ -693,6 +682,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                         te.q12[e] = q12;
                         te.s[e] = firstP + j;
                         te.rb[e] = __float_as_uint(__ldg(&fr[7].x));
+                        te.tl[e] = qx & TILE_MASK;
                         te.rect[e] = (unsigned)i0 | ((unsigned)j0 << 8) | (w << 16) | (h << 24);
                     }
                     if (COUNT) ++cTests;
@@ -713,8 +703,8 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
             for (unsigned cb = 0; cb < totalC; cb += 32) {
                 const unsigned c = cb + lane;
                 bool hit = false;
-                float th = 0.f, d2 = 0.f;
-                uint32_t e = 0, q = 0;
+                float th = 0.f, d2 = 0.f, ct = 0.f;
+                uint32_t e = 0, q = 0, pp = 0;
                 // entry with cstart <= c < cstart + count: which sub-pass, then binary search over its lanes
                 unsigned usel = 0;
 #pragma unroll
@@ -762,6 +752,11 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                         r.dx = d.x; r.dy = d.y; r.dz = d.z;
                         hit = disk_test(r, p, th, d2);
                         if (COUNT) ++cTests;
+                        if (MODE == 0 && hit) {
+                            const float4 w = te.dr[e];
+                            ct = -__fmaf_rn(d.z, w.z, __fmaf_rn(d.y, w.y, d.x * w.x));   // Dot(wo = -d, wi)
+                            pp = pj * 16u + pi;
+                        }
                     }
                 }
                 if (MODE != 0) {
@@ -772,7 +767,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                 if (mh == 0u) continue;
                 if (hit) {
                     const unsigned pos = nbuf + __popc(mh & lt);
-                    hb.e[pos] = e; hb.q[pos] = q; hb.th[pos] = th; hb.d2[pos] = d2;
+                    hb.e[pos] = e | (pp << 8); hb.q[pos] = q; hb.th[pos] = th; hb.d2[pos] = d2; hb.ct[pos] = ct;
                 }
                 nbuf += __popc(mh);
                 __syncwarp();

@@ -253,11 +253,42 @@ struct LeafArgs {
     const float *tau;            // grid media: optical-depth tables
     const float2 *span;
     int tauSteps;
+    uint32_t tauW, tauTilesX;    // tauW != 0: the table is tile-blocked [tile][step][256 px] for an image tauW wide (k_tau_tile)
+    uint32_t rayBase;            // index of ro[0] in the whole launch (ray batches): the tile-blocked table wants absolute pixels
     uint32_t *hitCounts;         // MODE 1: per-ray hit counts; MODE 2: per-ray write cursors
     const uint64_t *hitOffsets;  // MODE 2
     uint32_t *hitIdx;            // MODE 2
     float4 *frames;              // FRAME_V4 float4 per packet: PacketFrame of coherent packets (K5a -> k_leaf_fat)
 };
+
+// Optical depth of a grid medium at ray parameter th: linear interpolation in the ray's table.
+// base/stride address the table entries of this ray (ray layout: stride 1; tile-blocked: stride 256).
+__device__ __forceinline__ float optical_depth_at(const LeafArgs &A, const float2 sp, const float *base, size_t stride,
+                                                  float th) {
+    float od = 0.f;
+    if (sp.y > sp.x) {
+        const float sc = (th - sp.x) * __fdividef((float)A.tauSteps, sp.y - sp.x);
+        if (sc > 0.f) {
+            if (sc >= (float)A.tauSteps) od = __ldg(base + (size_t)A.tauSteps * stride);
+            else {
+                const int k = (int)sc;
+                const float f = sc - (float)k;
+                const float a = __ldg(base + (size_t)k * stride), b = __ldg(base + (size_t)(k + 1) * stride);
+                od = __fmaf_rn(f, b - a, a);
+            }
+        }
+    }
+    return od;
+}
+__device__ __forceinline__ float optical_depth(const LeafArgs &A, uint32_t q, float th) {
+    const float2 sp = __ldg(A.span + q);
+    if (A.tauW) {
+        const uint32_t qa = A.rayBase + q, x = qa % A.tauW, y = qa / A.tauW;
+        const size_t tile = (size_t)(y >> 4) * A.tauTilesX + (x >> 4);
+        return optical_depth_at(A, sp, A.tau + tile * (size_t)(A.tauSteps + 1) * 256u + ((y & 15u) * 16u + (x & 15u)), 256, th);
+    }
+    return optical_depth_at(A, sp, A.tau + (size_t)q * (A.tauSteps + 1), 1, th);
+}
 
 // Radiance of one hit (photon s, ray q, ray parameter th, squared distance d2).
 // Only the hit DECISION has to be bit-exact; the weight uses the fast reciprocal / exp units
@@ -277,23 +308,7 @@ __device__ __forceinline__ float3 hit_radiance(const LeafArgs &A, uint32_t s, ui
     const float rs = rsqrtf(denom);
     const float wp = wgt * BRE_INV4PI * (1.f - g * g) * rs * rs * rs;
     float od = th;                                           // homogeneous: optical depth = sigma_t * t
-    if (A.m.kind == 1) {
-        const float2 sp = __ldg(A.span + q);
-        const float *tau = A.tau + (size_t)q * (A.tauSteps + 1);
-        od = 0.f;
-        if (sp.y > sp.x) {
-            float sc = (th - sp.x) * __fdividef((float)A.tauSteps, sp.y - sp.x);
-            if (sc > 0.f) {
-                if (sc >= (float)A.tauSteps) od = __ldg(tau + A.tauSteps);
-                else {
-                    int k = (int)sc;
-                    float f = sc - (float)k;
-                    float a = __ldg(tau + k), b = __ldg(tau + k + 1);
-                    od = a + f * (b - a);
-                }
-            }
-        }
-    }
+    if (A.m.kind == 1) od = optical_depth(A, q, th);
     float t0, t1, t2;
     t0 = __expf(-A.m.sigma_t[0] * od);
     if (A.m.gray) { t1 = t0; t2 = t0; }
