@@ -28,7 +28,7 @@ SYMBOLS = [
     "bre_set_triangle_attrs", "bre_set_lights_in_medium", "bre_set_camera", "bre_camera_rays",
     "bre_query_camera_to_film", "bre_last_build_kind",
     "bre_trace_exchange_photons", "bre_alloc_pinned", "bre_free_pinned", "bre_stage_rays", "bre_query_staged_to_film", "bre_save_photons", "bre_load_photons", "bre_film_save", "bre_film_load",
-    "bre_set_ray_grid", "bre_set_tile_sharding",
+    "bre_set_ray_grid", "bre_set_tile_sharding", "bre_film_gather",
 ]
 
 
@@ -371,6 +371,15 @@ class Bre:
         out = np.zeros((self._npix, 3), np.float32)
         self._ck(self.lib.bre_film_resolve(self.ctx, it, C.c_float(scale), _fp(out)))
         return out
+
+    def film_gather(self, it, scale=1.0, mean_only=False, want=True):
+        """Collective (tile-sharded camera pass): rank 0 passes want=True and gets the image, the others None."""
+        out = np.zeros((self._npix, 3), np.float32) if want else None
+        self._ck(self.lib.bre_film_gather(self.ctx, it, C.c_float(scale), _fp(out) if want else None, int(mean_only)))
+        return out
+
+    def film_gather_ptr(self, it, scale, out_ptr):
+        self._ck(self.lib.bre_film_gather(self.ctx, it, C.c_float(scale), C.cast(out_ptr, C.POINTER(C.c_float)), 0))
 
     def film_mean(self, it):
         out = np.zeros((self._npix, 3), np.float32)

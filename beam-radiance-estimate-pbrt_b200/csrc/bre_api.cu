@@ -168,7 +168,7 @@ int bre_destroy(bre_ctx *ctx) {
                    &ctx->node_lo, &ctx->node_hi, &ctx->node_range, &ctx->parent, &ctx->leaf_lo,
                    &ctx->leaf_hi, &ctx->flags, &ctx->fast, &ctx->scratch, &ctx->rays_o, &ctx->rays_d,
                    &ctx->out_rgb, &ctx->tau, &ctx->hit_counts, &ctx->hit_offsets, &ctx->hit_idx,
-                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->frames, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb, &ctx->entry, &ctx->rays_stage, &ctx->p2p_scratch, &ctx->aos, &ctx->tframes, &ctx->tile_state, &ctx->top_cut, &ctx->tile_wq};
+                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->frames, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb, &ctx->entry, &ctx->rays_stage, &ctx->p2p_scratch, &ctx->aos, &ctx->tframes, &ctx->tile_state, &ctx->top_cut, &ctx->tile_wq, &ctx->gather};
     for (Buf *b : bufs) if (b->p) cudaFree(b->p);
     if (ctx->lights_d) cudaFree(ctx->lights_d);
     if (ctx->est_host) cudaFreeHost(ctx->est_host);
@@ -381,7 +381,10 @@ int bre_trace_exchange_photons(bre_ctx *ctx, uint64_t nPathsTotal, int maxDepth,
     uint64_t first = 0, count = nPathsTotal;
     bre_shard_range(nPathsTotal, ctx->n_ranks, ctx->rank, &first, &count);
     int s;
-    if (ctx->n_ranks > 1 && !ctx->p2p_disabled && ctx->n_ranks <= 8 && count <= TRACE_CHUNK) {
+    // the path must be the same on every rank (both are collectives): decide from GLOBAL values only --
+    // the largest shard any rank gets, not this rank's own
+    const uint64_t maxShard = (nPathsTotal + (uint64_t)ctx->n_ranks - 1) / (uint64_t)ctx->n_ranks;
+    if (ctx->n_ranks > 1 && !ctx->p2p_disabled && ctx->n_ranks <= 8 && maxShard <= TRACE_CHUNK) {
         s = trace_exchange_p2p(ctx, nPathsTotal, maxDepth, radius);
     } else {
         ctx->n_photons = 0;
@@ -677,6 +680,12 @@ int bre_film_mean(bre_ctx *ctx, int iter, float *rgb_out) {
     CTX_CHECK();
     if (!rgb_out || iter < 0) return set_err(ctx, BRE_ERR_INVALID, "bad resolve arguments");
     return film_resolve(ctx, iter, 1.f, rgb_out, 1);
+}
+
+int bre_film_gather(bre_ctx *ctx, int iter, float scale, float *rgb_out, int mean_only) {
+    CTX_CHECK();
+    if (iter < 0) return set_err(ctx, BRE_ERR_INVALID, "bad resolve arguments");
+    return film_gather(ctx, iter, scale, rgb_out, mean_only);
 }
 
 // ---------------------------------------------------------------- timing

@@ -17,6 +17,8 @@ struct CameraDev {
     float r2c[16], c2w[12];
     float oErr[3];
     int x0, y0, w, h, inMedium;
+    int haveBox;             // no triangles: the absorbing scene box of bre_set_bounds ends the camera rays too
+    float blo[3], bhi[3];
 };
 
 __global__ void __launch_bounds__(128) k_camera_rays(CameraDev cam, MeshDev mesh, float offx, float offy,
@@ -47,7 +49,23 @@ __global__ void __launch_bounds__(128) k_camera_rays(CameraDev cam, MeshDev mesh
         tMax -= dt;
     }
     SurfHit h;
-    if (mesh.n && mesh_intersect(mesh, o, d, tMax, h, false)) tMax = h.t;
+    if (mesh.n) { if (mesh_intersect(mesh, o, d, tMax, h, false)) tMax = h.t; }
+    else if (cam.haveBox) {
+        // Bounds3::IntersectP(ray, &t0, &t1), geometry.h:1386-1408: the ray ends where it leaves the box
+        float t0 = 0.f, t1 = tMax;
+        bool hit = true;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            const float invD = 1.f / d[i];
+            float tNear = (cam.blo[i] - o[i]) * invD, tFar = (cam.bhi[i] - o[i]) * invD;
+            if (tNear > tFar) { const float sw = tNear; tNear = tFar; tFar = sw; }
+            tFar *= BRE_SLAB_WIDEN;
+            t0 = tNear > t0 ? tNear : t0;
+            t1 = tFar < t1 ? tFar : t1;
+            if (t0 > t1) hit = false;
+        }
+        tMax = hit ? t1 : 0.f;
+    }
     float len = sqrtf(l2), inv = 1 / len;
     float t = cam.inMedium ? fminf(tMax * len, 3.402823466e+38f) : 0.f;
     ro[q] = make_float4(o[0], o[1], o[2], t);
@@ -70,6 +88,8 @@ int camera_rays(bre_ctx *ctx, float offx, float offy) {
         cd.oErr[r] = g3 * (std::fabs(m[0] * 0.f) + std::fabs(m[1] * 0.f) + std::fabs(m[2] * 0.f) + std::fabs(m[3]));
     }
     cd.x0 = c.x0; cd.y0 = c.y0; cd.w = c.width; cd.h = c.height; cd.inMedium = c.in_medium;
+    cd.haveBox = (ctx->n_tri == 0 && ctx->have_bounds) ? 1 : 0;
+    for (int r = 0; r < 3; ++r) { cd.blo[r] = ctx->blo[r]; cd.bhi[r] = ctx->bhi[r]; }
     MeshDev mesh{ctx->n_tri, (const float4 *)ctx->tri.p, (const float *)ctx->tri_kdb.p};
     k_camera_rays<<<(n + 127) / 128, 128, 0, ctx->stream>>>(cd, mesh, offx, offy, (float4 *)ctx->rays_o.p,
                                                            (float4 *)ctx->rays_d.p);

@@ -209,6 +209,10 @@ struct bre_ctx {
     bool p2p_open = false;
     bool p2p_disabled = false;             // BRE_NO_P2P=1, or IPC mapping failed once
     bre::Buf p2p_scratch;
+    // film gather of the tile-sharded camera pass (bre_film_gather): rank 0's image buffer, mapped on every rank
+    bre::Buf gather;
+    void *gather_peer0 = nullptr, *gather_exported = nullptr;
+    uint32_t gather_mapped_pixels = 0, gather_calls = 0;
     std::vector<void *> p2p_zombies;       // exported stores replaced since: freed once peers closed them
     // per-phase device timing (bre_set_timing)
     bool timing = false;
@@ -256,6 +260,7 @@ int trace_photons(bre_ctx *ctx, uint64_t first, uint64_t nPaths, int maxDepth, f
 int nccl_init(bre_ctx *ctx, const void *uid);
 int nccl_allgather_photons(bre_ctx *ctx);
 int trace_exchange_p2p(bre_ctx *ctx, uint64_t nPathsTotal, int maxDepth, float radius);
+int film_gather(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int meanOnly);
 void nccl_destroy(bre_ctx *ctx);
 int nccl_unique_id(void *out128);
 

@@ -9,6 +9,7 @@
 #include "bre_internal.cuh"
 #include <dlfcn.h>
 #include <cstring>
+#include <algorithm>
 #include <vector>
 
 namespace {
@@ -20,6 +21,7 @@ typedef int (*fnCommInitRank)(ncclComm_p *, int, ncclUniqueId_t, int);
 typedef int (*fnCommDestroy)(ncclComm_p);
 typedef int (*fnAllGather)(const void *, void *, size_t, int, ncclComm_p, cudaStream_t);
 typedef int (*fnBroadcast)(const void *, void *, size_t, int, int, ncclComm_p, cudaStream_t);
+typedef int (*fnReduce)(const void *, void *, size_t, int, int, int, ncclComm_p, cudaStream_t);
 typedef int (*fnGroup)(void);
 typedef const char *(*fnErrStr)(int);
 
@@ -30,6 +32,7 @@ struct Nccl {
     fnCommDestroy CommDestroy = nullptr;
     fnAllGather AllGather = nullptr;
     fnBroadcast Broadcast = nullptr;
+    fnReduce Reduce = nullptr;
     fnGroup GroupStart = nullptr, GroupEnd = nullptr;
     fnErrStr GetErrorString = nullptr;
     bool ok = false;
@@ -51,6 +54,7 @@ bool load() {
     SYM(CommDestroy, "ncclCommDestroy");
     SYM(AllGather, "ncclAllGather");
     SYM(Broadcast, "ncclBroadcast");
+    SYM(Reduce, "ncclReduce");
     SYM(GroupStart, "ncclGroupStart");
     SYM(GroupEnd, "ncclGroupEnd");
     SYM(GetErrorString, "ncclGetErrorString");
@@ -68,6 +72,7 @@ int nccl_err(bre_ctx *ctx, int r, const char *what) {
 namespace bre {
 
 int grow_photon_store(bre_ctx *ctx, uint64_t newCount);
+static void p2p_close(bre_ctx *ctx);
 
 int nccl_unique_id(void *out128) {
     if (!out128) return BRE_ERR_INVALID;
@@ -101,14 +106,21 @@ void nccl_destroy(bre_ctx *ctx) {
 // rank-major offset -- no padding, no second compaction pass.
 int nccl_allgather_photons(bre_ctx *ctx) {
     if (!ctx->nccl_comm) return set_err(ctx, BRE_ERR_INVALID, "context was created without NCCL");
-    if (ctx->p2p_open)
-        return set_err(ctx, BRE_ERR_INVALID, "this context exchanges photons over P2P (bre_trace_exchange_photons); "
-                                             "set BRE_NO_P2P=1 to use the NCCL all-gather instead");
     ncclComm_p comm = (ncclComm_p)ctx->nccl_comm;
     const int R = ctx->n_ranks;
     int s;
-    if ((s = ensure(ctx, ctx->counters_d, 8 * (size_t)(R + 1) + 64)) != BRE_OK) return s;
+    if ((s = ensure(ctx, ctx->counters_d, 32 * (size_t)(R + 1) + 64)) != BRE_OK) return s;
     uint64_t *cnt_d = (uint64_t *)ctx->counters_d.p;
+    if (ctx->p2p_open) {
+        // an earlier exchange went over P2P (the choice between the two paths is a function of global values,
+        // so every rank is here together): unmap the peers' stores before the slabs below replace them
+        p2p_close(ctx);
+        int r0 = g.AllGather(cnt_d + 2 * R, cnt_d, 1, kNcclUint64, comm, ctx->stream);
+        if (r0 != 0) return nccl_err(ctx, r0, "ncclAllGather(unmap barrier)");
+        BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+        for (void *z : ctx->p2p_zombies) cudaFree(z);
+        ctx->p2p_zombies.clear();
+    }
     uint64_t mine = ctx->n_photons;
     BRE_CUDA(cudaMemcpyAsync(cnt_d + R, &mine, 8, cudaMemcpyHostToDevice, ctx->stream));
     int r = g.AllGather(cnt_d + R, cnt_d, 1, kNcclUint64, comm, ctx->stream);
@@ -200,7 +212,10 @@ static void p2p_close(bre_ctx *ctx) {
     ctx->p2p_open = false;
 }
 void p2p_destroy(bre_ctx *ctx) {
-    const bool was = ctx->p2p_open;
+    if (ctx->gather_peer0 && ctx->rank != 0) cudaIpcCloseMemHandle(ctx->gather_peer0);
+    const bool hadGather = ctx->gather_peer0 != nullptr;
+    ctx->gather_peer0 = nullptr;
+    const bool was = ctx->p2p_open || hadGather;
     p2p_close(ctx);
     if (was && ctx->nccl_comm) {
         // peers must have unmapped this rank's store before bre_destroy frees it
@@ -263,24 +278,32 @@ int trace_exchange_p2p(bre_ctx *ctx, uint64_t nPathsTotal, int maxDepth, float r
         if ((s = trace_to_slots(ctx, first, (uint32_t)count, maxDepth, radius, &v)) != BRE_OK) return s;
     }
     // ---- counts (+ "my store moved" flag) to everyone; doubles as the pre-push barrier
-    if ((s = ensure(ctx, ctx->counters_d, 16 * (size_t)(R + 1) + 64)) != BRE_OK) return s;
+    if ((s = ensure(ctx, ctx->counters_d, 32 * (size_t)(R + 1) + 64)) != BRE_OK) return s;
     uint64_t *cnt_d = (uint64_t *)ctx->counters_d.p;
     const bool moved = !ctx->p2p_open || ctx->p2p_exported[0] != ctx->pos_r.p ||
                        ctx->p2p_exported[1] != ctx->pow.p || ctx->p2p_exported[2] != ctx->dir.p;
-    uint64_t mine[2] = {v.total, moved ? 1ull : 0ull};
-    BRE_CUDA(cudaMemcpyAsync(cnt_d + 2 * R, mine, 16, cudaMemcpyHostToDevice, ctx->stream));
-    int r = g.AllGather(cnt_d + 2 * R, cnt_d, 2, kNcclUint64, comm, ctx->stream);
+    // {photons traced, "my store moved", my store's capacity}: everything the collective decisions below need,
+    // so that every rank takes the same branches whatever its own buffers look like
+    const size_t myCap = std::min(ctx->pos_r.cap, std::min(ctx->pow.cap, ctx->dir.cap));
+    uint64_t mine[3] = {v.total, moved ? 1ull : 0ull, (uint64_t)myCap};
+    BRE_CUDA(cudaMemcpyAsync(cnt_d + 3 * R, mine, 24, cudaMemcpyHostToDevice, ctx->stream));
+    int r = g.AllGather(cnt_d + 3 * R, cnt_d, 3, kNcclUint64, comm, ctx->stream);
     if (r != 0) return nccl_err(ctx, r, "ncclAllGather(counts)");
-    std::vector<uint64_t> got(2 * (size_t)R), off(R + 1, 0);
-    BRE_CUDA(cudaMemcpyAsync(got.data(), cnt_d, 16 * (size_t)R, cudaMemcpyDeviceToHost, ctx->stream));
+    std::vector<uint64_t> got(3 * (size_t)R), off(R + 1, 0);
+    BRE_CUDA(cudaMemcpyAsync(got.data(), cnt_d, 24 * (size_t)R, cudaMemcpyDeviceToHost, ctx->stream));
     BRE_CUDA(cudaStreamSynchronize(ctx->stream));
     bool anyMoved = false;
-    for (int i = 0; i < R; ++i) { off[i + 1] = off[i] + got[2 * i]; anyMoved |= got[2 * i + 1] != 0; }
+    uint64_t minCap = ~0ull;
+    for (int i = 0; i < R; ++i) {
+        off[i + 1] = off[i] + got[3 * i];
+        anyMoved |= got[3 * i + 1] != 0;
+        minCap = std::min(minCap, got[3 * i + 2]);
+    }
     const uint64_t total = off[R];
     if (total >= BRE_MAX_PHOTONS) return set_err(ctx, BRE_ERR_UNSUPPORTED, "photon count exceeds 2^27");
-    // ---- capacity: the same decision on every rank (total is global), with 25 % head room
+    // ---- capacity: ONE decision for all ranks (total and the smallest store are global), with 25 % head room
     const size_t need = (size_t)total * 16;
-    const bool grow = ctx->pos_r.cap < need || ctx->pow.cap < need || ctx->dir.cap < need;
+    const bool grow = minCap < need;
     if (grow || anyMoved) {
         // everyone unmaps everyone first; only then may an exported store be freed
         p2p_close(ctx);
@@ -316,6 +339,119 @@ int trace_exchange_p2p(bre_ctx *ctx, uint64_t nPathsTotal, int maxDepth, float r
     if (r != 0) return nccl_err(ctx, r, "ncclAllGather(barrier)");
     BRE_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->n_photons = total;
+    return BRE_OK;
+}
+
+
+// ---------------------------------------------------------------- film gather (tile-sharded camera pass)
+// Every rank holds the accumulators of the 16x16 tiles bre_tile_owner gives it (integrators/photonbeam.cpp:
+// 345-347,444-477: the reference's tiles own their pixels too).  k_film_resolve_tiles resolves them
+// (L = Ld / (iter + 1), photonbeam.cpp:578; Film::SetImage / WriteImage arithmetic, core/film.cpp:132-140,168-204)
+// and writes the result straight into RANK 0's image buffer -- the local one on rank 0, a CUDA-IPC mapping over
+// NVLink on the others -- so the gather IS the resolve: no staging copy, no reduction (tiles are disjoint).
+// A one-word all-gather afterwards is the arrival barrier.  Rank 0's buffer is double-buffered by call parity:
+// a fast rank may already push image k + 1 while rank 0 still copies image k to the host.
+__device__ __forceinline__ float3 film_convert(float r, float g, float b, float scale, int meanOnly) {
+    if (meanOnly) return make_float3(r, g, b);
+    // RGBToXYZ spectrum.h:62-66, XYZToRGB spectrum.h:56-60, max(0, .) * scale film.cpp:178-201
+    float X = fadd(fadd(fmul(0.412453f, r), fmul(0.357580f, g)), fmul(0.180423f, b));
+    float Y = fadd(fadd(fmul(0.212671f, r), fmul(0.715160f, g)), fmul(0.072169f, b));
+    float Z = fadd(fadd(fmul(0.019334f, r), fmul(0.119193f, g)), fmul(0.950227f, b));
+    float R = fsub(fsub(fmul(3.240479f, X), fmul(1.537150f, Y)), fmul(0.498535f, Z));
+    float G = fadd(fadd(fmul(-0.969256f, X), fmul(1.875991f, Y)), fmul(0.041556f, Z));
+    float B = fadd(fsub(fmul(0.055648f, X), fmul(0.204043f, Y)), fmul(1.057311f, Z));
+    return make_float3(fmul(fmaxf(0.f, R), scale), fmul(fmaxf(0.f, G), scale), fmul(fmaxf(0.f, B), scale));
+}
+// one block per tile of the image, thread = pixel; tiles of other ranks return at once
+__global__ void __launch_bounds__(256) k_film_resolve_tiles(const float4 *__restrict__ film, uint32_t imgW, uint32_t imgH,
+                                                            uint32_t tilesX, float inv, float scale, int meanOnly,
+                                                            int nRanks, int rank, float *__restrict__ dst) {
+    const uint32_t tile = blockIdx.x;
+    if (nRanks > 1 && (int)(tile % (uint32_t)nRanks) != rank) return;
+    const uint32_t x = (tile % tilesX) * 16u + (threadIdx.x & 15u), y = (tile / tilesX) * 16u + (threadIdx.x >> 4);
+    if (x >= imgW || y >= imgH) return;
+    const size_t i = (size_t)y * imgW + x;
+    const float4 f = __ldg(film + i);
+    const float3 v = film_convert(fmul(f.x, inv), fmul(f.y, inv), fmul(f.z, inv), scale, meanOnly);
+    dst[3 * i + 0] = v.x; dst[3 * i + 1] = v.y; dst[3 * i + 2] = v.z;
+}
+
+int film_gather(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int meanOnly) {
+    if (!ctx->film.p) return set_err(ctx, BRE_ERR_INVALID, "bre_film_create has not been called");
+    const uint32_t n = ctx->n_pixels;
+    if (ctx->grid_w == 0 || (uint64_t)ctx->grid_w * ctx->grid_h != n)
+        return set_err(ctx, BRE_ERR_INVALID, "bre_film_gather needs the image layout (bre_set_ray_grid width * height == film pixels)");
+    const uint32_t W = ctx->grid_w, H = ctx->grid_h, tX = (W + 15) / 16, tY = (H + 15) / 16;
+    const int R = ctx->n_ranks;
+    const float inv = 1.f / (float)(iter + 1);
+    const size_t imgBytes = (size_t)n * 12;
+    int s;
+    if ((s = ensure(ctx, ctx->gather, 2 * imgBytes)) != BRE_OK) return s;
+    if (R == 1 || !ctx->tile_shard) {
+        if (ctx->rank == 0 && !rgb_out_host) return set_err(ctx, BRE_ERR_INVALID, "rank 0 needs an output array");
+        k_film_resolve_tiles<<<tX * tY, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, W, H, tX, inv, scale, meanOnly, 1, 0,
+                                                              (float *)ctx->gather.p);
+        BRE_CUDA(cudaGetLastError());
+        if (rgb_out_host) BRE_CUDA(cudaMemcpyAsync(rgb_out_host, ctx->gather.p, imgBytes, cudaMemcpyDeviceToHost, ctx->stream));
+        BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+        return BRE_OK;
+    }
+    if (!ctx->nccl_comm) return set_err(ctx, BRE_ERR_INVALID, "context was created without NCCL");
+    if (ctx->rank == 0 && !rgb_out_host) return set_err(ctx, BRE_ERR_INVALID, "rank 0 needs an output array");
+    ncclComm_p comm = (ncclComm_p)ctx->nccl_comm;
+    if ((s = ensure(ctx, ctx->counters_d, 16 * (size_t)(R + 1) + 64)) != BRE_OK) return s;
+    uint64_t *cnt_d = (uint64_t *)ctx->counters_d.p;
+    const size_t half = (size_t)(ctx->gather_calls & 1u) * imgBytes;
+    ++ctx->gather_calls;
+    if (ctx->p2p_disabled || R > MAX_P2P_RANKS) {
+        // NCCL path: every rank resolves its tiles into a zeroed local image, ncclReduce(sum) to rank 0 (disjoint tiles)
+        float *loc = (float *)((char *)ctx->gather.p + half);
+        BRE_CUDA(cudaMemsetAsync(loc, 0, imgBytes, ctx->stream));
+        k_film_resolve_tiles<<<tX * tY, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, W, H, tX, inv, scale, meanOnly, R,
+                                                              ctx->rank, loc);
+        BRE_CUDA(cudaGetLastError());
+        int r = g.Reduce(loc, loc, (size_t)n * 3, kNcclFloat, 0 /* ncclSum */, 0, comm, ctx->stream);
+        if (r != 0) return nccl_err(ctx, r, "ncclReduce(film)");
+        if (ctx->rank == 0) BRE_CUDA(cudaMemcpyAsync(rgb_out_host, loc, imgBytes, cudaMemcpyDeviceToHost, ctx->stream));
+        BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+        return BRE_OK;
+    }
+    // ---- rank 0's image buffer mapped on every rank (once per film size: every rank takes this branch together)
+    if (ctx->gather_mapped_pixels != n || ctx->gather_exported != ctx->gather.p) {
+        if (ctx->gather_peer0 && ctx->rank != 0) { cudaIpcCloseMemHandle(ctx->gather_peer0); }
+        ctx->gather_peer0 = nullptr;
+        cudaIpcMemHandle_t h;
+        memset(&h, 0, sizeof(h));
+        if (ctx->rank == 0) BRE_CUDA(cudaIpcGetMemHandle(&h, ctx->gather.p));
+        if ((s = ensure(ctx, ctx->p2p_scratch, 4096)) != BRE_OK) return s;
+        char *d = (char *)ctx->p2p_scratch.p;
+        BRE_CUDA(cudaMemcpyAsync(d, &h, sizeof(h), cudaMemcpyHostToDevice, ctx->stream));
+        int r = g.Broadcast(d, d, sizeof(h), 0 /* ncclChar */, 0, comm, ctx->stream);
+        if (r != 0) return nccl_err(ctx, r, "ncclBroadcast(film ipc handle)");
+        BRE_CUDA(cudaMemcpyAsync(&h, d, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+        BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ctx->rank == 0) ctx->gather_peer0 = ctx->gather.p;
+        else {
+            void *ptr = nullptr;
+            cudaError_t e = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+            if (e != cudaSuccess) {
+                cudaGetLastError();
+                return set_err(ctx, BRE_ERR_CUDA, std::string("cudaIpcOpenMemHandle(film): ") + cudaGetErrorString(e));
+            }
+            ctx->gather_peer0 = ptr;
+        }
+        ctx->gather_mapped_pixels = n;
+        ctx->gather_exported = ctx->gather.p;
+    }
+    float *dst = (float *)((char *)ctx->gather_peer0 + half);
+    k_film_resolve_tiles<<<tX * tY, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, W, H, tX, inv, scale, meanOnly, R, ctx->rank,
+                                                          dst);
+    BRE_CUDA(cudaGetLastError());
+    // arrival barrier: every rank's tiles have landed in rank 0's buffer
+    int r = g.AllGather(cnt_d + 2 * R, cnt_d, 1, kNcclUint64, comm, ctx->stream);
+    if (r != 0) return nccl_err(ctx, r, "ncclAllGather(film barrier)");
+    if (ctx->rank == 0) BRE_CUDA(cudaMemcpyAsync(rgb_out_host, dst, imgBytes, cudaMemcpyDeviceToHost, ctx->stream));
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
     return BRE_OK;
 }
 

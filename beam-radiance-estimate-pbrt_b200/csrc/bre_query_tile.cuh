@@ -410,7 +410,7 @@ __global__ void __launch_bounds__(TT_THREADS) k_tile_walk(
                 // (comparisons written so that a NaN anywhere makes the tile incoherent)
                 const bool coherent = !dead && bad == 0.f && twv >= 2 && thv >= 2 && wl2 > 1e-30f && g2 <= 0.25f &&
                                       oSp <= M * 0x1p-10f && pitch > 0.f && dev <= 2.f * pitch &&
-                                      fabsf(det) > 1e-3f * pitch * pitch && tFar < BIGF;
+                                      fabsf(det) > 1e-3f * pitch * pitch;     // (tFar may be +inf: no far cull)
                 if (!dead && !coherent) state = TS_INCOHERENT;
                 if (coherent) {
                     walk = true;

@@ -103,7 +103,8 @@ int bre_set_medium_grid(bre_ctx *ctx, const float sigma_a[3], const float sigma_
 /* scene.lights + ComputeLightPowerDistribution (core/integrator.cpp:217-225). */
 int bre_set_lights(bre_ctx *ctx, int n, const bre_light *lights);
 /* Absorbing axis-aligned scene box that ends photon paths (stand-in for Scene::Intersect,
- * core/scene.cpp:50-54, until the triangle intersector of SURVEY.md 8f-1 exists). */
+ * core/scene.cpp:50-54) for scenes given without triangles: it ends photon paths (K1) and, for the device
+ * camera (K0), the camera rays -- tMax = where the ray leaves the box. */
 int bre_set_bounds(bre_ctx *ctx, const float lo[3], const float hi[3]);
 /* Surfaces: Scene::Intersect (core/scene.cpp:50-54) over triangle shapes (shapes/triangle.cpp:177-392)
  * for device photon tracing (K1) and device camera rays (K0).  P = vertex positions xyz (as many as
@@ -248,7 +249,14 @@ int bre_film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out);
 /* rgb_out: n_pixels*3 floats = L = Ld/(iter+1) (integrators/photonbeam.cpp:578), no colour conversion:
  * the array a pbrt host passes to Film::SetImage (core/film.cpp:132-140) before Film::WriteImage. */
 int bre_film_mean(bre_ctx *ctx, int iter, float *rgb_out);
-/* Multi-GPU: after resolve on every rank, gather disjoint pixel ranges to rank 0. */
+/* Multi-GPU camera pass (bre_set_tile_sharding): every rank resolves the 16x16 tiles it owns (bre_tile_owner,
+ * integrators/photonbeam.cpp:345-347) and writes them straight into rank 0's image over NVLink (CUDA-IPC
+ * mapping; BRE_NO_P2P=1: ncclReduce of disjoint tiles).  Collective: every rank calls it with the same iter /
+ * scale / mean_only; rgb_out (n_pixels*3 floats) is filled on rank 0 only and may be NULL on the others.
+ * The image layout comes from bre_set_ray_grid (width * height == film pixels).  mean_only = 1 gives
+ * L = Ld/(iter+1) like bre_film_mean, 0 the Film::WriteImage arithmetic like bre_film_resolve.  With one rank
+ * (or sharding off) it is a plain resolve. */
+int bre_film_gather(bre_ctx *ctx, int iter, float scale, float *rgb_out, int mean_only);
 
 /* ---- on-disk interchange -----------------------------------------------
  * Photon file: 64-byte header {"BREPHOT\0", u32 version = 1, u32 0, u64 n, u64 n_paths, zeros} then

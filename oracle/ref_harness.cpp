@@ -62,7 +62,10 @@
 #include "transform.h"
 
 #include "ref_access.h"
+#include "photonbeambvh.h"
+#include "parallel.h"
 #include <atomic>
+#include <chrono>
 #include <thread>
 
 using namespace pbrt;
@@ -820,6 +823,79 @@ void gridtr(const char *path, const char *densPath, int nx, int ny, int nz, cons
     fprintf(stderr, "gridtr: %zu rays, %d samples each, grid %dx%dx%d\n", nRays, nSamples, nx, ny, nz);
 }
 
+// ---------------------------------------------------------------- mode: bvhquery
+// the reference's OWN photon-BVH code timed on the benchmark's photons.  Every photon becomes a
+// short PhotonBeam (length 1e-3 r along its direction, radius r) so that the unmodified PhotonBeamBVH (SAH build,
+// core/photonbeambvh.cpp:204-425) can hold it; camera rays walk it with the unmodified PhotonBeamBVH::Intersect
+// (collect-all traversal, :685-723, incl. its vector<shared_ptr> result) on all host threads (ParallelFor,
+// core/parallel.h:101-102), and every candidate runs the photon-disk predicate of the oracle.  A TIMING of
+// reference code, not a parity vector: PhotonBeam::WorldBound is not conservative (core/photonbeambvh.h:60-72,
+// SURVEY.md 7), so a few hits are culled -- the harness prints how many of the brute-force hits it found.
+// photons.bin: n x {p.xyz, r}; rays.bin: n x {o.xyz, d.xyz, tMax, 0}.
+void bvhquery(const char *photonPath, const char *rayPath, int nThreads, double maxSeconds) {
+    auto slurp = [](const char *path) {
+        std::vector<float> v;
+        FILE *f = fopen(path, "rb");
+        if (!f) { perror(path); exit(1); }
+        float buf[4096];
+        size_t got;
+        while ((got = fread(buf, 4, 4096, f)) > 0) v.insert(v.end(), buf, buf + got);
+        fclose(f);
+        return v;
+    };
+    const std::vector<float> ph = slurp(photonPath), ry = slurp(rayPath);
+    const size_t n = ph.size() / 4, nq = ry.size() / 8;
+    PbrtOptions.nThreads = nThreads;
+    ParallelInit();
+    std::vector<std::shared_ptr<PhotonBeam>> beams;
+    beams.reserve(n);
+    RNG rng(7);
+    for (size_t i = 0; i < n; ++i) {
+        const Point3f p(ph[4 * i], ph[4 * i + 1], ph[4 * i + 2]);
+        const float r = ph[4 * i + 3];
+        const Vector3f w = unit_from(rng) * (0.5e-3f * r);
+        beams.push_back(std::make_shared<PhotonBeam>(p - w, p + w, r, Spectrum(0.f), Spectrum(1.f)));
+    }
+    auto t0 = std::chrono::steady_clock::now();
+    PhotonBeamBVH bvh(std::move(beams));
+    const double buildS = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    std::atomic<uint64_t> cand(0), hits(0), done(0);
+    const int chunk = 256;
+    t0 = std::chrono::steady_clock::now();
+    double spent = 0;
+    size_t q0 = 0;
+    while (spent < maxSeconds) {
+        if (q0 >= nq) q0 = 0;                    // a short ray file is walked again until the time is up
+        const size_t q1 = std::min(nq, q0 + (size_t)chunk * 64);
+        ParallelFor([&](int64_t c) {
+            uint64_t lc = 0, lh = 0;
+            for (size_t q = q0 + (size_t)c * chunk; q < std::min(q1, q0 + (size_t)(c + 1) * chunk); ++q) {
+                const float *v = &ry[8 * q];
+                Ray ray(Point3f(v[0], v[1], v[2]), Vector3f(v[3], v[4], v[5]), v[6]);
+                auto got = bvh.Intersect(ray);
+                lc += got.size();
+                for (auto &b : got) {
+                    const Point3f p = b->start + (b->end - b->start) * 0.5f;
+                    const Vector3f pv = p - ray.o;
+                    const float t = Dot(pv, ray.d);
+                    if (!(t > 0 && t < ray.tMax)) continue;
+                    const Vector3f wv = pv - t * ray.d;
+                    if (Dot(wv, wv) < b->radius * b->radius) ++lh;
+                }
+            }
+            cand += lc; hits += lh;
+        }, (int64_t)((q1 - q0 + chunk - 1) / chunk), 1);
+        done += q1 - q0;
+        q0 = q1;
+        spent = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    }
+    ParallelCleanup();
+    printf("{\"photons\": %zu, \"rays\": %llu, \"threads\": %d, \"build_s\": %.3f, \"query_s\": %.3f, "
+           "\"queries_per_s\": %.1f, \"candidates\": %llu, \"hits\": %llu}\n",
+           n, (unsigned long long)done.load(), nThreads, buildS, spent, (double)done.load() / spent,
+           (unsigned long long)cand.load(), (unsigned long long)hits.load());
+}
+
 }  // namespace
 
 int main(int argc, char **argv) {
@@ -836,6 +912,10 @@ int main(int argc, char **argv) {
     }
     if (argc >= 8 && !strcmp(argv[1], "surfaces")) {
         surfaces(argv[2], strtoull(argv[3], 0, 10), strtoull(argv[4], 0, 10), atoi(argv[5]), atoi(argv[6]), atoi(argv[7]));
+        return 0;
+    }
+    if (argc >= 6 && !strcmp(argv[1], "bvhquery")) {
+        bvhquery(argv[2], argv[3], atoi(argv[4]), atof(argv[5]));
         return 0;
     }
     if (argc >= 13 && !strcmp(argv[1], "gridtr")) {

@@ -9,6 +9,7 @@
 #include <cstdlib>
 #include <iostream>
 #include <sstream>
+#include <string>
 
 namespace bre_shim {
 struct NullStream {
@@ -65,5 +66,11 @@ template <typename T> T CheckNotNull(const char *file, int line, const char *wha
 #define BRE_SHIM_LOG_FATAL ::bre_shim::FatalStream(__FILE__, __LINE__, "FATAL")
 #define LOG(sev) BRE_SHIM_LOG_##sev
 #define VLOG(n) ::bre_shim::NullStream()
+
+// main/pbrt.cpp (the reference's command line, built unmodified into oracle/_ref/pbrt) sets glog's flags
+namespace google { inline void InitGoogleLogging(const char *) {} }
+static int FLAGS_stderrthreshold = 1, FLAGS_minloglevel = 0, FLAGS_v = 0;
+static bool FLAGS_logtostderr = false;
+static std::string FLAGS_log_dir;
 
 #endif

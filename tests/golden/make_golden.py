@@ -13,6 +13,8 @@ compressed .npz fixtures.  The fixtures travel to the GPU box; /root/reference d
                              beam radiance estimate evaluated with reference arithmetic classes
   ref_trace_homogeneous.npz  volume-photon deposit loop executed by reference classes
   ref_trace_grid.npz         (sampler stream of photonbeam.cpp:386-391, deposit rule photonmap.cpp:696-724)
+  ref_gridtr.npz             GridDensityMedium::Tr statistics + fine integral of the reference's Density() through the
+                             64^3 / 256^3 smoke grids of bench.py: pins the optical-depth table at the product's steps
   ref_surfaces.npz           photon paths bouncing off matte triangle walls (photonbeam.cpp:296-323) and
                              crossing an interface-only medium boundary, walked by reference classes;
                              camera rays of a cropped PerspectiveCamera with first-hit tMax
@@ -48,7 +50,46 @@ def read_bref(path):
     return out
 
 
+def gridtr(tmp, n_rays=24, n_samples=4_000_000):
+    """ref_gridtr.npz: the reference's GridDensityMedium::Tr (mean / standard error of n_samples evaluations) and the
+    fine integral of the reference's own Density() along camera rays of bench.py's smoke scenes -- the 64^3 grid of
+    smoke10m_1080p and the 256^3 grid of smoke50m_4k -- from the ray origin to a random depth t.  Pins the product's
+    deterministic optical-depth table AT THE STEP COUNT IT RUNS WITH (tests/test_oracle_golden.py).  The density
+    grids are not stored: bench.smoke_density(n) regenerates them (a checksum is kept)."""
+    sys.path.insert(0, ROOT)
+    import bench
+    out = {}
+    for n in (64, 256):
+        dens = bench.smoke_density(n)
+        dp = os.path.join(tmp, f"dens{n}.bin")
+        dens.tofile(dp)
+        rng = np.random.default_rng(1000 + n)
+        ro, rd = bench.camera_rays(1920, 1080)
+        live = np.nonzero(ro[:, 3] > 0)[0]
+        pick = rng.choice(live, n_rays, replace=False)
+        rays = np.zeros((n_rays, 8), np.float32)
+        rays[:, :3] = ro[pick, :3]
+        rays[:, 3:6] = rd[pick]
+        # the camera sits outside the box: the medium spans roughly t in [tMax - 1.1, tMax]
+        rays[:, 6] = ro[pick, 3] - (rng.random(n_rays) * 0.9).astype(np.float32)
+        rays[: n_rays // 3, 6] = ro[pick[: n_rays // 3], 3]          # a third of them all the way through
+        rp = os.path.join(tmp, f"rays{n}.bin")
+        rays.tofile(rp)
+        ob = os.path.join(tmp, f"gridtr{n}.bin")
+        subprocess.check_call([HARNESS, "gridtr", ob, dp, str(n), str(n), str(n), rp, str(n_samples),
+                               str(bench.SIGMA_A[0]), str(bench.SIGMA_S[0]), repr(float(bench.ASPECT)),
+                               repr(float(bench.BOX_LO[0]))])
+        for k, v in read_bref(ob).items():
+            out[f"g{n}/{k}"] = v
+        out[f"g{n}/density_sum"] = np.array([dens.astype(np.float64).sum()])
+    np.savez_compressed(os.path.join(HERE, "ref_gridtr.npz"), **out)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "gridtr":       # only this fixture
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "ref", "-j8"])
+        gridtr(tempfile.mkdtemp())
+        return
     if not os.path.isdir("/root/reference/src"):
         sys.exit("the reference is not mounted here; fixtures can only be regenerated where it is")
     subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "ref", "-j8"])
@@ -76,6 +117,7 @@ def main():
     sb = os.path.join(tmp, "surfaces.bin")
     subprocess.check_call([HARNESS, "surfaces", sb, "0", "4000", "6", "64", "48"])
     np.savez_compressed(os.path.join(HERE, "ref_surfaces.npz"), **read_bref(sb))
+    gridtr(tmp)
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)), "bytes")

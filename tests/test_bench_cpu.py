@@ -22,7 +22,44 @@ def test_workloads_name_the_baseline_configs():
     assert wl["fog1m_1080p"]["grid"] == 0 and wl["fog1m_1080p"]["photons"] == 1_000_000      # configs[1]: homogeneous fog
     assert wl["smoke50m_4k"]["photons"] == 50_000_000 and (wl["smoke50m_4k"]["w"], wl["smoke50m_4k"]["h"]) == (3840, 2160)
     assert len(b.scene_lights(wl["fog1m_1080p"])) == 1 and len(b.scene_lights(wl["smoke10m_1080p"])) == 2
-    assert b.launches_per_step(1, wl["fog1m_1080p"]) + 1 == b.launches_per_step(1, wl["smoke10m_1080p"]) == 39
+    # both arms print the same config keys (the driver compares them)
+    assert set(b.base_config("smoke10m_1080p", wl["smoke10m_1080p"])) == set(b.base_config("fog1m_1080p", wl["fog1m_1080p"]))
+
+
+def test_camera_matrices_describe_the_same_pinhole_as_camera_rays():
+    """bre_camera of the end-to-end path (K0) vs the numpy rays of the device-resident path."""
+    b = load_bench()
+    w, h = 64, 36
+    r2c, c2w = b.camera_matrices(w, h)
+    _, d = b.camera_rays(w, h)
+    ys, xs = np.meshgrid(np.arange(h) + 0.5, np.arange(w) + 0.5, indexing="ij")
+    p = np.stack([xs.ravel(), ys.ravel(), np.zeros(w * h), np.ones(w * h)], axis=1) @ r2c.T.astype(np.float64)
+    pc = p[:, :3] / p[:, 3:4]
+    pc /= np.linalg.norm(pc, axis=1, keepdims=True)
+    assert np.allclose(pc @ c2w[:3, :3].T.astype(np.float64), d, atol=1e-6)
+    assert np.allclose(c2w[:3, 3], b.EYE)
+    # per-rank sample offsets of the weak-scaling mode move the rays inside their pixels
+    _, d2 = b.camera_rays(w, h, off=(0.25, 0.75))
+    assert not np.array_equal(d, d2) and np.abs(d - d2).max() < 2.0 / h
+
+
+def test_reference_arm_runs_the_unmodified_pbrt_binary():
+    """bench.py --impl reference: one bounded run of oracle/_ref/pbrt (Integrator "photonbeam") per step."""
+    import json
+    import subprocess
+    import sys
+    import pytest
+    b = load_bench()
+    if not os.path.exists(b.PBRT_BIN):
+        pytest.skip("oracle/_ref/pbrt has not been built (make -C oracle pbrt needs /root/reference)")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0",
+                        "--no-port", "--ref-photons", "3000", "--ref-crop", "0.06"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["cpu_baseline"]["kind"] == "reference" and line["value"] > 0
+    assert line["e2e"]["value"] == line["value"] and line["e2e"]["h2d_bytes_per_step"] == 0
+    assert set(line["config"]) == set(b.base_config("smoke10m_1080p", b.WORKLOADS["smoke10m_1080p"]))
+    assert line["cpu_baseline"]["pbrt_profile_s"]["camera_pass"] > 0 and "photonbeam" in line["cpu_baseline"]["sample"]
 
 
 def test_camera_rays_are_unit_and_end_at_the_medium_box():

@@ -26,3 +26,15 @@ def test_fused_trace_push_equals_nccl_allgather_and_single_rank():
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert r.stdout.count("True") >= 10
+
+
+@pytest.mark.skipif(_n_gpus() < 2, reason="needs two GPUs on one box")
+def test_tile_sharded_render_equals_single_gpu():
+    """tools/check_tiles.py under torchrun, world size 2: the tile-sharded camera pass + film gather reproduces the
+    single-GPU render (per-ray hit sets bit-exact on the owned tiles, image within 1e-4 mean / 1e-3 max), over
+    the P2P push and the NCCL reduce."""
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", "29537", os.path.join(ROOT, "tools", "check_tiles.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert r.stdout.count("False") == 0 and r.stdout.count("True") >= 12

@@ -225,3 +225,40 @@ def test_tile_path_matches_packet_path_radiance(oracle, ctx):
     ctx.set_ray_grid(0, 0)
     b = ctx.query(ro, rd, float(n))
     assert_radiance(a, b.astype(np.float64))
+
+
+def test_grid_medium_auto_tau_steps_match_the_oracle(oracle, ctx):
+    """bench.py's 64^3 smoke grid: the library picks its optical-depth table steps from the grid
+    (bre_config.tau_steps = 0 -> 96) exactly like the oracle (orc_tau_steps_auto, pinned against the reference's
+    GridDensityMedium::Tr in tests/test_oracle_golden.py); radiance of photons traced ON THE DEVICE through
+    that medium agrees with the oracle on both K5 paths, with the tile-blocked and the per-ray table layout."""
+    import bench
+    wl = dict(bench.WORKLOADS["smoke10m_1080p"], photons=60000)
+    bench.setup_scene(ctx, wl)
+    dens = bench.set_medium(oracle, wl)
+    assert oracle.medium.tau_steps == 96 and dens.shape == (64, 64, 64)
+    radius = 0.02
+    n = ctx.trace_photons(0, 25000, bench.MAX_DEPTH, radius)
+    pos, pw, dr, rad = ctx.download_photons()
+    assert n == pos.shape[0] > 30000
+    oracle.set_photons(pos, pw, dr, rad)
+    ctx.build()
+    w, h = 96, 54
+    ro, rd = bench.camera_rays(w, h)
+    ref_rgb, ref_offs, ref_idx, _ = oracle.query(ro, rd, 25000.0, want_hits=True, brute=True)
+    assert ref_offs[-1] > 10000
+    for grid in ((w, h), (0, 0)):
+        ctx.set_ray_grid(*grid)
+        rgb, offs, idx = ctx.query(ro, rd, 25000.0, want_hits=True)
+        assert np.array_equal(offs, ref_offs) and np.array_equal(idx, ref_idx)
+        assert_radiance(rgb, ref_rgb)
+    # the device camera (K0) clips its rays at the absorbing scene box when there are no triangles
+    r2c, c2w = bench.camera_matrices(w, h)
+    ctx.set_camera(r2c, c2w, 0, 0, w, h, True)
+    o2, d2 = ctx.camera_rays()
+    assert np.allclose(o2[:, 3], ro[:, 3], rtol=2e-6, atol=1e-6) and np.allclose(d2, rd, atol=2e-7)
+    ctx.film_create(w * h)
+    ctx.query_camera_to_film(25000.0)
+    img = ctx.film_mean(0)
+    ref2, _ = oracle.query(o2, d2, 25000.0)
+    assert_radiance(img, ref2)
