@@ -388,7 +388,6 @@ int film_gather(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int me
     int s;
     if ((s = ensure(ctx, ctx->gather, 2 * imgBytes)) != BRE_OK) return s;
     if (R == 1 || !ctx->tile_shard) {
-        if (ctx->rank == 0 && !rgb_out_host) return set_err(ctx, BRE_ERR_INVALID, "rank 0 needs an output array");
         k_film_resolve_tiles<<<tX * tY, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, W, H, tX, inv, scale, meanOnly, 1, 0,
                                                               (float *)ctx->gather.p);
         BRE_CUDA(cudaGetLastError());
@@ -397,7 +396,7 @@ int film_gather(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int me
         return BRE_OK;
     }
     if (!ctx->nccl_comm) return set_err(ctx, BRE_ERR_INVALID, "context was created without NCCL");
-    if (ctx->rank == 0 && !rgb_out_host) return set_err(ctx, BRE_ERR_INVALID, "rank 0 needs an output array");
+    // (rgb_out_host may be NULL on rank 0 too: the assembled image then stays in rank 0's device buffer)
     ncclComm_p comm = (ncclComm_p)ctx->nccl_comm;
     if ((s = ensure(ctx, ctx->counters_d, 16 * (size_t)(R + 1) + 64)) != BRE_OK) return s;
     uint64_t *cnt_d = (uint64_t *)ctx->counters_d.p;
@@ -412,7 +411,7 @@ int film_gather(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int me
         BRE_CUDA(cudaGetLastError());
         int r = g.Reduce(loc, loc, (size_t)n * 3, kNcclFloat, 0 /* ncclSum */, 0, comm, ctx->stream);
         if (r != 0) return nccl_err(ctx, r, "ncclReduce(film)");
-        if (ctx->rank == 0) BRE_CUDA(cudaMemcpyAsync(rgb_out_host, loc, imgBytes, cudaMemcpyDeviceToHost, ctx->stream));
+        if (ctx->rank == 0 && rgb_out_host) BRE_CUDA(cudaMemcpyAsync(rgb_out_host, loc, imgBytes, cudaMemcpyDeviceToHost, ctx->stream));
         BRE_CUDA(cudaStreamSynchronize(ctx->stream));
         return BRE_OK;
     }
@@ -450,7 +449,7 @@ int film_gather(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int me
     // arrival barrier: every rank's tiles have landed in rank 0's buffer
     int r = g.AllGather(cnt_d + 2 * R, cnt_d, 1, kNcclUint64, comm, ctx->stream);
     if (r != 0) return nccl_err(ctx, r, "ncclAllGather(film barrier)");
-    if (ctx->rank == 0) BRE_CUDA(cudaMemcpyAsync(rgb_out_host, dst, imgBytes, cudaMemcpyDeviceToHost, ctx->stream));
+    if (ctx->rank == 0 && rgb_out_host) BRE_CUDA(cudaMemcpyAsync(rgb_out_host, dst, imgBytes, cudaMemcpyDeviceToHost, ctx->stream));
     BRE_CUDA(cudaStreamSynchronize(ctx->stream));
     return BRE_OK;
 }

@@ -252,7 +252,8 @@ int bre_film_mean(bre_ctx *ctx, int iter, float *rgb_out);
 /* Multi-GPU camera pass (bre_set_tile_sharding): every rank resolves the 16x16 tiles it owns (bre_tile_owner,
  * integrators/photonbeam.cpp:345-347) and writes them straight into rank 0's image over NVLink (CUDA-IPC
  * mapping; BRE_NO_P2P=1: ncclReduce of disjoint tiles).  Collective: every rank calls it with the same iter /
- * scale / mean_only; rgb_out (n_pixels*3 floats) is filled on rank 0 only and may be NULL on the others.
+ * scale / mean_only; rgb_out (n_pixels*3 floats) is filled on rank 0 only and may be NULL on the others (NULL on
+ * rank 0 too: the assembled image stays in rank 0's device buffer).
  * The image layout comes from bre_set_ray_grid (width * height == film pixels).  mean_only = 1 gives
  * L = Ld/(iter+1) like bre_film_mean, 0 the Film::WriteImage arithmetic like bre_film_resolve.  With one rank
  * (or sharding off) it is a plain resolve. */

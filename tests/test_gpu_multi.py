@@ -37,4 +37,5 @@ def test_tile_sharded_render_equals_single_gpu():
            "--master-addr", "127.0.0.1", "--master-port", "29537", os.path.join(ROOT, "tools", "check_tiles.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    assert r.stdout.count("False") == 0 and r.stdout.count("True") >= 12
+    lines = [ln.split(":", 1)[1] for ln in r.stdout.splitlines() if ln.startswith("rank ")]
+    assert len(lines) >= 5 and all("False" not in ln for ln in lines), r.stdout[-2000:]

@@ -7,7 +7,7 @@ answers ONLY the 16x16 tiles bre_tile_owner gives it, and rank 0 gathers the fil
   * the photon store equals the single-rank store bit for bit;
   * per-ray hit-index sets: equal to the single-rank sets on owned tiles, empty elsewhere;
   * rank 0's gathered image equals the single-rank image within 1e-4 mean / 1e-3 max (float atomics);
-  * P2P gather == NCCL-reduce gather (BRE_NO_P2P contexts) bit for bit.
+  * fed with the single-rank radiance, the gather (P2P push and NCCL reduce) reproduces the single-rank image bit for bit.
 Prints one line per rank, exits 1 on any mismatch.
 """
 import ctypes
@@ -56,8 +56,13 @@ def main():
     solo.build()
     solo.set_ray_grid(W, H)
     s_rgb, s_offs, s_idx = solo.query(ro, rd, float(n_paths), want_hits=True)
+    # radiance carries the order of its float atomics: every rank uses RANK 0's single-rank radiance as the input
+    # of the exact-gather check below
+    t = torch.from_numpy(s_rgb).cuda()
+    dist.broadcast(t, 0)
+    s_rgb0 = t.cpu().numpy()
     solo.film_create(W * H)
-    solo.film_accumulate(s_rgb)
+    solo.film_accumulate(s_rgb0)
     s_img = solo.film_resolve(0, 1.0)
     s_store = solo.download_photons()
 
@@ -83,16 +88,32 @@ def main():
         c.film_accumulate(rgb)
         img = c.film_gather(0, 1.0, want=(rank == 0))
         img_ok = True
+        why = ""
         if rank == 0:
             err = np.abs(img.astype(np.float64) - s_img)
             img_ok = err.mean() <= 1e-4 * np.abs(s_img).mean() and err.max() <= 1e-3 * np.abs(s_img).max()
+            if not img_ok:
+                why += f" render mean {err.mean() / np.abs(s_img).mean():.2e} max {err.max() / np.abs(s_img).max():.2e}"
             imgs.append(img)
         # a second gather (other half of rank 0's double buffer) gives the same image
         img2 = c.film_gather(0, 1.0, want=(rank == 0))
         if rank == 0:
+            if not np.array_equal(img, img2):
+                why += " second-gather"
             img_ok = img_ok and np.array_equal(img, img2)
+        # the gather itself is exact: fed with the single-rank radiance of its own tiles, every rank's film
+        # assembles to the single-rank image bit for bit
+        c.film_clear()
+        c.film_accumulate(s_rgb0 * mine[:, None])
+        img3 = c.film_gather(0, 1.0, want=(rank == 0))
+        if rank == 0:
+            if not np.array_equal(img3, s_img):
+                bad = np.nonzero((img3 != s_img).any(axis=1))[0]
+                why += f" exact-gather {bad.size} px first {bad[:5].tolist()} {img3[bad[:2]].tolist()} vs {s_img[bad[:2]].tolist()}"
+            img_ok = img_ok and np.array_equal(img3, s_img)
+            imgs[-1] = img3
         print(f"rank {rank} no_p2p={no_p2p}: store {same_store} hits {hits_ok} image {img_ok} "
-              f"(owned rays {int(mine.sum())}, hits {int(cnt.sum())})", flush=True)
+              f"(owned rays {int(mine.sum())}, hits {int(cnt.sum())}){why}", flush=True)
         ok = ok and same_store and hits_ok and img_ok
         dist.barrier()
         c.close()
