@@ -31,6 +31,11 @@
 #include "scene.h"
 #include "stats.h"
 
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <thread>
+
 namespace pbrt {
 
 namespace {
@@ -49,6 +54,50 @@ class PathSampler : public Sampler {
     std::unique_ptr<Sampler> Clone(int) override { return nullptr; }
     RNG rng;
 };
+
+// ---- multi-GPU launch environment: one pbrt process per GPU ----------------------------------------
+int EnvInt(const char *const names[], int n, int dflt) {
+    for (int i = 0; i < n; ++i) {
+        const char *v = getenv(names[i]);
+        if (v && *v) return atoi(v);
+    }
+    return dflt;
+}
+struct RankInfo { int rank = 0, nRanks = 1, localRank = 0; };
+RankInfo FindRank() {
+    static const char *const r[] = {"BRE_RANK", "OMPI_COMM_WORLD_RANK", "RANK"};
+    static const char *const n[] = {"BRE_NRANKS", "OMPI_COMM_WORLD_SIZE", "WORLD_SIZE"};
+    static const char *const l[] = {"BRE_LOCAL_RANK", "OMPI_COMM_WORLD_LOCAL_RANK", "LOCAL_RANK"};
+    RankInfo ri;
+    ri.nRanks = std::max(1, EnvInt(n, 3, 1));
+    ri.rank = std::min(std::max(0, EnvInt(r, 3, 0)), ri.nRanks - 1);
+    ri.localRank = EnvInt(l, 3, ri.rank);
+    return ri;
+}
+// rank 0 creates the NCCL id and publishes it through a file; the others wait for the complete file
+bool ShareNcclId(const RankInfo &ri, unsigned char id[128]) {
+    const char *path = getenv("BRE_NCCL_ID_FILE");
+    if (!path || !*path) { Error("bre: %d ranks but BRE_NCCL_ID_FILE is not set", ri.nRanks); return false; }
+    if (ri.rank == 0) {
+        if (bre_nccl_unique_id(id) != BRE_OK) { Error("bre: bre_nccl_unique_id failed (libnccl.so.2 missing?)"); return false; }
+        const std::string tmp = std::string(path) + ".tmp";
+        FILE *f = fopen(tmp.c_str(), "wb");
+        if (!f || fwrite(id, 1, 128, f) != 128) { Error("bre: cannot write %s", tmp.c_str()); if (f) fclose(f); return false; }
+        fclose(f);
+        return rename(tmp.c_str(), path) == 0;
+    }
+    for (int tries = 0; tries < 6000; ++tries) {          // up to ~60 s
+        FILE *f = fopen(path, "rb");
+        if (f) {
+            const size_t got = fread(id, 1, 128, f);
+            fclose(f);
+            if (got == 128) return true;
+        }
+        std::this_thread::sleep_for(std::chrono::milliseconds(10));
+    }
+    Error("bre: rank %d never saw the NCCL id file %s", ri.rank, path);
+    return false;
+}
 
 bool Check(bre_ctx *ctx, int status, const char *what) {
     if (status == BRE_OK) return true;
@@ -261,9 +310,15 @@ void BreIntegrator::Render(const Scene &scene) {
         Error("bre: nothing to render (camera outside any medium, or rendermedia false)");
         return;
     }
+    const RankInfo ri = FindRank();
+    unsigned char ncclId[128];
+    if (ri.nRanks > 1 && !ShareNcclId(ri, ncclId)) return;
     bre_ctx *ctx = nullptr;
     bre_config cfg = {};
-    cfg.device = device; cfg.n_ranks = 1;
+    cfg.device = device >= 0 ? device : ri.localRank;
+    cfg.n_ranks = ri.nRanks; cfg.rank = ri.rank;
+    cfg.nccl_unique_id = ri.nRanks > 1 ? ncclId : nullptr;
+    const bool sharded = ri.nRanks > 1;
     int st = bre_create(&ctx, &cfg);
     if (st != BRE_OK) {
         Error("bre: bre_create failed (%d): a CUDA device is required, there is no CPU fallback", st);
@@ -304,10 +359,25 @@ void BreIntegrator::Render(const Scene &scene) {
     }
     std::unique_ptr<Spectrum[]> image(new Spectrum[nPixels]);
     if (!Check(ctx, bre_film_create(ctx, nPixels), "bre_film_create")) { bre_destroy(ctx); return; }
+    // the camera pass visits the image tile by tile (photonbeam.cpp:345-347,444-477): tell the library the layout
+    if (!Check(ctx, bre_set_ray_grid(ctx, (uint32_t)ext.x, (uint32_t)ext.y), "bre_set_ray_grid")) { bre_destroy(ctx); return; }
+    if (sharded) bre_set_tile_sharding(ctx, 1);
 
+    // radius schedule fast-forwarded to startiteration (photonbeam.cpp:354-356)
     Float radius = initialRadius;
-    ProgressReporter progress(nIterations, "Rendering (bre)");
-    for (int iter = 0; iter < nIterations; ++iter) {
+    for (int i = 0; i < startIteration; ++i) radius *= (i + alpha) / (i + 1);
+    if (startIteration > 0 && !checkpoint.empty()) {
+        // resume the SAME estimate: accumulators of the iterations already done (the reference restores the radius only)
+        uint64_t done = 0;
+        float rSaved = 0;
+        if (bre_film_load(ctx, checkpoint.c_str(), &done, &rSaved) == BRE_OK) {
+            if ((int)done != startIteration)
+                Warning("bre: checkpoint %s holds %d iterations, startiteration is %d", checkpoint.c_str(), (int)done, startIteration);
+        } else
+            Warning("bre: cannot load checkpoint %s (%s): starting from an empty film", checkpoint.c_str(), bre_last_error(ctx));
+    }
+    ProgressReporter progress(std::max(0, endIteration - startIteration), "Rendering (bre)");
+    for (int iter = startIteration; iter < endIteration; ++iter) {
         // iteration 0 looks through the pixel centres, later ones use a (2,3) Halton offset
         const Point2f off = iter == 0 ? Point2f(0.5f, 0.5f)
                                       : Point2f(RadicalInverse(0, iter), RadicalInverse(1, iter));
@@ -342,11 +412,20 @@ void BreIntegrator::Render(const Scene &scene) {
                           : Check(ctx, bre_set_radius(ctx, radius), "bre_set_radius");
         uint64_t stored = 0;
         if (!retrace) {
-        } else if (ok && deviceTracer)
-            ok = Check(ctx, bre_trace_photons(ctx, (uint64_t)iter * nPaths, nPaths, maxDepth, radius, &stored),
-                       "bre_trace_photons");
-        else if (ok)
-            stored = TracePhotonsHost(ctx, scene, *lightDistr, (uint64_t)iter * nPaths, nPaths, radius);
+        } else if (ok && deviceTracer && sharded && iter == 0) {
+            // fused: every rank traces its slice of [0, nPaths) and pushes it into everyone's store over NVLink.
+            // (The collective traces path indices from 0; later iterations of a sharded render use the split below.)
+            ok = Check(ctx, bre_trace_exchange_photons(ctx, nPaths, maxDepth, radius, &stored), "bre_trace_exchange_photons");
+        } else if (ok) {
+            uint64_t first = 0, count = nPaths;
+            bre_shard_range(nPaths, ri.nRanks, ri.rank, &first, &count);
+            if (deviceTracer)
+                ok = Check(ctx, bre_trace_photons(ctx, (uint64_t)iter * nPaths + first, count, maxDepth, radius, &stored),
+                           "bre_trace_photons");
+            else
+                stored = TracePhotonsHost(ctx, scene, *lightDistr, (uint64_t)iter * nPaths + first, count, radius);
+            if (ok && sharded) ok = Check(ctx, bre_allgather_photons(ctx), "bre_allgather_photons");
+        }
         lastPathsEmitted = nPaths;
         // ---- photon structure (photonbeam.cpp:438)
         ok = ok && Check(ctx, bre_build(ctx), "bre_build");
@@ -361,15 +440,22 @@ void BreIntegrator::Render(const Scene &scene) {
         // ---- progressive radius (photonbeam.cpp:562)
         radius *= (iter + alpha) / (iter + 1);
         // ---- film (photonbeam.cpp:565-584)
-        if (iter + 1 == nIterations || ((iter + 1) % writeFrequency) == 0) {
-            if (!Check(ctx, bre_film_mean(ctx, iter, mean.data()), "bre_film_mean")) break;
-            for (uint32_t i = 0; i < nPixels; ++i) {
-                Float rgb[3] = {mean[3 * i], mean[3 * i + 1], mean[3 * i + 2]};
-                image[i] = Spectrum::FromRGB(rgb);
+        // writeFrequency is the reference's: its default 1 << 31 (INT_MIN) never divides iter + 1, so only the last
+        // iteration writes; 0 would divide by zero there and is treated as "never" here
+        if (iter + 1 == endIteration || (writeFrequency != 0 && ((iter + 1) % writeFrequency) == 0)) {
+            // L = Ld / (iter + 1), photonbeam.cpp:578; sharded: the ranks' tiles are gathered on rank 0 (collective)
+            if (!Check(ctx, bre_film_gather(ctx, iter, 1.f, ri.rank == 0 ? mean.data() : nullptr, 1), "bre_film_gather")) break;
+            if (ri.rank == 0) {
+                for (uint32_t i = 0; i < nPixels; ++i) {
+                    Float rgb[3] = {mean[3 * i], mean[3 * i + 1], mean[3 * i + 2]};
+                    image[i] = Spectrum::FromRGB(rgb);
+                }
+                camera->film->SetImage(image.get());
+                camera->film->WriteImage();
             }
-            camera->film->SetImage(image.get());
-            camera->film->WriteImage();
         }
+        if (iter + 1 == endIteration && !checkpoint.empty() && !sharded)
+            Check(ctx, bre_film_save(ctx, checkpoint.c_str(), (uint64_t)endIteration, (float)radius), "bre_film_save");
         progress.Update();
         (void)stored;
     }
@@ -384,21 +470,37 @@ Integrator *CreateBreIntegrator(const ParamSet &params, std::shared_ptr<const Ca
     int maxDepth = params.FindOneInt("maxdepth", params.FindOneInt("maxphotondepth", 5));
     int photonsPerIter = params.FindOneInt("photonsperiteration", params.FindOneInt("volumephotons", -1));
     int writeFreq = params.FindOneInt("imagewritefrequency", 1 << 31);
+    int startIteration = params.FindOneInt("startiteration", 0);
+    int endIteration = params.FindOneInt("enditeration", nIterations);
+    if (!params.FindOneBool("rendersurfaces", true))
+        ;   // what this integrator does
+    else
+        Warning("bre: \"rendersurfaces\" true is not supported: only in-scattered media radiance is gathered, "
+                "surfaces stay black (set \"bool rendersurfaces\" [\"false\"] to silence this)");
     Float radius = params.FindOneFloat("initialbeamradius",
                                        params.FindOneFloat("radius", params.FindOneFloat("maxdist", 1.f)));
     Float alpha = params.FindOneFloat("alpha", 0.5f);
-    if (PbrtOptions.quickRender) nIterations = std::max(1, nIterations / 16);
+    if (PbrtOptions.quickRender) {
+        nIterations = std::max(1, nIterations / 16);
+        endIteration = std::min(endIteration, nIterations);
+        startIteration = std::min(startIteration, endIteration);
+    }
     bool renderMedia = params.FindOneBool("rendermedia", true);
     std::string tracer = params.FindOneString("photontracer", "host");
-    int device = params.FindOneInt("device", 0);
+    int device = params.FindOneInt("device", -1);    // -1: the process's local rank (0 for a single process)
     std::string camrays = params.FindOneString("camerarays", "device");
     if ((tracer != "host" && tracer != "device") || (camrays != "host" && camrays != "device")) {
         Error("bre: photontracer and camerarays must be \"host\" or \"device\"");
         return nullptr;
     }
+    if (startIteration < 0 || endIteration > nIterations || startIteration > endIteration) {
+        Error("bre: need 0 <= startiteration <= enditeration <= iterations");
+        return nullptr;
+    }
     return new BreIntegrator(camera, nIterations, photonsPerIter, maxDepth, radius, alpha,
-                             std::max(1, writeFreq), renderMedia, tracer == "device", camrays == "device",
-                             params.FindOneBool("reusephotons", false), device);
+                             writeFreq, renderMedia, tracer == "device", camrays == "device",
+                             params.FindOneBool("reusephotons", false), device, startIteration, endIteration,
+                             params.FindOneString("checkpoint", ""));
 }
 
 }  // namespace pbrt

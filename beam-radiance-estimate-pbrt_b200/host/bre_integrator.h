@@ -18,14 +18,27 @@
 //   gather radius    "float initialbeamradius" (photonbeam.cpp:598) | "float radius"
 //                    (vsppm.cpp:667) | "float maxdist" (photonmap.cpp:953)
 //   max depth        "integer maxdepth" (photonbeam.cpp:595) | "integer maxphotondepth" (photonmap.cpp:951)
-//   "integer iterations"|"numiterations", "float alpha", "integer imagewritefrequency",
-//   "bool rendermedia" as in photonbeam.cpp:590-603
+//   "integer iterations"|"numiterations", "float alpha", "integer imagewritefrequency" (default 1<<31 =
+//   INT_MIN: (iter+1) % it is never 0, so only the last iteration writes, photonbeam.cpp:565,598),
+//   "integer startiteration" / "integer enditeration" (photonbeam.cpp:354-358,594-595: the radius schedule
+//   is fast-forwarded, L is still divided by iter+1), "bool rendermedia" as in photonbeam.cpp:590-603;
+//   "bool rendersurfaces" is accepted: only media radiance is gathered, surfaces stay black
+//   (the reference's default true also shades surfaces, photonbeam.cpp:519-546) -- a warning says so.
+//   new: "string checkpoint" [""]  film accumulators + iterations done + radius are loaded from this file
+//        when startiteration > 0 and saved to it after the last iteration (bre_film_load / bre_film_save):
+//        a resumed render continues the SAME estimate; the reference's startiteration restores the radius only.
 //   new: "string photontracer" ["host"|"device"]  host = photon paths traced by pbrt's own
 //        Scene/Medium/BSDF code (any scene), device = K1 kernel (matte triangle scenes with point /
 //        spot lights; other scenes: media inside the absorbing world box).
 //   new: "string camerarays" ["device"|"host"]  device (default) = K0 kernel for a pinhole
 //        PerspectiveCamera over matte triangle scenes (bit-identical rays, no PCIe ray traffic);
 //        falls back to pbrt's camera + Scene::Intersect on the host for anything else.
+//   multi-GPU: one pbrt process per GPU.  Rank / world size come from BRE_RANK / BRE_NRANKS, else
+//        OMPI_COMM_WORLD_RANK / _SIZE, else RANK / WORLD_SIZE; the device defaults to the local rank; the 128-byte
+//        NCCL id travels through the file named by BRE_NCCL_ID_FILE (rank 0 writes it, the others wait for it).
+//        Photon paths are split by index and exchanged over NVLink, every rank answers the 16x16 image tiles
+//        bre_tile_owner gives it (photonbeam.cpp:345-347), the film is gathered on rank 0 and only rank 0
+//        calls Film::SetImage / WriteImage (photonbeam.cpp:582-583).
 //   new: "bool reusephotons" [false]  true = trace photons once, later iterations only shrink the
 //        radius (photonbeam.cpp:562) and refit the LBVH instead of re-tracing and rebuilding.
 #ifndef PBRT_INTEGRATORS_BRE_H
@@ -34,6 +47,7 @@
 #include "pbrt.h"
 #include "integrator.h"
 #include "camera.h"
+#include <string>
 
 struct bre_ctx;
 
@@ -43,11 +57,14 @@ class BreIntegrator : public Integrator {
   public:
     BreIntegrator(std::shared_ptr<const Camera> camera, int nIterations, int photonsPerIteration,
                   int maxDepth, Float initialRadius, Float alpha, int writeFrequency,
-                  bool renderMedia, bool deviceTracer, bool deviceCamera, bool reusePhotons, int device)
+                  bool renderMedia, bool deviceTracer, bool deviceCamera, bool reusePhotons, int device,
+                  int startIteration = 0, int endIteration = -1, std::string checkpoint = "")
         : camera(camera), nIterations(nIterations), photonsPerIteration(photonsPerIteration),
           maxDepth(maxDepth), initialRadius(initialRadius), alpha(alpha),
           writeFrequency(writeFrequency), renderMedia(renderMedia), deviceTracer(deviceTracer),
-          deviceCamera(deviceCamera), reusePhotons(reusePhotons), device(device) {}
+          deviceCamera(deviceCamera), reusePhotons(reusePhotons), device(device),
+          startIteration(startIteration), endIteration(endIteration < 0 ? nIterations : endIteration),
+          checkpoint(std::move(checkpoint)) {}
     void Render(const Scene &scene);
 
     // test hook: after Render, photons of the last iteration in reference layout (p, alpha, wi)
@@ -69,6 +86,8 @@ class BreIntegrator : public Integrator {
     const int writeFrequency;
     const bool renderMedia, deviceTracer, deviceCamera, reusePhotons;
     const int device;
+    const int startIteration, endIteration;
+    const std::string checkpoint;
 };
 
 Integrator *CreateBreIntegrator(const ParamSet &params, std::shared_ptr<const Camera> camera);

@@ -5,7 +5,7 @@
 // integrator is created the way core/api.cpp:1444-1468 would (CreateBreIntegrator(ParamSet, camera)),
 // Render() runs -- photon paths by pbrt host code or by the K1 kernel, everything else on the GPU
 // through libbre.so -- and the reference's Film writes the image (PFM through oracle/shim).
-//   bre_pbrt_render <out.pfm> <dump.bin> <host|device> <res> <nPaths> <radius> [iterations [camerarays host|device]]
+//   bre_pbrt_render <out.pfm> <dump.bin> <host|device> <res> <nPaths> <radius> [iterations [camerarays host|device [key=value ...]]]
 // dump.bin (BREF1 container, see ref_harness.cpp) holds the photons of the last iteration and the
 // camera rays, so that tests can evaluate the same estimate with the CPU oracle.
 #include <cstdio>
@@ -93,6 +93,16 @@ int main(int argc, char **argv) {
     { std::unique_ptr<Float[]> a(new Float[1]); a[0] = radius; ps.AddFloat("initialbeamradius", std::move(a), 1); }
     { std::unique_ptr<std::string[]> a(new std::string[1]); a[0] = tracer; ps.AddString("photontracer", std::move(a), 1); }
     { std::unique_ptr<std::string[]> a(new std::string[1]); a[0] = camrays; ps.AddString("camerarays", std::move(a), 1); }
+    // trailing key=value arguments: further integer / string parameters of the scene-file surface
+    // (startiteration=2 enditeration=4 imagewritefrequency=1 checkpoint=/tmp/film.bin rendersurfaces=false)
+    for (int i = 9; i < argc; ++i) {
+        const char *eq = strchr(argv[i], '=');
+        if (!eq) continue;
+        const std::string key(argv[i], eq - argv[i]), val(eq + 1);
+        if (key == "checkpoint") { std::unique_ptr<std::string[]> a(new std::string[1]); a[0] = val; ps.AddString(key, std::move(a), 1); }
+        else if (key == "rendersurfaces") { std::unique_ptr<bool[]> a(new bool[1]); a[0] = val == "true"; ps.AddBool(key, std::move(a), 1); }
+        else addInt(key.c_str(), atoi(val.c_str()));
+    }
     std::unique_ptr<Integrator> integ(CreateBreIntegrator(ps, camera));
     if (!integ) return 1;
     integ->Render(scene);

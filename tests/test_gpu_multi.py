@@ -39,3 +39,29 @@ def test_tile_sharded_render_equals_single_gpu():
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     lines = [ln.split(":", 1)[1] for ln in r.stdout.splitlines() if ln.startswith("rank ")]
     assert len(lines) >= 5 and all("False" not in ln for ln in lines), r.stdout[-2000:]
+
+
+@pytest.mark.skipif(_n_gpus() < 2, reason="needs two GPUs on one box")
+@pytest.mark.parametrize("tracer", ["device", "host"])
+def test_pbrt_adapter_two_ranks(tmp_path, tracer):
+    """The pbrt-side adapter as two processes (BRE_RANK / BRE_NRANKS / BRE_NCCL_ID_FILE): photon paths split by index and
+    exchanged, image tiles sharded, film gathered -- rank 0 writes the image Film::WriteImage would, equal to the
+    single-process render within the radiance tolerance."""
+    import numpy as np
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from test_gpu_pbrt_adapter import BIN, read_pfm
+    if not os.path.exists(BIN):
+        pytest.skip("oracle/_ref/bre_pbrt_render not built")
+    args = [tracer, "48", "8000", "0.2", "2", "device", "rendersurfaces=false"]
+    subprocess.run([BIN, str(tmp_path / "one.pfm"), str(tmp_path / "d.bin"), *args], check=True, timeout=300)
+    one = read_pfm(str(tmp_path / "one.pfm"))
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, BRE_RANK=str(r), BRE_NRANKS="2", BRE_NCCL_ID_FILE=str(tmp_path / "nccl.id"))
+        procs.append(subprocess.Popen([BIN, str(tmp_path / f"two{r}.pfm"), str(tmp_path / f"d{r}.bin"), *args], env=env))
+    for p in procs:
+        assert p.wait(timeout=300) == 0
+    two = read_pfm(str(tmp_path / "two0.pfm"))
+    assert not os.path.exists(str(tmp_path / "two1.pfm"))            # only rank 0 writes (photonbeam.cpp:582-583)
+    err = np.abs(two.astype(np.float64) - one)
+    assert err.mean() <= 1e-4 * np.abs(one).mean() and err.max() <= 1e-3 * np.abs(one).max()

@@ -26,7 +26,9 @@ def read_pfm(path):
     return a[::-1].reshape(-1, 3).copy()        # PFM scanlines run bottom to top
 
 
-@pytest.mark.skipif(not os.path.exists(BIN), reason="oracle/_ref/bre_pbrt_render not built (needs /root/reference)")
+needs_bin = pytest.mark.skipif(not os.path.exists(BIN), reason="oracle/_ref/bre_pbrt_render not built (needs /root/reference)")
+
+
 def fog_box_mesh():
     """The 12 matte triangles bre_pbrt_render builds, in the same order."""
     L, H = (-4.0, -1.0, -4.0), (4.0, 2.0, 4.0)
@@ -43,6 +45,7 @@ def fog_box_mesh():
     return P, idx, Kd
 
 
+@needs_bin
 @pytest.mark.parametrize("tracer,camrays", [("host", "host"), ("host", "device"), ("device", "device")])
 def test_pbrt_adapter_renders_fog_box(tmp_path, oracle, bre, tracer, camrays):
     from make_golden import read_bref
@@ -76,3 +79,25 @@ def test_pbrt_adapter_renders_fog_box(tmp_path, oracle, bre, tracer, camrays):
     err = np.abs(img - ref)
     assert err.mean() <= 1e-4 * np.abs(ref).mean()
     assert err.max() <= 1e-3 * np.abs(ref).max()
+
+
+@needs_bin
+def test_pbrt_adapter_resumes_from_a_checkpoint(tmp_path):
+    """"startiteration" / "enditeration" (integrators/photonbeam.cpp:354-358,594-595) + "checkpoint": iterations 0-1 in
+    one process, 2-3 in a second one that reloads the film accumulators -- the image equals the uninterrupted 4-iteration
+    render (float atomics: within the radiance tolerance).  "imagewritefrequency" keeps the reference's default
+    (1 << 31: only the last iteration writes) and "rendersurfaces false" is accepted."""
+    def run(out, *extra):
+        subprocess.run([BIN, str(tmp_path / out), str(tmp_path / "dump.bin"), "device", "32", "5000", "0.2", "4", "device",
+                        "rendersurfaces=false", *extra], check=True, timeout=300)
+        return read_pfm(str(tmp_path / out))
+    full = run("full.pfm")
+    ck = str(tmp_path / "film.ck")
+    half = run("half.pfm", "enditeration=2", f"checkpoint={ck}")
+    assert os.path.exists(ck) and np.abs(half - full).max() > 0          # two iterations are a different estimate
+    resumed = run("resumed.pfm", "startiteration=2", f"checkpoint={ck}")
+    err = np.abs(resumed.astype(np.float64) - full)
+    assert err.mean() <= 1e-4 * np.abs(full).mean() and err.max() <= 1e-3 * np.abs(full).max()
+    # without the checkpoint the reference's own behaviour: L = Ld / (iter + 1) over the iterations run (half the light)
+    bare = run("bare.pfm", "startiteration=2")
+    assert 0.3 < bare.mean() / full.mean() < 0.7
