@@ -135,6 +135,10 @@ int bre_create(bre_ctx **out, const bre_config *cfg) {
         if (rd && atoi(rd) > 0) ctx->refit_direct = atoi(rd) < ctx->max_leaf ? ctx->max_leaf : atoi(rd);
         const char *np = getenv("BRE_NO_P2P");
         ctx->p2p_disabled = np && atoi(np) != 0;
+        const char *ct = getenv("BRE_COMPACT_TILED");
+        ctx->compact_tiled = !(ct && atoi(ct) == 0);
+        const char *so = getenv("BRE_SORT_ONESWEEP");
+        ctx->sort_onesweep = !(so && atoi(so) == 0);
         const char *ga = getenv("BRE_GATHER_AOS");
         ctx->gather_aos = !(ga && atoi(ga) == 0);
         const char *tn = getenv("BRE_TRACE_NESTED");
@@ -168,7 +172,7 @@ int bre_destroy(bre_ctx *ctx) {
                    &ctx->node_lo, &ctx->node_hi, &ctx->node_range, &ctx->parent, &ctx->leaf_lo,
                    &ctx->leaf_hi, &ctx->flags, &ctx->fast, &ctx->scratch, &ctx->rays_o, &ctx->rays_d,
                    &ctx->out_rgb, &ctx->tau, &ctx->hit_counts, &ctx->hit_offsets, &ctx->hit_idx,
-                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->frames, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb, &ctx->entry, &ctx->rays_stage, &ctx->p2p_scratch, &ctx->aos, &ctx->tframes, &ctx->tile_state, &ctx->top_cut, &ctx->tile_wq, &ctx->gather};
+                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->frames, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb, &ctx->entry, &ctx->rays_stage, &ctx->p2p_scratch, &ctx->aos, &ctx->tframes, &ctx->tile_state, &ctx->top_cut, &ctx->tile_wq, &ctx->gather, &ctx->os_scratch};
     for (Buf *b : bufs) if (b->p) cudaFree(b->p);
     if (ctx->lights_d) cudaFree(ctx->lights_d);
     if (ctx->est_host) cudaFreeHost(ctx->est_host);
@@ -216,6 +220,8 @@ int bre_set_medium_homogeneous(bre_ctx *ctx, const float sa[3], const float ss[3
     m.g = g;
     m.gray = (m.sigma_t[0] == m.sigma_t[1] && m.sigma_t[1] == m.sigma_t[2]) ? 1 : 0;
     ctx->have_medium = true;
+    ++ctx->medium_version;
+    ctx->tau_staged = false;
     return BRE_OK;
 }
 
@@ -242,6 +248,7 @@ int bre_set_medium_grid(bre_ctx *ctx, const float sa[3], const float ss[3], floa
     m.density = (const float *)ctx->density.p;
     m.invMaxDensity = 1 / maxDensity;
     memcpy(m.w2m, w2m, 12 * sizeof(float));
+    ++ctx->medium_version;
     if (ctx->tau_auto) {
         // 1.5 table steps per voxel of the longest axis, a multiple of 32 within [64, 128]: a step equal to the
         // voxel pitch aliases with the trilinear lattice (64 steps through 64^3: 1.3e-3 error of Tr, 96: 1.5e-4;
@@ -523,6 +530,21 @@ int bre_query_to_film(bre_ctx *ctx, uint32_t n, const float *o4, const float *d3
 
 // Asynchronous ray upload on a copy stream: the camera rays of a pass do not depend on the photon
 // pass, so a host can hand them over first and let the PCIe transfer overlap K1 and the LBVH build.
+// staging stream of bre_stage_*: starts after everything queued on the context stream so far (the ray / table
+// buffers may still be read by the previous camera pass)
+static int staging_begin(bre_ctx *ctx) {
+    if (!ctx->copy_stream) {
+        BRE_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        BRE_CUDA(cudaEventCreateWithFlags(&ctx->ev_stage, cudaEventDisableTiming));
+        BRE_CUDA(cudaEventCreateWithFlags(&ctx->ev_main, cudaEventDisableTiming));
+    }
+    BRE_CUDA(cudaEventRecord(ctx->ev_main, ctx->stream));
+    BRE_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_main, 0));
+    ctx->tau_staged = false;
+    ctx->cam_staged = false;
+    return BRE_OK;
+}
+
 int bre_stage_rays(bre_ctx *ctx, uint32_t n, const float *o4, const float *d3) {
     CTX_CHECK();
     if (n == 0 || !o4 || !d3) return set_err(ctx, BRE_ERR_INVALID, "bad ray arrays");
@@ -530,21 +552,45 @@ int bre_stage_rays(bre_ctx *ctx, uint32_t n, const float *o4, const float *d3) {
     if ((s = ensure(ctx, ctx->rays_o, (size_t)n * 16)) != BRE_OK) return s;
     if ((s = ensure(ctx, ctx->rays_d, (size_t)n * 16)) != BRE_OK) return s;
     if ((s = ensure(ctx, ctx->rays_stage, (size_t)n * 12)) != BRE_OK) return s;
-    if (!ctx->copy_stream) {
-        BRE_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
-        BRE_CUDA(cudaEventCreateWithFlags(&ctx->ev_stage, cudaEventDisableTiming));
-        BRE_CUDA(cudaEventCreateWithFlags(&ctx->ev_main, cudaEventDisableTiming));
-    }
-    // the ray buffers may still be read by work already queued on the context stream
-    BRE_CUDA(cudaEventRecord(ctx->ev_main, ctx->stream));
-    BRE_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_main, 0));
+    if ((s = staging_begin(ctx)) != BRE_OK) return s;
     BRE_CUDA(cudaMemcpyAsync(ctx->rays_o.p, o4, (size_t)n * 16, cudaMemcpyHostToDevice, ctx->copy_stream));
     BRE_CUDA(cudaMemcpyAsync(ctx->rays_stage.p, d3, (size_t)n * 12, cudaMemcpyHostToDevice, ctx->copy_stream));
     k_pack3<<<(n + 255) / 256, 256, 0, ctx->copy_stream>>>((const float *)ctx->rays_stage.p, n, nullptr, 0.f,
                                                            (float4 *)ctx->rays_d.p);
     BRE_CUDA(cudaGetLastError());
+    // grid media: the optical-depth table of these rays (K6) right behind the upload, under the photon pass
+    if ((s = stage_tau(ctx, n, (const float4 *)ctx->rays_o.p, (const float4 *)ctx->rays_d.p, ctx->copy_stream)) != BRE_OK) return s;
     BRE_CUDA(cudaEventRecord(ctx->ev_stage, ctx->copy_stream));
     ctx->staged_rays = n;
+    return BRE_OK;
+}
+
+int bre_stage_rays_d(bre_ctx *ctx, uint32_t n, const void *ro, const void *rd) {
+    CTX_CHECK();
+    if (n == 0 || !ro || !rd) return set_err(ctx, BRE_ERR_INVALID, "bad ray arrays");
+    int s;
+    if ((s = staging_begin(ctx)) != BRE_OK) return s;
+    if ((s = stage_tau(ctx, n, (const float4 *)ro, (const float4 *)rd, ctx->copy_stream)) != BRE_OK) return s;
+    BRE_CUDA(cudaEventRecord(ctx->ev_stage, ctx->copy_stream));
+    return BRE_OK;
+}
+
+int bre_stage_camera(bre_ctx *ctx, float offx, float offy) {
+    CTX_CHECK();
+    if (!ctx->have_camera) return set_err(ctx, BRE_ERR_INVALID, "bre_set_camera has not been called");
+    int s;
+    const uint32_t n = (uint32_t)ctx->camera.width * (uint32_t)ctx->camera.height;
+    if ((s = ensure(ctx, ctx->rays_o, (size_t)n * 16)) != BRE_OK) return s;     // (before the streams fork: ensure may free)
+    if ((s = ensure(ctx, ctx->rays_d, (size_t)n * 16)) != BRE_OK) return s;
+    if ((s = staging_begin(ctx)) != BRE_OK) return s;
+    if ((s = camera_rays(ctx, offx, offy, ctx->copy_stream)) != BRE_OK) return s;
+    const uint32_t gw = ctx->grid_w, gh = ctx->grid_h;
+    ctx->grid_w = (uint32_t)ctx->camera.width; ctx->grid_h = (uint32_t)ctx->camera.height;
+    s = stage_tau(ctx, n, (const float4 *)ctx->rays_o.p, (const float4 *)ctx->rays_d.p, ctx->copy_stream);
+    ctx->grid_w = gw; ctx->grid_h = gh;
+    if (s != BRE_OK) return s;
+    BRE_CUDA(cudaEventRecord(ctx->ev_stage, ctx->copy_stream));
+    ctx->cam_staged = true; ctx->cam_offx = offx; ctx->cam_offy = offy;
     return BRE_OK;
 }
 
@@ -596,7 +642,14 @@ int bre_query_camera_to_film(bre_ctx *ctx, float offx, float offy, float nPathsN
     const uint32_t n = (uint32_t)ctx->camera.width * (uint32_t)ctx->camera.height;
     if (!ctx->film.p || ctx->n_pixels != n)
         return set_err(ctx, BRE_ERR_INVALID, "bre_film_create(width*height) has not been called");
-    if ((s = camera_rays(ctx, offx, offy)) != BRE_OK) return s;
+    if (ctx->cam_staged && ctx->cam_offx == offx && ctx->cam_offy == offy) {
+        // bre_stage_camera generated exactly these rays (and their optical-depth table) under the photon pass
+        BRE_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_stage, 0));
+    } else {
+        ctx->tau_staged = false;
+        if ((s = camera_rays(ctx, offx, offy)) != BRE_OK) return s;
+    }
+    ctx->cam_staged = false;
     if ((s = ensure(ctx, ctx->out_rgb, (size_t)n * 16)) != BRE_OK) return s;
     // K0's rays are a width x height image by construction: the tile path applies whatever the caller's grid hint says
     const uint32_t gw = ctx->grid_w, gh = ctx->grid_h;

@@ -72,7 +72,8 @@ __global__ void __launch_bounds__(128) k_camera_rays(CameraDev cam, MeshDev mesh
     rd[q] = make_float4(d[0] * inv, d[1] * inv, d[2] * inv, 0.f);
 }
 
-int camera_rays(bre_ctx *ctx, float offx, float offy) {
+int camera_rays(bre_ctx *ctx, float offx, float offy, cudaStream_t st) {
+    if (!st) st = ctx->stream;
     if (!ctx->have_camera) return set_err(ctx, BRE_ERR_INVALID, "bre_set_camera has not been called");
     const bre_camera &c = ctx->camera;
     const uint32_t n = (uint32_t)c.width * (uint32_t)c.height;
@@ -91,7 +92,7 @@ int camera_rays(bre_ctx *ctx, float offx, float offy) {
     cd.haveBox = (ctx->n_tri == 0 && ctx->have_bounds) ? 1 : 0;
     for (int r = 0; r < 3; ++r) { cd.blo[r] = ctx->blo[r]; cd.bhi[r] = ctx->bhi[r]; }
     MeshDev mesh{ctx->n_tri, (const float4 *)ctx->tri.p, (const float *)ctx->tri_kdb.p};
-    k_camera_rays<<<(n + 127) / 128, 128, 0, ctx->stream>>>(cd, mesh, offx, offy, (float4 *)ctx->rays_o.p,
+    k_camera_rays<<<(n + 127) / 128, 128, 0, st>>>(cd, mesh, offx, offy, (float4 *)ctx->rays_o.p,
                                                            (float4 *)ctx->rays_d.p);
     BRE_CUDA(cudaGetLastError());
     return BRE_OK;
@@ -154,6 +155,7 @@ int bre_set_camera(bre_ctx *ctx, const bre_camera *cam) {
         return set_err(ctx, BRE_ERR_UNSUPPORTED, "camera_to_world must be affine");
     ctx->camera = *cam;
     ctx->have_camera = true;
+    ctx->cam_staged = false;
     return BRE_OK;
 }
 

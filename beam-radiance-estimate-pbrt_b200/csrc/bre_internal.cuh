@@ -145,6 +145,9 @@ struct bre_ctx {
     uint32_t n_tri = 0;
     bre::Buf tri, tri_kdb;
     int lights_in_medium = 1;
+    bool compact_tiled = true;              // BRE_COMPACT_TILED=0: one-thread-per-path k_compact (A/B)
+    bool sort_onesweep = true;              // BRE_SORT_ONESWEEP=0: the three-kernel radix passes (A/B)
+    bre::Buf os_scratch;
     bool gather_aos = true;                 // BRE_GATHER_AOS=0: gather straight from the three store arrays
     bool trace_nested = false;              // BRE_TRACE_NESTED=1: the nested-loop K1 (A/B experiments)
     bre_camera camera{};
@@ -192,6 +195,13 @@ struct bre_ctx {
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_stage = nullptr, ev_main = nullptr;
     uint32_t staged_rays = 0;
+    // optical-depth table computed ahead of the query by bre_stage_* (K6 under the photon pass + build)
+    struct TauKey { const void *ro, *rd; uint32_t n; int steps; uint32_t gridW; uint64_t mediumVersion; const float *tau; const float2 *span; };
+    TauKey tau_key{};
+    bool tau_staged = false;
+    uint64_t medium_version = 0;
+    bool cam_staged = false;                // K0's rays of (cam_offx, cam_offy) are in rays_o / rays_d (bre_stage_camera)
+    float cam_offx = 0, cam_offy = 0;
     cudaStream_t stream2 = nullptr;
     cudaEvent_t qev[4] = {};
     bre::Buf rays_o, rays_d, out_rgb, tau, hit_counts, hit_offsets, hit_idx, counters_d, pix_idx;
@@ -238,12 +248,13 @@ int ensure_canonical(bre_ctx *ctx);
 int run_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, float nPathsNorm,
               float4 *out);
 int run_count(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd);
+int stage_tau(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, cudaStream_t st);
 int run_hitdump(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, bre_hitdump *hd);
 // film.cu
 int film_accumulate(bre_ctx *ctx, uint32_t n, const uint32_t *pix_d, const float4 *rgb_d);
 int film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int meanOnly);
 // camera.cu
-int camera_rays(bre_ctx *ctx, float offx, float offy);
+int camera_rays(bre_ctx *ctx, float offx, float offy, cudaStream_t st = nullptr);
 // trace.cu
 constexpr uint64_t TRACE_CHUNK = 1u << 22;   // paths per trace launch (bounds the slot scratch)
 struct SlotView {
@@ -261,6 +272,7 @@ int nccl_init(bre_ctx *ctx, const void *uid);
 int nccl_allgather_photons(bre_ctx *ctx);
 int trace_exchange_p2p(bre_ctx *ctx, uint64_t nPathsTotal, int maxDepth, float radius);
 int film_gather(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int meanOnly);
+int compact_tiled_local(bre_ctx *ctx, const SlotView &v, uint64_t storeBase);
 void nccl_destroy(bre_ctx *ctx);
 int nccl_unique_id(void *out128);
 
@@ -269,12 +281,12 @@ TreeDev tree_view(const bre_ctx *ctx);
 enum Phase { PH_TRACE = 0, PH_BUILD = 1, PH_TAU = 2, PH_QUERY = 3, PH_FILM = 4, PH_QUERY_A = 5, PH_QUERY_B = 6 };
 // RAII event bracket around a phase on the context stream (no-op unless timing is enabled)
 struct PhaseTimer {
-    bre_ctx *c; int ph;
-    PhaseTimer(bre_ctx *ctx, int phase) : c(ctx), ph(phase) {
-        if (c->timing) cudaEventRecord(c->ev[ph][0], c->stream);
+    bre_ctx *c; int ph; cudaStream_t st;
+    PhaseTimer(bre_ctx *ctx, int phase, cudaStream_t stream = nullptr) : c(ctx), ph(phase), st(stream ? stream : ctx->stream) {
+        if (c->timing) cudaEventRecord(c->ev[ph][0], st);
     }
     ~PhaseTimer() {
-        if (c->timing) { cudaEventRecord(c->ev[ph][1], c->stream); c->ev_valid[ph] = true; }
+        if (c->timing) { cudaEventRecord(c->ev[ph][1], st); c->ev_valid[ph] = true; }
     }
 };
 

@@ -205,6 +205,25 @@ __global__ void __launch_bounds__(256) k_compact_push(uint32_t nPaths, int maxDe
     }
 }
 
+// Single-rank use of the same kernel: the tile-in-shared-memory compaction writes full coalesced runs where the
+// one-thread-per-path k_compact (bre_trace.cu) scatters 16-byte records (0.37 ms -> see profiles/ at 10 M photons).
+int compact_tiled_local(bre_ctx *ctx, const SlotView &v, uint64_t storeBase) {
+    if (v.nPaths == 0) return BRE_OK;
+    PeerStores ps;
+    for (int q = 0; q < MAX_P2P_RANKS; ++q) {
+        ps.pos[q] = (float4 *)ctx->pos_r.p; ps.pw[q] = (float4 *)ctx->pow.p; ps.dr[q] = (float4 *)ctx->dir.p;
+    }
+    uint32_t tilePaths = 256;
+    while (tilePaths > 1 && (size_t)tilePaths * v.maxDepth * 48 > 200 * 1024) tilePaths >>= 1;
+    const size_t smem = (size_t)tilePaths * v.maxDepth * 48;
+    if (smem > 200 * 1024) return BRE_ERR_UNSUPPORTED;      // caller falls back to k_compact
+    BRE_CUDA(cudaFuncSetAttribute(k_compact_push, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_compact_push<<<(unsigned)((v.nPaths + tilePaths - 1) / tilePaths), 256, smem, ctx->stream>>>(
+        v.nPaths, v.maxDepth, tilePaths, v.counts, v.offs, v.sp, v.sw, v.sd, ps, 1, 0, storeBase);
+    BRE_CUDA(cudaGetLastError());
+    return BRE_OK;
+}
+
 static void p2p_close(bre_ctx *ctx) {
     for (int r = 0; r < MAX_P2P_RANKS; ++r)
         for (int a = 0; a < 3; ++a)

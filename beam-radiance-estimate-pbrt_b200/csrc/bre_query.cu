@@ -259,10 +259,11 @@ constexpr int QT = 128;
 namespace bre {
 
 // image-tile path: the caller declared the rays to be a grid_w x grid_h image (bre_set_ray_grid / K0)
-static bool tile_mode(const bre_ctx *ctx, uint32_t n) {
+static bool grid_layout(const bre_ctx *ctx, uint32_t n) {
     return !BRE_WIDE && ctx->tile_path && ctx->grid_w >= 2 && ctx->grid_h >= 2 &&
-           (uint64_t)ctx->grid_w * ctx->grid_h == n && ctx->n_built > 0;
+           (uint64_t)ctx->grid_w * ctx->grid_h == n;
 }
+static bool tile_mode(const bre_ctx *ctx, uint32_t n) { return grid_layout(ctx, n) && ctx->n_built > 0; }
 
 // One block of launch state per ray batch, in ctx->packet_ctr (stride QB_STRIDE bytes):
 //   +0   queue control words (QC_*), zeroed before every launch
@@ -368,7 +369,7 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     LeafArgs A;
     A.t = tree_view(ctx); A.m = ctx->medium; A.ro = ro; A.rd = rd; A.nPathsNorm = nPathsNorm;
     A.out = out; A.tau = tau; A.span = span; A.tauSteps = ctx->tau_steps;
-    A.tauW = (tileMode && tau) ? imgW : 0u; A.tauTilesX = tilesX; A.rayBase = 0;
+    A.tauW = (grid_layout(ctx, n) && tau) ? ctx->grid_w : 0u; A.tauTilesX = (ctx->grid_w + 15) / 16; A.rayBase = 0;
     A.hitCounts = hitCounts; A.hitOffsets = hitOffsets; A.hitIdx = hitIdx;
     A.frames = nullptr;
     TileArgs TA{};
@@ -599,8 +600,10 @@ __global__ void __launch_bounds__(QT) k_count_canonical(TreeDev t, uint32_t n,
 }
 
 // ---------------------------------------------------------------- host drivers
+// K6 on stream `st` (the context stream, or the staging stream of bre_stage_*: the table only depends on the rays and
+// the medium, so a host that hands the rays over before the photon pass gets it computed UNDER the photon pass + build).
 static int prepare_tau(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd,
-                       const float **tau, const float2 **span) {
+                       const float **tau, const float2 **span, cudaStream_t st) {
     *tau = nullptr; *span = nullptr;
     if (ctx->medium.kind != 1) return BRE_OK;
     int s;
@@ -608,7 +611,7 @@ static int prepare_tau(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 
     size_t offSpan = ((size_t)n * rowBytes + 15) & ~(size_t)15;
     float *tp = nullptr;
     float2 *sp = nullptr;
-    const bool grid = tile_mode(ctx, n);
+    const bool grid = grid_layout(ctx, n);
     if (grid) {
         // tile-blocked table (k_tau_tile): [tile][step][256 pixels]
         const uint32_t tX = (ctx->grid_w + 15) / 16, tY = (ctx->grid_h + 15) / 16;
@@ -617,30 +620,50 @@ static int prepare_tau(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 
         if ((s = ensure(ctx, ctx->tau, offSpan + (size_t)n * 8)) != BRE_OK) return s;
         tp = (float *)ctx->tau.p;
         sp = (float2 *)((char *)ctx->tau.p + offSpan);
-        PhaseTimer pt(ctx, PH_TAU);
+        PhaseTimer pt(ctx, PH_TAU, st);
         const int shardMod = (ctx->tile_shard && ctx->n_ranks > 1) ? ctx->n_ranks : 1;
-        k_tau_tile<<<tX * tY, 256, 0, ctx->stream>>>(ctx->medium, ctx->grid_w, ctx->grid_h, tX, ro, rd, ctx->tau_steps,
-                                                   tp, sp, shardMod, ctx->rank);
+        k_tau_tile<<<tX * tY, 256, 0, st>>>(ctx->medium, ctx->grid_w, ctx->grid_h, tX, ro, rd, ctx->tau_steps,
+                                          tp, sp, shardMod, ctx->rank);
     } else {
         if ((s = ensure(ctx, ctx->tau, offSpan + (size_t)n * 8)) != BRE_OK) return s;
         tp = (float *)ctx->tau.p;
         sp = (float2 *)((char *)ctx->tau.p + offSpan);
-        PhaseTimer pt(ctx, PH_TAU);
+        PhaseTimer pt(ctx, PH_TAU, st);
         const size_t smem = (size_t)128 * (ctx->tau_steps + 1) * 4;   // tau_steps <= 384 (bre_create)
         if (smem > 48 * 1024)
             BRE_CUDA(cudaFuncSetAttribute(k_tau_table, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_tau_table<<<(n + 127) / 128, 128, smem, ctx->stream>>>(
+        k_tau_table<<<(n + 127) / 128, 128, smem, st>>>(
             ctx->medium, n, ro, rd, ctx->tau_steps, tp, sp);
     }
     *tau = tp; *span = sp;
+    ctx->tau_key = {ro, rd, n, ctx->tau_steps, grid ? ctx->grid_w : 0u, ctx->medium_version, tp, sp};
     return BRE_OK;
+}
+
+// bre_stage_*: K6 for the rays of the NEXT query, on the staging stream (after the rays themselves are there)
+int stage_tau(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, cudaStream_t st) {
+    const float *tau; const float2 *span;
+    ctx->tau_staged = false;
+    if (!ctx->have_medium || ctx->medium.kind != 1) return BRE_OK;
+    int s = prepare_tau(ctx, n, ro, rd, &tau, &span, st);
+    if (s == BRE_OK) ctx->tau_staged = true;
+    return s;
 }
 
 int run_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, float nPathsNorm,
               float4 *out) {
     if (n == 0) return BRE_OK;
-    const float *tau; const float2 *span;
-    int s = prepare_tau(ctx, n, ro, rd, &tau, &span);
+    const float *tau = nullptr; const float2 *span = nullptr;
+    int s = BRE_OK;
+    const bre_ctx::TauKey &k = ctx->tau_key;
+    if (ctx->tau_staged && ctx->medium.kind == 1 && k.ro == ro && k.rd == rd && k.n == n && k.steps == ctx->tau_steps &&
+        k.gridW == (grid_layout(ctx, n) ? ctx->grid_w : 0u) && k.mediumVersion == ctx->medium_version) {
+        // the table of exactly these rays was computed by bre_stage_* under the photon pass: wait for it
+        tau = k.tau; span = k.span;
+        BRE_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_stage, 0));
+    } else
+        s = prepare_tau(ctx, n, ro, rd, &tau, &span, ctx->stream);
+    ctx->tau_staged = false;
     if (s != BRE_OK) return s;
     {
         PhaseTimer pt(ctx, PH_QUERY);

@@ -692,10 +692,14 @@ int trace_photons(bre_ctx *ctx, uint64_t first, uint64_t nPathsTotal, int maxDep
         int s = trace_to_slots(ctx, first + done, nPaths, maxDepth, radius, &v);
         if (s != BRE_OK) return s;
         if ((s = grow_store(ctx, ctx->n_photons + v.total)) != BRE_OK) return s;
-        k_compact<<<(nPaths + 255) / 256, 256, 0, ctx->stream>>>(
-            nPaths, maxDepth, v.counts, v.offs, v.sp, v.sw, v.sd, (float4 *)ctx->pos_r.p, (float4 *)ctx->pow.p,
-            (float4 *)ctx->dir.p, ctx->n_photons);
-        BRE_CUDA(cudaGetLastError());
+        // tile-in-shared-memory compaction (the kernel of the multi-GPU push, writing to this rank only): coalesced runs
+        if (ctx->compact_tiled && compact_tiled_local(ctx, v, ctx->n_photons) == BRE_OK) {
+        } else {
+            k_compact<<<(nPaths + 255) / 256, 256, 0, ctx->stream>>>(
+                nPaths, maxDepth, v.counts, v.offs, v.sp, v.sw, v.sd, (float4 *)ctx->pos_r.p, (float4 *)ctx->pow.p,
+                (float4 *)ctx->dir.p, ctx->n_photons);
+            BRE_CUDA(cudaGetLastError());
+        }
         ctx->n_photons += v.total;
     }
     return BRE_OK;

@@ -403,7 +403,8 @@ void BreIntegrator::Render(const Scene &scene) {
                 }
             }, ext.y, 4);
             if (!Check(ctx, bre_stage_rays(ctx, nPixels, rayO, rayD), "bre_stage_rays")) break;
-        }
+        } else if (!Check(ctx, bre_stage_camera(ctx, off.x, off.y), "bre_stage_camera"))   // K0 + K6 under the photon pass
+            break;
         // ---- photon pass (photonbeam.cpp:365-437): path indices iter*nPaths .. as :386-388
         // "reusephotons": the photon map of iteration 0 is kept and only its radius shrinks, so
         // bre_build degenerates to a refit of the existing LBVH

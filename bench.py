@@ -290,6 +290,10 @@ def run_ours(args):
             ctx.allgather_photons()
 
     def step_device():
+        # the rays of the pass are known before the photons: their optical-depth tables (K6) run on the staging
+        # stream under the photon pass and the build (bre_stage_rays_d), like the adapter's bre_stage_camera
+        if not args.no_stage:
+            ctx.stage_rays_d(nq, ro_d.data_ptr(), rd_d.data_ptr())
         photon_pass()
         ctx.build()
         ctx.query_d(nq, ro_d.data_ptr(), rd_d.data_ptr(), float(n_paths), out_d.data_ptr())
@@ -300,6 +304,8 @@ def run_ours(args):
     def step_e2e():
         # the calls the pbrt adapter makes: camera in, image out
         ctx.set_camera(r2c, c2w, 0, 0, W, H, True)
+        if not args.no_stage:
+            ctx.stage_camera(off[0], off[1])            # K0 + K6 under the photon pass
         photon_pass()
         ctx.build()
         ctx.query_camera_to_film(float(n_paths), off[0], off[1])
@@ -418,7 +424,7 @@ def run_ours(args):
                    "leaf_pairs_per_ray": cnt["leaf_pairs"] / nq, "pair_queue_overflow": cnt["pair_queue_overflow"]},
         "e2e": {"value": e2e_value, "unit": "queries/s", "h2d_bytes_per_step": 152,
                 "d2h_bytes_per_step": int(nq * 12), "ms_per_step": ms_e2e / args.steps,
-                "api": "bre_set_camera + photon pass + bre_build + bre_query_camera_to_film + bre_film_gather/resolve"},
+                "api": "bre_set_camera + bre_stage_camera + photon pass + bre_build + bre_query_camera_to_film + bre_film_gather/resolve"},
         "gpu_launches": (ours_launches * args.steps) if ours_launches is not None else None,
         "gpu_launches_per_step": ours_launches, "gpu_launches_per_step_all": all_launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -667,6 +673,7 @@ def main():
     ap.add_argument("--no-tile", action="store_true", help="K5 packet walk instead of the image-tile walk (A/B)")
     ap.add_argument("--no-host-rays", action="store_true", help="skip the second end-to-end figure (host rays)")
     ap.add_argument("--no-port", action="store_true", help="reference arm: skip the oracle-port figure")
+    ap.add_argument("--no-stage", action="store_true", help="K0 / K6 inside the query call instead of under the photon pass (A/B)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--ref-photons", type=int, default=50000, help="reference arm: photon paths per pbrt run")
     ap.add_argument("--ref-crop", type=float, default=0.12, help="reference arm: side of the crop window (fraction of 256)")

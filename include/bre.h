@@ -215,6 +215,16 @@ int bre_query_to_film(bre_ctx *ctx, uint32_t n_rays, const float *o_xyz_tmax, co
  * until bre_query_staged_to_film has returned), then traces / builds, then calls
  * bre_query_staged_to_film. */
 int bre_stage_rays(bre_ctx *ctx, uint32_t n_rays, const float *o_xyz_tmax, const float *d_xyz);
+/* The same head start for the other two ray sources.  A camera pass needs nothing from the photons until
+ * the walk: the rays (K0) and, for grid media, their optical-depth tables (K6) can be computed on the
+ * staging stream while the photon pass and the LBVH build run (the reference generates its camera rays
+ * inside the camera pass, integrators/photonbeam.cpp:444-481, after the photon pass).  Call right after
+ * bre_set_camera / before the photon pass; the matching query call picks the staged results up when its
+ * arguments are the same, and computes them itself otherwise.
+ *   bre_stage_camera   -> bre_query_camera_to_film(same offsets)
+ *   bre_stage_rays_d   -> bre_query_d(same n and device pointers; the arrays must not change in between) */
+int bre_stage_camera(bre_ctx *ctx, float offset_x, float offset_y);
+int bre_stage_rays_d(bre_ctx *ctx, uint32_t n_rays, const void *rays_o_d, const void *rays_d_d);
 int bre_query_staged_to_film(bre_ctx *ctx, const uint32_t *pixel_idx, float n_paths_norm);
 /* Ray layout hint for every query entry point: when width * height == n_rays, ray q is pixel
  * (q % width, q / width) of an image, the way the reference's camera pass visits them tile by tile
