@@ -28,7 +28,7 @@ SYMBOLS = [
     "bre_set_triangle_attrs", "bre_set_lights_in_medium", "bre_set_camera", "bre_camera_rays",
     "bre_query_camera_to_film", "bre_last_build_kind",
     "bre_trace_exchange_photons", "bre_alloc_pinned", "bre_free_pinned", "bre_stage_rays", "bre_query_staged_to_film", "bre_save_photons", "bre_load_photons", "bre_film_save", "bre_film_load",
-    "bre_set_ray_grid", "bre_set_tile_sharding", "bre_film_gather", "bre_stage_camera", "bre_stage_rays_d",
+    "bre_set_ray_grid", "bre_set_tile_sharding", "bre_set_photon_sharding", "bre_film_gather", "bre_stage_camera", "bre_stage_rays_d",
 ]
 
 
@@ -294,6 +294,9 @@ class Bre:
 
     def set_tile_sharding(self, on=True):
         self._ck(self.lib.bre_set_tile_sharding(self.ctx, int(on)))
+
+    def set_photon_sharding(self, on=True):
+        self._ck(self.lib.bre_set_photon_sharding(self.ctx, int(on)))
 
     def query_d(self, n, rays_o_ptr, rays_d_ptr, n_paths_norm, out_ptr):
         self._ck(self.lib.bre_query_d(self.ctx, n, C.c_void_p(rays_o_ptr), C.c_void_p(rays_d_ptr),

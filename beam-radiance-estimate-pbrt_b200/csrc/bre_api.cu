@@ -391,7 +391,12 @@ int bre_trace_exchange_photons(bre_ctx *ctx, uint64_t nPathsTotal, int maxDepth,
     // the path must be the same on every rank (both are collectives): decide from GLOBAL values only --
     // the largest shard any rank gets, not this rank's own
     const uint64_t maxShard = (nPathsTotal + (uint64_t)ctx->n_ranks - 1) / (uint64_t)ctx->n_ranks;
-    if (ctx->n_ranks > 1 && !ctx->p2p_disabled && ctx->n_ranks <= 8 && maxShard <= TRACE_CHUNK) {
+    if (ctx->photon_shard && ctx->n_ranks > 1) {
+        // photon-sharded render: the slice stays here, nothing is exchanged (the films are summed instead)
+        ctx->n_photons = 0;
+        ctx->built = false; ctx->topo_valid = false;
+        s = trace_photons(ctx, first, count, maxDepth, radius);
+    } else if (ctx->n_ranks > 1 && !ctx->p2p_disabled && ctx->n_ranks <= 8 && maxShard <= TRACE_CHUNK) {
         s = trace_exchange_p2p(ctx, nPathsTotal, maxDepth, radius);
     } else {
         ctx->n_photons = 0;
@@ -504,6 +509,14 @@ int bre_set_ray_grid(bre_ctx *ctx, uint32_t width, uint32_t height) {
 int bre_set_tile_sharding(bre_ctx *ctx, int enabled) {
     CTX_CHECK();
     ctx->tile_shard = enabled != 0;
+    if (ctx->tile_shard) ctx->photon_shard = false;
+    return BRE_OK;
+}
+
+int bre_set_photon_sharding(bre_ctx *ctx, int enabled) {
+    CTX_CHECK();
+    ctx->photon_shard = enabled != 0;
+    if (ctx->photon_shard) ctx->tile_shard = false;
     return BRE_OK;
 }
 
@@ -689,6 +702,11 @@ int bre_get_counters(bre_ctx *ctx, bre_counters *out) {
 int bre_film_create(bre_ctx *ctx, uint32_t nPixels) {
     CTX_CHECK();
     if (nPixels == 0) return set_err(ctx, BRE_ERR_INVALID, "empty film");
+    if (ctx->film_peers_open && ctx->film.p && ctx->film.cap < (size_t)nPixels * 16) {
+        // peers still map this film (photon-sharded gather): keep it alive until they have unmapped it
+        ctx->p2p_zombies.push_back(ctx->film.p);
+        ctx->film.p = nullptr; ctx->film.cap = 0;
+    }
     int s = ensure(ctx, ctx->film, (size_t)nPixels * 16);
     if (s != BRE_OK) return s;
     ctx->n_pixels = nPixels;

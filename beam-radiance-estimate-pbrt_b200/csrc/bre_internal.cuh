@@ -223,6 +223,12 @@ struct bre_ctx {
     bre::Buf gather;
     void *gather_peer0 = nullptr, *gather_exported = nullptr;
     uint32_t gather_mapped_pixels = 0, gather_calls = 0;
+    // photon-sharded render (bre_set_photon_sharding): every rank keeps the photons it traced, builds its own LBVH
+    // and answers every pixel from it; bre_film_gather sums the partial films over CUDA-IPC mappings of the films
+    bool photon_shard = false;
+    void *film_peer[8] = {};
+    void *film_exported = nullptr;
+    bool film_peers_open = false;
     std::vector<void *> p2p_zombies;       // exported stores replaced since: freed once peers closed them
     // per-phase device timing (bre_set_timing)
     bool timing = false;

@@ -230,10 +230,19 @@ static void p2p_close(bre_ctx *ctx) {
             if (ctx->p2p_peer[r][a] && r != ctx->rank) { cudaIpcCloseMemHandle(ctx->p2p_peer[r][a]); ctx->p2p_peer[r][a] = nullptr; }
     ctx->p2p_open = false;
 }
+static void film_peers_close(bre_ctx *ctx) {
+    for (int r = 0; r < MAX_P2P_RANKS; ++r) {
+        if (ctx->film_peer[r] && r != ctx->rank) cudaIpcCloseMemHandle(ctx->film_peer[r]);
+        ctx->film_peer[r] = nullptr;
+    }
+    ctx->film_peers_open = false;
+    ctx->film_exported = nullptr;
+}
 void p2p_destroy(bre_ctx *ctx) {
     if (ctx->gather_peer0 && ctx->rank != 0) cudaIpcCloseMemHandle(ctx->gather_peer0);
-    const bool hadGather = ctx->gather_peer0 != nullptr;
+    const bool hadGather = ctx->gather_peer0 != nullptr || ctx->film_peers_open;
     ctx->gather_peer0 = nullptr;
+    film_peers_close(ctx);
     const bool was = ctx->p2p_open || hadGather;
     p2p_close(ctx);
     if (was && ctx->nccl_comm) {
@@ -395,6 +404,145 @@ __global__ void __launch_bounds__(256) k_film_resolve_tiles(const float4 *__rest
     dst[3 * i + 0] = v.x; dst[3 * i + 1] = v.y; dst[3 * i + 2] = v.z;
 }
 
+
+// ---------------------------------------------------------------- film gather (photon-sharded render)
+// Radiance is a sum over photons (integrators/photonbeam.cpp:494-508), so R ranks that each hold 1/R of the photon
+// paths produce R partial films whose sum is the film of the whole map.  The sum is a reduce-scatter written by hand
+// over NVLink: rank r owns a contiguous run of pixels, PULLS that run from every rank's film through CUDA-IPC
+// mappings (adds in rank order: deterministic for given partials), resolves it (photonbeam.cpp:578, core/film.cpp:
+// 168-204) and writes the finished triples into rank 0's image -- 16 + 12 bytes per pixel cross the switch once,
+// instead of the (R - 1) x 16 of a reduce onto rank 0.  Blocks stage their 256 pixels in shared memory so that the
+// remote stores are full 16-byte vectors.
+struct FilmPeers { const float4 *film[MAX_P2P_RANKS]; };
+__global__ void __launch_bounds__(256) k_film_sum_resolve(FilmPeers P, int nRanks, uint32_t first, uint32_t last, float inv,
+                                                         float scale, int meanOnly, float *__restrict__ dst) {
+    __shared__ __align__(16) float out[768];
+    const uint32_t base = first + blockIdx.x * 256u, i = base + threadIdx.x;   // base is a multiple of 256
+    if (i < last) {
+        float4 a = P.film[0][i];
+        for (int r = 1; r < nRanks; ++r) {
+            const float4 b = P.film[r][i];
+            a.x = fadd(a.x, b.x); a.y = fadd(a.y, b.y); a.z = fadd(a.z, b.z);
+        }
+        const float3 v = film_convert(fmul(a.x, inv), fmul(a.y, inv), fmul(a.z, inv), scale, meanOnly);
+        out[3 * threadIdx.x] = v.x; out[3 * threadIdx.x + 1] = v.y; out[3 * threadIdx.x + 2] = v.z;
+    }
+    __syncthreads();
+    const uint32_t nPix = min(256u, last - base), nFloats = 3u * nPix;
+    float *d = dst + 3 * (size_t)base;                                         // 3072-byte aligned
+    if (threadIdx.x < nFloats / 4) ((float4 *)d)[threadIdx.x] = ((const float4 *)out)[threadIdx.x];
+    if (threadIdx.x < (nFloats & 3u)) d[(nFloats & ~3u) + threadIdx.x] = out[(nFloats & ~3u) + threadIdx.x];
+}
+
+static int film_gather_sum(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int meanOnly) {
+    const uint32_t n = ctx->n_pixels;
+    const int R = ctx->n_ranks;
+    const float inv = 1.f / (float)(iter + 1);
+    const size_t imgBytes = (size_t)n * 12, imgStride = (imgBytes + 255) & ~(size_t)255;
+    ncclComm_p comm = (ncclComm_p)ctx->nccl_comm;
+    int s;
+    const size_t need = 2 * imgStride + (size_t)n * 16;
+    if (ctx->gather.p && ctx->gather.cap < need && ctx->gather_exported == ctx->gather.p) {
+        ctx->p2p_zombies.push_back(ctx->gather.p);      // peers still map it: freed after the next remap
+        ctx->gather.p = nullptr; ctx->gather.cap = 0;
+    }
+    if ((s = ensure(ctx, ctx->gather, need)) != BRE_OK) return s;
+    if ((s = ensure(ctx, ctx->counters_d, 16 * (size_t)(R + 1) + 64)) != BRE_OK) return s;
+    uint64_t *cnt_d = (uint64_t *)ctx->counters_d.p;
+    const size_t half = (size_t)(ctx->gather_calls & 1u) * imgStride;
+    ++ctx->gather_calls;
+    if (ctx->p2p_disabled || R > MAX_P2P_RANKS) {
+        // NCCL path: ncclReduce(sum) of the float4 accumulators onto rank 0, which resolves
+        float4 *sum = (float4 *)((char *)ctx->gather.p + 2 * imgStride);
+        int r = g.Reduce(ctx->film.p, sum, (size_t)n * 4, kNcclFloat, 0 /* ncclSum */, 0, comm, ctx->stream);
+        if (r != 0) return nccl_err(ctx, r, "ncclReduce(film sum)");
+        if (ctx->rank == 0) {
+            float *loc = (float *)((char *)ctx->gather.p + half);
+            FilmPeers P{};
+            P.film[0] = sum;
+            k_film_sum_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>(P, 1, 0, n, inv, scale, meanOnly, loc);
+            BRE_CUDA(cudaGetLastError());
+            if (rgb_out_host) BRE_CUDA(cudaMemcpyAsync(rgb_out_host, loc, imgBytes, cudaMemcpyDeviceToHost, ctx->stream));
+        }
+        BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+        return BRE_OK;
+    }
+    // ---- arrival of every rank's camera pass + "my film / image buffer moved" flags, one all-gather
+    const bool moved = !ctx->film_peers_open || ctx->film_exported != ctx->film.p || ctx->gather_mapped_pixels != n ||
+                       ctx->gather_exported != ctx->gather.p;
+    uint64_t mine = moved ? 1ull : 0ull;
+    BRE_CUDA(cudaMemcpyAsync(cnt_d + 2 * R, &mine, 8, cudaMemcpyHostToDevice, ctx->stream));
+    int r = g.AllGather(cnt_d + 2 * R, cnt_d, 1, kNcclUint64, comm, ctx->stream);
+    if (r != 0) return nccl_err(ctx, r, "ncclAllGather(film flags)");
+    std::vector<uint64_t> got(R);
+    BRE_CUDA(cudaMemcpyAsync(got.data(), cnt_d, 8 * (size_t)R, cudaMemcpyDeviceToHost, ctx->stream));
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    bool anyMoved = false;
+    for (int q = 0; q < R; ++q) anyMoved |= got[q] != 0;
+    if (anyMoved) {
+        // every rank: unmap, export {film, image buffer}, all-gather the handles, map
+        film_peers_close(ctx);
+        if (ctx->gather_peer0 && ctx->rank != 0) cudaIpcCloseMemHandle(ctx->gather_peer0);
+        ctx->gather_peer0 = nullptr;
+        cudaIpcMemHandle_t h[2];
+        BRE_CUDA(cudaIpcGetMemHandle(&h[0], ctx->film.p));
+        BRE_CUDA(cudaIpcGetMemHandle(&h[1], ctx->gather.p));
+        const size_t hb = sizeof(h);
+        if ((s = ensure(ctx, ctx->p2p_scratch, hb * (size_t)(R + 1))) != BRE_OK) return s;
+        char *d = (char *)ctx->p2p_scratch.p;
+        BRE_CUDA(cudaMemcpyAsync(d + hb * R, h, hb, cudaMemcpyHostToDevice, ctx->stream));
+        r = g.AllGather(d + hb * R, d, hb, 0 /* ncclChar */, comm, ctx->stream);
+        if (r != 0) return nccl_err(ctx, r, "ncclAllGather(film ipc handles)");
+        std::vector<cudaIpcMemHandle_t> all(2 * (size_t)R);
+        BRE_CUDA(cudaMemcpyAsync(all.data(), d, hb * R, cudaMemcpyDeviceToHost, ctx->stream));
+        BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+        for (int q = 0; q < R; ++q) {
+            if (q == ctx->rank) { ctx->film_peer[q] = ctx->film.p; continue; }
+            void *ptr = nullptr;
+            cudaError_t e = cudaIpcOpenMemHandle(&ptr, all[2 * q], cudaIpcMemLazyEnablePeerAccess);
+            if (e != cudaSuccess) {
+                cudaGetLastError();
+                return set_err(ctx, BRE_ERR_CUDA, std::string("cudaIpcOpenMemHandle(peer film): ") + cudaGetErrorString(e));
+            }
+            ctx->film_peer[q] = ptr;
+        }
+        if (ctx->rank == 0) ctx->gather_peer0 = ctx->gather.p;
+        else {
+            void *ptr = nullptr;
+            cudaError_t e = cudaIpcOpenMemHandle(&ptr, all[1], cudaIpcMemLazyEnablePeerAccess);
+            if (e != cudaSuccess) {
+                cudaGetLastError();
+                return set_err(ctx, BRE_ERR_CUDA, std::string("cudaIpcOpenMemHandle(film image): ") + cudaGetErrorString(e));
+            }
+            ctx->gather_peer0 = ptr;
+        }
+        ctx->film_peers_open = true;
+        ctx->film_exported = ctx->film.p;
+        ctx->gather_mapped_pixels = n;
+        ctx->gather_exported = ctx->gather.p;
+        // the old films / image buffers are unmapped everywhere once every rank got here
+        for (void *z : ctx->p2p_zombies) cudaFree(z);
+        ctx->p2p_zombies.clear();
+    }
+    // ---- pixel run of this rank (multiples of 256 pixels: 16-byte aligned triples)
+    const uint32_t per = (uint32_t)((((uint64_t)n + R - 1) / R + 255) / 256 * 256);
+    const uint32_t first = (uint32_t)std::min<uint64_t>((uint64_t)per * ctx->rank, n);
+    const uint32_t last = (uint32_t)std::min<uint64_t>((uint64_t)first + per, n);
+    float *dst = (float *)((char *)ctx->gather_peer0 + half);
+    if (last > first) {
+        FilmPeers P{};
+        for (int q = 0; q < R; ++q) P.film[q] = (const float4 *)ctx->film_peer[q];
+        k_film_sum_resolve<<<(last - first + 255) / 256, 256, 0, ctx->stream>>>(P, R, first, last, inv, scale, meanOnly, dst);
+        BRE_CUDA(cudaGetLastError());
+    }
+    // ---- every run has landed in rank 0's image, and nobody writes its film again before everyone has read it
+    r = g.AllGather(cnt_d + 2 * R, cnt_d, 1, kNcclUint64, comm, ctx->stream);
+    if (r != 0) return nccl_err(ctx, r, "ncclAllGather(film barrier)");
+    if (ctx->rank == 0 && rgb_out_host) BRE_CUDA(cudaMemcpyAsync(rgb_out_host, dst, imgBytes, cudaMemcpyDeviceToHost, ctx->stream));
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return BRE_OK;
+}
+
 int film_gather(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int meanOnly) {
     if (!ctx->film.p) return set_err(ctx, BRE_ERR_INVALID, "bre_film_create has not been called");
     const uint32_t n = ctx->n_pixels;
@@ -406,6 +554,10 @@ int film_gather(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int me
     const size_t imgBytes = (size_t)n * 12;
     int s;
     if ((s = ensure(ctx, ctx->gather, 2 * imgBytes)) != BRE_OK) return s;
+    if (R > 1 && ctx->photon_shard) {
+        if (!ctx->nccl_comm) return set_err(ctx, BRE_ERR_INVALID, "context was created without NCCL");
+        return film_gather_sum(ctx, iter, scale, rgb_out_host, meanOnly);
+    }
     if (R == 1 || !ctx->tile_shard) {
         k_film_resolve_tiles<<<tX * tY, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, W, H, tX, inv, scale, meanOnly, 1, 0,
                                                               (float *)ctx->gather.p);

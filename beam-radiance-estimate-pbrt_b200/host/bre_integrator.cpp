@@ -361,7 +361,11 @@ void BreIntegrator::Render(const Scene &scene) {
     if (!Check(ctx, bre_film_create(ctx, nPixels), "bre_film_create")) { bre_destroy(ctx); return; }
     // the camera pass visits the image tile by tile (photonbeam.cpp:345-347,444-477): tell the library the layout
     if (!Check(ctx, bre_set_ray_grid(ctx, (uint32_t)ext.x, (uint32_t)ext.y), "bre_set_ray_grid")) { bre_destroy(ctx); return; }
-    if (sharded) bre_set_tile_sharding(ctx, 1);
+    // several ranks: "photons" (default) -- every rank keeps the photon paths it traces, builds and queries its own
+    // 1/N of the map, and the partial films are summed on rank 0; "tiles" -- photons all-gathered, image tiles split
+    const bool byPhoton = sharded && sharding != "tiles";
+    if (byPhoton) bre_set_photon_sharding(ctx, 1);
+    else if (sharded) bre_set_tile_sharding(ctx, 1);
 
     // radius schedule fast-forwarded to startiteration (photonbeam.cpp:354-356)
     Float radius = initialRadius;
@@ -413,7 +417,7 @@ void BreIntegrator::Render(const Scene &scene) {
                           : Check(ctx, bre_set_radius(ctx, radius), "bre_set_radius");
         uint64_t stored = 0;
         if (!retrace) {
-        } else if (ok && deviceTracer && sharded && iter == 0) {
+        } else if (ok && deviceTracer && sharded && !byPhoton && iter == 0) {
             // fused: every rank traces its slice of [0, nPaths) and pushes it into everyone's store over NVLink.
             // (The collective traces path indices from 0; later iterations of a sharded render use the split below.)
             ok = Check(ctx, bre_trace_exchange_photons(ctx, nPaths, maxDepth, radius, &stored), "bre_trace_exchange_photons");
@@ -425,7 +429,7 @@ void BreIntegrator::Render(const Scene &scene) {
                            "bre_trace_photons");
             else
                 stored = TracePhotonsHost(ctx, scene, *lightDistr, (uint64_t)iter * nPaths + first, count, radius);
-            if (ok && sharded) ok = Check(ctx, bre_allgather_photons(ctx), "bre_allgather_photons");
+            if (ok && sharded && !byPhoton) ok = Check(ctx, bre_allgather_photons(ctx), "bre_allgather_photons");
         }
         lastPathsEmitted = nPaths;
         // ---- photon structure (photonbeam.cpp:438)
@@ -501,7 +505,7 @@ Integrator *CreateBreIntegrator(const ParamSet &params, std::shared_ptr<const Ca
     return new BreIntegrator(camera, nIterations, photonsPerIter, maxDepth, radius, alpha,
                              writeFreq, renderMedia, tracer == "device", camrays == "device",
                              params.FindOneBool("reusephotons", false), device, startIteration, endIteration,
-                             params.FindOneString("checkpoint", ""));
+                             params.FindOneString("checkpoint", ""), params.FindOneString("sharding", "photons"));
 }
 
 }  // namespace pbrt

@@ -27,6 +27,9 @@
 //   new: "string checkpoint" [""]  film accumulators + iterations done + radius are loaded from this file
 //        when startiteration > 0 and saved to it after the last iteration (bre_film_load / bre_film_save):
 //        a resumed render continues the SAME estimate; the reference's startiteration restores the radius only.
+//   new: "string sharding" ["photons"|"tiles"]  several ranks (BRE_NRANKS / BRE_RANK / BRE_NCCL_ID_FILE): shard the
+//        photon paths (each rank builds and queries its own 1/N of the map, bre_film_gather sums the films; default)
+//        or the 16x16 image tiles (photons all-gathered); rank 0 writes the image either way.
 //   new: "string photontracer" ["host"|"device"]  host = photon paths traced by pbrt's own
 //        Scene/Medium/BSDF code (any scene), device = K1 kernel (matte triangle scenes with point /
 //        spot lights; other scenes: media inside the absorbing world box).
@@ -58,13 +61,14 @@ class BreIntegrator : public Integrator {
     BreIntegrator(std::shared_ptr<const Camera> camera, int nIterations, int photonsPerIteration,
                   int maxDepth, Float initialRadius, Float alpha, int writeFrequency,
                   bool renderMedia, bool deviceTracer, bool deviceCamera, bool reusePhotons, int device,
-                  int startIteration = 0, int endIteration = -1, std::string checkpoint = "")
+                  int startIteration = 0, int endIteration = -1, std::string checkpoint = "",
+                  std::string sharding = "photons")
         : camera(camera), nIterations(nIterations), photonsPerIteration(photonsPerIteration),
           maxDepth(maxDepth), initialRadius(initialRadius), alpha(alpha),
           writeFrequency(writeFrequency), renderMedia(renderMedia), deviceTracer(deviceTracer),
           deviceCamera(deviceCamera), reusePhotons(reusePhotons), device(device),
           startIteration(startIteration), endIteration(endIteration < 0 ? nIterations : endIteration),
-          checkpoint(std::move(checkpoint)) {}
+          checkpoint(std::move(checkpoint)), sharding(std::move(sharding)) {}
     void Render(const Scene &scene);
 
     // test hook: after Render, photons of the last iteration in reference layout (p, alpha, wi)
@@ -88,6 +92,7 @@ class BreIntegrator : public Integrator {
     const int device;
     const int startIteration, endIteration;
     const std::string checkpoint;
+    const std::string sharding;
 };
 
 Integrator *CreateBreIntegrator(const ParamSet &params, std::shared_ptr<const Camera> camera);

@@ -9,10 +9,12 @@ Workload (BASELINE.json configs[2], the 10M-photon config the roofline target is
 heterogeneous GridDensityMedium smoke volume (64^3 grid of 8 seeded Gaussian blobs), ~10M volume
 photons, 1920x1080 camera rays, fixed gather radius.
 
-Multi-GPU (`--scaling strong`, default): the FIXED 1080p frame is split by 16x16 image tile
-(bre_tile_owner, integrators/photonbeam.cpp:345-347) -- a rank answers only its tiles and the film
-tiles are gathered on rank 0; photon paths are split by index and all-gathered.  value = rays of the
-frame / step time.  `--scaling weak`: every rank renders the whole frame at its own sample offset
+Multi-GPU (`--scaling strong`, default): ONE fixed frame on N GPUs.  `--shard photons` (default): the
+photon paths are split by index and stay where they were traced -- every rank builds the LBVH of its 1/N
+of the map, answers all rays from it, and the partial films are summed into rank 0's image
+(bre_set_photon_sharding; the estimate is a sum over photons, integrators/photonbeam.cpp:494-508).
+`--shard tiles`: photons all-gathered, the frame split by 16x16 image tile (bre_tile_owner,
+integrators/photonbeam.cpp:345-347), film tiles gathered on rank 0.  value = rays of the frame / step time.  `--scaling weak`: every rank renders the whole frame at its own sample offset
 (N x samples per pixel), value = N x rays / step time.
 
 `value`   = beam queries/s, whole job, inputs resident in HBM (device-timed, CUDA events).
@@ -275,14 +277,18 @@ def run_ours(args):
     if sharded:
         if not tile:
             raise SystemExit("--scaling strong on several GPUs needs the tile path")
-        ctx.set_tile_sharding(True)
+        if args.shard == "photons":
+            ctx.set_photon_sharding(True)   # every rank keeps its photons: 1/N trace, build and photon tests, films summed
+        else:
+            ctx.set_tile_sharding(True)     # photons replicated, 1/N of the image tiles per rank
+    by_photon = sharded and args.shard == "photons"
     r2c, c2w = camera_matrices(W, H)
     stream = torch.cuda.ExternalStream(ctx.stream, device=torch.device("cuda", local))
 
     def photon_pass():
         # N > 1: fused trace + push over NVLink P2P (--exchange p2p, default) or trace + NCCL all-gather
-        if world > 1 and args.exchange == "p2p":
-            ctx.trace_exchange_photons(n_paths, MAX_DEPTH, radius)
+        if world > 1 and (args.exchange == "p2p" or by_photon):
+            ctx.trace_exchange_photons(n_paths, MAX_DEPTH, radius)   # photon sharding: the slice stays local
             return
         ctx.clear_photons()
         ctx.trace_photons(p_first, p_count, MAX_DEPTH, radius)
@@ -412,7 +418,8 @@ def run_ours(args):
         "config": base_config(args.workload, wl),
         "detail": {"photons_traced": int(n_photons), "photon_paths": int(n_paths), "rays_per_step": int(total_rays),
                    "max_leaf_photons": ctx_leaf(args), "k5_path": "image tiles" if tile else "ray packets",
-                   "multi_gpu": (("16x16 image tiles round-robin over ranks + film gather to rank 0"
+                   "multi_gpu": ((("photon paths sharded: per-rank trace + LBVH + query of 1/N of the map, films summed on rank 0"
+                                   if by_photon else "16x16 image tiles round-robin over ranks + film gather to rank 0")
                                   if strong else "every rank renders the whole frame at its own sample offset")
                                  if world > 1 else None),
                    "exchange": (args.exchange if world > 1 else None),
@@ -669,6 +676,9 @@ def main():
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"])
     ap.add_argument("--leaf", type=int, default=0)
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"])
+    ap.add_argument("--shard", default="photons", choices=["photons", "tiles"],
+                    help="strong scaling on N > 1 GPUs: shard the photon paths (each rank builds and queries its own "
+                         "1/N of the map, films summed) or the image tiles (photons replicated)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-tile", action="store_true", help="K5 packet walk instead of the image-tile walk (A/B)")
     ap.add_argument("--no-host-rays", action="store_true", help="skip the second end-to-end figure (host rays)")

@@ -238,6 +238,14 @@ int bre_set_ray_grid(bre_ctx *ctx, uint32_t width, uint32_t height);
  * only the 16x16 tiles bre_tile_owner() gives to this rank (the other pixels' radiance stays 0);
  * bre_film_gather() then assembles the image on rank 0. */
 int bre_set_tile_sharding(bre_ctx *ctx, int enabled);
+/* Multi-GPU render sharded by PHOTON PATH instead (the estimate is a sum over photons, integrators/
+ * photonbeam.cpp:494-508): when enabled on a context with n_ranks > 1, bre_trace_exchange_photons traces this
+ * rank's slice of the paths (bre_shard_range) and keeps it -- no exchange --, bre_build builds the LBVH of that
+ * slice only, every query answers all its rays from it, and bre_film_gather SUMS the partial films (a
+ * reduce-scatter over CUDA-IPC mappings of the films, the owner of a pixel run resolving it into rank 0's image;
+ * BRE_NO_P2P=1: ncclReduce).  Trace, build and the photon tests of the query all shrink with the rank count;
+ * only K6 (the rays' optical-depth tables) is replicated.  Enabling one sharding mode disables the other. */
+int bre_set_photon_sharding(bre_ctx *ctx, int enabled);
 /* Counting pass on the canonical tree for the same rays (fills V,T,H,bytes) plus the
  * production kernel's own counters. */
 int bre_count(bre_ctx *ctx, uint32_t n_rays, const float *o_xyz_tmax, const float *d_xyz);
@@ -259,7 +267,8 @@ int bre_film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out);
 /* rgb_out: n_pixels*3 floats = L = Ld/(iter+1) (integrators/photonbeam.cpp:578), no colour conversion:
  * the array a pbrt host passes to Film::SetImage (core/film.cpp:132-140) before Film::WriteImage. */
 int bre_film_mean(bre_ctx *ctx, int iter, float *rgb_out);
-/* Multi-GPU camera pass (bre_set_tile_sharding): every rank resolves the 16x16 tiles it owns (bre_tile_owner,
+/* Multi-GPU camera pass.  bre_set_photon_sharding: the partial films of all ranks are summed pixel by pixel (rank
+ * order), resolved and written into rank 0's image.  bre_set_tile_sharding: every rank resolves the 16x16 tiles it owns (bre_tile_owner,
  * integrators/photonbeam.cpp:345-347) and writes them straight into rank 0's image over NVLink (CUDA-IPC
  * mapping; BRE_NO_P2P=1: ncclReduce of disjoint tiles).  Collective: every rank calls it with the same iter /
  * scale / mean_only; rgb_out (n_pixels*3 floats) is filled on rank 0 only and may be NULL on the others (NULL on

@@ -99,7 +99,7 @@ int main(int argc, char **argv) {
         const char *eq = strchr(argv[i], '=');
         if (!eq) continue;
         const std::string key(argv[i], eq - argv[i]), val(eq + 1);
-        if (key == "checkpoint") { std::unique_ptr<std::string[]> a(new std::string[1]); a[0] = val; ps.AddString(key, std::move(a), 1); }
+        if (key == "checkpoint" || key == "sharding") { std::unique_ptr<std::string[]> a(new std::string[1]); a[0] = val; ps.AddString(key, std::move(a), 1); }
         else if (key == "rendersurfaces") { std::unique_ptr<bool[]> a(new bool[1]); a[0] = val == "true"; ps.AddBool(key, std::move(a), 1); }
         else addInt(key.c_str(), atoi(val.c_str()));
     }

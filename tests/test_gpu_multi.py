@@ -42,17 +42,33 @@ def test_tile_sharded_render_equals_single_gpu():
 
 
 @pytest.mark.skipif(_n_gpus() < 2, reason="needs two GPUs on one box")
+def test_photon_sharded_render_equals_single_gpu():
+    """tools/check_photon_shard.py under torchrun, world size 2: every rank keeps the photon paths it traced, builds and
+    queries its own half of the map, bre_film_gather sums the films (per-rank stores = slices of the single-rank
+    store, hit counts add up to the single-rank counts, image within 1e-4 mean / 1e-3 max; the gather itself bit-exact
+    on exactly summable partials, P2P reduce-scatter == ncclReduce)."""
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", "29539", os.path.join(ROOT, "tools", "check_photon_shard.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    lines = [ln.split(":", 1)[1] for ln in r.stdout.splitlines() if ln.startswith("rank ")]
+    assert len(lines) >= 5 and all("False" not in ln for ln in lines), r.stdout[-2000:]
+
+
+@pytest.mark.skipif(_n_gpus() < 2, reason="needs two GPUs on one box")
+@pytest.mark.parametrize("sharding", ["photons", "tiles"])
 @pytest.mark.parametrize("tracer", ["device", "host"])
-def test_pbrt_adapter_two_ranks(tmp_path, tracer):
-    """The pbrt-side adapter as two processes (BRE_RANK / BRE_NRANKS / BRE_NCCL_ID_FILE): photon paths split by index and
-    exchanged, image tiles sharded, film gathered -- rank 0 writes the image Film::WriteImage would, equal to the
-    single-process render within the radiance tolerance."""
+def test_pbrt_adapter_two_ranks(tmp_path, tracer, sharding):
+    """The pbrt-side adapter as two processes (BRE_RANK / BRE_NRANKS / BRE_NCCL_ID_FILE), "string sharding" photons
+    (paths split by index and kept, films summed) or tiles (paths exchanged, image tiles split, film gathered) --
+    rank 0 writes the image Film::WriteImage would, equal to the single-process render within the radiance
+    tolerance."""
     import numpy as np
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from test_gpu_pbrt_adapter import BIN, read_pfm
     if not os.path.exists(BIN):
         pytest.skip("oracle/_ref/bre_pbrt_render not built")
-    args = [tracer, "48", "8000", "0.2", "2", "device", "rendersurfaces=false"]
+    args = [tracer, "48", "8000", "0.2", "2", "device", "rendersurfaces=false", "sharding=" + sharding]
     subprocess.run([BIN, str(tmp_path / "one.pfm"), str(tmp_path / "d.bin"), *args], check=True, timeout=300)
     one = read_pfm(str(tmp_path / "one.pfm"))
     procs = []
