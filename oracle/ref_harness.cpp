@@ -16,6 +16,12 @@
 //        PerspectiveCamera + Scene::Intersect, and evaluates the beam radiance estimate over the
 //        dumped photons by BRUTE FORCE with reference vector/phase/medium/kernel code.
 //        out.bin = photons, rays, per-ray hit lists and radiance (format: write_fogbox below).
+//        A trailing "digest" stores per-ray hit counts + set digests instead of the lists (configs[0]-size fixture).
+//   ref_harness gridspot <out.bin> <nPaths> <res> <radius>
+//        query fixture for a GRID medium lit by a SPOT light: photon paths walked by reference classes through a
+//        GridDensityMedium (as mode trace), camera rays of the reference's PerspectiveCamera, brute-force estimate
+//        with transmittance from a fine integral of the reference's own Density() (its Tr is a stochastic
+//        ratio-tracking estimate, media/grid.cpp:89-121; the integral is what it estimates).
 //   ref_harness trace <out.bin> <homogeneous|grid> <firstPath> <nPaths> <maxDepth>
 //        the volume-photon deposit loop (integrators/photonmap.cpp:696-724) driven with the
 //        sampler stream of integrators/photonbeam.cpp:386-391 inside an absorbing triangle box,
@@ -410,7 +416,14 @@ struct BinWriter {
 };
 
 // ---------------------------------------------------------------- mode: fogbox
-void fogbox(const char *path, int nVolumeWanted, int res, float radius, uint32_t keep) {
+// order-independent hit-set digest of the large fixtures: sum over the set of splitmix64(index)
+static inline uint64_t hit_hash(uint32_t i) {
+    uint64_t z = (uint64_t)i + 0x9e3779b97f4a7c15ull;
+    z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ull;
+    z = (z ^ (z >> 27)) * 0x94d049bb133111ebull;
+    return z ^ (z >> 31);
+}
+void fogbox(const char *path, int nVolumeWanted, int res, float radius, uint32_t keep, bool digestOnly) {
     const float sa = 0.05f, ss = 0.4f, g = 0.3f;
     HomogeneousMedium fog{Spectrum(sa), Spectrum(ss), g};
     MediumInterface inFog(&fog, &fog);
@@ -455,37 +468,58 @@ void fogbox(const char *path, int nVolumeWanted, int res, float radius, uint32_t
             push3(rd, ray.d);
         }
 
-    // ---- beam radiance estimate, brute force, reference arithmetic classes
+    // ---- beam radiance estimate, brute force, reference arithmetic classes (rays over all host threads)
     const float nPaths = (float)dump.nShot;
     const float r2 = radius * radius;
     HenyeyGreenstein hg(g);
-    StreamSampler smp(1);
+    const size_t nRays = rays.size();
+    std::vector<std::vector<uint32_t>> hitsOf(nRays);
+    std::vector<float> rgb(3 * nRays);
+    {
+        std::atomic<size_t> next(0);
+        std::vector<std::thread> pool;
+        const unsigned nThreads = std::max(1u, std::thread::hardware_concurrency());
+        for (unsigned tIdx = 0; tIdx < nThreads; ++tIdx)
+            pool.emplace_back([&]() {
+                StreamSampler smp(1);
+                for (size_t q = next++; q < nRays; q = next++) {
+                    const Ray &ray = rays[q];
+                    Spectrum L(0.f);
+                    for (uint32_t i = 0; i < n; ++i) {
+                        Point3f p(dump.p[3 * i], dump.p[3 * i + 1], dump.p[3 * i + 2]);
+                        Vector3f v = p - ray.o;
+                        Float t = Dot(v, ray.d);
+                        if (!(t > 0 && t < ray.tMax)) continue;
+                        Vector3f w = v - t * ray.d;
+                        Float d2 = w.LengthSquared();
+                        if (!(d2 < r2)) continue;            // strict <, core/kdtree.h:182-184
+                        hitsOf[q].push_back(i);
+                        float pp[3] = {p.x, p.y, p.z};
+                        Point3f c = ray(t);
+                        float cc[3] = {c.x, c.y, c.z};
+                        Float k = refx::kernel(pp, cc, r2);   // integrators/photonmap.cpp:170-174
+                        Vector3f wi(dump.wi[3 * i], dump.wi[3 * i + 1], dump.wi[3 * i + 2]);
+                        Spectrum alpha = rgbS(dump.alpha[3 * i], dump.alpha[3 * i + 1], dump.alpha[3 * i + 2]);
+                        Spectrum Tr = fog.Tr(Ray(ray.o, ray.d, t), smp);
+                        // photonmap.cpp:198 normalisation, vsppm.cpp:488-489 phase orientation
+                        L += (k / (nPaths * r2)) * hg.p(-ray.d, wi) * Tr * alpha;
+                    }
+                    Float c3[3];
+                    L.ToRGB(c3);
+                    rgb[3 * q] = c3[0]; rgb[3 * q + 1] = c3[1]; rgb[3 * q + 2] = c3[2];
+                }
+            });
+        for (auto &th : pool) th.join();
+    }
     std::vector<uint64_t> offs(1, 0);
-    std::vector<uint32_t> idx;
-    std::vector<float> rgb;
-    for (const Ray &ray : rays) {
-        Spectrum L(0.f);
-        for (uint32_t i = 0; i < n; ++i) {
-            Point3f p(dump.p[3 * i], dump.p[3 * i + 1], dump.p[3 * i + 2]);
-            Vector3f v = p - ray.o;
-            Float t = Dot(v, ray.d);
-            if (!(t > 0 && t < ray.tMax)) continue;
-            Vector3f w = v - t * ray.d;
-            Float d2 = w.LengthSquared();
-            if (!(d2 < r2)) continue;            // strict <, core/kdtree.h:182-184
-            idx.push_back(i);
-            float pp[3] = {p.x, p.y, p.z};
-            Point3f c = ray(t);
-            float cc[3] = {c.x, c.y, c.z};
-            Float k = refx::kernel(pp, cc, r2);   // integrators/photonmap.cpp:170-174
-            Vector3f wi(dump.wi[3 * i], dump.wi[3 * i + 1], dump.wi[3 * i + 2]);
-            Spectrum alpha = rgbS(dump.alpha[3 * i], dump.alpha[3 * i + 1], dump.alpha[3 * i + 2]);
-            Spectrum Tr = fog.Tr(Ray(ray.o, ray.d, t), smp);
-            // photonmap.cpp:198 normalisation, vsppm.cpp:488-489 phase orientation
-            L += (k / (nPaths * r2)) * hg.p(-ray.d, wi) * Tr * alpha;
-        }
+    std::vector<uint32_t> idx, counts;
+    std::vector<uint64_t> digest;
+    for (size_t q = 0; q < nRays; ++q) {
+        uint64_t dg = 0;
+        for (uint32_t i : hitsOf[q]) { idx.push_back(i); dg += hit_hash(i); }
         offs.push_back(idx.size());
-        pushS(rgb, L);
+        counts.push_back((uint32_t)hitsOf[q].size());
+        digest.push_back(dg);
     }
 
     BinWriter bw(path);
@@ -495,9 +529,58 @@ void fogbox(const char *path, int nVolumeWanted, int res, float radius, uint32_t
     bw.u4("res", {(uint32_t)res, (uint32_t)res});
     bw.f4("photon_p", dump.p); bw.f4("photon_alpha", dump.alpha); bw.f4("photon_wi", dump.wi);
     bw.f4("ray_o_tmax", ro); bw.f4("ray_d", rd);
-    bw.u8("hit_offsets", offs); bw.u4("hit_indices", idx); bw.f4("radiance", rgb);
+    if (digestOnly) {
+        // large fixtures: per-ray hit count + order-independent digest (sum of splitmix64(photon index)) instead of lists
+        bw.u4("hit_counts", counts); bw.u8("hit_digest", digest);
+    } else {
+        bw.u8("hit_offsets", offs); bw.u4("hit_indices", idx);
+    }
+    bw.f4("radiance", rgb);
     fprintf(stderr, "fogbox: %u volume photons from %u paths, %zu rays, %zu hits\n", n, dump.nShot,
             rays.size(), idx.size());
+}
+
+// The volume-photon deposit loop of modes trace / gridspot: sampler stream of photonbeam.cpp:386-391, deposit rule of
+// photonmap.cpp:696-724, every step executed by reference classes.
+static void walk_volume_paths(const Scene &scene, const Distribution1D *lightDistr, uint64_t first, uint64_t nPaths,
+                              int maxDepth, std::vector<float> &pp, std::vector<float> &pa, std::vector<float> &pw,
+                              std::vector<uint32_t> &pid) {
+    MemoryArena arena;
+    for (uint64_t pi = first; pi < first + nPaths; ++pi) {
+        StreamSampler sampler(pi + 1);                       // photonbeam.cpp:386-391
+        Float lightPdf;
+        int lightNum = lightDistr->SampleDiscrete(sampler.Get1D(), &lightPdf);   // :394-398
+        const std::shared_ptr<Light> &light = scene.lights[lightNum];
+        Point2f uLight0 = sampler.Get2D();
+        Point2f uLight1 = sampler.Get2D();
+        Float uLightTime = sampler.Get1D();
+        RayDifferential photonRay;
+        Normal3f nLight;
+        Float pdfPos, pdfDir;
+        Spectrum Le = light->Sample_Le(uLight0, uLight1, uLightTime, &photonRay, &nLight, &pdfPos, &pdfDir);
+        if (pdfPos == 0 || pdfDir == 0 || Le.IsBlack()) continue;
+        Spectrum alpha = (AbsDot(nLight, photonRay.d) * Le) / (lightPdf * pdfPos * pdfDir);   // :413-414
+        if (alpha.IsBlack()) continue;
+        SurfaceInteraction sisect;
+        int nIntersections = 0;
+        while (scene.Intersect(photonRay, &sisect)) {        // photonmap.cpp:696
+            ++nIntersections;
+            MediumInteraction misect;
+            if (photonRay.medium) alpha *= photonRay.medium->Sample(photonRay, sampler, arena, &misect);
+            if (alpha.IsBlack()) break;
+            if (!misect.IsValid()) break;                    // reached the absorbing wall
+            const Vector3f wo = -photonRay.d;
+            Vector3f wi;
+            misect.phase->Sample_p(wo, &wi, sampler.Get2D());
+            push3(pp, misect.p); pushS(pa, alpha); push3(pw, wo);   // Photon(misect.p, alpha, wo) :720-723
+            pid.push_back((uint32_t)pi);
+            photonRay = misect.SpawnRay(wi);
+            if (nIntersections >= maxDepth) break;           // :794
+            Float sample = sampler.Get1D();                  // RR draw, continueProb == 1 (:799-804)
+            if (sample > 1.f) break;
+        }
+        arena.Reset();
+    }
 }
 
 // ---------------------------------------------------------------- mode: trace
@@ -536,42 +619,7 @@ void trace(const char *path, const char *kind, uint64_t first, uint64_t nPaths, 
 
     std::vector<float> pp, pa, pw;
     std::vector<uint32_t> pid;
-    MemoryArena arena;
-    for (uint64_t pi = first; pi < first + nPaths; ++pi) {
-        StreamSampler sampler(pi + 1);                       // photonbeam.cpp:386-391
-        Float lightPdf;
-        int lightNum = lightDistr->SampleDiscrete(sampler.Get1D(), &lightPdf);   // :394-398
-        const std::shared_ptr<Light> &light = scene.lights[lightNum];
-        Point2f uLight0 = sampler.Get2D();
-        Point2f uLight1 = sampler.Get2D();
-        Float uLightTime = sampler.Get1D();
-        RayDifferential photonRay;
-        Normal3f nLight;
-        Float pdfPos, pdfDir;
-        Spectrum Le = light->Sample_Le(uLight0, uLight1, uLightTime, &photonRay, &nLight, &pdfPos, &pdfDir);
-        if (pdfPos == 0 || pdfDir == 0 || Le.IsBlack()) continue;
-        Spectrum alpha = (AbsDot(nLight, photonRay.d) * Le) / (lightPdf * pdfPos * pdfDir);   // :413-414
-        if (alpha.IsBlack()) continue;
-        SurfaceInteraction sisect;
-        int nIntersections = 0;
-        while (scene.Intersect(photonRay, &sisect)) {        // photonmap.cpp:696
-            ++nIntersections;
-            MediumInteraction misect;
-            if (photonRay.medium) alpha *= photonRay.medium->Sample(photonRay, sampler, arena, &misect);
-            if (alpha.IsBlack()) break;
-            if (!misect.IsValid()) break;                    // reached the absorbing wall
-            const Vector3f wo = -photonRay.d;
-            Vector3f wi;
-            misect.phase->Sample_p(wo, &wi, sampler.Get2D());
-            push3(pp, misect.p); pushS(pa, alpha); push3(pw, wo);   // Photon(misect.p, alpha, wo) :720-723
-            pid.push_back((uint32_t)pi);
-            photonRay = misect.SpawnRay(wi);
-            if (nIntersections >= maxDepth) break;           // :794
-            Float sample = sampler.Get1D();                  // RR draw, continueProb == 1 (:799-804)
-            if (sample > 1.f) break;
-        }
-        arena.Reset();
-    }
+    walk_volume_paths(scene, lightDistr.get(), first, nPaths, maxDepth, pp, pa, pw, pid);
     std::vector<float> w2mf;
     for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) w2mf.push_back(w2m.GetMatrix().m[i][j]);
     std::vector<float> lightAxis;
@@ -588,6 +636,148 @@ void trace(const char *path, const char *kind, uint64_t first, uint64_t nPaths, 
     bw.u8("range", {first, nPaths, (uint64_t)maxDepth});
     bw.f4("photon_p", pp); bw.f4("photon_alpha", pa); bw.f4("photon_wi", pw); bw.u4("path_id", pid);
     fprintf(stderr, "trace %s: %zu photons from %llu paths\n", kind, pid.size(), (unsigned long long)nPaths);
+}
+
+// ---------------------------------------------------------------- mode: gridspot
+// Query fixture for a heterogeneous medium lit by a spot light.  Photons: reference classes walk paths from a
+// SpotLight (lights/spot.cpp) through a GridDensityMedium filling the box (walk_volume_paths).  Rays: the reference's
+// PerspectiveCamera inside the box + Scene::Intersect for tMax.  Estimate: brute force over all photons with the
+// reference's vector / kernel / phase code; the transmittance to a hit at depth t is exp(-sigma_t * integral of the
+// reference's Density() over [0, t]) with the integral taken by a 4096-step midpoint rule in double -- the quantity
+// GridDensityMedium::Tr (ratio tracking, media/grid.cpp:89-121) estimates without bias (see mode gridtr).
+void gridspot(const char *path, uint64_t nPaths, int res, float radius) {
+    const float sa = 0.05f, ss = 1.6f, g = 0.3f;
+    const int nx = 12, ny = 10, nz = 8;
+    std::vector<float> dens = test_grid(nx, ny, nz, 43);
+    Transform m2w = Translate(Vector3f(kBoxLo[0], kBoxLo[1], kBoxLo[2])) *
+                    Scale(kBoxHi[0] - kBoxLo[0], kBoxHi[1] - kBoxLo[1], kBoxHi[2] - kBoxLo[2]);
+    Transform w2m = Inverse(m2w);
+    GridDensityMedium med(Spectrum(sa), Spectrum(ss), g, nx, ny, nz, m2w, dens.data());
+    MediumInterface in(&med, &med);
+    std::vector<std::shared_ptr<Primitive>> prims = box_prims(nullptr, in);
+    std::shared_ptr<BVHAccel> bvh = std::make_shared<BVHAccel>(prims);
+    std::vector<std::shared_ptr<Light>> lights;
+    const Point3f spotFrom(-1.5f, 1.8f, -1.f), spotTo(0.4f, 0.2f, 0.6f);
+    {
+        ParamSet ps;
+        std::unique_ptr<Point3f[]> from(new Point3f[1]), to(new Point3f[1]);
+        from[0] = spotFrom; to[0] = spotTo;
+        std::unique_ptr<Float[]> I(new Float[3]), ca(new Float[1]), cd(new Float[1]);
+        I[0] = 30.f; I[1] = 25.f; I[2] = 20.f; ca[0] = 30.f; cd[0] = 8.f;
+        ps.AddPoint3f("from", std::move(from), 1); ps.AddPoint3f("to", std::move(to), 1);
+        ps.AddRGBSpectrum("I", std::move(I), 3);
+        ps.AddFloat("coneangle", std::move(ca), 1); ps.AddFloat("conedeltaangle", std::move(cd), 1);
+        lights.push_back(CreateSpotLight(Transform(), &med, ps));
+    }
+    Scene scene(bvh, lights);
+    std::unique_ptr<Distribution1D> lightDistr = ComputeLightPowerDistribution(scene);
+    std::vector<float> pp, pa, pw;
+    std::vector<uint32_t> pid;
+    walk_volume_paths(scene, lightDistr.get(), 0, nPaths, 5, pp, pa, pw, pid);
+    const uint32_t n = (uint32_t)pid.size();
+
+    Film *film = new Film(Point2i(res, res), Bounds2f(Point2f(0, 0), Point2f(1, 1)),
+                          std::unique_ptr<Filter>(new BoxFilter(Vector2f(0.5f, 0.5f))), 35.f,
+                          "/tmp/bre_ref_gridspot.pfm", 1.f);
+    Transform c2w = Inverse(LookAt(Point3f(0.3f, 0.6f, -3.6f), Point3f(0.1f, 0.4f, 0.f), Vector3f(0, 1, 0)));
+    AnimatedTransform ac2w(&c2w, 0.f, &c2w, 1.f);
+    std::shared_ptr<const Camera> camera = std::make_shared<PerspectiveCamera>(
+        ac2w, Bounds2f(Point2f(-1, -1), Point2f(1, 1)), 0.f, 1.f, 0.f, 1e6f, 50.f, film, &med);
+    std::vector<float> ro, rd;
+    std::vector<Ray> rays;
+    for (int y = 0; y < res; ++y)
+        for (int x = 0; x < res; ++x) {
+            CameraSample cs;
+            cs.pFilm = Point2f(x + 0.5f, y + 0.5f);
+            cs.pLens = Point2f(0.5f, 0.5f);
+            cs.time = 0.f;
+            RayDifferential ray;
+            camera->GenerateRayDifferential(cs, &ray);
+            SurfaceInteraction isect;
+            scene.Intersect(ray, &isect);   // shortens ray.tMax (core/primitive.cpp:97-101)
+            rays.push_back(ray);
+            ro.push_back(ray.o.x); ro.push_back(ray.o.y); ro.push_back(ray.o.z); ro.push_back(ray.tMax);
+            push3(rd, ray.d);
+        }
+    const float nPathsF = (float)nPaths;
+    const float r2 = radius * radius;
+    const double sigT = (double)sa + (double)ss;
+    HenyeyGreenstein hg(g);
+    const size_t nRays = rays.size();
+    std::vector<std::vector<uint32_t>> hitsOf(nRays);
+    std::vector<std::vector<float>> tauOf(nRays);
+    std::vector<float> rgb(3 * nRays);
+    {
+        std::atomic<size_t> next(0);
+        std::vector<std::thread> pool;
+        const unsigned nThreads = std::max(1u, std::thread::hardware_concurrency());
+        for (unsigned tIdx = 0; tIdx < nThreads; ++tIdx)
+            pool.emplace_back([&]() {
+                for (size_t q = next++; q < nRays; q = next++) {
+                    const Ray &ray = rays[q];
+                    Spectrum L(0.f);
+                    for (uint32_t i = 0; i < n; ++i) {
+                        Point3f p(pp[3 * i], pp[3 * i + 1], pp[3 * i + 2]);
+                        Vector3f v = p - ray.o;
+                        Float t = Dot(v, ray.d);
+                        if (!(t > 0 && t < ray.tMax)) continue;
+                        Vector3f w = v - t * ray.d;
+                        Float d2 = w.LengthSquared();
+                        if (!(d2 < r2)) continue;            // strict <, core/kdtree.h:182-184
+                        hitsOf[q].push_back(i);
+                        float ppf[3] = {p.x, p.y, p.z};
+                        Point3f c = ray(t);
+                        float cc[3] = {c.x, c.y, c.z};
+                        Float k = refx::kernel(ppf, cc, r2);   // integrators/photonmap.cpp:170-174
+                        Vector3f wi(pw[3 * i], pw[3 * i + 1], pw[3 * i + 2]);
+                        Spectrum alpha = rgbS(pa[3 * i], pa[3 * i + 1], pa[3 * i + 2]);
+                        // optical depth over [0, t]: fine midpoint integral of the reference's Density() in medium space
+                        Ray rm = w2m(Ray(ray.o, ray.d, t));
+                        Float t0, t1;
+                        double tau = 0;
+                        if (Bounds3f(Point3f(0, 0, 0), Point3f(1, 1, 1)).IntersectP(rm, &t0, &t1)) {
+                            const int N = 4096;
+                            const double dt = ((double)t1 - (double)t0) / N;
+                            for (int s2 = 0; s2 < N; ++s2) {
+                                const double tt = (double)t0 + (s2 + 0.5) * dt;
+                                Point3f pm((Float)(rm.o.x + rm.d.x * tt), (Float)(rm.o.y + rm.d.y * tt),
+                                           (Float)(rm.o.z + rm.d.z * tt));
+                                tau += (double)med.Density(pm) * dt;
+                            }
+                        }
+                        tauOf[q].push_back((float)tau);
+                        const Float Tr = (Float)std::exp(-sigT * tau);
+                        L += (k / (nPathsF * r2)) * hg.p(-ray.d, wi) * Tr * alpha;
+                    }
+                    Float c3[3];
+                    L.ToRGB(c3);
+                    rgb[3 * q] = c3[0]; rgb[3 * q + 1] = c3[1]; rgb[3 * q + 2] = c3[2];
+                }
+            });
+        for (auto &th : pool) th.join();
+    }
+    std::vector<uint64_t> offs(1, 0);
+    std::vector<uint32_t> idx;
+    std::vector<float> taus;
+    for (size_t q = 0; q < nRays; ++q) {
+        idx.insert(idx.end(), hitsOf[q].begin(), hitsOf[q].end());
+        taus.insert(taus.end(), tauOf[q].begin(), tauOf[q].end());
+        offs.push_back(idx.size());
+    }
+    std::vector<float> w2mf;
+    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) w2mf.push_back(w2m.GetMatrix().m[i][j]);
+    BinWriter bw(path);
+    bw.f4("medium", {sa, sa, sa, ss, ss, ss, g});
+    bw.u4("grid_dims", {(uint32_t)nx, (uint32_t)ny, (uint32_t)nz});
+    bw.f4("grid_density", dens); bw.f4("w2m", w2mf);
+    bw.f4("radius", {radius});
+    bw.f4("n_paths", {nPathsF});
+    bw.u4("res", {(uint32_t)res, (uint32_t)res});
+    bw.f4("photon_p", pp); bw.f4("photon_alpha", pa); bw.f4("photon_wi", pw);
+    bw.f4("ray_o_tmax", ro); bw.f4("ray_d", rd);
+    bw.u8("hit_offsets", offs); bw.u4("hit_indices", idx); bw.f4("hit_tau", taus); bw.f4("radiance", rgb);
+    fprintf(stderr, "gridspot: %u volume photons from %llu paths, %zu rays, %zu hits\n", n, (unsigned long long)nPaths,
+            rays.size(), idx.size());
 }
 
 // ---------------------------------------------------------------- mode: surfaces
@@ -903,7 +1093,12 @@ int main(int argc, char **argv) {
     PbrtOptions.nThreads = 1;   // ShootPhotons claims blocks under a mutex: one thread = one order
     if (argc >= 3 && !strcmp(argv[1], "primitives")) { primitives(argv[2]); return 0; }
     if (argc >= 6 && !strcmp(argv[1], "fogbox")) {
-        fogbox(argv[2], atoi(argv[3]), atoi(argv[4]), (float)atof(argv[5]), argc >= 7 ? (uint32_t)atoi(argv[6]) : 0u);
+        fogbox(argv[2], atoi(argv[3]), atoi(argv[4]), (float)atof(argv[5]), argc >= 7 ? (uint32_t)atoi(argv[6]) : 0u,
+               argc >= 8 && !strcmp(argv[7], "digest"));
+        return 0;
+    }
+    if (argc >= 6 && !strcmp(argv[1], "gridspot")) {
+        gridspot(argv[2], (uint64_t)atoll(argv[3]), atoi(argv[4]), (float)atof(argv[5]));
         return 0;
     }
     if (argc >= 7 && !strcmp(argv[1], "trace")) {

@@ -11,6 +11,11 @@ compressed .npz fixtures.  The fixtures travel to the GPU box; /root/reference d
   ref_fogbox.npz             photons dumped from the reference's PhotonIntegrator::ShootPhotons on the
                              fog-box scene + reference camera rays + brute-force
                              beam radiance estimate evaluated with reference arithmetic classes
+  ref_fogbox_100k.npz        the same at configs[0] size: 100 000 reference photons, 256 x 256 reference camera rays; per-ray
+                             hit COUNTS and order-independent set digests (sum of splitmix64(index)) instead of lists
+  ref_gridspot.npz           query fixture for a GridDensityMedium lit by a SpotLight: photons walked by reference classes,
+                             reference camera rays, brute-force estimate with transmittance from a fine integral of the
+                             reference's Density()
   ref_trace_homogeneous.npz  volume-photon deposit loop executed by reference classes
   ref_trace_grid.npz         (sampler stream of photonbeam.cpp:386-391, deposit rule photonmap.cpp:696-724)
   ref_gridtr.npz             GridDensityMedium::Tr statistics + fine integral of the reference's Density() through the
@@ -85,7 +90,23 @@ def gridtr(tmp, n_rays=24, n_samples=4_000_000):
     np.savez_compressed(os.path.join(HERE, "ref_gridtr.npz"), **out)
 
 
+def fogbox_big(tmp):
+    fb = os.path.join(tmp, "fogbox_100k.bin")
+    subprocess.check_call([HARNESS, "fogbox", fb, "100000", "256", "0.05", "100000", "digest"], stdout=subprocess.DEVNULL)
+    np.savez_compressed(os.path.join(HERE, "ref_fogbox_100k.npz"), **read_bref(fb))
+
+
+def gridspot(tmp):
+    gb = os.path.join(tmp, "gridspot.bin")
+    subprocess.check_call([HARNESS, "gridspot", gb, "5000", "40", "0.11"])
+    np.savez_compressed(os.path.join(HERE, "ref_gridspot.npz"), **read_bref(gb))
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] in ("fogbox_100k", "gridspot"):       # only this fixture
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "ref", "-j8"])
+        {"fogbox_100k": fogbox_big, "gridspot": gridspot}[sys.argv[1]](tempfile.mkdtemp())
+        return
     if len(sys.argv) > 1 and sys.argv[1] == "gridtr":       # only this fixture
         subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "ref", "-j8"])
         gridtr(tempfile.mkdtemp())
@@ -118,6 +139,8 @@ def main():
     subprocess.check_call([HARNESS, "surfaces", sb, "0", "4000", "6", "64", "48"])
     np.savez_compressed(os.path.join(HERE, "ref_surfaces.npz"), **read_bref(sb))
     gridtr(tmp)
+    fogbox_big(tmp)
+    gridspot(tmp)
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)), "bytes")

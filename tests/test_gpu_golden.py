@@ -116,3 +116,68 @@ def test_device_photon_tracing_vs_reference_classes(bre, kind):
         assert same >= 0.97 * len(starts), f"{same}/{len(starts)} paths match"
     finally:
         ctx.close()
+
+
+# ------------------------------------------------------------------ larger reference fixtures (round 2)
+def _hit_digests(offs, idx):
+    from test_oracle_golden import hit_digests
+    return hit_digests(offs, idx)
+
+
+@pytest.mark.parametrize("grid", [False, True])
+def test_reference_photon_dump_configs0_size(bre, grid):
+    """BASELINE.json configs[0] size -- 100 000 photons of the reference's ShootPhotons, 256 x 256 reference camera rays,
+    brute force by reference classes: per-ray hit counts and set digests bit-exact, radiance within 1e-4 mean /
+    1e-3 max, on the per-ray walk and (grid) the image-tile path."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    g = gold("ref_fogbox_100k.npz")
+    m = g["medium"]
+    ctx = bre.Bre(device=0)
+    try:
+        ctx.set_medium_homogeneous(m[0:3], m[3:6], float(m[6]))
+        ctx.upload_photons(g["photon_p"].reshape(-1, 3), g["photon_alpha"].reshape(-1, 3),
+                           g["photon_wi"].reshape(-1, 3), radius=float(g["radius"][0]))
+        ctx.build()
+        if grid:
+            ctx.set_ray_grid(int(g["res"][0]), int(g["res"][1]))
+        ro, rd = g["ray_o_tmax"].reshape(-1, 4), g["ray_d"].reshape(-1, 3)
+        rgb, offs, idx = ctx.query(ro, rd, float(g["n_paths"][0]), want_hits=True)
+        assert np.array_equal(np.diff(offs.astype(np.int64)), g["hit_counts"].astype(np.int64))
+        assert np.array_equal(_hit_digests(offs, idx), g["hit_digest"])
+        ref = g["radiance"].reshape(-1, 3).astype(np.float64)
+        err = np.abs(rgb - ref)
+        assert err.mean() <= MEAN_TOL * np.abs(ref).mean()
+        assert err.max() <= MAX_TOL * np.abs(ref).max()
+    finally:
+        ctx.close()
+
+
+@pytest.mark.parametrize("grid", [False, True])
+@pytest.mark.parametrize("steps,mean_tol,max_tol", [(0, 1e-3, 5e-3), (256, MEAN_TOL, MAX_TOL)])
+def test_grid_medium_spot_light_query_vs_reference(bre, steps, mean_tol, max_tol, grid):
+    """Reference-generated query fixture for a GridDensityMedium lit by a SpotLight (oracle/ref_harness.cpp gridspot):
+    hit lists bit-exact; radiance through K6's stepped optical-depth table -- second order in the step; this
+    white-noise grid is its worst case -- within 1e-3 mean / 5e-3 max at the automatic step count (64) and within the
+    north_star tolerance 1e-4 mean / 1e-3 max at bre_config.tau_steps = 256."""
+    g = gold("ref_gridspot.npz")
+    m = g["medium"]
+    nx, ny, nz = [int(x) for x in g["grid_dims"]]
+    ctx = bre.Bre(device=0, tau_steps=steps)
+    try:
+        ctx.set_medium_grid(m[0:3], m[3:6], float(m[6]), g["grid_density"].reshape(nz, ny, nx), g["w2m"].reshape(4, 4))
+        ctx.upload_photons(g["photon_p"].reshape(-1, 3), g["photon_alpha"].reshape(-1, 3),
+                           g["photon_wi"].reshape(-1, 3), radius=float(g["radius"][0]))
+        ctx.build()
+        if grid:
+            ctx.set_ray_grid(int(g["res"][0]), int(g["res"][1]))
+        ro, rd = g["ray_o_tmax"].reshape(-1, 4), g["ray_d"].reshape(-1, 3)
+        rgb, offs, idx = ctx.query(ro, rd, float(g["n_paths"][0]), want_hits=True)
+        assert np.array_equal(offs, g["hit_offsets"])
+        assert np.array_equal(idx, g["hit_indices"])
+        ref = g["radiance"].reshape(-1, 3).astype(np.float64)
+        err = np.abs(rgb - ref)
+        assert err.mean() <= mean_tol * np.abs(ref).mean(), err.mean() / np.abs(ref).mean()
+        assert err.max() <= max_tol * np.abs(ref).max(), err.max() / np.abs(ref).max()
+    finally:
+        ctx.close()

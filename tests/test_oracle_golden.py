@@ -336,3 +336,72 @@ def test_beam_estimate_on_reference_photon_dump(oracle):
         err = np.abs(rgb.astype(np.float64) - ref_rgb)
         assert err.max() <= 1e-5 * np.abs(ref_rgb).max()
         assert err.mean() <= 1e-6 * np.abs(ref_rgb).mean()
+
+
+# ------------------------------------------------------------------ larger reference fixtures (round 2)
+def splitmix64(i):
+    z = i.astype(np.uint64) + np.uint64(0x9e3779b97f4a7c15)
+    z = (z ^ (z >> np.uint64(30))) * np.uint64(0xbf58476d1ce4e5b9)
+    z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94d049bb133111eb)
+    return z ^ (z >> np.uint64(31))
+
+
+def hit_digests(offs, idx):
+    """Per-ray order-independent digest of a hit list: sum of splitmix64(photon index) mod 2^64 (oracle/ref_harness.cpp hit_hash)."""
+    with np.errstate(over="ignore"):
+        csum = np.concatenate([[np.uint64(0)], np.cumsum(splitmix64(idx), dtype=np.uint64)])
+        return csum[offs[1:].astype(np.int64)] - csum[offs[:-1].astype(np.int64)]
+
+
+def test_beam_estimate_on_reference_photon_dump_configs0_size(oracle):
+    """BASELINE.json configs[0] size: 100 000 photons of the reference's ShootPhotons on the fog box, 256 x 256 rays of the
+    reference camera, brute-force estimate by reference classes (hit counts + set digests + radiance).  Oracle LBVH
+    query: counts and digests bit-exact, radiance within 1e-5 max / 1e-6 mean."""
+    g = gold("ref_fogbox_100k.npz")
+    m = g["medium"]
+    assert g["photon_p"].size == 300000 and g["ray_d"].size == 3 * 256 * 256
+    oracle.set_medium_homogeneous(m[0:3], m[3:6], float(m[6]))
+    oracle.set_photons(g["photon_p"], g["photon_alpha"], g["photon_wi"], float(g["radius"][0]))
+    oracle.build()
+    ro, rd = g["ray_o_tmax"].reshape(-1, 4), g["ray_d"].reshape(-1, 3)
+    rgb, offs, idx, cnt = oracle.query(ro, rd, float(g["n_paths"][0]), want_hits=True)
+    assert cnt["hits"] == int(g["hit_counts"].astype(np.int64).sum())
+    assert np.array_equal(np.diff(offs.astype(np.int64)), g["hit_counts"].astype(np.int64))
+    assert np.array_equal(hit_digests(offs, idx), g["hit_digest"])
+    ref_rgb = g["radiance"].reshape(-1, 3)
+    err = np.abs(rgb.astype(np.float64) - ref_rgb)
+    assert err.max() <= 1e-5 * np.abs(ref_rgb).max()
+    assert err.mean() <= 1e-6 * np.abs(ref_rgb).mean()
+
+
+def test_beam_estimate_grid_medium_spot_light_vs_reference(oracle):
+    """Query fixture for a heterogeneous medium lit by a spot light (oracle/ref_harness.cpp gridspot): photons walked by
+    reference classes through a GridDensityMedium, reference camera rays, brute force with the transmittance
+    exp(-sigma_t * fine integral of the reference's Density()) -- what the reference's ratio-tracking Tr estimates.
+    Oracle: hit lists bit-exact at every step count.  Radiance goes through the stepped optical-depth table, a
+    discretisation whose error falls as 1 / steps^2: this 12 x 10 x 8 grid of white noise (neighbouring voxels differ
+    by O(1), sigma_t = 1.65) is its worst case -- at the automatic step count (64) the bound is 1e-3 mean / 5e-3 max,
+    at 256 steps (bre_config.tau_steps) the radiance tolerance of north_star, 1e-4 mean / 1e-3 max, holds."""
+    g = gold("ref_gridspot.npz")
+    m = g["medium"]
+    nx, ny, nz = [int(x) for x in g["grid_dims"]]
+    ro, rd = g["ray_o_tmax"].reshape(-1, 4), g["ray_d"].reshape(-1, 3)
+    ref_rgb = g["radiance"].reshape(-1, 3)
+    assert len(g["hit_indices"]) > 50000
+    errs = {}
+    for steps, mean_tol, max_tol in ((0, 1e-3, 5e-3), (128, 2.5e-4, 1e-3), (256, 1e-4, 1e-3)):
+        oracle.set_medium_grid(m[0:3], m[3:6], float(m[6]), g["grid_density"].reshape(nz, ny, nx), g["w2m"].reshape(4, 4))
+        if steps:
+            oracle.set_tau_steps(steps)
+        else:
+            assert oracle.medium.tau_steps == 64
+        oracle.set_photons(g["photon_p"], g["photon_alpha"], g["photon_wi"], float(g["radius"][0]))
+        oracle.build()
+        rgb, offs, idx, _ = oracle.query(ro, rd, float(g["n_paths"][0]), want_hits=True)
+        assert np.array_equal(offs, g["hit_offsets"])
+        assert np.array_equal(idx, g["hit_indices"])
+        err = np.abs(rgb.astype(np.float64) - ref_rgb)
+        errs[steps] = err.mean() / np.abs(ref_rgb).mean()
+        assert errs[steps] <= mean_tol, (steps, errs[steps])
+        assert err.max() <= max_tol * np.abs(ref_rgb).max(), (steps, err.max() / np.abs(ref_rgb).max())
+    assert errs[128] < errs[0] / 3 and errs[256] < errs[128] / 3        # second order in the step
