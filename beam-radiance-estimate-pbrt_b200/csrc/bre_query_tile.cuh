@@ -527,7 +527,7 @@ __global__ void __launch_bounds__(TT_THREADS) k_tile_walk(
 // instead of three L2 sectors per hit), and adds its radiance with ONE vector atomic (RED.128).
 constexpr int TE_SUB = 2;                 // stage-1 sub-passes per stage 2
 constexpr int TE_N = 32 * TE_SUB;
-struct __align__(16) TileEnt {      // stage-1 results (entry = sub-pass * 32 + lane)
+struct __align__(16) TileEnt {      // stage-1 results, one entry per photon that has candidate pixels
     float4 p[TE_N];        // photon {pos, radius}
     float4 pw[TE_N];       // power
     float4 dr[TE_N];       // direction
@@ -537,6 +537,7 @@ struct __align__(16) TileEnt {      // stage-1 results (entry = sub-pass * 32 + 
     uint32_t rb[TE_N];     // ray index of the tile's pixel (0, 0)
     uint32_t tl[TE_N];     // tile index
     uint32_t rect[TE_N];   // i0 | j0 << 8 | w << 16 | h << 24
+    uint32_t cs[TE_N];     // first candidate of the entry (entries are compacted: only photons with candidates, ascending cs)
 };
 struct __align__(16) TileHits {
     uint32_t e[64], q[64];   // e = entry | pixel-in-tile << 8
@@ -625,7 +626,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
 #pragma unroll 1
         for (unsigned g0 = 0; g0 < LP_RUN / G; g0 += TE_SUB) {
             // ---- stage 1: TE_SUB x one photon per lane against its tile's pixel grid
-            unsigned cstart[TE_SUB], totalC = 0;
+            unsigned totalC = 0, nEnt = 0;
 #pragma unroll
             for (int u = 0; u < TE_SUB; ++u) {
                 const unsigned idx = (g0 + u) * G + sub;
@@ -635,7 +636,10 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                 const uint32_t firstP = qy & 0x07ffffffu;
                 const uint32_t cntP = ((qy >> 27) & 15u) + 1u;
                 const bool on = qx != PAIR_NONE && (qx & 0xc0000000u) == PAIR_TILE && j < cntP;
-                unsigned count = 0;
+                unsigned count = 0, ent_rect = 0;
+                float4 ent_p = make_float4(0.f, 0.f, 0.f, 0.f), ent_c = ent_p;
+                float ent_q12 = 0.f;
+                const float4 *ent_fr = tframes;
                 if (on) {
                     const float4 p = __ldg(A.t.s_pos_r + firstP + j);
                     const float4 *fr = tframes + (size_t)(qx & TILE_MASK) * TFRAME_V4;
@@ -674,8 +678,28 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                     }
                     if (i1 >= i0 && j1 >= j0) {
                         const unsigned w = (unsigned)(i1 - i0 + 1), h = (unsigned)(j1 - j0 + 1);
-                        const unsigned e = (unsigned)u * 32u + lane;
                         count = w * h;
+                    }
+                    if (COUNT) ++cTests;
+                    ent_p = p; ent_c = make_float4(ci, cj, q11, q22); ent_q12 = q12;
+                    ent_rect = (unsigned)i0 | ((unsigned)j0 << 8) | ((unsigned)(i1 - i0 + 1) << 16) | ((unsigned)(j1 - j0 + 1) << 24);
+                    ent_fr = fr;
+                }
+                // exclusive prefix of the candidate counts, continued over the sub-passes; entries are compacted
+                unsigned incl = count;
+#pragma unroll
+                for (int o2 = 1; o2 < 32; o2 <<= 1) {
+                    const unsigned v = __shfl_up_sync(FULL, incl, o2);
+                    if ((int)lane >= o2) incl += v;
+                }
+                const unsigned nz = __ballot_sync(FULL, count != 0u);
+                if (count) {
+                    const unsigned e = nEnt + __popc(nz & lt);
+                    {
+                        const float4 p = ent_p;
+                        const float4 *fr = ent_fr;
+                        const float ci = ent_c.x, cj = ent_c.y, q11 = ent_c.z, q22 = ent_c.w, q12 = ent_q12;
+                        te.cs[e] = totalC + incl - count;
                         te.p[e] = p;
                         if (MODE == 0) { te.pw[e] = __ldg(A.t.s_pow + firstP + j); te.dr[e] = __ldg(A.t.s_dir + firstP + j); }
                         te.c[e] = make_float4(ci, cj, q11, q22);
@@ -683,58 +707,37 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                         te.s[e] = firstP + j;
                         te.rb[e] = __float_as_uint(__ldg(&fr[7].x));
                         te.tl[e] = qx & TILE_MASK;
-                        te.rect[e] = (unsigned)i0 | ((unsigned)j0 << 8) | (w << 16) | (h << 24);
+                        te.rect[e] = ent_rect;
                     }
-                    if (COUNT) ++cTests;
                 }
-                // exclusive prefix of the candidate counts, continued over the sub-passes
-                unsigned incl = count;
-#pragma unroll
-                for (int o2 = 1; o2 < 32; o2 <<= 1) {
-                    const unsigned v = __shfl_up_sync(FULL, incl, o2);
-                    if ((int)lane >= o2) incl += v;
-                }
-                cstart[u] = totalC + incl - count;
+                nEnt += __popc(nz);
                 totalC += __shfl_sync(FULL, incl, 31);
             }
             if (totalC == 0u) continue;
             __syncwarp();
             // ---- stage 2: one candidate (photon, pixel) per lane
+            const unsigned cs0 = lane < nEnt ? te.cs[lane] : 0u, cs1 = lane + 32u < nEnt ? te.cs[lane + 32u] : 0u;
+            unsigned nBefore = 0;
             for (unsigned cb = 0; cb < totalC; cb += 32) {
                 const unsigned c = cb + lane;
                 bool hit = false;
                 float th = 0.f, d2 = 0.f, ct = 0.f;
                 uint32_t e = 0, q = 0, pp = 0;
-                // entry with cstart <= c < cstart + count: which sub-pass, then binary search over its lanes
-                unsigned usel = 0;
-#pragma unroll
-                for (int u = 1; u < TE_SUB; ++u)
-                    if (c >= __shfl_sync(FULL, cstart[u], 0)) usel = (unsigned)u;
-                unsigned mine = cstart[0];
-                unsigned lo = 0, hi = 31;
-#pragma unroll
-                for (int it = 0; it < 5; ++it) {
-                    const unsigned mid = (lo + hi + 1) >> 1;
-                    unsigned v = __shfl_sync(FULL, cstart[0], mid);
-#pragma unroll
-                    for (int u = 1; u < TE_SUB; ++u) {
-                        const unsigned vu = __shfl_sync(FULL, cstart[u], mid);
-                        if (usel == (unsigned)u) v = vu;
-                    }
-                    if (v <= c) lo = mid; else hi = mid - 1;
-                }
+                // entry with cs <= c < cs + count.  Every entry has candidates, so the cs are distinct: the entries that START
+                // inside this window of 32 candidates set one bit each (a warp OR-reduction), and candidate lane c
+                // belongs to entry (entries started before the window) - 1 + (heads at or below lane c)
+                unsigned h = 0;
                 {
-                    unsigned v = __shfl_sync(FULL, cstart[0], lo);
-#pragma unroll
-                    for (int u = 1; u < TE_SUB; ++u) {
-                        const unsigned vu = __shfl_sync(FULL, cstart[u], lo);
-                        if (usel == (unsigned)u) v = vu;
-                    }
-                    mine = v;
+                    const unsigned d0 = cs0 - cb, d1 = cs1 - cb;
+                    if (lane < nEnt && d0 < 32u) h = 1u << d0;
+                    if (lane + 32u < nEnt && d1 < 32u) h |= 1u << d1;
                 }
+                const unsigned heads = __reduce_or_sync(FULL, h);
+                const unsigned eSel = nBefore - 1u + __popc(heads & (lt | (1u << lane)));
+                nBefore += __popc(heads);
                 if (c < totalC) {
-                    e = usel * 32u + lo;
-                    const unsigned k = c - mine;
+                    e = eSel;
+                    const unsigned k = c - te.cs[e];
                     const unsigned rect = te.rect[e];
                     const unsigned w = (rect >> 16) & 255u;
                     const unsigned jj = (k * ((65536u + w - 1u) / w)) >> 16;   // k / w for k < 256, w <= 16
