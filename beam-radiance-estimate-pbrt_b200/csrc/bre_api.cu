@@ -141,6 +141,8 @@ int bre_create(bre_ctx **out, const bre_config *cfg) {
         ctx->sort_onesweep = !(so && atoi(so) == 0);
         const char *ga = getenv("BRE_GATHER_AOS");
         ctx->gather_aos = !(ga && atoi(ga) == 0);
+        const char *lp = getenv("BRE_LAZY_PAYLOAD");
+        ctx->lazy_payload = !(lp && atoi(lp) == 0);
         const char *tn = getenv("BRE_TRACE_NESTED");
         ctx->trace_nested = tn && atoi(tn) != 0;
         const char *tp = getenv("BRE_TILE");

@@ -508,6 +508,33 @@ __global__ void __launch_bounds__(256) k_gather_aos(const float4 *__restrict__ a
     if ((threadIdx.x & 31) == 0 && amax > 0.f) atomicMax(bnd + 6, __float_as_uint(amax));
 }
 
+// Lazy payload (default): only the 16-byte position records move into Morton order; power / direction stay in the
+// store and are read through `order` where a (tile, photon) entry is staged (bre_query_tile.cuh).
+__global__ void __launch_bounds__(256) k_gather_pos(const float4 *__restrict__ pos_r, const uint32_t *__restrict__ order,
+                                                    uint32_t n, float4 *__restrict__ s_pos_r, uint32_t *__restrict__ bnd) {
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    float amax = 0.f;
+    if (s < n) {
+        const float4 p = __ldg(pos_r + __ldg(order + s));
+        s_pos_r[s] = p;
+        float4 lo, hi;
+        leaf_box(p, lo, hi);
+        amax = box_abs_max(lo, hi);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    if ((threadIdx.x & 31) == 0 && amax > 0.f) atomicMax(bnd + 6, __float_as_uint(amax));
+}
+__global__ void __launch_bounds__(256) k_gather_payload(const float4 *__restrict__ pw, const float4 *__restrict__ dr,
+                                                        const uint32_t *__restrict__ order, uint32_t n,
+                                                        float4 *__restrict__ s_pow, float4 *__restrict__ s_dir) {
+    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    const uint32_t i = __ldg(order + s);
+    s_pow[s] = __ldg(pw + i);
+    s_dir[s] = __ldg(dr + i);
+}
+
 __global__ void __launch_bounds__(256) k_leafboxes(const float4 *__restrict__ s_pos_r, uint32_t n,
                                                    float4 *__restrict__ leaf_lo,
                                                    float4 *__restrict__ leaf_hi) {
@@ -932,6 +959,20 @@ static int launch_refit_emit(bre_ctx *ctx) {
 
 // Canonical 1-photon-per-leaf boxes (leaf boxes + every internal node), materialised on demand for
 // the counting kernel, bre_download_tree and parity tests; not part of the render path.
+int ensure_sorted_payload(bre_ctx *ctx) {
+    if (ctx->payload_sorted || !ctx->built || ctx->n_built == 0) return BRE_OK;
+    const uint32_t n = ctx->n_built;
+    int s;
+    if ((s = ensure(ctx, ctx->s_pow, (size_t)n * 16)) != BRE_OK) return s;
+    if ((s = ensure(ctx, ctx->s_dir, (size_t)n * 16)) != BRE_OK) return s;
+    k_gather_payload<<<(n + 255) / 256, 256, 0, ctx->stream>>>((const float4 *)ctx->pow.p, (const float4 *)ctx->dir.p,
+                                                              (const uint32_t *)ctx->order.p, n, (float4 *)ctx->s_pow.p,
+                                                              (float4 *)ctx->s_dir.p);
+    BRE_CUDA(cudaGetLastError());
+    ctx->payload_sorted = true;
+    return BRE_OK;
+}
+
 int ensure_canonical(bre_ctx *ctx) {
     if (ctx->canon_valid || !ctx->built || ctx->n_built == 0) return BRE_OK;
     const uint32_t n = ctx->n_built;
@@ -995,7 +1036,9 @@ int build_tree(bre_ctx *ctx) {
     const size_t n4 = (size_t)n * sizeof(float4);
     int s;
 #define ENS(buf, bytes) if ((s = ensure(ctx, ctx->buf, (bytes))) != BRE_OK) return s
-    ENS(s_pos_r, n4); ENS(s_pow, n4); ENS(s_dir, n4);
+    ENS(s_pos_r, n4);
+    if (!ctx->lazy_payload) { ENS(s_pow, n4); ENS(s_dir, n4); }
+    ctx->payload_sorted = false;
     ENS(order, (size_t)n * 4); ENS(codes, (size_t)n * 4);
     ENS(keys_alt, (size_t)n * 4); ENS(vals_alt, (size_t)n * 4);
     ENS(node_lo, n4); ENS(node_hi, n4);
@@ -1049,7 +1092,9 @@ int build_tree(bre_ctx *ctx) {
         t = vin; vin = vout; vout = t;
     }
     // after 4 passes kin == codes, vin == order
-    if (ctx->gather_aos) {
+    if (ctx->lazy_payload) {
+        k_gather_pos<<<g256, 256, 0, st>>>(pos_r, order, n, (float4 *)ctx->s_pos_r.p, bnd);
+    } else if (ctx->gather_aos) {
         if ((s = ensure(ctx, ctx->aos, (size_t)n * 48)) != BRE_OK) { delete pt; return s; }
         k_interleave<<<g256, 256, 0, st>>>(pos_r, (const float4 *)ctx->pow.p, (const float4 *)ctx->dir.p, n,
                                            (float4 *)ctx->aos.p);
@@ -1074,6 +1119,7 @@ int build_tree(bre_ctx *ctx) {
     memcpy(&ctx->abs_max, &amaxBits, 4);
     ctx->root_ref = (n <= (uint32_t)ctx->max_leaf) ? leaf_ref(0u, n) : 0;
     ctx->built = true;
+    ctx->payload_sorted = !ctx->lazy_payload;
     ctx->canon_valid = false;
     ctx->topo_valid = true;
     ctx->last_build_kind = 1;
@@ -1084,8 +1130,10 @@ TreeDev tree_view(const bre_ctx *ctx) {
     TreeDev t;
     t.n = ctx->n_built;
     t.s_pos_r = (const float4 *)ctx->s_pos_r.p;
-    t.s_pow = (const float4 *)ctx->s_pow.p;
-    t.s_dir = (const float4 *)ctx->s_dir.p;
+    t.s_pow = ctx->payload_sorted ? (const float4 *)ctx->s_pow.p : nullptr;
+    t.s_dir = ctx->payload_sorted ? (const float4 *)ctx->s_dir.p : nullptr;
+    t.pow_u = (const float4 *)ctx->pow.p;
+    t.dir_u = (const float4 *)ctx->dir.p;
     t.order = (const uint32_t *)ctx->order.p;
     t.node_lo = (const float4 *)ctx->node_lo.p;
     t.node_hi = (const float4 *)ctx->node_hi.p;

@@ -106,7 +106,8 @@ constexpr int TOP_CUT = 512;
 
 struct TreeDev {
     uint32_t n;               // photons
-    const float4 *s_pos_r, *s_pow, *s_dir;
+    const float4 *s_pos_r, *s_pow, *s_dir;   // s_pow / s_dir == nullptr: payload not gathered (lazy), read it through order
+    const float4 *pow_u, *dir_u;             // the photon store's power / direction arrays (store order)
     const uint32_t *order;
     const float4 *node_lo, *node_hi;   // .w = child refs as int bits
     const float4 *leaf_lo, *leaf_hi;
@@ -114,6 +115,14 @@ struct TreeDev {
     int root_ref;             // fast-path root: internal 0, or a leaf ref when n <= max leaf
     float abs_max;            // max |coordinate| of any leaf box
 };
+
+// Power / direction of the photon at sorted position s.  The image-tile path stages them once per (tile, photon)
+// and reads them through the Morton permutation straight from the store (bre_build then moves only the 16-byte
+// position records); the per-ray paths gather them first (ensure_sorted_payload).
+__device__ __forceinline__ void photon_payload(const TreeDev &t, uint32_t s, float4 &pw, float4 &dr) {
+    if (t.s_pow) { pw = __ldg(t.s_pow + s); dr = __ldg(t.s_dir + s); }
+    else { const uint32_t i = __ldg(t.order + s); pw = __ldg(t.pow_u + i); dr = __ldg(t.dir_u + i); }
+}
 
 // ------------------------------------------------------------------ context
 struct Buf {
@@ -148,6 +157,8 @@ struct bre_ctx {
     bool compact_tiled = true;              // BRE_COMPACT_TILED=0: one-thread-per-path k_compact (A/B)
     bool sort_onesweep = true;              // BRE_SORT_ONESWEEP=0: the three-kernel radix passes (A/B)
     bre::Buf os_scratch;
+    bool lazy_payload = true;               // BRE_LAZY_PAYLOAD=0: bre_build also gathers power / direction into Morton order
+    bool payload_sorted = false;            // s_pow / s_dir hold the Morton-ordered payload of the current build
     bool gather_aos = true;                 // BRE_GATHER_AOS=0: gather straight from the three store arrays
     bool trace_nested = false;              // BRE_TRACE_NESTED=1: the nested-loop K1 (A/B experiments)
     bre_camera camera{};
@@ -250,6 +261,7 @@ int check_cuda(bre_ctx *c, cudaError_t e, const char *what);
 // build.cu
 int build_tree(bre_ctx *ctx);
 int ensure_canonical(bre_ctx *ctx);
+int ensure_sorted_payload(bre_ctx *ctx);   // per-ray query paths: gather power / direction into Morton order once per build
 // query.cu
 int run_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, float nPathsNorm,
               float4 *out);

@@ -306,6 +306,8 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
     if (n >= (1u << 30)) return set_err(ctx, BRE_ERR_UNSUPPORTED, "more than 2^30 rays in one query");
     // ---- image-tile path: the caller declared the rays to be a grid_w x grid_h image (bre_set_ray_grid / K0)
     const bool tileMode = tile_mode(ctx, n);
+    // the per-ray paths read a hit's power / direction per HIT: they want them in Morton order (once per build)
+    if (MODE == 0 && !tileMode && (s = ensure_sorted_payload(ctx)) != BRE_OK) return s;
     const uint32_t imgW = tileMode ? ctx->grid_w : 0, imgH = tileMode ? ctx->grid_h : 0;
     const uint32_t tilesX = tileMode ? (imgW + TILE_W - 1) / TILE_W : 0, tilesY = tileMode ? (imgH + TILE_H - 1) / TILE_H : 0;
     // ---- pair queue capacity: 128 pairs per ray, at least 1M, at most 256M pairs (2 GiB)

@@ -87,6 +87,13 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned phase) {
         : "memory");
 }
 
+// 16-byte asynchronous copy global -> shared (SASS: LDGSTS), bypassing L1
+__device__ __forceinline__ void cp_async16(void *dstSmem, const void *srcGlobal) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(dstSmem)), "l"(srcGlobal)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 // max over the box of N.X >= c   (N.xyz, c in pl); all six frustum planes have this form
 __device__ __forceinline__ bool plane_in(const float4 pl, float lox, float loy, float loz, float hix, float hiy,
                                          float hiz) {
@@ -596,6 +603,8 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
 
     // shade `cnt` buffered hits starting at hb[from], one per lane
     auto shade = [&](unsigned from, unsigned cnt) {
+        cp_async_wait_all();
+        __syncwarp();
         if (lane < cnt) {
             const unsigned ep = hb.e[from + lane], q = hb.q[from + lane];
             const unsigned e = ep & 255u;
@@ -701,7 +710,15 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                         const float ci = ent_c.x, cj = ent_c.y, q11 = ent_c.z, q22 = ent_c.w, q12 = ent_q12;
                         te.cs[e] = totalC + incl - count;
                         te.p[e] = p;
-                        if (MODE == 0) { te.pw[e] = __ldg(A.t.s_pow + firstP + j); te.dr[e] = __ldg(A.t.s_dir + firstP + j); }
+                        if (MODE == 0) {
+                            // power / direction are not needed before the first hit is shaded: asynchronous copies
+                            // (LDGSTS) hide the latency of the store-order reads behind the candidate passes
+                            const float4 *gpw, *gdr;
+                            if (A.t.s_pow) { gpw = A.t.s_pow + firstP + j; gdr = A.t.s_dir + firstP + j; }
+                            else { const uint32_t oi = __ldg(A.t.order + firstP + j); gpw = A.t.pow_u + oi; gdr = A.t.dir_u + oi; }
+                            cp_async16(&te.pw[e], gpw);
+                            cp_async16(&te.dr[e], gdr);
+                        }
                         te.c[e] = make_float4(ci, cj, q11, q22);
                         te.q12[e] = q12;
                         te.s[e] = firstP + j;

@@ -295,8 +295,8 @@ __device__ __forceinline__ float optical_depth(const LeafArgs &A, uint32_t q, fl
 // (relative error ~1e-6, tolerance is 1e-4 mean / 1e-3 max).
 __device__ __forceinline__ float3 hit_radiance(const LeafArgs &A, uint32_t s, uint32_t q, float th, float d2) {
     const float radius = __ldg(&A.t.s_pos_r[s].w);
-    const float4 w = __ldg(A.t.s_dir + s);
-    const float4 pw = __ldg(A.t.s_pow + s);
+    float4 w, pw;
+    photon_payload(A.t, s, pw, w);
     const float4 d = __ldg(A.rd + q);
     const float r2 = radius * radius;
     const float invr2 = __fdividef(1.f, r2);
