@@ -115,8 +115,11 @@ int bre_create(bre_ctx **out, const bre_config *cfg) {
         delete ctx;
         return BRE_ERR_INVALID;
     }
+    int prLeast = 0, prGreatest = 0;
+    // the context stream outranks the staging stream (bre_stage_*: K0 / K6 fill the slots its kernels leave free)
     if (cudaSetDevice(ctx->device) != cudaSuccess ||
-        cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        cudaDeviceGetStreamPriorityRange(&prLeast, &prGreatest) != cudaSuccess ||
+        cudaStreamCreateWithPriority(&ctx->stream, cudaStreamNonBlocking, prGreatest) != cudaSuccess) {
         delete ctx;
         return BRE_ERR_CUDA;
     }
@@ -141,6 +144,8 @@ int bre_create(bre_ctx **out, const bre_config *cfg) {
         ctx->sort_onesweep = !(so && atoi(so) == 0);
         const char *ga = getenv("BRE_GATHER_AOS");
         ctx->gather_aos = !(ga && atoi(ga) == 0);
+        const char *td = getenv("BRE_TAU_DEFER");
+        ctx->tau_defer = !(td && atoi(td) == 0);
         const char *lp = getenv("BRE_LAZY_PAYLOAD");
         ctx->lazy_payload = !(lp && atoi(lp) == 0);
         const char *tn = getenv("BRE_TRACE_NESTED");
@@ -549,13 +554,17 @@ int bre_query_to_film(bre_ctx *ctx, uint32_t n, const float *o4, const float *d3
 // buffers may still be read by the previous camera pass)
 static int staging_begin(bre_ctx *ctx) {
     if (!ctx->copy_stream) {
-        BRE_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        int prLeast = 0, prGreatest = 0;
+        BRE_CUDA(cudaDeviceGetStreamPriorityRange(&prLeast, &prGreatest));
+        // lowest priority: its kernels take the SM slots the context stream's kernels leave free
+        BRE_CUDA(cudaStreamCreateWithPriority(&ctx->copy_stream, cudaStreamNonBlocking, prLeast));
         BRE_CUDA(cudaEventCreateWithFlags(&ctx->ev_stage, cudaEventDisableTiming));
         BRE_CUDA(cudaEventCreateWithFlags(&ctx->ev_main, cudaEventDisableTiming));
     }
     BRE_CUDA(cudaEventRecord(ctx->ev_main, ctx->stream));
     BRE_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_main, 0));
     ctx->tau_staged = false;
+    ctx->tau_pending.on = false;
     ctx->cam_staged = false;
     return BRE_OK;
 }
@@ -574,7 +583,7 @@ int bre_stage_rays(bre_ctx *ctx, uint32_t n, const float *o4, const float *d3) {
                                                            (float4 *)ctx->rays_d.p);
     BRE_CUDA(cudaGetLastError());
     // grid media: the optical-depth table of these rays (K6) right behind the upload, under the photon pass
-    if ((s = stage_tau(ctx, n, (const float4 *)ctx->rays_o.p, (const float4 *)ctx->rays_d.p, ctx->copy_stream)) != BRE_OK) return s;
+    if ((s = stage_tau_deferred(ctx, n, (const float4 *)ctx->rays_o.p, (const float4 *)ctx->rays_d.p, false, 0, 0)) != BRE_OK) return s;
     BRE_CUDA(cudaEventRecord(ctx->ev_stage, ctx->copy_stream));
     ctx->staged_rays = n;
     return BRE_OK;
@@ -585,7 +594,7 @@ int bre_stage_rays_d(bre_ctx *ctx, uint32_t n, const void *ro, const void *rd) {
     if (n == 0 || !ro || !rd) return set_err(ctx, BRE_ERR_INVALID, "bad ray arrays");
     int s;
     if ((s = staging_begin(ctx)) != BRE_OK) return s;
-    if ((s = stage_tau(ctx, n, (const float4 *)ro, (const float4 *)rd, ctx->copy_stream)) != BRE_OK) return s;
+    if ((s = stage_tau_deferred(ctx, n, (const float4 *)ro, (const float4 *)rd, false, 0, 0)) != BRE_OK) return s;
     BRE_CUDA(cudaEventRecord(ctx->ev_stage, ctx->copy_stream));
     return BRE_OK;
 }
@@ -599,10 +608,8 @@ int bre_stage_camera(bre_ctx *ctx, float offx, float offy) {
     if ((s = ensure(ctx, ctx->rays_d, (size_t)n * 16)) != BRE_OK) return s;
     if ((s = staging_begin(ctx)) != BRE_OK) return s;
     if ((s = camera_rays(ctx, offx, offy, ctx->copy_stream)) != BRE_OK) return s;
-    const uint32_t gw = ctx->grid_w, gh = ctx->grid_h;
-    ctx->grid_w = (uint32_t)ctx->camera.width; ctx->grid_h = (uint32_t)ctx->camera.height;
-    s = stage_tau(ctx, n, (const float4 *)ctx->rays_o.p, (const float4 *)ctx->rays_d.p, ctx->copy_stream);
-    ctx->grid_w = gw; ctx->grid_h = gh;
+    s = stage_tau_deferred(ctx, n, (const float4 *)ctx->rays_o.p, (const float4 *)ctx->rays_d.p, true,
+                           (uint32_t)ctx->camera.width, (uint32_t)ctx->camera.height);
     if (s != BRE_OK) return s;
     BRE_CUDA(cudaEventRecord(ctx->ev_stage, ctx->copy_stream));
     ctx->cam_staged = true; ctx->cam_offx = offx; ctx->cam_offy = offy;

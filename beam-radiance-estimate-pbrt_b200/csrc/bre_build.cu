@@ -1022,6 +1022,11 @@ static int refit_tree(bre_ctx *ctx) {
 
 int build_tree(bre_ctx *ctx) {
     ctx->built = false;
+    {
+        // K6 of the rays staged by bre_stage_*: ALU-bound, it fills the issue slots the sort / gather kernels leave idle
+        const int sp = launch_pending_tau(ctx);
+        if (sp != BRE_OK) return sp;
+    }
     // only radii changed since the last full build (bre_set_radius): keep order and topology
     if (ctx->topo_valid && ctx->n_built == ctx->n_photons && ctx->n_built > 0) return refit_tree(ctx);
     ctx->topo_valid = false;

@@ -210,6 +210,10 @@ struct bre_ctx {
     struct TauKey { const void *ro, *rd; uint32_t n; int steps; uint32_t gridW; uint64_t mediumVersion; const float *tau; const float2 *span; };
     TauKey tau_key{};
     bool tau_staged = false;
+    // K6 of staged rays is launched when bre_build starts (under the latency-bound sort / gather kernels, on the
+    // low-priority staging stream) instead of under the issue-bound photon tracer: BRE_TAU_DEFER=0 launches it at once
+    bool tau_defer = true;
+    struct TauPending { bool on = false; uint32_t n = 0; const void *ro = nullptr, *rd = nullptr; uint32_t gridW = 0, gridH = 0; bool useGrid = false; } tau_pending;
     uint64_t medium_version = 0;
     bool cam_staged = false;                // K0's rays of (cam_offx, cam_offy) are in rays_o / rays_d (bre_stage_camera)
     float cam_offx = 0, cam_offy = 0;
@@ -267,6 +271,8 @@ int run_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, floa
               float4 *out);
 int run_count(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd);
 int stage_tau(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, cudaStream_t st);
+int stage_tau_deferred(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, bool useGrid, uint32_t gridW, uint32_t gridH);
+int launch_pending_tau(bre_ctx *ctx);      // bre_build / the query entry points: start the deferred K6 now
 int run_hitdump(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, bre_hitdump *hd);
 // film.cu
 int film_accumulate(bre_ctx *ctx, uint32_t n, const uint32_t *pix_d, const float4 *rgb_d);

@@ -652,9 +652,47 @@ int stage_tau(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, cuda
     return s;
 }
 
+// bre_stage_*: remember the rays whose table is wanted; launch_pending_tau starts K6 on the staging stream behind
+// everything queued on the context stream so far (= behind the photon pass when bre_build calls it)
+int stage_tau_deferred(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, bool useGrid, uint32_t gridW,
+                       uint32_t gridH) {
+    ctx->tau_staged = false;
+    ctx->tau_pending.on = false;
+    if (!ctx->have_medium || ctx->medium.kind != 1) return BRE_OK;
+    if (!ctx->tau_defer) {
+        const uint32_t gw = ctx->grid_w, gh = ctx->grid_h;
+        if (useGrid) { ctx->grid_w = gridW; ctx->grid_h = gridH; }
+        const int s = stage_tau(ctx, n, ro, rd, ctx->copy_stream);
+        ctx->grid_w = gw; ctx->grid_h = gh;
+        return s;
+    }
+    ctx->tau_pending.on = true; ctx->tau_pending.n = n; ctx->tau_pending.ro = ro; ctx->tau_pending.rd = rd;
+    ctx->tau_pending.useGrid = useGrid; ctx->tau_pending.gridW = gridW; ctx->tau_pending.gridH = gridH;
+    return BRE_OK;
+}
+int launch_pending_tau(bre_ctx *ctx) {
+    if (!ctx->tau_pending.on) return BRE_OK;
+    const bre_ctx::TauPending p = ctx->tau_pending;
+    ctx->tau_pending.on = false;
+    if (!ctx->copy_stream || !ctx->have_medium || ctx->medium.kind != 1) return BRE_OK;
+    BRE_CUDA(cudaEventRecord(ctx->ev_main, ctx->stream));
+    BRE_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_main, 0));
+    const uint32_t gw = ctx->grid_w, gh = ctx->grid_h;
+    if (p.useGrid) { ctx->grid_w = p.gridW; ctx->grid_h = p.gridH; }
+    const int s = stage_tau(ctx, p.n, (const float4 *)p.ro, (const float4 *)p.rd, ctx->copy_stream);
+    ctx->grid_w = gw; ctx->grid_h = gh;
+    if (s != BRE_OK) return s;
+    BRE_CUDA(cudaEventRecord(ctx->ev_stage, ctx->copy_stream));
+    return BRE_OK;
+}
+
 int run_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, float nPathsNorm,
               float4 *out) {
     if (n == 0) return BRE_OK;
+    {
+        const int sp = launch_pending_tau(ctx);      // staged, but bre_build was not called in between
+        if (sp != BRE_OK) return sp;
+    }
     const float *tau = nullptr; const float2 *span = nullptr;
     int s = BRE_OK;
     const bre_ctx::TauKey &k = ctx->tau_key;

@@ -603,8 +603,6 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
 
     // shade `cnt` buffered hits starting at hb[from], one per lane
     auto shade = [&](unsigned from, unsigned cnt) {
-        cp_async_wait_all();
-        __syncwarp();
         if (lane < cnt) {
             const unsigned ep = hb.e[from + lane], q = hb.q[from + lane];
             const unsigned e = ep & 255u;
@@ -635,6 +633,9 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
 #pragma unroll 1
         for (unsigned g0 = 0; g0 < LP_RUN / G; g0 += TE_SUB) {
             // ---- stage 1: TE_SUB x one photon per lane against its tile's pixel grid
+            // (a pass without hits never waited for its payload copies: they must have landed before the entries
+            // are written again -- two copies in flight to one address may land in either order)
+            if (MODE == 0) cp_async_wait_all();
             unsigned totalC = 0, nEnt = 0;
 #pragma unroll
             for (int u = 0; u < TE_SUB; ++u) {
@@ -735,10 +736,11 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
             // ---- stage 2: one candidate (photon, pixel) per lane
             const unsigned cs0 = lane < nEnt ? te.cs[lane] : 0u, cs1 = lane + 32u < nEnt ? te.cs[lane + 32u] : 0u;
             unsigned nBefore = 0;
+            bool payloadIn = MODE != 0;
             for (unsigned cb = 0; cb < totalC; cb += 32) {
                 const unsigned c = cb + lane;
                 bool hit = false;
-                float th = 0.f, d2 = 0.f, ct = 0.f;
+                float th = 0.f, d2 = 0.f, ct = 0.f, hdx = 0.f, hdy = 0.f, hdz = 0.f;
                 uint32_t e = 0, q = 0, pp = 0;
                 // entry with cs <= c < cs + count.  Every entry has candidates, so the cs are distinct: the entries that START
                 // inside this window of 32 candidates set one bit each (a warp OR-reduction), and candidate lane c
@@ -772,11 +774,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                         r.dx = d.x; r.dy = d.y; r.dz = d.z;
                         hit = disk_test(r, p, th, d2);
                         if (COUNT) ++cTests;
-                        if (MODE == 0 && hit) {
-                            const float4 w = te.dr[e];
-                            ct = -__fmaf_rn(d.z, w.z, __fmaf_rn(d.y, w.y, d.x * w.x));   // Dot(wo = -d, wi)
-                            pp = pj * 16u + pi;
-                        }
+                        if (MODE == 0 && hit) { hdx = d.x; hdy = d.y; hdz = d.z; pp = pj * 16u + pi; }
                     }
                 }
                 if (MODE != 0) {
@@ -785,7 +783,11 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                 }
                 const unsigned mh = __ballot_sync(FULL, hit);
                 if (mh == 0u) continue;
+                // the first hit of the pass needs the photon directions: their asynchronous copies must have landed
+                if (!payloadIn) { cp_async_wait_all(); __syncwarp(); payloadIn = true; }
                 if (hit) {
+                    const float4 w = te.dr[e];
+                    ct = -__fmaf_rn(hdz, w.z, __fmaf_rn(hdy, w.y, hdx * w.x));   // Dot(wo = -d, wi)
                     const unsigned pos = nbuf + __popc(mh & lt);
                     hb.e[pos] = e | (pp << 8); hb.q[pos] = q; hb.th[pos] = th; hb.d2[pos] = d2; hb.ct[pos] = ct;
                 }
