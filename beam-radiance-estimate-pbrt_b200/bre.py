@@ -28,7 +28,7 @@ SYMBOLS = [
     "bre_set_triangle_attrs", "bre_set_lights_in_medium", "bre_set_camera", "bre_camera_rays",
     "bre_query_camera_to_film", "bre_last_build_kind",
     "bre_trace_exchange_photons", "bre_alloc_pinned", "bre_free_pinned", "bre_stage_rays", "bre_query_staged_to_film", "bre_save_photons", "bre_load_photons", "bre_film_save", "bre_film_load",
-    "bre_set_ray_grid", "bre_set_tile_sharding", "bre_set_photon_sharding", "bre_film_gather", "bre_stage_camera", "bre_stage_rays_d",
+    "bre_film_resolve_static", "bre_set_ray_grid", "bre_set_tile_sharding", "bre_set_photon_sharding", "bre_film_gather", "bre_stage_camera", "bre_stage_rays_d",
 ]
 
 
@@ -379,6 +379,12 @@ class Bre:
     def film_resolve(self, it, scale=1.0):
         out = np.zeros((self._npix, 3), np.float32)
         self._ck(self.lib.bre_film_resolve(self.ctx, it, C.c_float(scale), _fp(out)))
+        return out
+
+    def film_resolve_static(self, it, scale=1.0, mean_only=False):
+        """bre_film_resolve / bre_film_mean without any allocation (static device scratch, <= 2^21 pixels)."""
+        out = np.zeros((self._npix, 3), np.float32)
+        self._ck(self.lib.bre_film_resolve_static(self.ctx, it, C.c_float(scale), _fp(out), int(mean_only)))
         return out
 
     def film_gather(self, it, scale=1.0, mean_only=False, want=True):

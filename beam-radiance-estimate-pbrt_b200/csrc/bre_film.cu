@@ -6,6 +6,9 @@
 // with RGBToXYZ / XYZToRGB of core/spectrum.h:56-66.
 #include "bre_internal.cuh"
 
+#include <mutex>
+#include <string>
+
 namespace bre {
 
 __global__ void __launch_bounds__(256) k_film_add(float4 *__restrict__ film, uint32_t n,
@@ -78,3 +81,61 @@ int film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int m
 }
 
 }  // namespace bre
+
+// ---------------------------------------------------------------- K7 without any allocation
+// bre_film_resolve_static: the resolve kernel above with its device staging buffer (the RGB triples before the
+// device -> host copy; bre_film_resolve takes it from a grow-only cudaMalloc) in a file-scope device array.  For
+// callers that must not allocate: CUDA graph capture, serving loops, harnesses that forbid cudaMalloc.  No
+// counterpart in the reference.
+//   * BRE_STATIC_RESOLVE_MAX_PIXELS pixels x 12 bytes = 24 MiB, held by every GPU that loads libbre.so until exit.
+//   * In host code `g_resolve_scratch` is a host-side stand-in, not a device address: the address the kernel gets
+//     comes from cudaGetSymbolAddress, once per device, with that device current.
+//   * Every call on a device shares the array; it keeps the last call's contents.  Nothing has to start at zero
+//     (the kernel writes all 3 n floats before the copy reads them), but two calls that overlap on one GPU (two
+//     contexts / streams / threads) race on it: serialise them.
+static __device__ __align__(256) float g_resolve_scratch[3u * BRE_STATIC_RESOLVE_MAX_PIXELS];
+
+namespace bre {
+constexpr int STATIC_MAX_DEVICES = 64;
+static float *g_resolve_scratch_addr[STATIC_MAX_DEVICES] = {};
+static std::mutex g_resolve_scratch_mu;
+
+// device address of g_resolve_scratch on ctx->device (which is current: CTX_CHECK-style cudaSetDevice by the caller)
+static int resolve_scratch_ptr(bre_ctx *ctx, float **out) {
+    if (ctx->device < 0 || ctx->device >= STATIC_MAX_DEVICES)
+        return set_err(ctx, BRE_ERR_UNSUPPORTED, "bre_film_resolve_static: device ordinal beyond 63");
+    std::lock_guard<std::mutex> lock(g_resolve_scratch_mu);
+    float *&slot = g_resolve_scratch_addr[ctx->device];
+    if (!slot) {
+        float *ptr = nullptr;
+        BRE_CUDA(cudaGetSymbolAddress((void **)&ptr, g_resolve_scratch));
+        if (!ptr) return set_err(ctx, BRE_ERR_CUDA, "cudaGetSymbolAddress(g_resolve_scratch) returned a null address");
+        slot = ptr;
+    }
+    *out = slot;
+    return BRE_OK;
+}
+}  // namespace bre
+
+extern "C" int bre_film_resolve_static(bre_ctx *ctx, int iter, float scale, float *rgb_out, int mean_only) {
+    using namespace bre;
+    if (!ctx) return BRE_ERR_INVALID;
+    BRE_CUDA(cudaSetDevice(ctx->device));
+    if (!rgb_out || iter < 0) return set_err(ctx, BRE_ERR_INVALID, "bad resolve arguments");
+    if (!ctx->film.p) return set_err(ctx, BRE_ERR_INVALID, "bre_film_create has not been called");
+    const uint32_t n = ctx->n_pixels;
+    if (n > BRE_STATIC_RESOLVE_MAX_PIXELS)
+        return set_err(ctx, BRE_ERR_UNSUPPORTED,
+                       "bre_film_resolve_static: film of " + std::to_string(n) + " pixels exceeds the static scratch of " +
+                           std::to_string(BRE_STATIC_RESOLVE_MAX_PIXELS) + " pixels (BRE_STATIC_RESOLVE_MAX_PIXELS); use bre_film_resolve");
+    float *scratch = nullptr;
+    int s = resolve_scratch_ptr(ctx, &scratch);
+    if (s != BRE_OK) return s;
+    const float inv = 1.f / (float)(iter + 1);
+    k_film_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, n, inv, scale, mean_only ? 1 : 0,
+                                                             scratch);
+    BRE_CUDA(cudaGetLastError());
+    BRE_CUDA(cudaMemcpyAsync(rgb_out, scratch, (size_t)n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+    BRE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return BRE_OK;
+}

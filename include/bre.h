@@ -267,6 +267,16 @@ int bre_film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out);
 /* rgb_out: n_pixels*3 floats = L = Ld/(iter+1) (integrators/photonbeam.cpp:578), no colour conversion:
  * the array a pbrt host passes to Film::SetImage (core/film.cpp:132-140) before Film::WriteImage. */
 int bre_film_mean(bre_ctx *ctx, int iter, float *rgb_out);
+/* bre_film_resolve / bre_film_mean (mean_only = 1) for callers that must not allocate -- code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc.  NO counterpart in the reference.
+ * The device staging buffer of the resolved triples is a file-scope static device
+ * array of BRE_STATIC_RESOLVE_MAX_PIXELS pixels (24 MiB, held by every GPU that loads the library until exit); the
+ * call makes no cudaMalloc / cudaFree / allocating library call.  Films with more pixels are rejected with
+ * BRE_ERR_UNSUPPORTED and a message (bre_last_error).  Every call on one GPU shares the array: calls that overlap
+ * on the GPU (other contexts, streams or threads) race -- serialise them.  Results are bit-identical to
+ * bre_film_resolve / bre_film_mean. */
+#define BRE_STATIC_RESOLVE_MAX_PIXELS (1u << 21)   /* 2 097 152 >= 1920 x 1080 */
+int bre_film_resolve_static(bre_ctx *ctx, int iter, float scale, float *rgb_out, int mean_only);
 /* Multi-GPU camera pass.  bre_set_photon_sharding: the partial films of all ranks are summed pixel by pixel (rank
  * order), resolved and written into rank 0's image.  bre_set_tile_sharding: every rank resolves the 16x16 tiles it owns (bre_tile_owner,
  * integrators/photonbeam.cpp:345-347) and writes them straight into rank 0's image over NVLink (CUDA-IPC
