@@ -56,6 +56,7 @@ struct TileArgs {
     const float4 *cut;       // TOP_CUT x 2 float4 (lo|ref, hi|0), padded with ref = FAST_NONE
     uint32_t nCut;           // != 0: cut[2 * TOP_CUT].x holds the number of entries (as bits); 0: start from the root
     float4 *tframes;         // TFRAME_V4 float4 per tile
+    float4 *trays;           // 256 float4 per tile: {d.xyz, tMax} of pixel (i, j) at [j * 16 + i] (tile-blocked copy of the rays)
     unsigned char *tileState;
     uint32_t imgW, imgH, tilesX, tilesY;
 };
@@ -384,7 +385,7 @@ __global__ void __launch_bounds__(TT_THREADS) k_tile_walk(
                 // ---- the tile's rays, 8 per lane: bounds, deviation from the model, coherence
                 const float BIGF = 3.0e38f;
                 float sLo = BIGF, sHi = -BIGF, tLo = BIGF, tHi = -BIGF, dev = 0.f, g2 = 0.f, tFar = 0.f, oSp = 0.f, oAbs = 0.f;
-                float bad = 0.f;
+                float bad = 0.f, oDiff = 0.f;
                 const unsigned ti = lane & (TILE_W - 1);
 #pragma unroll 4
                 for (unsigned k = 0; k < TILE_H / 2; ++k) {
@@ -392,7 +393,12 @@ __global__ void __launch_bounds__(TT_THREADS) k_tile_walk(
                     if (ti < twv && tj < thv) {
                         const unsigned q = q00 + tj * T.imgW + ti;
                         const float4 o = __ldg(A.ro + q), d = __ldg(A.rd + q);
+                        // tile-blocked copy for k_leaf_tile: a candidate reads 16 bytes next to its row neighbours'
+                        // instead of two 32-byte sectors of the image-ordered arrays
+                        __stcg(T.trays + (size_t)tile * 256u + tj * 16u + ti, make_float4(d.x, d.y, d.z, o.w));
                         if (o.w > 0.f) {
+                            if (__float_as_uint(o.x) != __float_as_uint(o0.x) || __float_as_uint(o.y) != __float_as_uint(o0.y) ||
+                                __float_as_uint(o.z) != __float_as_uint(o0.z)) oDiff = 1.f;
                             float myS, myT, myDa;
                             gno(d, myS, myT, myDa);
                             const float ps = s00 + (float)ti * As + (float)tj * Bs, pt = t00 + (float)ti * At + (float)tj * Bt;
@@ -409,7 +415,7 @@ __global__ void __launch_bounds__(TT_THREADS) k_tile_walk(
                 }
                 sLo = warp_min(sLo); sHi = warp_max(sHi); tLo = warp_min(tLo); tHi = warp_max(tHi);
                 dev = warp_max(dev); g2 = warp_max(g2); tFar = warp_max(tFar); oSp = warp_max(oSp);
-                oAbs = warp_max(oAbs); bad = warp_max(bad);
+                oAbs = warp_max(oAbs); bad = warp_max(bad); oDiff = warp_max(oDiff);
                 const bool dead = !(tFar > 0.f) && bad == 0.f;
                 const float M = oAbs + t.abs_max;
                 const float det = As * Bt - Bs * At;
@@ -454,7 +460,8 @@ __global__ void __launch_bounds__(TT_THREADS) k_tile_walk(
                         case 5: fv = make_float4(sqrtf(Mi00 * Mi00 + Mi01 * Mi01), sqrtf(Mi10 * Mi10 + Mi11 * Mi11), oSlack, kphi); break;
                         case 6: fv = make_float4(As * As + At * At, As * Bs + At * Bt, Bs * Bs + Bt * Bt,
                                                  __uint_as_float(twv | (thv << 8))); break;
-                        default: fv = make_float4(__uint_as_float(q00), 0.f, 0.f, 0.f); break;
+                        // .y: every live ray starts at exactly o0 (a pinhole camera): candidates take the origin from the frame
+                        default: fv = make_float4(__uint_as_float(q00), oDiff == 0.f ? 1.f : 0.f, 0.f, 0.f); break;
                     }
                     float4 *fr = T.tframes + (size_t)tile * TFRAME_V4;
                     if (lane < 8) __stcg(fr + lane, fv);
@@ -532,7 +539,10 @@ __global__ void __launch_bounds__(TT_THREADS) k_tile_walk(
 // before the next pass overwrites the entries, so a hit only carries {entry, ray, t, d2} and takes the
 // photon's radius / power / direction from the entry in shared memory (staged ONCE per (tile, photon)
 // instead of three L2 sectors per hit), and adds its radiance with ONE vector atomic (RED.128).
-constexpr int TE_SUB = 2;                 // stage-1 sub-passes per stage 2
+#ifndef BRE_TE_SUB
+#define BRE_TE_SUB 1
+#endif
+constexpr int TE_SUB = BRE_TE_SUB;        // stage-1 sub-passes per stage 2
 constexpr int TE_N = 32 * TE_SUB;
 struct __align__(16) TileEnt {      // stage-1 results, one entry per photon that has candidate pixels
     float4 p[TE_N];        // photon {pos, radius}
@@ -544,6 +554,7 @@ struct __align__(16) TileEnt {      // stage-1 results, one entry per photon tha
     uint32_t rb[TE_N];     // ray index of the tile's pixel (0, 0)
     uint32_t tl[TE_N];     // tile index
     uint32_t rect[TE_N];   // i0 | j0 << 8 | w << 16 | h << 24
+    float4 o[TE_N];        // the tile's ray origin, .w != 0: every ray of the tile starts exactly there
     uint32_t cs[TE_N];     // first candidate of the entry (entries are compacted: only photons with candidates, ascending cs)
 };
 struct __align__(16) TileHits {
@@ -582,7 +593,7 @@ __device__ __forceinline__ float3 hit_radiance_p(const LeafArgs &A, float radius
 
 template <int MODE, bool COUNT, int LW>
 __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs A, const float4 *__restrict__ tframes,
-                                                                    uint32_t imgW,
+                                                                    const float4 *__restrict__ trays, uint32_t imgW,
                                                                     const uint2 *__restrict__ queue,
                                                                     unsigned int queueCap,
                                                                     unsigned int *__restrict__ queueCtl,
@@ -723,7 +734,9 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                         te.c[e] = make_float4(ci, cj, q11, q22);
                         te.q12[e] = q12;
                         te.s[e] = firstP + j;
-                        te.rb[e] = __float_as_uint(__ldg(&fr[7].x));
+                        const float4 f7 = __ldg(fr + 7), f0o = __ldg(fr);
+                        te.rb[e] = __float_as_uint(f7.x);
+                        te.o[e] = make_float4(f0o.x, f0o.y, f0o.z, f7.y);
                         te.tl[e] = qx & TILE_MASK;
                         te.rect[e] = ent_rect;
                     }
@@ -768,9 +781,11 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                     if (!(qf > 1.f)) {
                         q = te.rb[e] + pj * imgW + pi;
                         const float4 p = te.p[e];
-                        const float4 o = __ldg(A.ro + q), d = __ldg(A.rd + q);
+                        const float4 d = __ldg(trays + (size_t)te.tl[e] * 256u + pj * 16u + pi);     // {d.xyz, tMax}
+                        float4 o = te.o[e];
+                        if (o.w == 0.f) o = __ldg(A.ro + q);
                         RayS r;
-                        r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tMax = o.w;
+                        r.ox = o.x; r.oy = o.y; r.oz = o.z; r.tMax = d.w;
                         r.dx = d.x; r.dy = d.y; r.dz = d.z;
                         hit = disk_test(r, p, th, d2);
                         if (COUNT) ++cTests;
