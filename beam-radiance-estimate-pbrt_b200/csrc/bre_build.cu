@@ -358,26 +358,32 @@ __global__ void __launch_bounds__(RS_THREADS, 4) k_os_scatter(
     const uint32_t tbase = tile * RS_TILE + w * (RS_ITEMS * 32);
     uint32_t key[RS_ITEMS], rank[RS_ITEMS];
     const uint32_t lt = (1u << lane) - 1u;
+    // (a) all keys of the lane in flight at once
 #pragma unroll
     for (int k = 0; k < RS_ITEMS; ++k) {
         const uint32_t idx = tbase + k * 32 + lane;
-        const bool valid = idx < n;
-        key[k] = valid ? __ldg(keysIn + idx) : 0xffffffffu;
-        const uint32_t d = (key[k] >> shift) & 255u;
+        key[k] = idx < n ? __ldg(keysIn + idx) : 0xffffffffu;
+    }
+    // (b) the lanes of the warp that hold the same digit, for every item: RS_ITEMS independent MATCH operations
+    //     (rank[k] holds the peer mask until (c))
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) {
+        const bool valid = tbase + k * 32 + lane < n;
         const uint32_t vmask = __ballot_sync(0xffffffffu, valid);
-        rank[k] = 0;
-        if (valid) {
-            const uint32_t peers = __match_any_sync(vmask, d);
-            const int leader = __ffs(peers) - 1;
-            uint32_t old = 0;
-            if ((int)lane == leader) {
-                old = whist[w][d];
-                whist[w][d] = old + __popc(peers);
-            }
-            old = __shfl_sync(peers, old, leader);
-            rank[k] = old + __popc(peers & lt);
-        }
+        rank[k] = valid ? __match_any_sync(vmask, (key[k] >> shift) & 255u) : 0u;
+    }
+    // (c) stable rank inside the warp: the only serial chain left is one shared-memory load and one store per item
+    //     (every peer reads the running count itself; the lowest peer lane adds the group)
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) {
+        const uint32_t peers = rank[k];
+        const uint32_t d = (key[k] >> shift) & 255u;
+        uint32_t old = 0;
+        if (peers) old = whist[w][d];
         __syncwarp();
+        if (peers && (peers & lt) == 0u) whist[w][d] = old + __popc(peers);
+        __syncwarp();
+        rank[k] = old + __popc(peers & lt);
     }
     __syncthreads();
     {
@@ -420,16 +426,25 @@ __global__ void __launch_bounds__(RS_THREADS, 4) k_os_scatter(
         binGlobal[d] = __ldg(base + d) + excl - exclLocal;   // dst = binGlobal[d] + position inside the sorted tile
     }
     __syncthreads();
+    // keys into their sorted place of the tile; then the values with all loads in flight at once (the key
+    // registers are free by then)
 #pragma unroll
     for (int k = 0; k < RS_ITEMS; ++k) {
-        const uint32_t idx = tbase + k * 32 + lane;
-        if (idx < n) {
+        if (tbase + k * 32 + lane < n) {
             const uint32_t d = (key[k] >> shift) & 255u;
             const uint32_t lpos = binLocal[d] + whist[w][d] + rank[k];
             skey[lpos] = key[k];
-            sval[lpos] = iotaVals ? idx : __ldg(valsIn + idx);
+            rank[k] = lpos;
         }
     }
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k) {
+        const uint32_t idx = tbase + k * 32 + lane;
+        key[k] = (iotaVals || idx >= n) ? idx : __ldg(valsIn + idx);
+    }
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; ++k)
+        if (tbase + k * 32 + lane < n) sval[rank[k]] = key[k];
     __syncthreads();
     const uint32_t tile0 = tile * RS_TILE;
     const uint32_t nValid = n - tile0 < (uint32_t)RS_TILE ? n - tile0 : (uint32_t)RS_TILE;
