@@ -527,14 +527,24 @@ __global__ void __launch_bounds__(256) k_gather_aos(const float4 *__restrict__ a
 // store and are read through `order` where a (tile, photon) entry is staged (bre_query_tile.cuh).
 __global__ void __launch_bounds__(256) k_gather_pos(const float4 *__restrict__ pos_r, const uint32_t *__restrict__ order,
                                                     uint32_t n, float4 *__restrict__ s_pos_r, uint32_t *__restrict__ bnd) {
-    uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    // four sorted positions per thread, block-strided: four random 16-byte reads in flight per thread
+    const uint32_t s0 = blockIdx.x * (blockDim.x * 4u) + threadIdx.x;
+    uint32_t src[4];
+    float4 p[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { const uint32_t s = s0 + k * 256u; src[k] = s < n ? __ldg(order + s) : 0u; }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) p[k] = __ldg(pos_r + src[k]);
     float amax = 0.f;
-    if (s < n) {
-        const float4 p = __ldg(pos_r + __ldg(order + s));
-        s_pos_r[s] = p;
-        float4 lo, hi;
-        leaf_box(p, lo, hi);
-        amax = box_abs_max(lo, hi);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const uint32_t s = s0 + k * 256u;
+        if (s < n) {
+            s_pos_r[s] = p[k];
+            float4 lo, hi;
+            leaf_box(p[k], lo, hi);
+            amax = fmaxf(amax, box_abs_max(lo, hi));
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
@@ -1113,7 +1123,7 @@ int build_tree(bre_ctx *ctx) {
     }
     // after 4 passes kin == codes, vin == order
     if (ctx->lazy_payload) {
-        k_gather_pos<<<g256, 256, 0, st>>>(pos_r, order, n, (float4 *)ctx->s_pos_r.p, bnd);
+        k_gather_pos<<<(n + 1023) / 1024, 256, 0, st>>>(pos_r, order, n, (float4 *)ctx->s_pos_r.p, bnd);
     } else if (ctx->gather_aos) {
         if ((s = ensure(ctx, ctx->aos, (size_t)n * 48)) != BRE_OK) { delete pt; return s; }
         k_interleave<<<g256, 256, 0, st>>>(pos_r, (const float4 *)ctx->pow.p, (const float4 *)ctx->dir.p, n,
