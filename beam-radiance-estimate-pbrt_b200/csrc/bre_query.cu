@@ -661,7 +661,12 @@ int stage_tau_deferred(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 
     ctx->tau_staged = false;
     ctx->tau_pending.on = false;
     if (!ctx->have_medium || ctx->medium.kind != 1) return BRE_OK;
-    if (!ctx->tau_defer) {
+    // Deferring pays when K6 fits under the build (its latency-bound kernels leave issue slots free); when K6 is the
+    // longer of the two -- small photon shards on several GPUs, 4K frames -- it starts at once and also runs in the
+    // gaps of the photon pass.  Estimates from measured rates: 3.2e-9 ms per table sample, 1.9e-7 ms per photon of the
+    // last build.
+    const double k6Ms = 3.2e-9 * (double)n * (double)ctx->tau_steps, buildMs = 1.9e-7 * (double)ctx->n_built;
+    if (!ctx->tau_defer || k6Ms > 0.6 * buildMs) {
         const uint32_t gw = ctx->grid_w, gh = ctx->grid_h;
         if (useGrid) { ctx->grid_w = gridW; ctx->grid_h = gridH; }
         const int s = stage_tau(ctx, n, ro, rd, ctx->copy_stream);
