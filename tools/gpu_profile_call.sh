@@ -1,9 +1,10 @@
 # One gpurun call (1 GPU): smoke, bench (both arms), ncu launch list, ncu captures, other workloads.
 # Outputs land in gpurun_out/ (<= 64 MiB in total or nothing comes back: the raw pages are exported to CSV on the box
 # and only the K5 report, which carries the source page, is kept); summaries for the record are copied to profiles/.
-TAG=${1:-r02_v22}
+TAG=${1:-r02_v23}
 mkdir -p gpurun_out
 rm -f gpurun_out/*.ncu-rep
+(timeout 900 python -m pytest tests -m gpu -q > gpurun_out/${TAG}_pytest_gpu.log 2>&1; echo "pytest exit $?" >> gpurun_out/${TAG}_pytest_gpu.log); tail -2 gpurun_out/${TAG}_pytest_gpu.log
 timeout 120 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1
 timeout 400 python bench.py > gpurun_out/${TAG}_bench_smoke10m.json 2> gpurun_out/${TAG}_bench.err
 timeout 400 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/${TAG}_bench_ref.json 2> gpurun_out/${TAG}_bench_ref.err
