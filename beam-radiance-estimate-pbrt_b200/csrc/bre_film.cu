@@ -11,7 +11,7 @@
 
 namespace bre {
 
-__global__ void __launch_bounds__(256) k_film_add(float4 *__restrict__ film, uint32_t n,
+__global__ void __launch_bounds__(256) k_film_add(float4 *__restrict__ film, uint32_t n, uint32_t nPixels,
                                                   const uint32_t *__restrict__ pix,
                                                   const float4 *__restrict__ rgb) {
     uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
@@ -22,18 +22,21 @@ __global__ void __launch_bounds__(256) k_film_add(float4 *__restrict__ film, uin
         f.x = fadd(f.x, v.x); f.y = fadd(f.y, v.y); f.z = fadd(f.z, v.z);
         film[q] = f;
     } else {
-        float *f = reinterpret_cast<float *>(film + __ldg(pix + q));
+        const uint32_t p = __ldg(pix + q);
+        if (p >= nPixels) return;             // a caller's index beyond the film is dropped, never written
+        float *f = reinterpret_cast<float *>(film + p);
         atomicAdd(f + 0, v.x); atomicAdd(f + 1, v.y); atomicAdd(f + 2, v.z);
     }
 }
 
 __global__ void __launch_bounds__(256) k_film_resolve(const float4 *__restrict__ film, uint32_t n,
-                                                      float inv, float scale, int meanOnly,
+                                                      float div, float scale, int meanOnly,
                                                       float *__restrict__ out) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float4 f = __ldg(film + i);
-    float r = fmul(f.x, inv), g = fmul(f.y, inv), b = fmul(f.z, inv);
+    // Ld / (iter + 1): the reference divides every channel (spectrum.h:181-188), no reciprocal
+    float r = fdiv(f.x, div), g = fdiv(f.y, div), b = fdiv(f.z, div);
     if (meanOnly) {   // L = Ld / (iter+1), photonbeam.cpp:578: what the host hands to Film::SetImage
         out[3 * (size_t)i + 0] = r; out[3 * (size_t)i + 1] = g; out[3 * (size_t)i + 2] = b;
         return;
@@ -59,7 +62,7 @@ int film_accumulate(bre_ctx *ctx, uint32_t n, const uint32_t *pix_d, const float
     if (n == 0) return BRE_OK;
     {
         PhaseTimer pt(ctx, PH_FILM);
-        k_film_add<<<(n + 255) / 256, 256, 0, ctx->stream>>>((float4 *)ctx->film.p, n, pix_d, rgb_d);
+        k_film_add<<<(n + 255) / 256, 256, 0, ctx->stream>>>((float4 *)ctx->film.p, n, ctx->n_pixels, pix_d, rgb_d);
     }
     BRE_CUDA(cudaGetLastError());
     return BRE_OK;
@@ -70,8 +73,8 @@ int film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int m
     uint32_t n = ctx->n_pixels;
     int s;
     if ((s = ensure(ctx, ctx->out_rgb, (size_t)n * 12)) != BRE_OK) return s;
-    float inv = 1.f / (float)(iter + 1);
-    k_film_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, n, inv,
+    const float div = (float)(iter + 1);     // the divisor (the kernel divides, like the reference)
+    k_film_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, n, div,
                                                              scale, meanOnly, (float *)ctx->out_rgb.p);
     BRE_CUDA(cudaGetLastError());
     BRE_CUDA(cudaMemcpyAsync(rgb_out_host, ctx->out_rgb.p, (size_t)n * 12, cudaMemcpyDeviceToHost,
@@ -131,8 +134,8 @@ extern "C" int bre_film_resolve_static(bre_ctx *ctx, int iter, float scale, floa
     float *scratch = nullptr;
     int s = resolve_scratch_ptr(ctx, &scratch);
     if (s != BRE_OK) return s;
-    const float inv = 1.f / (float)(iter + 1);
-    k_film_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, n, inv, scale, mean_only ? 1 : 0,
+    const float div = (float)(iter + 1);     // the divisor (the kernel divides, like the reference)
+    k_film_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, n, div, scale, mean_only ? 1 : 0,
                                                              scratch);
     BRE_CUDA(cudaGetLastError());
     BRE_CUDA(cudaMemcpyAsync(rgb_out, scratch, (size_t)n * 12, cudaMemcpyDeviceToHost, ctx->stream));

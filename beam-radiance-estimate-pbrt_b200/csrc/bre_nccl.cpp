@@ -392,7 +392,7 @@ __device__ __forceinline__ float3 film_convert(float r, float g, float b, float 
 }
 // one block per tile of the image, thread = pixel; tiles of other ranks return at once
 __global__ void __launch_bounds__(256) k_film_resolve_tiles(const float4 *__restrict__ film, uint32_t imgW, uint32_t imgH,
-                                                            uint32_t tilesX, float inv, float scale, int meanOnly,
+                                                            uint32_t tilesX, float div, float scale, int meanOnly,
                                                             int nRanks, int rank, float *__restrict__ dst) {
     const uint32_t tile = blockIdx.x;
     if (nRanks > 1 && (int)(tile % (uint32_t)nRanks) != rank) return;
@@ -400,7 +400,7 @@ __global__ void __launch_bounds__(256) k_film_resolve_tiles(const float4 *__rest
     if (x >= imgW || y >= imgH) return;
     const size_t i = (size_t)y * imgW + x;
     const float4 f = __ldg(film + i);
-    const float3 v = film_convert(fmul(f.x, inv), fmul(f.y, inv), fmul(f.z, inv), scale, meanOnly);
+    const float3 v = film_convert(fdiv(f.x, div), fdiv(f.y, div), fdiv(f.z, div), scale, meanOnly);
     dst[3 * i + 0] = v.x; dst[3 * i + 1] = v.y; dst[3 * i + 2] = v.z;
 }
 
@@ -414,7 +414,7 @@ __global__ void __launch_bounds__(256) k_film_resolve_tiles(const float4 *__rest
 // instead of the (R - 1) x 16 of a reduce onto rank 0.  Blocks stage their 256 pixels in shared memory so that the
 // remote stores are full 16-byte vectors.
 struct FilmPeers { const float4 *film[MAX_P2P_RANKS]; };
-__global__ void __launch_bounds__(256) k_film_sum_resolve(FilmPeers P, int nRanks, uint32_t first, uint32_t last, float inv,
+__global__ void __launch_bounds__(256) k_film_sum_resolve(FilmPeers P, int nRanks, uint32_t first, uint32_t last, float div,
                                                          float scale, int meanOnly, float *__restrict__ dst) {
     __shared__ __align__(16) float out[768];
     const uint32_t base = first + blockIdx.x * 256u, i = base + threadIdx.x;   // base is a multiple of 256
@@ -424,7 +424,7 @@ __global__ void __launch_bounds__(256) k_film_sum_resolve(FilmPeers P, int nRank
             const float4 b = P.film[r][i];
             a.x = fadd(a.x, b.x); a.y = fadd(a.y, b.y); a.z = fadd(a.z, b.z);
         }
-        const float3 v = film_convert(fmul(a.x, inv), fmul(a.y, inv), fmul(a.z, inv), scale, meanOnly);
+        const float3 v = film_convert(fdiv(a.x, div), fdiv(a.y, div), fdiv(a.z, div), scale, meanOnly);
         out[3 * threadIdx.x] = v.x; out[3 * threadIdx.x + 1] = v.y; out[3 * threadIdx.x + 2] = v.z;
     }
     __syncthreads();
@@ -437,7 +437,7 @@ __global__ void __launch_bounds__(256) k_film_sum_resolve(FilmPeers P, int nRank
 static int film_gather_sum(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int meanOnly) {
     const uint32_t n = ctx->n_pixels;
     const int R = ctx->n_ranks;
-    const float inv = 1.f / (float)(iter + 1);
+    const float div = (float)(iter + 1);     // the DIVISOR: the kernels divide like the reference (spectrum.h:181-188)
     const size_t imgBytes = (size_t)n * 12, imgStride = (imgBytes + 255) & ~(size_t)255;
     ncclComm_p comm = (ncclComm_p)ctx->nccl_comm;
     int s;
@@ -460,7 +460,7 @@ static int film_gather_sum(bre_ctx *ctx, int iter, float scale, float *rgb_out_h
             float *loc = (float *)((char *)ctx->gather.p + half);
             FilmPeers P{};
             P.film[0] = sum;
-            k_film_sum_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>(P, 1, 0, n, inv, scale, meanOnly, loc);
+            k_film_sum_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>(P, 1, 0, n, div, scale, meanOnly, loc);
             BRE_CUDA(cudaGetLastError());
             if (rgb_out_host) BRE_CUDA(cudaMemcpyAsync(rgb_out_host, loc, imgBytes, cudaMemcpyDeviceToHost, ctx->stream));
         }
@@ -532,7 +532,7 @@ static int film_gather_sum(bre_ctx *ctx, int iter, float scale, float *rgb_out_h
     if (last > first) {
         FilmPeers P{};
         for (int q = 0; q < R; ++q) P.film[q] = (const float4 *)ctx->film_peer[q];
-        k_film_sum_resolve<<<(last - first + 255) / 256, 256, 0, ctx->stream>>>(P, R, first, last, inv, scale, meanOnly, dst);
+        k_film_sum_resolve<<<(last - first + 255) / 256, 256, 0, ctx->stream>>>(P, R, first, last, div, scale, meanOnly, dst);
         BRE_CUDA(cudaGetLastError());
     }
     // ---- every run has landed in rank 0's image, and nobody writes its film again before everyone has read it
@@ -550,7 +550,7 @@ int film_gather(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int me
         return set_err(ctx, BRE_ERR_INVALID, "bre_film_gather needs the image layout (bre_set_ray_grid width * height == film pixels)");
     const uint32_t W = ctx->grid_w, H = ctx->grid_h, tX = (W + 15) / 16, tY = (H + 15) / 16;
     const int R = ctx->n_ranks;
-    const float inv = 1.f / (float)(iter + 1);
+    const float div = (float)(iter + 1);     // the DIVISOR: the kernels divide like the reference (spectrum.h:181-188)
     const size_t imgBytes = (size_t)n * 12;
     int s;
     if ((s = ensure(ctx, ctx->gather, 2 * imgBytes)) != BRE_OK) return s;
@@ -559,7 +559,7 @@ int film_gather(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int me
         return film_gather_sum(ctx, iter, scale, rgb_out_host, meanOnly);
     }
     if (R == 1 || !ctx->tile_shard) {
-        k_film_resolve_tiles<<<tX * tY, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, W, H, tX, inv, scale, meanOnly, 1, 0,
+        k_film_resolve_tiles<<<tX * tY, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, W, H, tX, div, scale, meanOnly, 1, 0,
                                                               (float *)ctx->gather.p);
         BRE_CUDA(cudaGetLastError());
         if (rgb_out_host) BRE_CUDA(cudaMemcpyAsync(rgb_out_host, ctx->gather.p, imgBytes, cudaMemcpyDeviceToHost, ctx->stream));
@@ -577,7 +577,7 @@ int film_gather(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int me
         // NCCL path: every rank resolves its tiles into a zeroed local image, ncclReduce(sum) to rank 0 (disjoint tiles)
         float *loc = (float *)((char *)ctx->gather.p + half);
         BRE_CUDA(cudaMemsetAsync(loc, 0, imgBytes, ctx->stream));
-        k_film_resolve_tiles<<<tX * tY, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, W, H, tX, inv, scale, meanOnly, R,
+        k_film_resolve_tiles<<<tX * tY, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, W, H, tX, div, scale, meanOnly, R,
                                                               ctx->rank, loc);
         BRE_CUDA(cudaGetLastError());
         int r = g.Reduce(loc, loc, (size_t)n * 3, kNcclFloat, 0 /* ncclSum */, 0, comm, ctx->stream);
@@ -614,7 +614,7 @@ int film_gather(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int me
         ctx->gather_exported = ctx->gather.p;
     }
     float *dst = (float *)((char *)ctx->gather_peer0 + half);
-    k_film_resolve_tiles<<<tX * tY, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, W, H, tX, inv, scale, meanOnly, R, ctx->rank,
+    k_film_resolve_tiles<<<tX * tY, 256, 0, ctx->stream>>>((const float4 *)ctx->film.p, W, H, tX, div, scale, meanOnly, R, ctx->rank,
                                                           dst);
     BRE_CUDA(cudaGetLastError());
     // arrival barrier: every rank's tiles have landed in rank 0's buffer

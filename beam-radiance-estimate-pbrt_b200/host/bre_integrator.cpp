@@ -163,7 +163,9 @@ bool BreIntegrator::SetupLights(bre_ctx *ctx, const Scene &scene) const {
 // or no material, no area lights; medium interfaces that are either no transition or a transition
 // between the camera's medium and vacuum.  Anything else returns false (the caller then keeps pbrt's
 // own host code for that stage).
-bool BreIntegrator::SetupSurfaces(bre_ctx *ctx, const Scene &scene, const Medium *medium) const {
+static const size_t kMaxDeviceTriangles = 4096;
+bool BreIntegrator::SetupSurfaces(bre_ctx *ctx, const Scene &scene, const Medium *medium, bool *tooMany) const {
+    *tooMany = false;
     const BVHAccel *bvh = dynamic_cast<const BVHAccel *>(scene.aggregate.get());
     if (!bvh) return false;
     std::vector<float> P, Kd;
@@ -201,6 +203,14 @@ bool BreIntegrator::SetupSurfaces(bre_ctx *ctx, const Scene &scene, const Medium
         attrs.push_back(a);
     }
     if (attrs.empty()) return false;
+    // K0 / K1 test the triangles by brute force (pixels x triangles, paths x triangles): fine for the boxes and blockers
+    // of this path's scenes, a hang for a real mesh.  Beyond the cap the host camera / host tracer of pbrt take over.
+    if (attrs.size() > kMaxDeviceTriangles) {
+        Warning("bre: %d triangles exceed the device paths' brute-force cap (%d): camera rays and photon paths are "
+                "generated by pbrt's host code", (int)attrs.size(), (int)kMaxDeviceTriangles);
+        *tooMany = true;
+        return false;
+    }
     return Check(ctx, bre_set_triangles(ctx, (uint32_t)attrs.size(), P.data(), idx.data(), Kd.data()), "bre_set_triangles") &&
            Check(ctx, bre_set_triangle_attrs(ctx, (uint32_t)attrs.size(), attrs.data()), "bre_set_triangle_attrs");
 }
@@ -329,7 +339,10 @@ void BreIntegrator::Render(const Scene &scene) {
     if (!lightDistr) { Error("bre: the scene has no lights"); bre_destroy(ctx); return; }
     // surfaces on the device: needed by the device photon tracer (else: absorbing world box) and by
     // the device camera rays (else: rays generated by pbrt's camera on the host)
-    const bool haveSurfaces = (deviceTracer || deviceCamera) && SetupSurfaces(ctx, scene, medium);
+    bool tooManyTriangles = false;
+    const bool haveSurfaces = (this->deviceTracer || deviceCamera) && SetupSurfaces(ctx, scene, medium, &tooManyTriangles);
+    // (shadows the member from here on: a mesh beyond the brute-force cap is traced by pbrt's host code)
+    const bool deviceTracer = this->deviceTracer && !tooManyTriangles;
     if (deviceTracer) {
         const Bounds3f wb = scene.WorldBound();
         float lo[3] = {wb.pMin.x, wb.pMin.y, wb.pMin.z}, hi[3] = {wb.pMax.x, wb.pMax.y, wb.pMax.z};

@@ -79,7 +79,7 @@ class BreIntegrator : public Integrator {
   private:
     bool SetupMedium(bre_ctx *ctx, const Medium *medium) const;
     bool SetupLights(bre_ctx *ctx, const Scene &scene) const;
-    bool SetupSurfaces(bre_ctx *ctx, const Scene &scene, const Medium *medium) const;
+    bool SetupSurfaces(bre_ctx *ctx, const Scene &scene, const Medium *medium, bool *tooMany) const;
     bool SetupCamera(bre_ctx *ctx, const Bounds2i &pixelBounds) const;
     uint64_t TracePhotonsHost(bre_ctx *ctx, const Scene &scene, const Distribution1D &lightDistr,
                               uint64_t firstIndex, uint64_t nPaths, Float radius);

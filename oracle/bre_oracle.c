@@ -635,9 +635,10 @@ void orc_film_accumulate(float *ld, uint32_t nRays, const uint32_t *pixel, const
 }
 void orc_film_resolve(const float *ld, uint32_t nPixels, int iter, float scale, float *out) {
     for (uint32_t i = 0; i < nPixels; ++i) {
-        /* L = Ld / (iter+1)  photonbeam.cpp:578 (Spectrum / Float multiplies by the reciprocal) */
-        float inv = 1.f / (float)(iter + 1);
-        float rgb[3] = {ld[3 * (size_t)i] * inv, ld[3 * (size_t)i + 1] * inv, ld[3 * (size_t)i + 2] * inv};
+        /* L = Ld / (iter+1)  photonbeam.cpp:578; CoefficientSpectrum::operator/(Float) divides every channel
+         * (spectrum.h:181-188: ret.c[i] /= a), it does not multiply by a reciprocal */
+        const float div = (float)(iter + 1);
+        float rgb[3] = {ld[3 * (size_t)i] / div, ld[3 * (size_t)i + 1] / div, ld[3 * (size_t)i + 2] / div};
         /* Film::SetImage: RGB -> XYZ, weight 1  film.cpp:132-140, spectrum.h:62-66 */
         float xyz[3];
         xyz[0] = 0.412453f * rgb[0] + 0.357580f * rgb[1] + 0.180423f * rgb[2];

@@ -37,7 +37,9 @@ def pinhole(q):
     d[..., 2] = 1
     d /= np.linalg.norm(d, axis=2, keepdims=True).astype(np.float32)
     d = d.reshape(-1, 3)
-    return clip_to_cube(np.broadcast_to(eye, d.shape).copy(), d)
+    o4, dd = clip_to_cube(np.broadcast_to(eye, d.shape).copy(), d)
+    pinhole.last_wh = (w, h)
+    return o4, dd
 
 
 def incoherent(q, seed=4):
@@ -66,6 +68,7 @@ def main():
     ap.add_argument("--hits", type=float, nargs="+", default=[8, 64])
     ap.add_argument("--rays", type=int, nargs="+", default=[65536, 2073600])
     ap.add_argument("--incoherent", action="store_true")
+    ap.add_argument("--no-grid", action="store_true", help="pinhole rays take the per-ray / packet walk instead of the tile path")
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--leaf", type=int, default=0)
     ap.add_argument("--g", type=float, default=0.3)
@@ -99,6 +102,11 @@ def main():
                 for kind in (["pinhole", "incoherent"] if args.incoherent else ["pinhole"]):
                     ro, rd = pinhole(q) if kind == "pinhole" else incoherent(q)
                     nq = ro.shape[0]
+                    # pinhole rays are a w x h image: the image-tile path of K5 (bre_set_ray_grid) unless --no-grid
+                    if kind == "pinhole" and not args.no_grid:
+                        ctx.set_ray_grid(*pinhole.last_wh)
+                    else:
+                        ctx.set_ray_grid(0, 0)
                     ro_d = torch.from_numpy(ro).cuda()
                     rd4 = np.zeros((nq, 4), np.float32); rd4[:, :3] = rd
                     rd_d = torch.from_numpy(rd4).cuda()
@@ -113,6 +121,7 @@ def main():
                     k5 = float(np.median(ka) + np.median(kb))
                     print(json.dumps({
                         "photons": n, "hits_knob": h, "radius": r, "rays": nq, "kind": kind,
+                        "k5_path": "tiles" if (kind == "pinhole" and not args.no_grid) else "per-ray",
                         "build": build_kind, "build_ms": round(build_ms, 3),
                         "k5a_ms": round(float(np.median(ka)), 3), "k5b_ms": round(float(np.median(kb)), 3),
                         "mqueries_per_s": round(nq / k5 / 1e3, 2),
