@@ -87,3 +87,52 @@ def test_two_rank_sharding_equals_single_process(tmp_path):
     assert np.array_equal(got["image"].view(np.uint32), rgb.view(np.uint32))
     assert set(got["owner"].tolist()) == {0, 1}
     assert rgb.max() > 0
+
+
+def _worker_photon_shard(rank, world, port, out_path):
+    """Photon sharding (bre_set_photon_sharding): a rank keeps the paths it traced, builds its own tree, answers EVERY
+    pixel from it; the partial films are summed onto rank 0 (the GPU path: reduce-scatter over CUDA-IPC / ncclReduce)."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    bre, orc = _setup()
+    lib = bre.load_library()
+    o = orc.Oracle()
+    o.set_medium_homogeneous(SA, SS, G)
+    first, count = bre.shard_range(N_PATHS, world, rank, lib)
+    pos, pw, dr, _ = o.trace(LIGHTS, LO, HI, first, count, DEPTH)
+    o.set_photons(pos, pw, dr, RADIUS)
+    o.build()
+    ro, rd = o.synth_rays_pinhole(W, H)
+    rgb, offs, idx, _ = o.query(ro, rd, float(N_PATHS), want_hits=True)      # normalised by ALL emitted paths
+    film = torch.from_numpy(rgb.astype(np.float32).copy())
+    hits = torch.from_numpy(np.diff(offs.astype(np.int64)))
+    n_local = torch.tensor([pos.shape[0]], dtype=torch.int64)
+    dist.reduce(film, 0, op=dist.ReduceOp.SUM)
+    dist.reduce(hits, 0, op=dist.ReduceOp.SUM)
+    dist.reduce(n_local, 0, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        np.savez(out_path, image=film.numpy(), hits=hits.numpy(), n=n_local.numpy())
+    dist.destroy_process_group()
+
+
+def test_two_rank_photon_sharding_sums_to_the_single_process_image(tmp_path):
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    out = str(tmp_path / "summed.npz")
+    mp.spawn(_worker_photon_shard, args=(2, port, out), nprocs=2, join=True)
+    got = np.load(out)
+    bre, orc = _setup()
+    o = orc.Oracle()
+    o.set_medium_homogeneous(SA, SS, G)
+    pos, pw, dr, _ = o.trace(LIGHTS, LO, HI, 0, N_PATHS, DEPTH)
+    assert int(got["n"][0]) == pos.shape[0]                       # the slices partition the photon set
+    o.set_photons(pos, pw, dr, RADIUS)
+    o.build()
+    ro, rd = o.synth_rays_pinhole(W, H)
+    rgb, offs, idx, _ = o.query(ro, rd, float(N_PATHS), want_hits=True)
+    assert np.array_equal(got["hits"], np.diff(offs.astype(np.int64)))   # hit sets partition by photon
+    err = np.abs(got["image"].astype(np.float64) - rgb)
+    assert err.mean() <= 1e-4 * np.abs(rgb).mean() and err.max() <= 1e-3 * np.abs(rgb).max()   # float summation order
+    assert rgb.max() > 0
