@@ -237,6 +237,8 @@ int bre_set_medium_grid(bre_ctx *ctx, const float sa[3], const float ss[3], floa
     CTX_CHECK();
     if (!sa || !ss || !density || !w2m || nx < 1 || ny < 1 || nz < 1)
         return set_err(ctx, BRE_ERR_INVALID, "bad grid medium arguments");
+    if ((uint64_t)nx * (uint64_t)ny * (uint64_t)nz >= (1ull << 31))
+        return set_err(ctx, BRE_ERR_UNSUPPORTED, "density grid of 2^31 voxels or more (32-bit voxel indices on the device)");
     // GridDensityMedium requires a spectrally uniform sigma_t (media/grid.h:63-67)
     float st0 = sa[0] + ss[0];
     if (sa[1] + ss[1] != st0 || sa[2] + ss[2] != st0)

@@ -116,6 +116,19 @@ struct TreeDev {
     float abs_max;            // max |coordinate| of any leaf box
 };
 
+// The eight corners of the INTERIOR cell (ix, iy, iz) of a density grid, with 32-bit index arithmetic (the grid holds
+// fewer than 2^31 voxels, checked by bre_set_medium_grid): four pointers = four IMAD.WIDE, where size_t indexing of
+// signed coordinates cost ~25 integer instructions per sample in K1's tracker and K6.
+__device__ __forceinline__ void grid_cell_corners(const MediumDev &m, int ix, int iy, int iz, float &v000, float &v100,
+                                                  float &v010, float &v110, float &v001, float &v101, float &v011,
+                                                  float &v111) {
+    const unsigned nx = (unsigned)m.nx, zs = nx * (unsigned)m.ny;
+    const unsigned i0 = ((unsigned)iz * (unsigned)m.ny + (unsigned)iy) * nx + (unsigned)ix;
+    const float *b0 = m.density + i0, *b1 = m.density + (i0 + nx), *b2 = m.density + (i0 + zs), *b3 = m.density + (i0 + zs + nx);
+    v000 = __ldg(b0); v100 = __ldg(b0 + 1); v010 = __ldg(b1); v110 = __ldg(b1 + 1);
+    v001 = __ldg(b2); v101 = __ldg(b2 + 1); v011 = __ldg(b3); v111 = __ldg(b3 + 1);
+}
+
 // Power / direction of the photon at sorted position s.  The image-tile path stages them once per (tile, photon)
 // and reads them through the Morton permutation straight from the store (bre_build then moves only the 16-byte
 // position records); the per-ray paths gather them first (ensure_sorted_payload).

@@ -110,10 +110,7 @@ __device__ float grid_density_t(const MediumDev &m, float px, float py, float pz
     float v000, v100, v010, v110, v001, v101, v011, v111;
     if ((unsigned)ix < (unsigned)(m.nx - 1) && (unsigned)iy < (unsigned)(m.ny - 1) &&
         (unsigned)iz < (unsigned)(m.nz - 1)) {   // interior: no bounds compares
-        const float *b = m.density + ((size_t)iz * m.ny + iy) * m.nx + ix;
-        const size_t ys = (size_t)m.nx, zs = (size_t)m.nx * m.ny;
-        v000 = __ldg(b); v100 = __ldg(b + 1); v010 = __ldg(b + ys); v110 = __ldg(b + ys + 1);
-        v001 = __ldg(b + zs); v101 = __ldg(b + zs + 1); v011 = __ldg(b + zs + ys); v111 = __ldg(b + zs + ys + 1);
+        grid_cell_corners(m, ix, iy, iz, v000, v100, v010, v110, v001, v101, v011, v111);
     } else {
         v000 = gridD(m, ix, iy, iz); v100 = gridD(m, ix + 1, iy, iz);
         v010 = gridD(m, ix, iy + 1, iz); v110 = gridD(m, ix + 1, iy + 1, iz);
@@ -145,10 +142,7 @@ __device__ __forceinline__ float grid_density_fused(const MediumDev &m, float px
     float v000, v100, v010, v110, v001, v101, v011, v111;
     if ((unsigned)ix < (unsigned)(m.nx - 1) && (unsigned)iy < (unsigned)(m.ny - 1) &&
         (unsigned)iz < (unsigned)(m.nz - 1)) {
-        const float *b = m.density + ((size_t)iz * m.ny + iy) * m.nx + ix;
-        const size_t ys = (size_t)m.nx, zs = (size_t)m.nx * m.ny;
-        v000 = __ldg(b); v100 = __ldg(b + 1); v010 = __ldg(b + ys); v110 = __ldg(b + ys + 1);
-        v001 = __ldg(b + zs); v101 = __ldg(b + zs + 1); v011 = __ldg(b + zs + ys); v111 = __ldg(b + zs + ys + 1);
+        grid_cell_corners(m, ix, iy, iz, v000, v100, v010, v110, v001, v101, v011, v111);
     } else {
         v000 = gridD(m, ix, iy, iz); v100 = gridD(m, ix + 1, iy, iz);
         v010 = gridD(m, ix, iy + 1, iz); v110 = gridD(m, ix + 1, iy + 1, iz);
