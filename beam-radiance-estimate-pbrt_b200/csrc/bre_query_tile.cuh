@@ -182,7 +182,10 @@ __device__ __forceinline__ float warp_min(float v) {
 __device__ __forceinline__ int ld_vol_s(const int *p) { return *reinterpret_cast<const volatile int *>(p); }
 
 template <int MODE, bool COUNT>
-__global__ void __launch_bounds__(TT_THREADS) k_tile_walk(
+#ifndef TW_MINB
+#define TW_MINB 3
+#endif
+__global__ void __launch_bounds__(TT_THREADS, TW_MINB) k_tile_walk(
     LeafArgs A, const LeafArgs *__restrict__ Ag, TileArgs T, WalkQueue W, uint32_t tile0, uint32_t nTiles,
     uint2 *__restrict__ queue, unsigned int queueCap, unsigned int *__restrict__ queueCtl,
     const unsigned int *__restrict__ heavyIn, const unsigned int *__restrict__ nHeavyInPtr,
@@ -562,7 +565,7 @@ struct __align__(16) TileHits {
     float th[64], d2[64], ct[64];
 };
 #ifndef TILE_MINB
-#define TILE_MINB 4
+#define TILE_MINB 5
 #endif
 constexpr size_t LEAF_TILE_SMEM = LP_WARPS * (sizeof(TileEnt) + sizeof(TileHits));
 
