@@ -1134,9 +1134,92 @@ uint64_t orc_trace_photons_mesh(const orc_medium *m, const orc_light *lights, in
     return stored;
 }
 
+/* ---- camera samples of the reference's HaltonSampler (samplers/halton.cpp) ----------------------------------
+ * The camera pass draws the film position of pixel p in iteration `iter` as p + (dimension 0, dimension 1) of a
+ * HaltonSampler(nIterations, pixelBounds) after StartPixel(p), SetSampleNumber(iter) (integrators/photonbeam.cpp:341,
+ * 459-466; GetCameraSample core/sampler.cpp:46-52; the AwesomeSampler wrapper passes the first 1000 draws through,
+ * photonbeam.cpp:199-213).  Restated: constructor halton.cpp:64-91, GetIndexForSample :94-114, SampleDimension
+ * :116-125 (dimensions 0 and 1 are not scrambled), InverseRadicalInverse core/lowdiscrepancy.h:82-91,
+ * RadicalInverse core/lowdiscrepancy.cpp:437-447 with RadicalInverseSpecialized<3> :395-408. */
+static int64_t orc_mod64(int64_t a, int64_t b) { int64_t r = a - (a / b) * b; return r < 0 ? r + b : r; } /* pbrt.h Mod */
+static void orc_ext_gcd(uint64_t a, uint64_t b, int64_t *x, int64_t *y) {                                 /* halton.cpp:51-61 */
+    if (b == 0) { *x = 1; *y = 0; return; }
+    int64_t d = (int64_t)(a / b), xp, yp;
+    orc_ext_gcd(b, a % b, &xp, &yp);
+    *x = yp;
+    *y = xp - (d * yp);
+}
+static uint64_t orc_mult_inverse(int64_t a, int64_t n) { int64_t x, y; orc_ext_gcd((uint64_t)a, (uint64_t)n, &x, &y); return (uint64_t)orc_mod64(x, n); }
+static uint64_t orc_inv_radical_inverse(uint64_t inverse, int base, int nDigits) {
+    uint64_t index = 0;
+    for (int i = 0; i < nDigits; ++i) { uint64_t digit = inverse % (uint64_t)base; inverse /= (uint64_t)base; index = index * (uint64_t)base + digit; }
+    return index;
+}
+static uint64_t orc_reverse_bits64(uint64_t n) {
+    uint64_t r = 0;
+    for (int i = 0; i < 64; ++i) { r = (r << 1) | (n & 1u); n >>= 1; }
+    return r;
+}
+static float orc_radical_inverse2(uint64_t a) { return (float)((double)orc_reverse_bits64(a) * 0x1p-64); } /* uint64 * double, narrowed */
+static float orc_radical_inverse3(uint64_t a) {
+    const float invBase = (float)1 / (float)3;
+    uint64_t reversedDigits = 0;
+    float invBaseN = 1;
+    while (a) {
+        uint64_t next = a / 3;
+        uint64_t digit = a - next * 3;
+        reversedDigits = reversedDigits * 3 + digit;
+        invBaseN *= invBase;
+        a = next;
+    }
+    float v = (float)reversedDigits * invBaseN;
+    return v < 0x1.fffffep-1f ? v : 0x1.fffffep-1f;       /* min(., OneMinusEpsilon) */
+}
+void orc_halton_setup(int resX, int resY, orc_halton *hs) {
+    const int kMaxResolution = 128;
+    const int res[2] = {resX, resY};
+    for (int i = 0; i < 2; ++i) {
+        int base = (i == 0) ? 2 : 3, scale = 1, e = 0;
+        const int lim = res[i] < kMaxResolution ? res[i] : kMaxResolution;
+        while (scale < lim) { scale *= base; ++e; }
+        hs->baseScales[i] = scale;
+        hs->baseExponents[i] = e;
+    }
+    hs->sampleStride = (int64_t)hs->baseScales[0] * hs->baseScales[1];
+    hs->multInverse[0] = orc_mult_inverse(hs->baseScales[1], hs->baseScales[0]);
+    hs->multInverse[1] = orc_mult_inverse(hs->baseScales[0], hs->baseScales[1]);
+}
+void orc_halton_camera_samples(int x0, int y0, int x1, int y1, int64_t sampleNum, float *out_xy) {
+    orc_halton hs;
+    orc_halton_setup(x1 - x0, y1 - y0, &hs);
+    for (int y = y0; y < y1; ++y)
+        for (int x = x0; x < x1; ++x) {
+            int64_t offset = 0;
+            if (hs.sampleStride > 1) {
+                const int64_t pm[2] = {orc_mod64(x, 128), orc_mod64(y, 128)};
+                uint64_t acc = 0;
+                for (int i = 0; i < 2; ++i) {
+                    const uint64_t dimOffset = orc_inv_radical_inverse((uint64_t)pm[i], i == 0 ? 2 : 3, hs.baseExponents[i]);
+                    acc += dimOffset * (uint64_t)(hs.sampleStride / hs.baseScales[i]) * hs.multInverse[i];
+                }
+                offset = (int64_t)(acc % (uint64_t)hs.sampleStride);
+            }
+            const int64_t index = offset + sampleNum * hs.sampleStride;
+            const size_t q = (size_t)(y - y0) * (size_t)(x1 - x0) + (size_t)(x - x0);
+            out_xy[2 * q] = orc_radical_inverse2((uint64_t)(index >> hs.baseExponents[0]));
+            out_xy[2 * q + 1] = orc_radical_inverse3((uint64_t)(index / hs.baseScales[1]));
+        }
+}
+
 void orc_camera_rays(const float r2c[16], const float c2w[16], int x0, int y0, int w, int h,
                      float offx, float offy, const orc_mesh *mesh, int cameraInMedium,
                      float *o_tmax, float *dirs) {
+    orc_camera_rays_px(r2c, c2w, x0, y0, w, h, offx, offy, NULL, mesh, cameraInMedium, o_tmax, dirs);
+}
+/* offs_xy != NULL: the sample position of pixel q inside the pixel is (offs_xy[2q], offs_xy[2q+1]) */
+void orc_camera_rays_px(const float r2c[16], const float c2w[16], int x0, int y0, int w, int h,
+                        float offx, float offy, const float *offs_xy, const orc_mesh *mesh, int cameraInMedium,
+                        float *o_tmax, float *dirs) {
     /* pinhole PerspectiveCamera (lensRadius 0), one ray per pixel of [x0,x0+w) x [y0,y0+h);
      * then what the adapter's camera pass does (integrators/photonbeam.cpp:465-481): Scene::Intersect
      * shortens tMax, direction normalised, tMax scaled by its length; tMax = 0 outside the medium. */
@@ -1146,6 +1229,7 @@ void orc_camera_rays(const float r2c[16], const float c2w[16], int x0, int y0, i
     for (int y = 0; y < h; ++y)
         for (int x = 0; x < w; ++x) {
             size_t q = (size_t)y * w + x;
+            if (offs_xy) { offx = offs_xy[2 * q]; offy = offs_xy[2 * q + 1]; }
             float fx = (float)(x0 + x) + offx, fy = (float)(y0 + y) + offy, fz = 0.f;
             float pc[3];
             for (int r = 0; r < 3; ++r) pc[r] = r2c[4 * r] * fx + r2c[4 * r + 1] * fy + r2c[4 * r + 2] * fz + r2c[4 * r + 3];

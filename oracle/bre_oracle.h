@@ -195,6 +195,14 @@ uint64_t orc_trace_photons_mesh(const orc_medium *m, const orc_light *lights, in
                                 uint64_t nPaths, int maxDepth, float *pos, float *power, float *dir,
                                 uint32_t *path_id, uint64_t cap);
 /* Pinhole camera rays + first-surface tMax; o_tmax 4 floats per pixel, dirs 3 (unit length). */
+/* HaltonSampler camera samples (samplers/halton.cpp): see bre_oracle.c */
+typedef struct { int baseScales[2], baseExponents[2]; int64_t sampleStride; uint64_t multInverse[2]; } orc_halton;
+void orc_halton_setup(int resX, int resY, orc_halton *hs);
+/* out_xy: 2 floats per pixel of [x0,x1) x [y0,y1) (row major): dimensions 0 and 1 of sample `sampleNum` of that pixel */
+void orc_halton_camera_samples(int x0, int y0, int x1, int y1, int64_t sampleNum, float *out_xy);
+void orc_camera_rays_px(const float raster_to_camera[16], const float camera_to_world[16], int x0, int y0,
+                        int w, int h, float offx, float offy, const float *offs_xy, const orc_mesh *mesh,
+                        int cameraInMedium, float *o_tmax, float *dirs);
 void orc_camera_rays(const float raster_to_camera[16], const float camera_to_world[16], int x0, int y0,
                      int w, int h, float offx, float offy, const orc_mesh *mesh, int cameraInMedium,
                      float *o_tmax, float *dirs);

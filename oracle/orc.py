@@ -222,6 +222,20 @@ class Oracle:
         n = min(int(n), cap)
         return pos[:n], pw[:n], dr[:n], pid[:n]
 
+    def halton_camera_samples(self, x0, y0, x1, y1, sample_num):
+        """(dimension 0, dimension 1) of the reference's HaltonSampler per pixel of [x0,x1) x [y0,y1), row major."""
+        out = np.zeros(((x1 - x0) * (y1 - y0), 2), np.float32)
+        self.lib.orc_halton_camera_samples(int(x0), int(y0), int(x1), int(y1), C.c_int64(int(sample_num)), _fp(out))
+        return out
+
+    def camera_rays_px(self, r2c, c2w, x0, y0, w, h, offs_xy, use_mesh=True, camera_in_medium=True):
+        r2c, c2w, offs = _f32(r2c).reshape(16), _f32(c2w).reshape(16), _f32(offs_xy).reshape(-1)
+        o, d = np.zeros((w * h, 4), np.float32), np.zeros((w * h, 3), np.float32)
+        mesh = C.byref(self.mesh) if use_mesh else None
+        self.lib.orc_camera_rays_px(_fp(r2c), _fp(c2w), x0, y0, w, h, C.c_float(0), C.c_float(0), _fp(offs), mesh,
+                                    int(camera_in_medium), _fp(o), _fp(d))
+        return o, d
+
     def camera_rays(self, r2c, c2w, x0, y0, w, h, offx, offy, use_mesh=True, camera_in_medium=True):
         r2c, c2w = _f32(r2c).reshape(16), _f32(c2w).reshape(16)
         o = np.zeros((w * h, 4), np.float32); d = np.zeros((w * h, 3), np.float32)

@@ -44,6 +44,7 @@
 
 #include "pbrt.h"
 #include "accelerators/bvh.h"
+#include "samplers/halton.h"
 #include "cameras/perspective.h"
 #include "film.h"
 #include "filters/box.h"
@@ -780,6 +781,43 @@ void gridspot(const char *path, uint64_t nPaths, int res, float radius) {
             rays.size(), idx.size());
 }
 
+// ---------------------------------------------------------------- mode: halton
+// Camera samples as the reference's camera pass draws them (integrators/photonbeam.cpp:341,459-466):
+// HaltonSampler(nIterations, pixelBounds); per pixel StartPixel(p), SetSampleNumber(iter), then the first Get2D of
+// GetCameraSample (core/sampler.cpp:46-52).  Several pixel windows (smaller and larger than kMaxResolution = 128,
+// non-zero origin) x several iterations.
+void halton(const char *path) {
+    const int windows[4][4] = {{0, 0, 40, 30}, {3, 5, 150, 105}, {17, 9, 17 + 140, 9 + 131}, {100, 200, 101, 201}};
+    // iterations stored per window (bit mask over iters[]): the large windows keep two / one of them
+    const unsigned keep[4] = {15u, 5u, 8u, 15u};
+    const int iters[4] = {0, 1, 7, 1000};
+    BinWriter bw(path);
+    std::vector<uint32_t> win;
+    for (int wi = 0; wi < 4; ++wi) {
+        const int *W = windows[wi];
+        Bounds2i pb(Point2i(W[0], W[1]), Point2i(W[2], W[3]));
+        for (int k = 0; k < 4; ++k) win.push_back((uint32_t)W[k]);
+        HaltonSampler sampler(64, pb);
+        for (int it = 0; it < 4; ++it) {
+            if (!(keep[wi] >> it & 1u)) continue;
+            std::vector<float> xy;
+            for (Point2i p : pb) {
+                sampler.StartPixel(p);
+                sampler.SetSampleNumber(iters[it]);
+                CameraSample cs = sampler.GetCameraSample(p);
+                xy.push_back(cs.pFilm.x);
+                xy.push_back(cs.pFilm.y);
+            }
+            char name[24];
+            snprintf(name, sizeof(name), "w%d_i%d", wi, iters[it]);
+            bw.f4(name, xy);
+        }
+    }
+    bw.u4("windows", win);
+    bw.u4("iters", {0, 1, 7, 1000});
+    fprintf(stderr, "halton: 4 windows x 4 iterations\n");
+}
+
 // ---------------------------------------------------------------- mode: surfaces
 // Fog box with matte walls of different reflectance, one reverse-orientation wall, and an
 // interface-only quad (no material, MediumInterface inside = fog, outside = vacuum) at x = 1.5 that
@@ -1097,6 +1135,7 @@ int main(int argc, char **argv) {
                argc >= 8 && !strcmp(argv[7], "digest"));
         return 0;
     }
+    if (argc >= 3 && !strcmp(argv[1], "halton")) { halton(argv[2]); return 0; }
     if (argc >= 6 && !strcmp(argv[1], "gridspot")) {
         gridspot(argv[2], (uint64_t)atoll(argv[3]), atoi(argv[4]), (float)atof(argv[5]));
         return 0;

@@ -16,6 +16,8 @@ compressed .npz fixtures.  The fixtures travel to the GPU box; /root/reference d
   ref_gridspot.npz           query fixture for a GridDensityMedium lit by a SpotLight: photons walked by reference classes,
                              reference camera rays, brute-force estimate with transmittance from a fine integral of the
                              reference's Density()
+  ref_halton.npz             film positions of the camera samples the reference's HaltonSampler hands to the camera pass
+                             (StartPixel / SetSampleNumber(iter) / GetCameraSample) for several pixel windows and iterations
   ref_trace_homogeneous.npz  volume-photon deposit loop executed by reference classes
   ref_trace_grid.npz         (sampler stream of photonbeam.cpp:386-391, deposit rule photonmap.cpp:696-724)
   ref_gridtr.npz             GridDensityMedium::Tr statistics + fine integral of the reference's Density() through the
@@ -102,7 +104,17 @@ def gridspot(tmp):
     np.savez_compressed(os.path.join(HERE, "ref_gridspot.npz"), **read_bref(gb))
 
 
+def halton(tmp):
+    hb = os.path.join(tmp, "halton.bin")
+    subprocess.check_call([HARNESS, "halton", hb])
+    np.savez_compressed(os.path.join(HERE, "ref_halton.npz"), **read_bref(hb))
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "halton":
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "ref", "-j8"])
+        halton(tempfile.mkdtemp())
+        return
     if len(sys.argv) > 1 and sys.argv[1] in ("fogbox_100k", "gridspot"):       # only this fixture
         subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "ref", "-j8"])
         {"fogbox_100k": fogbox_big, "gridspot": gridspot}[sys.argv[1]](tempfile.mkdtemp())
@@ -141,6 +153,7 @@ def main():
     gridtr(tmp)
     fogbox_big(tmp)
     gridspot(tmp)
+    halton(tmp)
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)), "bytes")

@@ -405,3 +405,30 @@ def test_beam_estimate_grid_medium_spot_light_vs_reference(oracle):
         assert errs[steps] <= mean_tol, (steps, errs[steps])
         assert err.max() <= max_tol * np.abs(ref_rgb).max(), (steps, err.max() / np.abs(ref_rgb).max())
     assert errs[128] < errs[0] / 3 and errs[256] < errs[128] / 3        # second order in the step
+
+
+def test_halton_camera_samples_bit_exact_vs_reference_sampler(oracle):
+    """Film positions of the camera samples: the reference's HaltonSampler (StartPixel / SetSampleNumber(iter) /
+    GetCameraSample, as integrators/photonbeam.cpp:459-466 draws them) for pixel windows below and above
+    kMaxResolution = 128, with non-zero origins, a single pixel, and sample numbers up to 1000 -- against the oracle's
+    restatement of samplers/halton.cpp + core/lowdiscrepancy.cpp, bit for bit."""
+    g = gold("ref_halton.npz")
+    wins = g["windows"].reshape(-1, 4)
+    checked = 0
+    for wi, (x0, y0, x1, y1) in enumerate(wins.tolist()):
+        xs, ys = np.meshgrid(np.arange(x0, x1, dtype=np.float32), np.arange(y0, y1, dtype=np.float32))
+        px = np.stack([xs.reshape(-1), ys.reshape(-1)], axis=1)
+        for it in g["iters"].tolist():
+            key = f"w{wi}_i{it}"
+            if key not in g.files:
+                continue
+            ref = g[key].reshape(-1, 2)
+            u = oracle.halton_camera_samples(x0, y0, x1, y1, it)
+            assert (u >= 0).all() and (u < 1).all()
+            mine = px + u                                   # (Point2f)pRaster + Get2D(), core/sampler.cpp:48
+            assert np.array_equal(bits(mine), bits(ref)), key
+            checked += 1
+    assert checked == 11
+    # the samples of one pixel differ between iterations, and neighbours differ
+    u0, u1 = oracle.halton_camera_samples(0, 0, 40, 30, 0), oracle.halton_camera_samples(0, 0, 40, 30, 1)
+    assert not np.array_equal(u0, u1) and len(np.unique(u0[:, 0])) > 30
