@@ -28,7 +28,7 @@ SYMBOLS = [
     "bre_set_triangle_attrs", "bre_set_lights_in_medium", "bre_set_camera", "bre_camera_rays",
     "bre_query_camera_to_film", "bre_last_build_kind",
     "bre_trace_exchange_photons", "bre_alloc_pinned", "bre_free_pinned", "bre_stage_rays", "bre_query_staged_to_film", "bre_save_photons", "bre_load_photons", "bre_film_save", "bre_film_load",
-    "bre_film_resolve_static", "bre_set_ray_grid", "bre_set_tile_sharding", "bre_set_photon_sharding", "bre_film_gather", "bre_stage_camera", "bre_stage_rays_d",
+    "bre_film_resolve_static", "bre_camera_rays_halton", "bre_stage_camera_halton", "bre_query_camera_halton_to_film", "bre_set_ray_grid", "bre_set_tile_sharding", "bre_set_photon_sharding", "bre_film_gather", "bre_stage_camera", "bre_stage_rays_d",
 ]
 
 
@@ -185,6 +185,18 @@ class Bre:
         o = np.zeros((n, 4), np.float32); d = np.zeros((n, 3), np.float32)
         self._ck(self.lib.bre_camera_rays(self.ctx, C.c_float(offx), C.c_float(offy), _fp(o), _fp(d)))
         return o, d
+
+    def camera_rays_halton(self, sample_num):
+        n = getattr(self, "_cam_n", 0)
+        o = np.zeros((n, 4), np.float32); d = np.zeros((n, 3), np.float32)
+        self._ck(self.lib.bre_camera_rays_halton(self.ctx, C.c_int64(int(sample_num)), _fp(o), _fp(d)))
+        return o, d
+
+    def stage_camera_halton(self, sample_num):
+        self._ck(self.lib.bre_stage_camera_halton(self.ctx, C.c_int64(int(sample_num))))
+
+    def query_camera_halton_to_film(self, n_paths_norm, sample_num):
+        self._ck(self.lib.bre_query_camera_halton_to_film(self.ctx, C.c_int64(int(sample_num)), C.c_float(n_paths_norm)))
 
     def stage_camera(self, offx=0.5, offy=0.5):
         self._ck(self.lib.bre_stage_camera(self.ctx, C.c_float(offx), C.c_float(offy)))

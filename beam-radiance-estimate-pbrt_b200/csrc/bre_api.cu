@@ -601,20 +601,29 @@ int bre_stage_rays_d(bre_ctx *ctx, uint32_t n, const void *ro, const void *rd) {
     return BRE_OK;
 }
 
+static int stage_camera_impl(bre_ctx *ctx, float offx, float offy, long long halton);
 int bre_stage_camera(bre_ctx *ctx, float offx, float offy) {
     CTX_CHECK();
+    return stage_camera_impl(ctx, offx, offy, -1);
+}
+int bre_stage_camera_halton(bre_ctx *ctx, int64_t sample_num) {
+    CTX_CHECK();
+    if (sample_num < 0) return set_err(ctx, BRE_ERR_INVALID, "negative sample number");
+    return stage_camera_impl(ctx, 0.f, 0.f, (long long)sample_num);
+}
+static int stage_camera_impl(bre_ctx *ctx, float offx, float offy, long long halton) {
     if (!ctx->have_camera) return set_err(ctx, BRE_ERR_INVALID, "bre_set_camera has not been called");
     int s;
     const uint32_t n = (uint32_t)ctx->camera.width * (uint32_t)ctx->camera.height;
     if ((s = ensure(ctx, ctx->rays_o, (size_t)n * 16)) != BRE_OK) return s;     // (before the streams fork: ensure may free)
     if ((s = ensure(ctx, ctx->rays_d, (size_t)n * 16)) != BRE_OK) return s;
     if ((s = staging_begin(ctx)) != BRE_OK) return s;
-    if ((s = camera_rays(ctx, offx, offy, ctx->copy_stream)) != BRE_OK) return s;
+    if ((s = camera_rays(ctx, offx, offy, ctx->copy_stream, halton)) != BRE_OK) return s;
     s = stage_tau_deferred(ctx, n, (const float4 *)ctx->rays_o.p, (const float4 *)ctx->rays_d.p, true,
                            (uint32_t)ctx->camera.width, (uint32_t)ctx->camera.height);
     if (s != BRE_OK) return s;
     BRE_CUDA(cudaEventRecord(ctx->ev_stage, ctx->copy_stream));
-    ctx->cam_staged = true; ctx->cam_offx = offx; ctx->cam_offy = offy;
+    ctx->cam_staged = true; ctx->cam_offx = offx; ctx->cam_offy = offy; ctx->cam_halton = halton;
     return BRE_OK;
 }
 
@@ -642,9 +651,19 @@ int bre_query_staged_to_film(bre_ctx *ctx, const uint32_t *pix, float nPathsNorm
     return film_accumulate(ctx, n, pd, (const float4 *)ctx->out_rgb.p);
 }
 
+static int camera_rays_impl(bre_ctx *ctx, float offx, float offy, long long halton, float *o4, float *d3);
 int bre_camera_rays(bre_ctx *ctx, float offx, float offy, float *o4, float *d3) {
     CTX_CHECK();
-    int s = camera_rays(ctx, offx, offy);
+    return camera_rays_impl(ctx, offx, offy, -1, o4, d3);
+}
+int bre_camera_rays_halton(bre_ctx *ctx, int64_t sample_num, float *o4, float *d3) {
+    CTX_CHECK();
+    if (sample_num < 0) return set_err(ctx, BRE_ERR_INVALID, "negative sample number");
+    return camera_rays_impl(ctx, 0.f, 0.f, (long long)sample_num, o4, d3);
+}
+static int camera_rays_impl(bre_ctx *ctx, float offx, float offy, long long halton, float *o4, float *d3) {
+    ctx->cam_staged = false;
+    int s = camera_rays(ctx, offx, offy, nullptr, halton);
     if (s != BRE_OK) return s;
     const uint32_t n = (uint32_t)ctx->camera.width * (uint32_t)ctx->camera.height;
     if (o4) BRE_CUDA(cudaMemcpyAsync(o4, ctx->rays_o.p, (size_t)n * 16, cudaMemcpyDeviceToHost, ctx->stream));
@@ -658,20 +677,29 @@ int bre_camera_rays(bre_ctx *ctx, float offx, float offy, float *o4, float *d3) 
     return BRE_OK;
 }
 
+static int query_camera_impl(bre_ctx *ctx, float offx, float offy, long long halton, float nPathsNorm);
 int bre_query_camera_to_film(bre_ctx *ctx, float offx, float offy, float nPathsNorm) {
     CTX_CHECK();
+    return query_camera_impl(ctx, offx, offy, -1, nPathsNorm);
+}
+int bre_query_camera_halton_to_film(bre_ctx *ctx, int64_t sample_num, float nPathsNorm) {
+    CTX_CHECK();
+    if (sample_num < 0) return set_err(ctx, BRE_ERR_INVALID, "negative sample number");
+    return query_camera_impl(ctx, 0.f, 0.f, (long long)sample_num, nPathsNorm);
+}
+static int query_camera_impl(bre_ctx *ctx, float offx, float offy, long long halton, float nPathsNorm) {
     int s = query_ready(ctx);
     if (s != BRE_OK) return s;
     if (!ctx->have_camera) return set_err(ctx, BRE_ERR_INVALID, "bre_set_camera has not been called");
     const uint32_t n = (uint32_t)ctx->camera.width * (uint32_t)ctx->camera.height;
     if (!ctx->film.p || ctx->n_pixels != n)
         return set_err(ctx, BRE_ERR_INVALID, "bre_film_create(width*height) has not been called");
-    if (ctx->cam_staged && ctx->cam_offx == offx && ctx->cam_offy == offy) {
+    if (ctx->cam_staged && ctx->cam_halton == halton && (halton >= 0 || (ctx->cam_offx == offx && ctx->cam_offy == offy))) {
         // bre_stage_camera generated exactly these rays (and their optical-depth table) under the photon pass
         BRE_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_stage, 0));
     } else {
         ctx->tau_staged = false;
-        if ((s = camera_rays(ctx, offx, offy)) != BRE_OK) return s;
+        if ((s = camera_rays(ctx, offx, offy, nullptr, halton)) != BRE_OK) return s;
     }
     ctx->cam_staged = false;
     if ((s = ensure(ctx, ctx->out_rgb, (size_t)n * 16)) != BRE_OK) return s;

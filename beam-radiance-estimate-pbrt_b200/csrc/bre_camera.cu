@@ -8,6 +8,7 @@
 // no ray data over PCIe.
 #include "bre_internal.cuh"
 #include "bre_surface.cuh"
+#include <algorithm>
 #include <cstring>
 #include <vector>
 
@@ -21,11 +22,58 @@ struct CameraDev {
     float blo[3], bhi[3];
 };
 
-__global__ void __launch_bounds__(128) k_camera_rays(CameraDev cam, MeshDev mesh, float offx, float offy,
+// Camera samples of the reference's HaltonSampler (samplers/halton.cpp): the film position of pixel p in iteration
+// `sample` is p + (dimension 0, dimension 1) of HaltonSampler(nIterations, pixelBounds) after StartPixel(p),
+// SetSampleNumber(sample) (integrators/photonbeam.cpp:341,459-466; GetCameraSample core/sampler.cpp:46-52).
+// Host part = the constructor (halton.cpp:64-91); device part = GetIndexForSample (:94-114) and SampleDimension for the
+// unscrambled dimensions 0 / 1 (:116-125; InverseRadicalInverse lowdiscrepancy.h:82-91, RadicalInverse
+// lowdiscrepancy.cpp:437-447, RadicalInverseSpecialized<3> :395-408).  Bit-exact with the oracle's restatement,
+// which is pinned to the reference class (tests/golden/ref_halton.npz).
+struct HaltonDev {
+    int on;                       // 0: the uniform (offx, offy) of the launch
+    int exp0, exp1;               // baseExponents
+    uint32_t scale0, scale1;      // baseScales
+    uint64_t stride, mi0, mi1;    // sampleStride, multInverse
+    uint64_t sample;              // sample number (= iteration)
+};
+__device__ __forceinline__ uint64_t inv_radical_inverse(uint64_t inverse, uint32_t base, int nDigits) {
+    uint64_t index = 0;
+    for (int i = 0; i < nDigits; ++i) {
+        const uint64_t digit = inverse % base;
+        inverse /= base;
+        index = index * base + digit;
+    }
+    return index;
+}
+__device__ __forceinline__ void halton_camera_sample(const HaltonDev &hs, int px, int py, float &u, float &v) {
+    uint64_t offset = 0;
+    if (hs.stride > 1) {
+        const int mx = ((px % 128) + 128) % 128, my = ((py % 128) + 128) % 128;      // Mod(p, kMaxResolution)
+        const uint64_t d0 = inv_radical_inverse((uint64_t)mx, 2u, hs.exp0), d1 = inv_radical_inverse((uint64_t)my, 3u, hs.exp1);
+        offset = (d0 * (hs.stride / hs.scale0) * hs.mi0 + d1 * (hs.stride / hs.scale1) * hs.mi1) % hs.stride;
+    }
+    const uint64_t index = offset + hs.sample * hs.stride;
+    // base 2: ReverseBits64(a) * 0x1p-64 is a uint64 x DOUBLE product narrowed to float
+    u = __double2float_rn(__ull2double_rn(__brevll(index >> hs.exp0)) * 0x1p-64);
+    // base 3: digits reversed into an integer, scaled by (1/3)^n accumulated in float
+    uint64_t a = index / hs.scale1, rev = 0;
+    const float invBase = 1.f / 3.f;
+    float invBaseN = 1.f;
+    while (a) {
+        const uint64_t next = a / 3u;
+        rev = rev * 3u + (a - next * 3u);
+        invBaseN = __fmul_rn(invBaseN, invBase);
+        a = next;
+    }
+    v = fminf(__fmul_rn(__ull2float_rn(rev), invBaseN), 0x1.fffffep-1f);     // min(., OneMinusEpsilon)
+}
+
+__global__ void __launch_bounds__(128) k_camera_rays(CameraDev cam, MeshDev mesh, float offx, float offy, HaltonDev hs,
                                                      float4 *__restrict__ ro, float4 *__restrict__ rd) {
     uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= (uint32_t)(cam.w * cam.h)) return;
     int x = (int)(q % (uint32_t)cam.w), y = (int)(q / (uint32_t)cam.w);
+    if (hs.on) halton_camera_sample(hs, cam.x0 + x, cam.y0 + y, offx, offy);
     float fx = (float)(cam.x0 + x) + offx, fy = (float)(cam.y0 + y) + offy, fz = 0.f;
     float pc[3];
 #pragma unroll
@@ -72,7 +120,22 @@ __global__ void __launch_bounds__(128) k_camera_rays(CameraDev cam, MeshDev mesh
     rd[q] = make_float4(d[0] * inv, d[1] * inv, d[2] * inv, 0.f);
 }
 
-int camera_rays(bre_ctx *ctx, float offx, float offy, cudaStream_t st) {
+// halton.cpp:45-61
+static void extended_gcd(uint64_t a, uint64_t b, int64_t *x, int64_t *y) {
+    if (b == 0) { *x = 1; *y = 0; return; }
+    int64_t d = (int64_t)(a / b), xp, yp;
+    extended_gcd(b, a % b, &xp, &yp);
+    *x = yp;
+    *y = xp - (d * yp);
+}
+static uint64_t multiplicative_inverse(int64_t a, int64_t n) {
+    int64_t x, y;
+    extended_gcd((uint64_t)a, (uint64_t)n, &x, &y);
+    int64_t r = x - (x / n) * n;
+    return (uint64_t)(r < 0 ? r + n : r);
+}
+
+int camera_rays(bre_ctx *ctx, float offx, float offy, cudaStream_t st, long long haltonSample) {
     if (!st) st = ctx->stream;
     if (!ctx->have_camera) return set_err(ctx, BRE_ERR_INVALID, "bre_set_camera has not been called");
     const bre_camera &c = ctx->camera;
@@ -92,7 +155,25 @@ int camera_rays(bre_ctx *ctx, float offx, float offy, cudaStream_t st) {
     cd.haveBox = (ctx->n_tri == 0 && ctx->have_bounds) ? 1 : 0;
     for (int r = 0; r < 3; ++r) { cd.blo[r] = ctx->blo[r]; cd.bhi[r] = ctx->bhi[r]; }
     MeshDev mesh{ctx->n_tri, (const float4 *)ctx->tri.p, (const float *)ctx->tri_kdb.p};
-    k_camera_rays<<<(n + 127) / 128, 128, 0, st>>>(cd, mesh, offx, offy, (float4 *)ctx->rays_o.p,
+    HaltonDev hs{};
+    if (haltonSample >= 0) {
+        // HaltonSampler constructor for sampleBounds = the camera's pixel window (halton.cpp:73-91)
+        const int res[2] = {c.width, c.height};
+        uint32_t scale[2];
+        int ex[2];
+        for (int i = 0; i < 2; ++i) {
+            const int base = i == 0 ? 2 : 3, lim = std::min(res[i], 128);
+            int sc = 1, e = 0;
+            while (sc < lim) { sc *= base; ++e; }
+            scale[i] = (uint32_t)sc; ex[i] = e;
+        }
+        hs.on = 1; hs.exp0 = ex[0]; hs.exp1 = ex[1]; hs.scale0 = scale[0]; hs.scale1 = scale[1];
+        hs.stride = (uint64_t)scale[0] * scale[1];
+        hs.mi0 = multiplicative_inverse(scale[1], scale[0]);
+        hs.mi1 = multiplicative_inverse(scale[0], scale[1]);
+        hs.sample = (uint64_t)haltonSample;
+    }
+    k_camera_rays<<<(n + 127) / 128, 128, 0, st>>>(cd, mesh, offx, offy, hs, (float4 *)ctx->rays_o.p,
                                                            (float4 *)ctx->rays_d.p);
     BRE_CUDA(cudaGetLastError());
     return BRE_OK;

@@ -230,6 +230,7 @@ struct bre_ctx {
     uint64_t medium_version = 0;
     bool cam_staged = false;                // K0's rays of (cam_offx, cam_offy) are in rays_o / rays_d (bre_stage_camera)
     float cam_offx = 0, cam_offy = 0;
+    long long cam_halton = -1;              // >= 0: the staged rays are the Halton camera samples of that sample number
     cudaStream_t stream2 = nullptr;
     cudaEvent_t qev[4] = {};
     bre::Buf rays_o, rays_d, out_rgb, tau, hit_counts, hit_offsets, hit_idx, counters_d, pix_idx;
@@ -291,7 +292,7 @@ int run_hitdump(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4 *rd, br
 int film_accumulate(bre_ctx *ctx, uint32_t n, const uint32_t *pix_d, const float4 *rgb_d);
 int film_resolve(bre_ctx *ctx, int iter, float scale, float *rgb_out_host, int meanOnly);
 // camera.cu
-int camera_rays(bre_ctx *ctx, float offx, float offy, cudaStream_t st = nullptr);
+int camera_rays(bre_ctx *ctx, float offx, float offy, cudaStream_t st = nullptr, long long haltonSample = -1);
 // trace.cu
 constexpr uint64_t TRACE_CHUNK = 1u << 22;   // paths per trace launch (bounds the slot scratch)
 struct SlotView {

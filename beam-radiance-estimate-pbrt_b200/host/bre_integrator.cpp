@@ -4,6 +4,7 @@
 // density grid, WorldToMedium; pLight, I, cone cosines): INTEGRATION.md adds
 // `friend class BreIntegrator;` to media/homogeneous.h, media/grid.h, lights/point.h, lights/spot.h.
 #include "bre_integrator.h"
+#include "samplers/halton.h"
 
 #include "bre.h"   // the C ABI (include/bre.h of the B200 library)
 
@@ -393,21 +394,34 @@ void BreIntegrator::Render(const Scene &scene) {
         } else
             Warning("bre: cannot load checkpoint %s (%s): starting from an empty film", checkpoint.c_str(), bre_last_error(ctx));
     }
+    const bool haltonSamples = cameraSamples != "uniform";
+    HaltonSampler haltonSampler(nIterations, pixelBounds);          // photonbeam.cpp:341
     ProgressReporter progress(std::max(0, endIteration - startIteration), "Rendering (bre)");
     for (int iter = startIteration; iter < endIteration; ++iter) {
-        // iteration 0 looks through the pixel centres, later ones use a (2,3) Halton offset
+        // ---- camera samples.  "halton" (default): what the reference draws -- pixel p of iteration iter looks through
+        // p + the first two dimensions of HaltonSampler(nIterations, pixelBounds) after StartPixel(p),
+        // SetSampleNumber(iter) (photonbeam.cpp:341,459-466).  "uniform": one (2,3) Halton offset per iteration for
+        // every pixel (pixel centres in iteration 0): a regular ray grid.
         const Point2f off = iter == 0 ? Point2f(0.5f, 0.5f)
                                       : Point2f(RadicalInverse(0, iter), RadicalInverse(1, iter));
         // ---- camera rays first (photonbeam.cpp:444-481): they do not depend on the photons, so the
         // host generates them now and the upload overlaps the photon pass and the LBVH build
         if (!cameraOnDevice) {
             ParallelFor([&](int64_t y) {
+                std::unique_ptr<Sampler> rowSampler = haltonSamples ? haltonSampler.Clone((int)y) : nullptr;
                 for (int x = 0; x < ext.x; ++x) {
                     const size_t q = (size_t)y * ext.x + x;
                     CameraSample cs;
-                    cs.pFilm = Point2f(pixelBounds.pMin.x + x + off.x, pixelBounds.pMin.y + y + off.y);
-                    cs.pLens = Point2f(0.5f, 0.5f);
-                    cs.time = camera->shutterOpen;
+                    if (haltonSamples) {
+                        const Point2i pPixel(pixelBounds.pMin.x + x, pixelBounds.pMin.y + (int)y);
+                        rowSampler->StartPixel(pPixel);
+                        rowSampler->SetSampleNumber(iter);
+                        cs = rowSampler->GetCameraSample(pPixel);    // pFilm, time, pLens as the reference's sampler gives them
+                    } else {
+                        cs.pFilm = Point2f(pixelBounds.pMin.x + x + off.x, pixelBounds.pMin.y + y + off.y);
+                        cs.pLens = Point2f(0.5f, 0.5f);
+                        cs.time = camera->shutterOpen;
+                    }
                     RayDifferential ray;
                     Float w = camera->GenerateRayDifferential(cs, &ray);
                     SurfaceInteraction isect;
@@ -420,7 +434,8 @@ void BreIntegrator::Render(const Scene &scene) {
                 }
             }, ext.y, 4);
             if (!Check(ctx, bre_stage_rays(ctx, nPixels, rayO, rayD), "bre_stage_rays")) break;
-        } else if (!Check(ctx, bre_stage_camera(ctx, off.x, off.y), "bre_stage_camera"))   // K0 + K6 under the photon pass
+        } else if (!(haltonSamples ? Check(ctx, bre_stage_camera_halton(ctx, iter), "bre_stage_camera_halton")
+                                   : Check(ctx, bre_stage_camera(ctx, off.x, off.y), "bre_stage_camera")))   // K0 + K6 under the photon pass
             break;
         // ---- photon pass (photonbeam.cpp:365-437): path indices iter*nPaths .. as :386-388
         // "reusephotons": the photon map of iteration 0 is kept and only its radius shrinks, so
@@ -449,7 +464,9 @@ void BreIntegrator::Render(const Scene &scene) {
         ok = ok && Check(ctx, bre_build(ctx), "bre_build");
         // ---- camera pass (photonbeam.cpp:444-557): one query segment per pixel
         if (ok) {
-            if (cameraOnDevice)
+            if (cameraOnDevice && haltonSamples)
+                ok = Check(ctx, bre_query_camera_halton_to_film(ctx, iter, (float)nPaths), "bre_query_camera_halton_to_film");
+            else if (cameraOnDevice)
                 ok = Check(ctx, bre_query_camera_to_film(ctx, off.x, off.y, (float)nPaths), "bre_query_camera_to_film");
             else
                 ok = Check(ctx, bre_query_staged_to_film(ctx, nullptr, (float)nPaths), "bre_query_staged_to_film");
@@ -518,7 +535,8 @@ Integrator *CreateBreIntegrator(const ParamSet &params, std::shared_ptr<const Ca
     return new BreIntegrator(camera, nIterations, photonsPerIter, maxDepth, radius, alpha,
                              writeFreq, renderMedia, tracer == "device", camrays == "device",
                              params.FindOneBool("reusephotons", false), device, startIteration, endIteration,
-                             params.FindOneString("checkpoint", ""), params.FindOneString("sharding", "photons"));
+                             params.FindOneString("checkpoint", ""), params.FindOneString("sharding", "photons"),
+                             params.FindOneString("camerasamples", "halton"));
 }
 
 }  // namespace pbrt

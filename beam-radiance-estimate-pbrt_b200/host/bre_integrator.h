@@ -27,6 +27,10 @@
 //   new: "string checkpoint" [""]  film accumulators + iterations done + radius are loaded from this file
 //        when startiteration > 0 and saved to it after the last iteration (bre_film_load / bre_film_save):
 //        a resumed render continues the SAME estimate; the reference's startiteration restores the radius only.
+//   new: "string camerasamples" ["halton"|"uniform"]  halton (default) = the reference's camera samples: pixel p of
+//        iteration i looks through p + HaltonSampler(nIterations, pixelBounds) sample i (photonbeam.cpp:341,459-466),
+//        computed per pixel on the device (bre_stage_camera_halton) or by pbrt's own sampler for host rays;
+//        uniform = one sub-pixel offset per iteration for every pixel (a regular ray grid).
 //   new: "string sharding" ["photons"|"tiles"]  several ranks (BRE_NRANKS / BRE_RANK / BRE_NCCL_ID_FILE): shard the
 //        photon paths (each rank builds and queries its own 1/N of the map, bre_film_gather sums the films; default)
 //        or the 16x16 image tiles (photons all-gathered); rank 0 writes the image either way.
@@ -62,13 +66,13 @@ class BreIntegrator : public Integrator {
                   int maxDepth, Float initialRadius, Float alpha, int writeFrequency,
                   bool renderMedia, bool deviceTracer, bool deviceCamera, bool reusePhotons, int device,
                   int startIteration = 0, int endIteration = -1, std::string checkpoint = "",
-                  std::string sharding = "photons")
+                  std::string sharding = "photons", std::string cameraSamples = "halton")
         : camera(camera), nIterations(nIterations), photonsPerIteration(photonsPerIteration),
           maxDepth(maxDepth), initialRadius(initialRadius), alpha(alpha),
           writeFrequency(writeFrequency), renderMedia(renderMedia), deviceTracer(deviceTracer),
           deviceCamera(deviceCamera), reusePhotons(reusePhotons), device(device),
           startIteration(startIteration), endIteration(endIteration < 0 ? nIterations : endIteration),
-          checkpoint(std::move(checkpoint)), sharding(std::move(sharding)) {}
+          checkpoint(std::move(checkpoint)), sharding(std::move(sharding)), cameraSamples(std::move(cameraSamples)) {}
     void Render(const Scene &scene);
 
     // test hook: after Render, photons of the last iteration in reference layout (p, alpha, wi)
@@ -93,6 +97,7 @@ class BreIntegrator : public Integrator {
     const int startIteration, endIteration;
     const std::string checkpoint;
     const std::string sharding;
+    const std::string cameraSamples;
 };
 
 Integrator *CreateBreIntegrator(const ParamSet &params, std::shared_ptr<const Camera> camera);

@@ -142,6 +142,15 @@ int bre_camera_rays(bre_ctx *ctx, float offset_x, float offset_y, float *o_xyz_t
 /* K0 + K5/K6 + K7 without any host<->device ray traffic: generate, query, accumulate into the film
  * (created with width*height pixels). */
 int bre_query_camera_to_film(bre_ctx *ctx, float offset_x, float offset_y, float n_paths_norm);
+/* The same three calls with the sample position of every pixel drawn as the reference's camera pass draws it:
+ * pixel p of iteration `sample_num` looks through p + (dimension 0, dimension 1) of HaltonSampler(nIterations,
+ * pixelBounds) after StartPixel(p), SetSampleNumber(sample_num) (integrators/photonbeam.cpp:341,459-466;
+ * samplers/halton.cpp:64-125; GetCameraSample core/sampler.cpp:46-52), computed per pixel on the device.
+ * pixelBounds = the window given to bre_set_camera.  bre_stage_camera_halton -> bre_query_camera_halton_to_film
+ * with the same sample number picks up the staged rays. */
+int bre_camera_rays_halton(bre_ctx *ctx, int64_t sample_num, float *o_xyz_tmax, float *d_xyz);
+int bre_stage_camera_halton(bre_ctx *ctx, int64_t sample_num);
+int bre_query_camera_halton_to_film(bre_ctx *ctx, int64_t sample_num, float n_paths_norm);
 
 /* ---- K1: volume photon tracing ---------------------------------------------------
  * Replaces the photon pass of PhotonBeamIntegrator::Render (integrators/photonbeam.cpp:365-437,

@@ -23,6 +23,7 @@
 #include "materials/matte.h"
 #include "media/homogeneous.h"
 #include "paramset.h"
+#include "samplers/halton.h"
 #include "parallel.h"
 #include "scene.h"
 #include "shapes/triangle.h"
@@ -95,11 +96,13 @@ int main(int argc, char **argv) {
     { std::unique_ptr<std::string[]> a(new std::string[1]); a[0] = camrays; ps.AddString("camerarays", std::move(a), 1); }
     // trailing key=value arguments: further integer / string parameters of the scene-file surface
     // (startiteration=2 enditeration=4 imagewritefrequency=1 checkpoint=/tmp/film.bin rendersurfaces=false)
+    bool uniformSamples = false;
     for (int i = 9; i < argc; ++i) {
         const char *eq = strchr(argv[i], '=');
         if (!eq) continue;
         const std::string key(argv[i], eq - argv[i]), val(eq + 1);
-        if (key == "checkpoint" || key == "sharding") { std::unique_ptr<std::string[]> a(new std::string[1]); a[0] = val; ps.AddString(key, std::move(a), 1); }
+        if (key == "camerasamples") uniformSamples = val == "uniform";
+        if (key == "checkpoint" || key == "sharding" || key == "camerasamples") { std::unique_ptr<std::string[]> a(new std::string[1]); a[0] = val; ps.AddString(key, std::move(a), 1); }
         else if (key == "rendersurfaces") { std::unique_ptr<bool[]> a(new bool[1]); a[0] = val == "true"; ps.AddBool(key, std::move(a), 1); }
         else addInt(key.c_str(), atoi(val.c_str()));
     }
@@ -109,11 +112,18 @@ int main(int argc, char **argv) {
 
     // dump what the oracle needs to evaluate the same estimate
     BreIntegrator *bi = static_cast<BreIntegrator *>(integ.get());
+    // (the rays of ITERATION 0: pixel centres with "camerasamples uniform", else sample 0 of the reference's HaltonSampler)
     std::vector<float> ro, rd;
+    HaltonSampler hsamp(1, camera->film->croppedPixelBounds);
     for (int y = 0; y < res; ++y)
         for (int x = 0; x < res; ++x) {
             CameraSample cs;
             cs.pFilm = Point2f(x + 0.5f, y + 0.5f); cs.pLens = Point2f(0.5f, 0.5f); cs.time = 0.f;
+            if (!uniformSamples) {
+                hsamp.StartPixel(Point2i(x, y));
+                hsamp.SetSampleNumber(0);
+                cs = hsamp.GetCameraSample(Point2i(x, y));
+            }
             RayDifferential ray;
             camera->GenerateRayDifferential(cs, &ray);
             SurfaceInteraction isect;

@@ -139,3 +139,53 @@ def test_triangle_api_errors(ctx, bre):
     ctx.set_triangles(P, np.zeros(0, np.uint32), np.zeros(0, np.float32))   # n_tri = 0 removes the mesh
     with pytest.raises(bre.BreError):
         ctx.trace_photons(0, 10, 3, 0.1)
+
+
+@pytest.mark.parametrize("sample", [0, 3, 1000])
+def test_camera_rays_halton_samples_bit_exact(ctx, g, oracle, sample):
+    """K0 with the reference's per-pixel Halton camera samples (bre_camera_rays_halton): bit-exact against the oracle's
+    camera rays through the oracle's Halton sample positions -- which tests/test_oracle_golden.py pins, bit for bit,
+    to the reference's HaltonSampler (tests/golden/ref_halton.npz) and PerspectiveCamera (ref_surfaces.npz)."""
+    setup_scene(ctx, g)
+    x0, y0, w, h = [int(v) for v in g["window"]]
+    ctx.set_camera(g["raster_to_camera"], g["camera_to_world"], x0, y0, w, h)
+    ro, rd = ctx.camera_rays_halton(sample)
+    offs = oracle.halton_camera_samples(x0, y0, x0 + w, y0 + h, sample)
+    oracle.set_mesh(g["mesh_P"], g["mesh_idx"], g["mesh_Kd"], g["mesh_attr"].astype(np.uint8))
+    oo, od = oracle.camera_rays_px(g["raster_to_camera"], g["camera_to_world"], x0, y0, w, h, offs)
+    assert np.array_equal(bits(ro), bits(oo))
+    assert np.array_equal(bits(rd), bits(od))
+    # not the pixel centres, and not one offset for every pixel
+    c_ro, c_rd = ctx.camera_rays(0.5, 0.5)
+    assert not np.array_equal(bits(rd), bits(c_rd))
+    assert len(np.unique(offs[:, 0])) > min(w, 16)
+
+
+def test_camera_halton_query_to_film_staged_equals_unstaged(ctx, g):
+    """bre_stage_camera_halton + bre_query_camera_halton_to_film (K0 / K6 under the photon pass) == the unstaged call
+    == bre_query_to_film fed with the rays of bre_camera_rays_halton; another sample number is not picked up."""
+    setup_scene(ctx, g)
+    x0, y0, w, h = [int(v) for v in g["window"]]
+    n_paths = 20000
+    ctx.set_camera(g["raster_to_camera"], g["camera_to_world"], x0, y0, w, h)
+    ctx.film_create(w * h)
+    ctx.stage_camera_halton(5)
+    ctx.trace_photons(0, n_paths, 6, 0.15)
+    ctx.build()
+    ctx.query_camera_halton_to_film(float(n_paths), 5)
+    a = ctx.film_mean(0)
+    ctx.film_clear()
+    ctx.query_camera_halton_to_film(float(n_paths), 5)          # nothing staged now
+    b = ctx.film_mean(0)
+    ro, rd = ctx.camera_rays_halton(5)
+    ctx.film_clear()
+    ctx.query_to_film(ro, rd, float(n_paths))
+    c = ctx.film_mean(0)
+    ctx.film_clear()
+    ctx.stage_camera_halton(5)
+    ctx.query_camera_halton_to_film(float(n_paths), 6)          # staged sample 5, asked for 6: regenerated
+    d = ctx.film_mean(0)
+    assert a.max() > 0
+    assert np.allclose(a, b, rtol=1e-5, atol=1e-9 * a.max())
+    assert np.allclose(a, c, rtol=1e-5, atol=1e-9 * a.max())
+    assert not np.allclose(a, d, rtol=1e-5, atol=1e-9 * a.max())
