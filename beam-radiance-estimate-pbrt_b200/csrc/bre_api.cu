@@ -179,7 +179,7 @@ int bre_destroy(bre_ctx *ctx) {
                    &ctx->node_lo, &ctx->node_hi, &ctx->node_range, &ctx->parent, &ctx->leaf_lo,
                    &ctx->leaf_hi, &ctx->flags, &ctx->fast, &ctx->scratch, &ctx->rays_o, &ctx->rays_d,
                    &ctx->out_rgb, &ctx->tau, &ctx->hit_counts, &ctx->hit_offsets, &ctx->hit_idx,
-                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->frames, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb, &ctx->entry, &ctx->rays_stage, &ctx->p2p_scratch, &ctx->aos, &ctx->tframes, &ctx->trays, &ctx->tile_state, &ctx->top_cut, &ctx->tile_wq, &ctx->gather, &ctx->os_scratch};
+                   &ctx->counters_d, &ctx->pix_idx, &ctx->packet_ctr, &ctx->pair_queue, &ctx->heavy, &ctx->frames, &ctx->film, &ctx->path_counts, &ctx->path_offsets, &ctx->tri, &ctx->tri_kdb, &ctx->entry, &ctx->rays_stage, &ctx->p2p_scratch, &ctx->aos, &ctx->tframes, &ctx->trays, &ctx->tjit, &ctx->tile_state, &ctx->top_cut, &ctx->tile_wq, &ctx->gather, &ctx->os_scratch};
     for (Buf *b : bufs) if (b->p) cudaFree(b->p);
     if (ctx->lights_d) cudaFree(ctx->lights_d);
     if (ctx->est_host) cudaFreeHost(ctx->est_host);

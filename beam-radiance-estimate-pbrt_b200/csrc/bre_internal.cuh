@@ -198,7 +198,7 @@ struct bre_ctx {
     bool tile_shard = false;                // bre_set_tile_sharding: this rank answers only the tiles bre_tile_owner gives it
     int k5t_blocks_per_sm = 0;              // BRE_K5T_BLOCKS: cap on resident k_traverse_tile blocks per SM
     cudaEvent_t ev_est = nullptr;           // recorded after the copy of the queue control words into est_host
-    bre::Buf tframes, trays, tile_state, top_cut, tile_wq;
+    bre::Buf tframes, trays, tjit, tile_state, top_cut, tile_wq;
     uint64_t tile_wq_items = 0, tile_wq_cap_override = 0;   // BRE_TILE_WQ_CAP (tests force the depth-first spill)
     // heavy-first packet order fed from one radiance query to the next (bre_query.cu)
     size_t heavy_half = 0;

@@ -378,10 +378,12 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
         if ((s = ensure(ctx, ctx->tframes, nT * 16 * TFRAME_V4)) != BRE_OK) return s;
         if ((s = ensure(ctx, ctx->tile_state, nT)) != BRE_OK) return s;
         if ((s = ensure(ctx, ctx->trays, nT * 256 * 16)) != BRE_OK) return s;
+        if ((s = ensure(ctx, ctx->tjit, nT * 256 * 8)) != BRE_OK) return s;
         TA.cut = (const float4 *)ctx->top_cut.p;
         TA.nCut = (ctx->top_cut.p && ctx->n_built > 1) ? 1u : 0u;      // the kernel reads the entry count from the cut's header
         TA.tframes = (float4 *)ctx->tframes.p;
         TA.trays = (float4 *)ctx->trays.p;
+        TA.tjit = (float2 *)ctx->tjit.p;
         TA.tileState = (unsigned char *)ctx->tile_state.p;
         TA.imgW = imgW; TA.imgH = imgH; TA.tilesX = tilesX; TA.tilesY = tilesY;
         // global work queue of the tile walk: 4 items per photon (frontier of a breadth-first sweep; more is
@@ -518,14 +520,20 @@ static int launch_query(bre_ctx *ctx, uint32_t n, const float4 *ro, const float4
         // the leaf kernels scan the queue; each leaves at once if K5a emitted no pair of its kind
         if (tileMode) {
             if (ctx->max_leaf <= 4) {
-                BRE_CUDA(cudaFuncSetAttribute(k_leaf_tile<MODE, COUNT, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LEAF_TILE_SMEM));
-                k_leaf_tile<MODE, COUNT, 4><<<gb, LP_WARPS * 32, LEAF_TILE_SMEM, sb>>>(A, TA.tframes, TA.trays, imgW, queue, cap, ctl, counters);
+                BRE_CUDA(cudaFuncSetAttribute(k_leaf_tile<MODE, COUNT, 4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LEAF_TILE_SMEM));
+                BRE_CUDA(cudaFuncSetAttribute(k_leaf_tile<MODE, COUNT, 4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LEAF_TILE_SMEM));
+                k_leaf_tile<MODE, COUNT, 4, false><<<gb, LP_WARPS * 32, LEAF_TILE_SMEM, sb>>>(A, TA.tframes, TA.trays, TA.tjit, imgW, queue, cap, ctl, counters);
+                k_leaf_tile<MODE, COUNT, 4, true><<<gb, LP_WARPS * 32, LEAF_TILE_SMEM, sb>>>(A, TA.tframes, TA.trays, TA.tjit, imgW, queue, cap, ctl, counters);
             } else if (ctx->max_leaf <= 8) {
-                BRE_CUDA(cudaFuncSetAttribute(k_leaf_tile<MODE, COUNT, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LEAF_TILE_SMEM));
-                k_leaf_tile<MODE, COUNT, 8><<<gb, LP_WARPS * 32, LEAF_TILE_SMEM, sb>>>(A, TA.tframes, TA.trays, imgW, queue, cap, ctl, counters);
+                BRE_CUDA(cudaFuncSetAttribute(k_leaf_tile<MODE, COUNT, 8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LEAF_TILE_SMEM));
+                BRE_CUDA(cudaFuncSetAttribute(k_leaf_tile<MODE, COUNT, 8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LEAF_TILE_SMEM));
+                k_leaf_tile<MODE, COUNT, 8, false><<<gb, LP_WARPS * 32, LEAF_TILE_SMEM, sb>>>(A, TA.tframes, TA.trays, TA.tjit, imgW, queue, cap, ctl, counters);
+                k_leaf_tile<MODE, COUNT, 8, true><<<gb, LP_WARPS * 32, LEAF_TILE_SMEM, sb>>>(A, TA.tframes, TA.trays, TA.tjit, imgW, queue, cap, ctl, counters);
             } else {
-                BRE_CUDA(cudaFuncSetAttribute(k_leaf_tile<MODE, COUNT, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LEAF_TILE_SMEM));
-                k_leaf_tile<MODE, COUNT, 16><<<gb, LP_WARPS * 32, LEAF_TILE_SMEM, sb>>>(A, TA.tframes, TA.trays, imgW, queue, cap, ctl, counters);
+                BRE_CUDA(cudaFuncSetAttribute(k_leaf_tile<MODE, COUNT, 16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LEAF_TILE_SMEM));
+                BRE_CUDA(cudaFuncSetAttribute(k_leaf_tile<MODE, COUNT, 16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)LEAF_TILE_SMEM));
+                k_leaf_tile<MODE, COUNT, 16, false><<<gb, LP_WARPS * 32, LEAF_TILE_SMEM, sb>>>(A, TA.tframes, TA.trays, TA.tjit, imgW, queue, cap, ctl, counters);
+                k_leaf_tile<MODE, COUNT, 16, true><<<gb, LP_WARPS * 32, LEAF_TILE_SMEM, sb>>>(A, TA.tframes, TA.trays, TA.tjit, imgW, queue, cap, ctl, counters);
             }
         }
         if (ctx->max_leaf <= 4) {

@@ -32,8 +32,11 @@
 // k_phi = sqrt(1 + g2 (1 + g2)), g2 = max_i (s_i^2 + t_i^2).  B - A lies in the plane spanned by
 // (v, n), so |B - A|^2 = (sp - s_i)^2 + (tp - t_i)^2.  Slack: r is widened by 2 x the spread of the
 // origins + 2^-18 x the coordinate scale (rounding of P', the dot products and the rays' own (s, t):
-// > 5x their worst case), rho by 1.5 x dev (model vs real ray) and 1e-4 relative.
-// Tiles whose rays do not fit (different origins, |dev| above two pixels, a direction more than
+// > 5x their worst case), rho by 2e-3 pixel pitches and 1e-4 relative.  Where a ray is NOT at its pixel's model
+// position (sub-pixel camera jitter: the reference's Halton camera samples) the tile setup stores its offset in pixel
+// units per pixel (tjit): the candidate rectangle grows by the tile's largest offset, the pretest uses the ray's own
+// position, so the number of exact tests per hit stays that of a regular grid.
+// Tiles whose rays do not fit (different origins, a sample more than two pixels off its pixel, a direction more than
 // 26 degrees off the tile axis, NaNs, fewer than 2 columns or rows) are flagged and their rays take
 // the per-ray walk of k_traverse in the same launch.
 #pragma once
@@ -57,6 +60,7 @@ struct TileArgs {
     uint32_t nCut;           // != 0: cut[2 * TOP_CUT].x holds the number of entries (as bits); 0: start from the root
     float4 *tframes;         // TFRAME_V4 float4 per tile
     float4 *trays;           // 256 float4 per tile: {d.xyz, tMax} of pixel (i, j) at [j * 16 + i] (tile-blocked copy of the rays)
+    float2 *tjit;            // 256 float2 per tile: where the ray of pixel (i, j) really is in the tile's pixel model, minus (i, j)
     unsigned char *tileState;
     uint32_t imgW, imgH, tilesX, tilesY;
 };
@@ -384,11 +388,16 @@ __global__ void __launch_bounds__(TT_THREADS, TW_MINB) k_tile_walk(
                 gno(d10, s10, t10, daC);
                 gno(d01, s01, t01, daC);
                 const float fi = 1.f / (float)max(twv - 1u, 1u), fj = 1.f / (float)max(thv - 1u, 1u);
-                const float As = (s10 - s00) * fi, At = (t10 - t00) * fi, Bs = (s01 - s00) * fj, Bt = (t01 - t00) * fj;
+                float As = (s10 - s00) * fi, At = (t10 - t00) * fi, Bs = (s01 - s00) * fj, Bt = (t01 - t00) * fj;
                 // ---- the tile's rays, 8 per lane: bounds, deviation from the model, coherence
                 const float BIGF = 3.0e38f;
                 float sLo = BIGF, sHi = -BIGF, tLo = BIGF, tHi = -BIGF, dev = 0.f, g2 = 0.f, tFar = 0.f, oSp = 0.f, oAbs = 0.f;
-                float bad = 0.f, oDiff = 0.f;
+                float bad = 0.f, oDiff = 0.f, jI = 0.f, jJ = 0.f, nLive = 0.f;
+                // inverse of the affine pixel model: the sample position of a ray inside its pixel (camera jitter) is taken
+                // out of the model error and stored per pixel, so that the candidate pretest of k_leaf_tile stays as sharp
+                // for jittered samples (the reference's Halton camera samples) as for a regular grid
+                const float idet0 = 1.f / (As * Bt - Bs * At);
+                const float Ni00 = Bt * idet0, Ni01 = -Bs * idet0, Ni10 = -At * idet0, Ni11 = As * idet0;
                 const unsigned ti = lane & (TILE_W - 1);
 #pragma unroll 4
                 for (unsigned k = 0; k < TILE_H / 2; ++k) {
@@ -399,13 +408,18 @@ __global__ void __launch_bounds__(TT_THREADS, TW_MINB) k_tile_walk(
                         // tile-blocked copy for k_leaf_tile: a candidate reads 16 bytes next to its row neighbours'
                         // instead of two 32-byte sectors of the image-ordered arrays
                         __stcg(T.trays + (size_t)tile * 256u + tj * 16u + ti, make_float4(d.x, d.y, d.z, o.w));
+                        float2 jit = make_float2(0.f, 0.f);
                         if (o.w > 0.f) {
+                            nLive += 1.f;
                             if (__float_as_uint(o.x) != __float_as_uint(o0.x) || __float_as_uint(o.y) != __float_as_uint(o0.y) ||
                                 __float_as_uint(o.z) != __float_as_uint(o0.z)) oDiff = 1.f;
                             float myS, myT, myDa;
                             gno(d, myS, myT, myDa);
                             const float ps = s00 + (float)ti * As + (float)tj * Bs, pt = t00 + (float)ti * At + (float)tj * Bt;
-                            const float dv = fmaxf(fabsf(myS - ps), fabsf(myT - pt));
+                            const float es = myS - ps, et = myT - pt;
+                            jit = make_float2(Ni00 * es + Ni01 * et, Ni10 * es + Ni11 * et);
+                            jI = fmaxf(jI, fabsf(jit.x)); jJ = fmaxf(jJ, fabsf(jit.y));
+                            const float dv = fmaxf(fabsf(jit.x), fabsf(jit.y));      // in pixels
                             const float gg = myS * myS + myT * myT;
                             const float os = fmaxf(fmaxf(fabsf(o.x - o0.x), fabsf(o.y - o0.y)), fabsf(o.z - o0.z));
                             sLo = fminf(sLo, myS); sHi = fmaxf(sHi, myS); tLo = fminf(tLo, myT); tHi = fmaxf(tHi, myT);
@@ -414,18 +428,68 @@ __global__ void __launch_bounds__(TT_THREADS, TW_MINB) k_tile_walk(
                             // a live ray that breaks the model (NaN anywhere, far off axis) makes the tile incoherent
                             if (!(myDa > 0.85f && dv == dv && gg == gg && os == os)) bad = 1.f;
                         } else if (!(o.w <= 0.f)) bad = 1.f;      // NaN tMax
+                        __stcg(T.tjit + (size_t)tile * 256u + tj * 16u + ti, jit);
                     }
                 }
                 sLo = warp_min(sLo); sHi = warp_max(sHi); tLo = warp_min(tLo); tHi = warp_max(tHi);
                 dev = warp_max(dev); g2 = warp_max(g2); tFar = warp_max(tFar); oSp = warp_max(oSp);
-                oAbs = warp_max(oAbs); bad = warp_max(bad); oDiff = warp_max(oDiff);
+                oAbs = warp_max(oAbs); bad = warp_max(bad); oDiff = warp_max(oDiff); jI = warp_max(jI); jJ = warp_max(jJ);
+#pragma unroll
+                for (int o2 = 16; o2 > 0; o2 >>= 1) nLive += __shfl_xor_sync(FULL, nLive, o2);
+                // ---- jittered samples: the three corner rays carry their own jitter, so the model through them is skewed by
+                // up to a pixel across the tile.  With every ray alive the least-squares affine fit over the full rectangle
+                // is closed-form (i and j are orthogonal there); the per-pixel offsets are then re-measured against it and
+                // shrink to the jitter itself (|.| <= ~0.5 pixels for samples inside their pixels).
+                if ((jI > 1e-3f || jJ > 1e-3f) && bad == 0.f && twv >= 2 && thv >= 2 && nLive == (float)(twv * thv)) {
+                    const float ib = 0.5f * (float)(twv - 1u), jb = 0.5f * (float)(thv - 1u);
+                    float S = 0.f, Tt = 0.f, Sis = 0.f, Sit = 0.f, Sjs = 0.f, Sjt = 0.f;
+                    for (unsigned k = 0; k < TILE_H / 2; ++k) {
+                        const unsigned tj = (lane >> 4) + 2 * k;
+                        if (ti < twv && tj < thv) {
+                            const float4 d = __ldcg(T.trays + (size_t)tile * 256u + tj * 16u + ti);
+                            float myS, myT, myDa;
+                            gno(d, myS, myT, myDa);
+                            const float wi2 = (float)ti - ib, wj2 = (float)tj - jb;
+                            S += myS; Tt += myT; Sis += wi2 * myS; Sit += wi2 * myT; Sjs += wj2 * myS; Sjt += wj2 * myT;
+                        }
+                    }
+#pragma unroll
+                    for (int o2 = 16; o2 > 0; o2 >>= 1) {
+                        S += __shfl_xor_sync(FULL, S, o2); Tt += __shfl_xor_sync(FULL, Tt, o2);
+                        Sis += __shfl_xor_sync(FULL, Sis, o2); Sit += __shfl_xor_sync(FULL, Sit, o2);
+                        Sjs += __shfl_xor_sync(FULL, Sjs, o2); Sjt += __shfl_xor_sync(FULL, Sjt, o2);
+                    }
+                    const float tw = (float)twv, th = (float)thv;
+                    const float Sii = th * tw * (tw * tw - 1.f) * (1.f / 12.f), Sjj = tw * th * (th * th - 1.f) * (1.f / 12.f);
+                    As = Sis / Sii; At = Sit / Sii; Bs = Sjs / Sjj; Bt = Sjt / Sjj;
+                    s00 = S / nLive - ib * As - jb * Bs;
+                    t00 = Tt / nLive - ib * At - jb * Bt;
+                    const float idet1 = 1.f / (As * Bt - Bs * At);
+                    const float R00 = Bt * idet1, R01 = -Bs * idet1, R10 = -At * idet1, R11 = As * idet1;
+                    jI = 0.f; jJ = 0.f;
+                    for (unsigned k = 0; k < TILE_H / 2; ++k) {
+                        const unsigned tj = (lane >> 4) + 2 * k;
+                        if (ti < twv && tj < thv) {
+                            const float4 d = __ldcg(T.trays + (size_t)tile * 256u + tj * 16u + ti);
+                            float myS, myT, myDa;
+                            gno(d, myS, myT, myDa);
+                            const float es = myS - (s00 + (float)ti * As + (float)tj * Bs), et = myT - (t00 + (float)ti * At + (float)tj * Bt);
+                            const float2 jit = make_float2(R00 * es + R01 * et, R10 * es + R11 * et);
+                            jI = fmaxf(jI, fabsf(jit.x)); jJ = fmaxf(jJ, fabsf(jit.y));
+                            __stcg(T.tjit + (size_t)tile * 256u + tj * 16u + ti, jit);
+                        }
+                    }
+                    jI = warp_max(jI); jJ = warp_max(jJ);
+                    dev = fmaxf(jI, jJ);       // (NaN -> the comparisons below fail -> incoherent)
+                    if (!(jI == jI && jJ == jJ)) bad = 1.f;
+                }
                 const bool dead = !(tFar > 0.f) && bad == 0.f;
                 const float M = oAbs + t.abs_max;
                 const float det = As * Bt - Bs * At;
                 const float pitch = sqrtf(fminf(As * As + At * At, Bs * Bs + Bt * Bt));
                 // (comparisons written so that a NaN anywhere makes the tile incoherent)
                 const bool coherent = !dead && bad == 0.f && twv >= 2 && thv >= 2 && wl2 > 1e-30f && g2 <= 0.25f &&
-                                      oSp <= M * 0x1p-10f && pitch > 0.f && dev <= 2.f * pitch &&
+                                      oSp <= M * 0x1p-10f && pitch > 0.f && dev <= 2.f && jI <= 2.f && jJ <= 2.f &&
                                       fabsf(det) > 1e-3f * pitch * pitch;     // (tFar may be +inf: no far cull)
                 if (!dead && !coherent) state = TS_INCOHERENT;
                 if (coherent) {
@@ -456,7 +520,7 @@ __global__ void __launch_bounds__(TT_THREADS, TW_MINB) k_tile_walk(
                     float4 fv;
                     switch (lane) {
                         case 0: fv = make_float4(o0.x, o0.y, o0.z, tFar); break;
-                        case 1: fv = make_float4(ux, uy, uz, 1.5f * dev); break;
+                        case 1: fv = make_float4(ux, uy, uz, 2e-3f * sqrtf(fmaxf(As * As + At * At, Bs * Bs + Bt * Bt))); break;   // .w: slack of rho (2e-3 pixels: rounding of the stored jitter, jitter below 1e-3 pixels is ignored)
                         case 2: fv = make_float4(vx, vy, vz, s00); break;
                         case 3: fv = make_float4(nx, ny, nz, t00); break;
                         case 4: fv = make_float4(Mi00, Mi01, Mi10, Mi11); break;
@@ -464,10 +528,11 @@ __global__ void __launch_bounds__(TT_THREADS, TW_MINB) k_tile_walk(
                         case 6: fv = make_float4(As * As + At * At, As * Bs + At * Bt, Bs * Bs + Bt * Bt,
                                                  __uint_as_float(twv | (thv << 8))); break;
                         // .y: every live ray starts at exactly o0 (a pinhole camera): candidates take the origin from the frame
-                        default: fv = make_float4(__uint_as_float(q00), oDiff == 0.f ? 1.f : 0.f, 0.f, 0.f); break;
+                        default: fv = make_float4(__uint_as_float(q00), oDiff == 0.f ? 1.f : 0.f, jI, jJ); break;   // .zw: largest |jitter| in pixels
                     }
                     float4 *fr = T.tframes + (size_t)tile * TFRAME_V4;
                     if (lane < 8) __stcg(fr + lane, fv);
+                    if (lane == 0 && (jI > 1e-3f || jJ > 1e-3f)) atomicOr(queueCtl + QC_KINDS, (unsigned)KIND_TILE_JIT);
                 }
             }
             if (lane == 0) {
@@ -594,9 +659,9 @@ __device__ __forceinline__ float3 hit_radiance_p(const LeafArgs &A, float radius
     return make_float3(wp * t0 * pw.x, wp * t1 * pw.y, wp * t2 * pw.z);
 }
 
-template <int MODE, bool COUNT, int LW>
+template <int MODE, bool COUNT, int LW, bool JIT>
 __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs A, const float4 *__restrict__ tframes,
-                                                                    const float4 *__restrict__ trays, uint32_t imgW,
+                                                                    const float4 *__restrict__ trays, const float2 *__restrict__ tjit, uint32_t imgW,
                                                                     const uint2 *__restrict__ queue,
                                                                     unsigned int queueCap,
                                                                     unsigned int *__restrict__ queueCtl,
@@ -609,7 +674,12 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt = (1u << lane) - 1u;
     const unsigned sub = lane / LW, j = lane % LW;
-    if (!(__ldg(queueCtl + QC_KINDS) & KIND_TILE)) return;
+    {
+        // JIT: some tile's rays sit off their pixels' model positions (camera jitter): this variant widens the candidate
+        // rectangles and reads the per-pixel offsets; exactly one of the two variants runs
+        const unsigned kinds = __ldg(queueCtl + QC_KINDS);
+        if (!(kinds & KIND_TILE) || ((kinds & KIND_TILE_JIT) != 0u) != JIT) return;
+    }
     const unsigned total = min(__ldg(queueCtl + QC_PAIR_TAIL), queueCap);
     const unsigned warpsTotal = gridDim.x * LP_WARPS;
     unsigned long long cTests = 0;
@@ -620,7 +690,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
         if (lane < cnt) {
             const unsigned ep = hb.e[from + lane], q = hb.q[from + lane];
             const unsigned e = ep & 255u;
-            const float3 v = hit_radiance_p(A, te.p[e].w, te.pw[e], hb.ct[from + lane], q, te.tl[e], ep >> 8,
+            const float3 v = hit_radiance_p(A, te.p[e].w, te.pw[e], hb.ct[from + lane], q, te.tl[e] & TILE_MASK, ep >> 8,
                                             hb.th[from + lane], hb.d2[from + lane]);
             atomicAdd(A.out + q, make_float4(v.x, v.y, v.z, 0.f));   // RED.E.ADD.F32x4
         }
@@ -664,11 +734,12 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                 float4 ent_p = make_float4(0.f, 0.f, 0.f, 0.f), ent_c = ent_p;
                 float ent_q12 = 0.f;
                 const float4 *ent_fr = tframes;
+                bool ent_jit = false;
                 if (on) {
                     const float4 p = __ldg(A.t.s_pos_r + firstP + j);
                     const float4 *fr = tframes + (size_t)(qx & TILE_MASK) * TFRAME_V4;
                     const float4 f0 = __ldg(fr), f1 = __ldg(fr + 1), f2 = __ldg(fr + 2), f3 = __ldg(fr + 3);
-                    const float4 f5 = __ldg(fr + 5);
+                    const float4 f5 = __ldg(fr + 5), f7 = __ldg(fr + 7);
                     const float x = p.x - f0.x, y = p.y - f0.y, z = p.z - f0.z;
                     const float dz = __fmaf_rn(z, f1.z, __fmaf_rn(y, f1.y, x * f1.x));
                     const float da = __fmaf_rn(z, f2.z, __fmaf_rn(y, f2.y, x * f2.x));
@@ -691,7 +762,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                         const float4 f4 = __ldg(fr + 4);
                         ci = __fmaf_rn(f4.y, tp, f4.x * sp);
                         cj = __fmaf_rn(f4.w, tp, f4.z * sp);
-                        const float ei = __fmaf_rn(rho, f5.x, 1e-3f), ej = __fmaf_rn(rho, f5.y, 1e-3f);
+                        const float ei = __fmaf_rn(rho, f5.x, 1e-3f) + (JIT ? f7.z : 0.f), ej = __fmaf_rn(rho, f5.y, 1e-3f) + (JIT ? f7.w : 0.f);   // + the tile's largest jitter
                         const float lo_i = fmaxf(ceilf(ci - ei), 0.f), hi_i = fminf(floorf(ci + ei), (float)(twv - 1));
                         const float lo_j = fmaxf(ceilf(cj - ej), 0.f), hi_j = fminf(floorf(cj + ej), (float)(thv - 1));
                         if (lo_i <= hi_i && lo_j <= hi_j) { i0 = (int)lo_i; i1 = (int)hi_i; j0 = (int)lo_j; j1 = (int)hi_j; }
@@ -708,6 +779,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                     ent_p = p; ent_c = make_float4(ci, cj, q11, q22); ent_q12 = q12;
                     ent_rect = (unsigned)i0 | ((unsigned)j0 << 8) | ((unsigned)(i1 - i0 + 1) << 16) | ((unsigned)(j1 - j0 + 1) << 24);
                     ent_fr = fr;
+                    ent_jit = JIT && (f7.z > 1e-3f || f7.w > 1e-3f);
                 }
                 // exclusive prefix of the candidate counts, continued over the sub-passes; entries are compacted
                 unsigned incl = count;
@@ -740,7 +812,7 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                         const float4 f7 = __ldg(fr + 7), f0o = __ldg(fr);
                         te.rb[e] = __float_as_uint(f7.x);
                         te.o[e] = make_float4(f0o.x, f0o.y, f0o.z, f7.y);
-                        te.tl[e] = qx & TILE_MASK;
+                        te.tl[e] = (qx & TILE_MASK) | (ent_jit ? 0x80000000u : 0u);      // bit 31: the tile's rays carry per-pixel jitter
                         te.rect[e] = ent_rect;
                     }
                 }
@@ -779,12 +851,20 @@ __global__ void __launch_bounds__(LP_WARPS * 32, TILE_MINB) k_leaf_tile(LeafArgs
                     const unsigned ii = k - jj * w;
                     const unsigned pi = (rect & 255u) + ii, pj = ((rect >> 8) & 255u) + jj;
                     const float4 cc = te.c[e];
-                    const float di = (float)pi - cc.x, dj = (float)pj - cc.y;
+                    // (without jitter the tile index is read by the survivors of the pretest only: the kernel is bound by
+                    // shared-memory / L1 wavefronts)
+                    unsigned tlv = JIT ? te.tl[e] : 0u;
+                    float di = (float)pi - cc.x, dj = (float)pj - cc.y;
+                    if (JIT && (tlv & 0x80000000u)) {      // where this pixel's ray really is in the pixel model
+                        const float2 jt = __ldg(tjit + (size_t)(tlv & TILE_MASK) * 256u + pj * 16u + pi);
+                        di += jt.x; dj += jt.y;
+                    }
                     const float qf = __fmaf_rn(cc.z * di, di, __fmaf_rn(2.f * te.q12[e] * di, dj, cc.w * dj * dj));
                     if (!(qf > 1.f)) {
+                        if (!JIT) tlv = te.tl[e];
                         q = te.rb[e] + pj * imgW + pi;
                         const float4 p = te.p[e];
-                        const float4 d = __ldg(trays + (size_t)te.tl[e] * 256u + pj * 16u + pi);     // {d.xyz, tMax}
+                        const float4 d = __ldg(trays + (size_t)(tlv & TILE_MASK) * 256u + pj * 16u + pi);     // {d.xyz, tMax}
                         float4 o = te.o[e];
                         if (o.w == 0.f) o = __ldg(A.ro + q);
                         RayS r;

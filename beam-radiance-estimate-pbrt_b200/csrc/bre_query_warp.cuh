@@ -67,7 +67,7 @@ constexpr unsigned HEAVY_CAP = 65536;   // heavy packets remembered per launch
 // queueCtl words (zeroed before every launch)
 enum { QC_PAIR_TAIL = 0, QC_PACKET = 1, QC_INPLACE = 2, QC_EMITTED = 3, QC_KINDS = 4, QC_RUN_THIN = 5, QC_RUN_FAT = 6,
        QC_RUN_TILE = 7, QC_NINCOH = 8, QC_WQ_HEAD = 9, QC_WQ_TAIL = 10, QC_WQ_INFLIGHT = 11, QC_TILE = 12, QC_WORDS = 16 };
-enum { KIND_THIN = 1u, KIND_FAT = 2u, KIND_TILE = 4u };   // QC_KINDS bits: which kinds of pair K5a put into the queue
+enum { KIND_THIN = 1u, KIND_FAT = 2u, KIND_TILE = 4u, KIND_TILE_JIT = 8u };   // QC_KINDS bits: which kinds of pair K5a put into the queue
 
 struct __align__(16) WarpSmem {
     int nref[WQ_NCAP];

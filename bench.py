@@ -20,7 +20,8 @@ integrators/photonbeam.cpp:345-347), film tiles gathered on rank 0.  value = ray
 `value`   = beam queries/s, whole job, inputs resident in HBM (device-timed, CUDA events).
 `e2e`     = the same step through the calls the pbrt adapter makes, host in / host out:
             bre_set_camera (the camera matrices are the step's input) -> photon pass -> build ->
-            bre_query_camera_to_film (K0 generates the rays on the device) -> bre_film_gather to a
+            bre_query_camera_halton_to_film (K0 generates the rays on the device, at the reference's Halton camera
+            samples; --camera-samples uniform: bre_query_camera_to_film) -> bre_film_gather to a
             pinned host image.  `e2e_host_rays` (N = 1): the variant that uploads 58 MB of host rays.
 `roofline`= K5 (k_tile_walk + k_leaf_tile): DRAM bytes of one launch (ncu, profiles/k5_traffic.json,
             which names the build it was captured on) / kernel time, against the measured HBM copy
@@ -310,11 +311,18 @@ def run_ours(args):
     def step_e2e():
         # the calls the pbrt adapter makes: camera in, image out
         ctx.set_camera(r2c, c2w, 0, 0, W, H, True)
+        halton = args.camera_samples == "halton" and (strong or world == 1)
         if not args.no_stage:
-            ctx.stage_camera(off[0], off[1])            # K0 + K6 under the photon pass
+            if halton:
+                ctx.stage_camera_halton(0)              # K0 (the reference's per-pixel Halton camera samples) + K6 under the photon pass
+            else:
+                ctx.stage_camera(off[0], off[1])        # one sub-pixel offset for every pixel
         photon_pass()
         ctx.build()
-        ctx.query_camera_to_film(float(n_paths), off[0], off[1])
+        if halton:
+            ctx.query_camera_halton_to_film(float(n_paths), 0)
+        else:
+            ctx.query_camera_to_film(float(n_paths), off[0], off[1])
         if sharded:
             ctx.film_gather_ptr(0, 1.0, img_pin.data_ptr() if rank == 0 else None)
         else:
@@ -431,7 +439,10 @@ def run_ours(args):
                    "leaf_pairs_per_ray": cnt["leaf_pairs"] / nq, "pair_queue_overflow": cnt["pair_queue_overflow"]},
         "e2e": {"value": e2e_value, "unit": "queries/s", "h2d_bytes_per_step": 152,
                 "d2h_bytes_per_step": int(nq * 12), "ms_per_step": ms_e2e / args.steps,
-                "api": "bre_set_camera + bre_stage_camera + photon pass + bre_build + bre_query_camera_to_film + bre_film_gather/resolve"},
+                "camera_samples": args.camera_samples,
+                "api": ("bre_set_camera + bre_stage_camera_halton + photon pass + bre_build + bre_query_camera_halton_to_film + bre_film_gather/resolve"
+                        if args.camera_samples == "halton" else
+                        "bre_set_camera + bre_stage_camera + photon pass + bre_build + bre_query_camera_to_film + bre_film_gather/resolve")},
         "gpu_launches": (ours_launches * args.steps) if ours_launches is not None else None,
         "gpu_launches_per_step": ours_launches, "gpu_launches_per_step_all": all_launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -676,6 +687,8 @@ def main():
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"])
     ap.add_argument("--leaf", type=int, default=0)
     ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"])
+    ap.add_argument("--camera-samples", default="halton", choices=["halton", "uniform"],
+                    help="e2e arm: the reference's per-pixel Halton camera samples (the adapter's default) or one offset for all pixels")
     ap.add_argument("--shard", default="photons", choices=["photons", "tiles"],
                     help="strong scaling on N > 1 GPUs: shard the photon paths (each rank builds and queries its own "
                          "1/N of the map, films summed) or the image tiles (photons replicated)")
