@@ -408,7 +408,6 @@ __global__ void __launch_bounds__(TT_THREADS, TW_MINB) k_tile_walk(
                         // tile-blocked copy for k_leaf_tile: a candidate reads 16 bytes next to its row neighbours'
                         // instead of two 32-byte sectors of the image-ordered arrays
                         __stcg(T.trays + (size_t)tile * 256u + tj * 16u + ti, make_float4(d.x, d.y, d.z, o.w));
-                        float2 jit = make_float2(0.f, 0.f);
                         if (o.w > 0.f) {
                             nLive += 1.f;
                             if (__float_as_uint(o.x) != __float_as_uint(o0.x) || __float_as_uint(o.y) != __float_as_uint(o0.y) ||
@@ -417,7 +416,7 @@ __global__ void __launch_bounds__(TT_THREADS, TW_MINB) k_tile_walk(
                             gno(d, myS, myT, myDa);
                             const float ps = s00 + (float)ti * As + (float)tj * Bs, pt = t00 + (float)ti * At + (float)tj * Bt;
                             const float es = myS - ps, et = myT - pt;
-                            jit = make_float2(Ni00 * es + Ni01 * et, Ni10 * es + Ni11 * et);
+                            const float2 jit = make_float2(Ni00 * es + Ni01 * et, Ni10 * es + Ni11 * et);
                             jI = fmaxf(jI, fabsf(jit.x)); jJ = fmaxf(jJ, fabsf(jit.y));
                             const float dv = fmaxf(fabsf(jit.x), fabsf(jit.y));      // in pixels
                             const float gg = myS * myS + myT * myT;
@@ -428,7 +427,6 @@ __global__ void __launch_bounds__(TT_THREADS, TW_MINB) k_tile_walk(
                             // a live ray that breaks the model (NaN anywhere, far off axis) makes the tile incoherent
                             if (!(myDa > 0.85f && dv == dv && gg == gg && os == os)) bad = 1.f;
                         } else if (!(o.w <= 0.f)) bad = 1.f;      // NaN tMax
-                        __stcg(T.tjit + (size_t)tile * 256u + tj * 16u + ti, jit);
                     }
                 }
                 sLo = warp_min(sLo); sHi = warp_max(sHi); tLo = warp_min(tLo); tHi = warp_max(tHi);
@@ -440,7 +438,28 @@ __global__ void __launch_bounds__(TT_THREADS, TW_MINB) k_tile_walk(
                 // up to a pixel across the tile.  With every ray alive the least-squares affine fit over the full rectangle
                 // is closed-form (i and j are orthogonal there); the per-pixel offsets are then re-measured against it and
                 // shrink to the jitter itself (|.| <= ~0.5 pixels for samples inside their pixels).
-                if ((jI > 1e-3f || jJ > 1e-3f) && bad == 0.f && twv >= 2 && thv >= 2 && nLive == (float)(twv * thv)) {
+                // (the offset table is written for jittered tiles only -- 17 MB at 1080p that a regular grid never reads and
+                // that would otherwise sit dirty in L2 while k_leaf_tile runs)
+                const bool jittered = jI > 1e-3f || jJ > 1e-3f;
+                const bool refit = jittered && bad == 0.f && twv >= 2 && thv >= 2 && nLive == (float)(twv * thv);
+                if (jittered && !refit) {
+                    // rays missing or a ragged tile: the offsets against the model through the corner rays
+                    for (unsigned k = 0; k < TILE_H / 2; ++k) {
+                        const unsigned tj = (lane >> 4) + 2 * k;
+                        if (ti < twv && tj < thv) {
+                            const float4 d = __ldcg(T.trays + (size_t)tile * 256u + tj * 16u + ti);
+                            float2 jit = make_float2(0.f, 0.f);
+                            if (d.w > 0.f) {
+                                float myS, myT, myDa;
+                                gno(d, myS, myT, myDa);
+                                const float es = myS - (s00 + (float)ti * As + (float)tj * Bs), et = myT - (t00 + (float)ti * At + (float)tj * Bt);
+                                jit = make_float2(Ni00 * es + Ni01 * et, Ni10 * es + Ni11 * et);
+                            }
+                            __stcg(T.tjit + (size_t)tile * 256u + tj * 16u + ti, jit);
+                        }
+                    }
+                }
+                if (refit) {
                     const float ib = 0.5f * (float)(twv - 1u), jb = 0.5f * (float)(thv - 1u);
                     float S = 0.f, Tt = 0.f, Sis = 0.f, Sit = 0.f, Sjs = 0.f, Sjt = 0.f;
                     for (unsigned k = 0; k < TILE_H / 2; ++k) {
