@@ -391,6 +391,18 @@ void primitives(const char *path) {
             memcpy(&out[(size_t)y * w * 3], &raw[(size_t)(h - 1 - y) * w * 3], (size_t)w * 12);
         js.ints("dims", {W, H}); js.floats("scale", {1.5f});
         js.floats("rgb_in", in); js.floats("rgb_out", out);
+        // the same accumulators after three iterations: L = Ld / (iter + 1) with iter = 2 (integrators/photonbeam.cpp:578,
+        // CoefficientSpectrum::operator/(Float) core/spectrum.h:181-188 -- a division per channel, not a reciprocal)
+        std::vector<Spectrum> img3(W * H);
+        for (int i = 0; i < W * H; ++i) img3[i] = img[i] / (2 + 1);
+        film.SetImage(img3.data());
+        film.WriteImage();
+        std::ifstream f3(tmp, std::ios::binary);
+        f3 >> magic >> w >> h >> sc; f3.get();
+        f3.read((char *)raw.data(), raw.size() * 4);
+        for (int y = 0; y < h; ++y)
+            memcpy(&out[(size_t)y * w * 3], &raw[(size_t)(h - 1 - y) * w * 3], (size_t)w * 12);
+        js.floats("rgb_out_iter2", out);
         js.end();
         remove(tmp);
     }

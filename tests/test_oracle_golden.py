@@ -228,6 +228,12 @@ def test_film_resolve_bit_exact(oracle, prim):
     assert got.shape == (w * h, 3)
     assert np.array_equal(bits(got), bits(rgb_out))
     assert (rgb_out >= 0).all() and (rgb_out[5] == 0).any()   # the negative input was clamped
+    # three iterations: L = Ld / (iter + 1) is a DIVISION per channel in the reference (core/spectrum.h:181-188); a
+    # multiplication by the rounded reciprocal of 3 differs in the last bit for some of these values
+    got3 = oracle.film_resolve(rgb_in, 2, float(prim["film/scale"][0]))
+    assert np.array_equal(bits(got3), bits(prim["film/rgb_out_iter2"].reshape(-1, 3)))
+    recip = (rgb_in * np.float32(1.0 / 3.0)).astype(np.float32)
+    assert not np.array_equal(bits(recip), bits((rgb_in / np.float32(3)).astype(np.float32)))
 
 
 # ------------------------------------------------------------------ photon deposit loop
